@@ -1,0 +1,316 @@
+"""Scene assembly that mirrors what mjlab does to a robot MJCF before compiling.
+
+Restates, against this package's `Spec`, the spec edits the reference applies:
+  * terrain body + plane geom         (src/mjlab/terrains/terrain_importer.py:154-163)
+  * entity attach with "<name>/" prefix (src/mjlab/scene/scene.py:147-152)
+  * CollisionCfg.edit_spec            (src/mjlab/utils/spec_config.py:206-237)
+  * ActuatorSetCfg.edit_spec          (src/mjlab/utils/spec_config.py:361-414)
+  * ContactSensor -> one mjSENS_CONTACT per (primary, field)
+                                      (src/mjlab/sensor/contact_sensor.py:164-190,472-533)
+  * init_state keyframe               (src/mjlab/entity/entity.py:144-166)
+and the task-level settings of Mjlab-Velocity-Flat-Unitree-G1
+(src/mjlab/tasks/velocity/velocity_env_cfg.py:53-61, config/g1/env_cfgs.py:16-43).
+
+The robot MJCF itself is read from the reference checkout when model fixtures
+are (re)generated (`tools/export_models.py`); the runtime loads the exported
+`assets/*.npz` model blobs, so nothing here needs /root/reference on the GPU box.
+"""
+from __future__ import annotations
+
+import math
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from .hostmodel import HostModel
+from .mjcf import Spec, filter_names, resolve_expr
+
+ASSET_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets")
+
+CONTACT_DATA = {"found": 0, "force": 1, "torque": 2, "dist": 3, "pos": 4, "normal": 5, "tangent": 6}
+CONTACT_REDUCE = {"none": 0, "mindist": 1, "maxforce": 2, "netforce": 3}
+
+
+@dataclass
+class CollisionCfg:
+  geom_names_expr: tuple
+  contype: object = 1
+  conaffinity: object = 1
+  condim: object = 3
+  priority: object = 0
+  friction: object = None
+  solref: object = None
+  solimp: object = None
+  disable_other_geoms: bool = True
+
+
+@dataclass
+class ActuatorCfg:
+  joint_names_expr: tuple
+  effort_limit: float
+  stiffness: float
+  damping: float
+  frictionloss: float = 0.0
+  armature: float = 0.0
+
+
+@dataclass
+class ContactMatch:
+  mode: str
+  pattern: object
+  entity: str | None = None
+
+
+@dataclass
+class ContactSensorCfg:
+  name: str
+  primary: ContactMatch
+  secondary: ContactMatch | None = None
+  fields: tuple = ("found", "force")
+  reduce: str = "maxforce"
+  num_slots: int = 1
+
+
+def _resolve(fieldval, names, default):
+  if isinstance(fieldval, dict):
+    return resolve_expr(fieldval, names, default)
+  return tuple([fieldval] * len(names))
+
+
+def apply_collision_cfg(spec: Spec, cfg: CollisionCfg) -> None:
+  names = tuple(g.name for g in spec.geoms)
+  subset = filter_names(cfg.geom_names_expr, names)
+  res = {k: _resolve(getattr(cfg, k), subset, d) for k, d in
+         (("condim", 1), ("contype", 1), ("conaffinity", 1), ("priority", 0),
+          ("friction", None), ("solref", None), ("solimp", None))}
+  for i, n in enumerate(subset):
+    g = spec.geom(n)
+    g.condim, g.contype = res["condim"][i], res["contype"][i]
+    g.conaffinity, g.priority = res["conaffinity"][i], res["priority"][i]
+    for k in ("friction", "solref", "solimp"):
+      v = res[k][i]
+      if v is not None:
+        getattr(g, k)[:len(v)] = list(v)
+  if cfg.disable_other_geoms:
+    for g in spec.geoms:
+      if g.name not in subset:
+        g.contype = g.conaffinity = 0
+
+
+def apply_actuator_cfgs(spec: Spec, cfgs) -> None:
+  jnts = [j for j in spec.joints if j.type != "free"]
+  jnames = tuple(j.name for j in jnts)
+  pairs = []
+  for c in cfgs:
+    for n in filter_names(c.joint_names_expr, jnames):
+      pairs.append((c, n))
+  pairs.sort(key=lambda p: jnames.index(p[1]))
+  for c, n in pairs:
+    j = spec.joint(n)
+    if not (j.range[0] < j.range[1]):
+      raise ValueError(f"Joint {n} must be limited for position control")
+    j.armature, j.frictionloss = c.armature, c.frictionloss
+    spec.add_actuator(name=n, joint=n, gaintype=0, biastype=1, gainprm=[c.stiffness, 0.0, 0.0],
+                      biasprm=[0.0, -c.stiffness, -c.damping], inheritrange=1.0,
+                      forcerange=[-c.effort_limit, c.effort_limit])
+
+
+def add_init_state_key(spec: Spec, pos, rot, joint_pos: dict) -> None:
+  jn = tuple(j.name for j in spec.joints if j.type != "free")
+  jp = resolve_expr(joint_pos, jn, 0.0)
+  has_free = any(j.type == "free" for j in spec.joints)
+  qpos = (list(pos) + list(rot) if has_free else []) + list(jp)
+  name2pos = dict(zip(jn, jp))
+  ctrl = [name2pos.get(a.name, 0.0) for a in spec.actuators]
+  spec.keys["init_state"] = dict(qpos=qpos, ctrl=ctrl)
+
+
+def add_contact_sensor(scene: Spec, cfg: ContactSensorCfg, entity_bodies: dict) -> None:
+  """entity_bodies: entity name -> tuple of un-prefixed body names (for regex expansion)."""
+  prim = cfg.primary
+  if prim.entity:
+    pats = (prim.pattern,) if isinstance(prim.pattern, str) else tuple(prim.pattern)
+    prim_names = filter_names_full(pats, entity_bodies[prim.entity])
+  else:
+    prim_names = (prim.pattern,) if isinstance(prim.pattern, str) else tuple(prim.pattern)
+  sec_name = None
+  if cfg.secondary is not None:
+    sec_name = cfg.secondary.pattern
+    if cfg.secondary.entity and cfg.secondary.mode != "subtree":
+      sec_name = filter_names_full((sec_name,), entity_bodies[cfg.secondary.entity])[0]
+  objt = {"geom": "geom", "body": "body", "subtree": "xbody"}
+  for p in prim_names:
+    for f in cfg.fields:
+      s = scene.add_sensor(name=f"{cfg.name}_{p}_{f}", type="contact", objtype=objt[prim.mode],
+                           objname=(f"{prim.entity}/{p}" if prim.entity else p),
+                           intprm=[1 << CONTACT_DATA[f], CONTACT_REDUCE[cfg.reduce], cfg.num_slots])
+      if sec_name is not None:
+        s.reftype = objt[cfg.secondary.mode]
+        s.refname = f"{cfg.secondary.entity}/{sec_name}" if cfg.secondary.entity else sec_name
+
+
+def filter_names_full(pats, names):
+  import re
+  out = []
+  for n in names:
+    if any(re.fullmatch(p, n) for p in pats):
+      out.append(n)
+  return tuple(out)
+
+
+# ---------------------------------------------------------------------------
+# Unitree G1 (values restated from src/mjlab/asset_zoo/robots/unitree_g1/g1_constants.py:44-283)
+# ---------------------------------------------------------------------------
+def _refl(rotor, gear):
+  return rotor[0]*(gear[1]*gear[2])**2 + rotor[1]*gear[2]**2 + rotor[2]
+
+
+G1_ARM_5020 = _refl((0.139e-4, 0.017e-4, 0.169e-4), (1, 1 + 46/18, 1 + 56/16))
+G1_ARM_7520_14 = _refl((0.489e-4, 0.098e-4, 0.533e-4), (1, 4.5, 1 + 48/22))
+G1_ARM_7520_22 = _refl((0.489e-4, 0.109e-4, 0.738e-4), (1, 4.5, 5))
+G1_ARM_4010 = _refl((0.068e-4, 0.0, 0.0), (1, 5, 5))
+_WN = 10 * 2.0 * 3.1415926535
+_ZETA = 2.0
+
+
+def _act(exprs, arm, effort, scale=1.0):
+  a = arm*scale
+  return ActuatorCfg(joint_names_expr=exprs, effort_limit=effort*scale, armature=a,
+                     stiffness=a*_WN**2, damping=2.0*_ZETA*a*_WN)
+
+
+G1_ACTUATORS = (
+  _act((".*_elbow_joint", ".*_shoulder_pitch_joint", ".*_shoulder_roll_joint",
+        ".*_shoulder_yaw_joint", ".*_wrist_roll_joint"), G1_ARM_5020, 25.0),
+  _act((".*_hip_pitch_joint", ".*_hip_yaw_joint", "waist_yaw_joint"), G1_ARM_7520_14, 88.0),
+  _act((".*_hip_roll_joint", ".*_knee_joint"), G1_ARM_7520_22, 139.0),
+  _act((".*_wrist_pitch_joint", ".*_wrist_yaw_joint"), G1_ARM_4010, 5.0),
+  _act(("waist_pitch_joint", "waist_roll_joint"), G1_ARM_5020, 25.0, 2.0),
+  _act((".*_ankle_pitch_joint", ".*_ankle_roll_joint"), G1_ARM_5020, 25.0, 2.0),
+)
+_FOOT = r"^(left|right)_foot[1-7]_collision$"
+G1_FULL_COLLISION = CollisionCfg(
+  geom_names_expr=(".*_collision",), condim={_FOOT: 3, ".*_collision": 1},
+  priority={_FOOT: 1}, friction={_FOOT: (0.6,)})
+G1_KNEES_BENT = dict(pos=(0.0, 0.0, 0.76), rot=(1.0, 0.0, 0.0, 0.0), joint_pos={
+  ".*_hip_pitch_joint": -0.312, ".*_knee_joint": 0.669, ".*_ankle_pitch_joint": -0.363,
+  ".*_elbow_joint": 0.6, "left_shoulder_roll_joint": 0.2, "left_shoulder_pitch_joint": 0.2,
+  "right_shoulder_roll_joint": -0.2, "right_shoulder_pitch_joint": 0.2})
+
+
+def g1_action_scale(joint_names) -> np.ndarray:
+  """0.25 * effort / stiffness per actuated joint (g1_constants.py:286-297)."""
+  out = np.zeros(len(joint_names))
+  for c in G1_ACTUATORS:
+    for n in filter_names(c.joint_names_expr, tuple(joint_names)):
+      out[list(joint_names).index(n)] = 0.25 * c.effort_limit / c.stiffness
+  return out
+
+
+def velocity_sim_options(spec: Spec) -> None:
+  """SIM_CFG of the velocity task (velocity_env_cfg.py:53-61) + MujocoCfg defaults (sim.py:41-62)."""
+  spec.option.update(timestep=0.005, iterations=10, ls_iterations=20, integrator="implicitfast",
+                     solver="newton", cone="pyramidal", tolerance=1e-8, ls_tolerance=0.01,
+                     impratio=1.0, gravity=[0.0, 0.0, -9.81])
+
+
+def build_robot_entity(xml_path, collision: CollisionCfg | None, actuators, init_state) -> Spec:
+  spec = Spec.from_file(xml_path)
+  if collision is not None:
+    apply_collision_cfg(spec, collision)
+  if actuators:
+    apply_actuator_cfgs(spec, actuators)
+  if init_state is not None:
+    add_init_state_key(spec, **init_state)
+  return spec
+
+
+def build_scene(entities: dict, sensors=(), plane=True, num_origin_sites=0, env_spacing=2.5) -> Spec:
+  scene = Spec()
+  if plane:
+    t = scene.worldbody.add_body(name="terrain")
+    t.add_geom(name="terrain", type="plane", size=[0.0, 0.0, 0.01])
+  for e in range(num_origin_sites):  # SURVEY.md §0 fact 10 (one site per env on the world body)
+    scene.worldbody.add_site(name=f"env_origin_{e}", pos=list(env_origins_grid(num_origin_sites, env_spacing)[e]))
+  ent_bodies = {}
+  for name, espec in entities.items():
+    ent_bodies[name] = tuple(b.name for b in espec.bodies[1:])
+    scene.attach(espec, prefix=f"{name}/")
+  for s in sensors:
+    add_contact_sensor(scene, s, ent_bodies)
+  return scene
+
+
+def env_origins_grid(num_envs: int, spacing: float) -> np.ndarray:
+  """Grid origins (src/mjlab/terrains/terrain_importer.py:225-240)."""
+  rows = math.ceil(num_envs / int(math.sqrt(num_envs)))
+  cols = math.ceil(num_envs / rows)
+  ii, jj = np.meshgrid(np.arange(rows), np.arange(cols), indexing="ij")
+  o = np.zeros((num_envs, 3))
+  o[:, 0] = -(ii.flatten()[:num_envs] - (rows - 1) / 2) * spacing
+  o[:, 1] = (jj.flatten()[:num_envs] - (cols - 1) / 2) * spacing
+  return o
+
+
+def build_g1_flat(xml_path) -> HostModel:
+  """Compiled model of Mjlab-Velocity-Flat-Unitree-G1 (one world)."""
+  robot = build_robot_entity(xml_path, G1_FULL_COLLISION, G1_ACTUATORS, G1_KNEES_BENT)
+  feet = ContactSensorCfg(
+    name="feet_ground_contact",
+    primary=ContactMatch("subtree", r"^(left_ankle_roll_link|right_ankle_roll_link)$", "robot"),
+    secondary=ContactMatch("body", "terrain"), fields=("found", "force"), reduce="netforce", num_slots=1)
+  selfc = ContactSensorCfg(
+    name="self_collision", primary=ContactMatch("subtree", "pelvis", "robot"),
+    secondary=ContactMatch("subtree", "pelvis", "robot"), fields=("found",), reduce="none", num_slots=1)
+  scene = build_scene({"robot": robot}, sensors=(feet, selfc))
+  velocity_sim_options(scene)
+  m = scene.compile()
+  m.meta = dict(task="Mjlab-Velocity-Flat-Unitree-G1", nconmax=50, njmax=300, decimation=4)
+  return m
+
+
+# ---------------------------------------------------------------------------
+# model blob (.npz) save / load
+# ---------------------------------------------------------------------------
+_OPT_KEYS = ("timestep", "integrator", "cone", "solver", "iterations", "ls_iterations", "tolerance",
+             "ls_tolerance", "impratio", "disableflags")
+
+
+def save_model(m: HostModel, path) -> None:
+  import json
+  d = {k: v for k, v in m.__dict__.items() if isinstance(v, np.ndarray)}
+  for k in ("nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nsensor", "nsensordata", "nexclude", "nmocap"):
+    d["_" + k] = np.int64(getattr(m, k))
+  meta = dict(names=m.names, keys=m.keys, opt={k: getattr(m.opt, k) for k in _OPT_KEYS},
+              gravity=list(map(float, m.opt.gravity)), meaninertia=m.stat.meaninertia,
+              meta=getattr(m, "meta", {}))
+  d["_json"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
+  np.savez_compressed(path, **d)
+
+
+def load_model(path) -> HostModel:
+  import json
+  z = np.load(path)
+  m = HostModel()
+  for k in z.files:
+    if k == "_json":
+      continue
+    if k.startswith("_"):
+      setattr(m, k[1:], int(z[k]))
+    else:
+      setattr(m, k, z[k])
+  meta = json.loads(bytes(z["_json"]).decode())
+  m.names, m.keys, m.meta = meta["names"], meta["keys"], meta["meta"]
+  for k, v in meta["opt"].items():
+    setattr(m.opt, k, v)
+  m.opt.gravity = np.array(meta["gravity"])
+  m.stat.meaninertia = meta["meaninertia"]
+  return m
+
+
+def load_asset(name: str) -> HostModel:
+  p = os.path.join(ASSET_DIR, name + ".npz")
+  if not os.path.exists(p):
+    raise FileNotFoundError(f"model blob {p} missing; regenerate with tools/export_models.py")
+  return load_model(p)

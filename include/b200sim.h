@@ -1,0 +1,266 @@
+/* b200sim.h -- C ABI of the B200-native batched rigid-body step backend.
+ *
+ * This is the drop-in boundary beneath mjlab's `Simulation`
+ * (reference: src/mjlab/sim/sim.py:97-199).  Each entry point replaces one call
+ * the reference makes into its un-vendored physics dependency `mujoco_warp`
+ * (pinned at google-deepmind/mujoco_warp @ e605c406, pyproject.toml:108):
+ *
+ *   b2s_model_create   <- mjwarp.put_model(mjm)                  sim.py:116
+ *   b2s_model_set_opt  <- model.opt.ls_parallel = ... etc.       sim.py:117-118
+ *   b2s_model_expand   <- expand_model_fields(model, nworld, f)  sim/randomization.py:20-54
+ *   b2s_data_create    <- mjwarp.put_data(mjm, mjd, nworld, nconmax, njmax)  sim.py:120-126
+ *   b2s_forward        <- mjwarp.forward(m, d)                   sim.py:146,191
+ *   b2s_step           <- mjwarp.step(m, d)                      sim.py:143,199
+ *   b2s_field          <- wp.to_torch(array) zero-copy views     sim/sim_data.py:21
+ *
+ * Conventions: plain pointers and sizes, no exceptions across the ABI, every
+ * function returns 0 on success and a negative code on failure with a message
+ * available from b2s_last_error().  `step`/`forward` never allocate, never
+ * synchronise with the host and launch only on the stream they are given, so
+ * they can be captured into a CUDA graph (sim.py:138-147).
+ *
+ * Model description: a flat struct of host arrays named after MuJoCo's MjModel
+ * fields.  Real-valued arrays are double (MjModel's mjtNum); the engine
+ * converts to fp32 at upload.  Array extents are given in the trailing comment
+ * of each member as an expression of the size members (the Python binding
+ * parses this header to build its ctypes mirror -- keep one member per line).
+ */
+#ifndef B200SIM_H_
+#define B200SIM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- enums (values follow MuJoCo's mjt* enums where those are stable) ---- */
+enum { B2S_JNT_FREE = 0, B2S_JNT_BALL = 1, B2S_JNT_SLIDE = 2, B2S_JNT_HINGE = 3 };
+enum { B2S_GEOM_PLANE = 0, B2S_GEOM_HFIELD = 1, B2S_GEOM_SPHERE = 2, B2S_GEOM_CAPSULE = 3,
+       B2S_GEOM_ELLIPSOID = 4, B2S_GEOM_CYLINDER = 5, B2S_GEOM_BOX = 6, B2S_GEOM_MESH = 7 };
+enum { B2S_INT_EULER = 0, B2S_INT_RK4 = 1, B2S_INT_IMPLICIT = 2, B2S_INT_IMPLICITFAST = 3 };
+enum { B2S_CONE_PYRAMIDAL = 0, B2S_CONE_ELLIPTIC = 1 };
+enum { B2S_SOL_PGS = 0, B2S_SOL_CG = 1, B2S_SOL_NEWTON = 2 };
+enum { B2S_OBJ_UNKNOWN = 0, B2S_OBJ_BODY = 1, B2S_OBJ_XBODY = 2, B2S_OBJ_JOINT = 3, B2S_OBJ_DOF = 4,
+       B2S_OBJ_GEOM = 5, B2S_OBJ_SITE = 6, B2S_OBJ_ACTUATOR = 19 };
+enum { B2S_BIAS_NONE = 0, B2S_BIAS_AFFINE = 1 };
+enum { B2S_GAIN_FIXED = 0, B2S_GAIN_AFFINE = 1 };
+/* sensor types: own numbering (MuJoCo's mjtSensor values moved between
+ * releases); the Python binding maps by NAME from a real MjModel. */
+enum { B2S_SENS_ACCELEROMETER = 1, B2S_SENS_VELOCIMETER = 2, B2S_SENS_GYRO = 3,
+       B2S_SENS_JOINTPOS = 9, B2S_SENS_JOINTVEL = 10, B2S_SENS_ACTUATORFRC = 15,
+       B2S_SENS_FRAMEPOS = 25, B2S_SENS_FRAMEQUAT = 26, B2S_SENS_FRAMEZAXIS = 29,
+       B2S_SENS_FRAMELINVEL = 30, B2S_SENS_FRAMEANGVEL = 31,
+       B2S_SENS_SUBTREECOM = 34, B2S_SENS_SUBTREELINVEL = 35, B2S_SENS_SUBTREEANGMOM = 36,
+       B2S_SENS_CONTACT = 42 };
+/* contact-sensor data bits (intprm[0]) and reduce modes (intprm[1]);
+ * reference: src/mjlab/sensor/contact_sensor.py:16-41,480-482 */
+enum { B2S_CON_FOUND = 1, B2S_CON_FORCE = 2, B2S_CON_TORQUE = 4, B2S_CON_DIST = 8,
+       B2S_CON_POS = 16, B2S_CON_NORMAL = 32, B2S_CON_TANGENT = 64 };
+enum { B2S_REDUCE_NONE = 0, B2S_REDUCE_MINDIST = 1, B2S_REDUCE_MAXFORCE = 2, B2S_REDUCE_NETFORCE = 3 };
+/* disable flags (subset of mjtDisableBit that this path honours) */
+enum { B2S_DSBL_CONSTRAINT = 1 << 0, B2S_DSBL_LIMIT = 1 << 3, B2S_DSBL_CONTACT = 1 << 4,
+       B2S_DSBL_PASSIVE = 1 << 5, B2S_DSBL_GRAVITY = 1 << 6, B2S_DSBL_CLAMPCTRL = 1 << 7,
+       B2S_DSBL_WARMSTART = 1 << 8, B2S_DSBL_FILTERPARENT = 1 << 9, B2S_DSBL_ACTUATION = 1 << 10,
+       B2S_DSBL_REFSAFE = 1 << 11, B2S_DSBL_EULERDAMP = 1 << 13 };
+
+/* ---- model description (host side; mirrors MjModel field names) ---- */
+typedef struct b2s_model_desc {
+  /* sizes */
+  int32_t nq;
+  int32_t nv;
+  int32_t nu;
+  int32_t na;
+  int32_t nbody;
+  int32_t njnt;
+  int32_t ngeom;
+  int32_t nsite;
+  int32_t nsensor;
+  int32_t nsensordata;
+  int32_t nexclude;
+  int32_t nmocap;
+  /* options (MjModel.opt; reference MujocoCfg.apply, sim.py:64-76) */
+  double opt_timestep;
+  double opt_gravity[3];
+  double opt_tolerance;
+  double opt_ls_tolerance;
+  double opt_impratio;
+  double opt_ls_parallel_min_step;
+  double stat_meaninertia;
+  int32_t opt_integrator;
+  int32_t opt_cone;
+  int32_t opt_solver;
+  int32_t opt_iterations;
+  int32_t opt_ls_iterations;
+  int32_t opt_disableflags;
+  int32_t opt_ls_parallel;
+  int32_t opt_contact_sensor_maxmatch;
+  /* bodies */
+  const int32_t* body_parentid;   /* nbody */
+  const int32_t* body_rootid;     /* nbody */
+  const int32_t* body_weldid;     /* nbody */
+  const int32_t* body_mocapid;    /* nbody */
+  const int32_t* body_jntnum;     /* nbody */
+  const int32_t* body_jntadr;     /* nbody */
+  const int32_t* body_dofnum;     /* nbody */
+  const int32_t* body_dofadr;     /* nbody */
+  const double* body_pos;         /* nbody*3 */
+  const double* body_quat;        /* nbody*4 */
+  const double* body_ipos;        /* nbody*3 */
+  const double* body_iquat;       /* nbody*4 */
+  const double* body_mass;        /* nbody */
+  const double* body_subtreemass; /* nbody */
+  const double* body_inertia;     /* nbody*3 */
+  const double* body_invweight0;  /* nbody*2 */
+  /* joints */
+  const int32_t* jnt_type;        /* njnt */
+  const int32_t* jnt_qposadr;     /* njnt */
+  const int32_t* jnt_dofadr;      /* njnt */
+  const int32_t* jnt_bodyid;      /* njnt */
+  const int32_t* jnt_limited;     /* njnt */
+  const double* jnt_pos;          /* njnt*3 */
+  const double* jnt_axis;         /* njnt*3 */
+  const double* jnt_stiffness;    /* njnt */
+  const double* jnt_range;        /* njnt*2 */
+  const double* jnt_margin;       /* njnt */
+  const double* jnt_solref;       /* njnt*2 */
+  const double* jnt_solimp;       /* njnt*5 */
+  const double* qpos0;            /* nq */
+  const double* qpos_spring;      /* nq */
+  /* dofs */
+  const int32_t* dof_bodyid;      /* nv */
+  const int32_t* dof_jntid;       /* nv */
+  const int32_t* dof_parentid;    /* nv */
+  const double* dof_armature;     /* nv */
+  const double* dof_damping;      /* nv */
+  const double* dof_frictionloss; /* nv */
+  const double* dof_invweight0;   /* nv */
+  /* geoms */
+  const int32_t* geom_type;       /* ngeom */
+  const int32_t* geom_bodyid;     /* ngeom */
+  const int32_t* geom_contype;    /* ngeom */
+  const int32_t* geom_conaffinity;/* ngeom */
+  const int32_t* geom_condim;     /* ngeom */
+  const int32_t* geom_priority;   /* ngeom */
+  const double* geom_size;        /* ngeom*3 */
+  const double* geom_pos;         /* ngeom*3 */
+  const double* geom_quat;        /* ngeom*4 */
+  const double* geom_friction;    /* ngeom*3 */
+  const double* geom_solmix;      /* ngeom */
+  const double* geom_solref;      /* ngeom*2 */
+  const double* geom_solimp;      /* ngeom*5 */
+  const double* geom_margin;      /* ngeom */
+  const double* geom_gap;         /* ngeom */
+  const double* geom_rbound;      /* ngeom */
+  /* sites */
+  const int32_t* site_bodyid;     /* nsite */
+  const double* site_pos;         /* nsite*3 */
+  const double* site_quat;        /* nsite*4 */
+  /* actuators (joint transmission only) */
+  const int32_t* actuator_trnid;       /* nu */
+  const int32_t* actuator_gaintype;    /* nu */
+  const int32_t* actuator_biastype;    /* nu */
+  const int32_t* actuator_ctrllimited; /* nu */
+  const int32_t* actuator_forcelimited;/* nu */
+  const double* actuator_gear;         /* nu */
+  const double* actuator_gainprm;      /* nu*3 */
+  const double* actuator_biasprm;      /* nu*3 */
+  const double* actuator_ctrlrange;    /* nu*2 */
+  const double* actuator_forcerange;   /* nu*2 */
+  /* sensors */
+  const int32_t* sensor_type;     /* nsensor */
+  const int32_t* sensor_objtype;  /* nsensor */
+  const int32_t* sensor_objid;    /* nsensor */
+  const int32_t* sensor_reftype;  /* nsensor */
+  const int32_t* sensor_refid;    /* nsensor */
+  const int32_t* sensor_intprm;   /* nsensor*3 */
+  const int32_t* sensor_dim;      /* nsensor */
+  const int32_t* sensor_adr;      /* nsensor */
+  const double* sensor_cutoff;    /* nsensor */
+  /* contact excludes (body pairs) */
+  const int32_t* exclude_body1;   /* nexclude */
+  const int32_t* exclude_body2;   /* nexclude */
+} b2s_model_desc;
+
+/* ---- initial state (host side; mirrors the MjData fields put_data reads) ---- */
+typedef struct b2s_state_desc {
+  const double* qpos;        /* nq */
+  const double* qvel;        /* nv */
+  const double* ctrl;        /* nu */
+  const double* mocap_pos;   /* nmocap*3 */
+  const double* mocap_quat;  /* nmocap*4 */
+  double time;
+} b2s_state_desc;
+
+/* ---- zero-copy field descriptor ---- */
+enum { B2S_F32 = 0, B2S_I32 = 1 };
+typedef struct b2s_field_info {
+  void* ptr;          /* device pointer */
+  int32_t dtype;      /* B2S_F32 | B2S_I32 */
+  int32_t ndim;
+  int64_t shape[4];   /* logical shape; dim 0 is nworld for Data fields */
+  int64_t stride[4];  /* in elements; stride[0] == 0 marks a broadcast (un-expanded) Model field */
+} b2s_field_info;
+
+typedef struct b2s_model b2s_model;
+typedef struct b2s_data b2s_data;
+
+/* Last error message of the calling thread ("" if none). */
+const char* b2s_last_error(void);
+/* Library/ABI version and the SM architecture the kernels were built for (100). */
+int b2s_version(void);
+int b2s_built_arch(void);
+/* Number of kernels this library has launched since load (all streams). */
+int64_t b2s_launch_count(void);
+
+/* put_model: validates (unsupported features are an error, never ignored),
+ * derives the traversal tables and uploads to `device`. */
+int b2s_model_create(const b2s_model_desc* desc, int device, b2s_model** out);
+int b2s_model_destroy(b2s_model* m);
+/* Settable options after creation (sim.py:117-118, tests/test_sim.py:71-82).
+ * Keys: "ls_parallel", "contact_sensor_maxmatch", "iterations", "ls_iterations",
+ * "tolerance", "ls_tolerance", "timestep", "impratio", "integrator", "cone",
+ * "gravity_x", "gravity_y", "gravity_z", "disableflags", "ls_parallel_min_step". */
+int b2s_model_set_opt(b2s_model* m, const char* key, double value);
+int b2s_model_get_opt(const b2s_model* m, const char* key, double* value);
+/* expand_model_fields: give `name` per-world storage (leading dim nworld).
+ * Invalidates previously captured graphs (pointers change), as in the
+ * reference (manager_based_rl_env.py:107-109 re-captures). */
+int b2s_model_expand(b2s_model* m, const char* name, int nworld);
+/* Model field view (per-world-capable fields have leading dim 1 or nworld). */
+int b2s_model_field(b2s_model* m, const char* name, b2s_field_info* out);
+int b2s_model_num_fields(const b2s_model* m);
+const char* b2s_model_field_name(const b2s_model* m, int i);
+
+/* put_data: allocate all per-world arrays and initialise every world from
+ * `init`.  nconmax = contacts per world, njmax = constraint rows per world
+ * (<= 0: heuristic). */
+int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, int nworld,
+                    int nconmax, int njmax, b2s_data** out);
+int b2s_data_destroy(b2s_data* d);
+int b2s_data_field(b2s_data* d, const char* name, b2s_field_info* out);
+int b2s_data_num_fields(const b2s_data* d);
+const char* b2s_data_field_name(const b2s_data* d, int i);
+int64_t b2s_data_bytes(const b2s_data* d);
+
+/* forward / step on `stream` (a cudaStream_t passed as void*). */
+int b2s_forward(const b2s_model* m, b2s_data* d, void* stream);
+int b2s_step(const b2s_model* m, b2s_data* d, void* stream);
+/* nsub sub-steps with ctrl held (one control decimation; manager_based_rl_env.py:114-119). */
+int b2s_step_n(const b2s_model* m, b2s_data* d, int nsub, void* stream);
+
+/* Host-buffer convenience used by the end-to-end benchmark and by FFI callers
+ * without a device allocator: copy ctrl (nworld*nu floats) from host, run nsub
+ * sub-steps, copy qpos|qvel|sensordata back.  Pinned buffers recommended. */
+int b2s_step_host(const b2s_model* m, b2s_data* d, const float* ctrl_host, int nsub,
+                  float* qpos_host, float* qvel_host, float* sensordata_host, void* stream);
+
+/* Per-stage device timing of one step (cudaEvents on `stream`, synchronises):
+ * fills up to `cap` (name, ms) pairs; returns the number of stages. */
+int b2s_profile_step(const b2s_model* m, b2s_data* d, void* stream, int reps,
+                     const char** names, float* ms, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SIM_H_ */

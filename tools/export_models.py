@@ -1,0 +1,15 @@
+"""Regenerate the compiled model blobs under asimov-mjlab_b200/assets/ from the
+reference checkout's MJCF files (run in the build container; the GPU box has no
+/root/reference).  Usage: python tools/export_models.py [/root/reference]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from asimov_mjlab_b200 import scenes  # noqa: E402
+
+ref = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
+zoo = os.path.join(ref, "src/mjlab/asset_zoo/robots")
+m = scenes.build_g1_flat(os.path.join(zoo, "unitree_g1/xmls/g1.xml"))
+scenes.save_model(m, os.path.join(scenes.ASSET_DIR, "g1_flat.npz"))
+print("g1_flat: nq", m.nq, "nv", m.nv, "nu", m.nu, "nbody", m.nbody, "ngeom", m.ngeom,
+      "nsite", m.nsite, "nsensordata", m.nsensordata, "meaninertia", m.stat.meaninertia)
