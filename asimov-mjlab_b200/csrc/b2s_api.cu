@@ -1,0 +1,558 @@
+// b2s_api.cu -- the C ABI declared in include/b200sim.h: model validation and upload (put_model),
+// per-world allocation (put_data), zero-copy field registry, and the forward/step launch sequences.
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "b2s_api.h"
+
+#define B2S_VERSION 100
+
+static thread_local std::string g_err;
+static std::atomic<long long> g_launches{0};
+void b2s_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static int fail(const std::string& msg) { g_err = msg; return -1; }
+#define CU(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+struct FieldRec {
+  std::string name;
+  int dtype, ndim;
+  long long shape[4];
+  void* ptr;                 // Data fields / fixed Model fields
+  WField<float>* wf;         // expandable Model fields (ptr lives in the ModelDev)
+  long long elems;           // per-world element count
+};
+
+struct b2s_model {
+  int device = 0;
+  ModelDev dev;
+  std::vector<void*> allocs;
+  std::vector<FieldRec> fields;
+  std::map<std::string, int> index;
+  int nexpanded = 0;
+  ~b2s_model() { for (void* p : allocs) cudaFree(p); }
+};
+struct b2s_data {
+  int device = 0;
+  DataDev dev;
+  void* arena = nullptr;
+  size_t bytes = 0;
+  std::vector<FieldRec> fields;
+  std::map<std::string, int> index;
+  cudaEvent_t ev[16];
+  bool have_ev = false;
+  ~b2s_data() { if (arena) cudaFree(arena); if (have_ev) for (auto& e : ev) cudaEventDestroy(e); }
+};
+
+extern "C" const char* b2s_last_error(void) { return g_err.c_str(); }
+extern "C" int b2s_version(void) { return B2S_VERSION; }
+extern "C" int b2s_built_arch(void) { return 100; }
+extern "C" int64_t b2s_launch_count(void) { return (int64_t)g_launches.load(); }
+
+// tile src[n] into dst[nworld][n]
+__global__ void k_tile(float* dst, const float* src, long long n, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) dst[i] = src[i % n];
+}
+__global__ void k_fill_i(int* dst, int v, long long total) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) dst[i] = v;
+}
+
+namespace {
+struct Uploader {
+  b2s_model* m;
+  bool ok = true;
+  std::string err;
+  template <typename T>
+  T* raw(const std::vector<T>& h) {
+    T* p = nullptr;
+    size_t n = h.size() ? h.size() : 1;
+    if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) { ok = false; err = "cudaMalloc failed"; return nullptr; }
+    m->allocs.push_back(p);
+    if (h.size() && cudaMemcpy(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) { ok = false; err = "cudaMemcpy failed"; }
+    return p;
+  }
+  const float* f(const double* src, long long n) {
+    std::vector<float> h((size_t)n);
+    for (long long i = 0; i < n; i++) h[(size_t)i] = (float)src[i];
+    return raw(h);
+  }
+  const int* i(const int32_t* src, long long n) {
+    std::vector<int> h(src, src + n);
+    return raw(h);
+  }
+};
+const char* geom_name(int t) {
+  static const char* n[] = {"plane", "hfield", "sphere", "capsule", "ellipsoid", "cylinder", "box", "mesh"};
+  return (t >= 0 && t < 8) ? n[t] : "?";
+}
+bool pair_supported(int t1, int t2) {
+  if (t1 == B2S_GEOM_PLANE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
+  if (t1 == B2S_GEOM_SPHERE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
+  if (t1 == B2S_GEOM_CAPSULE) return t2 == B2S_GEOM_CAPSULE;
+  return false;
+}
+void add_field(std::vector<FieldRec>& v, std::map<std::string, int>& idx, const char* name, int dtype, void* ptr, WField<float>* wf,
+               const std::vector<long long>& shape) {
+  FieldRec r;
+  r.name = name; r.dtype = dtype; r.ptr = ptr; r.wf = wf; r.ndim = (int)shape.size(); r.elems = 1;
+  int k = 0;
+  for (long long s : shape) { r.shape[k++] = s; r.elems *= s; }
+  for (; k < 4; k++) r.shape[k] = 1;
+  idx[name] = (int)v.size();
+  v.push_back(r);
+}
+}  // namespace
+
+extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model** out) {
+  if (!s || !out) return fail("null argument");
+  // ---------------------------------------------------------------- validation: unsupported features are errors
+  if (s->na > 0) return fail("stateful actuators (na > 0) are not supported");
+  if (s->nv < 1 || s->nv > B2S_MAX_NV) return fail("nv must be in [1, " + std::to_string(B2S_MAX_NV) + "]");
+  if (s->opt_cone != B2S_CONE_PYRAMIDAL) return fail("only the pyramidal friction cone is supported");
+  if (s->opt_solver != B2S_SOL_NEWTON) return fail("only the Newton solver is supported");
+  if (s->opt_integrator != B2S_INT_EULER && s->opt_integrator != B2S_INT_IMPLICITFAST) return fail("integrator must be euler or implicitfast");
+  const int nb = s->nbody, nv = s->nv;
+  for (int i = 0; i < nv; i++) if (s->dof_frictionloss[i] != 0.0) return fail("dof_frictionloss is not supported");
+  for (int j = 0; j < s->njnt; j++) {
+    if (s->jnt_type[j] < 0 || s->jnt_type[j] > 3) return fail("unknown joint type");
+    if (s->jnt_type[j] == B2S_JNT_BALL && s->jnt_limited[j]) return fail("ball joint limits are not supported");
+  }
+  for (int u = 0; u < s->nu; u++) {
+    const int j = s->actuator_trnid[u];
+    if (j < 0 || j >= s->njnt || (s->jnt_type[j] != B2S_JNT_HINGE && s->jnt_type[j] != B2S_JNT_SLIDE)) return fail("actuators must target hinge or slide joints");
+  }
+  // bodies must be in DFS pre-order (MuJoCo's compiler guarantees it)
+  std::vector<int> send(nb), ssize(nb, 1), depth(nb, 0);
+  for (int i = 0; i < nb; i++) send[i] = i + 1;
+  for (int i = nb - 1; i > 0; i--) {
+    const int p = s->body_parentid[i];
+    if (p < 0 || p >= i) return fail("bodies are not topologically ordered");
+    send[p] = send[p] > send[i] ? send[p] : send[i];
+    ssize[p] += ssize[i];
+  }
+  for (int i = 0; i < nb; i++) if (send[i] - i != ssize[i]) return fail("bodies are not in depth-first order");
+  for (int i = 1; i < nb; i++) depth[i] = depth[s->body_parentid[i]] + 1;
+  for (int k = 0; k < s->nsensor; k++) {
+    switch (s->sensor_type[k]) {
+      case B2S_SENS_ACCELEROMETER: case B2S_SENS_VELOCIMETER: case B2S_SENS_GYRO: case B2S_SENS_JOINTPOS: case B2S_SENS_JOINTVEL:
+      case B2S_SENS_ACTUATORFRC: case B2S_SENS_FRAMEPOS: case B2S_SENS_FRAMEQUAT: case B2S_SENS_FRAMEZAXIS: case B2S_SENS_FRAMELINVEL:
+      case B2S_SENS_FRAMEANGVEL: case B2S_SENS_SUBTREECOM: case B2S_SENS_SUBTREELINVEL: case B2S_SENS_SUBTREEANGMOM: case B2S_SENS_CONTACT: break;
+      default: return fail("unsupported sensor type " + std::to_string(s->sensor_type[k]));
+    }
+  }
+  // ---------------------------------------------------------------- static collision pair table
+  std::vector<int> pairs;
+  for (int ga = 0; ga < s->ngeom; ga++) for (int gb = ga + 1; gb < s->ngeom; gb++) {
+    const int b1 = s->geom_bodyid[ga], b2 = s->geom_bodyid[gb];
+    if (!((s->geom_contype[ga] & s->geom_conaffinity[gb]) || (s->geom_contype[gb] & s->geom_conaffinity[ga]))) continue;
+    const int w1 = s->body_weldid[b1], w2 = s->body_weldid[b2];
+    if (w1 == w2) continue;
+    const int wp1 = s->body_weldid[s->body_parentid[w1]], wp2 = s->body_weldid[s->body_parentid[w2]];
+    if (!(s->opt_disableflags & B2S_DSBL_FILTERPARENT) && w1 != 0 && w2 != 0 && (w1 == wp2 || w2 == wp1)) continue;
+    bool ex = false;
+    for (int e = 0; e < s->nexclude; e++) {
+      const int e1 = s->exclude_body1[e], e2 = s->exclude_body2[e];
+      if ((e1 == b1 && e2 == b2) || (e1 == b2 && e2 == b1)) ex = true;
+    }
+    if (ex) continue;
+    int g1 = ga, g2 = gb;
+    if (s->geom_type[g1] > s->geom_type[g2]) { g1 = gb; g2 = ga; }
+    if (!pair_supported(s->geom_type[g1], s->geom_type[g2]))
+      return fail(std::string("unsupported collision pair ") + geom_name(s->geom_type[g1]) + "-" + geom_name(s->geom_type[g2]) +
+                  " (geoms " + std::to_string(g1) + ", " + std::to_string(g2) + ")");
+    pairs.push_back(g1); pairs.push_back(g2);
+  }
+  // ---------------------------------------------------------------- traversal tables
+  int nlevel = 0;
+  for (int i = 0; i < nb; i++) nlevel = depth[i] + 1 > nlevel ? depth[i] + 1 : nlevel;
+  std::vector<int> level_adr(nlevel + 1, 0), level_body(nb);
+  for (int i = 0; i < nb; i++) level_adr[depth[i] + 1]++;
+  for (int l = 0; l < nlevel; l++) level_adr[l + 1] += level_adr[l];
+  { std::vector<int> fill(level_adr.begin(), level_adr.end() - 1); for (int i = 0; i < nb; i++) level_body[fill[depth[i]]++] = i; }
+  std::vector<int> chain_adr(nb + 1, 0), chain;
+  std::vector<unsigned char> dofmask((size_t)nb * nv, 0), ancmask((size_t)nb * nb, 0);
+  int maxchain = 0;
+  for (int b = 0; b < nb; b++) {
+    int bb = b;
+    while (bb > 0 && s->body_dofnum[bb] == 0) bb = s->body_parentid[bb];
+    std::vector<int> c;
+    if (bb > 0) for (int i = s->body_dofadr[bb] + s->body_dofnum[bb] - 1; i >= 0; i = s->dof_parentid[i]) c.push_back(i);
+    for (size_t k = 1; k < c.size(); k++) if (c[k] >= c[k - 1]) return fail("dof chain is not ordered");
+    for (int k = (int)c.size() - 1; k >= 0; k--) { chain.push_back(c[k]); dofmask[(size_t)b * nv + c[k]] = 1; }
+    chain_adr[b + 1] = (int)chain.size();
+    maxchain = (int)c.size() > maxchain ? (int)c.size() : maxchain;
+    for (int a = b;; a = s->body_parentid[a]) { ancmask[(size_t)b * nb + a] = 1; if (a == 0) break; }
+  }
+  // ---------------------------------------------------------------- upload
+  CU(cudaSetDevice(device));
+  b2s_model* m = new b2s_model();
+  m->device = device;
+  Uploader up{m};
+  ModelDev& d = m->dev;
+  memset(&d, 0, sizeof(d));
+  d.nq = s->nq; d.nv = nv; d.nvp = (nv + 3) & ~3; d.nu = s->nu; d.nbody = nb; d.njnt = s->njnt; d.ngeom = s->ngeom; d.nsite = s->nsite;
+  d.nsensor = s->nsensor; d.nsensordata = s->nsensordata; d.nmocap = s->nmocap;
+  d.nlevel = nlevel; d.npair = (int)pairs.size() / 2; d.maxchain = maxchain;
+  d.timestep = (float)s->opt_timestep;
+  for (int k = 0; k < 3; k++) d.gravity[k] = (float)s->opt_gravity[k];
+  d.tolerance = (float)s->opt_tolerance; d.ls_tolerance = (float)s->opt_ls_tolerance; d.impratio = (float)s->opt_impratio;
+  d.ls_parallel_min_step = (float)(s->opt_ls_parallel_min_step > 0 ? s->opt_ls_parallel_min_step : 1e-6);
+  d.meaninertia = (float)s->stat_meaninertia;
+  d.integrator = s->opt_integrator; d.cone = s->opt_cone; d.iterations = s->opt_iterations; d.ls_iterations = s->opt_ls_iterations;
+  d.disableflags = s->opt_disableflags; d.ls_parallel = s->opt_ls_parallel;
+  d.contact_sensor_maxmatch = s->opt_contact_sensor_maxmatch > 0 ? s->opt_contact_sensor_maxmatch : 64;
+  d.body_parentid = up.i(s->body_parentid, nb); d.body_rootid = up.i(s->body_rootid, nb); d.body_mocapid = up.i(s->body_mocapid, nb);
+  d.body_jntnum = up.i(s->body_jntnum, nb); d.body_jntadr = up.i(s->body_jntadr, nb);
+  d.body_dofnum = up.i(s->body_dofnum, nb); d.body_dofadr = up.i(s->body_dofadr, nb);
+  d.body_subtree_end = up.raw(send); d.body_chain_adr = up.raw(chain_adr); d.body_chain = up.raw(chain);
+  d.level_adr = up.raw(level_adr); d.level_body = up.raw(level_body);
+  d.body_dofmask = up.raw(dofmask); d.body_ancmask = up.raw(ancmask);
+  d.body_subtreemass = up.f(s->body_subtreemass, nb); d.body_invweight0 = up.f(s->body_invweight0, 2 * nb);
+  d.jnt_type = up.i(s->jnt_type, s->njnt); d.jnt_qposadr = up.i(s->jnt_qposadr, s->njnt); d.jnt_dofadr = up.i(s->jnt_dofadr, s->njnt);
+  d.jnt_bodyid = up.i(s->jnt_bodyid, s->njnt); d.jnt_limited = up.i(s->jnt_limited, s->njnt);
+  d.jnt_pos = up.f(s->jnt_pos, 3 * s->njnt); d.jnt_axis = up.f(s->jnt_axis, 3 * s->njnt); d.jnt_margin = up.f(s->jnt_margin, s->njnt);
+  d.jnt_solref = up.f(s->jnt_solref, 2 * s->njnt); d.jnt_solimp = up.f(s->jnt_solimp, 5 * s->njnt);
+  d.dof_bodyid = up.i(s->dof_bodyid, nv); d.dof_jntid = up.i(s->dof_jntid, nv); d.dof_parentid = up.i(s->dof_parentid, nv);
+  d.dof_invweight0 = up.f(s->dof_invweight0, nv);
+  d.geom_type = up.i(s->geom_type, s->ngeom); d.geom_bodyid = up.i(s->geom_bodyid, s->ngeom);
+  d.geom_condim = up.i(s->geom_condim, s->ngeom); d.geom_priority = up.i(s->geom_priority, s->ngeom);
+  d.geom_size = up.f(s->geom_size, 3 * s->ngeom); d.geom_solmix = up.f(s->geom_solmix, s->ngeom);
+  d.geom_solref = up.f(s->geom_solref, 2 * s->ngeom); d.geom_solimp = up.f(s->geom_solimp, 5 * s->ngeom);
+  d.geom_margin = up.f(s->geom_margin, s->ngeom); d.geom_gap = up.f(s->geom_gap, s->ngeom); d.geom_rbound = up.f(s->geom_rbound, s->ngeom);
+  d.pair_geom = up.raw(pairs);
+  d.site_bodyid = up.i(s->site_bodyid, s->nsite);
+  d.actuator_trnid = up.i(s->actuator_trnid, s->nu); d.actuator_gaintype = up.i(s->actuator_gaintype, s->nu);
+  d.actuator_biastype = up.i(s->actuator_biastype, s->nu); d.actuator_ctrllimited = up.i(s->actuator_ctrllimited, s->nu);
+  d.actuator_forcelimited = up.i(s->actuator_forcelimited, s->nu); d.actuator_gear = up.f(s->actuator_gear, s->nu);
+  d.actuator_ctrlrange = up.f(s->actuator_ctrlrange, 2 * s->nu); d.actuator_forcerange = up.f(s->actuator_forcerange, 2 * s->nu);
+  d.sensor_type = up.i(s->sensor_type, s->nsensor); d.sensor_objtype = up.i(s->sensor_objtype, s->nsensor);
+  d.sensor_objid = up.i(s->sensor_objid, s->nsensor); d.sensor_reftype = up.i(s->sensor_reftype, s->nsensor);
+  d.sensor_refid = up.i(s->sensor_refid, s->nsensor); d.sensor_intprm = up.i(s->sensor_intprm, 3 * s->nsensor);
+  d.sensor_dim = up.i(s->sensor_dim, s->nsensor); d.sensor_adr = up.i(s->sensor_adr, s->nsensor); d.sensor_cutoff = up.f(s->sensor_cutoff, s->nsensor);
+  for (int k = 0; k < s->nsensor; k++)
+    if (s->sensor_type[k] == B2S_SENS_SUBTREELINVEL || s->sensor_type[k] == B2S_SENS_SUBTREEANGMOM) d.need_subtreevel = 1;
+  // expandable (per-world capable) fields: leading dim 1 with world stride 0 until b2s_model_expand
+  std::vector<double> rgba((size_t)4 * s->ngeom, 0.5);
+  for (int g = 0; g < s->ngeom; g++) rgba[4 * g + 3] = 1.0;
+  struct { const char* name; WField<float>* wf; const double* src; std::vector<long long> shape; } ex[] = {
+    {"body_pos", &d.body_pos, s->body_pos, {nb, 3}}, {"body_quat", &d.body_quat, s->body_quat, {nb, 4}},
+    {"body_ipos", &d.body_ipos, s->body_ipos, {nb, 3}}, {"body_iquat", &d.body_iquat, s->body_iquat, {nb, 4}},
+    {"body_mass", &d.body_mass, s->body_mass, {nb}}, {"body_inertia", &d.body_inertia, s->body_inertia, {nb, 3}},
+    {"jnt_range", &d.jnt_range, s->jnt_range, {s->njnt, 2}}, {"jnt_stiffness", &d.jnt_stiffness, s->jnt_stiffness, {s->njnt}},
+    {"qpos0", &d.qpos0, s->qpos0, {s->nq}}, {"qpos_spring", &d.qpos_spring, s->qpos_spring, {s->nq}},
+    {"dof_armature", &d.dof_armature, s->dof_armature, {nv}}, {"dof_damping", &d.dof_damping, s->dof_damping, {nv}},
+    {"dof_frictionloss", &d.dof_frictionloss, s->dof_frictionloss, {nv}},
+    {"geom_pos", &d.geom_pos, s->geom_pos, {s->ngeom, 3}}, {"geom_quat", &d.geom_quat, s->geom_quat, {s->ngeom, 4}},
+    {"geom_friction", &d.geom_friction, s->geom_friction, {s->ngeom, 3}}, {"geom_rgba", &d.geom_rgba, rgba.data(), {s->ngeom, 4}},
+    {"site_pos", &d.site_pos, s->site_pos, {s->nsite, 3}}, {"site_quat", &d.site_quat, s->site_quat, {s->nsite, 4}},
+    {"actuator_gainprm", &d.actuator_gainprm, s->actuator_gainprm, {s->nu, 3}},
+    {"actuator_biasprm", &d.actuator_biasprm, s->actuator_biasprm, {s->nu, 3}},
+  };
+  for (auto& e : ex) {
+    long long n = 1;
+    for (long long v : e.shape) n *= v;
+    e.wf->ptr = up.f(e.src, n); e.wf->wstride = 0;
+    add_field(m->fields, m->index, e.name, B2S_F32, nullptr, e.wf, e.shape);
+  }
+  add_field(m->fields, m->index, "geom_bodyid", B2S_I32, (void*)d.geom_bodyid, nullptr, {s->ngeom});
+  add_field(m->fields, m->index, "site_bodyid", B2S_I32, (void*)d.site_bodyid, nullptr, {s->nsite});
+  add_field(m->fields, m->index, "body_parentid", B2S_I32, (void*)d.body_parentid, nullptr, {nb});
+  add_field(m->fields, m->index, "body_rootid", B2S_I32, (void*)d.body_rootid, nullptr, {nb});
+  add_field(m->fields, m->index, "jnt_qposadr", B2S_I32, (void*)d.jnt_qposadr, nullptr, {s->njnt});
+  add_field(m->fields, m->index, "jnt_dofadr", B2S_I32, (void*)d.jnt_dofadr, nullptr, {s->njnt});
+  add_field(m->fields, m->index, "geom_type", B2S_I32, (void*)d.geom_type, nullptr, {s->ngeom});
+  add_field(m->fields, m->index, "geom_size", B2S_F32, (void*)d.geom_size, nullptr, {s->ngeom, 3});
+  add_field(m->fields, m->index, "body_subtreemass", B2S_F32, (void*)d.body_subtreemass, nullptr, {nb});
+  add_field(m->fields, m->index, "dof_invweight0", B2S_F32, (void*)d.dof_invweight0, nullptr, {nv});
+  add_field(m->fields, m->index, "body_invweight0", B2S_F32, (void*)d.body_invweight0, nullptr, {nb, 2});
+  add_field(m->fields, m->index, "pair_geom", B2S_I32, (void*)d.pair_geom, nullptr, {d.npair, 2});
+  if (!up.ok) { std::string e = up.err; delete m; return fail(e); }
+  *out = m;
+  return 0;
+}
+
+extern "C" int b2s_model_destroy(b2s_model* m) { delete m; return 0; }
+
+extern "C" int b2s_model_set_opt(b2s_model* m, const char* key, double v) {
+  if (!m || !key) return fail("null argument");
+  ModelDev& d = m->dev;
+  const std::string k(key);
+  if (k == "ls_parallel") d.ls_parallel = v != 0;
+  else if (k == "contact_sensor_maxmatch") d.contact_sensor_maxmatch = (int)v;
+  else if (k == "iterations") d.iterations = (int)v;
+  else if (k == "ls_iterations") d.ls_iterations = (int)v;
+  else if (k == "tolerance") d.tolerance = (float)v;
+  else if (k == "ls_tolerance") d.ls_tolerance = (float)v;
+  else if (k == "timestep") d.timestep = (float)v;
+  else if (k == "impratio") d.impratio = (float)v;
+  else if (k == "ls_parallel_min_step") d.ls_parallel_min_step = (float)v;
+  else if (k == "gravity_x") d.gravity[0] = (float)v;
+  else if (k == "gravity_y") d.gravity[1] = (float)v;
+  else if (k == "gravity_z") d.gravity[2] = (float)v;
+  else if (k == "disableflags") d.disableflags = (int)v;
+  else if (k == "integrator") {
+    if ((int)v != B2S_INT_EULER && (int)v != B2S_INT_IMPLICITFAST) return fail("integrator must be euler or implicitfast");
+    d.integrator = (int)v;
+  } else if (k == "cone") {
+    if ((int)v != B2S_CONE_PYRAMIDAL) return fail("only the pyramidal friction cone is supported");
+  } else return fail("unknown option " + k);
+  return 0;
+}
+extern "C" int b2s_model_get_opt(const b2s_model* m, const char* key, double* v) {
+  if (!m || !key || !v) return fail("null argument");
+  const ModelDev& d = m->dev;
+  const std::string k(key);
+  if (k == "ls_parallel") *v = d.ls_parallel;
+  else if (k == "contact_sensor_maxmatch") *v = d.contact_sensor_maxmatch;
+  else if (k == "iterations") *v = d.iterations;
+  else if (k == "ls_iterations") *v = d.ls_iterations;
+  else if (k == "tolerance") *v = d.tolerance;
+  else if (k == "ls_tolerance") *v = d.ls_tolerance;
+  else if (k == "timestep") *v = d.timestep;
+  else if (k == "impratio") *v = d.impratio;
+  else if (k == "ls_parallel_min_step") *v = d.ls_parallel_min_step;
+  else if (k == "gravity_x") *v = d.gravity[0];
+  else if (k == "gravity_y") *v = d.gravity[1];
+  else if (k == "gravity_z") *v = d.gravity[2];
+  else if (k == "disableflags") *v = d.disableflags;
+  else if (k == "integrator") *v = d.integrator;
+  else if (k == "cone") *v = d.cone;
+  else if (k == "npair") *v = d.npair;
+  else if (k == "nvp") *v = d.nvp;
+  else return fail("unknown option " + k);
+  return 0;
+}
+
+extern "C" int b2s_model_expand(b2s_model* m, const char* name, int nworld) {
+  if (!m || !name) return fail("null argument");
+  auto it = m->index.find(name);
+  if (it == m->index.end()) return fail(std::string("unknown model field ") + name);
+  FieldRec& r = m->fields[it->second];
+  if (!r.wf) return fail(std::string("model field ") + name + " cannot vary per world");
+  if (r.wf->wstride != 0) return 0;   // already expanded
+  if (r.elems == 0) return 0;
+  CU(cudaSetDevice(m->device));
+  float* p = nullptr;
+  CU(cudaMalloc(&p, (size_t)nworld * r.elems * sizeof(float)));
+  m->allocs.push_back(p);
+  const long long total = (long long)nworld * r.elems;
+  k_tile<<<(int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256), 256>>>(p, r.wf->ptr, r.elems, total);
+  b2s_count_launch();
+  CU(cudaDeviceSynchronize());
+  r.wf->ptr = p; r.wf->wstride = (int)r.elems;
+  m->nexpanded++;
+  return 0;
+}
+
+static void fill_info(const FieldRec& r, long long lead, bool broadcast, void* ptr, b2s_field_info* o) {
+  o->ptr = ptr; o->dtype = r.dtype; o->ndim = r.ndim + 1;
+  o->shape[0] = lead;
+  for (int k = 0; k < r.ndim; k++) o->shape[k + 1] = r.shape[k];
+  for (int k = r.ndim + 1; k < 4; k++) o->shape[k] = 1;
+  long long st = 1;
+  for (int k = o->ndim - 1; k >= 1; k--) { o->stride[k] = st; st *= o->shape[k]; }
+  for (int k = o->ndim; k < 4; k++) o->stride[k] = 1;
+  o->stride[0] = broadcast ? 0 : st;
+}
+extern "C" int b2s_model_field(b2s_model* m, const char* name, b2s_field_info* out) {
+  if (!m || !name || !out) return fail("null argument");
+  auto it = m->index.find(name);
+  if (it == m->index.end()) return fail(std::string("unknown model field ") + name);
+  const FieldRec& r = m->fields[it->second];
+  if (r.wf) {
+    const bool ex = r.wf->wstride != 0;
+    fill_info(r, ex ? -1 : 1, !ex, (void*)r.wf->ptr, out);   // shape[0] = -1: caller substitutes nworld
+  } else {
+    out->ptr = r.ptr; out->dtype = r.dtype; out->ndim = r.ndim;
+    long long st = 1;
+    for (int k = 0; k < 4; k++) out->shape[k] = r.shape[k];
+    for (int k = r.ndim - 1; k >= 0; k--) { out->stride[k] = st; st *= r.shape[k]; }
+    for (int k = r.ndim; k < 4; k++) out->stride[k] = 1;
+  }
+  return 0;
+}
+extern "C" int b2s_model_num_fields(const b2s_model* m) { return m ? (int)m->fields.size() : 0; }
+extern "C" const char* b2s_model_field_name(const b2s_model* m, int i) {
+  return (m && i >= 0 && i < (int)m->fields.size()) ? m->fields[i].name.c_str() : nullptr;
+}
+
+// ------------------------------------------------------------------------------------------------ put_data
+extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, int nworld, int nconmax, int njmax, b2s_data** out) {
+  if (!m || !init || !out) return fail("null argument");
+  if (nworld < 1) return fail("nworld must be positive");
+  const ModelDev& md = m->dev;
+  if (nconmax <= 0) nconmax = 64;
+  if (njmax <= 0) njmax = 4 * nconmax + 2 * md.njnt;
+  CU(cudaSetDevice(m->device));
+  b2s_data* D = new b2s_data();
+  D->device = m->device;
+  DataDev& d = D->dev;
+  memset(&d, 0, sizeof(d));
+  d.nworld = nworld; d.nconmax = nconmax; d.njmax = njmax;
+  const long long W = nworld, nb = md.nbody, nv = md.nv, nvp = md.nvp;
+  struct Slot { const char* name; int dtype; void** dst; std::vector<long long> shape; };
+  std::vector<Slot> slots = {
+    {"qpos", B2S_F32, (void**)&d.qpos, {md.nq}}, {"qvel", B2S_F32, (void**)&d.qvel, {nv}}, {"ctrl", B2S_F32, (void**)&d.ctrl, {md.nu}},
+    {"qacc_warmstart", B2S_F32, (void**)&d.qacc_warmstart, {nv}}, {"time", B2S_F32, (void**)&d.time, {}},
+    {"xfrc_applied", B2S_F32, (void**)&d.xfrc_applied, {nb, 6}}, {"qfrc_applied", B2S_F32, (void**)&d.qfrc_applied, {nv}},
+    {"mocap_pos", B2S_F32, (void**)&d.mocap_pos, {md.nmocap, 3}}, {"mocap_quat", B2S_F32, (void**)&d.mocap_quat, {md.nmocap, 4}},
+    {"xpos", B2S_F32, (void**)&d.xpos, {nb, 3}}, {"xquat", B2S_F32, (void**)&d.xquat, {nb, 4}}, {"xmat", B2S_F32, (void**)&d.xmat, {nb, 3, 3}},
+    {"xipos", B2S_F32, (void**)&d.xipos, {nb, 3}}, {"ximat", B2S_F32, (void**)&d.ximat, {nb, 3, 3}},
+    {"xanchor", B2S_F32, (void**)&d.xanchor, {md.njnt, 3}}, {"xaxis", B2S_F32, (void**)&d.xaxis, {md.njnt, 3}},
+    {"geom_xpos", B2S_F32, (void**)&d.geom_xpos, {md.ngeom, 3}}, {"geom_xmat", B2S_F32, (void**)&d.geom_xmat, {md.ngeom, 3, 3}},
+    {"site_xpos", B2S_F32, (void**)&d.site_xpos, {md.nsite, 3}}, {"site_xmat", B2S_F32, (void**)&d.site_xmat, {md.nsite, 3, 3}},
+    {"subtree_com", B2S_F32, (void**)&d.subtree_com, {nb, 3}}, {"cinert", B2S_F32, (void**)&d.cinert, {nb, 10}}, {"cdof", B2S_F32, (void**)&d.cdof, {nv, 6}},
+    {"cvel", B2S_F32, (void**)&d.cvel, {nb, 6}}, {"cdof_dot", B2S_F32, (void**)&d.cdof_dot, {nv, 6}}, {"qM", B2S_F32, (void**)&d.qM, {nv, nvp}},
+    {"qfrc_bias", B2S_F32, (void**)&d.qfrc_bias, {nv}}, {"qfrc_passive", B2S_F32, (void**)&d.qfrc_passive, {nv}},
+    {"actuator_length", B2S_F32, (void**)&d.actuator_length, {md.nu}}, {"actuator_velocity", B2S_F32, (void**)&d.actuator_velocity, {md.nu}},
+    {"actuator_force", B2S_F32, (void**)&d.actuator_force, {md.nu}}, {"qfrc_actuator", B2S_F32, (void**)&d.qfrc_actuator, {nv}},
+    {"qfrc_smooth", B2S_F32, (void**)&d.qfrc_smooth, {nv}}, {"qacc_smooth", B2S_F32, (void**)&d.qacc_smooth, {nv}},
+    {"ncon", B2S_I32, (void**)&d.ncon, {}}, {"contact_dim", B2S_I32, (void**)&d.con_dim, {nconmax}}, {"contact_geom", B2S_I32, (void**)&d.con_geom, {nconmax, 2}},
+    {"contact_efc_address", B2S_I32, (void**)&d.con_efc_address, {nconmax}}, {"contact_dist", B2S_F32, (void**)&d.con_dist, {nconmax}},
+    {"contact_pos", B2S_F32, (void**)&d.con_pos, {nconmax, 3}}, {"contact_frame", B2S_F32, (void**)&d.con_frame, {nconmax, 3, 3}},
+    {"contact_includemargin", B2S_F32, (void**)&d.con_includemargin, {nconmax}}, {"contact_friction", B2S_F32, (void**)&d.con_friction, {nconmax, 5}},
+    {"contact_solref", B2S_F32, (void**)&d.con_solref, {nconmax, 2}}, {"contact_solimp", B2S_F32, (void**)&d.con_solimp, {nconmax, 5}},
+    {"nefc", B2S_I32, (void**)&d.nefc, {}}, {"nl", B2S_I32, (void**)&d.nl, {}}, {"efc_type", B2S_I32, (void**)&d.efc_type, {njmax}}, {"efc_id", B2S_I32, (void**)&d.efc_id, {njmax}},
+    {"efc_J", B2S_F32, (void**)&d.efc_J, {njmax, nvp}}, {"efc_pos", B2S_F32, (void**)&d.efc_pos, {njmax}}, {"efc_margin", B2S_F32, (void**)&d.efc_margin, {njmax}},
+    {"efc_D", B2S_F32, (void**)&d.efc_D, {njmax}}, {"efc_vel", B2S_F32, (void**)&d.efc_vel, {njmax}}, {"efc_aref", B2S_F32, (void**)&d.efc_aref, {njmax}},
+    {"efc_force", B2S_F32, (void**)&d.efc_force, {njmax}},
+    {"qacc", B2S_F32, (void**)&d.qacc, {nv}}, {"qfrc_constraint", B2S_F32, (void**)&d.qfrc_constraint, {nv}},
+    {"solver_cost", B2S_F32, (void**)&d.solver_cost, {}}, {"solver_niter", B2S_I32, (void**)&d.solver_niter, {}},
+    {"cacc", B2S_F32, (void**)&d.cacc, {nb, 6}}, {"subtree_linvel", B2S_F32, (void**)&d.subtree_linvel, {nb, 3}},
+    {"subtree_angmom", B2S_F32, (void**)&d.subtree_angmom, {nb, 3}}, {"sensordata", B2S_F32, (void**)&d.sensordata, {md.nsensordata}},
+  };
+  // one arena; every field starts on a 256-byte boundary
+  size_t total = 0;
+  std::vector<size_t> offs;
+  for (auto& s : slots) {
+    long long n = 1;
+    for (long long v : s.shape) n *= v;
+    offs.push_back(total);
+    size_t bytes = (size_t)(W * n) * 4;
+    if (bytes == 0) bytes = 4;
+    total += (bytes + 255) & ~(size_t)255;
+  }
+  if (cudaMalloc(&D->arena, total) != cudaSuccess) { delete D; return fail("cudaMalloc of the data arena failed (" + std::to_string(total >> 20) + " MiB)"); }
+  D->bytes = total;
+  cudaMemset(D->arena, 0, total);
+  for (size_t i = 0; i < slots.size(); i++) {
+    *slots[i].dst = (char*)D->arena + offs[i];
+    add_field(D->fields, D->index, slots[i].name, slots[i].dtype, *slots[i].dst, nullptr, slots[i].shape);
+  }
+  // initial state, broadcast to every world
+  auto bcast = [&](float* dst, const double* src, long long n) -> int {
+    if (n == 0) return 0;
+    std::vector<float> h((size_t)n);
+    for (long long i = 0; i < n; i++) h[(size_t)i] = (float)src[i];
+    float* tmp = nullptr;
+    if (cudaMalloc(&tmp, (size_t)n * 4) != cudaSuccess) return -1;
+    cudaMemcpy(tmp, h.data(), (size_t)n * 4, cudaMemcpyHostToDevice);
+    const long long tot = W * n;
+    k_tile<<<(int)((tot + 255) / 256 > 4096 ? 4096 : (tot + 255) / 256), 256>>>(dst, tmp, n, tot);
+    b2s_count_launch();
+    cudaDeviceSynchronize();
+    cudaFree(tmp);
+    return 0;
+  };
+  int rc = bcast(d.qpos, init->qpos, md.nq) | bcast(d.qvel, init->qvel, nv) | bcast(d.ctrl, init->ctrl, md.nu) |
+           bcast(d.mocap_pos, init->mocap_pos, 3LL * md.nmocap) | bcast(d.mocap_quat, init->mocap_quat, 4LL * md.nmocap);
+  double t = init->time;
+  rc |= bcast(d.time, &t, 1);
+  if (rc || cudaGetLastError() != cudaSuccess) { delete D; return fail("initialising the data arena failed"); }
+  // raise the dynamic shared-memory limit of every stage once
+  struct { const void* fn; size_t smem; } st[] = {
+    {fn_position(), smem_position(md)}, {fn_dynamics(), smem_dynamics(md)}, {fn_collision(), smem_collision(md)},
+    {fn_constraint(), smem_constraint(md)}, {fn_solve(md), smem_solve(md, d)}, {fn_sensors(), smem_sensors(md)},
+    {fn_integrate(), smem_integrate(md)}};
+  for (auto& e : st) {
+    if (e.smem > 227 * 1024) { delete D; return fail("model too large for the shared-memory working set (" + std::to_string(e.smem) + " B per CTA)"); }
+    if (cudaFuncSetAttribute(e.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e.smem) != cudaSuccess) {
+      cudaGetLastError();
+      if (e.smem > 48 * 1024) { delete D; return fail("cannot raise the dynamic shared-memory limit"); }
+    }
+  }
+  for (auto& e : D->ev) cudaEventCreate(&e);
+  D->have_ev = true;
+  *out = D;
+  return 0;
+}
+extern "C" int b2s_data_destroy(b2s_data* d) { delete d; return 0; }
+extern "C" int b2s_data_field(b2s_data* d, const char* name, b2s_field_info* out) {
+  if (!d || !name || !out) return fail("null argument");
+  auto it = d->index.find(name);
+  if (it == d->index.end()) return fail(std::string("unknown data field ") + name);
+  fill_info(d->fields[it->second], d->dev.nworld, false, d->fields[it->second].ptr, out);
+  return 0;
+}
+extern "C" int b2s_data_num_fields(const b2s_data* d) { return d ? (int)d->fields.size() : 0; }
+extern "C" const char* b2s_data_field_name(const b2s_data* d, int i) {
+  return (d && i >= 0 && i < (int)d->fields.size()) ? d->fields[i].name.c_str() : nullptr;
+}
+extern "C" int64_t b2s_data_bytes(const b2s_data* d) { return d ? (int64_t)d->bytes : 0; }
+
+// ------------------------------------------------------------------------------------------ forward / step
+static void run_forward(const ModelDev& m, const DataDev& d, cudaStream_t st) {
+  launch_position(m, d, st);
+  launch_dynamics(m, d, st);
+  launch_collision(m, d, st);
+  launch_constraint(m, d, st);
+  launch_solve(m, d, st);
+  launch_sensors(m, d, st);
+}
+extern "C" int b2s_forward(const b2s_model* m, b2s_data* d, void* stream) {
+  if (!m || !d) return fail("null argument");
+  run_forward(m->dev, d->dev, (cudaStream_t)stream);
+  return 0;
+}
+extern "C" int b2s_step_n(const b2s_model* m, b2s_data* d, int nsub, void* stream) {
+  if (!m || !d) return fail("null argument");
+  for (int i = 0; i < nsub; i++) {
+    run_forward(m->dev, d->dev, (cudaStream_t)stream);
+    launch_integrate(m->dev, d->dev, (cudaStream_t)stream);
+  }
+  return 0;
+}
+extern "C" int b2s_step(const b2s_model* m, b2s_data* d, void* stream) { return b2s_step_n(m, d, 1, stream); }
+
+extern "C" int b2s_step_host(const b2s_model* m, b2s_data* d, const float* ctrl_host, int nsub, float* qpos_host, float* qvel_host,
+                             float* sensordata_host, void* stream) {
+  if (!m || !d) return fail("null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  const ModelDev& md = m->dev;
+  const size_t W = (size_t)d->dev.nworld;
+  CU(cudaSetDevice(m->device));
+  if (ctrl_host && md.nu) CU(cudaMemcpyAsync(d->dev.ctrl, ctrl_host, W * md.nu * 4, cudaMemcpyHostToDevice, st));
+  b2s_step_n(m, d, nsub, stream);
+  if (qpos_host) CU(cudaMemcpyAsync(qpos_host, d->dev.qpos, W * md.nq * 4, cudaMemcpyDeviceToHost, st));
+  if (qvel_host) CU(cudaMemcpyAsync(qvel_host, d->dev.qvel, W * md.nv * 4, cudaMemcpyDeviceToHost, st));
+  if (sensordata_host && md.nsensordata) CU(cudaMemcpyAsync(sensordata_host, d->dev.sensordata, W * md.nsensordata * 4, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" int b2s_profile_step(const b2s_model* m, b2s_data* d, void* stream, int reps, const char** names, float* ms, int cap) {
+  if (!m || !d) return fail("null argument");
+  static const char* nm[] = {"position", "dynamics", "collision", "constraint", "solve", "sensors", "integrate"};
+  typedef void (*fnT)(const ModelDev&, const DataDev&, cudaStream_t);
+  fnT fn[] = {launch_position, launch_dynamics, launch_collision, launch_constraint, launch_solve, launch_sensors, launch_integrate};
+  cudaStream_t st = (cudaStream_t)stream;
+  float acc[7] = {0, 0, 0, 0, 0, 0, 0};
+  for (int r = 0; r < reps; r++) {
+    cudaEventRecord(d->ev[0], st);
+    for (int k = 0; k < 7; k++) { fn[k](m->dev, d->dev, st); cudaEventRecord(d->ev[k + 1], st); }
+    CU(cudaStreamSynchronize(st));
+    for (int k = 0; k < 7; k++) { float t = 0; cudaEventElapsedTime(&t, d->ev[k], d->ev[k + 1]); acc[k] += t; }
+  }
+  int n = cap < 7 ? cap : 7;
+  for (int k = 0; k < n; k++) { names[k] = nm[k]; ms[k] = acc[k] / (reps > 0 ? reps : 1); }
+  return n;
+}

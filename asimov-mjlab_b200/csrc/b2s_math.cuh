@@ -1,0 +1,188 @@
+// b2s_math.cuh -- small fp32 device math used by every stage kernel.
+#pragma once
+#include <cuda_runtime.h>
+#include "b2s_types.h"
+
+#define FULL 0xffffffffu
+#define DEV __device__ __forceinline__
+
+struct v3 { float x, y, z; };
+struct q4 { float w, x, y, z; };
+struct m33 { float m[9]; };   // row-major
+struct sv6 { float v[6]; };   // spatial vector [angular, linear]
+
+DEV v3 mk3(float x, float y, float z) { v3 r = {x, y, z}; return r; }
+DEV v3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
+DEV void st3(float* p, v3 a) { p[0] = a.x; p[1] = a.y; p[2] = a.z; }
+DEV v3 operator+(v3 a, v3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+DEV v3 operator-(v3 a, v3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+DEV v3 operator*(v3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+DEV float dot(v3 a, v3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+DEV v3 cross(v3 a, v3 b) { return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+DEV float norm(v3 a) { return sqrtf(dot(a, a)); }
+DEV v3 normalized(v3 a) {
+  float n = norm(a);
+  if (n < B2S_MINVAL) return mk3(1.f, 0.f, 0.f);
+  float s = 1.0f / n;
+  return a * s;
+}
+DEV q4 ldq(const float* p) { q4 r = {p[0], p[1], p[2], p[3]}; return r; }
+DEV void stq(float* p, q4 a) { p[0] = a.w; p[1] = a.x; p[2] = a.y; p[3] = a.z; }
+DEV q4 qnormalize(q4 q) {
+  float n = sqrtf(q.w * q.w + q.x * q.x + q.y * q.y + q.z * q.z);
+  if (n < B2S_MINVAL) { q4 r = {1.f, 0.f, 0.f, 0.f}; return r; }
+  float s = 1.0f / n;
+  q4 r = {q.w * s, q.x * s, q.y * s, q.z * s};
+  return r;
+}
+DEV q4 qmul(q4 a, q4 b) {
+  q4 r = {a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z, a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y,
+          a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x, a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w};
+  return r;
+}
+DEV q4 axis_angle(v3 axis, float angle) {
+  float s, c;
+  sincosf(0.5f * angle, &s, &c);
+  q4 r = {c, axis.x * s, axis.y * s, axis.z * s};
+  return r;
+}
+DEV m33 q2m(q4 q) {
+  m33 r;
+  float q00 = q.w * q.w, q11 = q.x * q.x, q22 = q.y * q.y, q33 = q.z * q.z;
+  float q01 = q.w * q.x, q02 = q.w * q.y, q03 = q.w * q.z, q12 = q.x * q.y, q13 = q.x * q.z, q23 = q.y * q.z;
+  r.m[0] = q00 + q11 - q22 - q33; r.m[4] = q00 - q11 + q22 - q33; r.m[8] = q00 - q11 - q22 + q33;
+  r.m[1] = 2.f * (q12 - q03); r.m[2] = 2.f * (q13 + q02);
+  r.m[3] = 2.f * (q12 + q03); r.m[5] = 2.f * (q23 - q01);
+  r.m[6] = 2.f * (q13 - q02); r.m[7] = 2.f * (q23 + q01);
+  return r;
+}
+DEV m33 ldm(const float* p) { m33 r;
+#pragma unroll
+  for (int k = 0; k < 9; k++) r.m[k] = p[k];
+  return r; }
+DEV void stm(float* p, const m33& a) {
+#pragma unroll
+  for (int k = 0; k < 9; k++) p[k] = a.m[k]; }
+DEV v3 mulv(const m33& a, v3 v) {
+  return mk3(a.m[0] * v.x + a.m[1] * v.y + a.m[2] * v.z, a.m[3] * v.x + a.m[4] * v.y + a.m[5] * v.z,
+             a.m[6] * v.x + a.m[7] * v.y + a.m[8] * v.z);
+}
+DEV v3 mulTv(const m33& a, v3 v) {
+  return mk3(a.m[0] * v.x + a.m[3] * v.y + a.m[6] * v.z, a.m[1] * v.x + a.m[4] * v.y + a.m[7] * v.z,
+             a.m[2] * v.x + a.m[5] * v.y + a.m[8] * v.z);
+}
+DEV v3 col(const m33& a, int c) { return mk3(a.m[c], a.m[3 + c], a.m[6 + c]); }
+DEV q4 m2q(const m33& R) {
+  const float* m = R.m;
+  q4 q;
+  float tr = m[0] + m[4] + m[8];
+  if (tr > 0.f) { float s = sqrtf(tr + 1.f) * 2.f; q.w = 0.25f * s; q.x = (m[7] - m[5]) / s; q.y = (m[2] - m[6]) / s; q.z = (m[3] - m[1]) / s; }
+  else if (m[0] > m[4] && m[0] > m[8]) { float s = sqrtf(1.f + m[0] - m[4] - m[8]) * 2.f; q.w = (m[7] - m[5]) / s; q.x = 0.25f * s; q.y = (m[1] + m[3]) / s; q.z = (m[2] + m[6]) / s; }
+  else if (m[4] > m[8]) { float s = sqrtf(1.f + m[4] - m[0] - m[8]) * 2.f; q.w = (m[2] - m[6]) / s; q.x = (m[1] + m[3]) / s; q.y = 0.25f * s; q.z = (m[5] + m[7]) / s; }
+  else { float s = sqrtf(1.f + m[8] - m[0] - m[4]) * 2.f; q.w = (m[3] - m[1]) / s; q.x = (m[2] + m[6]) / s; q.y = (m[5] + m[7]) / s; q.z = 0.25f * s; }
+  return qnormalize(q);
+}
+
+// ---- spatial algebra (MuJoCo's com-based convention: [angular, linear] about the root subtree COM)
+DEV sv6 ld6(const float* p) { sv6 r;
+#pragma unroll
+  for (int k = 0; k < 6; k++) r.v[k] = p[k];
+  return r; }
+DEV void st6(float* p, const sv6& a) {
+#pragma unroll
+  for (int k = 0; k < 6; k++) p[k] = a.v[k]; }
+DEV sv6 zero6() { sv6 r;
+#pragma unroll
+  for (int k = 0; k < 6; k++) r.v[k] = 0.f;
+  return r; }
+DEV void axpy6(sv6& y, float a, const sv6& x) {
+#pragma unroll
+  for (int k = 0; k < 6; k++) y.v[k] += a * x.v[k]; }
+DEV float dot6(const sv6& a, const sv6& b) {
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 6; k++) s += a.v[k] * b.v[k];
+  return s; }
+// 10-number inertia about the common frame: [Ixx Iyy Izz Ixy Ixz Iyz mx my mz m]
+DEV sv6 mul_inert(const float* I, const sv6& x) {
+  const float* v = x.v; sv6 r;
+  r.v[0] = I[0] * v[0] + I[3] * v[1] + I[4] * v[2] - I[8] * v[4] + I[7] * v[5];
+  r.v[1] = I[3] * v[0] + I[1] * v[1] + I[5] * v[2] + I[8] * v[3] - I[6] * v[5];
+  r.v[2] = I[4] * v[0] + I[5] * v[1] + I[2] * v[2] - I[7] * v[3] + I[6] * v[4];
+  r.v[3] = I[8] * v[1] - I[7] * v[2] + I[9] * v[3];
+  r.v[4] = I[6] * v[2] - I[8] * v[0] + I[9] * v[4];
+  r.v[5] = I[7] * v[0] - I[6] * v[1] + I[9] * v[5];
+  return r;
+}
+DEV sv6 cross_motion(const sv6& a, const sv6& b) {
+  const float *vel = a.v, *v = b.v; sv6 r;
+  r.v[0] = -vel[2] * v[1] + vel[1] * v[2];
+  r.v[1] = vel[2] * v[0] - vel[0] * v[2];
+  r.v[2] = -vel[1] * v[0] + vel[0] * v[1];
+  r.v[3] = -vel[2] * v[4] + vel[1] * v[5] - vel[5] * v[1] + vel[4] * v[2];
+  r.v[4] = vel[2] * v[3] - vel[0] * v[5] + vel[5] * v[0] - vel[3] * v[2];
+  r.v[5] = -vel[1] * v[3] + vel[0] * v[4] - vel[4] * v[0] + vel[3] * v[1];
+  return r;
+}
+DEV sv6 cross_force(const sv6& a, const sv6& b) {
+  const float *vel = a.v, *f = b.v; sv6 r;
+  r.v[0] = -vel[2] * f[1] + vel[1] * f[2] - vel[5] * f[4] + vel[4] * f[5];
+  r.v[1] = vel[2] * f[0] - vel[0] * f[2] + vel[5] * f[3] - vel[3] * f[5];
+  r.v[2] = -vel[1] * f[0] + vel[0] * f[1] - vel[4] * f[3] + vel[3] * f[4];
+  r.v[3] = -vel[2] * f[4] + vel[1] * f[5];
+  r.v[4] = vel[2] * f[3] - vel[0] * f[5];
+  r.v[5] = -vel[1] * f[3] + vel[0] * f[4];
+  return r;
+}
+
+// ---- warp helpers
+DEV float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+DEV int warp_excl_scan(int v, int lane, int* total) {
+  int x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(FULL, x, o); if (lane >= o) x += y; }
+  *total = __shfl_sync(FULL, x, 31);
+  return x - v;
+}
+DEV float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// In-place dense Cholesky A = L L^T on the lower triangle of an n x n matrix held in shared memory with row
+// stride `ld` (ld odd => conflict-free column walks).  One warp; right-looking.
+DEV void warp_cholesky(float* A, int n, int ld, int lane) {
+  for (int k = 0; k < n; k++) {
+    __syncwarp();
+    float dkk = A[k * ld + k];
+    dkk = sqrtf(fmaxf(dkk, B2S_MINVAL));
+    float inv = 1.0f / dkk;
+    __syncwarp();
+    if (lane == 0) A[k * ld + k] = dkk;
+    for (int i = k + 1 + lane; i < n; i += 32) A[i * ld + k] *= inv;
+    __syncwarp();
+    for (int i = k + 1 + lane; i < n; i += 32) {
+      float lik = A[i * ld + k];
+      for (int j = k + 1; j <= i; j++) A[i * ld + j] -= lik * A[j * ld + k];
+    }
+  }
+  __syncwarp();
+}
+// Solve L L^T x = b with the factor above.  b is distributed: lane l holds b[l] in b0 and b[l+32] in b1.
+DEV void warp_chol_solve(const float* L, int n, int ld, int lane, float& b0, float& b1) {
+  for (int k = 0; k < n; k++) {   // forward: L y = b
+    float bk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) / L[k * ld + k];
+    if (lane == k) b0 = bk;
+    if (lane + 32 == k) b1 = bk;
+    if (lane > k && lane < n) b0 -= L[lane * ld + k] * bk;
+    if (lane + 32 > k && lane + 32 < n) b1 -= L[(lane + 32) * ld + k] * bk;
+  }
+  for (int k = n - 1; k >= 0; k--) {   // backward: L^T x = y
+    float xk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) / L[k * ld + k];
+    if (lane == k) b0 = xk;
+    if (lane + 32 == k) b1 = xk;
+    if (lane < k) b0 -= L[k * ld + lane] * xk;
+    if (lane + 32 < k) b1 -= L[k * ld + lane + 32] * xk;
+  }
+}

@@ -1,0 +1,88 @@
+// b2s_types.h -- device-side model/data descriptors shared by all kernels.
+//
+// Layout in HBM: every field is its own array (struct of
+// arrays), world-major, fp32/int32: field[world][...].  One warp owns one
+// world, so a warp's loads of a field are contiguous runs (coalesced), and
+// every field is directly a zero-copy torch tensor of the shape the
+// reference exposes (src/mjlab/sim/sim_data.py:21).
+#pragma once
+#include <stdint.h>
+
+#define B2S_WARPS_PER_CTA 4
+#define B2S_MAX_NV 56          // register-tiled Hessian: 7 x 7 tiles of up to 8 x 8
+#define B2S_MINVAL 1e-15f
+#define B2S_MINMU 1e-5f
+
+// A model field that may be per-world (after expand_model_fields): element
+// (w, i) lives at ptr[(w * wstride) + i]; wstride == 0 while un-expanded.
+template <typename T>
+struct WField {
+  const T* ptr;
+  int wstride;
+  __host__ __device__ const T* at(int w) const { return ptr + (size_t)w * wstride; }
+};
+
+struct ModelDev {
+  // sizes
+  int nq, nv, nvp, nu, nbody, njnt, ngeom, nsite, nsensor, nsensordata, nmocap;
+  int nlevel, npair, ncolgeom, maxchain;
+  // options
+  float timestep, gravity[3], tolerance, ls_tolerance, impratio, ls_parallel_min_step, meaninertia;
+  int integrator, cone, iterations, ls_iterations, disableflags, ls_parallel, contact_sensor_maxmatch;
+  // ---- bodies
+  const int *body_parentid, *body_rootid, *body_mocapid, *body_jntnum, *body_jntadr, *body_dofnum, *body_dofadr;
+  const int *body_subtree_end;      // bodies are in DFS pre-order: subtree(b) = [b, body_subtree_end[b])
+  const int *body_chain_adr;        // CSR over ancestor-or-self dofs of each body, root first  [nbody+1]
+  const int *body_chain;            // dof ids
+  const int *level_adr, *level_body; // bodies grouped by tree depth (level 0 = world) [nlevel+1], [nbody]
+  const unsigned char *body_dofmask; // [nbody][nv] 1 if dof is an ancestor-or-self dof of the body
+  const unsigned char *body_ancmask; // [nbody][nbody] 1 if column body is an ancestor-or-self of row body
+  WField<float> body_pos, body_quat, body_ipos, body_iquat, body_mass, body_inertia;
+  const float *body_subtreemass, *body_invweight0;
+  // ---- joints / dofs
+  const int *jnt_type, *jnt_qposadr, *jnt_dofadr, *jnt_bodyid, *jnt_limited;
+  const float *jnt_pos, *jnt_axis, *jnt_margin, *jnt_solref, *jnt_solimp;
+  WField<float> jnt_range, jnt_stiffness, qpos0, qpos_spring;
+  const int *dof_bodyid, *dof_jntid, *dof_parentid;
+  WField<float> dof_armature, dof_damping, dof_frictionloss;
+  const float *dof_invweight0;
+  // ---- geoms
+  const int *geom_type, *geom_bodyid, *geom_condim, *geom_priority;
+  const float *geom_size, *geom_solmix, *geom_solref, *geom_solimp, *geom_margin, *geom_gap, *geom_rbound;
+  WField<float> geom_pos, geom_quat, geom_friction, geom_rgba;
+  const int *pair_geom;             // [npair][2] after type ordering (type1 <= type2), sorted by (min id, max id)
+  // ---- sites
+  const int *site_bodyid;
+  WField<float> site_pos, site_quat;
+  // ---- actuators
+  const int *actuator_trnid, *actuator_gaintype, *actuator_biastype, *actuator_ctrllimited, *actuator_forcelimited;
+  const float *actuator_gear, *actuator_ctrlrange, *actuator_forcerange;
+  WField<float> actuator_gainprm, actuator_biasprm;   // 3 per actuator
+  // ---- sensors
+  const int *sensor_type, *sensor_objtype, *sensor_objid, *sensor_reftype, *sensor_refid, *sensor_intprm, *sensor_dim, *sensor_adr;
+  const float *sensor_cutoff;
+  int need_subtreevel;
+};
+
+struct DataDev {
+  int nworld, nconmax, njmax;
+  // state / inputs
+  float *qpos, *qvel, *ctrl, *qacc_warmstart, *time, *xfrc_applied, *qfrc_applied, *mocap_pos, *mocap_quat;
+  // position stage
+  float *xpos, *xquat, *xmat, *xipos, *ximat, *xanchor, *xaxis, *geom_xpos, *geom_xmat, *site_xpos, *site_xmat;
+  float *subtree_com, *cinert, *cdof;
+  // dynamics stage
+  float *cvel, *cdof_dot, *qM, *qfrc_bias, *qfrc_passive, *actuator_length, *actuator_velocity, *actuator_force;
+  float *qfrc_actuator, *qfrc_smooth, *qacc_smooth;
+  // collision
+  int *ncon, *con_dim, *con_geom, *con_efc_address;
+  float *con_dist, *con_pos, *con_frame, *con_includemargin, *con_friction, *con_solref, *con_solimp;
+  // constraints
+  int *nefc, *nl, *efc_type, *efc_id;
+  float *efc_J, *efc_pos, *efc_margin, *efc_D, *efc_vel, *efc_aref, *efc_force;
+  // solver
+  float *qacc, *qfrc_constraint, *solver_cost;
+  int *solver_niter;
+  // post
+  float *cacc, *subtree_linvel, *subtree_angmom, *sensordata;
+};

@@ -1,0 +1,352 @@
+// k_post.cu -- sensors (+ the acceleration half of rne_postconstraint, subtree_vel) and the integrator,
+// one warp per world.
+#include "b2s_math.cuh"
+#include "b2s_api.h"
+
+extern __shared__ float b2s_smem[];
+
+// 6D velocity [ang, lin] of a frame at `pos` riding on `body` (mj_objectVelocity), world orientation
+DEV sv6 object_velocity(const ModelDev& m, const float* cvel, const float* com, int body, v3 pos) {
+  sv6 cv = ld6(cvel + 6 * body);
+  v3 ang = mk3(cv.v[0], cv.v[1], cv.v[2]);
+  v3 lin = mk3(cv.v[3], cv.v[4], cv.v[5]) + cross(ang, pos - ld3(com + 3 * m.body_rootid[body]));
+  sv6 r; r.v[0] = ang.x; r.v[1] = ang.y; r.v[2] = ang.z; r.v[3] = lin.x; r.v[4] = lin.y; r.v[5] = lin.z;
+  return r;
+}
+DEV bool side_match(const ModelDev& m, int objtype, int objid, int geom) {
+  const int body = m.geom_bodyid[geom];
+  if (objtype == B2S_OBJ_GEOM) return geom == objid;
+  if (objtype == B2S_OBJ_BODY) return body == objid;
+  if (objtype == B2S_OBJ_XBODY) return m.body_ancmask[(size_t)body * m.nbody + objid] != 0;
+  return true;
+}
+// contact wrench in the contact frame from the pyramid forces (mju_decodePyramid)
+DEV void contact_wrench(const DataDev& d, size_t con0, size_t row0, int c, float* f6) {
+#pragma unroll
+  for (int k = 0; k < 6; k++) f6[k] = 0.f;
+  const int adr = d.con_efc_address[con0 + c], dim = d.con_dim[con0 + c];
+  if (adr < 0) return;
+  if (dim == 1) { f6[0] = d.efc_force[row0 + adr]; return; }
+  for (int k = 0; k < dim - 1; k++) {
+    const float a = d.efc_force[row0 + adr + 2 * k], b = d.efc_force[row0 + adr + 2 * k + 1];
+    f6[0] += a + b;
+    f6[1 + k] = d.con_friction[5 * (con0 + c) + k] * (a - b);
+  }
+}
+struct Frame { v3 pos; m33 mat; int body; };
+DEV Frame obj_frame(const ModelDev& m, const DataDev& d, int w, int type, int id) {
+  Frame f;
+  if (type == B2S_OBJ_SITE) { f.pos = ld3(d.site_xpos + ((size_t)w * m.nsite + id) * 3); f.mat = ldm(d.site_xmat + ((size_t)w * m.nsite + id) * 9); f.body = m.site_bodyid[id]; }
+  else if (type == B2S_OBJ_GEOM) { f.pos = ld3(d.geom_xpos + ((size_t)w * m.ngeom + id) * 3); f.mat = ldm(d.geom_xmat + ((size_t)w * m.ngeom + id) * 9); f.body = m.geom_bodyid[id]; }
+  else if (type == B2S_OBJ_XBODY) { f.pos = ld3(d.xpos + ((size_t)w * m.nbody + id) * 3); f.mat = ldm(d.xmat + ((size_t)w * m.nbody + id) * 9); f.body = id; }
+  else { f.pos = ld3(d.xipos + ((size_t)w * m.nbody + id) * 3); f.mat = ldm(d.ximat + ((size_t)w * m.nbody + id) * 9); f.body = id; }
+  return f;
+}
+
+DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float* out) {
+  const int bits = m.sensor_intprm[3 * s], reduce = m.sensor_intprm[3 * s + 1], nslot = m.sensor_intprm[3 * s + 2];
+  const int ot = m.sensor_objtype[s], id = m.sensor_objid[s], rt = m.sensor_reftype[s], rid = m.sensor_refid[s];
+  const int dim = m.sensor_dim[s], maxm = m.contact_sensor_maxmatch;
+  const size_t con0 = (size_t)w * d.nconmax, row0 = (size_t)w * d.njmax;
+  const int ncon = d.ncon[w];
+  for (int k = 0; k < dim; k++) out[k] = 0.f;
+  if (nslot <= 0) return;
+  const int slotdim = dim / nslot;
+  // pass 1: count matches (capped), and for netforce the force-weighted centroid
+  int nmatch = 0; float wsum = 0.f; v3 P = mk3(0.f, 0.f, 0.f), Pm = mk3(0.f, 0.f, 0.f);
+  for (int c = 0; c < ncon && nmatch < maxm; c++) {
+    const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
+    const bool fwd = side_match(m, ot, id, g1) && (rid < 0 || side_match(m, rt, rid, g2));
+    const bool bwd = side_match(m, ot, id, g2) && (rid < 0 || side_match(m, rt, rid, g1));
+    if (!fwd && !bwd) continue;
+    nmatch++;
+    if (reduce == B2S_REDUCE_NETFORCE) {
+      float f6[6]; contact_wrench(d, con0, row0, c, f6);
+      const float wt = sqrtf(f6[0] * f6[0] + f6[1] * f6[1] + f6[2] * f6[2]);
+      v3 cp = ld3(d.con_pos + 3 * (con0 + c));
+      P = P + cp * wt; Pm = Pm + cp; wsum += wt;
+    }
+  }
+  if (nmatch == 0) return;
+  if (reduce == B2S_REDUCE_NETFORCE) {
+    P = wsum > B2S_MINVAL ? P * (1.f / wsum) : Pm * (1.f / (float)nmatch);
+    v3 F = mk3(0.f, 0.f, 0.f), Tq = mk3(0.f, 0.f, 0.f);
+    int seen = 0;
+    for (int c = 0; c < ncon && seen < maxm; c++) {
+      const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
+      const bool fwd = side_match(m, ot, id, g1) && (rid < 0 || side_match(m, rt, rid, g2));
+      const bool bwd = side_match(m, ot, id, g2) && (rid < 0 || side_match(m, rt, rid, g1));
+      if (!fwd && !bwd) continue;
+      seen++;
+      const float dir = fwd ? 1.f : -1.f;
+      float f6[6]; contact_wrench(d, con0, row0, c, f6);
+      m33 fr = ldm(d.con_frame + 9 * (con0 + c));
+      v3 fg = mulTv(fr, mk3(f6[0], f6[1], f6[2])) * dir, tg = mulTv(fr, mk3(f6[3], f6[4], f6[5])) * dir;
+      v3 arm = ld3(d.con_pos + 3 * (con0 + c)) - P;
+      F = F + fg; Tq = Tq + tg + cross(arm, fg);
+    }
+    float* o = out;
+    if (bits & B2S_CON_FOUND) *o++ = (float)nmatch;
+    if (bits & B2S_CON_FORCE) { st3(o, F); o += 3; }
+    if (bits & B2S_CON_TORQUE) { st3(o, Tq); o += 3; }
+    if (bits & B2S_CON_DIST) *o++ = 0.f;
+    if (bits & B2S_CON_POS) { st3(o, P); o += 3; }
+    if (bits & B2S_CON_NORMAL) { st3(o, mk3(1.f, 0.f, 0.f)); o += 3; }
+    if (bits & B2S_CON_TANGENT) { st3(o, mk3(0.f, 1.f, 0.f)); o += 3; }
+    return;
+  }
+  // slots: selection by repeated scan in (key, match-order) order -- no per-lane match list needed
+  float pkey = -3.0e38f; int pord = -1;
+  for (int sl = 0; sl < nslot && sl < nmatch; sl++) {
+    float bkey = 3.0e38f; int bord = -1, bc = -1; float bdir = 1.f;
+    int ord = 0;
+    for (int c = 0; c < ncon && ord < maxm; c++) {
+      const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
+      const bool fwd = side_match(m, ot, id, g1) && (rid < 0 || side_match(m, rt, rid, g2));
+      const bool bwd = side_match(m, ot, id, g2) && (rid < 0 || side_match(m, rt, rid, g1));
+      if (!fwd && !bwd) continue;
+      float key;
+      if (reduce == B2S_REDUCE_NONE) key = (float)ord;
+      else if (reduce == B2S_REDUCE_MINDIST) key = d.con_dist[con0 + c];
+      else { float f6[6]; contact_wrench(d, con0, row0, c, f6); key = -sqrtf(f6[0] * f6[0] + f6[1] * f6[1] + f6[2] * f6[2]); }
+      const bool after = key > pkey || (key == pkey && ord > pord);
+      const bool better = key < bkey || (key == bkey && ord < bord);
+      if (after && (bord < 0 || better)) { bkey = key; bord = ord; bc = c; bdir = fwd ? 1.f : -1.f; }
+      ord++;
+    }
+    if (bc < 0) break;
+    pkey = bkey; pord = bord;
+    float f6[6]; contact_wrench(d, con0, row0, bc, f6);
+    const float* fr = d.con_frame + 9 * (con0 + bc);
+    float* o = out + sl * slotdim;
+    if (bits & B2S_CON_FOUND) *o++ = (float)nmatch;
+    if (bits & B2S_CON_FORCE) { o[0] = f6[0]; o[1] = bdir * f6[1]; o[2] = bdir * f6[2]; o += 3; }
+    if (bits & B2S_CON_TORQUE) { o[0] = f6[3]; o[1] = bdir * f6[4]; o[2] = bdir * f6[5]; o += 3; }
+    if (bits & B2S_CON_DIST) *o++ = d.con_dist[con0 + bc];
+    if (bits & B2S_CON_POS) { st3(o, ld3(d.con_pos + 3 * (con0 + bc))); o += 3; }
+    if (bits & B2S_CON_NORMAL) { st3(o, ld3(fr) * bdir); o += 3; }
+    if (bits & B2S_CON_TANGENT) { st3(o, ld3(fr + 3) * bdir); o += 3; }
+  }
+}
+
+// shared per warp: cacc 6nb | bvel 6nb | lm 3nb | am 3nb | slv 3nb
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelDev m, const DataDev d) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
+  if (w >= d.nworld) return;
+  const int nb = m.nbody, nv = m.nv;
+  float* s_cacc = b2s_smem + (size_t)warp * 21 * nb;
+  float* s_bvel = s_cacc + 6 * nb;
+  float* s_lm = s_bvel + 6 * nb;
+  float* s_am = s_lm + 3 * nb;
+  float* s_slv = s_am + 3 * nb;
+  const float* qvel = d.qvel + (size_t)w * nv;
+  const float* qacc = d.qacc + (size_t)w * nv;
+  const float* cdof = d.cdof + (size_t)w * 6 * nv;
+  const float* cdd = d.cdof_dot + (size_t)w * 6 * nv;
+  const float* cvel = d.cvel + (size_t)w * 6 * nb;
+  const float* com = d.subtree_com + (size_t)w * 3 * nb;
+  const float* xipos = d.xipos + (size_t)w * 3 * nb;
+  // cacc = cacc_world + sum over ancestor dofs (cdof_dot qvel + cdof qacc)
+  const bool grav = !(m.disableflags & B2S_DSBL_GRAVITY);
+  for (int b = lane; b < nb; b += 32) {
+    sv6 a = zero6();
+    if (grav) { a.v[3] = -m.gravity[0]; a.v[4] = -m.gravity[1]; a.v[5] = -m.gravity[2]; }
+    for (int c = m.body_chain_adr[b]; c < m.body_chain_adr[b + 1]; c++) {
+      const int j = m.body_chain[c];
+      axpy6(a, qvel[j], ld6(cdd + 6 * j));
+      axpy6(a, qacc[j], ld6(cdof + 6 * j));
+    }
+    st6(s_cacc + 6 * b, a);
+    st6(d.cacc + ((size_t)w * nb + b) * 6, a);
+  }
+  if (m.need_subtreevel) {
+    const float* mass = m.body_mass.at(w);
+    const float* inertia = m.body_inertia.at(w);
+    for (int b = lane; b < nb; b += 32) {
+      sv6 v = object_velocity(m, cvel, com, b, ld3(xipos + 3 * b));
+      st6(s_bvel + 6 * b, v);
+      st3(s_lm + 3 * b, mk3(v.v[3], v.v[4], v.v[5]) * mass[b]);
+      m33 R = ldm(d.ximat + ((size_t)w * nb + b) * 9);
+      v3 loc = mulTv(R, mk3(v.v[0], v.v[1], v.v[2]));
+      loc = mk3(loc.x * inertia[3 * b], loc.y * inertia[3 * b + 1], loc.z * inertia[3 * b + 2]);
+      st3(s_am + 3 * b, mulv(R, loc));
+    }
+    __syncwarp();
+    for (int b = lane; b < nb; b += 32) {
+      v3 acc = mk3(0.f, 0.f, 0.f);
+      const int e = m.body_subtree_end[b];
+      for (int j = b; j < e; j++) acc = acc + ld3(s_lm + 3 * j);
+      acc = acc * (1.0f / fmaxf(m.body_subtreemass[b], B2S_MINVAL));
+      st3(s_slv + 3 * b, acc);
+      st3(d.subtree_linvel + ((size_t)w * nb + b) * 3, acc);
+    }
+    __syncwarp();
+    for (int b = lane; b < nb; b += 32) {
+      // angular momentum of the subtree about its own COM (closed form of mj_subtreeVel's recursion)
+      v3 L = mk3(0.f, 0.f, 0.f);
+      const v3 cb = ld3(com + 3 * b), Vb = ld3(s_slv + 3 * b);
+      const int e = m.body_subtree_end[b];
+      for (int j = b; j < e; j++) {
+        v3 dx = ld3(xipos + 3 * j) - cb;
+        v3 dv = (mk3(s_bvel[6 * j + 3], s_bvel[6 * j + 4], s_bvel[6 * j + 5]) - Vb) * mass[j];
+        L = L + ld3(s_am + 3 * j) + cross(dx, dv);
+      }
+      st3(d.subtree_angmom + ((size_t)w * nb + b) * 3, L);
+    }
+  }
+  __syncwarp();
+  // one lane per sensor
+  for (int s = lane; s < m.nsensor; s += 32) {
+    const int type = m.sensor_type[s], id = m.sensor_objid[s], ot = m.sensor_objtype[s], dim = m.sensor_dim[s];
+    float* out = d.sensordata + (size_t)w * m.nsensordata + m.sensor_adr[s];
+    switch (type) {
+      case B2S_SENS_GYRO: case B2S_SENS_VELOCIMETER: case B2S_SENS_ACCELEROMETER: {
+        Frame f = obj_frame(m, d, w, B2S_OBJ_SITE, id);
+        sv6 v = object_velocity(m, cvel, com, f.body, f.pos);
+        v3 wl = mulTv(f.mat, mk3(v.v[0], v.v[1], v.v[2])), vl = mulTv(f.mat, mk3(v.v[3], v.v[4], v.v[5]));
+        if (type == B2S_SENS_GYRO) st3(out, wl);
+        else if (type == B2S_SENS_VELOCIMETER) st3(out, vl);
+        else {
+          const float* ca = s_cacc + 6 * f.body;
+          v3 aang = mk3(ca[0], ca[1], ca[2]);
+          v3 alin = mk3(ca[3], ca[4], ca[5]) + cross(aang, f.pos - ld3(com + 3 * m.body_rootid[f.body]));
+          st3(out, mulTv(f.mat, alin) + cross(wl, vl));
+        }
+      } break;
+      case B2S_SENS_JOINTPOS: out[0] = d.qpos[(size_t)w * m.nq + m.jnt_qposadr[id]]; break;
+      case B2S_SENS_JOINTVEL: out[0] = qvel[m.jnt_dofadr[id]]; break;
+      case B2S_SENS_ACTUATORFRC: out[0] = d.actuator_force[(size_t)w * m.nu + id]; break;
+      case B2S_SENS_SUBTREECOM: st3(out, ld3(com + 3 * id)); break;
+      case B2S_SENS_SUBTREELINVEL: st3(out, ld3(s_slv + 3 * id)); break;
+      case B2S_SENS_SUBTREEANGMOM: st3(out, ld3(d.subtree_angmom + ((size_t)w * nb + id) * 3)); break;
+      case B2S_SENS_FRAMEPOS: case B2S_SENS_FRAMEQUAT: case B2S_SENS_FRAMEZAXIS: {
+        Frame f = obj_frame(m, d, w, ot, id);
+        const bool hasref = m.sensor_refid[s] >= 0;
+        Frame r = f;
+        if (hasref) r = obj_frame(m, d, w, m.sensor_reftype[s], m.sensor_refid[s]);
+        if (type == B2S_SENS_FRAMEPOS) st3(out, hasref ? mulTv(r.mat, f.pos - r.pos) : f.pos);
+        else if (type == B2S_SENS_FRAMEZAXIS) st3(out, hasref ? mulTv(r.mat, col(f.mat, 2)) : col(f.mat, 2));
+        else {
+          m33 R = f.mat;
+          if (hasref) for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) {
+            float acc = 0.f;
+            for (int k = 0; k < 3; k++) acc += r.mat.m[3 * k + a] * f.mat.m[3 * k + b];
+            R.m[3 * a + b] = acc;
+          }
+          stq(out, m2q(R));
+        }
+      } break;
+      case B2S_SENS_FRAMELINVEL: case B2S_SENS_FRAMEANGVEL: {
+        Frame f = obj_frame(m, d, w, ot, id);
+        sv6 v = object_velocity(m, cvel, com, f.body, f.pos);
+        if (type == B2S_SENS_FRAMELINVEL) st3(out, mk3(v.v[3], v.v[4], v.v[5])); else st3(out, mk3(v.v[0], v.v[1], v.v[2]));
+      } break;
+      case B2S_SENS_CONTACT: contact_sensor(m, d, w, s, out); break;
+      default: for (int k = 0; k < dim; k++) out[k] = 0.f;
+    }
+    const float cut = m.sensor_cutoff[s];
+    if (cut > 0.f && type != B2S_SENS_CONTACT) for (int k = 0; k < dim; k++) out[k] = clampf(out[k], -cut, cut);
+  }
+}
+
+// ------------------------------------------------------------------------------------------- k_integrate
+// shared per warp: A nv*ld | dg nvp | qa nvp
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const ModelDev m, const DataDev d) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
+  if (w >= d.nworld) return;
+  const int nv = m.nv, nvp = m.nvp, ld = nvp + 1;
+  float* A = b2s_smem + (size_t)warp * (nv * ld + 2 * nvp);
+  float* dg = A + nv * ld;
+  float* qa = dg + nvp;
+  const float dt = m.timestep;
+  float* qvel = d.qvel + (size_t)w * nv;
+  float* qpos = d.qpos + (size_t)w * m.nq;
+  const float* qacc = d.qacc + (size_t)w * nv;
+  for (int i = lane; i < nvp; i += 32) { dg[i] = 0.f; qa[i] = i < nv ? qacc[i] : 0.f; }
+  __syncwarp();
+  bool use = false;
+  if (m.integrator == B2S_INT_IMPLICITFAST) {
+    use = true;
+    if (!(m.disableflags & B2S_DSBL_ACTUATION)) {
+      const float* gainprm = m.actuator_gainprm.at(w);
+      const float* biasprm = m.actuator_biasprm.at(w);
+      for (int u = lane; u < m.nu; u += 32) {
+        float bv = 0.f;
+        if (m.actuator_biastype[u] == B2S_BIAS_AFFINE) bv += biasprm[3 * u + 2];
+        if (m.actuator_gaintype[u] == B2S_GAIN_AFFINE) {
+          float c = d.ctrl[(size_t)w * m.nu + u];
+          if (m.actuator_ctrllimited[u] && !(m.disableflags & B2S_DSBL_CLAMPCTRL)) c = clampf(c, m.actuator_ctrlrange[2 * u], m.actuator_ctrlrange[2 * u + 1]);
+          bv += gainprm[3 * u + 2] * c;
+        }
+        if (bv == 0.f) continue;
+        if (m.actuator_forcelimited[u]) {
+          const float f = d.actuator_force[(size_t)w * m.nu + u];
+          if (f <= m.actuator_forcerange[2 * u] || f >= m.actuator_forcerange[2 * u + 1]) continue;
+        }
+        const float g = m.actuator_gear[u];
+        atomicAdd(&dg[m.jnt_dofadr[m.actuator_trnid[u]]], g * g * bv);
+      }
+    }
+    __syncwarp();
+    if (!(m.disableflags & B2S_DSBL_PASSIVE)) {
+      const float* damping = m.dof_damping.at(w);
+      for (int i = lane; i < nv; i += 32) dg[i] -= damping[i];
+    }
+  } else if (m.integrator == B2S_INT_EULER && !(m.disableflags & (B2S_DSBL_EULERDAMP | B2S_DSBL_PASSIVE))) {
+    const float* damping = m.dof_damping.at(w);
+    bool any = false;
+    for (int i = lane; i < nv; i += 32) if (damping[i] > 0.f) { any = true; dg[i] = -damping[i]; }
+    use = __any_sync(FULL, any);
+  }
+  __syncwarp();
+  if (use) {
+    const float* M = d.qM + (size_t)w * nv * nvp;
+    for (int i = lane; i < nv * nvp; i += 32) {
+      const int r = i / nvp, c = i - r * nvp;
+      if (c <= r) A[r * ld + c] = M[i] - (c == r ? dt * dg[r] : 0.f);
+    }
+    __syncwarp();
+    warp_cholesky(A, nv, ld, lane);
+    float b0 = 0.f, b1 = 0.f;
+    if (lane < nv) b0 = d.qfrc_smooth[(size_t)w * nv + lane] + d.qfrc_constraint[(size_t)w * nv + lane];
+    if (lane + 32 < nv) b1 = d.qfrc_smooth[(size_t)w * nv + lane + 32] + d.qfrc_constraint[(size_t)w * nv + lane + 32];
+    warp_chol_solve(A, nv, ld, lane, b0, b1);
+    if (lane < nv) qa[lane] = b0;
+    if (lane + 32 < nv) qa[lane + 32] = b1;
+  }
+  __syncwarp();
+  // mj_advance
+  for (int i = lane; i < nv; i += 32) { const float v = qvel[i] + dt * qa[i]; qvel[i] = v; dg[i] = v; }
+  __syncwarp();
+  for (int j = lane; j < m.njnt; j += 32) {
+    int pa = m.jnt_qposadr[j], da = m.jnt_dofadr[j];
+    const int t = m.jnt_type[j];
+    if (t == B2S_JNT_FREE) { for (int k = 0; k < 3; k++) qpos[pa + k] += dt * dg[da + k]; pa += 3; da += 3; }
+    if (t == B2S_JNT_FREE || t == B2S_JNT_BALL) {
+      v3 wv = mk3(dg[da], dg[da + 1], dg[da + 2]);
+      const float ang = norm(wv) * dt;
+      q4 q = qnormalize(ldq(qpos + pa));
+      q4 dq = axis_angle(normalized(wv), ang);
+      stq(qpos + pa, qnormalize(qmul(q, dq)));
+    } else qpos[pa] += dt * dg[da];
+  }
+  for (int i = lane; i < nv; i += 32) d.qacc_warmstart[(size_t)w * nv + i] = qacc[i];
+  if (lane == 0) d.time[w] += dt;
+}
+
+void launch_sensors(const ModelDev& m, const DataDev& d, cudaStream_t st) {
+  const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
+  k_sensors<<<grid, 32 * B2S_WARPS_PER_CTA, smem_sensors(m), st>>>(m, d);
+  b2s_count_launch();
+}
+void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st) {
+  const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
+  k_integrate<<<grid, 32 * B2S_WARPS_PER_CTA, smem_integrate(m), st>>>(m, d);
+  b2s_count_launch();
+}
+size_t smem_sensors(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * 21 * m.nbody * sizeof(float); }
+size_t smem_integrate(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * (m.nv * (m.nvp + 1) + 2 * m.nvp) * sizeof(float); }
+const void* fn_sensors() { return (const void*)k_sensors; }
+const void* fn_integrate() { return (const void*)k_integrate; }

@@ -1,0 +1,364 @@
+// k_smooth.cu -- position and smooth-dynamics stages, one warp per world.
+//
+//   k_position : kinematics + com_pos          
+//   k_dynamics : crb, com_vel, rne, passive, actuation, qfrc_smooth,
+//                in-shared-memory Cholesky of M, qacc_smooth   (rows K4, K9-K12)
+//
+// Tree recursions are turned into independent per-body sums: every spatial
+// quantity is expressed about the root's subtree COM in world orientation, so
+// cvel/cacc of a body is a sum over its ancestor dofs (body_chain) and
+// composite inertia / bias force of a body is a sum over the contiguous id
+// range of its subtree (bodies are stored in DFS pre-order).  No level-by-level
+// launches, no atomics: lanes own bodies/dofs and meet only at __syncwarp().
+#include "b2s_math.cuh"
+#include "b2s_api.h"
+
+extern __shared__ float b2s_smem[];
+
+// ---------------------------------------------------------------------------------------------- k_position
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const ModelDev m, const DataDev d) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
+  if (w >= d.nworld) return;
+  const int nb = m.nbody;
+  float* sx = b2s_smem + (size_t)warp * 22 * nb;   // xpos
+  float* sq = sx + 3 * nb;                          // xquat
+  float* sm = sq + 4 * nb;                          // xmat
+  float* sip = sm + 9 * nb;                         // xipos
+  float* scom = sip + 3 * nb;                       // subtree_com
+  const float* qpos = d.qpos + (size_t)w * m.nq;
+  const float* qpos0 = m.qpos0.at(w);
+  const float* bpos = m.body_pos.at(w);
+  const float* bquat = m.body_quat.at(w);
+  if (lane == 0) {
+    sx[0] = sx[1] = sx[2] = 0.f; sq[0] = 1.f; sq[1] = sq[2] = sq[3] = 0.f;
+    for (int k = 0; k < 9; k++) sm[k] = (k % 4 == 0) ? 1.f : 0.f;
+  }
+  for (int L = 1; L < m.nlevel; L++) {
+    __syncwarp();
+    for (int idx = m.level_adr[L] + lane; idx < m.level_adr[L + 1]; idx += 32) {
+      const int b = m.level_body[idx], p = m.body_parentid[b];
+      v3 lp; q4 lq;
+      const int mid = m.body_mocapid[b];
+      if (mid >= 0) {
+        lp = ld3(d.mocap_pos + ((size_t)w * m.nmocap + mid) * 3);
+        lq = qnormalize(ldq(d.mocap_quat + ((size_t)w * m.nmocap + mid) * 4));
+      } else { lp = ld3(bpos + 3 * b); lq = ldq(bquat + 4 * b); }
+      m33 pm = ldm(sm + 9 * p);
+      v3 pos = ld3(sx + 3 * p) + mulv(pm, lp);
+      q4 quat = qmul(ldq(sq + 4 * p), lq);
+      const int jn = m.body_jntnum[b], ja = m.body_jntadr[b];
+      for (int jj = 0; jj < jn; jj++) {
+        const int j = ja + jj, qa = m.jnt_qposadr[j], t = m.jnt_type[j];
+        v3 jpos = ld3(m.jnt_pos + 3 * j), jaxis = ld3(m.jnt_axis + 3 * j);
+        float* xan = d.xanchor + ((size_t)w * m.njnt + j) * 3;
+        float* xax = d.xaxis + ((size_t)w * m.njnt + j) * 3;
+        if (t == B2S_JNT_FREE) {
+          pos = ld3(qpos + qa);
+          quat = qnormalize(ldq(qpos + qa + 3));
+          st3(xan, pos); st3(xax, mulv(q2m(quat), jaxis));
+          continue;
+        }
+        m33 R = q2m(quat);
+        v3 anchor = pos + mulv(R, jpos), axis = mulv(R, jaxis);
+        st3(xan, anchor); st3(xax, axis);
+        if (t == B2S_JNT_SLIDE) pos = pos + axis * (qpos[qa] - qpos0[qa]);
+        else {
+          q4 ql = (t == B2S_JNT_HINGE) ? axis_angle(jaxis, qpos[qa] - qpos0[qa]) : qnormalize(ldq(qpos + qa));
+          quat = qmul(quat, ql);
+          pos = anchor - mulv(q2m(quat), jpos);
+        }
+      }
+      quat = qnormalize(quat);
+      st3(sx + 3 * b, pos); stq(sq + 4 * b, quat); stm(sm + 9 * b, q2m(quat));
+    }
+  }
+  __syncwarp();
+  // inertial frames
+  {
+    const float* ipos = m.body_ipos.at(w);
+    const float* iquat = m.body_iquat.at(w);
+    for (int b = lane; b < nb; b += 32) {
+      m33 R = ldm(sm + 9 * b);
+      v3 xi = ld3(sx + 3 * b) + mulv(R, ld3(ipos + 3 * b));
+      st3(sip + 3 * b, xi);
+      st3(d.xipos + ((size_t)w * nb + b) * 3, xi);
+      stm(d.ximat + ((size_t)w * nb + b) * 9, q2m(qmul(ldq(sq + 4 * b), ldq(iquat + 4 * b))));
+    }
+  }
+  // coalesced write-out of body frames
+  for (int i = lane; i < 3 * nb; i += 32) d.xpos[(size_t)w * 3 * nb + i] = sx[i];
+  for (int i = lane; i < 4 * nb; i += 32) d.xquat[(size_t)w * 4 * nb + i] = sq[i];
+  for (int i = lane; i < 9 * nb; i += 32) d.xmat[(size_t)w * 9 * nb + i] = sm[i];
+  // geoms and sites
+  {
+    const float* gpos = m.geom_pos.at(w);
+    const float* gquat = m.geom_quat.at(w);
+    for (int g = lane; g < m.ngeom; g += 32) {
+      const int b = m.geom_bodyid[g];
+      st3(d.geom_xpos + ((size_t)w * m.ngeom + g) * 3, ld3(sx + 3 * b) + mulv(ldm(sm + 9 * b), ld3(gpos + 3 * g)));
+      stm(d.geom_xmat + ((size_t)w * m.ngeom + g) * 9, q2m(qmul(ldq(sq + 4 * b), ldq(gquat + 4 * g))));
+    }
+    const float* spos = m.site_pos.at(w);
+    const float* squat = m.site_quat.at(w);
+    for (int s = lane; s < m.nsite; s += 32) {
+      const int b = m.site_bodyid[s];
+      st3(d.site_xpos + ((size_t)w * m.nsite + s) * 3, ld3(sx + 3 * b) + mulv(ldm(sm + 9 * b), ld3(spos + 3 * s)));
+      stm(d.site_xmat + ((size_t)w * m.nsite + s) * 9, q2m(qmul(ldq(sq + 4 * b), ldq(squat + 4 * s))));
+    }
+  }
+  __syncwarp();
+  // subtree COM: direct sum over the subtree's contiguous id range
+  const float* mass = m.body_mass.at(w);
+  for (int b = lane; b < nb; b += 32) {
+    v3 acc = mk3(0.f, 0.f, 0.f);
+    const int e = m.body_subtree_end[b];
+    for (int j = b; j < e; j++) acc = acc + ld3(sip + 3 * j) * mass[j];
+    const float smass = m.body_subtreemass[b];
+    v3 com = (smass < B2S_MINVAL) ? ld3(sip + 3 * b) : acc * (1.0f / smass);
+    st3(scom + 3 * b, com);
+    st3(d.subtree_com + ((size_t)w * nb + b) * 3, com);
+  }
+  __syncwarp();
+  // cinert: body inertia about the root subtree COM, world orientation
+  {
+    const float* inertia = m.body_inertia.at(w);
+    for (int b = lane; b < nb; b += 32) {
+      m33 R = ldm(d.ximat + ((size_t)w * nb + b) * 9);   // written by this lane above
+      const float i0 = inertia[3 * b], i1 = inertia[3 * b + 1], i2 = inertia[3 * b + 2], ms = mass[b];
+      v3 off = ld3(sip + 3 * b) - ld3(scom + 3 * m.body_rootid[b]);
+      float* c = d.cinert + ((size_t)w * nb + b) * 10;
+      const float* r = R.m;
+      float Ixx = r[0] * i0 * r[0] + r[1] * i1 * r[1] + r[2] * i2 * r[2];
+      float Iyy = r[3] * i0 * r[3] + r[4] * i1 * r[4] + r[5] * i2 * r[5];
+      float Izz = r[6] * i0 * r[6] + r[7] * i1 * r[7] + r[8] * i2 * r[8];
+      float Ixy = r[0] * i0 * r[3] + r[1] * i1 * r[4] + r[2] * i2 * r[5];
+      float Ixz = r[0] * i0 * r[6] + r[1] * i1 * r[7] + r[2] * i2 * r[8];
+      float Iyz = r[3] * i0 * r[6] + r[4] * i1 * r[7] + r[5] * i2 * r[8];
+      float o2 = dot(off, off);
+      c[0] = Ixx + ms * (o2 - off.x * off.x); c[1] = Iyy + ms * (o2 - off.y * off.y); c[2] = Izz + ms * (o2 - off.z * off.z);
+      c[3] = Ixy - ms * off.x * off.y; c[4] = Ixz - ms * off.x * off.z; c[5] = Iyz - ms * off.y * off.z;
+      c[6] = ms * off.x; c[7] = ms * off.y; c[8] = ms * off.z; c[9] = ms;
+    }
+  }
+  // cdof: joint motion axes as spatial vectors about the root subtree COM
+  for (int j = lane; j < m.njnt; j += 32) {
+    const int b = m.jnt_bodyid[j], t = m.jnt_type[j];
+    int da = m.jnt_dofadr[j];
+    v3 off = ld3(scom + 3 * m.body_rootid[b]) - ld3(d.xanchor + ((size_t)w * m.njnt + j) * 3);
+    float* cd = d.cdof + ((size_t)w * m.nv + da) * 6;
+    if (t == B2S_JNT_FREE) {
+      for (int a = 0; a < 3; a++) { for (int k = 0; k < 6; k++) cd[6 * a + k] = 0.f; cd[6 * a + 3 + a] = 1.f; }
+      cd += 18;
+    }
+    if (t == B2S_JNT_FREE || t == B2S_JNT_BALL) {
+      m33 R = ldm(sm + 9 * b);
+      for (int a = 0; a < 3; a++) { v3 ax = col(R, a); st3(cd + 6 * a, ax); st3(cd + 6 * a + 3, cross(ax, off)); }
+    } else {
+      v3 ax = ld3(d.xaxis + ((size_t)w * m.njnt + j) * 3);
+      if (t == B2S_JNT_SLIDE) { st3(cd, mk3(0.f, 0.f, 0.f)); st3(cd + 3, ax); }
+      else { st3(cd, ax); st3(cd + 3, cross(ax, off)); }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- k_dynamics
+// shared memory per warp (floats): cdof 6nv | crb 10nb | cvel 6nb | cdd 6nv | cfrc 6nb | fext 6nb | M nv*ld | vec 4*nvp
+__host__ __device__ inline int dyn_smem_floats(int nv, int nvp, int nb) {
+  return 6 * nv + 10 * nb + 6 * nb + 6 * nv + 6 * nb + 6 * nb + nv * (nvp + 1) + 4 * nvp;
+}
+
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const ModelDev m, const DataDev d) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
+  if (w >= d.nworld) return;
+  const int nb = m.nbody, nv = m.nv, nvp = m.nvp, ld = nvp + 1;
+  float* s_cdof = b2s_smem + (size_t)warp * dyn_smem_floats(nv, nvp, nb);
+  float* s_crb = s_cdof + 6 * nv;
+  float* s_cvel = s_crb + 10 * nb;
+  float* s_cdd = s_cvel + 6 * nb;
+  float* s_cfrc = s_cdd + 6 * nv;
+  float* s_fext = s_cfrc + 6 * nb;
+  float* s_M = s_fext + 6 * nb;
+  float* s_qvel = s_M + nv * ld;
+  float* s_act = s_qvel + nvp;      // qfrc_actuator
+  float* s_rhs = s_act + nvp;       // qfrc_smooth
+  float* s_tmp = s_rhs + nvp;
+  const float* qvel = d.qvel + (size_t)w * nv;
+  const float* qpos = d.qpos + (size_t)w * m.nq;
+  // stage cdof, cinert, qvel
+  for (int i = lane; i < 6 * nv; i += 32) s_cdof[i] = d.cdof[(size_t)w * 6 * nv + i];
+  for (int i = lane; i < nv; i += 32) { s_qvel[i] = qvel[i]; s_act[i] = 0.f; }
+  for (int i = lane; i < nv * ld; i += 32) s_M[i] = 0.f;
+  __syncwarp();
+  // composite inertia: sum of cinert over the subtree range (same frame for all bodies)
+  for (int b = lane; b < nb; b += 32) {
+    float acc[10];
+#pragma unroll
+    for (int k = 0; k < 10; k++) acc[k] = 0.f;
+    const int e = m.body_subtree_end[b];
+    for (int j = b; j < e; j++) {
+      const float* c = d.cinert + ((size_t)w * nb + j) * 10;
+#pragma unroll
+      for (int k = 0; k < 10; k++) acc[k] += c[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 10; k++) s_crb[10 * b + k] = acc[k];
+  }
+  // com_vel: cvel(b) = sum over ancestor dofs; cdof_dot of the body's own dofs on the way
+  for (int b = lane; b < nb; b += 32) {
+    sv6 v = zero6();
+    const int c0 = m.body_chain_adr[b], c1 = m.body_chain_adr[b + 1], own = m.body_dofadr[b];
+    const int nown = m.body_dofnum[b];
+    int c = c0;
+    for (; c < c1 - nown; c++) { const int j = m.body_chain[c]; axpy6(v, s_qvel[j], ld6(s_cdof + 6 * j)); }
+    // own joints, in order
+    const int jn = m.body_jntnum[b], ja = m.body_jntadr[b];
+    for (int jj = 0; jj < jn; jj++) {
+      const int t = m.jnt_type[ja + jj];
+      int da = m.jnt_dofadr[ja + jj];
+      if (t == B2S_JNT_FREE) {
+        for (int a = 0; a < 3; a++) { st6(s_cdd + 6 * (da + a), zero6()); axpy6(v, s_qvel[da + a], ld6(s_cdof + 6 * (da + a))); }
+        da += 3;
+      }
+      if (t == B2S_JNT_FREE || t == B2S_JNT_BALL) {
+        for (int a = 0; a < 3; a++) st6(s_cdd + 6 * (da + a), cross_motion(v, ld6(s_cdof + 6 * (da + a))));
+        for (int a = 0; a < 3; a++) axpy6(v, s_qvel[da + a], ld6(s_cdof + 6 * (da + a)));
+      } else {
+        st6(s_cdd + 6 * da, cross_motion(v, ld6(s_cdof + 6 * da)));
+        axpy6(v, s_qvel[da], ld6(s_cdof + 6 * da));
+      }
+    }
+    (void)own;
+    st6(s_cvel + 6 * b, v);
+  }
+  __syncwarp();
+  for (int i = lane; i < 6 * nb; i += 32) d.cvel[(size_t)w * 6 * nb + i] = s_cvel[i];
+  for (int i = lane; i < 6 * nv; i += 32) d.cdof_dot[(size_t)w * 6 * nv + i] = s_cdd[i];
+  // mass matrix: M[i][j] = cdof_j . (crb[body_i] cdof_i) for j ancestor-or-self of i
+  const float* armature = m.dof_armature.at(w);
+  for (int i = lane; i < nv; i += 32) {
+    const int b = m.dof_bodyid[i];
+    sv6 buf = mul_inert(s_crb + 10 * b, ld6(s_cdof + 6 * i));
+    const int c0 = m.body_chain_adr[b], c1 = m.body_chain_adr[b + 1];
+    for (int c = c0; c < c1; c++) {
+      const int j = m.body_chain[c];
+      if (j > i) break;
+      float v = dot6(ld6(s_cdof + 6 * j), buf);
+      if (j == i) v += armature[i];
+      s_M[i * ld + j] = v;
+    }
+  }
+  // rne: bias force per body, then subtree sums
+  {
+    const bool grav = !(m.disableflags & B2S_DSBL_GRAVITY);
+    for (int b = lane; b < nb; b += 32) {
+      sv6 a = zero6();
+      if (grav) { a.v[3] = -m.gravity[0]; a.v[4] = -m.gravity[1]; a.v[5] = -m.gravity[2]; }
+      sv6 f = zero6(), fe = zero6();
+      if (b > 0) {
+        const int c0 = m.body_chain_adr[b], c1 = m.body_chain_adr[b + 1];
+        for (int c = c0; c < c1; c++) { const int j = m.body_chain[c]; axpy6(a, s_qvel[j], ld6(s_cdd + 6 * j)); }
+        const float* I = d.cinert + ((size_t)w * nb + b) * 10;
+        sv6 v = ld6(s_cvel + 6 * b);
+        f = mul_inert(I, a);
+        sv6 g = cross_force(v, mul_inert(I, v));
+        axpy6(f, 1.0f, g);
+        // external Cartesian wrench applied at xipos, as a spatial force about the root subtree COM
+        const float* x = d.xfrc_applied + ((size_t)w * nb + b) * 6;
+        v3 frc = ld3(x), trq = ld3(x + 3);
+        if (frc.x != 0.f || frc.y != 0.f || frc.z != 0.f || trq.x != 0.f || trq.y != 0.f || trq.z != 0.f) {
+          v3 off = ld3(d.xipos + ((size_t)w * nb + b) * 3) - ld3(d.subtree_com + ((size_t)w * nb + m.body_rootid[b]) * 3);
+          v3 t = trq + cross(off, frc);
+          fe.v[0] = t.x; fe.v[1] = t.y; fe.v[2] = t.z; fe.v[3] = frc.x; fe.v[4] = frc.y; fe.v[5] = frc.z;
+        }
+      }
+      st6(s_cfrc + 6 * b, f); st6(s_fext + 6 * b, fe);
+    }
+  }
+  __syncwarp();
+  // write M (symmetric, dense, row stride nvp) to HBM
+  for (int i = lane; i < nv * nvp; i += 32) {
+    const int r = i / nvp, c = i - r * nvp;
+    float v = 0.f;
+    if (c < nv) v = (c <= r) ? s_M[r * ld + c] : s_M[c * ld + r];
+    d.qM[(size_t)w * nv * nvp + i] = v;
+  }
+  // actuation (joint transmission)
+  if (!(m.disableflags & B2S_DSBL_ACTUATION)) {
+    const float* gainprm = m.actuator_gainprm.at(w);
+    const float* biasprm = m.actuator_biasprm.at(w);
+    for (int u = lane; u < m.nu; u += 32) {
+      const int j = m.actuator_trnid[u];
+      const float gear = m.actuator_gear[u];
+      const float len = gear * qpos[m.jnt_qposadr[j]], vel = gear * s_qvel[m.jnt_dofadr[j]];
+      float c = d.ctrl[(size_t)w * m.nu + u];
+      if (m.actuator_ctrllimited[u] && !(m.disableflags & B2S_DSBL_CLAMPCTRL)) c = clampf(c, m.actuator_ctrlrange[2 * u], m.actuator_ctrlrange[2 * u + 1]);
+      float gain = gainprm[3 * u];
+      if (m.actuator_gaintype[u] == B2S_GAIN_AFFINE) gain += gainprm[3 * u + 1] * len + gainprm[3 * u + 2] * vel;
+      float bias = 0.f;
+      if (m.actuator_biastype[u] == B2S_BIAS_AFFINE) bias = biasprm[3 * u] + biasprm[3 * u + 1] * len + biasprm[3 * u + 2] * vel;
+      float f = gain * c + bias;
+      if (m.actuator_forcelimited[u]) f = clampf(f, m.actuator_forcerange[2 * u], m.actuator_forcerange[2 * u + 1]);
+      d.actuator_length[(size_t)w * m.nu + u] = len;
+      d.actuator_velocity[(size_t)w * m.nu + u] = vel;
+      d.actuator_force[(size_t)w * m.nu + u] = f;
+      atomicAdd(&s_act[m.jnt_dofadr[j]], gear * f);
+    }
+  } else {
+    for (int u = lane; u < m.nu; u += 32) d.actuator_force[(size_t)w * m.nu + u] = 0.f;
+  }
+  __syncwarp();
+  // per-dof generalized forces: bias = cdof . sum_subtree(cfrc), applied = cdof . sum_subtree(fext)
+  {
+    const float* damping = m.dof_damping.at(w);
+    const float* stiff = m.jnt_stiffness.at(w);
+    const float* qspring = m.qpos_spring.at(w);
+    const bool passive = !(m.disableflags & B2S_DSBL_PASSIVE);
+    for (int i = lane; i < nv; i += 32) {
+      const int b = m.dof_bodyid[i], e = m.body_subtree_end[b];
+      sv6 fs = zero6(), es = zero6();
+      for (int j = b; j < e; j++) { axpy6(fs, 1.0f, ld6(s_cfrc + 6 * j)); axpy6(es, 1.0f, ld6(s_fext + 6 * j)); }
+      sv6 cd = ld6(s_cdof + 6 * i);
+      const float bias = dot6(cd, fs), ext = dot6(cd, es);
+      float pas = 0.f;
+      if (passive) {
+        const int j = m.dof_jntid[i], t = m.jnt_type[j];
+        if ((t == B2S_JNT_HINGE || t == B2S_JNT_SLIDE) && stiff[j] != 0.f) pas -= stiff[j] * (qpos[m.jnt_qposadr[j]] - qspring[m.jnt_qposadr[j]]);
+        pas -= damping[i] * s_qvel[i];
+      }
+      const float smooth = pas - bias + d.qfrc_applied[(size_t)w * nv + i] + s_act[i] + ext;
+      d.qfrc_bias[(size_t)w * nv + i] = bias;
+      d.qfrc_passive[(size_t)w * nv + i] = pas;
+      d.qfrc_actuator[(size_t)w * nv + i] = s_act[i];
+      d.qfrc_smooth[(size_t)w * nv + i] = smooth;
+      s_rhs[i] = smooth;
+    }
+  }
+  __syncwarp();
+  // factor M in shared memory and solve for the unconstrained acceleration
+  warp_cholesky(s_M, nv, ld, lane);
+  float b0 = lane < nv ? s_rhs[lane] : 0.f, b1 = lane + 32 < nv ? s_rhs[lane + 32] : 0.f;
+  warp_chol_solve(s_M, nv, ld, lane, b0, b1);
+  if (lane < nv) d.qacc_smooth[(size_t)w * nv + lane] = b0;
+  if (lane + 32 < nv) d.qacc_smooth[(size_t)w * nv + lane + 32] = b1;
+  (void)s_tmp;
+}
+
+// ---------------------------------------------------------------------------------------------- launchers
+void launch_position(const ModelDev& m, const DataDev& d, cudaStream_t st) {
+  const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
+  const size_t smem = (size_t)B2S_WARPS_PER_CTA * 22 * m.nbody * sizeof(float);
+  k_position<<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d);
+  b2s_count_launch();
+}
+void launch_dynamics(const ModelDev& m, const DataDev& d, cudaStream_t st) {
+  const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
+  const size_t smem = (size_t)B2S_WARPS_PER_CTA * dyn_smem_floats(m.nv, m.nvp, m.nbody) * sizeof(float);
+  k_dynamics<<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d);
+  b2s_count_launch();
+}
+size_t smem_position(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * 22 * m.nbody * sizeof(float); }
+size_t smem_dynamics(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * dyn_smem_floats(m.nv, m.nvp, m.nbody) * sizeof(float); }
+const void* fn_position() { return (const void*)k_position; }
+const void* fn_dynamics() { return (const void*)k_dynamics; }

@@ -1,0 +1,26 @@
+"""Shared helpers for the parity tests (seeded states, oracle/engine comparison)."""
+import numpy as np
+
+
+def g1_states(m, nworld, seed=0, spread=0.3, vel=0.5, zlo=0.70, zhi=0.80):
+  """Seeded G1 states around the knees-bent keyframe: joint noise, base height/tilt noise, random velocities."""
+  rng = np.random.default_rng(seed)
+  key = m.keys["robot/init_state"]
+  q0 = np.array(key["qpos"]); c0 = np.array(key["ctrl"])
+  qpos = np.tile(q0, (nworld, 1)); qvel = np.zeros((nworld, m.nv)); ctrl = np.tile(c0, (nworld, 1))
+  lo, hi = m.jnt_range[1:, 0], m.jnt_range[1:, 1]
+  for w in range(nworld):
+    s = spread * (w / max(nworld - 1, 1))
+    qpos[w, 7:] = np.clip(q0[7:] + rng.normal(0, s, m.nq - 7), lo - 0.05, hi + 0.05)
+    qpos[w, 2] = rng.uniform(zlo, zhi)
+    qpos[w, 0:2] = rng.normal(0, 1.0, 2)
+    ax = rng.normal(size=3); ax /= np.linalg.norm(ax)
+    ang = rng.normal(0, 0.15)
+    qpos[w, 3:7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
+    qvel[w] = rng.normal(0, vel, m.nv) * (w > 0)
+    ctrl[w] = c0 + rng.normal(0, 0.2, m.nu) * (w > 0)
+  return qpos, qvel, ctrl
+
+
+def contact_pairs(geom, n):
+  return sorted(map(tuple, np.asarray(geom).reshape(-1, 2)[:n].tolist()))
