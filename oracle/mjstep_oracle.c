@@ -635,13 +635,14 @@ void orc_make_constraint(const b2s_model_desc* m, orc_data* d) {
   d->nl[0] = nefc;
   /* contacts (mj_instantiateContact, pyramidal cone) */
   real* jp1 = (real*)malloc(sizeof(real)*nv*12); real* jr1 = jp1 + 3*nv; real* jp2 = jr1 + 3*nv; real* jr2 = jp2 + 3*nv;
+  int full = 0;  /* once the row budget overflows, this and all later contacts are dropped */
   for (int c = 0; c < d->ncon[0]; c++) {
     d->con_efc_address[c] = -1;
     if (m->opt_disableflags & B2S_DSBL_CONTACT) continue;
     if (d->con_dist[c] >= d->con_includemargin[c]) continue;
     int dim = d->con_dim[c];
     int nrow = dim == 1 ? 1 : 2*(dim - 1);
-    if (nefc + nrow > d->njmax) continue;
+    if (full || nefc + nrow > d->njmax) { full = 1; continue; }
     int g1 = d->con_geom[2*c], g2 = d->con_geom[2*c + 1];
     int b1 = m->geom_bodyid[g1], b2 = m->geom_bodyid[g2];
     const real* fr = d->con_frame + 9*c;

@@ -1,0 +1,198 @@
+"""Small MJCF fixtures (own models; same spirit as the fixture strings in the reference's tests,
+tests/test_contact_sensor.py:19-86, tests/test_entity_data.py:11-20, tests/test_sim.py:18-40)."""
+from asimov_mjlab_b200.mjcf import Spec
+
+SPHERE_DROP = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.002" integrator="euler"/>
+  <worldbody>
+    <body name="ground"><geom name="floor" type="plane" size="5 5 0.1" condim="1"/></body>
+    <body name="ball" pos="0 0 0.5">
+      <freejoint name="ball_joint"/>
+      <geom name="ball_geom" type="sphere" size="0.1" mass="2.0" condim="1"/>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
+FALLING_BOX = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.002"/>
+  <worldbody>
+    <body name="ground"><geom name="floor" type="plane" size="5 5 0.1"/></body>
+    <body name="box" pos="0 0 0.3" quat="0.98 0.1 0.15 0.05">
+      <freejoint name="box_joint"/>
+      <geom name="box_geom" type="box" size="0.1 0.08 0.06" mass="1.0"/>
+      <site name="box_site" pos="0.05 0 0.02"/>
+    </body>
+  </worldbody>
+  <sensor>
+    <gyro name="g" site="box_site"/>
+    <velocimeter name="v" site="box_site"/>
+    <accelerometer name="a" site="box_site"/>
+    <framepos name="p" objtype="site" objname="box_site"/>
+    <framequat name="q" objtype="body" objname="box"/>
+    <subtreelinvel name="slv" body="box"/>
+    <subtreeangmom name="sam" body="box"/>
+  </sensor>
+</mujoco>
+"""
+
+PENDULUM = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.001" integrator="euler"/>
+  <worldbody>
+    <body name="arm" pos="0 0 1">
+      <joint name="hinge" type="hinge" axis="0 1 0"/>
+      <geom name="rod" type="capsule" fromto="0 0 0 0 0 -0.5" size="0.02" mass="0" contype="0" conaffinity="0"/>
+      <geom name="bob" type="sphere" pos="0 0 -0.5" size="0.05" mass="1.0" contype="0" conaffinity="0"/>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
+SLIDER_PD = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.005" integrator="implicitfast" gravity="0 0 0"/>
+  <worldbody>
+    <body name="cart" pos="0 0 1">
+      <joint name="slide" type="slide" axis="1 0 0" range="-10 10"/>
+      <geom name="cart_geom" type="box" size="0.1 0.1 0.1" mass="3.0" contype="0" conaffinity="0"/>
+    </body>
+  </worldbody>
+  <actuator>
+    <position name="pd" joint="slide" kp="50" kv="4"/>
+  </actuator>
+</mujoco>
+"""
+
+SPINNER = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.002" integrator="euler" gravity="0 0 0"/>
+  <worldbody>
+    <body name="ball" pos="0 0 1">
+      <freejoint name="free"/>
+      <geom name="ball_geom" type="sphere" size="0.1" mass="1.0" contype="0" conaffinity="0"/>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
+TWO_SPHERES = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option gravity="0 0 0"/>
+  <worldbody>
+    <body name="a" pos="0 0 1"><freejoint/><geom name="ga" type="sphere" size="0.1" mass="1" condim="1"/></body>
+    <body name="b" pos="0.15 0.0 1.0"><freejoint/><geom name="gb" type="sphere" size="0.08" mass="1" condim="1"/></body>
+  </worldbody>
+</mujoco>
+"""
+
+CAPSULE_ON_PLANE = """
+<mujoco>
+  <compiler angle="radian"/>
+  <worldbody>
+    <body name="ground"><geom name="floor" type="plane" size="5 5 0.1"/></body>
+    <body name="cap" pos="0 0 0.045">
+      <freejoint/>
+      <geom name="cap_geom" type="capsule" fromto="-0.2 0 0 0.2 0 0" size="0.05" mass="1"/>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
+LIMITED_HINGE = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.002"/>
+  <worldbody>
+    <body name="arm" pos="0 0 1">
+      <joint name="hinge" type="hinge" axis="0 1 0" range="-0.3 0.4" damping="0.1"/>
+      <geom name="bob" type="sphere" pos="0.3 0 0" size="0.05" mass="1.0" contype="0" conaffinity="0"/>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
+# free-floating multi-geom robot over a plane: spheres + capsules + a box trunk (plane-box, plane-capsule, plane-sphere)
+LEGGED = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.004" integrator="implicitfast"/>
+  <default>
+    <default class="leg"><geom type="capsule" size="0.02" friction="0.8 0.01 0.001" conaffinity="0"/></default>
+  </default>
+  <worldbody>
+    <body name="ground"><geom name="floor" type="plane" size="5 5 0.1"/></body>
+    <body name="trunk" pos="0 0 0.35" childclass="leg">
+      <freejoint name="root"/>
+      <geom name="trunk_geom" type="box" size="0.2 0.1 0.05" mass="4.0"/>
+      <geom name="head_geom" type="sphere" size="0.07" pos="0.25 0 0.05" mass="0.4"/>
+      <site name="imu" pos="0.02 0 0.01"/>
+      <body name="fl" pos="0.15 0.1 -0.05">
+        <joint name="fl_hip" axis="0 1 0" range="-1 1" armature="0.01" damping="0.2"/>
+        <geom name="fl_thigh" fromto="0 0 0 0 0 -0.15" mass="0.3"/>
+        <body name="fl2" pos="0 0 -0.15">
+          <joint name="fl_knee" axis="0 1 0" range="-2 0" armature="0.01"/>
+          <geom name="fl_shin" fromto="0 0 0 0 0 -0.15" mass="0.2"/>
+          <geom name="fl_foot" type="sphere" size="0.03" pos="0 0 -0.15" mass="0.05" condim="3" priority="1" friction="0.6 0.005 0.0001"/>
+        </body>
+      </body>
+      <body name="fr" pos="0.15 -0.1 -0.05">
+        <joint name="fr_hip" axis="0 1 0" range="-1 1" armature="0.01" damping="0.2"/>
+        <geom name="fr_thigh" fromto="0 0 0 0 0 -0.15" mass="0.3"/>
+        <body name="fr2" pos="0 0 -0.15">
+          <joint name="fr_knee" axis="0 1 0" range="-2 0" armature="0.01"/>
+          <geom name="fr_shin" fromto="0 0 0 0 0 -0.15" mass="0.2"/>
+          <geom name="fr_foot" type="sphere" size="0.03" pos="0 0 -0.15" mass="0.05" condim="3" priority="1" friction="0.6 0.005 0.0001"/>
+        </body>
+      </body>
+      <body name="rear" pos="-0.15 0 -0.05">
+        <joint name="rear_slide" type="slide" axis="0 0 1" range="-0.05 0.05" stiffness="200" damping="2"/>
+        <geom name="rear_leg" fromto="0 0 0 0 0 -0.25" mass="0.4"/>
+      </body>
+    </body>
+  </worldbody>
+  <actuator>
+    <position name="fl_hip" joint="fl_hip" kp="20" kv="1" inheritrange="1" forcerange="-10 10"/>
+    <position name="fl_knee" joint="fl_knee" kp="20" kv="1" inheritrange="1" forcerange="-10 10"/>
+    <position name="fr_hip" joint="fr_hip" kp="20" kv="1" inheritrange="1" forcerange="-10 10"/>
+    <motor name="fr_knee" joint="fr_knee" ctrlrange="-5 5"/>
+  </actuator>
+  <sensor>
+    <gyro name="gyro" site="imu"/>
+    <accelerometer name="acc" site="imu"/>
+    <jointpos name="jp" joint="fl_knee"/>
+    <jointvel name="jv" joint="fl_knee"/>
+    <actuatorfrc name="af" actuator="fl_hip"/>
+    <subtreecom name="com" body="trunk"/>
+    <framelinvel name="flv" objtype="body" objname="fl2"/>
+    <frameangvel name="fav" objtype="xbody" objname="fl2"/>
+  </sensor>
+</mujoco>
+"""
+
+
+def compile_xml(xml, contact_sensors=()):
+  spec = Spec.from_string(xml)
+  for kw in contact_sensors:
+    spec.add_sensor(**kw)
+  return spec.compile()
+
+
+def legged_with_contact_sensors():
+  """LEGGED plus contact sensors in every reduce mode / object type (reference contact_sensor.py:16-47)."""
+  S = []
+  allbits = 1 | 2 | 4 | 8 | 16 | 32 | 64
+  S.append(dict(name="c_feet_net", type="contact", objtype="xbody", objname="fl", reftype="body", refname="ground", intprm=[1 | 2, 3, 1]))
+  S.append(dict(name="c_trunk_none", type="contact", objtype="body", objname="trunk", intprm=[allbits, 0, 2]))
+  S.append(dict(name="c_any_mindist", type="contact", objtype="xbody", objname="trunk", intprm=[1 | 8 | 16, 1, 3]))
+  S.append(dict(name="c_any_maxforce", type="contact", objtype="xbody", objname="trunk", reftype="geom", refname="floor", intprm=[1 | 2 | 32, 2, 2]))
+  S.append(dict(name="c_geom", type="contact", objtype="geom", objname="fr_foot", intprm=[1 | 2 | 4, 3, 1]))
+  return compile_xml(LEGGED, S)

@@ -1,0 +1,288 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle, on a B200.
+
+Bars (north_star): contact counts, contact pair indices and constraint counts bit-exact; qpos/qvel/qacc/
+efc_force within the fp32 tolerances written below, after 1 step and after a short horizon.
+"""
+import numpy as np
+import pytest
+
+import fixtures as fx
+from util import contact_pairs, g1_states
+
+pytestmark = pytest.mark.gpu
+
+# relative-to-field-scale tolerances (fp32; engine and oracle differ only in summation order)
+TOL_FORWARD = dict(xpos=2e-6, xquat=2e-6, xmat=2e-6, xipos=2e-6, ximat=2e-6, geom_xpos=2e-6, geom_xmat=2e-6, site_xpos=2e-6,
+                   site_xmat=2e-6, subtree_com=2e-6, cinert=5e-6, cdof=5e-6, cvel=2e-5, cdof_dot=2e-5, qfrc_bias=2e-5,
+                   qfrc_passive=1e-6, actuator_force=1e-5, qfrc_actuator=1e-5, qfrc_smooth=2e-5, qacc_smooth=1e-4,
+                   qacc=5e-4, qfrc_constraint=5e-4, cacc=5e-4, sensordata=5e-4)
+TOL_STEP1 = dict(qpos=1e-6, qvel=2e-4, qacc_warmstart=5e-4)
+
+
+def _setup(m, W, qpos=None, qvel=None, ctrl=None, ls_parallel=True, nconmax=50, njmax=300, dtype="f32"):
+  import torch
+  from asimov_mjlab_b200 import engine
+  from asimov_mjlab_b200.hostmodel import HostData
+  from oracle import Oracle
+  m.opt.ls_parallel = bool(ls_parallel)
+  M = engine.put_model(m, "cuda:0")
+  D = engine.put_data(m, HostData(m), W, nconmax, njmax, model=M)
+  orc = Oracle(m, dtype, D.nconmax, D.njmax, ls_parallel=int(ls_parallel))
+  worlds = []
+  for w in range(W):
+    worlds.append(orc.new_world(None if qpos is None else qpos[w], None if qvel is None else qvel[w], None if ctrl is None else ctrl[w]))
+  for name, arr in (("qpos", qpos), ("qvel", qvel), ("ctrl", ctrl)):
+    if arr is not None:
+      getattr(D, name)[:] = torch.as_tensor(np.asarray(arr), dtype=torch.float32, device="cuda:0")
+  return engine, M, D, orc, worlds
+
+
+def _rel_err(D, worlds, f):
+  g = getattr(D, f).cpu().numpy().reshape(len(worlds), -1).astype(np.float64)
+  o = np.stack([w[f] for w in worlds]).reshape(len(worlds), -1).astype(np.float64)
+  return np.abs(g - o).max() / (1e-6 + np.abs(o).max())
+
+
+def _check_counts(D, worlds):
+  ncon = D.ncon.cpu().numpy(); nefc = D.nefc.cpu().numpy(); nl = D.nl.cpu().numpy()
+  assert ncon.tolist() == [int(w["ncon"][0]) for w in worlds]
+  assert nefc.tolist() == [int(w["nefc"][0]) for w in worlds]
+  assert nl.tolist() == [int(w["nl"][0]) for w in worlds]
+  geom = D.contact_geom.cpu().numpy()
+  dim = D.contact_dim.cpu().numpy()
+  adr = D.contact_efc_address.cpu().numpy()
+  for i, w in enumerate(worlds):
+    n = int(ncon[i])
+    # same ORDER, not just the same multiset: both sides are deterministic (pair order)
+    assert geom[i, :n].reshape(-1).tolist() == w["con_geom"][: 2 * n].tolist()
+    assert dim[i, :n].tolist() == w["con_dim"][:n].tolist()
+    assert adr[i, :n].tolist() == w["con_efc_address"][:n].tolist()
+    assert contact_pairs(geom[i], n) == contact_pairs(w["con_geom"], n)
+
+
+@pytest.mark.parametrize("ls_parallel", [True, False])
+def test_g1_forward_matches_oracle(g1, ls_parallel):
+  W = 32
+  qpos, qvel, ctrl = g1_states(g1, W, seed=1)
+  engine, M, D, orc, worlds = _setup(g1, W, qpos, qvel, ctrl, ls_parallel)
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  _check_counts(D, worlds)
+  assert sum(int(w["ncon"][0]) for w in worlds) > 100   # the case exercises contacts
+  for f, tol in TOL_FORWARD.items():
+    assert _rel_err(D, worlds, f) < tol, f
+  # efc arrays on the active rows
+  nefc = D.nefc.cpu().numpy()
+  J = D.efc_J.cpu().numpy(); Dg = D.efc_D.cpu().numpy(); ar = D.efc_aref.cpu().numpy(); fo = D.efc_force.cpu().numpy()
+  for i, w in enumerate(worlds):
+    n = int(nefc[i])
+    if n == 0:
+      continue
+    Jo = w["efc_J"][: n * g1.nv].reshape(n, g1.nv)
+    assert np.abs(J[i, :n, : g1.nv] - Jo).max() < 1e-5 * (1 + np.abs(Jo).max())
+    assert np.allclose(Dg[i, :n], w["efc_D"][:n], rtol=1e-5)
+    assert np.abs(ar[i, :n] - w["efc_aref"][:n]).max() < 1e-4 * (1 + np.abs(w["efc_aref"][:n]).max())
+    assert np.abs(fo[i, :n] - w["efc_force"][:n]).max() < 1e-3 * (1 + np.abs(w["efc_force"][:n]).max())
+  assert D.solver_niter.cpu().numpy().tolist() == [int(w["solver_niter"][0]) for w in worlds]
+
+
+@pytest.mark.parametrize("ls_parallel", [True, False])
+def test_g1_one_step_and_short_horizon(g1, ls_parallel):
+  import torch
+  W = 16
+  qpos, qvel, ctrl = g1_states(g1, W, seed=2, spread=0.15, vel=0.2)
+  engine, M, D, orc, worlds = _setup(g1, W, qpos, qvel, ctrl, ls_parallel)
+  engine.step(M, D)
+  for w in worlds:
+    orc.step(w)
+  _check_counts(D, worlds)
+  for f, tol in TOL_STEP1.items():
+    assert _rel_err(D, worlds, f) < tol, f
+  assert np.allclose(D.time.cpu().numpy(), 0.005)
+  # short horizon: 20 more steps; contact sets must still agree exactly, state within a looser bound
+  engine.step(M, D, 20)
+  torch.cuda.synchronize()
+  for w in worlds:
+    orc.step(w, 20)
+  _check_counts(D, worlds)
+  assert _rel_err(D, worlds, "qpos") < 2e-4
+  assert _rel_err(D, worlds, "qvel") < 2e-2
+
+
+def test_g1_friction_domain_randomisation_per_world(g1):
+  """expand_model_fields + per-world geom_friction (reference events.py:228-253, randomization.py:20-54)."""
+  import torch
+  from oracle import Oracle
+  W = 8
+  key = g1.keys["robot/init_state"]
+  qpos = np.tile(key["qpos"], (W, 1)); qpos[:, 2] = 0.74
+  qvel = np.zeros((W, g1.nv)); qvel[:, 0] = 0.5   # sliding: friction matters
+  ctrl = np.tile(key["ctrl"], (W, 1))
+  engine, M, D, _, _ = _setup(g1, W, qpos, qvel, ctrl, True)
+  assert M.geom_friction.shape == (W, g1.ngeom, 3) and M.geom_friction.stride(0) == 0
+  engine.expand_model_fields(M, W, ["geom_friction"])
+  assert M.geom_friction.stride(0) == g1.ngeom * 3
+  rng = np.random.default_rng(0)
+  foot = [i for i, n in enumerate(g1.names["geom"]) if "foot" in n]
+  fr = rng.uniform(0.3, 1.2, size=(W, len(foot))).astype(np.float32)
+  M.geom_friction[:, foot, 0] = torch.as_tensor(fr, device="cuda:0")
+  engine.step(M, D, 10)
+  qv = D.qvel.cpu().numpy()
+  for w in range(W):
+    gf = g1.geom_friction.copy(); gf[foot, 0] = fr[w]
+    orc = Oracle(g1, "f32", 50, 300, overrides={"geom_friction": gf}, ls_parallel=1)
+    ow = orc.new_world(qpos[w], qvel[w], ctrl[w])
+    orc.step(ow, 10)
+    assert np.abs(qv[w] - ow["qvel"]).max() < 5e-3 * (1 + np.abs(ow["qvel"]).max())
+  assert np.std(qv[:, 0]) > 1e-4   # different friction -> different sliding speed
+
+
+@pytest.mark.parametrize("name", ["SPHERE_DROP", "FALLING_BOX", "PENDULUM", "SLIDER_PD", "SPINNER", "TWO_SPHERES",
+                                  "CAPSULE_ON_PLANE", "LIMITED_HINGE", "LEGGED"])
+def test_small_fixtures_rollout(name):
+  """Every joint type, primitive pair and sensor of the small fixtures, 200 steps, both sides from the same seed."""
+  import torch
+  m = fx.compile_xml(getattr(fx, name))
+  W = 4
+  rng = np.random.default_rng(5)
+  qpos = np.tile(m.qpos0, (W, 1)); qvel = rng.normal(0, 0.3, (W, m.nv)); ctrl = rng.normal(0, 0.3, (W, m.nu))
+  if name == "LIMITED_HINGE":
+    qpos[:, 0] = [-0.35, 0.0, 0.39, 0.45]
+  if name in ("FALLING_BOX", "LEGGED", "SPHERE_DROP"):
+    qpos[:, 2] += rng.uniform(-0.05, 0.05, W)
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=16, njmax=64)
+  for chunk in (1, 9, 40, 150):
+    engine.step(M, D, chunk)
+    torch.cuda.synchronize()
+    for w in worlds:
+      orc.step(w, chunk)
+    _check_counts(D, worlds)
+    assert _rel_err(D, worlds, "qpos") < 5e-4, name
+    assert _rel_err(D, worlds, "qvel") < 2e-2, name
+    if m.nsensordata:
+      assert _rel_err(D, worlds, "sensordata") < 2e-2, name
+
+
+def test_contact_sensor_modes_match_oracle():
+  import torch
+  m = fx.legged_with_contact_sensors()
+  W = 6
+  rng = np.random.default_rng(9)
+  qpos = np.tile(m.qpos0, (W, 1)); qpos[:, 2] = np.linspace(0.2, 0.34, W)
+  qpos[:, 7:] += rng.normal(0, 0.2, (W, m.nq - 7))
+  qvel = rng.normal(0, 0.2, (W, m.nv)); ctrl = rng.normal(0, 0.3, (W, m.nu))
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=24, njmax=96)
+  seen = 0
+  for _ in range(30):
+    engine.step(M, D, 5)
+    torch.cuda.synchronize()
+    for w in worlds:
+      orc.step(w, 5)
+    _check_counts(D, worlds)
+    sd = D.sensordata.cpu().numpy()
+    so = np.stack([w["sensordata"] for w in worlds])
+    assert np.abs(sd - so).max() < 2e-2 * (1 + np.abs(so).max())
+    adr = int(m.sensor_adr[m.name2id("sensor", "c_trunk_none")])
+    seen += int((so[:, adr] > 0).sum())
+  assert seen > 0   # the trunk touched the ground at some point: the contact paths were exercised
+
+
+def test_zero_copy_views_and_readonly_struct(g1):
+  """Boundary semantics pinned by the reference: aliasing + pointer stability (tests/test_sim_data.py:31-64),
+  rebinding raises (:67-75), derived fields are stale until forward() (tests/test_entity_data.py:135-158)."""
+  import torch
+  engine, M, D, orc, worlds = _setup(g1, 4)
+  p = D.qpos.data_ptr()
+  D.qpos[:, 2] = 1.25
+  assert D.qpos.data_ptr() == p and float(D.qpos[0, 2]) == 1.25
+  with pytest.raises(AttributeError):
+    D.qpos = torch.zeros_like(D.qpos)
+  with pytest.raises(AttributeError):
+    M.geom_friction = torch.zeros(1)
+  engine.forward(M, D)
+  z0 = float(D.xpos[0, 2, 2])
+  assert z0 == pytest.approx(1.25, abs=1e-6)
+  D.qpos[:, 2] = 2.0
+  assert float(D.xpos[0, 2, 2]) == pytest.approx(z0)        # stale
+  engine.forward(M, D)
+  assert float(D.xpos[0, 2, 2]) == pytest.approx(2.0, abs=1e-6)
+  assert D.xpos.shape == (4, g1.nbody, 3) and D.xmat.shape == (4, g1.nbody, 3, 3) and D.cvel.shape == (4, g1.nbody, 6)
+  assert D.sensordata.shape == (4, g1.nsensordata) and D.time.shape == (4,) and D.nworld == 4
+  assert D.contact.dist.shape == (4, D.nconmax) and D.efc.J.shape[:2] == (4, D.njmax)
+  assert M.opt.ls_parallel is True and M.opt.iterations == 10 and M.opt.integrator == 3
+
+
+def test_unsupported_features_raise():
+  from asimov_mjlab_b200 import engine
+  m = fx.compile_xml(fx.SPHERE_DROP)
+  m.opt.cone = 1
+  with pytest.raises(engine.BackendError, match="pyramidal"):
+    engine.put_model(m)
+  m.opt.cone = 0
+  m.opt.solver = 1
+  with pytest.raises(engine.BackendError, match="Newton"):
+    engine.put_model(m)
+  m.opt.solver = 2
+  m.dof_frictionloss = m.dof_frictionloss + 0.1
+  with pytest.raises(engine.BackendError, match="frictionloss"):
+    engine.put_model(m)
+  box2 = fx.FALLING_BOX.replace('<body name="ground">', '<body name="b2" pos="0 0 1"><freejoint/><geom type="box" size=".1 .1 .1"/></body><body name="ground">')
+  with pytest.raises(engine.BackendError, match="box-box"):
+    engine.put_model(fx.compile_xml(box2))
+  with pytest.raises(engine.BackendError, match="CUDA"):
+    engine.put_model(fx.compile_xml(fx.SPHERE_DROP), "cpu")
+
+
+def test_simulation_graphs_and_decimation(g1):
+  """Simulation boundary: graph replay == eager launches; one graph per decimation == 4 step graphs."""
+  import torch
+  from asimov_mjlab_b200.sim import MujocoCfg, Simulation, SimulationCfg
+  cfg = SimulationCfg(nconmax=50, njmax=300, mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20))
+  W = 64
+  qpos, qvel, ctrl = g1_states(g1, W, seed=4)
+  sims = [Simulation(W, cfg, g1, "cuda:0") for _ in range(2)]
+  for s in sims:
+    s.data.qpos[:] = torch.as_tensor(qpos, dtype=torch.float32, device="cuda:0")
+    s.data.qvel[:] = torch.as_tensor(qvel, dtype=torch.float32, device="cuda:0")
+    s.data.ctrl[:] = torch.as_tensor(ctrl, dtype=torch.float32, device="cuda:0")
+  sims[1].create_graph(decimation=4)
+  for _ in range(4):
+    sims[0].step()
+  sims[1].step_decimation()
+  torch.cuda.synchronize()
+  assert torch.equal(sims[0].data.qpos, sims[1].data.qpos) and torch.equal(sims[0].data.qvel, sims[1].data.qvel)
+  assert float(sims[0].data.time[0]) == pytest.approx(0.02)
+  sims[0].forward()
+  assert sims[0].model.opt.timestep[0] == pytest.approx(0.005)
+  with pytest.raises(ValueError):
+    sims[0].expand_model_fields(("not_a_field",))
+
+
+def test_full_size_determinism_and_world_independence(g1):
+  """BASELINE config size (4096 worlds): bit-identical replays, and a world's result does not depend on its
+  neighbours (identical inputs in different slots give bit-identical outputs)."""
+  import torch
+  from asimov_mjlab_b200 import engine
+  from asimov_mjlab_b200.hostmodel import HostData
+  W = 4096
+  qpos, qvel, ctrl = g1_states(g1, 64, seed=6)
+  reps = W // 64
+  g1.opt.ls_parallel = True
+  M = engine.put_model(g1)
+  outs = []
+  for trial in range(2):
+    D = engine.put_data(g1, HostData(g1), W, 50, 300, model=M)
+    D.qpos[:] = torch.as_tensor(np.tile(qpos, (reps, 1)), dtype=torch.float32, device="cuda:0")
+    D.qvel[:] = torch.as_tensor(np.tile(qvel, (reps, 1)), dtype=torch.float32, device="cuda:0")
+    D.ctrl[:] = torch.as_tensor(np.tile(ctrl, (reps, 1)), dtype=torch.float32, device="cuda:0")
+    engine.step(M, D, 8)
+    torch.cuda.synchronize()
+    outs.append((D.qpos.clone(), D.qvel.clone(), D.sensordata.clone(), D.ncon.clone(), D.nefc.clone()))
+    del D
+  for a, b in zip(*outs):
+    assert torch.equal(a, b)
+  q = outs[0][0].view(reps, 64, -1)
+  assert torch.equal(q, q[0:1].expand_as(q))
+  assert not torch.isnan(outs[0][1]).any()
+  assert int(outs[0][3].max()) <= 50 and int(outs[0][4].max()) <= 300

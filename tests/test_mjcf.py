@@ -1,0 +1,124 @@
+"""Model on-ramp: MJCF subset compiler and the mjlab scene assembly (host logic, CPU)."""
+import numpy as np
+import pytest
+
+import fixtures as fx
+from asimov_mjlab_b200 import hostmodel, scenes
+from asimov_mjlab_b200.mjcf import Spec
+
+
+def test_g1_flat_dimensions_match_survey_table(g1):
+  # SURVEY.md §8.0 (hand-derived from the MJCF and cfg code)
+  assert (g1.nq, g1.nv, g1.nu, g1.na) == (36, 35, 29, 0)
+  assert g1.nbody == 32 and g1.ngeom == 69 and g1.nsite == 6 and g1.nsensordata == 21
+  col = (g1.geom_contype != 0) | (g1.geom_conaffinity != 0)
+  assert int(col.sum()) == 34                      # 33 robot collision geoms + the plane
+  types = g1.geom_type[col]
+  assert int((types == 3).sum()) == 31 and int((types == 2).sum()) == 2 and int((types == 0).sum()) == 1
+  assert g1.names["body"][:3] == ["world", "terrain", "robot/pelvis"]
+  assert g1.opt.timestep == 0.005 and g1.opt.integrator == 3 and g1.opt.iterations == 10 and g1.opt.ls_iterations == 20
+  assert g1.nexclude == 4 and int(g1.jnt_limited.sum()) == 29
+
+
+def test_g1_collision_and_actuator_edits(g1):
+  names = g1.names["geom"]
+  foot = [i for i, n in enumerate(names) if "foot" in n and n.endswith("_collision")]
+  assert len(foot) == 14
+  assert set(g1.geom_condim[foot]) == {3} and set(g1.geom_priority[foot]) == {1}
+  assert np.allclose(g1.geom_friction[foot, 0], 0.6) and np.allclose(g1.geom_friction[foot, 1], 0.005)
+  other = [i for i, n in enumerate(names) if n.endswith("_collision") and "foot" not in n]
+  assert set(g1.geom_condim[other]) == {1}
+  vis = [i for i, n in enumerate(names) if not n.endswith("_collision") and n != "terrain"]
+  assert not g1.geom_contype[vis].any() and not g1.geom_conaffinity[vis].any()
+  # position actuators: kp on ctrl, affine bias (0, -kp, -kd), ctrlrange inherited from the joint range
+  kp = g1.actuator_gainprm[:, 0]
+  assert np.allclose(g1.actuator_biasprm[:, 1], -kp) and (g1.actuator_biasprm[:, 2] < 0).all()
+  j = g1.actuator_trnid[:, 0]
+  assert np.allclose(g1.actuator_ctrlrange, g1.jnt_range[j]) and g1.actuator_ctrllimited.all() and g1.actuator_forcelimited.all()
+  assert (g1.dof_armature[6:] > 0).all() and np.allclose(g1.dof_armature[:6], 0)
+  hip = g1.names["actuator"].index("robot/left_hip_pitch_joint")
+  assert g1.actuator_forcerange[hip].tolist() == [-88.0, 88.0]
+  assert kp[hip] == pytest.approx(scenes.G1_ARM_7520_14 * (20 * 3.1415926535) ** 2)
+
+
+def test_g1_contact_sensor_layout(g1):
+  names = g1.names["sensor"]
+  assert names[:4] == ["robot/imu_ang_vel", "robot/imu_lin_vel", "robot/imu_lin_acc", "robot/root_angmom"]
+  assert names[4:] == ["feet_ground_contact_left_ankle_roll_link_found", "feet_ground_contact_left_ankle_roll_link_force",
+                       "feet_ground_contact_right_ankle_roll_link_found", "feet_ground_contact_right_ankle_roll_link_force",
+                       "self_collision_pelvis_found"]
+  assert g1.sensor_dim.tolist() == [3, 3, 3, 3, 1, 3, 1, 3, 1]
+  assert g1.sensor_intprm[4].tolist() == [1, 3, 1] and g1.sensor_intprm[5].tolist() == [2, 3, 1] and g1.sensor_intprm[8].tolist() == [1, 0, 1]
+  assert g1.sensor_objtype[4] == 2 and g1.sensor_reftype[4] == 1 and g1.names["body"][g1.sensor_refid[4]] == "terrain"
+
+
+def test_inertia_from_geoms_closed_forms():
+  m = fx.compile_xml(fx.FALLING_BOX)
+  b = m.name2id("body", "box")
+  assert m.body_mass[b] == pytest.approx(1.0)
+  a, bb, c = 0.1, 0.08, 0.06
+  assert np.allclose(m.body_inertia[b], [(bb*bb + c*c) / 3, (a*a + c*c) / 3, (a*a + bb*bb) / 3])
+  m = fx.compile_xml(fx.CAPSULE_ON_PLANE)
+  r, h = 0.05, 0.2
+  vc, vs = np.pi * r * r * 2 * h, 4 / 3 * np.pi * r ** 3
+  izz = (vc * r * r / 2 + vs * 0.4 * r * r) / (vc + vs)
+  assert m.body_inertia[2, 2] == pytest.approx(izz)
+  assert m.geom_size[1, 1] == pytest.approx(0.2) and np.allclose(m.geom_pos[1], 0)
+  # fromto puts the capsule z axis along the segment
+  R = hostmodel._q2m(m.geom_quat[1])
+  assert abs(R[0, 2]) == pytest.approx(1.0)
+  assert m.geom_rbound[1] == pytest.approx(0.25)
+
+
+def test_multi_geom_body_principal_axes():
+  m = fx.compile_xml(fx.LEGGED)
+  b = m.name2id("body", "trunk")
+  assert m.body_mass[b] == pytest.approx(4.4)
+  assert np.all(np.diff(m.body_inertia[b]) <= 1e-12)        # sorted descending
+  R = hostmodel._q2m(m.body_iquat[b])
+  assert np.allclose(R @ R.T, np.eye(3), atol=1e-12) and np.linalg.det(R) == pytest.approx(1.0)
+  assert m.body_subtreemass[b] == pytest.approx(4.4 + 2 * (0.3 + 0.2 + 0.05) + 0.4)
+  assert m.dof_parentid.tolist() == [-1, 0, 1, 2, 3, 4, 5, 6, 5, 8, 5]
+  assert m.body_weldid[1] == 0 and m.body_rootid[b] == b
+  # invweight0 of a free body chain is positive and finite
+  assert (m.dof_invweight0 > 0).all() and np.isfinite(m.body_invweight0).all()
+
+
+def test_defaults_classes_degrees_and_limits():
+  xml = """
+  <mujoco>
+    <default><joint damping="0.5"/><default class="a"><joint armature="0.1" range="-90 90"/></default></default>
+    <worldbody><body name="b" pos="0 0 1">
+      <joint name="j0" axis="1 0 0"/>
+      <joint name="j1" class="a" axis="0 1 0"/>
+      <geom type="sphere" size="0.1"/>
+    </body></worldbody>
+  </mujoco>"""
+  m = Spec.from_string(xml).compile()
+  assert m.dof_damping.tolist() == [0.5, 0.5] and m.dof_armature.tolist() == [0.0, 0.1]
+  assert m.jnt_limited.tolist() == [0, 1]
+  assert np.allclose(m.jnt_range[1], [-np.pi / 2, np.pi / 2])     # default angle unit is degree
+  assert m.body_mass[1] == pytest.approx(1000 * 4 / 3 * np.pi * 1e-3)
+
+
+def test_unsupported_mjcf_raises():
+  with pytest.raises(NotImplementedError):
+    Spec.from_string("<mujoco><tendon><fixed name='t'/></tendon></mujoco>")
+  with pytest.raises(NotImplementedError):
+    Spec.from_string("<mujoco><worldbody><body><geom type='mesh' mesh='m'/></body></worldbody></mujoco>").compile()
+
+
+def test_model_blob_round_trip(tmp_path, g1):
+  p = tmp_path / "g1.npz"
+  scenes.save_model(g1, p)
+  m2 = scenes.load_model(p)
+  for k, v in g1.__dict__.items():
+    if isinstance(v, np.ndarray):
+      assert np.array_equal(v, getattr(m2, k)), k
+  assert m2.names == g1.names and m2.opt.timestep == g1.opt.timestep and m2.stat.meaninertia == g1.stat.meaninertia
+
+
+def test_env_origin_grid_matches_reference_formula():
+  o = scenes.env_origins_grid(16, 2.5)
+  assert o.shape == (16, 3) and np.allclose(o.mean(axis=0), 0)
+  assert sorted(set(np.round(o[:, 0], 6))) == [-3.75, -1.25, 1.25, 3.75]

@@ -1,0 +1,191 @@
+"""Known-answer tests that pin the CPU oracle (parity is otherwise unpinned: SURVEY.md §8c lists these)."""
+import numpy as np
+import pytest
+from scipy.optimize import brentq
+
+import fixtures as fx
+from asimov_mjlab_b200 import hostmodel
+from oracle import Oracle
+
+
+def test_free_fall_matches_semi_implicit_euler_closed_form():
+  m = fx.compile_xml(fx.SPINNER)
+  m.opt.gravity = np.array([0.0, 0.0, -9.81])
+  orc = Oracle(m, "f64")
+  w = orc.new_world()
+  n, dt, g = 200, m.opt.timestep, 9.81
+  orc.step(w, n)
+  assert w["qvel"][2] == pytest.approx(-g * n * dt, rel=1e-12)
+  assert w["qpos"][2] == pytest.approx(1.0 - g * dt * dt * n * (n + 1) / 2, rel=1e-12)
+  assert w["time"][0] == pytest.approx(n * dt)
+
+
+def test_quaternion_integration_of_constant_body_rate():
+  m = fx.compile_xml(fx.SPINNER)
+  orc = Oracle(m, "f64")
+  omega = np.array([0.3, -0.5, 0.8])
+  w = orc.new_world(qvel=np.concatenate([np.zeros(3), omega]))
+  n = 500
+  orc.step(w, n)
+  ang = np.linalg.norm(omega) * n * m.opt.timestep
+  expect = np.concatenate([[np.cos(ang / 2)], omega / np.linalg.norm(omega) * np.sin(ang / 2)])
+  assert np.allclose(w["qpos"][3:7], expect, atol=1e-10)
+  assert np.allclose(w["qvel"][3:], omega, atol=1e-12)   # sphere inertia: no precession
+
+
+def test_pendulum_energy_and_period():
+  m = fx.compile_xml(fx.PENDULUM)
+  orc = Oracle(m, "f64")
+  th0 = 0.2
+  w = orc.new_world(qpos=[th0])
+  orc.forward(w)
+  M = w["qM"][0]
+  L = 0.5
+  # point mass at L plus sphere inertia 2/5 m r^2
+  assert M == pytest.approx(1.0 * L * L + 0.4 * 0.05 ** 2, rel=1e-9)
+  period = 2 * np.pi * np.sqrt(M / (9.81 * L)) * (1 + th0 ** 2 / 16)
+  qs = []
+  for _ in range(int(1.5 * period / m.opt.timestep)):
+    orc.step(w)
+    qs.append(w["qpos"][0])
+  qs = np.array(qs)
+  # first return to a maximum after t = 0
+  k = np.argmax(qs[int(0.5 * period / m.opt.timestep):]) + int(0.5 * period / m.opt.timestep)
+  assert k * m.opt.timestep == pytest.approx(period, rel=5e-3)
+  assert qs[k] == pytest.approx(th0, rel=2e-2)
+
+
+def test_pd_actuator_one_implicitfast_step_closed_form():
+  m = fx.compile_xml(fx.SLIDER_PD)
+  orc = Oracle(m, "f64")
+  q0, v0, c = 0.1, -0.3, 0.5
+  w = orc.new_world(qpos=[q0], qvel=[v0], ctrl=[c])
+  orc.step(w)
+  mass, kp, kv, dt = 3.0, 50.0, 4.0, 0.005
+  f = kp * (c - q0) - kv * v0
+  assert w["actuator_force"][0] == pytest.approx(f)
+  assert w["qacc"][0] == pytest.approx(f / mass)
+  a_impl = f / (mass + dt * kv)
+  assert w["qvel"][0] == pytest.approx(v0 + dt * a_impl, rel=1e-12)
+  assert w["qpos"][0] == pytest.approx(q0 + dt * (v0 + dt * a_impl), rel=1e-12)
+
+
+def test_two_sphere_contact_geometry():
+  m = fx.compile_xml(fx.TWO_SPHERES)
+  orc = Oracle(m, "f64")
+  w = orc.forward(orc.new_world())
+  assert w["ncon"][0] == 1
+  assert w["con_dist"][0] == pytest.approx(0.15 - 0.18)
+  assert np.allclose(w["con_frame"][:3], [1, 0, 0])
+  assert np.allclose(w["con_pos"][:3], [0.1 + (0.15 - 0.18) / 2, 0, 1.0])
+  assert list(w["con_geom"][:2]) == [0, 1]
+  # frame is right-handed orthonormal
+  F = w["con_frame"][:9].reshape(3, 3)
+  assert np.allclose(F @ F.T, np.eye(3), atol=1e-12) and np.linalg.det(F) == pytest.approx(1.0)
+
+
+def test_capsule_on_plane_two_contacts():
+  m = fx.compile_xml(fx.CAPSULE_ON_PLANE)
+  orc = Oracle(m, "f64")
+  w = orc.forward(orc.new_world())
+  assert w["ncon"][0] == 2
+  assert np.allclose(w["con_dist"][:2], [-0.005, -0.005])
+  xs = sorted(w["con_pos"][:6].reshape(2, 3)[:, 0])
+  assert np.allclose(xs, [-0.2, 0.2])
+  assert np.allclose(w["con_pos"][:6].reshape(2, 3)[:, 2], -0.0025)
+  # normal = plane z, tangent aligned with the capsule axis
+  F = w["con_frame"][:9].reshape(3, 3)
+  assert np.allclose(F[0], [0, 0, 1]) and abs(F[1][0]) == pytest.approx(1.0)
+  # condim 3 pyramidal: 4 rows per contact
+  assert w["nefc"][0] == 8
+
+
+def test_sphere_rest_force_and_penetration_closed_form():
+  m = fx.compile_xml(fx.SPHERE_DROP)
+  orc = Oracle(m, "f64", ls_parallel=0)
+  w = orc.new_world()
+  w["qpos"][2] = 0.0999
+  orc.step(w, 4000)
+  assert abs(w["qvel"][2]) < 1e-9
+  mass, g = 2.0, 9.81
+  assert w["ncon"][0] == 1 and w["nefc"][0] == 1
+  assert w["efc_force"][0] == pytest.approx(mass * g, rel=1e-7)
+  # equilibrium: m g = D K imp(r) (-r), D = imp / ((1 - imp) * invweight), invweight = 1/m
+  d0, dw, width, mid, power = 0.9, 0.95, 0.001, 0.5, 2.0
+  tc = max(0.02, 2 * m.opt.timestep)
+  K = 1.0 / (dw * dw * tc * tc)
+
+  def imp(r):
+    x = min(abs(r) / width, 1.0)
+    y = x ** power / mid ** (power - 1) if x <= mid else 1 - (1 - x) ** power / (1 - mid) ** (power - 1)
+    return d0 + y * (dw - d0)
+
+  def balance(r):
+    i = imp(r)
+    return i / (1 - i) * mass * K * i * (-r) - mass * g
+  r = brentq(balance, -0.01, -1e-9)
+  assert w["con_dist"][0] == pytest.approx(r, rel=1e-6)
+  assert m.body_invweight0[2, 0] == pytest.approx(1 / mass)
+
+
+def test_limit_rows_sign_and_activation():
+  m = fx.compile_xml(fx.LIMITED_HINGE)
+  orc = Oracle(m, "f64")
+  w = orc.forward(orc.new_world(qpos=[-0.35]))
+  assert w["nefc"][0] == 1 and w["nl"][0] == 1
+  assert w["efc_J"][0] == 1.0 and w["efc_pos"][0] == pytest.approx(0.05 - 0.1 + 0.0, abs=1) and w["efc_pos"][0] == pytest.approx(-0.05)
+  w = orc.forward(orc.new_world(qpos=[0.45]))
+  assert w["nefc"][0] == 1 and w["efc_J"][0] == -1.0 and w["efc_pos"][0] == pytest.approx(-0.05)
+  assert w["efc_force"][0] > 0
+  w = orc.forward(orc.new_world(qpos=[0.0]))
+  assert w["nefc"][0] == 0
+
+
+def test_kinematics_and_mass_matrix_match_independent_numpy(g1):
+  """Oracle (C, tree recursion) vs hostmodel (numpy, float64) on random G1 poses."""
+  from util import g1_states
+  orc = Oracle(g1, "f64", 50, 300)
+  qpos, _, _ = g1_states(g1, 4, seed=7)
+  for q in qpos:
+    w = orc.forward(orc.new_world(qpos=q))
+    M, k, cdof = hostmodel.host_mass_matrix(g1, q / np.r_[np.ones(3), np.full(4, np.linalg.norm(q[3:7])), np.ones(g1.nq - 7)])
+    assert np.allclose(w["xpos"].reshape(-1, 3), k["xpos"], atol=1e-10)
+    assert np.allclose(w["xquat"].reshape(-1, 4), k["xquat"], atol=1e-10)
+    assert np.allclose(w["subtree_com"].reshape(-1, 3), k["subtree_com"], atol=1e-10)
+    assert np.allclose(w["cdof"].reshape(-1, 6), cdof, atol=1e-10)
+    assert np.allclose(w["qM"].reshape(g1.nv, g1.nv), M, atol=1e-9)
+    L = w["qL"].reshape(g1.nv, g1.nv)
+    assert np.allclose(L @ L.T, M, atol=1e-8)
+
+
+def test_g1_standing_contact_force_balances_weight(g1):
+  key = g1.keys["robot/init_state"]
+  orc = Oracle(g1, "f64", 50, 300, ls_parallel=0)
+  w = orc.new_world(qpos=key["qpos"], ctrl=key["ctrl"])
+  orc.step(w, 100)
+  sl_l, sl_r = g1.sensor_slice("feet_ground_contact_left_ankle_roll_link_force"), g1.sensor_slice("feet_ground_contact_right_ankle_roll_link_force")
+  fz = -(w["sensordata"][sl_l][2] + w["sensordata"][sl_r][2])
+  weight = g1.body_subtreemass[2] * 9.81
+  assert fz == pytest.approx(weight, rel=0.03)
+  assert w["sensordata"][g1.sensor_slice("feet_ground_contact_left_ankle_roll_link_found")][0] == 14
+  # accelerometer of a quasi-static robot reads +g along the site z axis
+  assert w["sensordata"][g1.sensor_slice("robot/imu_lin_acc")][2] == pytest.approx(9.81, rel=0.05)
+
+
+def test_solver_satisfies_kkt_for_contacts(g1):
+  """At the Newton solution: M(qacc - qacc_smooth) = J^T f, f >= 0, f = -D min(J qacc - aref, 0)."""
+  from util import g1_states
+  orc = Oracle(g1, "f64", 50, 300, ls_parallel=0, opt=dict(iterations=100, tolerance=1e-12))
+  qpos, qvel, ctrl = g1_states(g1, 6, seed=11)
+  for i in range(6):
+    w = orc.forward(orc.new_world(qpos[i], qvel[i], ctrl[i]))
+    n, nv = w["nefc"][0], g1.nv
+    if n == 0:
+      continue
+    J = w["efc_J"][: n * nv].reshape(n, nv); f = w["efc_force"][:n]
+    M = w["qM"].reshape(nv, nv)
+    assert np.all(f >= 0)
+    jar = J @ w["qacc"] - w["efc_aref"][:n]
+    assert np.allclose(f, -w["efc_D"][:n] * np.minimum(jar, 0), rtol=1e-9, atol=1e-9)
+    res = M @ (w["qacc"] - w["qacc_smooth"]) - J.T @ f
+    assert np.abs(res).max() < 1e-5 * (1 + np.abs(J.T @ f).max())
