@@ -470,9 +470,9 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   if (rc || cudaGetLastError() != cudaSuccess) { delete D; return fail("initialising the data arena failed"); }
   // raise the dynamic shared-memory limit of every stage once
   struct { const void* fn; size_t smem; } st[] = {
-    {fn_position(), smem_position(md)}, {fn_dynamics(), smem_dynamics(md)}, {fn_collision(), smem_collision(md)},
+    {fn_position(), smem_position(md)}, {fn_dynamics(md), smem_dynamics(md)}, {fn_collision(), smem_collision(md)},
     {fn_constraint(), smem_constraint(md)}, {fn_solve(md), smem_solve(md, d)}, {fn_sensors(), smem_sensors(md)},
-    {fn_integrate(), smem_integrate(md)}};
+    {fn_integrate(md), smem_integrate(md)}};
   for (auto& e : st) {
     if (e.smem > 227 * 1024) { delete D; return fail("model too large for the shared-memory working set (" + std::to_string(e.smem) + " B per CTA)"); }
     if (cudaFuncSetAttribute(e.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e.smem) != cudaSuccess) {

@@ -18,9 +18,9 @@ void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st);
 // dynamic shared memory each stage needs for this model (bytes per CTA) and its entry point,
 // so the host can raise cudaFuncAttributeMaxDynamicSharedMemorySize once per model.
 size_t smem_position(const ModelDev& m);  const void* fn_position();
-size_t smem_dynamics(const ModelDev& m);  const void* fn_dynamics();
+size_t smem_dynamics(const ModelDev& m);  const void* fn_dynamics(const ModelDev& m);
 size_t smem_collision(const ModelDev& m); const void* fn_collision();
 size_t smem_constraint(const ModelDev& m); const void* fn_constraint();
 size_t smem_solve(const ModelDev& m, const DataDev& d); const void* fn_solve(const ModelDev& m);
 size_t smem_sensors(const ModelDev& m);   const void* fn_sensors();
-size_t smem_integrate(const ModelDev& m); const void* fn_integrate();
+size_t smem_integrate(const ModelDev& m); const void* fn_integrate(const ModelDev& m);

@@ -186,3 +186,118 @@ DEV void warp_chol_solve(const float* L, int n, int ld, int lane, float& b0, flo
     if (lane + 32 < k) b1 -= L[k * ld + lane + 32] * xk;
   }
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Blocked Cholesky on REGISTER tiles.  The symmetric n x n matrix (n <= 7T) is cut into 7 x 7 blocks of T x T;
+// lane l < 28 owns lower-triangular block (bi, bj), bj <= bi, as a[T*T] in registers.  Per block column kb:
+// the diagonal owner factors its tile, panel owners solve against it, everybody else applies the rank-T
+// update; tiles are exchanged through the shared-memory matrix S (row stride ld), which ends up holding L
+// (lower triangle) for the substitution step, with 1/L[k][k] in invd[k].
+DEV void tile_owner(int lane, int& bi, int& bj) {
+  bi = -1; bj = 0;
+  if (lane < 28) { bi = 0; int l = lane; while (l > bi) { l -= bi + 1; bi++; } bj = l; }
+}
+template <int T>
+DEV void tile_cholesky_regs(float (&a)[T * T], int bi, int bj, float* S, int ld, float* invd) {
+#pragma unroll 1
+  for (int kb = 0; kb < 7; kb++) {
+    if (bi == kb && bj == kb) {
+      float* out = S + (kb * T) * ld + kb * T;
+#pragma unroll
+      for (int y = 0; y < T; y++) {
+        float sdiag = a[y * T + y];
+#pragma unroll
+        for (int z = 0; z < y; z++) sdiag -= a[y * T + z] * a[y * T + z];
+        const float dd = sqrtf(fmaxf(sdiag, B2S_MINVAL));
+        const float inv = 1.0f / dd;
+        a[y * T + y] = dd;
+        out[y * ld + y] = dd;
+        invd[kb * T + y] = inv;
+#pragma unroll
+        for (int x = y + 1; x < T; x++) {
+          float t = a[x * T + y];
+#pragma unroll
+          for (int z = 0; z < y; z++) t -= a[x * T + z] * a[y * T + z];
+          t *= inv;
+          a[x * T + y] = t;
+          out[x * ld + y] = t;
+        }
+      }
+    }
+    __syncwarp();
+    if (bj == kb && bi > kb) {
+      const float* lkk = S + (kb * T) * ld + kb * T;
+      float* out = S + (bi * T) * ld + kb * T;
+#pragma unroll
+      for (int y = 0; y < T; y++) {
+        const float inv = invd[kb * T + y];
+        float l[T];
+#pragma unroll
+        for (int z = 0; z < y; z++) l[z] = lkk[y * ld + z];
+#pragma unroll
+        for (int x = 0; x < T; x++) {
+          float t = a[x * T + y];
+#pragma unroll
+          for (int z = 0; z < y; z++) t -= a[x * T + z] * l[z];
+          t *= inv;
+          a[x * T + y] = t;
+          out[x * ld + y] = t;
+        }
+      }
+    }
+    __syncwarp();
+    if (bj > kb && bi >= bj) {
+      const float* li = S + (bi * T) * ld + kb * T;
+      const float* lj = S + (bj * T) * ld + kb * T;
+#pragma unroll
+      for (int z = 0; z < T; z++) {
+        float ci[T], cj[T];
+#pragma unroll
+        for (int x = 0; x < T; x++) { ci[x] = li[x * ld + z]; cj[x] = lj[x * ld + z]; }
+#pragma unroll
+        for (int x = 0; x < T; x++)
+#pragma unroll
+          for (int y = 0; y < T; y++) a[x * T + y] -= ci[x] * cj[y];
+      }
+    }
+  }
+  __syncwarp();
+}
+// Factor the lower triangle of the n x n matrix stored in S (row stride ld >= 7T) in place.
+template <int T>
+DEV void tile_cholesky_smem(float* S, int n, int ld, int lane, float* invd) {
+  int bi, bj;
+  tile_owner(lane, bi, bj);
+  float a[T * T];
+  if (bi >= 0) {
+#pragma unroll
+    for (int x = 0; x < T; x++)
+#pragma unroll
+      for (int y = 0; y < T; y++) {
+        const int i = bi * T + x, j = bj * T + y;
+        a[x * T + y] = (i < n && j < n) ? (j <= i ? S[i * ld + j] : S[j * ld + i]) : (i == j ? 1.0f : 0.0f);
+      }
+  }
+  __syncwarp();
+  tile_cholesky_regs<T>(a, bi, bj, S, ld, invd);
+}
+// Substitution with the factor above: lane l holds b[l] in b0 and b[l+32] in b1 (n <= 64).
+DEV void warp_chol_solve_inv(const float* L, const float* invd, int n, int ld, int lane, float& b0, float& b1) {
+  for (int k = 0; k < n; k++) {
+    const float bk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
+    if (lane == k) b0 = bk;
+    if (lane + 32 == k) b1 = bk;
+    if (lane > k && lane < n) b0 -= L[lane * ld + k] * bk;
+    if (lane + 32 > k && lane + 32 < n) b1 -= L[(lane + 32) * ld + k] * bk;
+  }
+  for (int k = n - 1; k >= 0; k--) {
+    const float xk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
+    if (lane == k) b0 = xk;
+    if (lane + 32 == k) b1 = xk;
+    if (lane < k) b0 -= L[k * ld + lane] * xk;
+    if (lane + 32 < k) b1 -= L[k * ld + lane + 32] * xk;
+  }
+}
+__host__ __device__ inline int b2s_hdim(int T) { return 7 * T; }                         // padded matrix dimension
+__host__ __device__ inline int b2s_hld(int T) { return (7 * T + 1) | 1; }                 // odd row stride > 7T
+__host__ __device__ inline int b2s_tile_for(int nv) { int T = (nv + 6) / 7; if (T < 1) T = 1; if (T == 7) T = 8; return T; }

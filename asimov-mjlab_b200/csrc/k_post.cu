@@ -251,14 +251,16 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
 }
 
 // ------------------------------------------------------------------------------------------- k_integrate
-// shared per warp: A nv*ld | dg nvp | qa nvp
+// shared per warp: A hdim*ld | invd 7T | dg nvp | qa nvp
+template <int T>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
-  const int nv = m.nv, nvp = m.nvp, ld = nvp + 1;
-  float* A = b2s_smem + (size_t)warp * (nv * ld + 2 * nvp);
-  float* dg = A + nv * ld;
+  const int nv = m.nv, nvp = m.nvp, ld = b2s_hld(T);
+  float* A = b2s_smem + (size_t)warp * (b2s_hdim(T) * ld + 7 * T + 2 * nvp);
+  float* invd = A + b2s_hdim(T) * ld;
+  float* dg = invd + 7 * T;
   float* qa = dg + nvp;
   const float dt = m.timestep;
   float* qvel = d.qvel + (size_t)w * nv;
@@ -308,11 +310,11 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const Mode
       if (c <= r) A[r * ld + c] = M[i] - (c == r ? dt * dg[r] : 0.f);
     }
     __syncwarp();
-    warp_cholesky(A, nv, ld, lane);
+    tile_cholesky_smem<T>(A, nv, ld, lane, invd);
     float b0 = 0.f, b1 = 0.f;
     if (lane < nv) b0 = d.qfrc_smooth[(size_t)w * nv + lane] + d.qfrc_constraint[(size_t)w * nv + lane];
     if (lane + 32 < nv) b1 = d.qfrc_smooth[(size_t)w * nv + lane + 32] + d.qfrc_constraint[(size_t)w * nv + lane + 32];
-    warp_chol_solve(A, nv, ld, lane, b0, b1);
+    warp_chol_solve_inv(A, invd, nv, ld, lane, b0, b1);
     if (lane < nv) qa[lane] = b0;
     if (lane + 32 < nv) qa[lane + 32] = b1;
   }
@@ -343,10 +345,32 @@ void launch_sensors(const ModelDev& m, const DataDev& d, cudaStream_t st) {
 }
 void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
-  k_integrate<<<grid, 32 * B2S_WARPS_PER_CTA, smem_integrate(m), st>>>(m, d);
+  const size_t smem = smem_integrate(m);
+  switch (b2s_tile_for(m.nv)) {
+    case 1: k_integrate<1><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d); break;
+    case 2: k_integrate<2><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d); break;
+    case 3: k_integrate<3><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d); break;
+    case 4: k_integrate<4><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d); break;
+    case 5: k_integrate<5><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d); break;
+    case 6: k_integrate<6><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d); break;
+    default: k_integrate<8><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d); break;
+  }
   b2s_count_launch();
 }
 size_t smem_sensors(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * 21 * m.nbody * sizeof(float); }
-size_t smem_integrate(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * (m.nv * (m.nvp + 1) + 2 * m.nvp) * sizeof(float); }
+size_t smem_integrate(const ModelDev& m) {
+  const int T = b2s_tile_for(m.nv);
+  return (size_t)B2S_WARPS_PER_CTA * (b2s_hdim(T) * b2s_hld(T) + 7 * T + 2 * m.nvp) * sizeof(float);
+}
 const void* fn_sensors() { return (const void*)k_sensors; }
-const void* fn_integrate() { return (const void*)k_integrate; }
+const void* fn_integrate(const ModelDev& m) {
+  switch (b2s_tile_for(m.nv)) {
+    case 1: return (const void*)k_integrate<1>;
+    case 2: return (const void*)k_integrate<2>;
+    case 3: return (const void*)k_integrate<3>;
+    case 4: return (const void*)k_integrate<4>;
+    case 5: return (const void*)k_integrate<5>;
+    case 6: return (const void*)k_integrate<6>;
+    default: return (const void*)k_integrate<8>;
+  }
+}

@@ -164,23 +164,25 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
 
 // ---------------------------------------------------------------------------------------------- k_dynamics
 // shared memory per warp (floats): cdof 6nv | crb 10nb | cvel 6nb | cdd 6nv | cfrc 6nb | fext 6nb | M nv*ld | vec 4*nvp
-__host__ __device__ inline int dyn_smem_floats(int nv, int nvp, int nb) {
-  return 6 * nv + 10 * nb + 6 * nb + 6 * nv + 6 * nb + 6 * nb + nv * (nvp + 1) + 4 * nvp;
+__host__ __device__ inline int dyn_smem_floats(int nv, int nvp, int nb, int T) {
+  return 6 * nv + 10 * nb + 6 * nb + 6 * nv + 6 * nb + 6 * nb + b2s_hdim(T) * b2s_hld(T) + 7 * T + 4 * nvp;
 }
 
+template <int T>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
-  const int nb = m.nbody, nv = m.nv, nvp = m.nvp, ld = nvp + 1;
-  float* s_cdof = b2s_smem + (size_t)warp * dyn_smem_floats(nv, nvp, nb);
+  const int nb = m.nbody, nv = m.nv, nvp = m.nvp, ld = b2s_hld(T);
+  float* s_cdof = b2s_smem + (size_t)warp * dyn_smem_floats(nv, nvp, nb, T);
   float* s_crb = s_cdof + 6 * nv;
   float* s_cvel = s_crb + 10 * nb;
   float* s_cdd = s_cvel + 6 * nb;
   float* s_cfrc = s_cdd + 6 * nv;
   float* s_fext = s_cfrc + 6 * nb;
   float* s_M = s_fext + 6 * nb;
-  float* s_qvel = s_M + nv * ld;
+  float* s_invd = s_M + b2s_hdim(T) * ld;
+  float* s_qvel = s_invd + 7 * T;
   float* s_act = s_qvel + nvp;      // qfrc_actuator
   float* s_rhs = s_act + nvp;       // qfrc_smooth
   float* s_tmp = s_rhs + nvp;
@@ -189,7 +191,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   // stage cdof, cinert, qvel
   for (int i = lane; i < 6 * nv; i += 32) s_cdof[i] = d.cdof[(size_t)w * 6 * nv + i];
   for (int i = lane; i < nv; i += 32) { s_qvel[i] = qvel[i]; s_act[i] = 0.f; }
-  for (int i = lane; i < nv * ld; i += 32) s_M[i] = 0.f;
+  for (int i = lane; i < b2s_hdim(T) * ld; i += 32) s_M[i] = 0.f;
   __syncwarp();
   // composite inertia: sum of cinert over the subtree range (same frame for all bodies)
   for (int b = lane; b < nb; b += 32) {
@@ -337,9 +339,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   }
   __syncwarp();
   // factor M in shared memory and solve for the unconstrained acceleration
-  warp_cholesky(s_M, nv, ld, lane);
+  tile_cholesky_smem<T>(s_M, nv, ld, lane, s_invd);
   float b0 = lane < nv ? s_rhs[lane] : 0.f, b1 = lane + 32 < nv ? s_rhs[lane + 32] : 0.f;
-  warp_chol_solve(s_M, nv, ld, lane, b0, b1);
+  warp_chol_solve_inv(s_M, s_invd, nv, ld, lane, b0, b1);
   if (lane < nv) d.qacc_smooth[(size_t)w * nv + lane] = b0;
   if (lane + 32 < nv) d.qacc_smooth[(size_t)w * nv + lane + 32] = b1;
   (void)s_tmp;
@@ -352,13 +354,29 @@ void launch_position(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   k_position<<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d);
   b2s_count_launch();
 }
+#define TILE_DISPATCH(NV, EXPR_T)                               \
+  switch (b2s_tile_for(NV)) {                                   \
+    case 1: { constexpr int T = 1; EXPR_T; } break;             \
+    case 2: { constexpr int T = 2; EXPR_T; } break;             \
+    case 3: { constexpr int T = 3; EXPR_T; } break;             \
+    case 4: { constexpr int T = 4; EXPR_T; } break;             \
+    case 5: { constexpr int T = 5; EXPR_T; } break;             \
+    case 6: { constexpr int T = 6; EXPR_T; } break;             \
+    default: { constexpr int T = 8; EXPR_T; } break;            \
+  }
 void launch_dynamics(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
-  const size_t smem = (size_t)B2S_WARPS_PER_CTA * dyn_smem_floats(m.nv, m.nvp, m.nbody) * sizeof(float);
-  k_dynamics<<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d);
+  const size_t smem = smem_dynamics(m);
+  TILE_DISPATCH(m.nv, (k_dynamics<T><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d)));
   b2s_count_launch();
 }
 size_t smem_position(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * 22 * m.nbody * sizeof(float); }
-size_t smem_dynamics(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * dyn_smem_floats(m.nv, m.nvp, m.nbody) * sizeof(float); }
+size_t smem_dynamics(const ModelDev& m) {
+  return (size_t)B2S_WARPS_PER_CTA * dyn_smem_floats(m.nv, m.nvp, m.nbody, b2s_tile_for(m.nv)) * sizeof(float);
+}
 const void* fn_position() { return (const void*)k_position; }
-const void* fn_dynamics() { return (const void*)k_dynamics; }
+const void* fn_dynamics(const ModelDev& m) {
+  const void* f = nullptr;
+  TILE_DISPATCH(m.nv, (f = (const void*)k_dynamics<T>));
+  return f;
+}

@@ -16,14 +16,14 @@ extern __shared__ float b2s_smem[];
 
 __host__ __device__ inline int solve_smem_floats(int nv, int nvp, int njmax, int T) {
   // staging tile first (16-byte aligned), total rounded up to a multiple of 4 floats
-  const int n = RB * nvp + 7 * T + 2 * RB + nv * (nvp + 1) + 8 * nvp + 2 * njmax;
+  const int n = RB * nvp + 7 * T + 2 * RB + b2s_hdim(T) * b2s_hld(T) + 7 * T + 8 * nvp + 2 * njmax;
   return (n + 3) & ~3;
 }
 
 struct SolveCtx {
   int lane, nv, nvp, nefc, ld;
   const float *M, *J, *D, *aref;
-  float *H, *qacc, *Ma, *grad, *search, *Mv, *qfs, *qas, *qfc, *Jaref, *Jv, *stage, *sDe, *sf;
+  float *H, *invd, *qacc, *Ma, *grad, *search, *Mv, *qfs, *qas, *qfc, *Jaref, *Jv, *stage, *sDe, *sf;
 };
 
 // y[i] = sum_j M[i][j] x[j]; M symmetric in HBM/L2, read column-wise so lanes hit contiguous addresses
@@ -116,11 +116,18 @@ DEV float ls_iterative(const SolveCtx& c, const ModelDev& m, const float* qg) {
 // row order by every lane (same order as the oracle), the best candidate wins (ties: smallest k)
 DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
   const int n = m.ls_iterations;
+  // efc_D of the active rows is re-read by every candidate: stage it in the (idle) J staging tile
+  const float* Dr = c.D;
+  if (c.nefc <= RB * c.nvp) {
+    for (int r = c.lane; r < c.nefc; r += 32) c.stage[r] = c.D[r];
+    __syncwarp();
+    Dr = c.stage;
+  }
   const float lg = logf(m.ls_parallel_min_step);
   float best = 0.f, balpha = 0.f; int bk = 0x7fffffff;
   {  // alpha = 0 baseline, evaluated the same way
     float s = qg[0];
-    for (int r = 0; r < c.nefc; r++) { const float x = c.Jaref[r]; if (x < 0.f) s += 0.5f * c.D[r] * x * x; }
+    for (int r = 0; r < c.nefc; r++) { const float x = c.Jaref[r]; if (x < 0.f) s += 0.5f * Dr[r] * x * x; }
     best = s; balpha = 0.f; bk = -1;
   }
   for (int base = 0; base < n; base += 32) {
@@ -130,7 +137,7 @@ DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
       float q0 = qg[0], q1 = qg[1], q2 = qg[2];
       for (int r = 0; r < c.nefc; r++) {
         const float ja = c.Jaref[r], jv = c.Jv[r];
-        if (ja + alpha * jv < 0.f) { const float D = c.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
+        if (ja + alpha * jv < 0.f) { const float D = Dr[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
       }
       const float cost = alpha * alpha * q2 + alpha * q1 + q0;
       if (cost < best) { best = cost; balpha = alpha; bk = k; }
@@ -143,6 +150,7 @@ DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
     const int ok = __shfl_xor_sync(FULL, bk, o);
     if (oc < best || (oc == best && ok < bk)) { best = oc; balpha = oa; bk = ok; }
   }
+  __syncwarp();
   return balpha;
 }
 
@@ -196,13 +204,13 @@ DEV void pass_JT(const SolveCtx& c, float* efc_force, bool withH, int bi, int bj
 }
 
 template <int T>
-__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_solve(const ModelDev m, const DataDev d) {
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
   const int nv = m.nv, nvp = m.nvp, njmax = d.njmax;
   SolveCtx c;
-  c.lane = lane; c.nv = nv; c.nvp = nvp; c.ld = nvp + 1; c.nefc = d.nefc[w];
+  c.lane = lane; c.nv = nv; c.nvp = nvp; c.ld = b2s_hld(T); c.nefc = d.nefc[w];
   c.M = d.qM + (size_t)w * nv * nvp;
   c.J = d.efc_J + (size_t)w * njmax * nvp;
   c.D = d.efc_D + (size_t)w * njmax;
@@ -210,7 +218,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_solve(const ModelDev
   float* base = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, njmax, T);
   c.stage = base; base += RB * nvp;          // read slightly past its end by the last Hessian block
   c.sDe = base + 7 * T; c.sf = c.sDe + RB; base += 7 * T + 2 * RB;
-  c.H = base; base += nv * c.ld;
+  c.H = base; base += b2s_hdim(T) * c.ld;
+  c.invd = base; base += 7 * T;
   c.qacc = base; c.Ma = base + nvp; c.grad = base + 2 * nvp; c.search = base + 3 * nvp; c.Mv = base + 4 * nvp;
   c.qfs = base + 5 * nvp; c.qas = base + 6 * nvp; c.qfc = base + 7 * nvp; base += 8 * nvp;
   c.Jaref = base; c.Jv = base + njmax; base += 2 * njmax;
@@ -231,8 +240,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_solve(const ModelDev
     return;
   }
   // lower-triangular Hessian block owned by this lane
-  int bi = -1, bj = 0;
-  if (lane < 28) { bi = 0; int l = lane; while (l > bi) { l -= bi + 1; bi++; } bj = l; }
+  int bi, bj;
+  tile_owner(lane, bi, bj);
   // ---- warm start (mj_fwdConstraint): keep qacc_warmstart only if it beats qacc_smooth
   const bool warm = !(m.disableflags & B2S_DSBL_WARMSTART);
   for (int i = lane; i < nv; i += 32) c.qacc[i] = warm ? d.qacc_warmstart[(size_t)w * nv + i] : c.qas[i];
@@ -268,19 +277,21 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_solve(const ModelDev
     gn = sqrtf(warp_sum(gn));
     if (iter > 0 && scale * gn < m.tolerance) break;
     if (iter >= m.iterations) break;
-    // H = M + J^T D J (lower triangle) -> shared memory, factorise, search = -H^-1 grad
+    // H = M + J^T D J: add M to the register tiles (identity on the padding), blocked Cholesky in registers
+    // (tiles exchanged through c.H, which ends up holding L), search = -H^-1 grad
     if (bi >= 0) {
 #pragma unroll
       for (int x = 0; x < T; x++)
 #pragma unroll
         for (int y = 0; y < T; y++) {
           const int i = bi * T + x, j = bj * T + y;
-          if (i < nv && j <= i) c.H[i * c.ld + j] = acc[x * T + y] + c.M[(size_t)i * nvp + j];
+          if (i < nv && j < nv) acc[x * T + y] += c.M[(size_t)i * nvp + j];
+          else acc[x * T + y] = (i == j) ? 1.0f : 0.0f;
         }
     }
-    warp_cholesky(c.H, nv, c.ld, lane);
+    tile_cholesky_regs<T>(acc, bi, bj, c.H, c.ld, c.invd);
     float b0 = lane < nv ? c.grad[lane] : 0.f, b1 = lane + 32 < nv ? c.grad[lane + 32] : 0.f;
-    warp_chol_solve(c.H, nv, c.ld, lane, b0, b1);
+    warp_chol_solve_inv(c.H, c.invd, nv, c.ld, lane, b0, b1);
     if (lane < nv) c.search[lane] = -b0;
     if (lane + 32 < nv) c.search[lane + 32] = -b1;
     __syncwarp();
@@ -311,7 +322,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_solve(const ModelDev
   if (lane == 0) { d.solver_niter[w] = iter; d.solver_cost[w] = cost; }
 }
 
-static int tile_for(int nv) { int T = (nv + 6) / 7; if (T < 1) T = 1; if (T == 7) T = 8; return T; }
+static int tile_for(int nv) { return b2s_tile_for(nv); }
 
 #define SOLVE_DISPATCH(EXPR_T)                                  \
   switch (tile_for(m.nv)) {                                     \
