@@ -50,7 +50,8 @@ struct b2s_data {
   std::map<std::string, int> index;
   cudaEvent_t ev[16];
   bool have_ev = false;
-  ~b2s_data() { if (arena) cudaFree(arena); if (have_ev) for (auto& e : ev) cudaEventDestroy(e); }
+  float* efc_J = nullptr;    // dense Jacobian, allocated and filled on demand (b2s_efc_jacobian)
+  ~b2s_data() { if (arena) cudaFree(arena); if (efc_J) cudaFree(efc_J); if (have_ev) for (auto& e : ev) cudaEventDestroy(e); }
 };
 
 extern "C" const char* b2s_last_error(void) { return g_err.c_str(); }
@@ -202,6 +203,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.nq = s->nq; d.nv = nv; d.nvp = (nv + 3) & ~3; d.nu = s->nu; d.nbody = nb; d.njnt = s->njnt; d.ngeom = s->ngeom; d.nsite = s->nsite;
   d.nsensor = s->nsensor; d.nsensordata = s->nsensordata; d.nmocap = s->nmocap;
   d.nlevel = nlevel; d.npair = (int)pairs.size() / 2; d.maxchain = maxchain;
+  d.ref_root = nv > 0 ? s->body_rootid[s->dof_bodyid[0]] : 0;
   d.timestep = (float)s->opt_timestep;
   for (int k = 0; k < 3; k++) d.gravity[k] = (float)s->opt_gravity[k];
   d.tolerance = (float)s->opt_tolerance; d.ls_tolerance = (float)s->opt_ls_tolerance; d.impratio = (float)s->opt_impratio;
@@ -422,7 +424,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"contact_includemargin", B2S_F32, (void**)&d.con_includemargin, {nconmax}}, {"contact_friction", B2S_F32, (void**)&d.con_friction, {nconmax, 5}},
     {"contact_solref", B2S_F32, (void**)&d.con_solref, {nconmax, 2}}, {"contact_solimp", B2S_F32, (void**)&d.con_solimp, {nconmax, 5}},
     {"nefc", B2S_I32, (void**)&d.nefc, {}}, {"nl", B2S_I32, (void**)&d.nl, {}}, {"efc_type", B2S_I32, (void**)&d.efc_type, {njmax}}, {"efc_id", B2S_I32, (void**)&d.efc_id, {njmax}},
-    {"efc_J", B2S_F32, (void**)&d.efc_J, {njmax, nvp}}, {"efc_pos", B2S_F32, (void**)&d.efc_pos, {njmax}}, {"efc_margin", B2S_F32, (void**)&d.efc_margin, {njmax}},
+    {"efc_g", B2S_F32, (void**)&d.efc_g, {njmax, 6}}, {"efc_bp", B2S_I32, (void**)&d.efc_bp, {njmax}}, {"efc_pos", B2S_F32, (void**)&d.efc_pos, {njmax}}, {"efc_margin", B2S_F32, (void**)&d.efc_margin, {njmax}},
     {"efc_D", B2S_F32, (void**)&d.efc_D, {njmax}}, {"efc_vel", B2S_F32, (void**)&d.efc_vel, {njmax}}, {"efc_aref", B2S_F32, (void**)&d.efc_aref, {njmax}},
     {"efc_force", B2S_F32, (void**)&d.efc_force, {njmax}},
     {"qacc", B2S_F32, (void**)&d.qacc, {nv}}, {"qfrc_constraint", B2S_F32, (void**)&d.qfrc_constraint, {nv}},
@@ -491,6 +493,20 @@ extern "C" int b2s_data_field(b2s_data* d, const char* name, b2s_field_info* out
   auto it = d->index.find(name);
   if (it == d->index.end()) return fail(std::string("unknown data field ") + name);
   fill_info(d->fields[it->second], d->dev.nworld, false, d->fields[it->second].ptr, out);
+  return 0;
+}
+// Dense constraint Jacobian (mjwarp's Data.efc.J) from the matrix-free rows: allocated on first use, refilled on
+// every call.  Not part of step/forward and not graph-capturable (it may allocate).
+extern "C" int b2s_efc_jacobian(const b2s_model* m, b2s_data* d, void* stream, b2s_field_info* out) {
+  if (!m || !d || !out) return fail("null argument");
+  CU(cudaSetDevice(d->device));
+  const size_t n = (size_t)d->dev.nworld * d->dev.njmax * m->dev.nvp;
+  if (!d->efc_J) CU(cudaMalloc(&d->efc_J, n * sizeof(float)));
+  launch_efc_jacobian(m->dev, d->dev, d->efc_J, (cudaStream_t)stream);
+  CU(cudaGetLastError());
+  out->ptr = d->efc_J; out->dtype = B2S_F32; out->ndim = 3;
+  out->shape[0] = d->dev.nworld; out->shape[1] = d->dev.njmax; out->shape[2] = m->dev.nvp; out->shape[3] = 1;
+  out->stride[2] = 1; out->stride[1] = m->dev.nvp; out->stride[0] = (long long)d->dev.njmax * m->dev.nvp; out->stride[3] = 1;
   return 0;
 }
 extern "C" int b2s_data_num_fields(const b2s_data* d) { return d ? (int)d->fields.size() : 0; }

@@ -26,6 +26,7 @@ struct ModelDev {
   // sizes
   int nq, nv, nvp, nu, nbody, njnt, ngeom, nsite, nsensor, nsensordata, nmocap;
   int nlevel, npair, ncolgeom, maxchain;
+  int ref_root;                     // root body of the first kinematic tree: its subtree COM is the constraint reference point
   // options
   float timestep, gravity[3], tolerance, ls_tolerance, impratio, ls_parallel_min_step, meaninertia;
   int integrator, cone, iterations, ls_iterations, disableflags, ls_parallel, contact_sensor_maxmatch;
@@ -78,8 +79,9 @@ struct DataDev {
   int *ncon, *con_dim, *con_geom, *con_efc_address;
   float *con_dist, *con_pos, *con_frame, *con_includemargin, *con_friction, *con_solref, *con_solimp;
   // constraints
-  int *nefc, *nl, *efc_type, *efc_id;
-  float *efc_J, *efc_pos, *efc_margin, *efc_D, *efc_vel, *efc_aref, *efc_force;
+  int *nefc, *nl, *efc_type, *efc_id, *efc_bp;   // efc_bp: contact rows body1 | body2 << 16, limit rows -1 - dof
+  float *efc_g;                                  // [njmax][6] row wrench about the reference point (limit rows: g[0] = +-1)
+  float *efc_pos, *efc_margin, *efc_D, *efc_vel, *efc_aref, *efc_force;
   // solver
   float *qacc, *qfrc_constraint, *solver_cost;
   int *solver_niter;

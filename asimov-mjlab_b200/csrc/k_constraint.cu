@@ -2,9 +2,20 @@
 //
 // Row order follows MuJoCo: limits (joint order, lower side before upper) then contacts (contact order;
 // pyramidal cone: 2(dim-1) rows per frictional contact, 1 row for condim 1).  Row addresses come from
-// ballot / warp-scan compaction, so the layout is deterministic.  Each contact's rows are produced
-// cooperatively: lanes own Jacobian columns (dofs), so efc_J rows are written with coalesced stores and
-// efc_vel = J qvel is a warp reduction.
+// ballot / warp-scan compaction, so the layout is deterministic.
+//
+// MATRIX-FREE ROWS.  The reference backend materialises the dense Jacobian efc_J (njmax x nv floats per
+// world, 42 KB for G1) and streams it through every solver iteration.  Here a row is stored in its
+// geometric form instead:
+//   limit row   : (dof, sign)                                  J[r][dof] = sign
+//   contact row : (body1, body2, g[6])  with g = [off x dir ; dir] the unit wrench of the row direction
+//                 about the world's reference point c_ref, so that
+//                 J[r][i] = (i in chain(body2)) g.cdof_i - (i in chain(body1)) g.cdof_i
+// (cdof are MuJoCo's com-based spatial motion axes; within one kinematic tree they already share the
+// reference point subtree_com[root], other trees are re-referenced to the first tree's).  J v, J^T f and
+// J^T D J then cost O(6) per row plus O(chain^2) per body pair (k_solver.cu), efc_vel is g.(cvel2 - cvel1),
+// and 28 bytes per row replace 144.  The dense efc_J is produced on demand by k_efc_jacobian for callers
+// that want to look at it (tests do).
 #include "b2s_math.cuh"
 #include "b2s_api.h"
 
@@ -50,20 +61,28 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
-  const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
-  float* s_cdof = b2s_smem + (size_t)warp * (6 * nv + nvp);
-  float* s_qvel = s_cdof + 6 * nv;
+  const int nv = m.nv, nb = m.nbody, njmax = d.njmax;
+  float* s_cvel = b2s_smem + (size_t)warp * 6 * nb;     // body velocities about the world's reference point
   if (m.disableflags & B2S_DSBL_CONSTRAINT) { if (lane == 0) { d.nefc[w] = 0; d.nl[w] = 0; } return; }
-  for (int i = lane; i < 6 * nv; i += 32) s_cdof[i] = d.cdof[(size_t)w * 6 * nv + i];
-  for (int i = lane; i < nvp; i += 32) s_qvel[i] = i < nv ? d.qvel[(size_t)w * nv + i] : 0.f;
+  const float* com = d.subtree_com + (size_t)w * nb * 3;
+  const v3 cref = ld3(com + 3 * m.ref_root);
+  for (int b = lane; b < nb; b += 32) {
+    sv6 cv = ld6(d.cvel + ((size_t)w * nb + b) * 6);
+    const int rb = m.body_rootid[b];
+    if (rb != m.ref_root) {
+      const v3 lin = mk3(cv.v[3], cv.v[4], cv.v[5]) + cross(mk3(cv.v[0], cv.v[1], cv.v[2]), cref - ld3(com + 3 * rb));
+      cv.v[3] = lin.x; cv.v[4] = lin.y; cv.v[5] = lin.z;
+    }
+    st6(s_cvel + 6 * b, cv);
+  }
   __syncwarp();
   const size_t row0 = (size_t)w * njmax;
-  float* J = d.efc_J + row0 * nvp;
   int nefc = 0;
   // ---- joint limits
   if (!(m.disableflags & B2S_DSBL_LIMIT)) {
     const float* range = m.jnt_range.at(w);
     const float* qpos = d.qpos + (size_t)w * m.nq;
+    const float* qvel = d.qvel + (size_t)w * nv;
     for (int base = 0; base < 2 * m.njnt; base += 32) {
       const int item = base + lane, j = item >> 1;
       const float side = (item & 1) ? 1.f : -1.f;
@@ -80,25 +99,26 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
       const int r = nefc + __popc(mask & ((1u << lane) - 1u));
       if (act && r < njmax) {
         const int dof = m.jnt_dofadr[j];
-        for (int i = 0; i < nvp; i++) J[(size_t)r * nvp + i] = 0.f;
-        J[(size_t)r * nvp + dof] = -side;
+        float* g = d.efc_g + (row0 + r) * 6;
+        g[0] = -side; g[1] = g[2] = g[3] = g[4] = g[5] = 0.f;
+        d.efc_bp[row0 + r] = -1 - dof;
         d.efc_type[row0 + r] = EFC_LIMIT; d.efc_id[row0 + r] = j;
-        finish_row(m, d, row0 + r, dist, margin, -side * s_qvel[dof], m.jnt_solref[2 * j], m.jnt_solref[2 * j + 1],
+        finish_row(m, d, row0 + r, dist, margin, -side * qvel[dof], m.jnt_solref[2 * j], m.jnt_solref[2 * j + 1],
                    m.jnt_solimp + 5 * j, m.dof_invweight0[dof], 1.f);
       }
       nefc = min(nefc + __popc(mask), njmax);
     }
   }
   const int nl = nefc;
-  // ---- contact row addresses
+  // ---- contact rows: one lane per contact (address by warp scan, then the lane writes its own rows)
   const int ncon = (m.disableflags & B2S_DSBL_CONTACT) ? 0 : d.ncon[w];
   const size_t con0 = (size_t)w * d.nconmax;
   bool full = false;
   for (int base = 0; base < ncon; base += 32) {
     const int c = base + lane;
-    int nrow = 0;
+    int nrow = 0, dim = 0;
     if (c < ncon && d.con_dist[con0 + c] < d.con_includemargin[con0 + c]) {
-      const int dim = d.con_dim[con0 + c];
+      dim = d.con_dim[con0 + c];
       nrow = dim == 1 ? 1 : 2 * (dim - 1);
     }
     int total;
@@ -114,60 +134,110 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
       nefc = used;
     } else nefc += total;
     if (c < ncon) d.con_efc_address[con0 + c] = nrow > 0 ? adr : -1;
-  }
-  __syncwarp();
-  // ---- contact rows, one contact at a time, lanes own dof columns
-  const float* com = d.subtree_com + (size_t)w * nb * 3;
-  for (int c = 0; c < ncon; c++) {
-    const int adr = d.con_efc_address[con0 + c];
-    if (adr < 0) continue;
-    const int dim = d.con_dim[con0 + c], nrow = dim == 1 ? 1 : 2 * (dim - 1);
-    const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
-    const int b1 = m.geom_bodyid[g1], b2 = m.geom_bodyid[g2];
-    const float* fr = d.con_frame + 9 * (con0 + c);
-    const float* fri = d.con_friction + 5 * (con0 + c);
-    const v3 pos = ld3(d.con_pos + 3 * (con0 + c));
-    const v3 off1 = pos - ld3(com + 3 * m.body_rootid[b1]), off2 = pos - ld3(com + 3 * m.body_rootid[b2]);
-    const v3 fn = ld3(fr), ft1 = ld3(fr + 3), ft2 = ld3(fr + 6);
-    const unsigned char* k1 = m.body_dofmask + (size_t)b1 * nv;
-    const unsigned char* k2 = m.body_dofmask + (size_t)b2 * nv;
-    float vel[10];
+    if (nrow > 0) {
+      const size_t o = con0 + c;
+      const int g1 = d.con_geom[2 * o], g2 = d.con_geom[2 * o + 1];
+      const int b1 = m.geom_bodyid[g1], b2 = m.geom_bodyid[g2];
+      const float* fr = d.con_frame + 9 * o;
+      const float* fri = d.con_friction + 5 * o;
+      const v3 off = ld3(d.con_pos + 3 * o) - cref;
+      // relative spatial velocity of the two bodies about c_ref
+      float vr[6];
 #pragma unroll
-    for (int k = 0; k < 10; k++) vel[k] = 0.f;
-    for (int i = lane; i < nvp; i += 32) {
-      float jc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (i < nv) {
-        const v3 ang = ld3(s_cdof + 6 * i), lin = ld3(s_cdof + 6 * i + 3);
-        v3 jp = mk3(0.f, 0.f, 0.f), jr = mk3(0.f, 0.f, 0.f);
-        if (k2[i]) { jp = jp + lin + cross(ang, off2); jr = jr + ang; }
-        if (k1[i]) { jp = jp - (lin + cross(ang, off1)); jr = jr - ang; }
-        jc[0] = dot(fn, jp); jc[1] = dot(ft1, jp); jc[2] = dot(ft2, jp);
-        jc[3] = dot(fn, jr); jc[4] = dot(ft1, jr); jc[5] = dot(ft2, jr);
-      }
-      const float qv = s_qvel[i];
-      if (dim == 1) { J[(size_t)adr * nvp + i] = jc[0]; vel[0] += jc[0] * qv; }
-      else {
-        for (int k = 0; k < nrow; k++) {
-          const float v = jc[0] + ((k & 1) ? -1.f : 1.f) * fri[k >> 1] * jc[1 + (k >> 1)];
-          J[(size_t)(adr + k) * nvp + i] = v;
-          vel[k] += v * qv;
+      for (int k = 0; k < 6; k++) vr[k] = s_cvel[6 * b2 + k] - s_cvel[6 * b1 + k];
+      // base wrenches: translational directions (normal, tangent1, tangent2), then rotational ones
+      float gb[6][6], vb[6];
+#pragma unroll
+      for (int k = 0; k < 6; k++) {
+        if (k < dim) {
+          const v3 dir = ld3(fr + 3 * (k % 3));
+          if (k < 3) { const v3 t = cross(off, dir); gb[k][0] = t.x; gb[k][1] = t.y; gb[k][2] = t.z; gb[k][3] = dir.x; gb[k][4] = dir.y; gb[k][5] = dir.z; }
+          else { gb[k][0] = dir.x; gb[k][1] = dir.y; gb[k][2] = dir.z; gb[k][3] = gb[k][4] = gb[k][5] = 0.f; }
+          float s = 0.f;
+#pragma unroll
+          for (int q = 0; q < 6; q++) s += gb[k][q] * vr[q];
+          vb[k] = s;
         }
       }
-    }
-    float myvel = 0.f;
-    for (int k = 0; k < nrow; k++) { const float s = warp_sum(vel[k]); if (lane == k) myvel = s; }
-    if (lane < nrow) {
       const float tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
       const float mu0 = fri[0];
       const float diag = dim == 1 ? tran : tran + mu0 * mu0 * tran;
       const float scale = dim == 1 ? 1.f : 2.f * mu0 * mu0 / m.impratio;
-      d.efc_type[row0 + adr + lane] = dim == 1 ? EFC_CONTACT_FRICTIONLESS : EFC_CONTACT_PYRAMIDAL;
-      d.efc_id[row0 + adr + lane] = c;
-      finish_row(m, d, row0 + adr + lane, d.con_dist[con0 + c], d.con_includemargin[con0 + c], myvel,
-                 d.con_solref[2 * (con0 + c)], d.con_solref[2 * (con0 + c) + 1], d.con_solimp + 5 * (con0 + c), diag, scale);
+      const float dist = d.con_dist[o], inc = d.con_includemargin[o];
+      const float sr0 = d.con_solref[2 * o], sr1 = d.con_solref[2 * o + 1];
+      const int bp = b1 | (b2 << 16);
+      for (int k = 0; k < nrow; k++) {
+        const size_t row = row0 + adr + k;
+        float* g = d.efc_g + row * 6;
+        float vel;
+        if (dim == 1) {
+#pragma unroll
+          for (int q = 0; q < 6; q++) g[q] = gb[0][q];
+          vel = vb[0];
+        } else {
+          const int ti = 1 + (k >> 1);
+          const float mu = ((k & 1) ? -1.f : 1.f) * fri[k >> 1];
+          // gb is indexed dynamically: select with a short unrolled scan so it stays in registers
+          float gt[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}; float vt = 0.f;
+#pragma unroll
+          for (int kk = 1; kk < 6; kk++) if (kk == ti) {
+#pragma unroll
+            for (int q = 0; q < 6; q++) gt[q] = gb[kk][q];
+            vt = vb[kk];
+          }
+#pragma unroll
+          for (int q = 0; q < 6; q++) g[q] = gb[0][q] + mu * gt[q];
+          vel = vb[0] + mu * vt;
+        }
+        d.efc_bp[row] = bp;
+        d.efc_type[row] = dim == 1 ? EFC_CONTACT_FRICTIONLESS : EFC_CONTACT_PYRAMIDAL;
+        d.efc_id[row] = c;
+        finish_row(m, d, row, dist, inc, vel, sr0, sr1, d.con_solimp + 5 * o, diag, scale);
+      }
     }
   }
   if (lane == 0) { d.nefc[w] = nefc; d.nl[w] = nl; }
+}
+
+// Dense efc_J from the matrix-free rows (on demand; not part of step/forward).
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_efc_jacobian(const ModelDev m, const DataDev d, float* J) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
+  if (w >= d.nworld) return;
+  const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
+  float* s_cdof = b2s_smem + (size_t)warp * 6 * nv;
+  const float* com = d.subtree_com + (size_t)w * nb * 3;
+  const v3 cref = ld3(com + 3 * m.ref_root);
+  for (int i = lane; i < nv; i += 32) {
+    sv6 cd = ld6(d.cdof + ((size_t)w * nv + i) * 6);
+    const int rb = m.body_rootid[m.dof_bodyid[i]];
+    if (rb != m.ref_root) {
+      const v3 lin = mk3(cd.v[3], cd.v[4], cd.v[5]) + cross(mk3(cd.v[0], cd.v[1], cd.v[2]), cref - ld3(com + 3 * rb));
+      cd.v[3] = lin.x; cd.v[4] = lin.y; cd.v[5] = lin.z;
+    }
+    st6(s_cdof + 6 * i, cd);
+  }
+  __syncwarp();
+  const int nefc = d.nefc[w];
+  const size_t row0 = (size_t)w * njmax;
+  for (int r = 0; r < njmax; r++) {
+    float* Jr = J + (row0 + r) * nvp;
+    if (r >= nefc) { for (int i = lane; i < nvp; i += 32) Jr[i] = 0.f; continue; }
+    const int bp = d.efc_bp[row0 + r];
+    const sv6 g = ld6(d.efc_g + (row0 + r) * 6);
+    for (int i = lane; i < nvp; i += 32) {
+      float v = 0.f;
+      if (i < nv) {
+        if (bp < 0) v = (i == -1 - bp) ? g.v[0] : 0.f;
+        else {
+          const int b1 = bp & 0xffff, b2 = bp >> 16;
+          const int s = (int)m.body_dofmask[(size_t)b2 * nv + i] - (int)m.body_dofmask[(size_t)b1 * nv + i];
+          if (s) v = (float)s * dot6(g, ld6(s_cdof + 6 * i));
+        }
+      }
+      Jr[i] = v;
+    }
+  }
 }
 
 void launch_constraint(const ModelDev& m, const DataDev& d, cudaStream_t st) {
@@ -175,5 +245,10 @@ void launch_constraint(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   k_constraint<<<grid, 32 * B2S_WARPS_PER_CTA, smem_constraint(m), st>>>(m, d);
   b2s_count_launch();
 }
-size_t smem_constraint(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * (6 * m.nv + m.nvp) * sizeof(float); }
+void launch_efc_jacobian(const ModelDev& m, const DataDev& d, float* J, cudaStream_t st) {
+  const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
+  k_efc_jacobian<<<grid, 32 * B2S_WARPS_PER_CTA, (size_t)B2S_WARPS_PER_CTA * 6 * m.nv * sizeof(float), st>>>(m, d, J);
+  b2s_count_launch();
+}
+size_t smem_constraint(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * 6 * m.nbody * sizeof(float); }
 const void* fn_constraint() { return (const void*)k_constraint; }

@@ -1,29 +1,34 @@
-// k_solver.cu -- Newton constraint solver, one warp per world.
+// k_solver.cu -- matrix-free Newton constraint solver, one warp per world.
 //
 // Minimises  1/2 (a-a_s)^T M (a-a_s) + s(J a - aref)  over the acceleration a (MuJoCo's primal problem).
-// Everything iteration-local lives on chip: the Hessian H = M + J^T D J is accumulated in REGISTER tiles
-// (7 x 7 blocks of T x T, one lower-triangular block per lane, fed from 8-row blocks of efc_J staged in
-// shared memory with coalesced 16-byte loads), factorised in shared memory (warp Cholesky) and applied with
-// register-resident substitution.  Jaref / Jv stay in shared memory across iterations; efc_J is streamed
-// from L2 twice per iteration (J v and the fused J^T f + Hessian pass).  Line search: mjwarp's parallel
+// The Jacobian is never materialised.  A contact row is (body1, body2, g) with g the 6-D unit wrench of the
+// row direction about the world's reference point (k_constraint.cu), a limit row is (dof, sign), so
+//   J x      = g . (X[body2] - X[body1]),  X[b] = sum_{i in chain(b)} cdof_i x_i      (one lane per body / row)
+//   J^T f    = per run of rows that share a body pair: W = sum_r f_r g_r, then  s_i cdof_i . W  on the
+//              signed chain difference of the pair (<= 2 x tree depth dofs)
+//   J^T D J  = per run: K = sum_r D_r g_r g_r^T (6x6, one lane per entry), then  (s_i cdof_i)^T K (s_j cdof_j)
+// which is O(6) per row plus O(chain^2) per body pair instead of O(nv^2) per row, with everything in shared
+// memory (cdof 6nv floats, H nv^2, per-row Jaref/Jv/D).  H = M + J^T D J is factorised by the blocked
+// register-tile Cholesky (b2s_math.cuh) and applied by shuffle substitution.  Line search: mjwarp's parallel
 // variant (one lane per candidate step, reference sim.py:91 ls_parallel=True) or MuJoCo's exact 1-D Newton
 // with bracketing (warp-collective evaluations).
 #include "b2s_math.cuh"
 #include "b2s_api.h"
 
 extern __shared__ float b2s_smem[];
-#define RB 8   // rows of efc_J staged per block
 
-__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int njmax, int T) {
-  // staging tile first (16-byte aligned), total rounded up to a multiple of 4 floats
-  const int n = RB * nvp + 7 * T + 2 * RB + b2s_hdim(T) * b2s_hld(T) + 7 * T + 8 * nvp + 2 * njmax;
+__host__ __device__ inline int solve_scratch_floats(int nb) { return 6 * (nb > 32 ? nb : 32) + 32 + 32; }
+__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int T) {
+  const int n = b2s_hdim(T) * b2s_hld(T) + 7 * T + 8 * nvp + 6 * nv + solve_scratch_floats(nb) + 3 * njmax;
   return (n + 3) & ~3;
 }
 
 struct SolveCtx {
-  int lane, nv, nvp, nefc, ld;
-  const float *M, *J, *D, *aref;
-  float *H, *invd, *qacc, *Ma, *grad, *search, *Mv, *qfs, *qas, *qfc, *Jaref, *Jv, *stage, *sDe, *sf;
+  int lane, nv, nvp, nb, nefc, nl, ld;
+  const float *M, *G, *aref;
+  const int* bp;
+  float *H, *invd, *qacc, *Ma, *grad, *search, *Mv, *qfs, *qas, *qfc, *cdof, *X, *KW, *Jaref, *Jv, *D;
+  int* Li;
 };
 
 // y[i] = sum_j M[i][j] x[j]; M symmetric in HBM/L2, read column-wise so lanes hit contiguous addresses
@@ -38,17 +43,31 @@ DEV void mat_vec_M(const SolveCtx& c, const float* x, float* y) {
   if (c.lane < c.nv) y[c.lane] = a0;
   if (c.lane + 32 < c.nv) y[c.lane + 32] = a1;
 }
-// out[r] = J[r] . x - sub[r]   (lane per row, 16-byte loads)
-DEV void mat_vec_J(const SolveCtx& c, const float* x, const float* sub, float* out) {
+// out[r] = J[r] . x - sub[r], matrix-free: body spatial vectors X[b] first (one lane per body), then one lane per row
+DEV void mat_vec_J(const SolveCtx& c, const ModelDev& m, const float* x, const float* sub, float* out) {
+  __syncwarp();
+  for (int b = c.lane; b < c.nb; b += 32) {
+    sv6 v = zero6();
+    for (int k = m.body_chain_adr[b]; k < m.body_chain_adr[b + 1]; k++) { const int i = m.body_chain[k]; axpy6(v, x[i], ld6(c.cdof + 6 * i)); }
+    st6(c.X + 6 * b, v);
+  }
+  __syncwarp();
   for (int r = c.lane; r < c.nefc; r += 32) {
-    const float4* row = reinterpret_cast<const float4*>(c.J + (size_t)r * c.nvp);
-    float s = 0.f;
-    for (int q = 0; q < c.nvp / 4; q++) {
-      const float4 v = row[q];
-      s += v.x * x[4 * q] + v.y * x[4 * q + 1] + v.z * x[4 * q + 2] + v.w * x[4 * q + 3];
+    const int bp = c.bp[r];
+    const float2* gp = reinterpret_cast<const float2*>(c.G + (size_t)r * 6);
+    const float2 g01 = gp[0];
+    float s;
+    if (bp < 0) s = g01.x * x[-1 - bp];
+    else {
+      const float2 g23 = gp[1], g45 = gp[2];
+      const float* x2 = c.X + 6 * (bp >> 16);
+      const float* x1 = c.X + 6 * (bp & 0xffff);
+      s = g01.x * (x2[0] - x1[0]) + g01.y * (x2[1] - x1[1]) + g23.x * (x2[2] - x1[2]) + g23.y * (x2[3] - x1[3]) +
+          g45.x * (x2[4] - x1[4]) + g45.y * (x2[5] - x1[5]);
     }
     out[r] = sub ? s - sub[r] : s;
   }
+  __syncwarp();
 }
 DEV float gauss_term(const SolveCtx& c) {
   float g = 0.f;
@@ -112,38 +131,27 @@ DEV float ls_iterative(const SolveCtx& c, const ModelDev& m, const float* qg) {
   if (p2.cost <= p1.cost && p2.cost < p0.cost) return p2.alpha;
   return 0.f;
 }
-// one lane per candidate step: alpha_k = min_step^(k/(n-1)), k = 0..n-1, plus alpha = 0; rows are summed in
-// row order by every lane (same order as the oracle), the best candidate wins (ties: smallest k)
+// one lane per candidate step: alpha_k = min_step^(k/(n-1)), k = 0..n-1, and alpha = 0 on one more lane; rows are
+// summed in row order by every lane (same order as the oracle), the best candidate wins (ties: alpha = 0, then
+// the smallest k), so a step is only taken if it strictly improves on alpha = 0
 DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
   const int n = m.ls_iterations;
-  // efc_D of the active rows is re-read by every candidate: stage it in the (idle) J staging tile
-  const float* Dr = c.D;
-  if (c.nefc <= RB * c.nvp) {
-    for (int r = c.lane; r < c.nefc; r += 32) c.stage[r] = c.D[r];
-    __syncwarp();
-    Dr = c.stage;
-  }
   const float lg = logf(m.ls_parallel_min_step);
-  float best = 0.f, balpha = 0.f; int bk = 0x7fffffff;
-  {  // alpha = 0 baseline, evaluated the same way
-    float s = qg[0];
-    for (int r = 0; r < c.nefc; r++) { const float x = c.Jaref[r]; if (x < 0.f) s += 0.5f * Dr[r] * x * x; }
-    best = s; balpha = 0.f; bk = -1;
-  }
-  for (int base = 0; base < n; base += 32) {
+  float best = 3.0e38f, balpha = 0.f; int bk = 0x7fffffff;
+  for (int base = 0; base <= n; base += 32) {
     const int k = base + c.lane;
-    if (k < n) {
-      const float alpha = n > 1 ? expf((float)k / (float)(n - 1) * lg) : 1.f;
+    if (k <= n) {
+      const float alpha = k == n ? 0.f : (n > 1 ? expf((float)k / (float)(n - 1) * lg) : 1.f);
       float q0 = qg[0], q1 = qg[1], q2 = qg[2];
       for (int r = 0; r < c.nefc; r++) {
         const float ja = c.Jaref[r], jv = c.Jv[r];
-        if (ja + alpha * jv < 0.f) { const float D = Dr[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
+        if (ja + alpha * jv < 0.f) { const float D = c.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
       }
       const float cost = alpha * alpha * q2 + alpha * q1 + q0;
-      if (cost < best) { best = cost; balpha = alpha; bk = k; }
+      const int kk = k == n ? -1 : k;
+      if (cost < best || (cost == best && kk < bk)) { best = cost; balpha = alpha; bk = kk; }
     }
   }
-  // warp arg-min on (cost, k); bk = -1 (alpha = 0) wins ties so a step is only taken if it strictly improves
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float oc = __shfl_xor_sync(FULL, best, o), oa = __shfl_xor_sync(FULL, balpha, o);
@@ -154,53 +162,143 @@ DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
   return balpha;
 }
 
-// Fused pass over efc_J: forces / active set from Jaref, qfrc_constraint = J^T f, and (if withH) the
-// register-tile accumulation of J^T D J.
-template <int T>
-DEV void pass_JT(const SolveCtx& c, float* efc_force, bool withH, int bi, int bj, float (&acc)[T * T]) {
-  float qf0 = 0.f, qf1 = 0.f;
+// A run of contact rows that share the body pair (b1, b2) has been reduced to K (21 lanes) and W (6 lanes):
+// apply it to qfrc_constraint and (withH) to the lower triangle of H.
+DEV void flush_run(const SolveCtx& c, const ModelDev& m, int bp, float acc, bool withH) {
+  c.KW[c.lane] = acc;
+  const int b1 = bp & 0xffff, b2 = bp >> 16;
+  const int a1 = m.body_chain_adr[b1], n1f = m.body_chain_adr[b1 + 1] - a1;
+  const int a2 = m.body_chain_adr[b2], n2f = m.body_chain_adr[b2 + 1] - a2;
+  // common ancestors are a common prefix of the two root-first chains: they cancel
+  int cp = 0;
+  {
+    const int nmin = min(n1f, n2f);
+    for (int base = 0; base < nmin; base += 32) {
+      const int k = base + c.lane;
+      const bool same = k < nmin && m.body_chain[a1 + k] == m.body_chain[a2 + k];
+      const unsigned mk = __ballot_sync(FULL, same);
+      if (mk != FULL) { cp = base + __ffs(~mk) - 1; break; }
+      cp = base + 32;
+    }
+    cp = min(cp, nmin);
+  }
+  const int n2 = n2f - cp, n1 = n1f - cp, ns = n1 + n2;
+  __syncwarp();
+  const float* K = c.KW; const float* W = c.KW + 21;
+  float* Y = c.X;    // 6 floats per support entry (the body-vector scratch is idle during assembly)
+  for (int base = 0; base < ns; base += 32) {
+    // supports longer than 32 dofs are processed in chunks; Y/Li then hold one chunk at a time, so the cross
+    // terms between chunks are handled by the (rare) slow path below
+    const int a = base + c.lane;
+    if (a < ns) {
+      const int i = a < n2 ? m.body_chain[a2 + cp + a] : m.body_chain[a1 + cp + a - n2];
+      const float s = a < n2 ? 1.f : -1.f;
+      const sv6 cd = ld6(c.cdof + 6 * i);
+      c.qfc[i] += s * (cd.v[0] * W[0] + cd.v[1] * W[1] + cd.v[2] * W[2] + cd.v[3] * W[3] + cd.v[4] * W[4] + cd.v[5] * W[5]);
+      if (withH && ns <= 32) {
+        // Y = s K cd with K symmetric, entries ordered (0,0) (1,0) (1,1) (2,0) ...
+        float y[6];
+        int e = 0;
+#pragma unroll
+        for (int p = 0; p < 6; p++) y[p] = 0.f;
+#pragma unroll
+        for (int p = 0; p < 6; p++)
+#pragma unroll
+          for (int q = 0; q <= p; q++) {
+            const float kv = K[e++];
+            y[p] += kv * cd.v[q];
+            if (q != p) y[q] += kv * cd.v[p];
+          }
+#pragma unroll
+        for (int p = 0; p < 6; p++) Y[6 * a + p] = s * y[p];
+        c.Li[a] = i | (a < n2 ? 0 : 0x10000);
+      }
+    }
+  }
+  __syncwarp();
   if (withH) {
-#pragma unroll
-    for (int k = 0; k < T * T; k++) acc[k] = 0.f;
-  }
-  const int nvp = c.nvp;
-  for (int r0 = 0; r0 < c.nefc; r0 += RB) {
-    const int nr = min(RB, c.nefc - r0);
-    const float4* src = reinterpret_cast<const float4*>(c.J + (size_t)r0 * nvp);
-    float4* dst = reinterpret_cast<float4*>(c.stage);
-    for (int i = c.lane; i < nr * nvp / 4; i += 32) dst[i] = src[i];
-    if (c.lane < RB) {
-      const int r = r0 + c.lane;
-      float De = 0.f, f = 0.f;
-      if (r < c.nefc) {
-        const float jar = c.Jaref[r];
-        if (jar < 0.f) { De = c.D[r]; f = -De * jar; }
-        efc_force[r] = f;
+    if (ns <= 32) {
+      const int T2 = ns * (ns + 1) / 2;
+      for (int t = c.lane; t < T2; t += 32) {
+        int a = (int)((sqrtf(8.f * (float)t + 1.f) - 1.f) * 0.5f);
+        while (a * (a + 1) / 2 > t) a--;
+        while ((a + 1) * (a + 2) / 2 <= t) a++;
+        const int b = t - a * (a + 1) / 2;
+        const int la = c.Li[a], lb = c.Li[b];
+        const int i = la & 0xffff, j = lb & 0xffff;
+        const float s = (la & 0x10000) ? -1.f : 1.f;
+        const float* cd = c.cdof + 6 * i;
+        const float* y = Y + 6 * b;
+        const float v = s * (cd[0] * y[0] + cd[1] * y[1] + cd[2] * y[2] + cd[3] * y[3] + cd[4] * y[4] + cd[5] * y[5]);
+        c.H[max(i, j) * c.ld + min(i, j)] += v;
       }
-      c.sDe[c.lane] = De; c.sf[c.lane] = f;
-    }
-    __syncwarp();
-    for (int rr = 0; rr < nr; rr++) {
-      const float De = c.sDe[rr];
-      if (De == 0.f) continue;
-      const float f = c.sf[rr];
-      const float* row = c.stage + rr * nvp;
-      if (c.lane < nvp) qf0 += row[c.lane] * f;
-      if (c.lane + 32 < nvp) qf1 += row[c.lane + 32] * f;
-      if (withH && bi >= 0) {
-        float a[T], b[T];
-#pragma unroll
-        for (int k = 0; k < T; k++) { a[k] = row[bi * T + k] * De; b[k] = row[bj * T + k]; }
-#pragma unroll
-        for (int x = 0; x < T; x++)
-#pragma unroll
-          for (int y = 0; y < T; y++) acc[x * T + y] += a[x] * b[y];
+    } else {
+      // slow path (support > 32 dofs): every lane walks whole (i, j) pairs recomputing K cd_j on the fly
+      const int T2 = ns * (ns + 1) / 2;
+      for (int t = c.lane; t < T2; t += 32) {
+        int a = (int)((sqrtf(8.f * (float)t + 1.f) - 1.f) * 0.5f);
+        while (a * (a + 1) / 2 > t) a--;
+        while ((a + 1) * (a + 2) / 2 <= t) a++;
+        const int b = t - a * (a + 1) / 2;
+        const int i = a < n2 ? m.body_chain[a2 + cp + a] : m.body_chain[a1 + cp + a - n2];
+        const int j = b < n2 ? m.body_chain[a2 + cp + b] : m.body_chain[a1 + cp + b - n2];
+        const float s = ((a < n2) == (b < n2)) ? 1.f : -1.f;
+        const float* ci = c.cdof + 6 * i; const float* cj = c.cdof + 6 * j;
+        float v = 0.f; int e = 0;
+        for (int p = 0; p < 6; p++) for (int q = 0; q <= p; q++) {
+          const float kv = K[e++];
+          v += kv * ci[p] * cj[q];
+          if (q != p) v += kv * ci[q] * cj[p];
+        }
+        c.H[max(i, j) * c.ld + min(i, j)] += s * v;
       }
     }
-    __syncwarp();
   }
-  if (c.lane < c.nv) c.qfc[c.lane] = qf0;
-  if (c.lane + 32 < c.nv) c.qfc[c.lane + 32] = qf1;
+  __syncwarp();
+}
+
+// Forces / active set from Jaref, qfrc_constraint = J^T f, and (withH) H = M + J^T D J in shared memory.
+DEV void assemble(const SolveCtx& c, const ModelDev& m, bool withH, int ia, int ib) {
+  __syncwarp();
+  for (int i = c.lane; i < c.nvp; i += 32) c.qfc[i] = 0.f;
+  if (withH) {
+    for (int idx = c.lane; idx < c.nv * c.nvp; idx += 32) {
+      const int r = idx / c.nvp, col = idx - r * c.nvp;
+      if (col <= r) c.H[r * c.ld + col] = c.M[idx];
+    }
+  }
+  __syncwarp();
+  // limit rows (they come first): one lane per row, J is +-1 on one dof
+  for (int r = c.lane; r < c.nl; r += 32) {
+    const float jar = c.Jaref[r];
+    if (jar < 0.f) {
+      const float De = c.D[r], g0 = c.G[(size_t)r * 6];
+      const int dof = -1 - c.bp[r];
+      atomicAdd(&c.qfc[dof], -g0 * De * jar);
+      if (withH) atomicAdd(&c.H[dof * c.ld + dof], De);
+    }
+  }
+  __syncwarp();
+  // contact rows: runs of rows with the same body pair are reduced to K (lanes 0..20) and W (lanes 21..26)
+  float acc = 0.f;
+  int cur = -1; bool any = false;
+  for (int r = c.nl; r < c.nefc; r++) {
+    const int bp = c.bp[r];
+    if (bp != cur) {
+      if (any) flush_run(c, m, cur, acc, withH);
+      cur = bp; acc = 0.f; any = false;
+    }
+    const float jar = c.Jaref[r];
+    if (jar < 0.f) {
+      const float De = c.D[r];
+      const float* g = c.G + (size_t)r * 6;
+      const float ga = g[ia];
+      acc += c.lane < 21 ? De * ga * g[ib] : (-De * jar) * ga;
+      any = true;
+    }
+  }
+  if (any) flush_run(c, m, cur, acc, withH);
+  __syncwarp();
 }
 
 template <int T>
@@ -208,21 +306,21 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
-  const int nv = m.nv, nvp = m.nvp, njmax = d.njmax;
+  const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
   SolveCtx c;
-  c.lane = lane; c.nv = nv; c.nvp = nvp; c.ld = b2s_hld(T); c.nefc = d.nefc[w];
+  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.ld = b2s_hld(T); c.nefc = d.nefc[w]; c.nl = d.nl[w];
   c.M = d.qM + (size_t)w * nv * nvp;
-  c.J = d.efc_J + (size_t)w * njmax * nvp;
-  c.D = d.efc_D + (size_t)w * njmax;
+  c.G = d.efc_g + (size_t)w * njmax * 6;
+  c.bp = d.efc_bp + (size_t)w * njmax;
   c.aref = d.efc_aref + (size_t)w * njmax;
-  float* base = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, njmax, T);
-  c.stage = base; base += RB * nvp;          // read slightly past its end by the last Hessian block
-  c.sDe = base + 7 * T; c.sf = c.sDe + RB; base += 7 * T + 2 * RB;
+  float* base = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, T);
   c.H = base; base += b2s_hdim(T) * c.ld;
   c.invd = base; base += 7 * T;
   c.qacc = base; c.Ma = base + nvp; c.grad = base + 2 * nvp; c.search = base + 3 * nvp; c.Mv = base + 4 * nvp;
   c.qfs = base + 5 * nvp; c.qas = base + 6 * nvp; c.qfc = base + 7 * nvp; base += 8 * nvp;
-  c.Jaref = base; c.Jv = base + njmax; base += 2 * njmax;
+  c.cdof = base; base += 6 * nv;
+  c.X = base; c.KW = base + 6 * max(nb, 32); c.Li = (int*)(c.KW + 32); base += solve_scratch_floats(nb);
+  c.Jaref = base; c.Jv = base + njmax; c.D = base + 2 * njmax;
   float* efc_force = d.efc_force + (size_t)w * njmax;
   float* g_qacc = d.qacc + (size_t)w * nv;
   float* g_qfc = d.qfrc_constraint + (size_t)w * nv;
@@ -231,29 +329,41 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
     c.qfs[i] = i < nv ? d.qfrc_smooth[(size_t)w * nv + i] : 0.f;
     c.search[i] = 0.f; c.qacc[i] = 0.f; c.qfc[i] = 0.f;
   }
-  // the RB*nvp staging tile is read slightly past nvp by the last Hessian block: keep the tail finite
-  for (int i = lane; i < RB * nvp + 7 * T; i += 32) c.stage[i] = 0.f;   // tail [RB*nvp, +7T) stays zero
-  __syncwarp();
   if (c.nefc == 0) {
+    __syncwarp();
     for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qas[i]; g_qfc[i] = 0.f; }
     if (lane == 0) { d.solver_niter[w] = 0; d.solver_cost[w] = 0.f; }
     return;
   }
-  // lower-triangular Hessian block owned by this lane
-  int bi, bj;
-  tile_owner(lane, bi, bj);
+  // cdof about the world's reference point (other kinematic trees are re-referenced), efc_D of the rows
+  {
+    const float* com = d.subtree_com + (size_t)w * nb * 3;
+    const v3 cref = ld3(com + 3 * m.ref_root);
+    for (int i = lane; i < nv; i += 32) {
+      sv6 cd = ld6(d.cdof + ((size_t)w * nv + i) * 6);
+      const int rb = m.body_rootid[m.dof_bodyid[i]];
+      if (rb != m.ref_root) {
+        const v3 lin = mk3(cd.v[3], cd.v[4], cd.v[5]) + cross(mk3(cd.v[0], cd.v[1], cd.v[2]), cref - ld3(com + 3 * rb));
+        cd.v[3] = lin.x; cd.v[4] = lin.y; cd.v[5] = lin.z;
+      }
+      st6(c.cdof + 6 * i, cd);
+    }
+    for (int r = lane; r < c.nefc; r += 32) c.D[r] = d.efc_D[(size_t)w * njmax + r];
+  }
+  // K / W entry owned by this lane in the run reduction: lanes 0..20 -> (ia, ib) of the symmetric 6x6, 21..26 -> W
+  int ia = 0, ib = 0;
+  if (lane < 21) { int e = lane; while (e > ia) { e -= ia + 1; ia++; } ib = e; }
+  else if (lane < 27) { ia = lane - 21; ib = 0; }
   // ---- warm start (mj_fwdConstraint): keep qacc_warmstart only if it beats qacc_smooth
   const bool warm = !(m.disableflags & B2S_DSBL_WARMSTART);
   for (int i = lane; i < nv; i += 32) c.qacc[i] = warm ? d.qacc_warmstart[(size_t)w * nv + i] : c.qas[i];
   __syncwarp();
   mat_vec_M(c, c.qacc, c.Ma);
-  mat_vec_J(c, c.qacc, c.aref, c.Jaref);
-  __syncwarp();
+  mat_vec_J(c, m, c.qacc, c.aref, c.Jaref);
   float gauss = gauss_term(c);
   float cost = constraint_cost(c, c.Jaref) + gauss;
   if (warm) {
-    mat_vec_J(c, c.qas, c.aref, c.Jv);   // Jv as scratch
-    __syncwarp();
+    mat_vec_J(c, m, c.qas, c.aref, c.Jv);   // Jv as scratch
     const float cost_smooth = constraint_cost(c, c.Jv);
     if (cost > cost_smooth) {
       for (int i = lane; i < nv; i += 32) c.qacc[i] = c.qas[i];
@@ -267,29 +377,15 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
   }
   const float scale = 1.0f / (m.meaninertia * (float)max(nv, 1));
   int iter = 0;
-  float acc[T * T];
   while (true) {
-    __syncwarp();
-    pass_JT<T>(c, efc_force, true, bi, bj, acc);
-    __syncwarp();
+    assemble(c, m, true, ia, ib);
     float gn = 0.f;
     for (int i = lane; i < nv; i += 32) { const float g = c.Ma[i] - c.qfs[i] - c.qfc[i]; c.grad[i] = g; gn += g * g; }
     gn = sqrtf(warp_sum(gn));
     if (iter > 0 && scale * gn < m.tolerance) break;
     if (iter >= m.iterations) break;
-    // H = M + J^T D J: add M to the register tiles (identity on the padding), blocked Cholesky in registers
-    // (tiles exchanged through c.H, which ends up holding L), search = -H^-1 grad
-    if (bi >= 0) {
-#pragma unroll
-      for (int x = 0; x < T; x++)
-#pragma unroll
-        for (int y = 0; y < T; y++) {
-          const int i = bi * T + x, j = bj * T + y;
-          if (i < nv && j < nv) acc[x * T + y] += c.M[(size_t)i * nvp + j];
-          else acc[x * T + y] = (i == j) ? 1.0f : 0.0f;
-        }
-    }
-    tile_cholesky_regs<T>(acc, bi, bj, c.H, c.ld, c.invd);
+    // blocked Cholesky of H on register tiles (c.H ends up holding L), search = -H^-1 grad
+    tile_cholesky_smem<T>(c.H, nv, c.ld, lane, c.invd);
     float b0 = lane < nv ? c.grad[lane] : 0.f, b1 = lane + 32 < nv ? c.grad[lane + 32] : 0.f;
     warp_chol_solve_inv(c.H, c.invd, nv, c.ld, lane, b0, b1);
     if (lane < nv) c.search[lane] = -b0;
@@ -297,8 +393,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
     __syncwarp();
     // line-search set-up: Mv, Jv, quadratic Gauss coefficients
     mat_vec_M(c, c.search, c.Mv);
-    mat_vec_J(c, c.search, nullptr, c.Jv);
-    __syncwarp();
+    mat_vec_J(c, m, c.search, nullptr, c.Jv);
     float g1 = 0.f, g2 = 0.f;
     for (int i = lane; i < nv; i += 32) { g1 += c.search[i] * (c.Ma[i] - c.qfs[i]); g2 += c.search[i] * c.Mv[i]; }
     float qg[3] = {gauss, warp_sum(g1), 0.5f * warp_sum(g2)};
@@ -312,13 +407,13 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
     cost = constraint_cost(c, c.Jaref) + gauss;
     iter++;
     if (scale * (old - cost) < m.tolerance) {
-      __syncwarp();
-      pass_JT<T>(c, efc_force, false, bi, bj, acc);
-      __syncwarp();
+      assemble(c, m, false, ia, ib);
       break;
     }
   }
+  __syncwarp();
   for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qacc[i]; g_qfc[i] = c.qfc[i]; }
+  for (int r = lane; r < c.nefc; r += 32) { const float jar = c.Jaref[r]; efc_force[r] = jar < 0.f ? -c.D[r] * jar : 0.f; }
   if (lane == 0) { d.solver_niter[w] = iter; d.solver_cost[w] = cost; }
 }
 
@@ -342,7 +437,7 @@ void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   b2s_count_launch();
 }
 size_t smem_solve(const ModelDev& m, const DataDev& d) {
-  return (size_t)B2S_WARPS_PER_CTA * solve_smem_floats(m.nv, m.nvp, d.njmax, tile_for(m.nv)) * sizeof(float);
+  return (size_t)B2S_WARPS_PER_CTA * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, tile_for(m.nv)) * sizeof(float);
 }
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;

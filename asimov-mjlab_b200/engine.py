@@ -63,6 +63,7 @@ def lib():
     L.b2s_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.b2s_step_n.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.b2s_step_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.b2s_efc_jacobian.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.b2s_profile_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
     _LIB = L
   return _LIB
@@ -222,7 +223,7 @@ class _Sub:
   def __getattr__(self, k):
     if k.startswith("_"):
       raise AttributeError(k)
-    return getattr(self._d, self._p + k)
+    return getattr(self._d, self._p + k)   # efc.J -> Data.efc_J (materialised on access)
 
 
 class Data(_Struct):
@@ -241,6 +242,17 @@ class Data(_Struct):
     _check(lib().b2s_data_field(self._h.ptr, name.encode(), C.byref(info)))
     t, _ = _as_tensor(self._h, info, self._device)
     return t
+
+  @property
+  def efc_J(self):
+    """Dense constraint Jacobian (mjwarp's Data.efc.J), shape (nworld, njmax, roundup4(nv)).  The step keeps
+    rows matrix-free (efc_g, efc_bp); every access re-materialises the dense matrix from the current rows."""
+    info = abi.FieldInfo()
+    _check(lib().b2s_efc_jacobian(self._model._h.ptr, self._h.ptr, _stream(self._model), C.byref(info)))
+    cache = self.__dict__["_cache"]
+    if "efc_J" not in cache:
+      cache["efc_J"], _ = _as_tensor(self._h, info, self._device)
+    return cache["efc_J"]
 
   @property
   def bytes(self):

@@ -243,6 +243,11 @@ int b2s_data_num_fields(const b2s_data* d);
 const char* b2s_data_field_name(const b2s_data* d, int i);
 int64_t b2s_data_bytes(const b2s_data* d);
 
+/* Dense constraint Jacobian (mjwarp's Data.efc.J, shape nworld x njmax x roundup4(nv)).  The step keeps
+ * constraint rows in a matrix-free geometric form (efc_g, efc_bp); this materialises the dense matrix on
+ * demand into storage owned by `d` (allocated on first use; call again after a step to refresh it). */
+int b2s_efc_jacobian(const b2s_model* m, b2s_data* d, void* stream, b2s_field_info* out);
+
 /* forward / step on `stream` (a cudaStream_t passed as void*). */
 int b2s_forward(const b2s_model* m, b2s_data* d, void* stream);
 int b2s_step(const b2s_model* m, b2s_data* d, void* stream);

@@ -25,6 +25,9 @@ D.ctrl[:] += (0.1 * torch.randn(W, m.nu, generator=g)).cuda()
 engine.step(M, D, warm)
 torch.cuda.synchronize()
 print("ncon mean %.1f nefc mean %.1f niter mean %.2f" % (D.ncon.float().mean().item(), D.nefc.float().mean().item(), D.solver_niter.float().mean().item()))
+print("nefc hist", torch.bincount(D.nefc.cpu() // 8).tolist())
+print("niter hist", torch.bincount(D.solver_niter.cpu()).tolist())
+print("ncon hist", torch.bincount(D.ncon.cpu()).tolist())
 engine.step(M, D, steps)
 torch.cuda.synchronize()
 print("stage ms", engine.profile_step(M, D, 10))
