@@ -282,20 +282,54 @@ DEV void tile_cholesky_smem(float* S, int n, int ld, int lane, float* invd) {
   tile_cholesky_regs<T>(a, bi, bj, S, ld, invd);
 }
 // Substitution with the factor above: lane l holds b[l] in b0 and b[l+32] in b1 (n <= 64).
+// REQUIRES the strict upper triangle of L's storage to be zero (rows < hdim): the running residual
+// t_l = b_l - sum_j L[l][j] y_j is then updated by every lane without predicates.
 DEV void warp_chol_solve_inv(const float* L, const float* invd, int n, int ld, int lane, float& b0, float& b1) {
-  for (int k = 0; k < n; k++) {
-    const float bk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
-    if (lane == k) b0 = bk;
-    if (lane + 32 == k) b1 = bk;
-    if (lane > k && lane < n) b0 -= L[lane * ld + k] * bk;
-    if (lane + 32 > k && lane + 32 < n) b1 -= L[(lane + 32) * ld + k] * bk;
+  const bool hi = n > 32;
+  const int row0 = min(lane, n - 1), row1 = min(lane + 32, n - 1);   // clamp: lanes without a row re-read row n-1 (result unused)
+  const int col0 = min(lane, ld - 1), col1 = min(lane + 32, ld - 1);
+  float y0 = 0.f, y1 = 0.f;
+  for (int k = 0; k < n; k++) {                // forward: L y = b
+    const float yk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
+    if (lane == (k & 31)) { if (k < 32) y0 = yk; else y1 = yk; }
+    b0 -= L[row0 * ld + k] * yk;
+    if (hi) b1 -= L[row1 * ld + k] * yk;
   }
+  // backward: L^T x = y
+  if (lane >= n) y0 = 0.f;
+  if (lane + 32 >= n) y1 = 0.f;
   for (int k = n - 1; k >= 0; k--) {
-    const float xk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
-    if (lane == k) b0 = xk;
-    if (lane + 32 == k) b1 = xk;
-    if (lane < k) b0 -= L[k * ld + lane] * xk;
-    if (lane + 32 < k) b1 -= L[k * ld + lane + 32] * xk;
+    const float xk = __shfl_sync(FULL, k < 32 ? y0 : y1, k & 31) * invd[k];
+    if (lane == (k & 31)) { if (k < 32) b0 = xk; else b1 = xk; }
+    y0 -= L[k * ld + col0] * xk;
+    if (hi) y1 -= L[k * ld + col1] * xk;
+  }
+}
+// Same substitution with the PADDED dimension N = 7T as a compile-time constant: fully unrolled, shared-memory
+// offsets become immediates.  Rows/cols n..N-1 of L are the identity padding written by the tile Cholesky and
+// the matching entries of b must be 0 on entry.  REQUIRES a zero strict upper triangle in L's storage.
+template <int T>
+DEV void tile_chol_solve(const float* L, const float* invd, int ld, int lane, float& b0, float& b1) {
+  constexpr int N = 7 * T;
+  constexpr bool HI = N > 32;
+  const float* Lr0 = L + min(lane, N - 1) * ld;
+  const float* Lr1 = L + min(lane + 32, N - 1) * ld;
+  const float* Lc0 = L + min(lane, N - 1);
+  const float* Lc1 = L + min(lane + 32, N - 1);
+  float y0 = 0.f, y1 = 0.f;
+#pragma unroll
+  for (int k = 0; k < N; k++) {
+    const float yk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
+    if (k < 32) { if (lane == k) y0 = yk; } else { if (lane == k - 32) y1 = yk; }
+    b0 -= Lr0[k] * yk;
+    if (HI) b1 -= Lr1[k] * yk;
+  }
+#pragma unroll
+  for (int k = N - 1; k >= 0; k--) {
+    const float xk = __shfl_sync(FULL, k < 32 ? y0 : y1, k & 31) * invd[k];
+    if (k < 32) { if (lane == k) b0 = xk; } else { if (lane == k - 32) b1 = xk; }
+    y0 -= Lc0[k * ld] * xk;
+    if (HI) y1 -= Lc1[k * ld] * xk;
   }
 }
 __host__ __device__ inline int b2s_hdim(int T) { return 7 * T; }                         // padded matrix dimension

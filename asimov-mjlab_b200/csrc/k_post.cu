@@ -308,6 +308,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const Mode
     for (int i = lane; i < nv * nvp; i += 32) {
       const int r = i / nvp, c = i - r * nvp;
       if (c <= r) A[r * ld + c] = M[i] - (c == r ? dt * dg[r] : 0.f);
+      else if (c < nv) A[r * ld + c] = 0.f;     // the substitution needs a zero strict upper triangle
     }
     __syncwarp();
     tile_cholesky_smem<T>(A, nv, ld, lane, invd);

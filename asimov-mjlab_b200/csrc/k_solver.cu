@@ -18,21 +18,48 @@
 extern __shared__ float b2s_smem[];
 
 __host__ __device__ inline int solve_scratch_floats(int nb) { return 6 * (nb > 32 ? nb : 32) + 32 + 32; }
-__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int T) {
-  const int n = b2s_hdim(T) * b2s_hld(T) + 7 * T + 8 * nvp + 6 * nv + solve_scratch_floats(nb) + 3 * njmax;
-  return (n + 3) & ~3;
+__host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      // offset of the scratch area
+  const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
+  return (HF + 8 * NVP + 6 * N + 3 * njmax + nconmax + 2 + 3) & ~3;
+}
+__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T) {
+  return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + 3) & ~3;
 }
 
+// Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
+//   H hdim*ld | invd 7T (padded to a float4 multiple) | 8 vectors of NVP | cdof 6*hdim | Jaref, Jv, D njmax each |
+//   run list nconmax+2 | scratch X/Y 6*max(nb,32), KW 32, Li 32
+template <int T>
 struct SolveCtx {
-  int lane, nv, nvp, nb, nefc, nl, ld;
+  static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 8 * NVP + 6 * N;
+  int lane, nv, nvp, nb, nefc, nl, nrun, njmax, soff;
+  static constexpr int ld = LD, hfloats = HF;
   const float *M, *G, *aref;
   const int* bp;
-  float *H, *invd, *qacc, *Ma, *grad, *search, *Mv, *qfs, *qas, *qfc, *cdof, *X, *KW, *Jaref, *Jv, *D;
-  int* Li;
+  float* sm;
+  DEV float* H() const { return sm; }
+  DEV float* invd() const { return sm + N * LD; }
+  DEV float* qacc() const { return sm + HF; }
+  DEV float* Ma() const { return sm + HF + NVP; }
+  DEV float* grad() const { return sm + HF + 2 * NVP; }
+  DEV float* search() const { return sm + HF + 3 * NVP; }
+  DEV float* Mv() const { return sm + HF + 4 * NVP; }
+  DEV float* qfs() const { return sm + HF + 5 * NVP; }
+  DEV float* qas() const { return sm + HF + 6 * NVP; }
+  DEV float* qfc() const { return sm + HF + 7 * NVP; }
+  DEV float* cdof() const { return sm + HF + 8 * NVP; }
+  DEV float* Jaref() const { return sm + FIX; }
+  DEV float* Jv() const { return sm + FIX + njmax; }
+  DEV float* D() const { return sm + FIX + 2 * njmax; }
+  DEV int* run() const { return (int*)(sm + FIX + 3 * njmax); }
+  DEV float* X() const { return sm + soff; }
+  DEV float* KW() const { return sm + soff + 6 * max(nb, 32); }
+  DEV int* Li() const { return (int*)(sm + soff + 6 * max(nb, 32) + 32); }
 };
 
 // y[i] = sum_j M[i][j] x[j]; M symmetric in HBM/L2, read column-wise so lanes hit contiguous addresses
-DEV void mat_vec_M(const SolveCtx& c, const float* x, float* y) {
+template <int T>
+DEV void mat_vec_M(const SolveCtx<T>& c, const float* x, float* y) {
   float a0 = 0.f, a1 = 0.f;
   for (int j = 0; j < c.nv; j++) {
     const float xj = x[j];
@@ -44,12 +71,13 @@ DEV void mat_vec_M(const SolveCtx& c, const float* x, float* y) {
   if (c.lane + 32 < c.nv) y[c.lane + 32] = a1;
 }
 // out[r] = J[r] . x - sub[r], matrix-free: body spatial vectors X[b] first (one lane per body), then one lane per row
-DEV void mat_vec_J(const SolveCtx& c, const ModelDev& m, const float* x, const float* sub, float* out) {
+template <int T>
+DEV void mat_vec_J(const SolveCtx<T>& c, const ModelDev& m, const float* x, const float* sub, float* out) {
   __syncwarp();
   for (int b = c.lane; b < c.nb; b += 32) {
     sv6 v = zero6();
-    for (int k = m.body_chain_adr[b]; k < m.body_chain_adr[b + 1]; k++) { const int i = m.body_chain[k]; axpy6(v, x[i], ld6(c.cdof + 6 * i)); }
-    st6(c.X + 6 * b, v);
+    for (int k = m.body_chain_adr[b]; k < m.body_chain_adr[b + 1]; k++) { const int i = m.body_chain[k]; axpy6(v, x[i], ld6(c.cdof() + 6 * i)); }
+    st6(c.X() + 6 * b, v);
   }
   __syncwarp();
   for (int r = c.lane; r < c.nefc; r += 32) {
@@ -60,8 +88,8 @@ DEV void mat_vec_J(const SolveCtx& c, const ModelDev& m, const float* x, const f
     if (bp < 0) s = g01.x * x[-1 - bp];
     else {
       const float2 g23 = gp[1], g45 = gp[2];
-      const float* x2 = c.X + 6 * (bp >> 16);
-      const float* x1 = c.X + 6 * (bp & 0xffff);
+      const float* x2 = c.X() + 6 * (bp >> 16);
+      const float* x1 = c.X() + 6 * (bp & 0xffff);
       s = g01.x * (x2[0] - x1[0]) + g01.y * (x2[1] - x1[1]) + g23.x * (x2[2] - x1[2]) + g23.y * (x2[3] - x1[3]) +
           g45.x * (x2[4] - x1[4]) + g45.y * (x2[5] - x1[5]);
     }
@@ -69,51 +97,58 @@ DEV void mat_vec_J(const SolveCtx& c, const ModelDev& m, const float* x, const f
   }
   __syncwarp();
 }
-DEV float gauss_term(const SolveCtx& c) {
+template <int T>
+DEV float gauss_term(const SolveCtx<T>& c) {
   float g = 0.f;
-  for (int i = c.lane; i < c.nv; i += 32) g += (c.Ma[i] - c.qfs[i]) * (c.qacc[i] - c.qas[i]);
+  for (int i = c.lane; i < c.nv; i += 32) g += (c.Ma()[i] - c.qfs()[i]) * (c.qacc()[i] - c.qas()[i]);
   return 0.5f * warp_sum(g);
 }
-DEV float constraint_cost(const SolveCtx& c, const float* jar) {
+template <int T>
+DEV float constraint_cost(const SolveCtx<T>& c, const float* jar) {
   float s = 0.f;
-  for (int r = c.lane; r < c.nefc; r += 32) { const float x = jar[r]; if (x < 0.f) s += 0.5f * c.D[r] * x * x; }
+  for (int r = c.lane; r < c.nefc; r += 32) { const float x = jar[r]; if (x < 0.f) s += 0.5f * c.D()[r] * x * x; }
   return warp_sum(s);
 }
 struct LsPoint { float alpha, cost, d0, d1; };
-DEV LsPoint ls_eval(const SolveCtx& c, const float* qg, float alpha) {
+// arguments of the exact (iterative) line search, passed BY VALUE so that this cold, out-of-line path does not
+// force the solver context into local memory
+struct LsArgs { const float *Jaref, *Jv, *D, *search; int nefc, nv, lane, maxit; float gtol_unit, q0, q1, q2; };
+__device__ __noinline__ LsPoint ls_eval(const LsArgs a, float alpha) {
   float q0 = 0.f, q1 = 0.f, q2 = 0.f;
-  for (int r = c.lane; r < c.nefc; r += 32) {
-    const float ja = c.Jaref[r], jv = c.Jv[r];
-    if (ja + alpha * jv < 0.f) { const float D = c.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
+#pragma unroll 1
+  for (int r = a.lane; r < a.nefc; r += 32) {
+    const float ja = a.Jaref[r], jv = a.Jv[r];
+    if (ja + alpha * jv < 0.f) { const float D = a.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
   }
-  q0 = warp_sum(q0) + qg[0]; q1 = warp_sum(q1) + qg[1]; q2 = warp_sum(q2) + qg[2];
+  q0 = warp_sum(q0) + a.q0; q1 = warp_sum(q1) + a.q1; q2 = warp_sum(q2) + a.q2;
   LsPoint p;
   p.alpha = alpha; p.cost = alpha * alpha * q2 + alpha * q1 + q0; p.d0 = 2.f * alpha * q2 + q1; p.d1 = fmaxf(2.f * q2, B2S_MINVAL);
   return p;
 }
-DEV float ls_iterative(const SolveCtx& c, const ModelDev& m, const float* qg) {
+__device__ __noinline__ float ls_iterative(const LsArgs a) {
   float sn = 0.f;
-  for (int i = c.lane; i < c.nv; i += 32) sn += c.search[i] * c.search[i];
+#pragma unroll 1
+  for (int i = a.lane; i < a.nv; i += 32) sn += a.search[i] * a.search[i];
   sn = sqrtf(warp_sum(sn));
   if (sn < B2S_MINVAL) return 0.f;
-  const float gtol = m.tolerance * m.ls_tolerance * sn * m.meaninertia * (float)max(c.nv, 1);
-  const int maxit = m.ls_iterations;
+  const float gtol = a.gtol_unit * sn;
+  const int maxit = a.maxit;
   int it = 0;
-  const LsPoint p0 = ls_eval(c, qg, 0.f);
-  LsPoint p1 = ls_eval(c, qg, p0.alpha - p0.d0 / p0.d1); it++;
+  const LsPoint p0 = ls_eval(a, 0.f);
+  LsPoint p1 = ls_eval(a, p0.alpha - p0.d0 / p0.d1); it++;
   if (p0.cost < p1.cost) p1 = p0;
   if (fabsf(p1.d0) < gtol) return p1.alpha;
   const float dir = p1.d0 < 0.f ? 1.f : -1.f;
   LsPoint p2 = p0; bool p2upd = false;
   while (p1.d0 * dir <= -gtol && it < maxit) {
     p2 = p1; p2upd = true;
-    p1 = ls_eval(c, qg, p1.alpha - p1.d0 / p1.d1); it++;
+    p1 = ls_eval(a, p1.alpha - p1.d0 / p1.d1); it++;
     if (fabsf(p1.d0) < gtol) return p1.alpha;
   }
   if (it >= maxit || !p2upd) return p1.alpha;
-  LsPoint p2next = p1, p1next = ls_eval(c, qg, p1.alpha - p1.d0 / p1.d1); it++;
+  LsPoint p2next = p1, p1next = ls_eval(a, p1.alpha - p1.d0 / p1.d1); it++;
   while (it < maxit) {
-    const LsPoint pmid = ls_eval(c, qg, 0.5f * (p1.alpha + p2.alpha)); it++;
+    const LsPoint pmid = ls_eval(a, 0.5f * (p1.alpha + p2.alpha)); it++;
     bool b1 = false, b2 = false;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
@@ -124,8 +159,8 @@ DEV float ls_iterative(const SolveCtx& c, const ModelDev& m, const float* qg) {
       else if (cd.d0 * dir > 0.f && in && !b1) { p1 = cd; b1 = true; }
     }
     if (!b1 && !b2) return pmid.cost < p0.cost ? pmid.alpha : 0.f;
-    if (b1) { p1next = ls_eval(c, qg, p1.alpha - p1.d0 / p1.d1); it++; }
-    if (b2) { p2next = ls_eval(c, qg, p2.alpha - p2.d0 / p2.d1); it++; }
+    if (b1) { p1next = ls_eval(a, p1.alpha - p1.d0 / p1.d1); it++; }
+    if (b2) { p2next = ls_eval(a, p2.alpha - p2.d0 / p2.d1); it++; }
   }
   if (p1.cost <= p2.cost && p1.cost < p0.cost) return p1.alpha;
   if (p2.cost <= p1.cost && p2.cost < p0.cost) return p2.alpha;
@@ -134,7 +169,8 @@ DEV float ls_iterative(const SolveCtx& c, const ModelDev& m, const float* qg) {
 // one lane per candidate step: alpha_k = min_step^(k/(n-1)), k = 0..n-1, and alpha = 0 on one more lane; rows are
 // summed in row order by every lane (same order as the oracle), the best candidate wins (ties: alpha = 0, then
 // the smallest k), so a step is only taken if it strictly improves on alpha = 0
-DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
+template <int T>
+DEV float ls_parallel(const SolveCtx<T>& c, const ModelDev& m, const float* qg) {
   const int n = m.ls_iterations;
   const float lg = logf(m.ls_parallel_min_step);
   float best = 3.0e38f, balpha = 0.f; int bk = 0x7fffffff;
@@ -144,8 +180,8 @@ DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
       const float alpha = k == n ? 0.f : (n > 1 ? expf((float)k / (float)(n - 1) * lg) : 1.f);
       float q0 = qg[0], q1 = qg[1], q2 = qg[2];
       for (int r = 0; r < c.nefc; r++) {
-        const float ja = c.Jaref[r], jv = c.Jv[r];
-        if (ja + alpha * jv < 0.f) { const float D = c.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
+        const float ja = c.Jaref()[r], jv = c.Jv()[r];
+        if (ja + alpha * jv < 0.f) { const float D = c.D()[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
       }
       const float cost = alpha * alpha * q2 + alpha * q1 + q0;
       const int kk = k == n ? -1 : k;
@@ -164,8 +200,9 @@ DEV float ls_parallel(const SolveCtx& c, const ModelDev& m, const float* qg) {
 
 // A run of contact rows that share the body pair (b1, b2) has been reduced to K (21 lanes) and W (6 lanes):
 // apply it to qfrc_constraint and (withH) to the lower triangle of H.
-DEV void flush_run(const SolveCtx& c, const ModelDev& m, int bp, float acc, bool withH) {
-  c.KW[c.lane] = acc;
+template <int T>
+DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, bool withH) {
+  c.KW()[c.lane] = acc;
   const int b1 = bp & 0xffff, b2 = bp >> 16;
   const int a1 = m.body_chain_adr[b1], n1f = m.body_chain_adr[b1 + 1] - a1;
   const int a2 = m.body_chain_adr[b2], n2f = m.body_chain_adr[b2 + 1] - a2;
@@ -184,8 +221,8 @@ DEV void flush_run(const SolveCtx& c, const ModelDev& m, int bp, float acc, bool
   }
   const int n2 = n2f - cp, n1 = n1f - cp, ns = n1 + n2;
   __syncwarp();
-  const float* K = c.KW; const float* W = c.KW + 21;
-  float* Y = c.X;    // 6 floats per support entry (the body-vector scratch is idle during assembly)
+  const float* K = c.KW(); const float* W = c.KW() + 21;
+  float* Y = c.X();    // 6 floats per support entry (the body-vector scratch is idle during assembly)
   for (int base = 0; base < ns; base += 32) {
     // supports longer than 32 dofs are processed in chunks; Y/Li then hold one chunk at a time, so the cross
     // terms between chunks are handled by the (rare) slow path below
@@ -193,8 +230,8 @@ DEV void flush_run(const SolveCtx& c, const ModelDev& m, int bp, float acc, bool
     if (a < ns) {
       const int i = a < n2 ? m.body_chain[a2 + cp + a] : m.body_chain[a1 + cp + a - n2];
       const float s = a < n2 ? 1.f : -1.f;
-      const sv6 cd = ld6(c.cdof + 6 * i);
-      c.qfc[i] += s * (cd.v[0] * W[0] + cd.v[1] * W[1] + cd.v[2] * W[2] + cd.v[3] * W[3] + cd.v[4] * W[4] + cd.v[5] * W[5]);
+      const sv6 cd = ld6(c.cdof() + 6 * i);
+      c.qfc()[i] += s * (cd.v[0] * W[0] + cd.v[1] * W[1] + cd.v[2] * W[2] + cd.v[3] * W[3] + cd.v[4] * W[4] + cd.v[5] * W[5]);
       if (withH && ns <= 32) {
         // Y = s K cd with K symmetric, entries ordered (0,0) (1,0) (1,1) (2,0) ...
         float y[6];
@@ -211,7 +248,7 @@ DEV void flush_run(const SolveCtx& c, const ModelDev& m, int bp, float acc, bool
           }
 #pragma unroll
         for (int p = 0; p < 6; p++) Y[6 * a + p] = s * y[p];
-        c.Li[a] = i | (a < n2 ? 0 : 0x10000);
+        c.Li()[a] = i | (a < n2 ? 0 : 0x10000);
       }
     }
   }
@@ -224,13 +261,13 @@ DEV void flush_run(const SolveCtx& c, const ModelDev& m, int bp, float acc, bool
         while (a * (a + 1) / 2 > t) a--;
         while ((a + 1) * (a + 2) / 2 <= t) a++;
         const int b = t - a * (a + 1) / 2;
-        const int la = c.Li[a], lb = c.Li[b];
+        const int la = c.Li()[a], lb = c.Li()[b];
         const int i = la & 0xffff, j = lb & 0xffff;
         const float s = (la & 0x10000) ? -1.f : 1.f;
-        const float* cd = c.cdof + 6 * i;
+        const float* cd = c.cdof() + 6 * i;
         const float* y = Y + 6 * b;
         const float v = s * (cd[0] * y[0] + cd[1] * y[1] + cd[2] * y[2] + cd[3] * y[3] + cd[4] * y[4] + cd[5] * y[5]);
-        c.H[max(i, j) * c.ld + min(i, j)] += v;
+        c.H()[max(i, j) * c.ld + min(i, j)] += v;
       }
     } else {
       // slow path (support > 32 dofs): every lane walks whole (i, j) pairs recomputing K cd_j on the fly
@@ -243,62 +280,93 @@ DEV void flush_run(const SolveCtx& c, const ModelDev& m, int bp, float acc, bool
         const int i = a < n2 ? m.body_chain[a2 + cp + a] : m.body_chain[a1 + cp + a - n2];
         const int j = b < n2 ? m.body_chain[a2 + cp + b] : m.body_chain[a1 + cp + b - n2];
         const float s = ((a < n2) == (b < n2)) ? 1.f : -1.f;
-        const float* ci = c.cdof + 6 * i; const float* cj = c.cdof + 6 * j;
+        const float* ci = c.cdof() + 6 * i; const float* cj = c.cdof() + 6 * j;
         float v = 0.f; int e = 0;
         for (int p = 0; p < 6; p++) for (int q = 0; q <= p; q++) {
           const float kv = K[e++];
           v += kv * ci[p] * cj[q];
           if (q != p) v += kv * ci[q] * cj[p];
         }
-        c.H[max(i, j) * c.ld + min(i, j)] += s * v;
+        c.H()[max(i, j) * c.ld + min(i, j)] += s * v;
       }
     }
   }
   __syncwarp();
 }
 
-// Forces / active set from Jaref, qfrc_constraint = J^T f, and (withH) H = M + J^T D J in shared memory.
-DEV void assemble(const SolveCtx& c, const ModelDev& m, bool withH, int ia, int ib) {
+// Forces / active set from Jaref, qfrc_constraint = J^T f, and (withH) J^T D J into the (zeroed) lower triangle
+// of H in shared memory; M is added when the tiles are loaded for the factorisation.
+template <int T>
+DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, int ib) {
   __syncwarp();
-  for (int i = c.lane; i < c.nvp; i += 32) c.qfc[i] = 0.f;
+  for (int i = c.lane; i < c.nvp; i += 32) c.qfc()[i] = 0.f;
   if (withH) {
-    for (int idx = c.lane; idx < c.nv * c.nvp; idx += 32) {
-      const int r = idx / c.nvp, col = idx - r * c.nvp;
-      if (col <= r) c.H[r * c.ld + col] = c.M[idx];
-    }
+    float4* h4 = reinterpret_cast<float4*>(c.H());
+    for (int i = c.lane; i < c.hfloats / 4; i += 32) h4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncwarp();
   // limit rows (they come first): one lane per row, J is +-1 on one dof
   for (int r = c.lane; r < c.nl; r += 32) {
-    const float jar = c.Jaref[r];
+    const float jar = c.Jaref()[r];
     if (jar < 0.f) {
-      const float De = c.D[r], g0 = c.G[(size_t)r * 6];
+      const float De = c.D()[r], g0 = c.G[(size_t)r * 6];
       const int dof = -1 - c.bp[r];
-      atomicAdd(&c.qfc[dof], -g0 * De * jar);
-      if (withH) atomicAdd(&c.H[dof * c.ld + dof], De);
+      atomicAdd(&c.qfc()[dof], -g0 * De * jar);
+      if (withH) atomicAdd(&c.H()[dof * c.ld + dof], De);
     }
   }
   __syncwarp();
-  // contact rows: runs of rows with the same body pair are reduced to K (lanes 0..20) and W (lanes 21..26)
-  float acc = 0.f;
-  int cur = -1; bool any = false;
-  for (int r = c.nl; r < c.nefc; r++) {
-    const int bp = c.bp[r];
-    if (bp != cur) {
-      if (any) flush_run(c, m, cur, acc, withH);
-      cur = bp; acc = 0.f; any = false;
+  // contact rows: each run of rows with the same body pair is reduced to K (lanes 0..20) and W (lanes 21..26)
+  const float* gA = c.G + ia;
+  const float* gB = c.G + ib;
+  const bool isK = c.lane < 21;
+  for (int k = 0; k < c.nrun; k++) {
+    const int r0 = c.run()[k], r1 = c.run()[k + 1];
+    float acc = 0.f;
+    bool any = false;
+#pragma unroll 4
+    for (int r = r0; r < r1; r++) {
+      const float jar = c.Jaref()[r];
+      const float De = jar < 0.f ? c.D()[r] : 0.f;
+      const float ga = gA[(size_t)r * 6], gb = gB[(size_t)r * 6];
+      acc += (isK ? De * gb : -De * jar) * ga;
+      any |= jar < 0.f;
     }
-    const float jar = c.Jaref[r];
-    if (jar < 0.f) {
-      const float De = c.D[r];
-      const float* g = c.G + (size_t)r * 6;
-      const float ga = g[ia];
-      acc += c.lane < 21 ? De * ga * g[ib] : (-De * jar) * ga;
-      any = true;
-    }
+    if (any) flush_run(c, m, c.bp[r0], acc, withH);
   }
-  if (any) flush_run(c, m, cur, acc, withH);
   __syncwarp();
+}
+
+// Load the lower-triangular register tiles of H = M + (J^T D J in shared memory) and factorise.
+template <int T>
+DEV void factor_H(const SolveCtx<T>& c, int bi, int bj) {
+  float a[T * T];
+  if (bi >= 0) {
+    const bool diag = bi == bj;
+    const float* hs = c.H() + (bi * T) * c.ld + bj * T;
+    const float* mg = c.M + (size_t)(bi * T) * c.nvp + bj * T;
+    if (c.nv == 7 * T) {     // no padding: every (i, j) of the tile is a real entry
+#pragma unroll
+      for (int x = 0; x < T; x++)
+#pragma unroll
+        for (int y = 0; y < T; y++) a[x * T + y] = hs[x * c.ld + y] + mg[x * c.nvp + y];
+    } else {
+#pragma unroll
+      for (int x = 0; x < T; x++)
+#pragma unroll
+        for (int y = 0; y < T; y++) {
+          const int i = bi * T + x, j = bj * T + y;
+          a[x * T + y] = (i < c.nv && j < c.nv) ? hs[x * c.ld + y] + mg[x * c.nvp + y] : (i == j ? 1.0f : 0.0f);
+        }
+    }
+    // diagonal tiles: only the lower half was assembled (M is symmetric, H's upper triangle is zero); mirror it
+#pragma unroll
+    for (int x = 0; x < T; x++)
+#pragma unroll
+      for (int y = x + 1; y < T; y++) if (diag) a[x * T + y] = a[y * T + x];
+  }
+  __syncwarp();
+  tile_cholesky_regs<T>(a, bi, bj, c.H(), c.ld, c.invd());
 }
 
 template <int T>
@@ -307,31 +375,29 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
   const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
-  SolveCtx c;
-  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.ld = b2s_hld(T); c.nefc = d.nefc[w]; c.nl = d.nl[w];
+  SolveCtx<T> c;
+  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.njmax = njmax;
+  c.soff = solve_soff(njmax, d.nconmax, T);
   c.M = d.qM + (size_t)w * nv * nvp;
   c.G = d.efc_g + (size_t)w * njmax * 6;
   c.bp = d.efc_bp + (size_t)w * njmax;
   c.aref = d.efc_aref + (size_t)w * njmax;
-  float* base = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, T);
-  c.H = base; base += b2s_hdim(T) * c.ld;
-  c.invd = base; base += 7 * T;
-  c.qacc = base; c.Ma = base + nvp; c.grad = base + 2 * nvp; c.search = base + 3 * nvp; c.Mv = base + 4 * nvp;
-  c.qfs = base + 5 * nvp; c.qas = base + 6 * nvp; c.qfc = base + 7 * nvp; base += 8 * nvp;
-  c.cdof = base; base += 6 * nv;
-  c.X = base; c.KW = base + 6 * max(nb, 32); c.Li = (int*)(c.KW + 32); base += solve_scratch_floats(nb);
-  c.Jaref = base; c.Jv = base + njmax; c.D = base + 2 * njmax;
+  c.sm = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, d.nconmax, T);
   float* efc_force = d.efc_force + (size_t)w * njmax;
   float* g_qacc = d.qacc + (size_t)w * nv;
   float* g_qfc = d.qfrc_constraint + (size_t)w * nv;
-  for (int i = lane; i < nvp; i += 32) {
-    c.qas[i] = i < nv ? d.qacc_smooth[(size_t)w * nv + i] : 0.f;
-    c.qfs[i] = i < nv ? d.qfrc_smooth[(size_t)w * nv + i] : 0.f;
-    c.search[i] = 0.f; c.qacc[i] = 0.f; c.qfc[i] = 0.f;
+  const bool warm = !(m.disableflags & B2S_DSBL_WARMSTART);
+#pragma unroll 1
+  for (int i = lane; i < SolveCtx<T>::NVP; i += 32) {
+    c.qas()[i] = i < nv ? d.qacc_smooth[(size_t)w * nv + i] : 0.f;
+    c.qfs()[i] = i < nv ? d.qfrc_smooth[(size_t)w * nv + i] : 0.f;
+    c.search()[i] = (i < nv && warm) ? d.qacc_warmstart[(size_t)w * nv + i] : 0.f;   // candidate start point
+    c.qacc()[i] = 0.f; c.qfc()[i] = 0.f;
   }
   if (c.nefc == 0) {
     __syncwarp();
-    for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qas[i]; g_qfc[i] = 0.f; }
+#pragma unroll 1
+    for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qas()[i]; g_qfc[i] = 0.f; }
     if (lane == 0) { d.solver_niter[w] = 0; d.solver_cost[w] = 0.f; }
     return;
   }
@@ -339,6 +405,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
   {
     const float* com = d.subtree_com + (size_t)w * nb * 3;
     const v3 cref = ld3(com + 3 * m.ref_root);
+#pragma unroll 1
     for (int i = lane; i < nv; i += 32) {
       sv6 cd = ld6(d.cdof + ((size_t)w * nv + i) * 6);
       const int rb = m.body_rootid[m.dof_bodyid[i]];
@@ -346,74 +413,110 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const Model
         const v3 lin = mk3(cd.v[3], cd.v[4], cd.v[5]) + cross(mk3(cd.v[0], cd.v[1], cd.v[2]), cref - ld3(com + 3 * rb));
         cd.v[3] = lin.x; cd.v[4] = lin.y; cd.v[5] = lin.z;
       }
-      st6(c.cdof + 6 * i, cd);
+      st6(c.cdof() + 6 * i, cd);
     }
-    for (int r = lane; r < c.nefc; r += 32) c.D[r] = d.efc_D[(size_t)w * njmax + r];
+#pragma unroll 1
+    for (int r = lane; r < c.nefc; r += 32) c.D()[r] = d.efc_D[(size_t)w * njmax + r];
   }
+  // runs of contact rows that share a body pair (fixed for the whole solve), in row order
+  {
+    int nrun = 0;
+#pragma unroll 1
+    for (int base_r = c.nl; base_r < c.nefc; base_r += 32) {
+      const int r = base_r + lane;
+      const bool start = r < c.nefc && (r == c.nl || c.bp[r] != c.bp[r - 1]);
+      const unsigned mk = __ballot_sync(FULL, start);
+      if (start) c.run()[nrun + __popc(mk & ((1u << lane) - 1u))] = r;
+      nrun += __popc(mk);
+    }
+    if (lane == 0) c.run()[nrun] = c.nefc;
+    c.nrun = nrun;
+  }
+  int bi, bj;
+  tile_owner(lane, bi, bj);
   // K / W entry owned by this lane in the run reduction: lanes 0..20 -> (ia, ib) of the symmetric 6x6, 21..26 -> W
   int ia = 0, ib = 0;
   if (lane < 21) { int e = lane; while (e > ia) { e -= ia + 1; ia++; } ib = e; }
   else if (lane < 27) { ia = lane - 21; ib = 0; }
-  // ---- warm start (mj_fwdConstraint): keep qacc_warmstart only if it beats qacc_smooth
-  const bool warm = !(m.disableflags & B2S_DSBL_WARMSTART);
-  for (int i = lane; i < nv; i += 32) c.qacc[i] = warm ? d.qacc_warmstart[(size_t)w * nv + i] : c.qas[i];
   __syncwarp();
-  mat_vec_M(c, c.qacc, c.Ma);
-  mat_vec_J(c, m, c.qacc, c.aref, c.Jaref);
-  float gauss = gauss_term(c);
-  float cost = constraint_cost(c, c.Jaref) + gauss;
-  if (warm) {
-    mat_vec_J(c, m, c.qas, c.aref, c.Jv);   // Jv as scratch
-    const float cost_smooth = constraint_cost(c, c.Jv);
-    if (cost > cost_smooth) {
-      for (int i = lane; i < nv; i += 32) c.qacc[i] = c.qas[i];
-      for (int r = lane; r < c.nefc; r += 32) c.Jaref[r] = c.Jv[r];
-      __syncwarp();
-      mat_vec_M(c, c.qacc, c.Ma);
-      __syncwarp();
-      gauss = gauss_term(c);
-      cost = cost_smooth + gauss;
+  // ---- warm start (mj_fwdConstraint): evaluate the cost at qacc_warmstart (held in c.search()) and at qacc_smooth;
+  // keep the warm start only if it is not worse.  One code path evaluates both points (pass 0: smooth, pass 1: warm).
+  float gauss = 0.f, cost = 0.f;
+#pragma unroll 1
+  for (int pass = warm ? 0 : 1; pass < 2; pass++) {
+    const float* x = (pass == 0 || !warm) ? c.qas() : c.search();
+    mat_vec_J(c, m, x, c.aref, c.Jv());
+    float cst = constraint_cost(c, c.Jv());
+    mat_vec_M(c, x, c.Mv());
+    __syncwarp();
+    float g = 0.f;
+#pragma unroll 1
+    for (int i = lane; i < nv; i += 32) g += (c.Mv()[i] - c.qfs()[i]) * (x[i] - c.qas()[i]);
+    const float gs = 0.5f * warp_sum(g);      // exactly 0 at qacc_smooth
+    // pass 0 evaluates qacc_smooth and is always adopted; pass 1 (the warm start) replaces it unless it is worse.
+    // The comparison is on the constraint cost + Gauss term of the warm start vs the constraint cost at qacc_smooth.
+    if (pass == 0 || !warm || !(cst + gs > cost)) {
+#pragma unroll 1
+      for (int i = lane; i < nv; i += 32) { c.qacc()[i] = x[i]; c.Ma()[i] = c.Mv()[i]; }
+#pragma unroll 1
+      for (int r = lane; r < c.nefc; r += 32) c.Jaref()[r] = c.Jv()[r];
+      gauss = gs; cost = cst + gs;
     }
+    __syncwarp();
   }
   const float scale = 1.0f / (m.meaninertia * (float)max(nv, 1));
   int iter = 0;
+  bool withH = true;
+#pragma unroll 1
   while (true) {
-    assemble(c, m, true, ia, ib);
+    assemble(c, m, withH, ia, ib);
+    if (!withH) break;
     float gn = 0.f;
-    for (int i = lane; i < nv; i += 32) { const float g = c.Ma[i] - c.qfs[i] - c.qfc[i]; c.grad[i] = g; gn += g * g; }
+#pragma unroll 1
+    for (int i = lane; i < nv; i += 32) { const float g = c.Ma()[i] - c.qfs()[i] - c.qfc()[i]; c.grad()[i] = g; gn += g * g; }
     gn = sqrtf(warp_sum(gn));
     if (iter > 0 && scale * gn < m.tolerance) break;
     if (iter >= m.iterations) break;
-    // blocked Cholesky of H on register tiles (c.H ends up holding L), search = -H^-1 grad
-    tile_cholesky_smem<T>(c.H, nv, c.ld, lane, c.invd);
-    float b0 = lane < nv ? c.grad[lane] : 0.f, b1 = lane + 32 < nv ? c.grad[lane + 32] : 0.f;
-    warp_chol_solve_inv(c.H, c.invd, nv, c.ld, lane, b0, b1);
-    if (lane < nv) c.search[lane] = -b0;
-    if (lane + 32 < nv) c.search[lane + 32] = -b1;
+    // blocked Cholesky of H on register tiles (c.H() ends up holding L), search = -H^-1 grad
+    factor_H<T>(c, bi, bj);
+    float b0 = lane < nv ? c.grad()[lane] : 0.f, b1 = lane + 32 < nv ? c.grad()[lane + 32] : 0.f;
+    tile_chol_solve<T>(c.H(), c.invd(), c.ld, lane, b0, b1);
+    if (lane < nv) c.search()[lane] = -b0;
+    if (lane + 32 < nv) c.search()[lane + 32] = -b1;
     __syncwarp();
     // line-search set-up: Mv, Jv, quadratic Gauss coefficients
-    mat_vec_M(c, c.search, c.Mv);
-    mat_vec_J(c, m, c.search, nullptr, c.Jv);
+    mat_vec_M(c, c.search(), c.Mv());
+    mat_vec_J(c, m, c.search(), nullptr, c.Jv());
     float g1 = 0.f, g2 = 0.f;
-    for (int i = lane; i < nv; i += 32) { g1 += c.search[i] * (c.Ma[i] - c.qfs[i]); g2 += c.search[i] * c.Mv[i]; }
+#pragma unroll 1
+    for (int i = lane; i < nv; i += 32) { g1 += c.search()[i] * (c.Ma()[i] - c.qfs()[i]); g2 += c.search()[i] * c.Mv()[i]; }
     float qg[3] = {gauss, warp_sum(g1), 0.5f * warp_sum(g2)};
-    const float alpha = m.ls_parallel ? ls_parallel(c, m, qg) : ls_iterative(c, m, qg);
+    float alpha;
+    if (m.ls_parallel) alpha = ls_parallel(c, m, qg);
+    else {
+      LsArgs la;
+      la.Jaref = c.Jaref(); la.Jv = c.Jv(); la.D = c.D(); la.search = c.search(); la.nefc = c.nefc; la.nv = nv; la.lane = lane;
+      la.maxit = m.ls_iterations; la.gtol_unit = m.tolerance * m.ls_tolerance * m.meaninertia * (float)max(nv, 1);
+      la.q0 = qg[0]; la.q1 = qg[1]; la.q2 = qg[2];
+      alpha = ls_iterative(la);
+    }
     if (alpha == 0.f) break;
-    for (int i = lane; i < nv; i += 32) { c.qacc[i] += alpha * c.search[i]; c.Ma[i] += alpha * c.Mv[i]; }
-    for (int r = lane; r < c.nefc; r += 32) c.Jaref[r] += alpha * c.Jv[r];
+#pragma unroll 1
+    for (int i = lane; i < nv; i += 32) { c.qacc()[i] += alpha * c.search()[i]; c.Ma()[i] += alpha * c.Mv()[i]; }
+#pragma unroll 1
+    for (int r = lane; r < c.nefc; r += 32) c.Jaref()[r] += alpha * c.Jv()[r];
     __syncwarp();
     const float old = cost;
     gauss = gauss_term(c);
-    cost = constraint_cost(c, c.Jaref) + gauss;
+    cost = constraint_cost(c, c.Jaref()) + gauss;
     iter++;
-    if (scale * (old - cost) < m.tolerance) {
-      assemble(c, m, false, ia, ib);
-      break;
-    }
+    if (scale * (old - cost) < m.tolerance) withH = false;     // converged: one more pass for the final forces only
   }
   __syncwarp();
-  for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qacc[i]; g_qfc[i] = c.qfc[i]; }
-  for (int r = lane; r < c.nefc; r += 32) { const float jar = c.Jaref[r]; efc_force[r] = jar < 0.f ? -c.D[r] * jar : 0.f; }
+#pragma unroll 1
+  for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qacc()[i]; g_qfc[i] = c.qfc()[i]; }
+#pragma unroll 1
+  for (int r = lane; r < c.nefc; r += 32) { const float jar = c.Jaref()[r]; efc_force[r] = jar < 0.f ? -c.D()[r] * jar : 0.f; }
   if (lane == 0) { d.solver_niter[w] = iter; d.solver_cost[w] = cost; }
 }
 
@@ -437,7 +540,7 @@ void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   b2s_count_launch();
 }
 size_t smem_solve(const ModelDev& m, const DataDev& d) {
-  return (size_t)B2S_WARPS_PER_CTA * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, tile_for(m.nv)) * sizeof(float);
+  return (size_t)B2S_WARPS_PER_CTA * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv)) * sizeof(float);
 }
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;
