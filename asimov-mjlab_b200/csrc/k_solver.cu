@@ -60,15 +60,30 @@ struct SolveCtx {
 // y[i] = sum_j M[i][j] x[j]; M symmetric in HBM/L2, read column-wise so lanes hit contiguous addresses
 template <int T>
 DEV void mat_vec_M(const SolveCtx<T>& c, const float* x, float* y) {
+  // all row loads are issued before the first use (static trip count 7T): one L2 round trip instead of nv
+  constexpr int N = 7 * T;
+  const float* col0 = c.M + min(c.lane, c.nv - 1);
+  const float* col1 = c.M + min(c.lane + 32, c.nv - 1);
+  constexpr int B = 12;          // loads in flight per batch
   float a0 = 0.f, a1 = 0.f;
-  for (int j = 0; j < c.nv; j++) {
-    const float xj = x[j];
-    const float* row = c.M + (size_t)j * c.nvp;
-    if (c.lane < c.nv) a0 += row[c.lane] * xj;
-    if (c.lane + 32 < c.nv) a1 += row[c.lane + 32] * xj;
+#pragma unroll 1
+  for (int j0 = 0; j0 < N; j0 += B) {
+    float m0[B], m1[B];
+#pragma unroll
+    for (int k = 0; k < B; k++) {
+      const int jj = min(j0 + k, c.nv - 1);
+      m0[k] = col0[(size_t)jj * c.nvp];
+      if (N > 32) m1[k] = col1[(size_t)jj * c.nvp];
+    }
+#pragma unroll
+    for (int k = 0; k < B; k++) if (j0 + k < N) {
+      const float xj = x[j0 + k];          // x is padded with zeros up to NVP >= N
+      a0 += m0[k] * xj;
+      if (N > 32) a1 += m1[k] * xj;
+    }
   }
   if (c.lane < c.nv) y[c.lane] = a0;
-  if (c.lane + 32 < c.nv) y[c.lane + 32] = a1;
+  if (N > 32 && c.lane + 32 < c.nv) y[c.lane + 32] = a1;
 }
 // out[r] = J[r] . x - sub[r], matrix-free: body spatial vectors X[b] first (one lane per body), then one lane per row
 template <int T>
