@@ -60,6 +60,7 @@ class ContactMatch:
   mode: str
   pattern: object
   entity: str | None = None
+  exclude: tuple = ()
 
 
 @dataclass
@@ -131,7 +132,8 @@ def add_contact_sensor(scene: Spec, cfg: ContactSensorCfg, entity_bodies: dict) 
   prim = cfg.primary
   if prim.entity:
     pats = (prim.pattern,) if isinstance(prim.pattern, str) else tuple(prim.pattern)
-    prim_names = filter_names_full(pats, entity_bodies[prim.entity])
+    pool = entity_bodies[prim.entity] if prim.mode != "geom" else entity_bodies[prim.entity + "#geoms"]
+    prim_names = tuple(n for n in filter_names_full(pats, pool) if n not in prim.exclude)
   else:
     prim_names = (prim.pattern,) if isinstance(prim.pattern, str) else tuple(prim.pattern)
   sec_name = None
@@ -236,6 +238,7 @@ def build_scene(entities: dict, sensors=(), plane=True, num_origin_sites=0, env_
   ent_bodies = {}
   for name, espec in entities.items():
     ent_bodies[name] = tuple(b.name for b in espec.bodies[1:])
+    ent_bodies[name + "#geoms"] = tuple(g.name for g in espec.geoms if g.name)
     scene.attach(espec, prefix=f"{name}/")
   for s in sensors:
     add_contact_sensor(scene, s, ent_bodies)
@@ -267,6 +270,66 @@ def build_g1_flat(xml_path) -> HostModel:
   velocity_sim_options(scene)
   m = scene.compile()
   m.meta = dict(task="Mjlab-Velocity-Flat-Unitree-G1", nconmax=50, njmax=300, decimation=4)
+  return m
+
+
+# ---------------------------------------------------------------------------
+# Unitree Go1 (values restated from src/mjlab/asset_zoo/robots/unitree_go1/go1_constants.py:33-153)
+# ---------------------------------------------------------------------------
+_GO1_ROTOR = 0.000111842
+_GO1_HIP_ARM = _GO1_ROTOR * 6.0 ** 2
+_GO1_KNEE_ARM = _GO1_ROTOR * 9.0 ** 2
+GO1_ACTUATORS = (
+  ActuatorCfg((".*_hip_joint", ".*_thigh_joint"), effort_limit=23.7, stiffness=_GO1_HIP_ARM * _WN ** 2,
+              damping=2.0 * _ZETA * _GO1_HIP_ARM * _WN, armature=_GO1_HIP_ARM),
+  ActuatorCfg((".*_calf_joint",), effort_limit=35.55, stiffness=_GO1_KNEE_ARM * _WN ** 2,
+              damping=2.0 * _ZETA * _GO1_KNEE_ARM * _WN, armature=_GO1_KNEE_ARM),
+)
+_GO1_FOOT = "^[FR][LR]_foot_collision$"
+GO1_FULL_COLLISION = CollisionCfg(
+  geom_names_expr=(".*_collision",), condim={_GO1_FOOT: 3, ".*_collision": 1}, priority={_GO1_FOOT: 1},
+  friction={_GO1_FOOT: (0.6,)}, solimp={_GO1_FOOT: (0.9, 0.95, 0.023)}, contype=1, conaffinity=0)
+GO1_INIT = dict(pos=(0.0, 0.0, 0.278), rot=(1.0, 0.0, 0.0, 0.0), joint_pos={
+  ".*thigh_joint": 0.9, ".*calf_joint": -1.8, ".*R_hip_joint": 0.1, ".*L_hip_joint": -0.1})
+
+
+def go1_action_scale(joint_names) -> np.ndarray:
+  out = np.zeros(len(joint_names))
+  for c in GO1_ACTUATORS:
+    for n in filter_names(c.joint_names_expr, tuple(joint_names)):
+      out[list(joint_names).index(n)] = 0.25 * c.effort_limit / c.stiffness
+  return out
+
+
+def _go1_sensors():
+  """Contact sensors of Mjlab-Velocity-*-Unitree-Go1 (tasks/velocity/config/go1/env_cfgs.py:24-47)."""
+  geom_names = tuple(f"{n}_foot_collision" for n in ("FR", "FL", "RR", "RL"))
+  feet = ContactSensorCfg(
+    name="feet_ground_contact", primary=ContactMatch("geom", geom_names, "robot"),
+    secondary=ContactMatch("body", "terrain"), fields=("found", "force"), reduce="netforce", num_slots=1)
+  nonfoot = ContactSensorCfg(
+    name="nonfoot_ground_touch", primary=ContactMatch("geom", r".*_collision\d*$", "robot", exclude=geom_names),
+    secondary=ContactMatch("body", "terrain"), fields=("found",), reduce="none", num_slots=1)
+  return feet, nonfoot
+
+
+def build_go1(xml_path, terrain="plane", terrain_seed=0) -> HostModel:
+  """Compiled model of Mjlab-Velocity-Flat-Unitree-Go1 (terrain="plane") or of the Rough task with the reference's
+  default box terrain (terrain="rough": terrains/config.py:7-27, generated by terrains.py)."""
+  robot = build_robot_entity(xml_path, GO1_FULL_COLLISION, GO1_ACTUATORS, GO1_INIT)
+  if terrain == "plane":
+    scene = build_scene({"robot": robot}, sensors=_go1_sensors())
+  else:
+    from . import terrains
+    scene = Spec()
+    terrains.add_rough_terrain(scene, seed=terrain_seed)
+    ent_bodies = {"robot": tuple(b.name for b in robot.bodies[1:]), "robot#geoms": tuple(g.name for g in robot.geoms if g.name)}
+    scene.attach(robot, prefix="robot/")
+    for sc in _go1_sensors():
+      add_contact_sensor(scene, sc, ent_bodies)
+  velocity_sim_options(scene)
+  m = scene.compile()
+  m.meta = dict(task="Mjlab-Velocity-%s-Unitree-Go1" % ("Flat" if terrain == "plane" else "Rough"), nconmax=50, njmax=300, decimation=4)
   return m
 
 

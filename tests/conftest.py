@@ -17,3 +17,9 @@ def pytest_configure(config):
 def g1():
   from asimov_mjlab_b200 import scenes
   return scenes.load_asset("g1_flat")
+
+
+@pytest.fixture(scope="session")
+def go1():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("go1_flat")

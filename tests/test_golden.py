@@ -13,11 +13,16 @@ from oracle import Oracle
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = [("g1_rollout_ls0.npz", "g1", 0, 50, 300, 40, 10), ("g1_rollout_ls1.npz", "g1", 1, 50, 300, 40, 10),
-         ("legged_rollout.npz", "legged", 0, 16, 64, 100, 25)]
+         ("legged_rollout.npz", "legged", 0, 16, 64, 100, 25), ("go1_flat_rollout_ls1.npz", "go1", 1, 50, 300, 40, 10)]
 
 
 def _model(kind, g1):
-  return g1 if kind == "g1" else fx.compile_xml(fx.LEGGED)
+  if kind == "g1":
+    return g1
+  if kind == "go1":
+    from asimov_mjlab_b200 import scenes
+    return scenes.load_asset("go1_flat")
+  return fx.compile_xml(fx.LEGGED)
 
 
 def _rollout_oracle(m, z, dtype, lsp, nconmax, njmax, nstep, every):

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import fixtures as fx
-from util import contact_pairs, g1_states
+from util import contact_pairs, g1_states, legged_states
 
 pytestmark = pytest.mark.gpu
 
@@ -114,6 +114,37 @@ def test_g1_one_step_and_short_horizon(g1, ls_parallel):
   _check_counts(D, worlds)
   assert _rel_err(D, worlds, "qpos") < 2e-4
   assert _rel_err(D, worlds, "qvel") < 2e-2
+
+
+@pytest.mark.parametrize("ls_parallel", [True, False])
+def test_go1_flat_forward_and_steps_match_oracle(go1, ls_parallel):
+  """Mjlab-Velocity-Flat-Unitree-Go1 (BASELINE.json configs[2] robot on the plane): plane-box / plane-sphere /
+  plane-capsule contacts, 4 geom-mode netforce feet sensors + 26 geom-mode `found` sensors (nsensordata 54)."""
+  import torch
+  W = 32
+  qpos, qvel, ctrl = legged_states(go1, W, seed=5, spread=0.25, vel=0.4, zlo=0.2, zhi=0.32)
+  engine, M, D, orc, worlds = _setup(go1, W, qpos, qvel, ctrl, ls_parallel)
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  _check_counts(D, worlds)
+  assert sum(int(w["ncon"][0]) for w in worlds) > 40
+  for f, tol in TOL_FORWARD.items():
+    assert _rel_err(D, worlds, f) < tol, f
+  engine.step(M, D)
+  for w in worlds:
+    orc.step(w)
+  _check_counts(D, worlds)
+  for f, tol in TOL_STEP1.items():
+    assert _rel_err(D, worlds, f) < tol, f
+  engine.step(M, D, 20)
+  torch.cuda.synchronize()
+  for w in worlds:
+    orc.step(w, 20)
+  _check_counts(D, worlds)
+  assert _rel_err(D, worlds, "qpos") < 2e-4
+  assert _rel_err(D, worlds, "qvel") < 2e-2
+  assert _rel_err(D, worlds, "sensordata") < 2e-2
 
 
 def test_g1_friction_domain_randomisation_per_world(g1):

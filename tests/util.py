@@ -24,3 +24,10 @@ def g1_states(m, nworld, seed=0, spread=0.3, vel=0.5, zlo=0.70, zhi=0.80):
 
 def contact_pairs(geom, n):
   return sorted(map(tuple, np.asarray(geom).reshape(-1, 2)[:n].tolist()))
+
+
+def legged_states(m, nworld, seed=0, spread=0.3, vel=0.5, zlo=None, zhi=None):
+  """Same for any floating-base robot with an init_state keyframe (Go1, ...)."""
+  key = m.keys["robot/init_state"]
+  z0 = key["qpos"][2]
+  return g1_states(m, nworld, seed, spread, vel, z0 - 0.03 if zlo is None else zlo, z0 + 0.07 if zhi is None else zhi)

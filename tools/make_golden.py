@@ -14,7 +14,7 @@ import numpy as np
 import fixtures as fx
 from asimov_mjlab_b200 import scenes
 from oracle import Oracle
-from util import g1_states
+from util import g1_states, legged_states
 
 OUT = os.path.join(ROOT, "tests", "golden")
 os.makedirs(OUT, exist_ok=True)
@@ -42,6 +42,10 @@ for lsp in (0, 1):
   qpos, qvel, ctrl = g1_states(g1, 4, seed=21, spread=0.1, vel=0.1, zlo=0.74, zhi=0.77)
   r = record(g1, qpos, qvel, ctrl, 40, 10, 50, 300, lsp)
   np.savez_compressed(os.path.join(OUT, f"g1_rollout_ls{lsp}.npz"), qpos0=qpos, qvel0=qvel, ctrl0=ctrl, **r)
+go1 = scenes.load_asset("go1_flat")
+qpos, qvel, ctrl = legged_states(go1, 4, seed=22, spread=0.1, vel=0.1, zlo=0.26, zhi=0.29)
+r = record(go1, qpos, qvel, ctrl, 40, 10, 50, 300, 1)
+np.savez_compressed(os.path.join(OUT, "go1_flat_rollout_ls1.npz"), qpos0=qpos, qvel0=qvel, ctrl0=ctrl, **r)
 m = fx.compile_xml(fx.LEGGED)
 rng = np.random.default_rng(3)
 qpos = np.tile(m.qpos0, (3, 1)); qpos[:, 2] = [0.3, 0.33, 0.36]
