@@ -1,0 +1,141 @@
+"""Procedural box terrain of the velocity-rough tasks, restated against this package's `Spec`.
+
+Follows the reference's generator for the sub-terrains that are ACTIVE in its default configuration
+(src/mjlab/terrains/config.py:7-27; the heightfield ones are commented out there):
+  * TerrainGenerator curriculum layout     src/mjlab/terrains/terrain_generator.py:166-196,198-213
+  * BoxFlatTerrainCfg                      src/mjlab/terrains/primitive_terrains.py:53-64, utils.py:11-33
+  * BoxPyramidStairsTerrainCfg             src/mjlab/terrains/primitive_terrains.py:66-222
+  * BoxInvertedPyramidStairsTerrainCfg     src/mjlab/terrains/primitive_terrains.py:225-373
+  * make_border                            src/mjlab/terrains/utils.py:36-107
+  * outer border                           src/mjlab/terrains/terrain_generator.py:250-275
+Colours and lights are not physics and are left out.  Geoms are named terrain_<k> in creation order
+(terrain_generator.py:110-113), all on one static body "terrain".
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+
+
+@dataclass
+class StairsCfg:
+  proportion: float
+  step_height_range: tuple = (0.0, 0.1)
+  step_width: float = 0.3
+  platform_width: float = 3.0
+  border_width: float = 1.0
+  inverted: bool = False
+
+
+@dataclass
+class FlatCfg:
+  proportion: float
+
+
+@dataclass
+class RoughTerrainCfg:
+  """ROUGH_TERRAINS_CFG (terrains/config.py:7-27) with curriculum=True (velocity_env_cfg.py:105-107)."""
+  size: tuple = (8.0, 8.0)
+  border_width: float = 20.0
+  border_height: float = 1.0
+  num_rows: int = 10
+  num_cols: int = 20
+  difficulty_range: tuple = (0.0, 1.0)
+  sub_terrains: tuple = field(default_factory=lambda: (
+    FlatCfg(0.4), StairsCfg(0.3), StairsCfg(0.3, inverted=True)))
+
+
+def _box(out, size, pos):
+  out.append((np.asarray(size, float) / 2.0, np.asarray(pos, float)))
+
+
+def _make_border(out, size, inner, height, position):
+  tx, ty = (size[0] - inner[0]) / 2.0, (size[1] - inner[1]) / 2.0
+  _box(out, (size[0], ty, height), (position[0], position[1] + inner[1] / 2.0 + ty / 2.0, position[2]))
+  _box(out, (size[0], ty, height), (position[0], position[1] - inner[1] / 2.0 - ty / 2.0, position[2]))
+  _box(out, (tx, inner[1], height), (position[0] - inner[0] / 2.0 - tx / 2.0, position[1], position[2]))
+  _box(out, (tx, inner[1], height), (position[0] + inner[0] / 2.0 + tx / 2.0, position[1], position[2]))
+
+
+def _flat(size):
+  out = []
+  _box(out, (size[0], size[1], 1.0), (size[0] / 2.0, size[1] / 2.0, -0.5))
+  return out, np.array([size[0] / 2, size[1] / 2, 0.0])
+
+
+def _stairs(c: StairsCfg, size, difficulty):
+  out = []
+  sh = c.step_height_range[0] + difficulty * (c.step_height_range[1] - c.step_height_range[0])
+  nx = (size[0] - 2 * c.border_width - c.platform_width) // (2 * c.step_width) + 1
+  ny = (size[1] - 2 * c.border_width - c.platform_width) // (2 * c.step_width) + 1
+  n = int(min(nx, ny))
+  total = (n + 1) * sh
+  if c.border_width > 0.0:
+    _make_border(out, size, (size[0] - 2 * c.border_width, size[1] - 2 * c.border_width), sh,
+                 (0.5 * size[0], 0.5 * size[1], -sh / 2))
+  cx, cy = 0.5 * size[0], 0.5 * size[1]
+  ts = (size[0] - 2 * c.border_width, size[1] - 2 * c.border_width)
+  for k in range(n):
+    bs = (ts[0] - 2 * k * c.step_width, ts[1] - 2 * k * c.step_width)
+    if c.inverted:
+      z = -total / 2 - (k + 1) * sh / 2.0
+      h = total - (k + 1) * sh
+    else:
+      z = k * sh / 2.0
+      h = (k + 2) * sh
+    off = (k + 0.5) * c.step_width
+    _box(out, (bs[0], c.step_width, h), (cx, cy + ts[1] / 2.0 - off, z))
+    _box(out, (bs[0], c.step_width, h), (cx, cy - ts[1] / 2.0 + off, z))
+    _box(out, (c.step_width, bs[1] - 2 * c.step_width, h), (cx + ts[0] / 2.0 - off, cy, z))
+    _box(out, (c.step_width, bs[1] - 2 * c.step_width, h), (cx - ts[0] / 2.0 + off, cy, z))
+  if c.inverted:
+    _box(out, (ts[0] - 2 * n * c.step_width, ts[1] - 2 * n * c.step_width, sh), (cx, cy, -total - sh / 2))
+    origin = np.array([cx, cy, -(n + 1) * sh])
+  else:
+    _box(out, (ts[0] - 2 * n * c.step_width, ts[1] - 2 * n * c.step_width, (n + 2) * sh), (cx, cy, n * sh / 2))
+    origin = np.array([cx, cy, (n + 1) * sh])
+  return out, origin
+
+
+def generate(cfg: RoughTerrainCfg, seed: int):
+  """-> (list of (half_size[3], pos[3]) boxes in creation order, terrain_origins[num_rows, num_cols, 3])."""
+  rng = np.random.default_rng(seed)
+  props = np.array([s.proportion for s in cfg.sub_terrains], float)
+  props /= props.sum()
+  sub_idx = [int(np.min(np.where(i / cfg.num_cols + 0.001 < np.cumsum(props))[0])) for i in range(cfg.num_cols)]
+  boxes, origins = [], np.zeros((cfg.num_rows, cfg.num_cols, 3))
+  for col in range(cfg.num_cols):
+    for row in range(cfg.num_rows):
+      lo, hi = cfg.difficulty_range
+      d = lo + (hi - lo) * ((row + rng.uniform()) / cfg.num_rows)
+      wp = np.array([-cfg.num_rows * cfg.size[0] * 0.5 + row * cfg.size[0], -cfg.num_cols * cfg.size[1] * 0.5 + col * cfg.size[1], 0.0])
+      sc = cfg.sub_terrains[sub_idx[col]]
+      tile, org = _flat(cfg.size) if isinstance(sc, FlatCfg) else _stairs(sc, cfg.size, d)
+      boxes += [(h, p + wp) for h, p in tile]
+      origins[row, col] = org + wp
+  bs = (cfg.num_rows * cfg.size[0] + 2 * cfg.border_width, cfg.num_cols * cfg.size[1] + 2 * cfg.border_width)
+  _make_border(boxes, bs, (cfg.num_rows * cfg.size[0], cfg.num_cols * cfg.size[1]), abs(cfg.border_height),
+               (0.0, 0.0, -cfg.border_height / 2))
+  return boxes, origins
+
+
+def add_rough_terrain(scene, seed=0, cfg: RoughTerrainCfg | None = None):
+  """Add body "terrain" with the generated boxes to `scene` (a mjcf.Spec); returns terrain_origins."""
+  cfg = cfg or RoughTerrainCfg()
+  boxes, origins = generate(cfg, seed)
+  body = scene.worldbody.add_body(name="terrain")
+  for k, (half, pos) in enumerate(boxes):
+    body.add_geom(name=f"terrain_{k}", type="box", size=[float(x) for x in half], pos=[float(x) for x in pos])
+  scene.terrain_origins = origins
+  return origins
+
+
+def env_origins_curriculum(num_envs, origins, seed=0, max_init_level=None):
+  """TerrainImporter._compute_env_origins_curriculum (terrain_importer.py:203-223) with a numpy RNG for the levels."""
+  nr, nc = origins.shape[:2]
+  mx = nr - 1 if max_init_level is None else min(max_init_level, nr - 1)
+  rng = np.random.default_rng(seed)
+  levels = rng.integers(0, mx + 1, num_envs)
+  types = np.floor(np.arange(num_envs) / (num_envs / nc)).astype(int)
+  return origins[levels, types], levels, types

@@ -454,6 +454,186 @@ static int col_sphere_box(rawcon* c, real margin, const real* p1, const real* s1
   return 1;
 }
 
+/* capsule-box: the capsule is a swept sphere, so each contact is the sphere-box contact of one point of the
+ * segment.  Point 1 is the segment point closest to the box (or, if the segment enters the box, the sampled point
+ * that is deepest inside); point 2 is a segment end whose own sphere-box contact exists and faces the same way
+ * (capsule lying along a face or an edge).  Own formulation (the reference's dependency ports MuJoCo's
+ * mjc_CapsuleBox, whose source is not available here): same contact model, possibly different tie-breaking. */
+static real seg_box_closest(const real* a, const real* dd, const real* h, int* inside_out) {
+  real ts[8]; int nt = 0;
+  ts[nt++] = 0; ts[nt++] = 1;
+  for (int i = 0; i < 3; i++) if (dd[i] != 0) for (int sgn = -1; sgn <= 1; sgn += 2) {
+    real t = (sgn*h[i] - a[i])/dd[i];
+    if (t > 0 && t < 1) ts[nt++] = t;
+  }
+  for (int i = 1; i < nt; i++) { real v = ts[i]; int j = i - 1; while (j >= 0 && ts[j] > v) { ts[j + 1] = ts[j]; j--; } ts[j + 1] = v; }
+  real best = (real)1e30, bt = 0; int inside = 0;
+  for (int k = 0; k + 1 < nt; k++) {
+    real t0 = ts[k], t1 = ts[k + 1], tm = (real)0.5*(t0 + t1), A = 0, B = 0;
+    int nout = 0;
+    for (int i = 0; i < 3; i++) {
+      real pm = a[i] + tm*dd[i];
+      real r = pm > h[i] ? h[i] : (pm < -h[i] ? -h[i] : 0);
+      if (pm > h[i] || pm < -h[i]) { A += dd[i]*dd[i]; B += dd[i]*(a[i] - r); nout++; }
+    }
+    real t = t0;
+    if (nout == 0) { inside = 1; }
+    else if (A > MINVAL) t = clipr(-B/A, t0, t1);
+    real d2 = 0;
+    for (int i = 0; i < 3; i++) { real pv = a[i] + t*dd[i]; real c = clipr(pv, -h[i], h[i]); d2 += (pv - c)*(pv - c); }
+    if (d2 < best) { best = d2; bt = t; }
+  }
+  if (inside) {   /* deepest of the sampled inside points */
+    real bd = -1;
+    for (int k = 0; k < nt + 1; k++) {
+      real t = k < nt ? ts[k] : (real)0.5;
+      real depth = (real)1e30; int in = 1;
+      for (int i = 0; i < 3; i++) { real pv = a[i] + t*dd[i]; real e = h[i] - (real)fabs((double)pv); if (e < 0) in = 0; if (e < depth) depth = e; }
+      if (in && depth > bd) { bd = depth; bt = t; }
+    }
+  }
+  *inside_out = inside;
+  return bt;
+}
+static int col_capsule_box(rawcon* c, real margin, const real* p1, const real* m1, const real* s1, const real* p2, const real* m2, const real* s2) {
+  real axis[3] = {m1[2], m1[5], m1[8]}, e0[3], e1[3], a[3], b[3], dd[3], tmp[3];
+  for (int k = 0; k < 3; k++) { e0[k] = p1[k] - axis[k]*s1[1]; e1[k] = p1[k] + axis[k]*s1[1]; }
+  for (int k = 0; k < 3; k++) tmp[k] = e0[k] - p2[k];
+  matT_vec(a, m2, tmp);
+  for (int k = 0; k < 3; k++) tmp[k] = e1[k] - p2[k];
+  matT_vec(b, m2, tmp);
+  for (int k = 0; k < 3; k++) dd[k] = b[k] - a[k];
+  int inside;
+  real tb = seg_box_closest(a, dd, s2, &inside);
+  real pt[3], rad[3] = {s1[0], 0, 0};
+  for (int k = 0; k < 3; k++) pt[k] = e0[k] + tb*(e1[k] - e0[k]);
+  int n = col_sphere_box(c, margin, pt, rad, p2, m2, s2);
+  if (n == 0) return 0;
+  for (int e = 0; e < 2 && n < 2; e++) {
+    real te = (real)e;
+    if ((real)fabs((double)(te - tb))*2*s1[1] < (real)1e-3*s1[0] + (real)1e-6) continue;   /* same point */
+    const real* pe = e == 0 ? e0 : e1;
+    if (col_sphere_box(c + n, margin, pe, rad, p2, m2, s2) && dot3(c[n].frame, c[0].frame) > (real)0.9) n++;
+  }
+  return n;
+}
+
+/* box-box: separating-axis test over the 15 candidate axes, then either a face contact (the incident face is
+ * clipped against the side planes of the reference face; every clipped vertex below the reference face within
+ * `margin` is a contact, up to 8) or one edge-edge contact.  Own formulation of the standard method (the
+ * reference's dependency ports MuJoCo's mjc_BoxBox); face axes are preferred over edge axes by a small bias. */
+static int col_box_box(rawcon* c, real margin, const real* p1, const real* m1, const real* s1, const real* p2, const real* m2, const real* s2) {
+  real R[9], AR[9], t[3], dp[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+  matT_vec(t, m1, dp);
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    real v = 0;
+    for (int k = 0; k < 3; k++) v += m1[3*k + i]*m2[3*k + j];
+    R[3*i + j] = v; AR[3*i + j] = (real)fabs((double)v) + (real)1e-6;
+  }
+  real best = (real)-1e30; int bestax = -1; real bestsign = 1;
+  /* face axes of box 1 */
+  for (int i = 0; i < 3; i++) {
+    real rb = s2[0]*AR[3*i] + s2[1]*AR[3*i + 1] + s2[2]*AR[3*i + 2];
+    real sep = (real)fabs((double)t[i]) - (s1[i] + rb);
+    if (sep > margin) return 0;
+    if (sep > best) { best = sep; bestax = i; bestsign = t[i] >= 0 ? (real)1 : (real)-1; }
+  }
+  /* face axes of box 2 */
+  for (int j = 0; j < 3; j++) {
+    real tj = t[0]*R[j] + t[1]*R[3 + j] + t[2]*R[6 + j];
+    real ra = s1[0]*AR[j] + s1[1]*AR[3 + j] + s1[2]*AR[6 + j];
+    real sep = (real)fabs((double)tj) - (ra + s2[j]);
+    if (sep > margin) return 0;
+    if (sep > best) { best = sep; bestax = 3 + j; bestsign = tj >= 0 ? (real)1 : (real)-1; }
+  }
+  /* edge-edge axes */
+  real ebest = (real)-1e30; int ei = -1, ej = -1; real esign = 1, eaxis[3] = {0, 0, 0};
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    /* L = A_i x B_j in box-1 coordinates */
+    real L[3] = {0, 0, 0};
+    L[i1] = -R[3*i2 + j]; L[i2] = R[3*i1 + j];
+    real ln = norm3(L);
+    if (ln < (real)1e-6) continue;   /* parallel edges: covered by the face axes */
+    real ra = s1[i1]*(real)fabs((double)R[3*i2 + j]) + s1[i2]*(real)fabs((double)R[3*i1 + j]);
+    real rb = s2[j1]*(real)fabs((double)R[3*i + j2]) + s2[j2]*(real)fabs((double)R[3*i + j1]);
+    real tl = t[i2]*R[3*i1 + j] - t[i1]*R[3*i2 + j];
+    real sep = ((real)fabs((double)tl) - (ra + rb))/ln;
+    if (sep > margin) return 0;
+    if (sep > ebest) { ebest = sep; ei = i; ej = j; esign = tl >= 0 ? (real)1 : (real)-1; for (int k = 0; k < 3; k++) eaxis[k] = L[k]/ln; }
+  }
+  if (ei >= 0 && ebest > best + (real)1e-3*(real)fabs((double)best) + (real)1e-5) {
+    /* edge-edge contact: closest points of the two supporting edges */
+    real nl[3] = {eaxis[0]*esign, eaxis[1]*esign, eaxis[2]*esign}, nw[3];   /* box1 -> box2, box-1 frame */
+    mat_vec(nw, m1, nl);
+    real pa[3], pb[3];
+    for (int k = 0; k < 3; k++) { pa[k] = p1[k]; pb[k] = p2[k]; }
+    for (int k = 0; k < 3; k++) if (k != ei) {
+      real sg = nl[k] > 0 ? (real)1 : (real)-1;
+      for (int q = 0; q < 3; q++) pa[q] += sg*s1[k]*m1[3*q + k];
+    }
+    for (int k = 0; k < 3; k++) if (k != ej) {
+      real nb = nl[0]*R[k] + nl[1]*R[3 + k] + nl[2]*R[6 + k];
+      real sg = nb > 0 ? (real)-1 : (real)1;
+      for (int q = 0; q < 3; q++) pb[q] += sg*s2[k]*m2[3*q + k];
+    }
+    real ua[3] = {m1[ei], m1[3 + ei], m1[6 + ei]}, ub[3] = {m2[ej], m2[3 + ej], m2[6 + ej]};
+    real w[3] = {pb[0] - pa[0], pb[1] - pa[1], pb[2] - pa[2]};
+    real uaub = dot3(ua, ub), q1 = dot3(ua, w), q2 = -dot3(ub, w), den = 1 - uaub*uaub;
+    real al = 0, be = 0;
+    if (den > (real)1e-8) { al = (q1 + uaub*q2)/den; be = (uaub*q1 + q2)/den; }
+    al = clipr(al, -s1[ei], s1[ei]); be = clipr(be, -s2[ej], s2[ej]);
+    for (int k = 0; k < 3; k++) { pa[k] += al*ua[k]; pb[k] += be*ub[k]; }
+    c->dist = ebest;
+    for (int k = 0; k < 3; k++) { c->pos[k] = (real)0.5*(pa[k] + pb[k]); c->frame[k] = nw[k]; c->frame[3 + k] = 0; }
+    return 1;
+  }
+  /* face contact */
+  const real *pr, *mr, *sr, *pi, *mi, *si; int ax; real nref[3], flip;
+  if (bestax < 3) { pr = p1; mr = m1; sr = s1; pi = p2; mi = m2; si = s2; ax = bestax; flip = 1; }
+  else { pr = p2; mr = m2; sr = s2; pi = p1; mi = m1; si = s1; ax = bestax - 3; flip = -1; }
+  /* outward normal of the reference face, pointing at the incident box */
+  real sgn = bestsign*flip;
+  for (int k = 0; k < 3; k++) nref[k] = sgn*mr[3*k + ax];
+  /* incident face: the face of the incident box most anti-parallel to nref */
+  int iax = 0; real imin = 2;
+  real isg = 1;
+  for (int k = 0; k < 3; k++) {
+    real dcol = nref[0]*mi[k] + nref[1]*mi[3 + k] + nref[2]*mi[6 + k];
+    if (-(real)fabs((double)dcol) < imin) { imin = -(real)fabs((double)dcol); iax = k; isg = dcol > 0 ? (real)-1 : (real)1; }
+  }
+  int u = (iax + 1) % 3, v = (iax + 2) % 3;
+  real poly[16][3], tmpoly[16][3]; int np = 4;
+  static const real su[4] = {1, -1, -1, 1}, sv[4] = {1, 1, -1, -1};
+  for (int q = 0; q < 4; q++) for (int k = 0; k < 3; k++)
+    poly[q][k] = pi[k] + isg*si[iax]*mi[3*k + iax] + su[q]*si[u]*mi[3*k + u] + sv[q]*si[v]*mi[3*k + v];
+  /* clip against the four side planes of the reference face */
+  int ru = (ax + 1) % 3, rv = (ax + 2) % 3;
+  for (int side = 0; side < 4 && np > 0; side++) {
+    int ka = side < 2 ? ru : rv; real sg = (side & 1) ? (real)-1 : (real)1;
+    real pn[3] = {sg*mr[ka], sg*mr[3 + ka], sg*mr[6 + ka]}, lim = sr[ka];
+    int nn = 0;
+    for (int q = 0; q < np; q++) {
+      const real* A = poly[q]; const real* B = poly[(q + 1) % np];
+      real da = (A[0] - pr[0])*pn[0] + (A[1] - pr[1])*pn[1] + (A[2] - pr[2])*pn[2] - lim;
+      real db = (B[0] - pr[0])*pn[0] + (B[1] - pr[1])*pn[1] + (B[2] - pr[2])*pn[2] - lim;
+      if (da <= 0) { for (int k = 0; k < 3; k++) tmpoly[nn][k] = A[k]; nn++; }
+      if ((da < 0 && db > 0) || (da > 0 && db < 0)) { real f = da/(da - db); for (int k = 0; k < 3; k++) tmpoly[nn][k] = A[k] + f*(B[k] - A[k]); nn++; }
+    }
+    np = nn > 16 ? 16 : nn;
+    for (int q = 0; q < np; q++) for (int k = 0; k < 3; k++) poly[q][k] = tmpoly[q][k];
+  }
+  int n = 0;
+  for (int q = 0; q < np && n < 8; q++) {
+    real dist = (poly[q][0] - pr[0])*nref[0] + (poly[q][1] - pr[1])*nref[1] + (poly[q][2] - pr[2])*nref[2] - sr[ax];
+    if (dist > margin) continue;
+    c[n].dist = dist;
+    for (int k = 0; k < 3; k++) { c[n].pos[k] = poly[q][k] - (real)0.5*dist*nref[k]; c[n].frame[k] = flip*nref[k]; c[n].frame[3 + k] = 0; }
+    n++;
+  }
+  return n;
+}
+
 /* mj_contactParam */
 static void contact_param(const b2s_model_desc* m, int g1, int g2, int* condim, real* fri5, real* solref, real* solimp, real* margin, real* gap) {
   int p1 = m->geom_priority[g1], p2 = m->geom_priority[g2];
@@ -503,18 +683,29 @@ void orc_collision(const b2s_model_desc* m, orc_data* d) {
   int ncon = 0;
   d->ncon[0] = 0;
   if (m->opt_disableflags & (B2S_DSBL_CONSTRAINT | B2S_DSBL_CONTACT)) return;
-  for (int ga = 0; ga < m->ngeom; ga++) for (int gb = ga + 1; gb < m->ngeom; gb++) {
+  /* pairs are visited in (ga, gb) order, ga < gb; two geoms on static (world-welded) bodies never collide, so for a
+   * static ga only the dynamic gb are visited (same order, far fewer iterations with thousands of terrain geoms) */
+  int ndyn = 0;
+  int* dyn = (int*)malloc(sizeof(int)*(size_t)(m->ngeom > 0 ? m->ngeom : 1));
+  for (int g = 0; g < m->ngeom; g++) if (m->body_weldid[m->geom_bodyid[g]] != 0) dyn[ndyn++] = g;
+  for (int ga = 0; ga < m->ngeom; ga++) {
+    const int ga_static = m->body_weldid[m->geom_bodyid[ga]] == 0;
+    int k0 = 0;
+    if (ga_static) { while (k0 < ndyn && dyn[k0] <= ga) k0++; }
+    const int cnt = ga_static ? ndyn - k0 : m->ngeom - ga - 1;
+    for (int kk = 0; kk < cnt; kk++) {
+    const int gb = ga_static ? dyn[k0 + kk] : ga + 1 + kk;
     if (pair_filtered(m, ga, gb)) continue;
     int g1 = ga, g2 = gb;
     if (m->geom_type[g1] > m->geom_type[g2]) { g1 = gb; g2 = ga; }
     int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
     int condim; real fri[5], solref[2], solimp[5], margin, gap;
-    contact_param(m, g1, g2, &condim, fri, solref, solimp, &margin, &gap);
     const real* p1 = d->geom_xpos + 3*g1; const real* p2 = d->geom_xpos + 3*g2;
     const real* m1 = d->geom_xmat + 9*g1; const real* m2 = d->geom_xmat + 9*g2;
     real s1[3] = {(real)m->geom_size[3*g1], (real)m->geom_size[3*g1+1], (real)m->geom_size[3*g1+2]};
     real s2[3] = {(real)m->geom_size[3*g2], (real)m->geom_size[3*g2+1], (real)m->geom_size[3*g2+2]};
-    /* bounding-sphere rejection (exact narrowphase follows, so this never changes the result) */
+    margin = (real)fmax(m->geom_margin[g1], m->geom_margin[g2]);
+    /* bounding rejection (exact narrowphase follows, so this never changes the result) */
     if (t1 == B2S_GEOM_PLANE) {
       real n[3] = {m1[2], m1[5], m1[8]}, dif[3] = {p2[0]-p1[0], p2[1]-p1[1], p2[2]-p1[2]};
       if (dot3(dif, n) > (real)m->geom_rbound[g2] + margin) continue;
@@ -522,7 +713,14 @@ void orc_collision(const b2s_model_desc* m, orc_data* d) {
       real dif[3] = {p2[0]-p1[0], p2[1]-p1[1], p2[2]-p1[2]};
       real bound = (real)m->geom_rbound[g1] + (real)m->geom_rbound[g2] + margin;
       if (dot3(dif, dif) > bound*bound) continue;
+      if (t2 == B2S_GEOM_BOX) {   /* bounding sphere of geom 1 against the oriented box 2 */
+        real loc[3], ndif[3] = {-dif[0], -dif[1], -dif[2]}, d2 = 0, rb = (real)m->geom_rbound[g1] + margin;
+        matT_vec(loc, m2, ndif);
+        for (int k = 0; k < 3; k++) { real e = (real)fabs((double)loc[k]) - s2[k]; if (e > 0) d2 += e*e; }
+        if (d2 > rb*rb) continue;
+      }
     }
+    contact_param(m, g1, g2, &condim, fri, solref, solimp, &margin, &gap);
     rawcon rc[8];
     int n = 0;
     if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_SPHERE) { real nn[3] = {m1[2], m1[5], m1[8]}; n = raw_plane_sphere(rc, margin, p1, nn, p2, s2[0]); }
@@ -532,6 +730,8 @@ void orc_collision(const b2s_model_desc* m, orc_data* d) {
     else if (t1 == B2S_GEOM_SPHERE && t2 == B2S_GEOM_CAPSULE) n = col_sphere_capsule(rc, margin, p1, s1, p2, m2, s2);
     else if (t1 == B2S_GEOM_CAPSULE && t2 == B2S_GEOM_CAPSULE) n = col_capsule_capsule(rc, margin, p1, m1, s1, p2, m2, s2);
     else if (t1 == B2S_GEOM_SPHERE && t2 == B2S_GEOM_BOX) n = col_sphere_box(rc, margin, p1, s1, p2, m2, s2);
+    else if (t1 == B2S_GEOM_CAPSULE && t2 == B2S_GEOM_BOX) n = col_capsule_box(rc, margin, p1, m1, s1, p2, m2, s2);
+    else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) n = col_box_box(rc, margin, p1, m1, s1, p2, m2, s2);
     else n = 0; /* unsupported pair types are rejected at model creation by the product */
     for (int i = 0; i < n && ncon < d->nconmax; i++) {
       int c = ncon++;
@@ -544,7 +744,9 @@ void orc_collision(const b2s_model_desc* m, orc_data* d) {
       d->con_solref[2*c] = solref[0]; d->con_solref[2*c + 1] = solref[1];
       d->con_dim[c] = condim; d->con_geom[2*c] = g1; d->con_geom[2*c + 1] = g2; d->con_efc_address[c] = -1;
     }
+    }
   }
+  free(dyn);
   d->ncon[0] = ncon;
 }
 

@@ -179,6 +179,25 @@ LEGGED = """
 """
 
 
+BOX_ON_BOX = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.002"/>
+  <worldbody>
+    <body name="terrain"><geom name="slab" type="box" size="1 1 0.25" pos="0 0 -0.25"/></body>
+    <body name="crate" pos="0.1 -0.05 0.1">
+      <freejoint name="crate_joint"/>
+      <geom name="crate_geom" type="box" size="0.15 0.1 0.1" mass="3.0"/>
+    </body>
+    <body name="rod" pos="-0.5 0.4 0.0499">
+      <freejoint name="rod_joint"/>
+      <geom name="rod_geom" type="capsule" fromto="-0.2 0 0 0.2 0 0" size="0.05" mass="1.5"/>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
+
 def compile_xml(xml, contact_sensors=()):
   spec = Spec.from_string(xml)
   for kw in contact_sensors:

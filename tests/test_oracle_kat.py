@@ -189,3 +189,53 @@ def test_solver_satisfies_kkt_for_contacts(g1):
     assert np.allclose(f, -w["efc_D"][:n] * np.minimum(jar, 0), rtol=1e-9, atol=1e-9)
     res = M @ (w["qacc"] - w["qacc_smooth"]) - J.T @ f
     assert np.abs(res).max() < 1e-5 * (1 + np.abs(J.T @ f).max())
+
+
+def test_box_and_capsule_rest_on_a_static_box():
+  """box-box face manifold (4 clipped vertices) and capsule-box (two end contacts): resting forces equal the weights,
+  contact normals point from geom1 to geom2, points lie on the slab's top face."""
+  m = fx.compile_xml(fx.BOX_ON_BOX)
+  orc = Oracle(m, "f64", ls_parallel=0)
+  w = orc.new_world()
+  orc.forward(w)
+  n = int(w["ncon"][0])
+  geoms = w["con_geom"][: 2 * n].reshape(n, 2).tolist()
+  slab, crate, rod = (m.names["geom"].index(k) for k in ("slab", "crate_geom", "rod_geom"))
+  assert geoms.count([slab, crate]) == 4 and geoms.count([rod, slab]) == 2
+  F = w["con_frame"][: 9 * n].reshape(n, 3, 3)
+  for i, (g1, g2) in enumerate(geoms):
+    assert np.allclose(F[i][0], [0, 0, 1] if g1 == slab else [0, 0, -1], atol=1e-12)
+    assert abs(w["con_pos"][3 * i + 2]) < 1e-3 and abs(w["con_dist"][i]) < 1e-3
+  # crate corners clipped to themselves (the crate lies inside the slab's face)
+  P = w["con_pos"][: 3 * n].reshape(n, 3)
+  cr = sorted(map(tuple, np.round(P[[i for i, g in enumerate(geoms) if g == [slab, crate]], :2], 9).tolist()))
+  assert np.allclose(cr, sorted([(0.1 + sx * 0.15, -0.05 + sy * 0.1) for sx in (-1, 1) for sy in (-1, 1)]), atol=1e-9)
+  orc.step(w, 3000)
+  assert np.abs(w["qvel"]).max() < 1e-6
+  n = int(w["ncon"][0]); geoms = w["con_geom"][: 2 * n].reshape(n, 2).tolist()
+  fz = {"crate": 0.0, "rod": 0.0}
+  for i, (g1, g2) in enumerate(geoms):
+    adr = int(w["con_efc_address"][i]); assert adr >= 0
+    f = w["efc_force"][adr: adr + 4].sum()          # pyramidal condim 3: normal force = sum of the 4 edge forces
+    fz["crate" if g2 == crate else "rod"] += f
+  assert fz["crate"] == pytest.approx(3.0 * 9.81, rel=1e-6) and fz["rod"] == pytest.approx(1.5 * 9.81, rel=1e-6)
+
+
+def test_box_box_edge_contact_and_separation():
+  """Two boxes crossed at 45 deg about two axes touch edge-to-edge: one contact along the common perpendicular;
+  moved apart beyond the margin they produce none."""
+  from asimov_mjlab_b200.mjcf import Spec
+  xml = """
+  <mujoco><compiler angle="radian"/><worldbody>
+    <body name="terrain"><geom name="a" type="box" size="0.5 0.1 0.1" euler="0.7853981633974483 0 0"/></body>
+    <body name="b" pos="0 0 0.27"><freejoint/><geom name="bg" type="box" size="0.1 0.5 0.1" euler="0 0.7853981633974483 0" mass="1"/></body>
+  </worldbody></mujoco>"""
+  m = Spec.from_string(xml).compile()
+  orc = Oracle(m, "f64")
+  w = orc.new_world(); orc.forward(w)
+  r = 0.1 * np.sqrt(2.0)
+  assert w["ncon"][0] == 1
+  assert w["con_dist"][0] == pytest.approx(0.27 - 2 * r, abs=1e-9)
+  assert np.allclose(w["con_frame"][:3], [0, 0, 1], atol=1e-9) and np.allclose(w["con_pos"][:3], [0, 0, 0.135], atol=1e-9)
+  w = orc.new_world(); w["qpos"][2] = 2 * r + 0.01; orc.forward(w)
+  assert w["ncon"][0] == 0
