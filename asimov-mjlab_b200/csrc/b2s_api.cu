@@ -98,8 +98,20 @@ const char* geom_name(int t) {
 bool pair_supported(int t1, int t2) {
   if (t1 == B2S_GEOM_PLANE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
   if (t1 == B2S_GEOM_SPHERE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
-  if (t1 == B2S_GEOM_CAPSULE) return t2 == B2S_GEOM_CAPSULE;
+  if (t1 == B2S_GEOM_CAPSULE) return t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
+  if (t1 == B2S_GEOM_BOX) return t2 == B2S_GEOM_BOX;
   return false;
+}
+// host-side pose algebra for the static-geom grid (double precision)
+void hq_mul(double* r, const double* a, const double* b) {
+  r[0] = a[0]*b[0] - a[1]*b[1] - a[2]*b[2] - a[3]*b[3]; r[1] = a[0]*b[1] + a[1]*b[0] + a[2]*b[3] - a[3]*b[2];
+  r[2] = a[0]*b[2] - a[1]*b[3] + a[2]*b[0] + a[3]*b[1]; r[3] = a[0]*b[3] + a[1]*b[2] - a[2]*b[1] + a[3]*b[0];
+}
+void hq_mat(double* m, const double* q) {
+  const double w = q[0], x = q[1], y = q[2], z = q[3];
+  m[0] = w*w + x*x - y*y - z*z; m[1] = 2*(x*y - w*z); m[2] = 2*(x*z + w*y);
+  m[3] = 2*(x*y + w*z); m[4] = w*w - x*x + y*y - z*z; m[5] = 2*(y*z - w*x);
+  m[6] = 2*(x*z - w*y); m[7] = 2*(y*z + w*x); m[8] = w*w - x*x - y*y + z*z;
 }
 void add_field(std::vector<FieldRec>& v, std::map<std::string, int>& idx, const char* name, int dtype, void* ptr, WField<float>* wf,
                const std::vector<long long>& shape) {
@@ -150,9 +162,90 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       default: return fail("unsupported sensor type " + std::to_string(s->sensor_type[k]));
     }
   }
+  // ---------------------------------------------------------------- static-geom grid (terrain)
+  // Non-plane geoms on world-welded bodies go into a uniform xy grid when there are many of them; their pairs with
+  // dynamic geoms are then found per step through the grid instead of the static pair table.
+  std::vector<char> in_grid((size_t)s->ngeom, 0);
+  std::vector<int> grid_geoms, dyn_geoms;
+  for (int g = 0; g < s->ngeom; g++) {
+    const bool collides = (s->geom_contype[g] | s->geom_conaffinity[g]) != 0;
+    const bool stat = s->body_weldid[s->geom_bodyid[g]] == 0;
+    if (collides && stat && s->geom_type[g] != B2S_GEOM_PLANE) grid_geoms.push_back(g);
+    if (collides && !stat) dyn_geoms.push_back(g);
+  }
+  const bool use_grid = (int)grid_geoms.size() > B2S_GRID_MIN_GEOMS;
+  std::vector<float> grid_aabb;
+  std::vector<int> grid_adr, grid_list;
+  int grid_nx = 0, grid_ny = 0; double grid_x0 = 0, grid_y0 = 0, grid_cell = 1.0, grid_margin = 0;
+  if (use_grid) {
+    if (s->ngeom > 65535) return fail("more than 65535 geoms are not supported with a static-geom grid");
+    grid_aabb.assign((size_t)6 * s->ngeom, 0.f);
+    double lo[2] = {1e300, 1e300}, hi[2] = {-1e300, -1e300};
+    std::vector<int> types_seen;
+    for (int g : grid_geoms) {
+      in_grid[g] = 1;
+      for (int e = 0; e < s->nexclude; e++)
+        if (s->exclude_body1[e] == s->geom_bodyid[g] || s->exclude_body2[e] == s->geom_bodyid[g])
+          return fail("contact excludes that involve a static terrain body are not supported");
+      // world pose of the static geom: compose the (joint-less) body chain
+      double q[4] = {1, 0, 0, 0}, p[3] = {0, 0, 0};
+      std::vector<int> chainb;
+      for (int b = s->geom_bodyid[g]; b > 0; b = s->body_parentid[b]) chainb.push_back(b);
+      for (int k = (int)chainb.size() - 1; k >= 0; k--) {
+        const int b = chainb[k];
+        double R[9], q2[4];
+        hq_mat(R, q);
+        for (int a = 0; a < 3; a++) p[a] += R[3*a]*s->body_pos[3*b] + R[3*a+1]*s->body_pos[3*b+1] + R[3*a+2]*s->body_pos[3*b+2];
+        hq_mul(q2, q, s->body_quat + 4*b);
+        for (int a = 0; a < 4; a++) q[a] = q2[a];
+      }
+      double R[9], qg[4], Rg[9], c[3];
+      hq_mat(R, q);
+      for (int a = 0; a < 3; a++) c[a] = p[a] + R[3*a]*s->geom_pos[3*g] + R[3*a+1]*s->geom_pos[3*g+1] + R[3*a+2]*s->geom_pos[3*g+2];
+      hq_mul(qg, q, s->geom_quat + 4*g);
+      hq_mat(Rg, qg);
+      const double* sz = s->geom_size + 3*g;
+      double h[3];
+      for (int a = 0; a < 3; a++) {
+        if (s->geom_type[g] == B2S_GEOM_BOX) h[a] = std::fabs(Rg[3*a])*sz[0] + std::fabs(Rg[3*a+1])*sz[1] + std::fabs(Rg[3*a+2])*sz[2];
+        else if (s->geom_type[g] == B2S_GEOM_SPHERE) h[a] = sz[0];
+        else if (s->geom_type[g] == B2S_GEOM_CAPSULE) h[a] = std::fabs(Rg[3*a+2])*sz[1] + sz[0];
+        else h[a] = s->geom_rbound[g];
+        h[a] += s->geom_margin[g];
+      }
+      grid_margin = s->geom_margin[g] > grid_margin ? s->geom_margin[g] : grid_margin;
+      for (int a = 0; a < 3; a++) { grid_aabb[(size_t)6*g + a] = (float)(c[a] - h[a]); grid_aabb[(size_t)6*g + 3 + a] = (float)(c[a] + h[a]); }
+      for (int a = 0; a < 2; a++) { lo[a] = std::fmin(lo[a], c[a] - h[a]); hi[a] = std::fmax(hi[a], c[a] + h[a]); }
+      // every dynamic collision geom type must have a narrowphase against this static geom type
+      for (int dg : dyn_geoms) {
+        if (!((s->geom_contype[g] & s->geom_conaffinity[dg]) || (s->geom_contype[dg] & s->geom_conaffinity[g]))) continue;
+        int t1 = s->geom_type[g], t2 = s->geom_type[dg];
+        if (t1 > t2) { int tt = t1; t1 = t2; t2 = tt; }
+        if (!pair_supported(t1, t2)) return fail(std::string("unsupported collision pair ") + geom_name(t1) + "-" + geom_name(t2) + " (terrain geom " + std::to_string(g) + ")");
+      }
+    }
+    while ((hi[0] - lo[0]) / grid_cell * ((hi[1] - lo[1]) / grid_cell) > 1.0e6) grid_cell *= 2.0;
+    grid_x0 = lo[0]; grid_y0 = lo[1];
+    grid_nx = (int)std::floor((hi[0] - lo[0]) / grid_cell) + 1; grid_ny = (int)std::floor((hi[1] - lo[1]) / grid_cell) + 1;
+    std::vector<int> count((size_t)grid_nx * grid_ny + 1, 0);
+    auto cells = [&](int g, int& x0, int& x1, int& y0, int& y1) {
+      // computed in float exactly as the kernel does, so both sides agree on a geom's first cell
+      const float inv = (float)(1.0 / grid_cell), fx0 = (float)grid_x0, fy0 = (float)grid_y0;
+      x0 = (int)std::floor((grid_aabb[(size_t)6*g] - fx0) * inv); x1 = (int)std::floor((grid_aabb[(size_t)6*g + 3] - fx0) * inv);
+      y0 = (int)std::floor((grid_aabb[(size_t)6*g + 1] - fy0) * inv); y1 = (int)std::floor((grid_aabb[(size_t)6*g + 4] - fy0) * inv);
+      x0 = x0 < 0 ? 0 : x0; y0 = y0 < 0 ? 0 : y0; x1 = x1 > grid_nx - 1 ? grid_nx - 1 : x1; y1 = y1 > grid_ny - 1 ? grid_ny - 1 : y1;
+    };
+    for (int g : grid_geoms) { int x0, x1, y0, y1; cells(g, x0, x1, y0, y1); for (int x = x0; x <= x1; x++) for (int y = y0; y <= y1; y++) count[(size_t)x * grid_ny + y + 1]++; }
+    for (size_t k = 1; k < count.size(); k++) count[k] += count[k - 1];
+    grid_adr = count;
+    grid_list.assign((size_t)grid_adr.back(), 0);
+    std::vector<int> fill(grid_adr.begin(), grid_adr.end() - 1);
+    for (int g : grid_geoms) { int x0, x1, y0, y1; cells(g, x0, x1, y0, y1); for (int x = x0; x <= x1; x++) for (int y = y0; y <= y1; y++) grid_list[(size_t)fill[(size_t)x * grid_ny + y]++] = g; }
+  }
   // ---------------------------------------------------------------- static collision pair table
   std::vector<int> pairs;
   for (int ga = 0; ga < s->ngeom; ga++) for (int gb = ga + 1; gb < s->ngeom; gb++) {
+    if (in_grid[ga] || in_grid[gb]) continue;      // found through the grid at run time
     const int b1 = s->geom_bodyid[ga], b2 = s->geom_bodyid[gb];
     if (!((s->geom_contype[ga] & s->geom_conaffinity[gb]) || (s->geom_contype[gb] & s->geom_conaffinity[ga]))) continue;
     const int w1 = s->body_weldid[b1], w2 = s->body_weldid[b2];
@@ -231,6 +324,12 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.geom_solref = up.f(s->geom_solref, 2 * s->ngeom); d.geom_solimp = up.f(s->geom_solimp, 5 * s->ngeom);
   d.geom_margin = up.f(s->geom_margin, s->ngeom); d.geom_gap = up.f(s->geom_gap, s->ngeom); d.geom_rbound = up.f(s->geom_rbound, s->ngeom);
   d.pair_geom = up.raw(pairs);
+  d.geom_contype = up.i(s->geom_contype, s->ngeom); d.geom_conaffinity = up.i(s->geom_conaffinity, s->ngeom);
+  d.ngrid = use_grid ? (int)grid_geoms.size() : 0;
+  d.ndyngeom = (int)dyn_geoms.size(); d.dyn_geom = up.raw(dyn_geoms);
+  d.grid_nx = grid_nx; d.grid_ny = grid_ny; d.grid_x0 = (float)grid_x0; d.grid_y0 = (float)grid_y0;
+  d.grid_inv = (float)(1.0 / grid_cell); d.grid_margin = (float)grid_margin;
+  d.grid_adr = up.raw(grid_adr); d.grid_geom = up.raw(grid_list); d.grid_aabb = up.raw(grid_aabb);
   d.site_bodyid = up.i(s->site_bodyid, s->nsite);
   d.actuator_trnid = up.i(s->actuator_trnid, s->nu); d.actuator_gaintype = up.i(s->actuator_gaintype, s->nu);
   d.actuator_biastype = up.i(s->actuator_biastype, s->nu); d.actuator_ctrllimited = up.i(s->actuator_ctrllimited, s->nu);

@@ -10,6 +10,7 @@
 
 #define B2S_WARPS_PER_CTA 4
 #define B2S_MAX_NV 56          // register-tiled Hessian: 7 x 7 tiles of up to 8 x 8
+#define B2S_GRID_MIN_GEOMS 64   // static non-plane geoms beyond this count are indexed by a uniform grid
 #define B2S_MINVAL 1e-15f
 #define B2S_MINMU 1e-5f
 
@@ -51,6 +52,12 @@ struct ModelDev {
   const int *geom_type, *geom_bodyid, *geom_condim, *geom_priority;
   const float *geom_size, *geom_solmix, *geom_solref, *geom_solimp, *geom_margin, *geom_gap, *geom_rbound;
   WField<float> geom_pos, geom_quat, geom_friction, geom_rgba;
+  const int *geom_contype, *geom_conaffinity;
+  // uniform xy grid over the static (world-welded) non-plane geoms, used when there are many of them (terrain)
+  int ngrid, ndyngeom, grid_nx, grid_ny;
+  float grid_x0, grid_y0, grid_inv, grid_margin;
+  const int *grid_adr, *grid_geom, *dyn_geom;   // CSR cell -> static geom ids; dynamic geoms that can collide
+  const float* grid_aabb;                       // [ngeom][6] world AABB (min xyz, max xyz) of grid geoms
   const int *pair_geom;             // [npair][2] after type ordering (type1 <= type2), sorted by (min id, max id)
   // ---- sites
   const int *site_bodyid;

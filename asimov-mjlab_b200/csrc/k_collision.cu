@@ -116,20 +116,193 @@ DEV int sphere_box(RawCon* c, float margin, v3 p1, v3 s1, v3 p2, const m33& m2, 
   return 1;
 }
 
+// capsule-box: each contact is the sphere-box contact of one point of the capsule segment -- the point closest to
+// the box (or the deepest sampled point if the segment enters it), then a segment end whose own contact faces the
+// same way (oracle: col_capsule_box).
+DEV float seg_box_closest(v3 a, v3 dd, v3 h, bool* inside_out) {
+  const float av[3] = {a.x, a.y, a.z}, dv[3] = {dd.x, dd.y, dd.z}, hv[3] = {h.x, h.y, h.z};
+  float ts[8]; int nt = 0;
+  ts[nt++] = 0.f; ts[nt++] = 1.f;
+  for (int i = 0; i < 3; i++) if (dv[i] != 0.f) for (int sgn = -1; sgn <= 1; sgn += 2) {
+    const float t = ((float)sgn * hv[i] - av[i]) / dv[i];
+    if (t > 0.f && t < 1.f) ts[nt++] = t;
+  }
+  for (int i = 1; i < nt; i++) { const float v = ts[i]; int j = i - 1; while (j >= 0 && ts[j] > v) { ts[j + 1] = ts[j]; j--; } ts[j + 1] = v; }
+  float best = 1e30f, bt = 0.f, tin = 0.f; bool inside = false;
+  for (int k = 0; k + 1 < nt; k++) {
+    const float t0 = ts[k], t1 = ts[k + 1], tm = 0.5f * (t0 + t1);
+    float A = 0.f, B = 0.f; int nout = 0;
+    for (int i = 0; i < 3; i++) {
+      const float pm = av[i] + tm * dv[i];
+      const float r = pm > hv[i] ? hv[i] : (pm < -hv[i] ? -hv[i] : 0.f);
+      if (pm > hv[i] || pm < -hv[i]) { A += dv[i] * dv[i]; B += dv[i] * (av[i] - r); nout++; }
+    }
+    float t = t0;
+    if (nout == 0) { inside = true; tin = tm; }   // the inside part of the segment is ONE interval: take its middle
+    else if (A > B2S_MINVAL) t = clampf(-B / A, t0, t1);
+    float d2 = 0.f;
+    for (int i = 0; i < 3; i++) { const float pv = av[i] + t * dv[i]; const float c = clampf(pv, -hv[i], hv[i]); d2 += (pv - c) * (pv - c); }
+    if (d2 < best) { best = d2; bt = t; }
+  }
+  *inside_out = inside;
+  if (inside) return tin;
+  return bt;
+}
+DEV int capsule_box(RawCon* c, float margin, v3 p1, const m33& m1, v3 s1, v3 p2, const m33& m2, v3 s2) {
+  const v3 axis = col(m1, 2), e0 = p1 - axis * s1.y, e1 = p1 + axis * s1.y;
+  const v3 a = mulTv(m2, e0 - p2), b = mulTv(m2, e1 - p2);
+  bool inside;
+  const float tb = seg_box_closest(a, b - a, s2, &inside);
+  const v3 rad = mk3(s1.x, 0.f, 0.f);
+  const v3 pt = e0 + (e1 - e0) * tb;
+  int n;
+  if (!inside) n = sphere_box(c, margin, pt, rad, p2, m2, s2);
+  else {
+    // segment through the box: contact at the middle of the inside part, pushed out along the box axis of least
+    // depth towards the side the capsule CENTRE is on (robust for thin boxes)
+    const v3 ps = a + (b - a) * tb, ctr = a + (b - a) * 0.5f;
+    const float psv[3] = {ps.x, ps.y, ps.z}, cv[3] = {ctr.x, ctr.y, ctr.z}, hv[3] = {s2.x, s2.y, s2.z};
+    int kb = 0; float bestd = hv[0] - fabsf(psv[0]);
+    for (int k = 1; k < 3; k++) { const float e = hv[k] - fabsf(psv[k]); if (e < bestd) { bestd = e; kb = k; } }
+    const float sg = cv[kb] >= 0.f ? 1.f : -1.f;
+    const v3 nl = mk3(kb == 0 ? -sg : 0.f, kb == 1 ? -sg : 0.f, kb == 2 ? -sg : 0.f);
+    const float depth = hv[kb] - sg * psv[kb];
+    c->n = mulv(m2, nl); c->dist = -depth - s1.x; c->pos = pt + c->n * (s1.x + c->dist * 0.5f); c->t = mk3(0.f, 0.f, 0.f);
+    n = 1;
+  }
+  if (n == 0) return 0;
+  for (int e = 0; e < 2 && n < 2; e++) {
+    const float te = (float)e;
+    if (fabsf(te - tb) * 2.f * s1.y < 1e-3f * s1.x + 1e-6f) continue;
+    if (sphere_box(c + n, margin, e == 0 ? e0 : e1, rad, p2, m2, s2) && dot(c[n].n, c[0].n) > 0.9f) n++;
+  }
+  return n;
+}
+// box-box: separating-axis test (15 axes), then a face manifold (incident face clipped against the reference face's
+// side planes, up to 8 points) or one edge-edge contact (oracle: col_box_box).
+DEV int box_box(RawCon* c, float margin, v3 p1, const m33& M1, v3 S1, v3 p2, const m33& M2, v3 S2) {
+  const float* m1 = M1.m; const float* m2 = M2.m;
+  const float s1[3] = {S1.x, S1.y, S1.z}, s2[3] = {S2.x, S2.y, S2.z};
+  const v3 tv = mulTv(M1, p2 - p1);
+  const float t[3] = {tv.x, tv.y, tv.z};
+  float R[9], AR[9];
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    float v = 0.f;
+    for (int k = 0; k < 3; k++) v += m1[3 * k + i] * m2[3 * k + j];
+    R[3 * i + j] = v; AR[3 * i + j] = fabsf(v) + 1e-6f;
+  }
+  float best = -1e30f; int bestax = -1; float bestsign = 1.f;
+  for (int i = 0; i < 3; i++) {
+    const float rb = s2[0] * AR[3 * i] + s2[1] * AR[3 * i + 1] + s2[2] * AR[3 * i + 2];
+    const float sep = fabsf(t[i]) - (s1[i] + rb);
+    if (sep > margin) return 0;
+    if (sep > best) { best = sep; bestax = i; bestsign = t[i] >= 0.f ? 1.f : -1.f; }
+  }
+  for (int j = 0; j < 3; j++) {
+    const float tj = t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j];
+    const float ra = s1[0] * AR[j] + s1[1] * AR[3 + j] + s1[2] * AR[6 + j];
+    const float sep = fabsf(tj) - (ra + s2[j]);
+    if (sep > margin) return 0;
+    if (sep > best) { best = sep; bestax = 3 + j; bestsign = tj >= 0.f ? 1.f : -1.f; }
+  }
+  float ebest = -1e30f; int ei = -1, ej = -1; float esign = 1.f, eaxis[3] = {0.f, 0.f, 0.f};
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    float L[3] = {0.f, 0.f, 0.f};
+    L[i1] = -R[3 * i2 + j]; L[i2] = R[3 * i1 + j];
+    const float ln = sqrtf(L[0] * L[0] + L[1] * L[1] + L[2] * L[2]);
+    if (ln < 1e-6f) continue;
+    const float ra = s1[i1] * fabsf(R[3 * i2 + j]) + s1[i2] * fabsf(R[3 * i1 + j]);
+    const float rb = s2[j1] * fabsf(R[3 * i + j2]) + s2[j2] * fabsf(R[3 * i + j1]);
+    const float tl = t[i2] * R[3 * i1 + j] - t[i1] * R[3 * i2 + j];
+    const float sep = (fabsf(tl) - (ra + rb)) / ln;
+    if (sep > margin) return 0;
+    if (sep > ebest) { ebest = sep; ei = i; ej = j; esign = tl >= 0.f ? 1.f : -1.f; for (int k = 0; k < 3; k++) eaxis[k] = L[k] / ln; }
+  }
+  if (ei >= 0 && ebest > best + 1e-3f * fabsf(best) + 1e-5f) {
+    const float nl[3] = {eaxis[0] * esign, eaxis[1] * esign, eaxis[2] * esign};
+    const v3 nw = mulv(M1, mk3(nl[0], nl[1], nl[2]));
+    float pa[3] = {p1.x, p1.y, p1.z}, pb[3] = {p2.x, p2.y, p2.z};
+    for (int k = 0; k < 3; k++) if (k != ei) {
+      const float sg = nl[k] > 0.f ? 1.f : -1.f;
+      for (int q = 0; q < 3; q++) pa[q] += sg * s1[k] * m1[3 * q + k];
+    }
+    for (int k = 0; k < 3; k++) if (k != ej) {
+      const float nb = nl[0] * R[k] + nl[1] * R[3 + k] + nl[2] * R[6 + k];
+      const float sg = nb > 0.f ? -1.f : 1.f;
+      for (int q = 0; q < 3; q++) pb[q] += sg * s2[k] * m2[3 * q + k];
+    }
+    const v3 ua = col(M1, ei), ub = col(M2, ej);
+    const v3 w = mk3(pb[0] - pa[0], pb[1] - pa[1], pb[2] - pa[2]);
+    const float uaub = dot(ua, ub), q1 = dot(ua, w), q2 = -dot(ub, w), den = 1.f - uaub * uaub;
+    float al = 0.f, be = 0.f;
+    if (den > 1e-8f) { al = (q1 + uaub * q2) / den; be = (uaub * q1 + q2) / den; }
+    al = clampf(al, -s1[ei], s1[ei]); be = clampf(be, -s2[ej], s2[ej]);
+    const v3 A = mk3(pa[0], pa[1], pa[2]) + ua * al, B = mk3(pb[0], pb[1], pb[2]) + ub * be;
+    c->dist = ebest; c->pos = (A + B) * 0.5f; c->n = nw; c->t = mk3(0.f, 0.f, 0.f);
+    return 1;
+  }
+  const bool ref1 = bestax < 3;
+  const v3 pr = ref1 ? p1 : p2, pi = ref1 ? p2 : p1;
+  const float* mr = ref1 ? m1 : m2; const float* mi = ref1 ? m2 : m1;
+  const float* sr = ref1 ? s1 : s2; const float* si = ref1 ? s2 : s1;
+  const int ax = ref1 ? bestax : bestax - 3;
+  const float flip = ref1 ? 1.f : -1.f, sgn = bestsign * flip;
+  const v3 nref = mk3(sgn * mr[ax], sgn * mr[3 + ax], sgn * mr[6 + ax]);
+  int iax = 0; float imin = 2.f, isg = 1.f;
+  for (int k = 0; k < 3; k++) {
+    const float dcol = nref.x * mi[k] + nref.y * mi[3 + k] + nref.z * mi[6 + k];
+    if (-fabsf(dcol) < imin) { imin = -fabsf(dcol); iax = k; isg = dcol > 0.f ? -1.f : 1.f; }
+  }
+  const int u = (iax + 1) % 3, v = (iax + 2) % 3;
+  v3 poly[16], tmp[16]; int np = 4;
+  const float su[4] = {1.f, -1.f, -1.f, 1.f}, sv[4] = {1.f, 1.f, -1.f, -1.f};
+  for (int q = 0; q < 4; q++)
+    poly[q] = pi + mk3(mi[iax], mi[3 + iax], mi[6 + iax]) * (isg * si[iax]) + mk3(mi[u], mi[3 + u], mi[6 + u]) * (su[q] * si[u]) +
+              mk3(mi[v], mi[3 + v], mi[6 + v]) * (sv[q] * si[v]);
+  const int ru = (ax + 1) % 3, rv = (ax + 2) % 3;
+  for (int side = 0; side < 4 && np > 0; side++) {
+    const int ka = side < 2 ? ru : rv; const float sg = (side & 1) ? -1.f : 1.f;
+    const v3 pn = mk3(sg * mr[ka], sg * mr[3 + ka], sg * mr[6 + ka]); const float lim = sr[ka];
+    int nn = 0;
+    for (int q = 0; q < np; q++) {
+      const v3 A = poly[q], B = poly[(q + 1) % np];
+      const float da = dot(A - pr, pn) - lim, db = dot(B - pr, pn) - lim;
+      if (da <= 0.f) tmp[nn++] = A;
+      if ((da < 0.f && db > 0.f) || (da > 0.f && db < 0.f)) { const float f = da / (da - db); tmp[nn++] = A + (B - A) * f; }
+    }
+    np = nn > 16 ? 16 : nn;
+    for (int q = 0; q < np; q++) poly[q] = tmp[q];
+  }
+  int n = 0;
+  for (int q = 0; q < np && n < 8; q++) {
+    const float dist = dot(poly[q] - pr, nref) - sr[ax];
+    if (dist > margin) continue;
+    c[n].dist = dist; c[n].pos = poly[q] - nref * (0.5f * dist); c[n].n = nref * flip; c[n].t = mk3(0.f, 0.f, 0.f);
+    n++;
+  }
+  return n;
+}
+
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
-  int* s_list = (int*)b2s_smem + warp * B2S_MAX_SURVIVORS;
+  // survivors are held as pair keys (min geom id << 16 | max geom id); ascending key order == the order in which
+  // the reference enumerates geom pairs, so contacts come out in a fixed order without atomics in the data path
+  unsigned* s_list = (unsigned*)b2s_smem + warp * (2 * B2S_MAX_SURVIVORS + 1);
+  unsigned* s_sort = s_list + B2S_MAX_SURVIVORS;
+  int* s_cnt = (int*)(s_sort + B2S_MAX_SURVIVORS);
   if (m.disableflags & (B2S_DSBL_CONSTRAINT | B2S_DSBL_CONTACT)) { if (lane == 0) d.ncon[w] = 0; return; }
   const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
   const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
   const float* gfri = m.geom_friction.at(w);
-  // A) broadphase over the static pair table
+  // A1) static pair table (dynamic-dynamic and plane-dynamic pairs, already in key order): bounding spheres
   int nsurv = 0;
   for (int base = 0; base < m.npair; base += 32) {
     const int p = base + lane;
     bool pass = false;
+    unsigned key = 0;
     if (p < m.npair) {
       const int g1 = m.pair_geom[2 * p], g2 = m.pair_geom[2 * p + 1];
       const float margin = fmaxf(m.geom_margin[g1], m.geom_margin[g2]);
@@ -140,25 +313,74 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       } else {
         const float bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
         pass = dot(dif, dif) <= bound * bound;
+        if (pass && m.geom_type[g2] == B2S_GEOM_BOX) {   // bounding sphere of geom 1 against the oriented box 2
+          const v3 loc = mulTv(ldm(gm + 9 * g2), dif * -1.f), h = ld3(m.geom_size + 3 * g2);
+          const float ex = fmaxf(fabsf(loc.x) - h.x, 0.f), ey = fmaxf(fabsf(loc.y) - h.y, 0.f), ez = fmaxf(fabsf(loc.z) - h.z, 0.f);
+          const float rb = m.geom_rbound[g1] + margin;
+          pass = ex * ex + ey * ey + ez * ez <= rb * rb;
+        }
       }
+      key = ((unsigned)min(g1, g2) << 16) | (unsigned)max(g1, g2);
     }
     const unsigned mask = __ballot_sync(FULL, pass);
-    if (pass) { const int pos = nsurv + __popc(mask & ((1u << lane) - 1u)); if (pos < B2S_MAX_SURVIVORS) s_list[pos] = p; }
+    if (pass) { const int pos = nsurv + __popc(mask & ((1u << lane) - 1u)); if (pos < B2S_MAX_SURVIVORS) s_list[pos] = key; }
     nsurv += __popc(mask);
   }
   nsurv = min(nsurv, B2S_MAX_SURVIVORS);
+  // A2) static terrain geoms through the uniform xy grid built at put_model: one lane per dynamic geom walks the
+  // cells under its bounding sphere; a static geom that spans several cells is taken in its first common cell only
+  if (m.ngrid > 0) {
+    if (lane == 0) *s_cnt = nsurv;
+    __syncwarp();
+    for (int k = lane; k < m.ndyngeom; k += 32) {
+      const int g = m.dyn_geom[k];
+      const v3 c = ld3(gx + 3 * g);
+      const float r = m.geom_rbound[g] + fmaxf(m.geom_margin[g], m.grid_margin);
+      const int ix0 = max((int)floorf((c.x - r - m.grid_x0) * m.grid_inv), 0), ix1 = min((int)floorf((c.x + r - m.grid_x0) * m.grid_inv), m.grid_nx - 1);
+      const int iy0 = max((int)floorf((c.y - r - m.grid_y0) * m.grid_inv), 0), iy1 = min((int)floorf((c.y + r - m.grid_y0) * m.grid_inv), m.grid_ny - 1);
+      for (int ix = ix0; ix <= ix1; ix++) for (int iy = iy0; iy <= iy1; iy++) {
+        const int cell = ix * m.grid_ny + iy;
+        for (int e = m.grid_adr[cell]; e < m.grid_adr[cell + 1]; e++) {
+          const int sg = m.grid_geom[e];
+          const float* bb = m.grid_aabb + 6 * sg;
+          const int sx0 = max((int)floorf((bb[0] - m.grid_x0) * m.grid_inv), 0), sy0 = max((int)floorf((bb[1] - m.grid_y0) * m.grid_inv), 0);
+          if (ix != max(ix0, sx0) || iy != max(iy0, sy0)) continue;           // not the first common cell
+          if (!((m.geom_contype[sg] & m.geom_conaffinity[g]) || (m.geom_contype[g] & m.geom_conaffinity[sg]))) continue;
+          const float ex = fmaxf(fmaxf(bb[0] - c.x, c.x - bb[3]), 0.f), ey = fmaxf(fmaxf(bb[1] - c.y, c.y - bb[4]), 0.f), ez = fmaxf(fmaxf(bb[2] - c.z, c.z - bb[5]), 0.f);
+          if (ex * ex + ey * ey + ez * ez > r * r) continue;
+          const int pos = atomicAdd(s_cnt, 1);
+          if (pos < B2S_MAX_SURVIVORS) s_list[pos] = ((unsigned)min(sg, g) << 16) | (unsigned)max(sg, g);
+        }
+      }
+    }
+    __syncwarp();
+    const int ntot = min(*s_cnt, B2S_MAX_SURVIVORS);
+    if (ntot > nsurv) {
+      // rank sort (keys are unique): deterministic order whatever order the lanes appended in
+      for (int i = lane; i < ntot; i += 32) {
+        const unsigned ki = s_list[i];
+        int rank = 0;
+        for (int j = 0; j < ntot; j++) rank += s_list[j] < ki;
+        s_sort[rank] = ki;
+      }
+      __syncwarp();
+      for (int i = lane; i < ntot; i += 32) s_list[i] = s_sort[i];
+    }
+    nsurv = ntot;
+  }
   __syncwarp();
   // B) narrowphase, 32 survivors per pass, ordered append
   int ncon = 0;
   const int cmax = d.nconmax;
   for (int base = 0; base < nsurv; base += 32) {
     const int i = base + lane;
-    RawCon rc[4];
+    RawCon rc[8];
     int n = 0, g1 = 0, g2 = 0;
     float margin = 0.f;
     if (i < nsurv) {
-      const int p = s_list[i];
-      g1 = m.pair_geom[2 * p]; g2 = m.pair_geom[2 * p + 1];
+      const unsigned key = s_list[i];
+      g1 = (int)(key >> 16); g2 = (int)(key & 0xffffu);
+      if (m.geom_type[g1] > m.geom_type[g2]) { const int tswap = g1; g1 = g2; g2 = tswap; }
       margin = fmaxf(m.geom_margin[g1], m.geom_margin[g2]);
       const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
       v3 p1 = ld3(gx + 3 * g1), p2 = ld3(gx + 3 * g2), s1 = ld3(m.geom_size + 3 * g1), s2 = ld3(m.geom_size + 3 * g2);
@@ -171,7 +393,10 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t2 == B2S_GEOM_SPHERE) n = sphere_sphere(rc, margin, p1, s1.x, p2, s2.x);
         else if (t2 == B2S_GEOM_CAPSULE) n = sphere_capsule(rc, margin, p1, s1, p2, m2, s2);
         else if (t2 == B2S_GEOM_BOX) n = sphere_box(rc, margin, p1, s1, p2, m2, s2);
-      } else if (t1 == B2S_GEOM_CAPSULE && t2 == B2S_GEOM_CAPSULE) n = capsule_capsule(rc, margin, p1, m1, s1, p2, m2, s2);
+      } else if (t1 == B2S_GEOM_CAPSULE) {
+        if (t2 == B2S_GEOM_CAPSULE) n = capsule_capsule(rc, margin, p1, m1, s1, p2, m2, s2);
+        else if (t2 == B2S_GEOM_BOX) n = capsule_box(rc, margin, p1, m1, s1, p2, m2, s2);
+      } else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) n = box_box(rc, margin, p1, m1, s1, p2, m2, s2);
     }
     int total;
     const int excl = warp_excl_scan(n, lane, &total);
@@ -227,5 +452,5 @@ void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   k_collision<<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
   b2s_count_launch();
 }
-size_t smem_collision(const ModelDev&) { return (size_t)B2S_WARPS_PER_CTA * B2S_MAX_SURVIVORS * sizeof(int); }
+size_t smem_collision(const ModelDev&) { return (size_t)B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1) * sizeof(int); }
 const void* fn_collision() { return (const void*)k_collision; }

@@ -330,6 +330,9 @@ def build_go1(xml_path, terrain="plane", terrain_seed=0) -> HostModel:
   velocity_sim_options(scene)
   m = scene.compile()
   m.meta = dict(task="Mjlab-Velocity-%s-Unitree-Go1" % ("Flat" if terrain == "plane" else "Rough"), nconmax=50, njmax=300, decimation=4)
+  if terrain != "plane":
+    m.meta["terrain_origins"] = np.asarray(scene.terrain_origins).tolist()   # [num_rows][num_cols][3] spawn points
+    m.meta["terrain_seed"] = terrain_seed
   return m
 
 

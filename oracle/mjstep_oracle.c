@@ -467,7 +467,7 @@ static real seg_box_closest(const real* a, const real* dd, const real* h, int* i
     if (t > 0 && t < 1) ts[nt++] = t;
   }
   for (int i = 1; i < nt; i++) { real v = ts[i]; int j = i - 1; while (j >= 0 && ts[j] > v) { ts[j + 1] = ts[j]; j--; } ts[j + 1] = v; }
-  real best = (real)1e30, bt = 0; int inside = 0;
+  real best = (real)1e30, bt = 0, tin = 0; int inside = 0;
   for (int k = 0; k + 1 < nt; k++) {
     real t0 = ts[k], t1 = ts[k + 1], tm = (real)0.5*(t0 + t1), A = 0, B = 0;
     int nout = 0;
@@ -477,23 +477,14 @@ static real seg_box_closest(const real* a, const real* dd, const real* h, int* i
       if (pm > h[i] || pm < -h[i]) { A += dd[i]*dd[i]; B += dd[i]*(a[i] - r); nout++; }
     }
     real t = t0;
-    if (nout == 0) { inside = 1; }
+    if (nout == 0) { inside = 1; tin = tm; }      /* the part of the segment inside the box is ONE interval: take its middle */
     else if (A > MINVAL) t = clipr(-B/A, t0, t1);
     real d2 = 0;
     for (int i = 0; i < 3; i++) { real pv = a[i] + t*dd[i]; real c = clipr(pv, -h[i], h[i]); d2 += (pv - c)*(pv - c); }
     if (d2 < best) { best = d2; bt = t; }
   }
-  if (inside) {   /* deepest of the sampled inside points */
-    real bd = -1;
-    for (int k = 0; k < nt + 1; k++) {
-      real t = k < nt ? ts[k] : (real)0.5;
-      real depth = (real)1e30; int in = 1;
-      for (int i = 0; i < 3; i++) { real pv = a[i] + t*dd[i]; real e = h[i] - (real)fabs((double)pv); if (e < 0) in = 0; if (e < depth) depth = e; }
-      if (in && depth > bd) { bd = depth; bt = t; }
-    }
-  }
   *inside_out = inside;
-  return bt;
+  return inside ? tin : bt;
 }
 static int col_capsule_box(rawcon* c, real margin, const real* p1, const real* m1, const real* s1, const real* p2, const real* m2, const real* s2) {
   real axis[3] = {m1[2], m1[5], m1[8]}, e0[3], e1[3], a[3], b[3], dd[3], tmp[3];
@@ -507,7 +498,23 @@ static int col_capsule_box(rawcon* c, real margin, const real* p1, const real* m
   real tb = seg_box_closest(a, dd, s2, &inside);
   real pt[3], rad[3] = {s1[0], 0, 0};
   for (int k = 0; k < 3; k++) pt[k] = e0[k] + tb*(e1[k] - e0[k]);
-  int n = col_sphere_box(c, margin, pt, rad, p2, m2, s2);
+  int n;
+  if (!inside) n = col_sphere_box(c, margin, pt, rad, p2, m2, s2);
+  else {
+    /* the segment passes through the box: contact at the middle of the inside part, pushed out along the box axis of
+     * least depth, towards the side the capsule CENTRE is on (robust for thin boxes, where both faces are equally near) */
+    real ps[3], ctr[3], nl[3] = {0, 0, 0};
+    for (int k = 0; k < 3; k++) { ps[k] = a[k] + tb*dd[k]; ctr[k] = a[k] + (real)0.5*dd[k]; }
+    int kb = 0; real bestd = s2[0] - (real)fabs((double)ps[0]);
+    for (int k = 1; k < 3; k++) { real e = s2[k] - (real)fabs((double)ps[k]); if (e < bestd) { bestd = e; kb = k; } }
+    real sg = ctr[kb] >= 0 ? (real)1 : (real)-1;
+    nl[kb] = -sg;
+    real depth = s2[kb] - sg*ps[kb];
+    mat_vec(c->frame, m2, nl);
+    c->dist = -depth - s1[0];
+    for (int k = 0; k < 3; k++) { c->pos[k] = pt[k] + c->frame[k]*(s1[0] + c->dist*(real)0.5); c->frame[3 + k] = 0; }
+    n = 1;
+  }
   if (n == 0) return 0;
   for (int e = 0; e < 2 && n < 2; e++) {
     real te = (real)e;

@@ -23,3 +23,9 @@ def g1():
 def go1():
   from asimov_mjlab_b200 import scenes
   return scenes.load_asset("go1_flat")
+
+
+@pytest.fixture(scope="session")
+def go1_rough():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("go1_rough")

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import fixtures as fx
-from util import contact_pairs, g1_states, legged_states
+from util import contact_pairs, g1_states, legged_states, rough_states
 
 pytestmark = pytest.mark.gpu
 
@@ -147,6 +147,73 @@ def test_go1_flat_forward_and_steps_match_oracle(go1, ls_parallel):
   assert _rel_err(D, worlds, "sensordata") < 2e-2
 
 
+def test_go1_rough_box_terrain_matches_oracle(go1_rough):
+  """Mjlab-Velocity-Rough-Unitree-Go1 with the reference's default box terrain (BASELINE.json configs[2], 3564 static
+  boxes found through the put_model grid): sphere-box, capsule-box contacts; same contacts in the same order."""
+  import torch
+  W = 24
+  qpos, qvel, ctrl = rough_states(go1_rough, W, seed=7, tumble=1.2)
+  engine, M, D, orc, worlds = _setup(go1_rough, W, qpos, qvel, ctrl, True)
+  seen = set()
+  # the oracle drives the trajectory (tumbling robots are chaotic: a contact at dist ~ 0 flips on a 1e-7 state
+  # difference); every 10 steps its state is copied to the device and forward() + one step are compared there
+  for chunk in range(8):
+    for w in worlds:
+      orc.step(w, 10)
+    for f in ("qpos", "qvel", "qacc_warmstart"):
+      getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+    engine.forward(M, D)
+    for w in worlds:
+      orc.forward(w)
+    _check_counts(D, worlds)
+    for f in ("geom_xpos", "qacc", "sensordata", "qfrc_constraint"):
+      assert _rel_err(D, worlds, f) < 2e-3, f
+    n_all = D.ncon.cpu().numpy()
+    P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy(); Di = D.contact_dist.cpu().numpy()
+    for i, w in enumerate(worlds):
+      n = int(n_all[i])
+      assert np.abs(P[i, :n].reshape(-1) - w["con_pos"][: 3 * n]).max(initial=0) < 1e-4
+      assert np.abs(Fr[i, :n].reshape(-1) - w["con_frame"][: 9 * n]).max(initial=0) < 1e-3
+      assert np.abs(Di[i, :n] - w["con_dist"][:n]).max(initial=0) < 1e-5
+      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
+        seen.add((int(go1_rough.geom_type[g1]), int(go1_rough.geom_type[g2])))
+  assert (2, 6) in seen and (3, 6) in seen          # sphere-box and capsule-box both exercised
+  engine.step(M, D)
+  for w in worlds:
+    orc.step(w)
+  assert _rel_err(D, worlds, "qpos") < 1e-5 and _rel_err(D, worlds, "qvel") < 5e-3
+
+
+def test_box_fixture_box_box_and_capsule_box(ls_parallel=True):
+  """box-box face manifold + capsule-box on a small fixture, through the static pair table."""
+  import torch
+  m = fx.compile_xml(fx.BOX_ON_BOX)
+  W = 8
+  rng = np.random.default_rng(11)
+  qpos = np.tile(m.qpos0, (W, 1)); qvel = np.zeros((W, m.nv)); ctrl = np.zeros((W, m.nu))
+  for w in range(1, W):
+    for k in (0, 7):       # crate, rod: random tilt and a small drop
+      ax = rng.normal(size=3); ax /= np.linalg.norm(ax); ang = rng.normal(0, 0.5)
+      qpos[w, k + 3: k + 7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
+      qpos[w, k + 2] += rng.uniform(0.0, 0.05)
+    qvel[w] = rng.normal(0, 0.3, m.nv)
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, ls_parallel, nconmax=24, njmax=96)
+  types = set()
+  for chunk in range(10):
+    engine.step(M, D, 20)
+    torch.cuda.synchronize()
+    for w in worlds:
+      orc.step(w, 20)
+    _check_counts(D, worlds)
+    for w in worlds:
+      n = int(w["ncon"][0])
+      types |= {(int(m.geom_type[a]), int(m.geom_type[b])) for a, b in w["con_geom"][: 2 * n].reshape(n, 2)}
+    if chunk == 0:
+      assert _rel_err(D, worlds, "qpos") < 1e-4
+  assert (6, 6) in types and (3, 6) in types
+  assert _rel_err(D, worlds, "qpos") < 2e-2
+
+
 def test_g1_friction_domain_randomisation_per_world(g1):
   """expand_model_fields + per-world geom_friction (reference events.py:228-253, randomization.py:20-54)."""
   import torch
@@ -264,9 +331,10 @@ def test_unsupported_features_raise():
   m.dof_frictionloss = m.dof_frictionloss + 0.1
   with pytest.raises(engine.BackendError, match="frictionloss"):
     engine.put_model(m)
-  box2 = fx.FALLING_BOX.replace('<body name="ground">', '<body name="b2" pos="0 0 1"><freejoint/><geom type="box" size=".1 .1 .1"/></body><body name="ground">')
-  with pytest.raises(engine.BackendError, match="box-box"):
-    engine.put_model(fx.compile_xml(box2))
+  cyl = fx.compile_xml(fx.FALLING_BOX)
+  cyl.geom_type = cyl.geom_type.copy(); cyl.geom_type[cyl.names["geom"].index("box_geom")] = 5   # cylinder: no narrowphase yet
+  with pytest.raises(engine.BackendError, match="plane-cylinder"):
+    engine.put_model(cyl)
   with pytest.raises(engine.BackendError, match="CUDA"):
     engine.put_model(fx.compile_xml(fx.SPHERE_DROP), "cpu")
 

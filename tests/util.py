@@ -31,3 +31,25 @@ def legged_states(m, nworld, seed=0, spread=0.3, vel=0.5, zlo=None, zhi=None):
   key = m.keys["robot/init_state"]
   z0 = key["qpos"][2]
   return g1_states(m, nworld, seed, spread, vel, z0 - 0.03 if zlo is None else zlo, z0 + 0.07 if zhi is None else zhi)
+
+
+def rough_states(m, nworld, seed=0, spread=0.2, vel=0.3, drop=(0.0, 0.08), tumble=0.0):
+  """Go1 on the box terrain: worlds spawn at the generator's terrain origins (all difficulty rows, flat / stairs /
+  inverted-stairs columns) with a random xy offset (so feet land on step edges), a small drop height and tilt."""
+  rng = np.random.default_rng(seed)
+  org = np.asarray(m.meta["terrain_origins"])
+  qpos, qvel, ctrl = legged_states(m, nworld, seed, spread, vel)
+  key = m.keys["robot/init_state"]
+  for w in range(nworld):
+    o = org[rng.integers(org.shape[0]), rng.integers(org.shape[1])]
+    off = rng.uniform(-2.2, 2.2, 2)
+    qpos[w, 0:2] = o[:2] + off
+    # ground height under the spawn point is not known in closed form on stairs: start from the platform height and
+    # let the robot drop (stairs descend away from the platform on pyramids, ascend on inverted ones)
+    qpos[w, 2] = max(o[2], 0.0) + key["qpos"][2] + rng.uniform(*drop)
+    if tumble > 0.0 and w % 2 == 1:   # every other world: large random tilt, lower start -> leg capsules / trunk box touch
+      ax = rng.normal(size=3); ax /= np.linalg.norm(ax)
+      ang = rng.normal(0, tumble)
+      qpos[w, 3:7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
+      qpos[w, 2] -= 0.12
+  return qpos, qvel, ctrl

@@ -14,7 +14,7 @@ scenes.save_model(m, os.path.join(scenes.ASSET_DIR, "g1_flat.npz"))
 print("g1_flat: nq", m.nq, "nv", m.nv, "nu", m.nu, "nbody", m.nbody, "ngeom", m.ngeom,
       "nsite", m.nsite, "nsensordata", m.nsensordata, "meaninertia", m.stat.meaninertia)
 
-for terr in ("plane",):
+for terr in ("plane", "rough"):
   g = scenes.build_go1(os.path.join(zoo, "unitree_go1/xmls/go1.xml"), terrain=terr)
   name = "go1_flat" if terr == "plane" else "go1_rough"
   scenes.save_model(g, os.path.join(scenes.ASSET_DIR, name + ".npz"))
