@@ -324,6 +324,15 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.geom_solref = up.f(s->geom_solref, 2 * s->ngeom); d.geom_solimp = up.f(s->geom_solimp, 5 * s->ngeom);
   d.geom_margin = up.f(s->geom_margin, s->ngeom); d.geom_gap = up.f(s->geom_gap, s->ngeom); d.geom_rbound = up.f(s->geom_rbound, s->ngeom);
   d.pair_geom = up.raw(pairs);
+  {
+    // a body is static if it is welded to the world and is not a mocap body
+    std::vector<int> pg, ps, sg, ss;
+    auto is_static = [&](int b) { return s->body_weldid[b] == 0 && s->body_mocapid[b] < 0; };
+    for (int g = 0; g < s->ngeom; g++) (is_static(s->geom_bodyid[g]) ? sg : pg).push_back(g);
+    for (int k = 0; k < s->nsite; k++) (is_static(s->site_bodyid[k]) ? ss : ps).push_back(k);
+    d.nposegeom = (int)pg.size(); d.nposesite = (int)ps.size(); d.nstatgeom = (int)sg.size(); d.nstatsite = (int)ss.size();
+    d.pose_geom = up.raw(pg); d.pose_site = up.raw(ps); d.stat_geom = up.raw(sg); d.stat_site = up.raw(ss);
+  }
   d.geom_contype = up.i(s->geom_contype, s->ngeom); d.geom_conaffinity = up.i(s->geom_conaffinity, s->ngeom);
   d.ngrid = use_grid ? (int)grid_geoms.size() : 0;
   d.ndyngeom = (int)dyn_geoms.size(); d.dyn_geom = up.raw(dyn_geoms);
@@ -583,7 +592,19 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   }
   for (auto& e : D->ev) cudaEventCreate(&e);
   D->have_ev = true;
+  // frames of everything attached to static bodies, once
+  launch_position(md, d, 0);
+  launch_static_frames(md, d, 0);
+  if (cudaDeviceSynchronize() != cudaSuccess) { delete D; return fail(std::string("initial position pass failed: ") + cudaGetErrorString(cudaGetLastError())); }
   *out = D;
+  return 0;
+}
+// Recompute the frames of geoms / sites on static bodies (after writing body_pos, body_quat, geom_pos, geom_quat,
+// site_pos or site_quat of a static body, e.g. per-world terrain randomisation).  step/forward never touch them.
+extern "C" int b2s_refresh_static(const b2s_model* m, b2s_data* d, void* stream) {
+  if (!m || !d) return fail("null argument");
+  launch_position(m->dev, d->dev, (cudaStream_t)stream);
+  launch_static_frames(m->dev, d->dev, (cudaStream_t)stream);
   return 0;
 }
 extern "C" int b2s_data_destroy(b2s_data* d) { delete d; return 0; }

@@ -8,6 +8,7 @@ void b2s_count_launch();
 
 // stage launchers (each is one kernel launch on `st`)
 void launch_position(const ModelDev& m, const DataDev& d, cudaStream_t st);
+void launch_static_frames(const ModelDev& m, const DataDev& d, cudaStream_t st);
 void launch_dynamics(const ModelDev& m, const DataDev& d, cudaStream_t st);
 void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st);
 void launch_constraint(const ModelDev& m, const DataDev& d, cudaStream_t st);

@@ -58,6 +58,10 @@ struct ModelDev {
   float grid_x0, grid_y0, grid_inv, grid_margin;
   const int *grid_adr, *grid_geom, *dyn_geom;   // CSR cell -> static geom ids; dynamic geoms that can collide
   const float* grid_aabb;                       // [ngeom][6] world AABB (min xyz, max xyz) of grid geoms
+  // geoms / sites on moving bodies (recomputed every step) and on static, world-welded bodies (computed once at
+  // put_data and by b2s_refresh_static: thousands of terrain geoms would otherwise dominate the position stage)
+  int nposegeom, nposesite, nstatgeom, nstatsite;
+  const int *pose_geom, *pose_site, *stat_geom, *stat_site;
   const int *pair_geom;             // [npair][2] after type ordering (type1 <= type2), sorted by (min id, max id)
   // ---- sites
   const int *site_bodyid;

@@ -63,6 +63,7 @@ def lib():
     L.b2s_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.b2s_step_n.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.b2s_step_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.b2s_refresh_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.b2s_efc_jacobian.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.b2s_profile_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
     _LIB = L
@@ -312,6 +313,11 @@ def _stream(m: Model):
 
 def forward(m: Model, d: Data) -> None:
   _check(lib().b2s_forward(m._h.ptr, d._h.ptr, _stream(m)))
+
+
+def refresh_static(m: Model, d: Data) -> None:
+  """Recompute geom/site frames of static bodies (they are not touched by step/forward; see include/b200sim.h)."""
+  _check(lib().b2s_refresh_static(m._h.ptr, d._h.ptr, _stream(m)))
 
 
 def step(m: Model, d: Data, nsub: int = 1) -> None:

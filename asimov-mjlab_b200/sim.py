@@ -94,6 +94,9 @@ class Simulation:
     side = torch.cuda.Stream(device=dev)
     side.wait_stream(torch.cuda.current_stream(dev))
     with torch.cuda.stream(side):   # warm up outside capture (lazy module loading)
+      # create_graph() follows expand_model_fields + startup randomisation (manager_based_rl_env.py:107-109): refresh the
+      # once-only frames of static bodies so terrain pose randomisation is honoured
+      engine.refresh_static(self._model, self._data)
       engine.forward(self._model, self._data)
     torch.cuda.current_stream(dev).wait_stream(side)
     torch.cuda.synchronize(dev)

@@ -22,7 +22,23 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-ALG_BYTES_PER_SUBSTEP_WORLD = 5268  # 4 B x (363 in + 747 out + 207 per-world Model reads)
+ALG_BYTES_PER_SUBSTEP_WORLD = 5268  # 4 B x (363 in + 747 out + 207 per-world Model reads), G1-flat
+WORKLOADS = {
+  "g1_flat": ("g1_flat", "Mjlab-Velocity-Flat-Unitree-G1 physics step, random actions (BASELINE.json configs[1])"),
+  "go1_flat": ("go1_flat", "Mjlab-Velocity-Flat-Unitree-Go1 physics step, random actions"),
+  "go1_rough": ("go1_rough", "Mjlab-Velocity-Rough-Unitree-Go1 physics step on the reference's default box terrain, random actions (BASELINE.json configs[2], box variant)"),
+}
+
+
+def alg_bytes(m, friction_geoms):
+  """SURVEY.md §8(d) formula: 4 B x (state in + state/manager-visible out + per-world Model reads) per world per sub-step.
+  in  = qpos + qvel + ctrl + qacc_warmstart + time + xfrc_applied + qfrc_applied
+  out = qpos + qvel + qacc + qacc_warmstart + time + sensordata + xpos + xquat + subtree_com + cvel (robot bodies count
+        as nbody) + site_xpos + site_xmat; Model = geom_friction of the geoms that are randomised per world."""
+  nb = m.nbody
+  r = m.nq + m.nv + m.nu + m.nv + 1 + 6 * nb + m.nv
+  w = m.nq + 3 * m.nv + 1 + m.nsensordata + (3 + 4 + 3 + 6) * nb + 12 * m.nsite
+  return 4 * (r + w + 3 * friction_geoms)
 DECIMATION = 4
 RESET_PERIOD_STEPS = 250            # reset every 1000 sub-steps (SURVEY.md §8d config 2), forward() inside the timed region
 
@@ -36,6 +52,7 @@ def parse():
   ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
   ap.add_argument("--cpu-baseline", type=int, default=1)
   ap.add_argument("--ls-parallel", type=int, default=1)
+  ap.add_argument("--workload", default="g1_flat", choices=sorted(WORKLOADS))
   return ap.parse_args()
 
 
@@ -84,9 +101,9 @@ class ClockSampler:
     return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def load_model(ls_parallel=1):
+def load_model(ls_parallel=1, workload="g1_flat"):
   from asimov_mjlab_b200 import scenes
-  m = scenes.load_asset("g1_flat")
+  m = scenes.load_asset(WORKLOADS[workload][0])
   m.opt.ls_parallel = bool(ls_parallel)
   return m
 
@@ -97,7 +114,7 @@ def action_targets(m, n_batches, envs, seed, device=None):
   from asimov_mjlab_b200 import scenes
   key = m.keys["robot/init_state"]
   jn = [n.split("/")[-1] for n in m.names["actuator"]]
-  scale = scenes.g1_action_scale(jn)
+  scale = scenes.g1_action_scale(jn) if m.nu == 29 else scenes.go1_action_scale(jn)
   rng = np.random.default_rng(seed)
   a = rng.uniform(-1.0, 1.0, size=(n_batches, envs, m.nu)).astype(np.float32)
   return (np.asarray(key["ctrl"], np.float32)[None, None, :] + scale.astype(np.float32)[None, None, :] * a)
@@ -127,7 +144,7 @@ def run_reference(args):
   rank = int(os.environ.get("RANK", "0"))
   if rank != 0:
     return
-  m = load_model(args.ls_parallel)
+  m = load_model(args.ls_parallel, args.workload)
   cores = os.cpu_count() or 1
   nworld = 16 * cores
   # warm-up then K timed steps, each a bounded sample: one decimation of `nworld` worlds
@@ -138,7 +155,7 @@ def run_reference(args):
     "impl": "reference", "metric": "env_steps_per_s", "value": rate, "unit": "physics sub-steps/s (1 env-step = 1 sim.step per world)",
     "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
     "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-    "config": {"workload": "Mjlab-Velocity-Flat-Unitree-G1 physics step, random actions", "envs_per_step": nworld, "decimation": DECIMATION},
+    "config": {"workload": WORKLOADS[args.workload][1], "envs_per_step": nworld, "decimation": DECIMATION},
     "cpu_baseline": {"value": rate, "unit": "physics sub-steps/s", "cores": cores, "kind": "port", "sample": sample},
     "e2e": {"value": rate, "unit": "physics sub-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
   }
@@ -163,7 +180,7 @@ def run_b200(args):
   if world > 1:
     dist.init_process_group("nccl", device_id=torch.device(dev))
   E = args.envs
-  m = load_model(args.ls_parallel)
+  m = load_model(args.ls_parallel, args.workload)
   cfg = SimulationCfg(nconmax=50, njmax=300, ls_parallel=bool(args.ls_parallel),
                       mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20))
   sim = Simulation(E, cfg, m, dev)
@@ -183,10 +200,17 @@ def run_b200(args):
   nbatch = 64
   ctrl_pool = torch.as_tensor(action_targets(m, nbatch, E, seed=1000 + rank), device=dev)
   origins = torch.zeros(E, 3, device=dev)
-  side = int(np.ceil(np.sqrt(E)))
-  idx = torch.arange(E, device=dev)
-  origins[:, 0] = (idx // side).float() * 2.5
-  origins[:, 1] = (idx % side).float() * 2.5
+  if "terrain_origins" in m.meta:     # curriculum spawn points of the box terrain (terrain_importer.py:203-223)
+    from asimov_mjlab_b200 import terrains
+    eo, _, _ = terrains.env_origins_curriculum(E, np.asarray(m.meta["terrain_origins"]), seed=rank)
+    origins[:] = torch.as_tensor(eo, dtype=torch.float32, device=dev)
+    origins[:, 0:2] += (torch.rand(E, 2, generator=g) - 0.5).to(dev) * 2.0     # off the platform centre, onto the steps
+    origins[:, 2].clamp_(min=0.0).add_(0.05)
+  else:
+    side = int(np.ceil(np.sqrt(E)))
+    idx = torch.arange(E, device=dev)
+    origins[:, 0] = (idx // side).float() * 2.5
+    origins[:, 1] = (idx % side).float() * 2.5
   noise = 0.02 * torch.randn(E, m.nq - 7, generator=g).to(dev)
 
   def reset_all():
@@ -262,14 +286,15 @@ def run_b200(args):
   e2e_value = world * E * DECIMATION * e2e_steps / (ms_e2e * 1e-3)
   peak, peak_src = measured_peak()
   per_gpu_substep_s = (ms * 1e-3) / (args.steps * DECIMATION)
-  achieved = E * ALG_BYTES_PER_SUBSTEP_WORLD / per_gpu_substep_s / 1e9
+  ab = ALG_BYTES_PER_SUBSTEP_WORLD if args.workload == "g1_flat" else alg_bytes(m, len(foot))
+  achieved = E * ab / per_gpu_substep_s / 1e9
   tot = sum(stages.values())
   top = max(stages, key=stages.get)
   out = {
     "metric": "env_steps_per_s", "value": value, "unit": "physics sub-steps/s (1 env-step = 1 sim.step per world)",
     "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
     "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-    "config": {"workload": "Mjlab-Velocity-Flat-Unitree-G1 physics step, random actions (BASELINE.json configs[1])",
+    "config": {"workload": WORKLOADS[args.workload][1],
                "envs_per_gpu": E, "decimation": DECIMATION, "substeps_per_step": DECIMATION, "timestep": 0.005,
                "nconmax": 50, "njmax": 300, "iterations": 10, "ls_iterations": 20, "ls_parallel": bool(args.ls_parallel),
                "friction_dr": True, "resets_in_timed_region": n_resets, "parallelism": f"env-shard x{world}, no collective on the step path",
@@ -279,14 +304,14 @@ def run_b200(args):
             "api": "b2s_step_host (C ABI) with pinned host buffers"},
     "gpu_launches": int(args.steps * per_graph["decimation"] + n_resets * per_graph["forward"]),
     "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                 "peak_source": peak_src, "scope": "whole sub-step (7 stage kernels); algorithmic bytes 5268 B per world per sub-step",
+                 "peak_source": peak_src, "scope": f"whole sub-step (7 stage kernels); algorithmic bytes {ab} B per world per sub-step",
                  "dominant_kernel": top, "dominant_share": stages[top] / tot, "stage_ms": stages},
     "clocks": clocks,
   }
   if args.cpu_baseline and world == 1:
     cores = os.cpu_count() or 1
     nw = 8 * cores
-    rate, dt = cpu_rollout(m, nw, 200, cores, ls_parallel=args.ls_parallel)
+    rate, dt = cpu_rollout(m, nw, 200 if m.ngeom < 500 else 40, cores, ls_parallel=args.ls_parallel)
     out["cpu_baseline"] = {"value": rate, "unit": "physics sub-steps/s", "cores": cores, "kind": "port",
                            "sample": f"{nw} worlds x 200 sub-steps, oracle f32 with OpenMP on {cores} threads ({dt:.1f} s)"}
   print(json.dumps(out), flush=True)

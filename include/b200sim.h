@@ -248,6 +248,10 @@ int64_t b2s_data_bytes(const b2s_data* d);
  * demand into storage owned by `d` (allocated on first use; call again after a step to refresh it). */
 int b2s_efc_jacobian(const b2s_model* m, b2s_data* d, void* stream, b2s_field_info* out);
 
+/* Frames of geoms and sites on static (world-welded) bodies are computed once at b2s_data_create; call this after
+ * writing pose fields of a static body (per-world terrain randomisation).  The reference recomputes them every step. */
+int b2s_refresh_static(const b2s_model* m, b2s_data* d, void* stream);
+
 /* forward / step on `stream` (a cudaStream_t passed as void*). */
 int b2s_forward(const b2s_model* m, b2s_data* d, void* stream);
 int b2s_step(const b2s_model* m, b2s_data* d, void* stream);
