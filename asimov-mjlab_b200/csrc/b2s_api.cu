@@ -139,9 +139,25 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     if (s->jnt_type[j] < 0 || s->jnt_type[j] > 3) return fail("unknown joint type");
     if (s->jnt_type[j] == B2S_JNT_BALL && s->jnt_limited[j]) return fail("ball joint limits are not supported");
   }
+  if (s->ntendon < 0 || s->nwrap < 0) return fail("negative tendon sizes");
+  for (int t = 0; t < s->ntendon; t++) {
+    if (s->tendon_limited[t]) return fail("tendon limits are not supported");
+    if (s->tendon_adr[t] < 0 || s->tendon_num[t] < 0 || s->tendon_adr[t] + s->tendon_num[t] > s->nwrap) return fail("tendon wrap range out of bounds");
+  }
+  for (int k = 0; k < s->nwrap; k++) {
+    const int j = s->wrap_objid[k];
+    if (s->wrap_type[k] != 1) return fail("only fixed tendons (joint wraps) are supported");
+    if (j < 0 || j >= s->njnt || (s->jnt_type[j] != B2S_JNT_HINGE && s->jnt_type[j] != B2S_JNT_SLIDE)) return fail("fixed tendons must wrap hinge or slide joints");
+  }
   for (int u = 0; u < s->nu; u++) {
     const int j = s->actuator_trnid[u];
-    if (j < 0 || j >= s->njnt || (s->jnt_type[j] != B2S_JNT_HINGE && s->jnt_type[j] != B2S_JNT_SLIDE)) return fail("actuators must target hinge or slide joints");
+    if (s->actuator_trntype[u] == B2S_TRN_TENDON) {
+      if (j < 0 || j >= s->ntendon) return fail("actuator tendon id out of range");
+    } else if (s->actuator_trntype[u] != B2S_TRN_JOINT) {
+      return fail("actuator transmission must be joint or tendon");
+    } else if (j < 0 || j >= s->njnt || (s->jnt_type[j] != B2S_JNT_HINGE && s->jnt_type[j] != B2S_JNT_SLIDE)) {
+      return fail("actuators must target hinge or slide joints");
+    }
   }
   // bodies must be in DFS pre-order (MuJoCo's compiler guarantees it)
   std::vector<int> send(nb), ssize(nb, 1), depth(nb, 0);
@@ -340,6 +356,17 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.grid_inv = (float)(1.0 / grid_cell); d.grid_margin = (float)grid_margin;
   d.grid_adr = up.raw(grid_adr); d.grid_geom = up.raw(grid_list); d.grid_aabb = up.raw(grid_aabb);
   d.site_bodyid = up.i(s->site_bodyid, s->nsite);
+  d.ntendon = s->ntendon; d.nwrap = s->nwrap;
+  {
+    std::vector<int> wdof((size_t)s->nwrap), wqpos((size_t)s->nwrap);
+    for (int k = 0; k < s->nwrap; k++) { wdof[k] = s->jnt_dofadr[s->wrap_objid[k]]; wqpos[k] = s->jnt_qposadr[s->wrap_objid[k]]; }
+    d.wrap_dof = up.raw(wdof); d.wrap_qpos = up.raw(wqpos);
+  }
+  d.tendon_adr = up.i(s->tendon_adr, s->ntendon); d.tendon_num = up.i(s->tendon_num, s->ntendon);
+  d.wrap_coef = up.f(s->wrap_prm, s->nwrap);
+  d.tendon_stiffness = up.f(s->tendon_stiffness, s->ntendon); d.tendon_damping = up.f(s->tendon_damping, s->ntendon);
+  d.tendon_lengthspring = up.f(s->tendon_lengthspring, 2 * s->ntendon);
+  d.actuator_trntype = up.i(s->actuator_trntype, s->nu);
   d.actuator_trnid = up.i(s->actuator_trnid, s->nu); d.actuator_gaintype = up.i(s->actuator_gaintype, s->nu);
   d.actuator_biastype = up.i(s->actuator_biastype, s->nu); d.actuator_ctrllimited = up.i(s->actuator_ctrllimited, s->nu);
   d.actuator_forcelimited = up.i(s->actuator_forcelimited, s->nu); d.actuator_gear = up.f(s->actuator_gear, s->nu);
@@ -523,6 +550,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"subtree_com", B2S_F32, (void**)&d.subtree_com, {nb, 3}}, {"cinert", B2S_F32, (void**)&d.cinert, {nb, 10}}, {"cdof", B2S_F32, (void**)&d.cdof, {nv, 6}},
     {"cvel", B2S_F32, (void**)&d.cvel, {nb, 6}}, {"cdof_dot", B2S_F32, (void**)&d.cdof_dot, {nv, 6}}, {"qM", B2S_F32, (void**)&d.qM, {nv, nvp}},
     {"qfrc_bias", B2S_F32, (void**)&d.qfrc_bias, {nv}}, {"qfrc_passive", B2S_F32, (void**)&d.qfrc_passive, {nv}},
+    {"ten_length", B2S_F32, (void**)&d.ten_length, {md.ntendon}}, {"ten_velocity", B2S_F32, (void**)&d.ten_velocity, {md.ntendon}},
     {"actuator_length", B2S_F32, (void**)&d.actuator_length, {md.nu}}, {"actuator_velocity", B2S_F32, (void**)&d.actuator_velocity, {md.nu}},
     {"actuator_force", B2S_F32, (void**)&d.actuator_force, {md.nu}}, {"qfrc_actuator", B2S_F32, (void**)&d.qfrc_actuator, {nv}},
     {"qfrc_smooth", B2S_F32, (void**)&d.qfrc_smooth, {nv}}, {"qacc_smooth", B2S_F32, (void**)&d.qacc_smooth, {nv}},

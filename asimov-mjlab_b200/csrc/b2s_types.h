@@ -66,7 +66,11 @@ struct ModelDev {
   // ---- sites
   const int *site_bodyid;
   WField<float> site_pos, site_quat;
-  // ---- actuators
+  // ---- fixed tendons (wraps flattened to dof / qpos addresses) and actuators
+  int ntendon, nwrap;
+  const int *tendon_adr, *tendon_num, *wrap_dof, *wrap_qpos;
+  const float *wrap_coef, *tendon_stiffness, *tendon_damping, *tendon_lengthspring;
+  const int *actuator_trntype;
   const int *actuator_trnid, *actuator_gaintype, *actuator_biastype, *actuator_ctrllimited, *actuator_forcelimited;
   const float *actuator_gear, *actuator_ctrlrange, *actuator_forcerange;
   WField<float> actuator_gainprm, actuator_biasprm;   // 3 per actuator
@@ -84,7 +88,7 @@ struct DataDev {
   float *xpos, *xquat, *xmat, *xipos, *ximat, *xanchor, *xaxis, *geom_xpos, *geom_xmat, *site_xpos, *site_xmat;
   float *subtree_com, *cinert, *cdof;
   // dynamics stage
-  float *cvel, *cdof_dot, *qM, *qfrc_bias, *qfrc_passive, *actuator_length, *actuator_velocity, *actuator_force;
+  float *cvel, *cdof_dot, *qM, *qfrc_bias, *qfrc_passive, *ten_length, *ten_velocity, *actuator_length, *actuator_velocity, *actuator_force;
   float *qfrc_actuator, *qfrc_smooth, *qacc_smooth;
   // collision
   int *ncon, *con_dim, *con_geom, *con_efc_address;

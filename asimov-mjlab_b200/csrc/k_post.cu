@@ -288,6 +288,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const Mode
           if (f <= m.actuator_forcerange[2 * u] || f >= m.actuator_forcerange[2 * u + 1]) continue;
         }
         const float g = m.actuator_gear[u];
+        if (m.actuator_trntype[u] == B2S_TRN_TENDON) continue;     // rank-1 term, added to A below
         atomicAdd(&dg[m.jnt_dofadr[m.actuator_trnid[u]]], g * g * bv);
       }
     }
@@ -309,6 +310,48 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const Mode
       const int r = i / nvp, c = i - r * nvp;
       if (c <= r) A[r * ld + c] = M[i] - (c == r ? dt * dg[r] : 0.f);
       else if (c < nv) A[r * ld + c] = 0.f;     // the substitution needs a zero strict upper triangle
+    }
+    __syncwarp();
+    if (m.ntendon > 0 && m.integrator == B2S_INT_IMPLICITFAST && lane == 0) {
+      // velocity derivatives carried by fixed tendons, moment^T s moment: actuators in order, then tendon dampers
+      // (one lane, sequential: the sum order is part of the result)
+      if (!(m.disableflags & B2S_DSBL_ACTUATION)) {
+        const float* gainprm = m.actuator_gainprm.at(w);
+        const float* biasprm = m.actuator_biasprm.at(w);
+        for (int u = 0; u < m.nu; u++) {
+          if (m.actuator_trntype[u] != B2S_TRN_TENDON) continue;
+          float bv = 0.f;
+          if (m.actuator_biastype[u] == B2S_BIAS_AFFINE) bv += biasprm[3 * u + 2];
+          if (m.actuator_gaintype[u] == B2S_GAIN_AFFINE) {
+            float c = d.ctrl[(size_t)w * m.nu + u];
+            if (m.actuator_ctrllimited[u] && !(m.disableflags & B2S_DSBL_CLAMPCTRL)) c = clampf(c, m.actuator_ctrlrange[2 * u], m.actuator_ctrlrange[2 * u + 1]);
+            bv += gainprm[3 * u + 2] * c;
+          }
+          if (bv == 0.f) continue;
+          if (m.actuator_forcelimited[u]) {
+            const float f = d.actuator_force[(size_t)w * m.nu + u];
+            if (f <= m.actuator_forcerange[2 * u] || f >= m.actuator_forcerange[2 * u + 1]) continue;
+          }
+          const float g = m.actuator_gear[u], sc = g * g * bv;
+          const int t = m.actuator_trnid[u], a0 = m.tendon_adr[t], a1 = a0 + m.tendon_num[t];
+          for (int a = a0; a < a1; a++)
+            for (int b = a0; b < a1; b++) {
+              const int r = m.wrap_dof[a], c = m.wrap_dof[b];
+              if (c <= r) A[r * ld + c] -= dt * (sc * m.wrap_coef[a] * m.wrap_coef[b]);
+            }
+        }
+      }
+      if (!(m.disableflags & B2S_DSBL_PASSIVE))
+        for (int t = 0; t < m.ntendon; t++) {
+          const float bd = m.tendon_damping[t];
+          if (bd == 0.f) continue;
+          const int a0 = m.tendon_adr[t], a1 = a0 + m.tendon_num[t];
+          for (int a = a0; a < a1; a++)
+            for (int b = a0; b < a1; b++) {
+              const int r = m.wrap_dof[a], c = m.wrap_dof[b];
+              if (c <= r) A[r * ld + c] += dt * (bd * m.wrap_coef[a] * m.wrap_coef[b]);
+            }
+        }
     }
     __syncwarp();
     tile_cholesky_smem<T>(A, nv, ld, lane, invd);

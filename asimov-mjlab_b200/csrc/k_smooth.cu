@@ -318,14 +318,39 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
     if (c < nv) v = (c <= r) ? s_M[r * ld + c] : s_M[c * ld + r];
     d.qM[(size_t)w * nv * nvp + i] = v;
   }
-  // actuation (joint transmission)
+  // fixed tendons: length / velocity; spring (deadband) and damper forces accumulate in s_tmp
+  if (m.ntendon > 0) {
+    for (int i = lane; i < nv; i += 32) s_tmp[i] = 0.f;
+    __syncwarp();
+    const bool passive = !(m.disableflags & B2S_DSBL_PASSIVE);
+    for (int t = lane; t < m.ntendon; t += 32) {
+      const int a0 = m.tendon_adr[t], a1 = a0 + m.tendon_num[t];
+      float len = 0.f, vel = 0.f;
+      for (int k = a0; k < a1; k++) { len += m.wrap_coef[k] * qpos[m.wrap_qpos[k]]; vel += m.wrap_coef[k] * s_qvel[m.wrap_dof[k]]; }
+      d.ten_length[(size_t)w * m.ntendon + t] = len;
+      d.ten_velocity[(size_t)w * m.ntendon + t] = vel;
+      const float ks = m.tendon_stiffness[t], kb = m.tendon_damping[t];
+      if (passive && (ks != 0.f || kb != 0.f)) {
+        const float lo = m.tendon_lengthspring[2 * t], hi = m.tendon_lengthspring[2 * t + 1];
+        float f = 0.f;
+        if (len > hi) f = ks * (hi - len); else if (len < lo) f = ks * (lo - len);
+        f -= kb * vel;
+        for (int k = a0; k < a1; k++) atomicAdd(&s_tmp[m.wrap_dof[k]], m.wrap_coef[k] * f);
+      }
+    }
+    __syncwarp();
+  }
+  // actuation (joint or fixed-tendon transmission)
   if (!(m.disableflags & B2S_DSBL_ACTUATION)) {
     const float* gainprm = m.actuator_gainprm.at(w);
     const float* biasprm = m.actuator_biasprm.at(w);
     for (int u = lane; u < m.nu; u += 32) {
       const int j = m.actuator_trnid[u];
       const float gear = m.actuator_gear[u];
-      const float len = gear * qpos[m.jnt_qposadr[j]], vel = gear * s_qvel[m.jnt_dofadr[j]];
+      const bool tend = m.actuator_trntype[u] == B2S_TRN_TENDON;
+      float len, vel;
+      if (tend) { len = gear * d.ten_length[(size_t)w * m.ntendon + j]; vel = gear * d.ten_velocity[(size_t)w * m.ntendon + j]; }
+      else { len = gear * qpos[m.jnt_qposadr[j]]; vel = gear * s_qvel[m.jnt_dofadr[j]]; }
       float c = d.ctrl[(size_t)w * m.nu + u];
       if (m.actuator_ctrllimited[u] && !(m.disableflags & B2S_DSBL_CLAMPCTRL)) c = clampf(c, m.actuator_ctrlrange[2 * u], m.actuator_ctrlrange[2 * u + 1]);
       float gain = gainprm[3 * u];
@@ -337,7 +362,10 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
       d.actuator_length[(size_t)w * m.nu + u] = len;
       d.actuator_velocity[(size_t)w * m.nu + u] = vel;
       d.actuator_force[(size_t)w * m.nu + u] = f;
-      atomicAdd(&s_act[m.jnt_dofadr[j]], gear * f);
+      if (tend) {
+        const int a0 = m.tendon_adr[j], a1 = a0 + m.tendon_num[j];
+        for (int k = a0; k < a1; k++) atomicAdd(&s_act[m.wrap_dof[k]], gear * m.wrap_coef[k] * f);
+      } else atomicAdd(&s_act[m.jnt_dofadr[j]], gear * f);
     }
   } else {
     for (int u = lane; u < m.nu; u += 32) d.actuator_force[(size_t)w * m.nu + u] = 0.f;
@@ -360,6 +388,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
         const int j = m.dof_jntid[i], t = m.jnt_type[j];
         if ((t == B2S_JNT_HINGE || t == B2S_JNT_SLIDE) && stiff[j] != 0.f) pas -= stiff[j] * (qpos[m.jnt_qposadr[j]] - qspring[m.jnt_qposadr[j]]);
         pas -= damping[i] * s_qvel[i];
+        if (m.ntendon > 0) pas += s_tmp[i];
       }
       const float smooth = pas - bias + d.qfrc_applied[(size_t)w * nv + i] + s_act[i] + ext;
       d.qfrc_bias[(size_t)w * nv + i] = bias;
@@ -376,7 +405,6 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   warp_chol_solve_inv(s_M, s_invd, nv, ld, lane, b0, b1);
   if (lane < nv) d.qacc_smooth[(size_t)w * nv + lane] = b0;
   if (lane + 32 < nv) d.qacc_smooth[(size_t)w * nv + lane + 32] = b1;
-  (void)s_tmp;
 }
 
 // ---------------------------------------------------------------------------------------------- launchers

@@ -36,6 +36,8 @@ class _Stat:
 
 class HostModel:
   """Attribute bag with MjModel field names (numpy arrays, float64 / int32)."""
+  ntendon = 0     # defaults for model blobs exported before tendons existed
+  nwrap = 0
 
   def __init__(self):
     self.opt = _Opt()

@@ -181,9 +181,22 @@ class BodySpec:
 
 
 @dataclass
+class TendonSpec:
+  """<tendon><fixed>: length = sum_k coef_k * qpos[joint_k]."""
+  name: str
+  joints: list = field(default_factory=list)      # [(joint name, coef)]
+  stiffness: float = 0.0
+  damping: float = 0.0
+  springlength: list = field(default_factory=lambda: [-1.0, -1.0])
+  range: list | None = None
+  limited: bool = False
+
+
+@dataclass
 class ActuatorSpec:
   name: str
-  joint: str
+  joint: str = ""
+  tendon: str = ""
   gaintype: int = 0
   biastype: int = 0
   gainprm: list = field(default_factory=lambda: [1.0, 0.0, 0.0])
@@ -213,6 +226,7 @@ class Spec:
     self.modelname = ""
     self.worldbody = BodySpec(name="world")
     self.actuators: list[ActuatorSpec] = []
+    self.tendons: list[TendonSpec] = []
     self.sensors: list[SensorSpec] = []
     self.excludes: list[tuple[str, str]] = []
     self.keys: dict[str, dict] = {}
@@ -300,8 +314,11 @@ class Spec:
     self.worldbody.bodies.extend(child.worldbody.bodies)
     self.worldbody.geoms.extend(child.worldbody.geoms)
     self.worldbody.sites.extend(child.worldbody.sites)
+    for t in child.tendons:
+      t.name = ren(t.name); t.joints = [(ren(j), c) for j, c in t.joints]
+      self.tendons.append(t)
     for a in child.actuators:
-      a.name, a.joint = ren(a.name), ren(a.joint)
+      a.name, a.joint, a.tendon = ren(a.name), ren(a.joint), ren(a.tendon)
       self.actuators.append(a)
     for s in child.sensors:
       s.name, s.objname, s.refname = ren(s.name), ren(s.objname), ren(s.refname)
@@ -363,7 +380,22 @@ class _Parser:
     for sec in root.findall("keyframe"):
       for k in sec.findall("key"):
         spec.keys[k.get("name", "")] = {a: _floats(k.get(a)) for a in ("qpos", "qvel", "ctrl") if k.get(a)}
-    for bad in ("equality", "tendon"):
+    for sec in root.findall("tendon"):
+      for el in sec:
+        if el.tag != "fixed":
+          raise NotImplementedError("only <fixed> tendons are supported (no spatial tendons)")
+        t = TendonSpec(name=el.get("name", ""))
+        t.joints = [(j.get("joint"), float(j.get("coef"))) for j in el.findall("joint")]
+        t.stiffness = float(el.get("stiffness", 0)); t.damping = float(el.get("damping", 0))
+        if el.get("springlength"):
+          v = _floats(el.get("springlength")); t.springlength = [v[0], v[-1]]
+        if el.get("range"):
+          t.range = _floats(el.get("range"), 2)
+          t.limited = (el.get("limited", "auto") == "true") or (el.get("limited", "auto") == "auto" and self.autolimits)
+        if float(el.get("frictionloss", 0)) != 0 or float(el.get("armature", 0)) != 0:
+          raise NotImplementedError("tendon frictionloss / armature are not supported")
+        spec.tendons.append(t)
+    for bad in ("equality",):
       if root.find(bad) is not None and len(root.find(bad)):
         raise NotImplementedError(f"<{bad}> is not supported by this backend")
     return spec
@@ -498,9 +530,9 @@ class _Parser:
 
   def _parse_actuator(self, el, spec):
     t = el.tag
-    a = ActuatorSpec(name=el.get("name", ""), joint=el.get("joint", ""))
-    if not a.joint:
-      raise NotImplementedError("only joint transmissions are supported")
+    a = ActuatorSpec(name=el.get("name", ""), joint=el.get("joint", ""), tendon=el.get("tendon", ""))
+    if not a.joint and not a.tendon:
+      raise NotImplementedError("only joint and (fixed) tendon transmissions are supported")
     a.gear = _floats(el.get("gear", "1"))[0]
     if el.get("ctrlrange"): a.ctrlrange = _floats(el.get("ctrlrange"), 2)
     if el.get("forcerange"): a.forcerange = _floats(el.get("forcerange"), 2)
@@ -763,16 +795,50 @@ def _compile(spec: Spec) -> HostModel:
   m.actuator_gainprm = np.zeros((nu, 10)); m.actuator_biasprm = np.zeros((nu, 10))
   m.actuator_ctrllimited = np.zeros(nu, np.int32); m.actuator_ctrlrange = np.zeros((nu, 2))
   m.actuator_forcelimited = np.zeros(nu, np.int32); m.actuator_forcerange = np.zeros((nu, 2))
+  # fixed tendons (mjWRAP_JOINT = 1 wraps only)
+  nt = len(spec.tendons)
+  m.ntendon = nt; m.names["tendon"] = [t.name for t in spec.tendons]
+  m.tendon_adr = np.zeros(nt, np.int32); m.tendon_num = np.zeros(nt, np.int32); m.tendon_limited = np.zeros(nt, np.int32)
+  m.tendon_stiffness = np.zeros(nt); m.tendon_damping = np.zeros(nt); m.tendon_lengthspring = np.zeros((nt, 2))
+  m.tendon_range = np.zeros((nt, 2)); m.tendon_length0 = np.zeros(nt)
+  wt, wo, wp = [], [], []
+  for k, t in enumerate(spec.tendons):
+    m.tendon_adr[k] = len(wo); m.tendon_num[k] = len(t.joints)
+    for jname, coef in t.joints:
+      if jname not in jn:
+        raise ValueError(f"tendon {t.name!r}: unknown joint {jname!r}")
+      jid = jn.index(jname)
+      if m.jnt_type[jid] in (0, 1):
+        raise NotImplementedError("fixed tendons over free/ball joints are not supported")
+      wt.append(1); wo.append(jid); wp.append(coef)
+      m.tendon_length0[k] += coef * m.qpos0[m.jnt_qposadr[jid]]
+    m.tendon_stiffness[k], m.tendon_damping[k] = t.stiffness, t.damping
+    sl = list(t.springlength)
+    if sl[0] == -1 and sl[1] == -1:  # springlength -1 (unset): use the length at qpos0 (MuJoCo compiler)
+      sl = [m.tendon_length0[k], m.tendon_length0[k]]
+    m.tendon_lengthspring[k] = sl
+    if t.range is not None:
+      m.tendon_range[k] = t.range
+    m.tendon_limited[k] = int(bool(t.limited))
+  m.nwrap = len(wo)
+  m.wrap_type = np.asarray(wt, np.int32); m.wrap_objid = np.asarray(wo, np.int32); m.wrap_prm = np.asarray(wp, float)
+  m.actuator_trntype = np.zeros(nu, np.int32)
+  tn = m.names["tendon"]
   for k, a in enumerate(spec.actuators):
-    if a.joint not in jn:
-      raise ValueError(f"actuator {a.name!r}: unknown joint {a.joint!r}")
-    jid = jn.index(a.joint)
-    if m.jnt_type[jid] in (0, 1):
-      raise NotImplementedError("actuators on free/ball joints are not supported")
+    if a.tendon:
+      if a.tendon not in tn:
+        raise ValueError(f"actuator {a.name!r}: unknown tendon {a.tendon!r}")
+      jid = tn.index(a.tendon); m.actuator_trntype[k] = 3      # mjTRN_TENDON
+    else:
+      if a.joint not in jn:
+        raise ValueError(f"actuator {a.name!r}: unknown joint {a.joint!r}")
+      jid = jn.index(a.joint)
+      if m.jnt_type[jid] in (0, 1):
+        raise NotImplementedError("actuators on free/ball joints are not supported")
     m.actuator_trnid[k] = [jid, -1]; m.actuator_gaintype[k] = a.gaintype; m.actuator_biastype[k] = a.biastype
     m.actuator_gear[k, 0] = a.gear; m.actuator_gainprm[k, :3] = a.gainprm; m.actuator_biasprm[k, :3] = a.biasprm
     cr = a.ctrlrange
-    if cr is None and a.inheritrange > 0:
+    if cr is None and a.inheritrange > 0 and not a.tendon:
       lo, hi = m.jnt_range[jid]
       mean, rad = 0.5*(lo + hi), 0.5*(hi - lo)*a.inheritrange
       cr = [mean - rad, mean + rad]

@@ -337,6 +337,104 @@ def build_go1(xml_path, terrain="plane", terrain_seed=0) -> HostModel:
 
 
 # ---------------------------------------------------------------------------
+# Asimov-toe (values restated from src/mjlab/asset_zoo/robots/asimov/asimov_toe_constants.py:40-271)
+# ---------------------------------------------------------------------------
+_ASV_WN = 8 * 2.0 * 3.1415926535      # NATURAL_FREQ, 8 Hz (asimov_toe_constants.py:106)
+_ASV_ZETA = 1.8                        # DAMPING_RATIO (:107)
+
+
+def _asv_act(exprs, arm, effort):
+  return ActuatorCfg(tuple(exprs), effort_limit=effort, stiffness=arm * _ASV_WN ** 2,
+                     damping=2.0 * _ASV_ZETA * arm * _ASV_WN, armature=arm)
+
+
+ASIMOV_TOE_ACTUATORS = (
+  _asv_act((".*_hip_pitch_joint",), G1_ARM_7520_14, 55.0),
+  _asv_act((".*_hip_roll_joint",), G1_ARM_7520_22, 90.0),
+  _asv_act((".*_hip_yaw_joint",), G1_ARM_7520_14, 60.0),
+  _asv_act((".*_knee_joint",), G1_ARM_7520_22, 50.0),
+  ActuatorCfg(("left_toe_joint", "right_toe_joint"), effort_limit=5.0, stiffness=50.0, damping=0.8, armature=0.0001),
+)
+_ASV_FOOT = r"^(left|right)_(foot|toe)\d+_collision$"
+ASIMOV_FEET_ONLY_COLLISION = CollisionCfg(
+  geom_names_expr=(_ASV_FOOT,), contype=0, conaffinity=1, condim=3, priority=1, friction=(0.8,))
+ASIMOV_KNEES_BENT = dict(pos=(0.0, 0.0, 0.73), rot=(1.0, 0.0, 0.0, 0.0), joint_pos={
+  "left_hip_pitch_joint": 0.2, "right_hip_pitch_joint": -0.2, ".*_hip_roll_joint": 0.0, ".*_hip_yaw_joint": 0.0,
+  "left_knee_joint": 0.4, "right_knee_joint": -0.4, "left_ankle_pitch_joint": -0.25, "right_ankle_pitch_joint": 0.25,
+  ".*_ankle_roll_joint": 0.0, "left_toe_joint": 0.0, "right_toe_joint": 0.0})
+ASIMOV_ANKLE_L, ASIMOV_ANKLE_D = 0.09, 0.02   # tendon coefficients of asimov_toe.xml:176-196
+
+
+def asimov_action_scale(joint_names) -> np.ndarray:
+  """ASIMOV_ACTION_SCALE (asimov_toe_constants.py:283-297): 0.25 * effort / stiffness per actuated joint."""
+  out = np.zeros(len(joint_names))
+  for c in ASIMOV_TOE_ACTUATORS:
+    for n in filter_names(c.joint_names_expr, tuple(joint_names)):
+      out[list(joint_names).index(n)] = 0.25 * c.effort_limit / c.stiffness
+  return out
+
+
+def ankle_pr_to_tendon(pitch_l, roll_l, pitch_r, roll_r):
+  """AnklePrToTendonAction's linear map (envs/mdp/actions/ankle_ab_action.py): ankle pitch/roll targets ->
+  length targets of the four tendon position actuators [L_A, L_B, R_A, R_B]."""
+  L, D = ASIMOV_ANKLE_L, ASIMOV_ANKLE_D
+  return np.stack([-L * pitch_l - D * roll_l, -L * pitch_l + D * roll_l,
+                   L * pitch_r - D * roll_r, L * pitch_r + D * roll_r], axis=-1)
+
+
+def build_asimov_toe(xml_path, terrain="plane", terrain_seed=0, mesh_collision="drop") -> HostModel:
+  """Compiled model of the fork's Asimov-toe velocity task (tasks/velocity/config/asimov_toe/env_cfgs.py:22-180):
+  4 fixed ankle tendons with tendon position actuators from the XML, then the joint actuators of
+  ASIMOV_ARTICULATION, FEET_ONLY_COLLISION capsules, KNEES_BENT keyframe.
+
+  The XML's link meshes are collision geoms too (class "collision", contype 0 / conaffinity 1: they hit the terrain
+  once the robot has fallen).  Convex-mesh colliders are SURVEY.md §8 row K7 and not built yet, so
+  mesh_collision="drop" clears their conaffinity and records it in meta["dropped_mesh_collision"]."""
+  robot = Spec.from_file(xml_path)
+  dropped = []
+  if mesh_collision == "drop":
+    for g in robot.geoms:
+      if g.type == "mesh" and (g.contype or g.conaffinity):
+        g.contype = g.conaffinity = 0
+        dropped.append(g.name)
+  apply_collision_cfg(robot, ASIMOV_FEET_ONLY_COLLISION)
+  apply_actuator_cfgs(robot, ASIMOV_TOE_ACTUATORS)
+  add_init_state_key(robot, **ASIMOV_KNEES_BENT)
+  # zero-action ctrl of the tendon actuators: AnklePrToTendonAction with the default ankle angles as offset
+  jp = ASIMOV_KNEES_BENT["joint_pos"]
+  ab = ankle_pr_to_tendon(jp["left_ankle_pitch_joint"], jp[".*_ankle_roll_joint"],
+                          jp["right_ankle_pitch_joint"], jp[".*_ankle_roll_joint"])
+  ctrl = robot.keys["init_state"]["ctrl"]
+  for k, n in enumerate(("left_ankle_A", "left_ankle_B", "right_ankle_A", "right_ankle_B")):
+    ctrl[[a.name for a in robot.actuators].index(n)] = float(ab[k])
+  feet = ContactSensorCfg(
+    name="feet_ground_contact",
+    primary=ContactMatch("subtree", r"^(left_ankle_roll_link|right_ankle_roll_link)$", "robot"),
+    secondary=ContactMatch("body", "terrain"), fields=("found", "force"), reduce="netforce", num_slots=1)
+  selfc = ContactSensorCfg(
+    name="self_collision", primary=ContactMatch("subtree", "pelvis_link", "robot"),
+    secondary=ContactMatch("subtree", "pelvis_link", "robot"), fields=("found",), reduce="none", num_slots=1)
+  if terrain == "plane":
+    scene = build_scene({"robot": robot}, sensors=(feet, selfc))
+  else:
+    from . import terrains
+    scene = Spec()
+    terrains.add_rough_terrain(scene, seed=terrain_seed)
+    ent_bodies = {"robot": tuple(b.name for b in robot.bodies[1:]), "robot#geoms": tuple(g.name for g in robot.geoms if g.name)}
+    scene.attach(robot, prefix="robot/")
+    for sc in (feet, selfc):
+      add_contact_sensor(scene, sc, ent_bodies)
+  velocity_sim_options(scene)
+  m = scene.compile()
+  m.meta = dict(task="Mjlab-Velocity-%s-Asimov-Toe" % ("Flat" if terrain == "plane" else "Rough"), nconmax=50, njmax=300,
+                decimation=4, dropped_mesh_collision=dropped)
+  if terrain != "plane":
+    m.meta["terrain_origins"] = np.asarray(scene.terrain_origins).tolist()
+    m.meta["terrain_seed"] = terrain_seed
+  return m
+
+
+# ---------------------------------------------------------------------------
 # model blob (.npz) save / load
 # ---------------------------------------------------------------------------
 _OPT_KEYS = ("timestep", "integrator", "cone", "solver", "iterations", "ls_iterations", "tolerance",
@@ -346,8 +444,8 @@ _OPT_KEYS = ("timestep", "integrator", "cone", "solver", "iterations", "ls_itera
 def save_model(m: HostModel, path) -> None:
   import json
   d = {k: v for k, v in m.__dict__.items() if isinstance(v, np.ndarray)}
-  for k in ("nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nsensor", "nsensordata", "nexclude", "nmocap"):
-    d["_" + k] = np.int64(getattr(m, k))
+  for k in ("nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nsensor", "nsensordata", "nexclude", "nmocap", "ntendon", "nwrap"):
+    d["_" + k] = np.int64(getattr(m, k, 0))
   meta = dict(names=m.names, keys=m.keys, opt={k: getattr(m.opt, k) for k in _OPT_KEYS},
               gravity=list(map(float, m.opt.gravity)), meaninertia=m.stat.meaninertia,
               meta=getattr(m, "meta", {}))

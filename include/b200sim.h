@@ -44,6 +44,7 @@ enum { B2S_SOL_PGS = 0, B2S_SOL_CG = 1, B2S_SOL_NEWTON = 2 };
 enum { B2S_OBJ_UNKNOWN = 0, B2S_OBJ_BODY = 1, B2S_OBJ_XBODY = 2, B2S_OBJ_JOINT = 3, B2S_OBJ_DOF = 4,
        B2S_OBJ_GEOM = 5, B2S_OBJ_SITE = 6, B2S_OBJ_ACTUATOR = 19 };
 enum { B2S_BIAS_NONE = 0, B2S_BIAS_AFFINE = 1 };
+enum { B2S_TRN_JOINT = 0, B2S_TRN_TENDON = 3 };
 enum { B2S_GAIN_FIXED = 0, B2S_GAIN_AFFINE = 1 };
 /* sensor types: own numbering (MuJoCo's mjtSensor values moved between
  * releases); the Python binding maps by NAME from a real MjModel. */
@@ -79,6 +80,8 @@ typedef struct b2s_model_desc {
   int32_t nsensordata;
   int32_t nexclude;
   int32_t nmocap;
+  int32_t ntendon;
+  int32_t nwrap;
   /* options (MjModel.opt; reference MujocoCfg.apply, sim.py:64-76) */
   double opt_timestep;
   double opt_gravity[3];
@@ -156,7 +159,18 @@ typedef struct b2s_model_desc {
   const int32_t* site_bodyid;     /* nsite */
   const double* site_pos;         /* nsite*3 */
   const double* site_quat;        /* nsite*4 */
-  /* actuators (joint transmission only) */
+  /* fixed tendons: length = sum over wraps of wrap_prm * qpos[joint wrap_objid] (mjWRAP_JOINT only) */
+  const int32_t* tendon_adr;           /* ntendon */
+  const int32_t* tendon_num;           /* ntendon */
+  const int32_t* tendon_limited;       /* ntendon */
+  const double* tendon_stiffness;      /* ntendon */
+  const double* tendon_damping;        /* ntendon */
+  const double* tendon_lengthspring;   /* ntendon*2 */
+  const int32_t* wrap_type;            /* nwrap */
+  const int32_t* wrap_objid;           /* nwrap */
+  const double* wrap_prm;              /* nwrap */
+  /* actuators (joint or fixed-tendon transmission) */
+  const int32_t* actuator_trntype;     /* nu */
   const int32_t* actuator_trnid;       /* nu */
   const int32_t* actuator_gaintype;    /* nu */
   const int32_t* actuator_biastype;    /* nu */

@@ -920,13 +920,28 @@ void orc_fwd_velocity(const b2s_model_desc* m, orc_data* d) {
     }
     for (int k = 0; k < 6; k++) d->cvel[6*i + k] = v[k];
   }
-  /* actuator length / velocity (joint transmission; mj_transmission + mj_fwdVelocity) */
+  /* fixed tendons (mj_tendon, mjWRAP_JOINT only): length = sum coef*qpos, velocity = ten_J . qvel */
+  for (int t = 0; t < m->ntendon; t++) {
+    real len = 0, vel = 0;
+    for (int k = m->tendon_adr[t]; k < m->tendon_adr[t] + m->tendon_num[t]; k++) {
+      int j = m->wrap_objid[k];
+      len += (real)m->wrap_prm[k]*d->qpos[m->jnt_qposadr[j]];
+      vel += (real)m->wrap_prm[k]*d->qvel[m->jnt_dofadr[j]];
+    }
+    d->ten_length[t] = len; d->ten_velocity[t] = vel;
+  }
+  /* actuator length / velocity (joint or tendon transmission; mj_transmission + mj_fwdVelocity) */
   for (int u = 0; u < m->nu; u++) {
     int j = m->actuator_trnid[u];
-    d->actuator_length[u] = (real)m->actuator_gear[u]*d->qpos[m->jnt_qposadr[j]];
-    d->actuator_velocity[u] = (real)m->actuator_gear[u]*d->qvel[m->jnt_dofadr[j]];
+    if (m->actuator_trntype[u] == B2S_TRN_TENDON) {
+      d->actuator_length[u] = (real)m->actuator_gear[u]*d->ten_length[j];
+      d->actuator_velocity[u] = (real)m->actuator_gear[u]*d->ten_velocity[j];
+    } else {
+      d->actuator_length[u] = (real)m->actuator_gear[u]*d->qpos[m->jnt_qposadr[j]];
+      d->actuator_velocity[u] = (real)m->actuator_gear[u]*d->qvel[m->jnt_dofadr[j]];
+    }
   }
-  /* mj_passive: joint springs and dampers */
+  /* mj_passive: joint springs and dampers, tendon springs (deadband lengthspring) and dampers */
   for (int i = 0; i < nv; i++) d->qfrc_passive[i] = 0;
   if (!(m->opt_disableflags & B2S_DSBL_PASSIVE)) {
     for (int j = 0; j < m->njnt; j++) {
@@ -937,6 +952,16 @@ void orc_fwd_velocity(const b2s_model_desc* m, orc_data* d) {
       d->qfrc_passive[m->jnt_dofadr[j]] -= k*(d->qpos[qa] - (real)m->qpos_spring[qa]);
     }
     for (int i = 0; i < nv; i++) d->qfrc_passive[i] -= (real)m->dof_damping[i]*d->qvel[i];
+    for (int t = 0; t < m->ntendon; t++) {
+      real k = (real)m->tendon_stiffness[t], b = (real)m->tendon_damping[t], f = 0;
+      if (k == 0 && b == 0) continue;
+      real lo = (real)m->tendon_lengthspring[2*t], hi = (real)m->tendon_lengthspring[2*t + 1];
+      if (d->ten_length[t] > hi) f = k*(hi - d->ten_length[t]);
+      else if (d->ten_length[t] < lo) f = k*(lo - d->ten_length[t]);
+      f -= b*d->ten_velocity[t];
+      for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
+        d->qfrc_passive[m->jnt_dofadr[m->wrap_objid[w]]] += (real)m->wrap_prm[w]*f;
+    }
   }
   /* mj_rne (flg_acc = 0): Coriolis, centrifugal and gravity */
   real* cfrc = (real*)malloc(sizeof(real)*6*nb);
@@ -988,7 +1013,11 @@ void orc_fwd_actuation(const b2s_model_desc* m, orc_data* d) {
     real f = gain*c + bias;
     if (m->actuator_forcelimited[u]) f = clipr(f, (real)m->actuator_forcerange[2*u], (real)m->actuator_forcerange[2*u + 1]);
     d->actuator_force[u] = f;
-    d->qfrc_actuator[m->jnt_dofadr[m->actuator_trnid[u]]] += (real)m->actuator_gear[u]*f;
+    if (m->actuator_trntype[u] == B2S_TRN_TENDON) {   /* moment = gear * ten_J row */
+      int t = m->actuator_trnid[u];
+      for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
+        d->qfrc_actuator[m->jnt_dofadr[m->wrap_objid[w]]] += (real)m->actuator_gear[u]*(real)m->wrap_prm[w]*f;
+    } else d->qfrc_actuator[m->jnt_dofadr[m->actuator_trnid[u]]] += (real)m->actuator_gear[u]*f;
   }
 }
 
@@ -1425,7 +1454,8 @@ void orc_integrate(const b2s_model_desc* m, orc_data* d) {
   real* qa = (real*)malloc(sizeof(real)*(size_t)(3*nv + 2*nv*nv));
   real* rhs = qa + nv; real* dg = rhs + nv; real* A = dg + nv; real* L = A + nv*nv;
   for (int i = 0; i < nv; i++) { rhs[i] = d->qfrc_smooth[i] + d->qfrc_constraint[i]; dg[i] = 0; qa[i] = d->qacc[i]; }
-  int use = 0;
+  int use = 0, ntrm = 0;
+  real* tact = (real*)calloc((size_t)(m->nu + 1), sizeof(real));   /* velocity gain of tendon-borne actuators */
   if (m->opt_integrator == B2S_INT_IMPLICITFAST) {
     /* qDeriv = d qfrc_smooth / d qvel: actuator velocity terms (mjd_actuator_vel) + joint damping (mjd_passive_vel) */
     if (!(m->opt_disableflags & B2S_DSBL_ACTUATION))
@@ -1444,7 +1474,8 @@ void orc_integrate(const b2s_model_desc* m, orc_data* d) {
           if (f <= (real)m->actuator_forcerange[2*u] || f >= (real)m->actuator_forcerange[2*u + 1]) continue;
         }
         real g = (real)m->actuator_gear[u];
-        dg[m->jnt_dofadr[m->actuator_trnid[u]]] += g*g*bv;
+        if (m->actuator_trntype[u] == B2S_TRN_TENDON) { tact[u] = g*g*bv; ntrm++; }
+        else dg[m->jnt_dofadr[m->actuator_trnid[u]]] += g*g*bv;
       }
     if (!(m->opt_disableflags & B2S_DSBL_PASSIVE)) for (int i = 0; i < nv; i++) dg[i] -= (real)m->dof_damping[i];
     use = 1;
@@ -1455,6 +1486,24 @@ void orc_integrate(const b2s_model_desc* m, orc_data* d) {
   if (use) {
     for (int i = 0; i < nv*nv; i++) A[i] = d->qM[i];
     for (int i = 0; i < nv; i++) A[i*nv + i] -= dt*dg[i];
+    if (m->opt_integrator == B2S_INT_IMPLICITFAST && m->ntendon > 0) {
+      /* rank-1 terms moment^T s moment through fixed tendons: actuators in order, then tendon dampers */
+      for (int u = 0; u < m->nu && ntrm; u++) {
+        if (tact[u] == 0) continue;
+        int t = m->actuator_trnid[u];
+        for (int a = m->tendon_adr[t]; a < m->tendon_adr[t] + m->tendon_num[t]; a++)
+          for (int b = m->tendon_adr[t]; b < m->tendon_adr[t] + m->tendon_num[t]; b++)
+            A[m->jnt_dofadr[m->wrap_objid[a]]*nv + m->jnt_dofadr[m->wrap_objid[b]]] -= dt*(tact[u]*(real)m->wrap_prm[a]*(real)m->wrap_prm[b]);
+      }
+      if (!(m->opt_disableflags & B2S_DSBL_PASSIVE))
+        for (int t = 0; t < m->ntendon; t++) {
+          real bd = (real)m->tendon_damping[t];
+          if (bd == 0) continue;
+          for (int a = m->tendon_adr[t]; a < m->tendon_adr[t] + m->tendon_num[t]; a++)
+            for (int b = m->tendon_adr[t]; b < m->tendon_adr[t] + m->tendon_num[t]; b++)
+              A[m->jnt_dofadr[m->wrap_objid[a]]*nv + m->jnt_dofadr[m->wrap_objid[b]]] += dt*(bd*(real)m->wrap_prm[a]*(real)m->wrap_prm[b]);
+        }
+    }
     chol_factor(L, A, nv);
     chol_solve(qa, L, rhs, nv);
   }
@@ -1477,7 +1526,7 @@ void orc_integrate(const b2s_model_desc* m, orc_data* d) {
   }
   d->time[0] += dt;
   for (int i = 0; i < nv; i++) d->qacc_warmstart[i] = d->qacc[i];
-  free(qa);
+  free(qa); free(tact);
 }
 
 /* -------------------------------------------------------------- top level */

@@ -66,6 +66,8 @@ typedef struct orc_data {
   real* subtree_angmom;  /* nbody*3 */
   real* qfrc_bias;       /* nv */
   real* qfrc_passive;    /* nv */
+  real* ten_length;      /* ntendon */
+  real* ten_velocity;    /* ntendon */
   real* actuator_length; /* nu */
   real* actuator_velocity; /* nu */
   real* actuator_force;  /* nu */

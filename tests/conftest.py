@@ -26,6 +26,18 @@ def go1():
 
 
 @pytest.fixture(scope="session")
+def asimov_toe():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("asimov_toe_flat")
+
+
+@pytest.fixture(scope="session")
+def asimov_toe_rough():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("asimov_toe_rough")
+
+
+@pytest.fixture(scope="session")
 def go1_rough():
   from asimov_mjlab_b200 import scenes
   return scenes.load_asset("go1_rough")

@@ -198,6 +198,64 @@ BOX_ON_BOX = """
 """
 
 
+TENDON_SLIDERS = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.005" integrator="implicitfast" gravity="0 0 0"/>
+  <worldbody>
+    <body name="c1" pos="0 0 1">
+      <joint name="s1" type="slide" axis="1 0 0" range="-10 10"/>
+      <geom type="box" size="0.1 0.1 0.1" mass="3.0" contype="0" conaffinity="0"/>
+    </body>
+    <body name="c2" pos="0 1 1">
+      <joint name="s2" type="slide" axis="1 0 0" range="-10 10"/>
+      <geom type="box" size="0.1 0.1 0.1" mass="0.5" contype="0" conaffinity="0"/>
+    </body>
+  </worldbody>
+  <tendon>
+    <fixed name="t" stiffness="20" damping="1.5" springlength="0.05"><joint joint="s1" coef="0.7"/><joint joint="s2" coef="-0.4"/></fixed>
+  </tendon>
+  <actuator>
+    <position name="pd" tendon="t" kp="50" kv="4"/>
+  </actuator>
+</mujoco>
+"""
+
+# Asimov-toe's ankle in miniature: a pitch/roll hinge pair under gravity driven by two fixed tendons with position
+# actuators (one clamped by ctrlrange / forcerange, one with a velocity gain), a sprung + damped third tendon with
+# a dead band, and a joint motor on the same dof (asimov_toe.xml:175-204).
+TENDON_ANKLE = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.005" integrator="implicitfast"/>
+  <worldbody>
+    <body name="shank" pos="0 0 1">
+      <joint name="pitch" axis="0 1 0" range="-0.6 0.6" armature="0.01" damping="0.05"/>
+      <geom type="capsule" fromto="0 0 0 0 0 -0.1" size="0.02" mass="0.3" contype="0" conaffinity="0"/>
+      <body name="foot" pos="0 0 -0.1">
+        <joint name="roll" axis="1 0 0" range="-0.4 0.4" armature="0.01"/>
+        <geom type="box" size="0.1 0.04 0.015" pos="0.03 0 -0.02" mass="0.6" contype="0" conaffinity="0"/>
+        <body name="toe" pos="0.13 0 -0.02">
+          <joint name="toe" axis="0 1 0" range="-0.6 0.1" armature="0.001" stiffness="2" damping="0.02"/>
+          <geom type="box" size="0.03 0.04 0.01" pos="0.03 0 0" mass="0.1" contype="0" conaffinity="0"/>
+        </body>
+      </body>
+    </body>
+  </worldbody>
+  <tendon>
+    <fixed name="A"><joint joint="pitch" coef="-0.09"/><joint joint="roll" coef="-0.02"/></fixed>
+    <fixed name="B"><joint joint="pitch" coef="-0.09"/><joint joint="roll" coef="0.02"/></fixed>
+    <fixed name="C" stiffness="40" damping="0.8" springlength="-0.01 0.02"><joint joint="roll" coef="0.05"/><joint joint="toe" coef="0.1"/></fixed>
+  </tendon>
+  <actuator>
+    <position name="A" tendon="A" kp="300" ctrlrange="-0.08 0.08" forcerange="-12 12"/>
+    <position name="B" tendon="B" kp="300" kv="10"/>
+    <motor name="m" joint="pitch" gear="2"/>
+  </actuator>
+</mujoco>
+"""
+
+
 def compile_xml(xml, contact_sensors=()):
   spec = Spec.from_string(xml)
   for kw in contact_sensors:

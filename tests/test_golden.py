@@ -13,15 +13,16 @@ from oracle import Oracle
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = [("g1_rollout_ls0.npz", "g1", 0, 50, 300, 40, 10), ("g1_rollout_ls1.npz", "g1", 1, 50, 300, 40, 10),
-         ("legged_rollout.npz", "legged", 0, 16, 64, 100, 25), ("go1_flat_rollout_ls1.npz", "go1", 1, 50, 300, 40, 10)]
+         ("legged_rollout.npz", "legged", 0, 16, 64, 100, 25), ("go1_flat_rollout_ls1.npz", "go1", 1, 50, 300, 40, 10),
+         ("asimov_toe_flat_rollout_ls1.npz", "asimov_toe", 1, 50, 300, 8, 4)]
 
 
 def _model(kind, g1):
   if kind == "g1":
     return g1
-  if kind == "go1":
+  if kind in ("go1", "asimov_toe"):
     from asimov_mjlab_b200 import scenes
-    return scenes.load_asset("go1_flat")
+    return scenes.load_asset(kind + "_flat")
   return fx.compile_xml(fx.LEGGED)
 
 

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import fixtures as fx
-from util import contact_pairs, g1_states, legged_states, rough_states
+from util import asimov_states, contact_pairs, g1_states, legged_states, rough_states
 
 pytestmark = pytest.mark.gpu
 
@@ -212,6 +212,95 @@ def test_box_fixture_box_box_and_capsule_box(ls_parallel=True):
       assert _rel_err(D, worlds, "qpos") < 1e-4
   assert (6, 6) in types and (3, 6) in types
   assert _rel_err(D, worlds, "qpos") < 2e-2
+
+
+def test_tendon_fixture_actuation_passive_and_implicit_terms():
+  """K3/K9 on the TENDON_ANKLE fixture: tendon length / velocity, tendon-borne actuator moments with ctrl and force
+  clamps, tendon spring dead band + damper, and the rank-1 implicitfast derivative of the kv actuator and the
+  tendon damper -- forward fields and 50 steps against the oracle."""
+  import torch
+  m = fx.compile_xml(fx.TENDON_ANKLE)
+  W = 32
+  rng = np.random.default_rng(17)
+  qpos = rng.uniform(-0.5, 0.5, (W, m.nq)); qvel = rng.normal(0, 2.0, (W, m.nv))
+  ctrl = np.stack([rng.uniform(-0.15, 0.15, W), rng.uniform(-0.05, 0.05, W), rng.normal(0, 1.0, W)], axis=1)
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=4, njmax=16)
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  _check_counts(D, worlds)
+  assert any(abs(w["actuator_force"][0]) == 12.0 for w in worlds) and any(abs(w["actuator_force"][0]) < 12.0 for w in worlds)
+  for f in ("ten_length", "ten_velocity", "actuator_length", "actuator_velocity", "actuator_force", "qfrc_actuator",
+            "qfrc_passive", "qfrc_smooth", "qacc_smooth", "qacc"):
+    assert _rel_err(D, worlds, f) < 2e-5, f
+  engine.step(M, D)
+  for w in worlds:
+    orc.step(w)
+  assert _rel_err(D, worlds, "qvel") < 1e-5 and _rel_err(D, worlds, "qpos") < 1e-6
+  engine.step(M, D, 50)
+  torch.cuda.synchronize()
+  for w in worlds:
+    orc.step(w, 50)
+  _check_counts(D, worlds)
+  assert _rel_err(D, worlds, "qpos") < 1e-3 and _rel_err(D, worlds, "qvel") < 1e-2
+
+
+def test_asimov_toe_flat_matches_oracle(asimov_toe):
+  """The fork's Asimov-toe velocity scene (tasks/velocity/config/asimov_toe/env_cfgs.py): 4 fixed ankle tendons with
+  tendon position actuators + 10 joint actuators, 20 foot / toe capsules on the plane, subtree contact sensors.
+  The model is chaotic within ~10 steps (saturating toe actuators on ~1e-4 kg m^2), so the oracle drives the
+  trajectory and the device is re-seeded from it every 5 steps; forward() and one step are compared each time."""
+  import torch
+  W = 32
+  qpos, qvel, ctrl = asimov_states(asimov_toe, W, seed=9, spread=0.2, vel=0.3, zlo=0.70, zhi=0.76)
+  engine, M, D, orc, worlds = _setup(asimov_toe, W, qpos, qvel, ctrl, True)
+  ncon_total = 0
+  for chunk in range(8):
+    if chunk:
+      for w in worlds:
+        orc.step(w, 5)
+      for f in ("qpos", "qvel", "qacc_warmstart"):
+        getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+    engine.forward(M, D)
+    for w in worlds:
+      orc.forward(w)
+    _check_counts(D, worlds)
+    ncon_total += sum(int(w["ncon"][0]) for w in worlds)
+    for f in ("ten_length", "ten_velocity", "actuator_length", "actuator_force", "qfrc_actuator", "qfrc_passive",
+              "qfrc_smooth", "geom_xpos", "site_xpos", "subtree_com"):
+      assert _rel_err(D, worlds, f) < 5e-5, f
+    for f in ("qacc_smooth", "qacc", "qfrc_constraint", "sensordata"):
+      assert _rel_err(D, worlds, f) < 2e-3, f
+  assert ncon_total > 200
+  engine.step(M, D)
+  for w in worlds:
+    orc.step(w)
+  _check_counts(D, worlds)
+  assert _rel_err(D, worlds, "qpos") < 1e-5 and _rel_err(D, worlds, "qvel") < 5e-3
+
+
+def test_asimov_toe_rough_box_terrain_matches_oracle(asimov_toe_rough):
+  """Asimov-toe on the default box terrain (capsule-box through the grid broadphase)."""
+  import torch
+  W = 16
+  qpos, qvel, ctrl = rough_states(asimov_toe_rough, W, seed=13, spread=0.1, vel=0.2, drop=(0.0, 0.03))
+  c0 = np.array(asimov_toe_rough.keys["robot/init_state"]["ctrl"])
+  ctrl = c0 + 0.25 * (ctrl - c0)
+  engine, M, D, orc, worlds = _setup(asimov_toe_rough, W, qpos, qvel, ctrl, True)
+  ncon_total = 0
+  for chunk in range(6):
+    for w in worlds:
+      orc.step(w, 5)
+    for f in ("qpos", "qvel", "qacc_warmstart"):
+      getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+    engine.forward(M, D)
+    for w in worlds:
+      orc.forward(w)
+    _check_counts(D, worlds)
+    ncon_total += sum(int(w["ncon"][0]) for w in worlds)
+    for f in ("geom_xpos", "qacc", "sensordata", "qfrc_constraint", "actuator_force"):
+      assert _rel_err(D, worlds, f) < 2e-3, f
+  assert ncon_total > 100
 
 
 def test_g1_friction_domain_randomisation_per_world(g1):

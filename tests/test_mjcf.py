@@ -103,9 +103,33 @@ def test_defaults_classes_degrees_and_limits():
 
 def test_unsupported_mjcf_raises():
   with pytest.raises(NotImplementedError):
-    Spec.from_string("<mujoco><tendon><fixed name='t'/></tendon></mujoco>")
+    Spec.from_string("<mujoco><tendon><spatial name='t'/></tendon></mujoco>")
   with pytest.raises(NotImplementedError):
     Spec.from_string("<mujoco><worldbody><body><geom type='mesh' mesh='m'/></body></worldbody></mujoco>").compile()
+
+
+def test_fixed_tendon_and_tendon_actuator_compile():
+  """asimov_toe.xml:175-204: <fixed> tendons over two hinges, <position tendon=...> actuators."""
+  xml = """<mujoco><compiler angle="radian"/>
+    <worldbody><body name="a" pos="0 0 1"><joint name="p" axis="0 1 0"/><geom type="sphere" size="0.1"/>
+      <body name="b" pos="0 0 -0.2"><joint name="r" axis="1 0 0"/><geom type="sphere" size="0.05"/></body></body></worldbody>
+    <tendon>
+      <fixed name="A"><joint joint="p" coef="-0.09"/><joint joint="r" coef="-0.02"/></fixed>
+      <fixed name="B" stiffness="3" damping="0.5"><joint joint="p" coef="-0.09"/><joint joint="r" coef="0.02"/></fixed>
+    </tendon>
+    <actuator>
+      <position name="A" tendon="A" kp="300" ctrlrange="-0.08 0.08" forcerange="-72 72"/>
+      <position name="B" tendon="B" kp="300" kv="2"/>
+      <motor name="m" joint="p"/>
+    </actuator></mujoco>"""
+  m = Spec.from_string(xml).compile()
+  assert (m.ntendon, m.nwrap) == (2, 4)
+  assert m.tendon_adr.tolist() == [0, 2] and m.tendon_num.tolist() == [2, 2]
+  assert m.wrap_objid.tolist() == [0, 1, 0, 1] and np.allclose(m.wrap_prm, [-0.09, -0.02, -0.09, 0.02])
+  assert m.tendon_stiffness.tolist() == [0.0, 3.0] and m.tendon_damping.tolist() == [0.0, 0.5]
+  assert m.actuator_trntype.tolist() == [3, 3, 0] and m.actuator_trnid[:, 0].tolist() == [0, 1, 0]
+  assert np.allclose(m.actuator_biasprm[1][:3], [0, -300, -2])
+  assert m.actuator_ctrllimited.tolist() == [1, 0, 0] and m.actuator_forcelimited.tolist() == [1, 0, 0]
 
 
 def test_model_blob_round_trip(tmp_path, g1):

@@ -70,6 +70,51 @@ def test_pd_actuator_one_implicitfast_step_closed_form():
   assert w["qpos"][0] == pytest.approx(q0 + dt * (v0 + dt * a_impl), rel=1e-12)
 
 
+def test_fixed_tendon_actuator_spring_damper_closed_form():
+  """K3/K9: fixed tendon length/velocity, tendon position actuator, tendon spring + damper, and the implicitfast
+  rank-1 velocity derivative c c^T (kv + b) -- one step against the closed form."""
+  m = fx.compile_xml(fx.TENDON_SLIDERS)
+  orc = Oracle(m, "f64")
+  q = np.array([0.1, -0.2]); v = np.array([-0.3, 0.5]); u = 0.25
+  w = orc.new_world(qpos=q, qvel=v, ctrl=[u])
+  orc.step(w)
+  c = np.array([0.7, -0.4]); M = np.diag([3.0, 0.5]); kp, kv, ks, kb, l0, dt = 50.0, 4.0, 20.0, 1.5, 0.05, 0.005
+  length, vel = c @ q, c @ v
+  assert w["ten_length"][0] == pytest.approx(length) and w["ten_velocity"][0] == pytest.approx(vel)
+  assert w["actuator_length"][0] == pytest.approx(length) and w["actuator_velocity"][0] == pytest.approx(vel)
+  f_act = kp * (u - length) - kv * vel
+  f_pas = ks * (l0 - length) - kb * vel
+  assert w["actuator_force"][0] == pytest.approx(f_act)
+  assert np.allclose(w["qfrc_actuator"], c * f_act) and np.allclose(w["qfrc_passive"], c * f_pas)
+  rhs = c * (f_act + f_pas)
+  assert np.allclose(w["qacc"], np.linalg.solve(M, rhs))
+  a_impl = np.linalg.solve(M + dt * (kv + kb) * np.outer(c, c), rhs)
+  assert np.allclose(w["qvel"], v + dt * a_impl, rtol=1e-12, atol=0)
+  assert np.allclose(w["qpos"], q + dt * (v + dt * a_impl), rtol=1e-12, atol=0)
+
+
+def test_tendon_spring_dead_band_and_clamped_actuator():
+  m = fx.compile_xml(fx.TENDON_ANKLE)
+  assert np.allclose(m.tendon_lengthspring[2], [-0.01, 0.02])
+  orc = Oracle(m, "f64")
+  # tendon C = 0.05 roll + 0.1 toe: inside the dead band -> spring silent, damper only
+  w = orc.forward(orc.new_world(qpos=[0.1, 0.2, 0.0], qvel=[0, 0, 1.0], ctrl=[0, 0, 0]))
+  assert w["ten_length"][2] == pytest.approx(0.01)
+  assert w["qfrc_passive"][1] == pytest.approx(0.05 * (-0.8 * 0.1))
+  # above the band: pulls back towards the upper edge
+  w = orc.forward(orc.new_world(qpos=[0.1, 0.4, 0.05], qvel=[0, 0, 0], ctrl=[0, 0, 0]))
+  assert w["qfrc_passive"][1] == pytest.approx(0.05 * 40 * (0.02 - 0.025))
+  # actuator A: ctrl clamped to 0.08, then force clamped to 12; moment = tendon coefficients
+  w = orc.forward(orc.new_world(qpos=[0.3, 0.1, 0.0], qvel=[0, 0, 0], ctrl=[0.5, 0.0, 0.0]))
+  la = -0.09 * 0.3 - 0.02 * 0.1
+  assert 300 * (0.08 - la) > 12 and w["actuator_force"][0] == pytest.approx(12.0)
+  lb = -0.09 * 0.3 + 0.02 * 0.1
+  fb = 300 * (0.0 - lb)
+  assert w["actuator_force"][1] == pytest.approx(fb)
+  assert w["qfrc_actuator"][0] == pytest.approx(-0.09 * 12.0 - 0.09 * fb)
+  assert w["qfrc_actuator"][1] == pytest.approx(-0.02 * 12.0 + 0.02 * fb)
+
+
 def test_two_sphere_contact_geometry():
   m = fx.compile_xml(fx.TWO_SPHERES)
   orc = Oracle(m, "f64")

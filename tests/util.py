@@ -33,6 +33,16 @@ def legged_states(m, nworld, seed=0, spread=0.3, vel=0.5, zlo=None, zhi=None):
   return g1_states(m, nworld, seed, spread, vel, z0 - 0.03 if zlo is None else zlo, z0 + 0.07 if zhi is None else zhi)
 
 
+def asimov_states(m, nworld, seed=0, spread=0.2, vel=0.3, zlo=0.70, zhi=0.76):
+  """Asimov-toe: like legged_states; the ctrl noise of the four tendon position actuators (length targets in metres,
+  ctrlrange +-0.08) is scaled down so that some worlds sit inside the ctrl and force clamps and some outside."""
+  qpos, qvel, ctrl = legged_states(m, nworld, seed, spread, vel, zlo, zhi)
+  c0 = np.array(m.keys["robot/init_state"]["ctrl"])
+  tend = np.asarray(m.actuator_trntype) == 3
+  ctrl[:, tend] = c0[tend] + 0.25 * (ctrl[:, tend] - c0[tend])
+  return qpos, qvel, ctrl
+
+
 def rough_states(m, nworld, seed=0, spread=0.2, vel=0.3, drop=(0.0, 0.08), tumble=0.0):
   """Go1 on the box terrain: worlds spawn at the generator's terrain origins (all difficulty rows, flat / stairs /
   inverted-stairs columns) with a random xy offset (so feet land on step edges), a small drop height and tilt."""

@@ -20,3 +20,10 @@ for terr in ("plane", "rough"):
   scenes.save_model(g, os.path.join(scenes.ASSET_DIR, name + ".npz"))
   print(name, ": nq", g.nq, "nv", g.nv, "nu", g.nu, "nbody", g.nbody, "ngeom", g.ngeom,
         "nsite", g.nsite, "nsensordata", g.nsensordata, "meaninertia", g.stat.meaninertia)
+
+for terr in ("plane", "rough"):
+  a = scenes.build_asimov_toe(os.path.join(zoo, "asimov/xmls/asimov_toe.xml"), terrain=terr)
+  name = "asimov_toe_flat" if terr == "plane" else "asimov_toe_rough"
+  scenes.save_model(a, os.path.join(scenes.ASSET_DIR, name + ".npz"))
+  print(name, ": nq", a.nq, "nv", a.nv, "nu", a.nu, "nbody", a.nbody, "ngeom", a.ngeom, "ntendon", a.ntendon,
+        "nsensordata", a.nsensordata, "meaninertia", a.stat.meaninertia)

@@ -14,7 +14,7 @@ import numpy as np
 import fixtures as fx
 from asimov_mjlab_b200 import scenes
 from oracle import Oracle
-from util import g1_states, legged_states
+from util import asimov_states, g1_states, legged_states
 
 OUT = os.path.join(ROOT, "tests", "golden")
 os.makedirs(OUT, exist_ok=True)
@@ -46,6 +46,13 @@ go1 = scenes.load_asset("go1_flat")
 qpos, qvel, ctrl = legged_states(go1, 4, seed=22, spread=0.1, vel=0.1, zlo=0.26, zhi=0.29)
 r = record(go1, qpos, qvel, ctrl, 40, 10, 50, 300, 1)
 np.savez_compressed(os.path.join(OUT, "go1_flat_rollout_ls1.npz"), qpos0=qpos, qvel0=qvel, ctrl0=ctrl, **r)
+asv = scenes.load_asset("asimov_toe_flat")
+# short horizon: saturating toe actuators (5 Nm on ~1.5e-4 kg m^2) make this model chaotic within ~10 steps
+qpos, qvel, ctrl = asimov_states(asv, 4, seed=23, spread=0.05, vel=0.1, zlo=0.725, zhi=0.75)
+c0 = np.array(asv.keys["robot/init_state"]["ctrl"])
+ctrl = c0 + 0.2 * (ctrl - c0)
+r = record(asv, qpos, qvel, ctrl, 8, 4, 50, 300, 1)
+np.savez_compressed(os.path.join(OUT, "asimov_toe_flat_rollout_ls1.npz"), qpos0=qpos, qvel0=qvel, ctrl0=ctrl, **r)
 m = fx.compile_xml(fx.LEGGED)
 rng = np.random.default_rng(3)
 qpos = np.tile(m.qpos0, (3, 1)); qpos[:, 2] = [0.3, 0.33, 0.36]
