@@ -102,6 +102,14 @@ bool pair_supported(int t1, int t2) {
   if (t1 == B2S_GEOM_BOX) return t2 == B2S_GEOM_BOX;
   return false;
 }
+// most contacts the narrowphase returns for a (type-ordered) pair
+int pair_max_contacts(int t1, int t2) {
+  if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) return 8;
+  if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_BOX) return 4;
+  if (t2 == B2S_GEOM_CAPSULE && (t1 == B2S_GEOM_PLANE || t1 == B2S_GEOM_CAPSULE)) return 2;
+  if (t1 == B2S_GEOM_CAPSULE && t2 == B2S_GEOM_BOX) return 2;
+  return 1;
+}
 // host-side pose algebra for the static-geom grid (double precision)
 void hq_mul(double* r, const double* a, const double* b) {
   r[0] = a[0]*b[0] - a[1]*b[1] - a[2]*b[2] - a[3]*b[3]; r[1] = a[0]*b[1] + a[1]*b[0] + a[2]*b[3] - a[3]*b[2];
@@ -260,6 +268,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   }
   // ---------------------------------------------------------------- static collision pair table
   std::vector<int> pairs;
+  int col_maxc = 1;          // most contacts one geom pair of this model can produce: picks the narrowphase variant
   for (int ga = 0; ga < s->ngeom; ga++) for (int gb = ga + 1; gb < s->ngeom; gb++) {
     if (in_grid[ga] || in_grid[gb]) continue;      // found through the grid at run time
     const int b1 = s->geom_bodyid[ga], b2 = s->geom_bodyid[gb];
@@ -280,7 +289,14 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       return fail(std::string("unsupported collision pair ") + geom_name(s->geom_type[g1]) + "-" + geom_name(s->geom_type[g2]) +
                   " (geoms " + std::to_string(g1) + ", " + std::to_string(g2) + ")");
     pairs.push_back(g1); pairs.push_back(g2);
+    col_maxc = std::max(col_maxc, pair_max_contacts(s->geom_type[g1], s->geom_type[g2]));
   }
+  if (use_grid)   // grid pairs: every dynamic geom against every geom type present in the grid
+    for (int ga : dyn_geoms) for (int gb : grid_geoms) {
+      if (!((s->geom_contype[ga] & s->geom_conaffinity[gb]) || (s->geom_contype[gb] & s->geom_conaffinity[ga]))) continue;
+      const int t1 = std::min(s->geom_type[ga], s->geom_type[gb]), t2 = std::max(s->geom_type[ga], s->geom_type[gb]);
+      col_maxc = std::max(col_maxc, pair_max_contacts(t1, t2));
+    }
   // ---------------------------------------------------------------- traversal tables
   int nlevel = 0;
   for (int i = 0; i < nb; i++) nlevel = depth[i] + 1 > nlevel ? depth[i] + 1 : nlevel;
@@ -350,6 +366,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     d.pose_geom = up.raw(pg); d.pose_site = up.raw(ps); d.stat_geom = up.raw(sg); d.stat_site = up.raw(ss);
   }
   d.geom_contype = up.i(s->geom_contype, s->ngeom); d.geom_conaffinity = up.i(s->geom_conaffinity, s->ngeom);
+  d.col_maxc = col_maxc <= 2 ? 2 : (col_maxc <= 4 ? 4 : 8);
   d.ngrid = use_grid ? (int)grid_geoms.size() : 0;
   d.ndyngeom = (int)dyn_geoms.size(); d.dyn_geom = up.raw(dyn_geoms);
   d.grid_nx = grid_nx; d.grid_ny = grid_ny; d.grid_x0 = (float)grid_x0; d.grid_y0 = (float)grid_y0;
@@ -608,7 +625,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   if (rc || cudaGetLastError() != cudaSuccess) { delete D; return fail("initialising the data arena failed"); }
   // raise the dynamic shared-memory limit of every stage once
   struct { const void* fn; size_t smem; } st[] = {
-    {fn_position(), smem_position(md)}, {fn_dynamics(md), smem_dynamics(md)}, {fn_collision(), smem_collision(md)},
+    {fn_position(), smem_position(md)}, {fn_dynamics(md), smem_dynamics(md)}, {fn_collision(md), smem_collision(md)},
     {fn_constraint(), smem_constraint(md)}, {fn_solve(md), smem_solve(md, d)}, {fn_sensors(), smem_sensors(md)},
     {fn_integrate(md), smem_integrate(md)}};
   for (auto& e : st) {

@@ -21,7 +21,7 @@ void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st);
 // so the host can raise cudaFuncAttributeMaxDynamicSharedMemorySize once per model.
 size_t smem_position(const ModelDev& m);  const void* fn_position();
 size_t smem_dynamics(const ModelDev& m);  const void* fn_dynamics(const ModelDev& m);
-size_t smem_collision(const ModelDev& m); const void* fn_collision();
+size_t smem_collision(const ModelDev& m); const void* fn_collision(const ModelDev& m);
 size_t smem_constraint(const ModelDev& m); const void* fn_constraint();
 size_t smem_solve(const ModelDev& m, const DataDev& d); const void* fn_solve(const ModelDev& m);
 size_t smem_sensors(const ModelDev& m);   const void* fn_sensors();

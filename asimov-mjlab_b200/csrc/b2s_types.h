@@ -67,6 +67,7 @@ struct ModelDev {
   const int *site_bodyid;
   WField<float> site_pos, site_quat;
   // ---- fixed tendons (wraps flattened to dof / qpos addresses) and actuators
+  int col_maxc;      // narrowphase variant: most contacts per geom pair (2, 4 or 8)
   int ntendon, nwrap;
   const int *tendon_adr, *tendon_num, *wrap_dof, *wrap_qpos;
   const float *wrap_coef, *tendon_stiffness, *tendon_damping, *tendon_lengthspring;

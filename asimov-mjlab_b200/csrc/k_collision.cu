@@ -284,6 +284,9 @@ DEV int box_box(RawCon* c, float margin, v3 p1, const m33& M1, v3 S1, v3 p2, con
   return n;
 }
 
+// MAXC = most contacts one pair of this model can produce (put_model picks 2 / 4 / 8): the contact scratch stays in
+// registers for sphere / capsule robots and the box colliders are compiled out where no box pair exists
+template <int MAXC>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
@@ -374,7 +377,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   const int cmax = d.nconmax;
   for (int base = 0; base < nsurv; base += 32) {
     const int i = base + lane;
-    RawCon rc[8];
+    RawCon rc[MAXC];
     int n = 0, g1 = 0, g2 = 0;
     float margin = 0.f;
     if (i < nsurv) {
@@ -388,7 +391,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       if (t1 == B2S_GEOM_PLANE) {
         if (t2 == B2S_GEOM_SPHERE) n = plane_sphere(rc, margin, p1, col(m1, 2), p2, s2.x);
         else if (t2 == B2S_GEOM_CAPSULE) n = plane_capsule(rc, margin, p1, m1, p2, m2, s2);
-        else if (t2 == B2S_GEOM_BOX) n = plane_box(rc, margin, p1, m1, p2, m2, s2);
+        else if (t2 == B2S_GEOM_BOX) { if constexpr (MAXC >= 4) n = plane_box(rc, margin, p1, m1, p2, m2, s2); }
       } else if (t1 == B2S_GEOM_SPHERE) {
         if (t2 == B2S_GEOM_SPHERE) n = sphere_sphere(rc, margin, p1, s1.x, p2, s2.x);
         else if (t2 == B2S_GEOM_CAPSULE) n = sphere_capsule(rc, margin, p1, s1, p2, m2, s2);
@@ -396,7 +399,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       } else if (t1 == B2S_GEOM_CAPSULE) {
         if (t2 == B2S_GEOM_CAPSULE) n = capsule_capsule(rc, margin, p1, m1, s1, p2, m2, s2);
         else if (t2 == B2S_GEOM_BOX) n = capsule_box(rc, margin, p1, m1, s1, p2, m2, s2);
-      } else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) n = box_box(rc, margin, p1, m1, s1, p2, m2, s2);
+      } else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) { if constexpr (MAXC >= 8) n = box_box(rc, margin, p1, m1, s1, p2, m2, s2); }
     }
     int total;
     const int excl = warp_excl_scan(n, lane, &total);
@@ -427,7 +430,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       }
       f0 = fmaxf(f0, B2S_MINMU); f1 = fmaxf(f1, B2S_MINMU); f2 = fmaxf(f2, B2S_MINMU);
       const float gap = fmaxf(m.geom_gap[g1], m.geom_gap[g2]);
-      for (int k = 0; k < n; k++) {
+#pragma unroll
+      for (int k = 0; k < MAXC; k++) {
+        if (k >= n) break;
         const int c = ncon + excl + k;
         if (c >= cmax) break;
         const size_t o = (size_t)w * cmax + c;
@@ -447,10 +452,20 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   if (lane == 0) d.ncon[w] = min(ncon, cmax);
 }
 
+#define COL_DISPATCH(M, EXPR)                                   \
+  switch ((M).col_maxc) {                                       \
+    case 2: { constexpr int MAXC = 2; EXPR; } break;            \
+    case 4: { constexpr int MAXC = 4; EXPR; } break;            \
+    default: { constexpr int MAXC = 8; EXPR; } break;           \
+  }
 void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
-  k_collision<<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
+  COL_DISPATCH(m, (k_collision<MAXC><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
   b2s_count_launch();
 }
 size_t smem_collision(const ModelDev&) { return (size_t)B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1) * sizeof(int); }
-const void* fn_collision() { return (const void*)k_collision; }
+const void* fn_collision(const ModelDev& m) {
+  const void* f = nullptr;
+  COL_DISPATCH(m, (f = (const void*)k_collision<MAXC>));
+  return f;
+}

@@ -26,6 +26,8 @@ ALG_BYTES_PER_SUBSTEP_WORLD = 5268  # 4 B x (363 in + 747 out 
 WORKLOADS = {
   "g1_flat": ("g1_flat", "Mjlab-Velocity-Flat-Unitree-G1 physics step, random actions (BASELINE.json configs[1])"),
   "go1_flat": ("go1_flat", "Mjlab-Velocity-Flat-Unitree-Go1 physics step, random actions"),
+  "asimov_toe_flat": ("asimov_toe_flat", "Asimov-toe velocity task physics step on the plane (fixed ankle tendons + tendon position actuators; mesh collision geoms dropped), random actions"),
+  "asimov_toe_rough": ("asimov_toe_rough", "Asimov-toe velocity task physics step on the reference's default box terrain, random actions"),
   "go1_rough": ("go1_rough", "Mjlab-Velocity-Rough-Unitree-Go1 physics step on the reference's default box terrain, random actions (BASELINE.json configs[2], box variant)"),
 }
 
@@ -114,9 +116,19 @@ def action_targets(m, n_batches, envs, seed, device=None):
   from asimov_mjlab_b200 import scenes
   key = m.keys["robot/init_state"]
   jn = [n.split("/")[-1] for n in m.names["actuator"]]
-  scale = scenes.g1_action_scale(jn) if m.nu == 29 else scenes.go1_action_scale(jn)
   rng = np.random.default_rng(seed)
   a = rng.uniform(-1.0, 1.0, size=(n_batches, envs, m.nu)).astype(np.float32)
+  if getattr(m, "ntendon", 0):
+    # Asimov-toe (env_cfgs.py:136-160): joint_pos action on hips / knees / toes... and ankle_ab on the 4 tendon
+    # actuators = AnklePrToTendonAction(default ankle angles + 1.0 * a) (its scale dict has no ankle entry -> 1.0)
+    scale = scenes.asimov_action_scale(jn)
+    ctrl = np.asarray(key["ctrl"], np.float32)[None, None, :] + scale.astype(np.float32)[None, None, :] * a
+    jp = scenes.ASIMOV_KNEES_BENT["joint_pos"]
+    ab = scenes.ankle_pr_to_tendon(jp["left_ankle_pitch_joint"] + a[..., 0], a[..., 1], jp["right_ankle_pitch_joint"] + a[..., 2], a[..., 3])
+    for k, n in enumerate(("left_ankle_A", "left_ankle_B", "right_ankle_A", "right_ankle_B")):
+      ctrl[..., jn.index(n)] = ab[..., k]
+    return ctrl.astype(np.float32)
+  scale = scenes.g1_action_scale(jn) if m.nu == 29 else scenes.go1_action_scale(jn)
   return (np.asarray(key["ctrl"], np.float32)[None, None, :] + scale.astype(np.float32)[None, None, :] * a)
 
 
@@ -188,7 +200,7 @@ def run_b200(args):
   # foot-friction domain randomisation ON (per-world Model reads stay honest; velocity_env_cfg.py:230-240)
   sim.expand_model_fields(("geom_friction",))
   g = torch.Generator(device="cpu").manual_seed(rank)
-  foot = [i for i, n in enumerate(m.names["geom"]) if "foot" in n and n.endswith("_collision")]
+  foot = [i for i, n in enumerate(m.names["geom"]) if ("foot" in n or "_toe" in n) and n.endswith("_collision")]
   fr = 0.3 + 0.9 * torch.rand(E, len(foot), generator=g)
   M.geom_friction[:, foot, 0] = fr.to(dev)
   n0 = engine.launch_count()
@@ -197,6 +209,7 @@ def run_b200(args):
   assert engine.launch_count() - n0 >= per_graph["decimation"]
   key = m.keys["robot/init_state"]
   q0 = torch.tensor(key["qpos"], dtype=torch.float32, device=dev)
+  c0 = torch.tensor(key["ctrl"], dtype=torch.float32, device=dev)
   nbatch = 64
   ctrl_pool = torch.as_tensor(action_targets(m, nbatch, E, seed=1000 + rank), device=dev)
   origins = torch.zeros(E, 3, device=dev)
@@ -218,7 +231,7 @@ def run_b200(args):
     D.qpos[:, 0:3] += origins
     D.qpos[:, 7:] += noise
     D.qvel.zero_(); D.qacc_warmstart.zero_(); D.time.zero_()
-    D.ctrl[:] = q0[7:]
+    D.ctrl[:] = c0
     sim.forward()
 
   def one_step(i):
