@@ -95,15 +95,22 @@ const char* geom_name(int t) {
   static const char* n[] = {"plane", "hfield", "sphere", "capsule", "ellipsoid", "cylinder", "box", "mesh"};
   return (t >= 0 && t < 8) ? n[t] : "?";
 }
+bool convex_core(int t) { return t == B2S_GEOM_SPHERE || t == B2S_GEOM_CAPSULE || t == B2S_GEOM_BOX || t == B2S_GEOM_MESH; }
 bool pair_supported(int t1, int t2) {
-  if (t1 == B2S_GEOM_PLANE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
+  if (t1 == B2S_GEOM_PLANE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX || t2 == B2S_GEOM_MESH;
+  if (t1 == B2S_GEOM_HFIELD) return convex_core(t2);
+  if (t2 == B2S_GEOM_MESH) return convex_core(t1);
   if (t1 == B2S_GEOM_SPHERE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
   if (t1 == B2S_GEOM_CAPSULE) return t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
   if (t1 == B2S_GEOM_BOX) return t2 == B2S_GEOM_BOX;
   return false;
 }
+// pairs that go through the GJK/EPA, plane-mesh or height-field colliders (k_convex.cuh)
+bool pair_convex(int t1, int t2) { return t1 == B2S_GEOM_HFIELD || t2 == B2S_GEOM_MESH; }
 // most contacts the narrowphase returns for a (type-ordered) pair
 int pair_max_contacts(int t1, int t2) {
+  if (t1 == B2S_GEOM_HFIELD) return 8;
+  if (t2 == B2S_GEOM_MESH) return t1 == B2S_GEOM_PLANE ? 4 : 1;
   if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) return 8;
   if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_BOX) return 4;
   if (t2 == B2S_GEOM_CAPSULE && (t1 == B2S_GEOM_PLANE || t1 == B2S_GEOM_CAPSULE)) return 2;
@@ -146,6 +153,20 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   for (int j = 0; j < s->njnt; j++) {
     if (s->jnt_type[j] < 0 || s->jnt_type[j] > 3) return fail("unknown joint type");
     if (s->jnt_type[j] == B2S_JNT_BALL && s->jnt_limited[j]) return fail("ball joint limits are not supported");
+  }
+  for (int g = 0; g < s->ngeom; g++) {
+    const bool collides = (s->geom_contype[g] | s->geom_conaffinity[g]) != 0;
+    if (s->geom_type[g] == B2S_GEOM_MESH && collides) {
+      const int id = s->geom_dataid[g];
+      if (id < 0 || id >= s->nmesh || s->mesh_vertnum[id] < 1 || s->mesh_vertadr[id] < 0 || s->mesh_vertadr[id] + s->mesh_vertnum[id] > s->nmeshvert)
+        return fail("colliding mesh geom " + std::to_string(g) + " has no convex-hull vertices (geom_dataid / mesh_vert)");
+    }
+    if (s->geom_type[g] == B2S_GEOM_HFIELD && collides) {
+      const int id = s->geom_dataid[g];
+      if (id < 0 || id >= s->nhfield || s->hfield_nrow[id] < 2 || s->hfield_ncol[id] < 2 ||
+          s->hfield_adr[id] < 0 || s->hfield_adr[id] + s->hfield_nrow[id] * s->hfield_ncol[id] > s->nhfielddata)
+        return fail("height-field geom " + std::to_string(g) + " has no elevation data");
+    }
   }
   if (s->ntendon < 0 || s->nwrap < 0) return fail("negative tendon sizes");
   for (int t = 0; t < s->ntendon; t++) {
@@ -230,8 +251,16 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       hq_mat(Rg, qg);
       const double* sz = s->geom_size + 3*g;
       double h[3];
+      double hfs[3] = {0, 0, 0};
+      if (s->geom_type[g] == B2S_GEOM_HFIELD) {       // box [-sx,sx] x [-sy,sy] x [-base, top] in the field's frame
+        const double* hs = s->hfield_size + 4*s->geom_dataid[g];
+        const double zc = 0.5*(hs[2] - hs[3]);
+        for (int a = 0; a < 3; a++) c[a] += Rg[3*a+2]*zc;
+        hfs[0] = hs[0]; hfs[1] = hs[1]; hfs[2] = 0.5*(hs[2] + hs[3]);
+      }
       for (int a = 0; a < 3; a++) {
-        if (s->geom_type[g] == B2S_GEOM_BOX) h[a] = std::fabs(Rg[3*a])*sz[0] + std::fabs(Rg[3*a+1])*sz[1] + std::fabs(Rg[3*a+2])*sz[2];
+        if (s->geom_type[g] == B2S_GEOM_HFIELD) h[a] = std::fabs(Rg[3*a])*hfs[0] + std::fabs(Rg[3*a+1])*hfs[1] + std::fabs(Rg[3*a+2])*hfs[2];
+        else if (s->geom_type[g] == B2S_GEOM_BOX) h[a] = std::fabs(Rg[3*a])*sz[0] + std::fabs(Rg[3*a+1])*sz[1] + std::fabs(Rg[3*a+2])*sz[2];
         else if (s->geom_type[g] == B2S_GEOM_SPHERE) h[a] = sz[0];
         else if (s->geom_type[g] == B2S_GEOM_CAPSULE) h[a] = std::fabs(Rg[3*a+2])*sz[1] + sz[0];
         else h[a] = s->geom_rbound[g];
@@ -268,6 +297,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   }
   // ---------------------------------------------------------------- static collision pair table
   std::vector<int> pairs;
+  int col_convex = 0;
   int col_maxc = 1;          // most contacts one geom pair of this model can produce: picks the narrowphase variant
   for (int ga = 0; ga < s->ngeom; ga++) for (int gb = ga + 1; gb < s->ngeom; gb++) {
     if (in_grid[ga] || in_grid[gb]) continue;      // found through the grid at run time
@@ -290,12 +320,14 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
                   " (geoms " + std::to_string(g1) + ", " + std::to_string(g2) + ")");
     pairs.push_back(g1); pairs.push_back(g2);
     col_maxc = std::max(col_maxc, pair_max_contacts(s->geom_type[g1], s->geom_type[g2]));
+    col_convex |= pair_convex(s->geom_type[g1], s->geom_type[g2]) ? 1 : 0;
   }
   if (use_grid)   // grid pairs: every dynamic geom against every geom type present in the grid
     for (int ga : dyn_geoms) for (int gb : grid_geoms) {
       if (!((s->geom_contype[ga] & s->geom_conaffinity[gb]) || (s->geom_contype[gb] & s->geom_conaffinity[ga]))) continue;
       const int t1 = std::min(s->geom_type[ga], s->geom_type[gb]), t2 = std::max(s->geom_type[ga], s->geom_type[gb]);
       col_maxc = std::max(col_maxc, pair_max_contacts(t1, t2));
+      col_convex |= pair_convex(t1, t2) ? 1 : 0;
     }
   // ---------------------------------------------------------------- traversal tables
   int nlevel = 0;
@@ -367,6 +399,12 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   }
   d.geom_contype = up.i(s->geom_contype, s->ngeom); d.geom_conaffinity = up.i(s->geom_conaffinity, s->ngeom);
   d.col_maxc = col_maxc <= 2 ? 2 : (col_maxc <= 4 ? 4 : 8);
+  d.col_convex = col_convex;
+  d.geom_dataid = up.i(s->geom_dataid, s->ngeom);
+  d.mesh_vertadr = up.i(s->mesh_vertadr, s->nmesh); d.mesh_vertnum = up.i(s->mesh_vertnum, s->nmesh);
+  d.mesh_vert = up.f(s->mesh_vert, 3LL * s->nmeshvert);
+  d.hfield_size = up.f(s->hfield_size, 4LL * s->nhfield); d.hfield_data = up.f(s->hfield_data, s->nhfielddata);
+  d.hfield_nrow = up.i(s->hfield_nrow, s->nhfield); d.hfield_ncol = up.i(s->hfield_ncol, s->nhfield); d.hfield_adr = up.i(s->hfield_adr, s->nhfield);
   d.ngrid = use_grid ? (int)grid_geoms.size() : 0;
   d.ndyngeom = (int)dyn_geoms.size(); d.dyn_geom = up.raw(dyn_geoms);
   d.grid_nx = grid_nx; d.grid_ny = grid_ny; d.grid_x0 = (float)grid_x0; d.grid_y0 = (float)grid_y0;

@@ -68,6 +68,9 @@ struct ModelDev {
   WField<float> site_pos, site_quat;
   // ---- fixed tendons (wraps flattened to dof / qpos addresses) and actuators
   int col_maxc;      // narrowphase variant: most contacts per geom pair (2, 4 or 8)
+  int col_convex;    // 1: some pair needs the GJK/EPA, plane-mesh or height-field colliders
+  const int *geom_dataid, *mesh_vertadr, *mesh_vertnum, *hfield_nrow, *hfield_ncol, *hfield_adr;
+  const float *mesh_vert, *hfield_size, *hfield_data;
   int ntendon, nwrap;
   const int *tendon_adr, *tendon_num, *wrap_dof, *wrap_qpos;
   const float *wrap_coef, *tendon_stiffness, *tendon_damping, *tendon_lengthspring;

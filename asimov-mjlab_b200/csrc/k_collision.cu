@@ -11,6 +11,7 @@
 // with an atomic counter (src/mjlab/utils/random.py:12-14 notes its non-determinism).
 #include "b2s_math.cuh"
 #include "b2s_api.h"
+#include "k_convex.cuh"
 
 extern __shared__ float b2s_smem[];
 #define B2S_MAX_SURVIVORS 160
@@ -286,7 +287,7 @@ DEV int box_box(RawCon* c, float margin, v3 p1, const m33& M1, v3 S1, v3 p2, con
 
 // MAXC = most contacts one pair of this model can produce (put_model picks 2 / 4 / 8): the contact scratch stays in
 // registers for sphere / capsule robots and the box colliders are compiled out where no box pair exists
-template <int MAXC>
+template <int MAXC, bool CONVEX>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
@@ -313,6 +314,12 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       if (m.geom_type[g1] == B2S_GEOM_PLANE) {
         v3 n = mk3(gm[9 * g1 + 2], gm[9 * g1 + 5], gm[9 * g1 + 8]);
         pass = dot(dif, n) <= m.geom_rbound[g2] + margin;
+      } else if (CONVEX && m.geom_type[g1] == B2S_GEOM_HFIELD) {
+        // bounding sphere of geom 2 against the field's box, in the field's frame
+        const float* hs = m.hfield_size + 4 * m.geom_dataid[g1];
+        const v3 pl = mulTv(ldm(gm + 9 * g1), dif);
+        const float r = m.geom_rbound[g2] + margin;
+        pass = !(pl.x + r < -hs[0] || pl.x - r > hs[0] || pl.y + r < -hs[1] || pl.y - r > hs[1] || pl.z - r > hs[2] || pl.z + r < -hs[3]);
       } else {
         const float bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
         pass = dot(dif, dif) <= bound * bound;
@@ -400,6 +407,30 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t2 == B2S_GEOM_CAPSULE) n = capsule_capsule(rc, margin, p1, m1, s1, p2, m2, s2);
         else if (t2 == B2S_GEOM_BOX) n = capsule_box(rc, margin, p1, m1, s1, p2, m2, s2);
       } else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) { if constexpr (MAXC >= 8) n = box_box(rc, margin, p1, m1, s1, p2, m2, s2); }
+      if constexpr (CONVEX) {
+        if (t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_HFIELD) {
+          Cvx B;
+          B.pos = p2; B.mat = m2; B.size = s2; B.vert = nullptr; B.nvert = 0; B.world = false; B.radius = 0.f;
+          if (t2 == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = s2.x; }
+          else if (t2 == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = s2.x; }
+          else if (t2 == B2S_GEOM_BOX) B.type = CVX_BOX;
+          else { const int id = m.geom_dataid[g2]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
+          if (t1 == B2S_GEOM_PLANE) n = plane_mesh(rc, margin, p1, m1, p2, m2, B.vert, B.nvert);
+          else if (t1 == B2S_GEOM_HFIELD) {
+            const int h = m.geom_dataid[g1];
+            n = hfield_convex<MAXC>(rc, margin, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h],
+                                    p1, m1, B, m.geom_rbound[g2]);
+          } else {
+            Cvx A;
+            A.pos = p1; A.mat = m1; A.size = s1; A.vert = nullptr; A.nvert = 0; A.world = false; A.radius = 0.f;
+            if (t1 == B2S_GEOM_SPHERE) { A.type = CVX_POINT; A.radius = s1.x; }
+            else if (t1 == B2S_GEOM_CAPSULE) { A.type = CVX_SEGMENT; A.radius = s1.x; }
+            else if (t1 == B2S_GEOM_BOX) A.type = CVX_BOX;
+            else { const int id = m.geom_dataid[g1]; A.type = CVX_VERTS; A.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; A.nvert = m.mesh_vertnum[id]; }
+            n = convex_pair(rc, margin, A, B);
+          }
+        }
+      }
     }
     int total;
     const int excl = warp_excl_scan(n, lane, &total);
@@ -452,20 +483,21 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   if (lane == 0) d.ncon[w] = min(ncon, cmax);
 }
 
-#define COL_DISPATCH(M, EXPR)                                   \
-  switch ((M).col_maxc) {                                       \
-    case 2: { constexpr int MAXC = 2; EXPR; } break;            \
-    case 4: { constexpr int MAXC = 4; EXPR; } break;            \
-    default: { constexpr int MAXC = 8; EXPR; } break;           \
+#define COL_DISPATCH(M, EXPR)                                                                   \
+  if ((M).col_convex) { constexpr int MAXC = 8; constexpr bool CONVEX = true; EXPR; }           \
+  else switch ((M).col_maxc) {                                                                  \
+    case 2: { constexpr int MAXC = 2; constexpr bool CONVEX = false; EXPR; } break;             \
+    case 4: { constexpr int MAXC = 4; constexpr bool CONVEX = false; EXPR; } break;             \
+    default: { constexpr int MAXC = 8; constexpr bool CONVEX = false; EXPR; } break;            \
   }
 void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
-  COL_DISPATCH(m, (k_collision<MAXC><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
+  COL_DISPATCH(m, (k_collision<MAXC, CONVEX><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
   b2s_count_launch();
 }
 size_t smem_collision(const ModelDev&) { return (size_t)B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1) * sizeof(int); }
 const void* fn_collision(const ModelDev& m) {
   const void* f = nullptr;
-  COL_DISPATCH(m, (f = (const void*)k_collision<MAXC>));
+  COL_DISPATCH(m, (f = (const void*)k_collision<MAXC, CONVEX>));
   return f;
 }

@@ -1,0 +1,406 @@
+// k_convex.cuh -- convex / height-field narrowphase, one lane per geom pair.
+//
+// GJK distance + EPA penetration between convex CORES (point, segment, box, vertex cloud); spheres and capsules are a
+// core plus a radius, so their results are exact for the rounded shape.  plane-mesh scans the hull vertices and keeps a
+// 4-point manifold; a height field is visited as triangular prisms over the sub-grid under the other geom's bounding
+// sphere.  Needed by the fork's Asimov robots (mesh collision geoms, asimov_toe.xml:12,49) and by height-field terrain
+// (terrains/heightfield_terrains.py:213-242).  Everything is per-thread state: the simplex lives in registers, the EPA
+// polytope (28 vertices, 56 faces) in local memory; none of it is instantiated for models without mesh / hfield pairs.
+#pragma once
+#include "b2s_math.cuh"
+
+#define CVX_POINT 0
+#define CVX_SEGMENT 1
+#define CVX_BOX 2
+#define CVX_VERTS 3
+#define GJK_MAXIT 48
+#define EPA_MAXIT 48
+#define EPA_MAXV 28
+#define EPA_MAXF 56
+#define CVX_TOL 1e-6f
+
+struct Cvx {
+  int type;
+  v3 pos;
+  m33 mat;
+  v3 size;             // SEGMENT: size.y = half length along local z; BOX: half sizes
+  const float* vert;   // VERTS: vertices in the local frame (world == false) or already in the world frame
+  int nvert;
+  bool world;
+  float radius;
+};
+struct CvxRes { float dist; v3 n, pa, pb; };
+struct Simplex { v3 Y[4], A[4]; float lam[4]; int n; };
+
+// support point of the core in world direction dir (ties: lowest vertex index)
+__device__ __noinline__ v3 cvx_support(const Cvx& s, v3 dir) {
+  if (s.type == CVX_POINT) return s.pos;
+  if (s.type == CVX_VERTS && s.world) {
+    int best = 0; float bd = dot(ld3(s.vert), dir);
+    for (int i = 1; i < s.nvert; i++) { const float t = dot(ld3(s.vert + 3 * i), dir); if (t > bd) { bd = t; best = i; } }
+    return ld3(s.vert + 3 * best);
+  }
+  const v3 dl = mulTv(s.mat, dir);
+  v3 loc;
+  if (s.type == CVX_SEGMENT) loc = mk3(0.f, 0.f, dl.z >= 0.f ? s.size.y : -s.size.y);
+  else if (s.type == CVX_BOX) loc = mk3(dl.x >= 0.f ? s.size.x : -s.size.x, dl.y >= 0.f ? s.size.y : -s.size.y, dl.z >= 0.f ? s.size.z : -s.size.z);
+  else {
+    int best = 0; float bd = s.vert[0] * dl.x + s.vert[1] * dl.y + s.vert[2] * dl.z;
+    for (int i = 1; i < s.nvert; i++) {
+      const float t = s.vert[3 * i] * dl.x + s.vert[3 * i + 1] * dl.y + s.vert[3 * i + 2] * dl.z;
+      if (t > bd) { bd = t; best = i; }
+    }
+    loc = ld3(s.vert + 3 * best);
+  }
+  return mulv(s.mat, loc) + s.pos;
+}
+DEV void mink_support(const Cvx& A, const Cvx& B, v3 dir, v3& y, v3& a) {
+  a = cvx_support(A, dir);
+  const v3 b = cvx_support(B, dir * -1.f);
+  y = a - b;
+}
+
+// ---- closest point to the origin on a simplex (Voronoi regions); the simplex is reduced in place
+DEV void sx_keep1(Simplex& s, int i) { s.Y[0] = s.Y[i]; s.A[0] = s.A[i]; s.n = 1; s.lam[0] = 1.f; }
+DEV void sx_keep2(Simplex& s, int i, int j, float t) {
+  const v3 y0 = s.Y[i], y1 = s.Y[j], a0 = s.A[i], a1 = s.A[j];
+  s.Y[0] = y0; s.Y[1] = y1; s.A[0] = a0; s.A[1] = a1; s.n = 2; s.lam[0] = 1.f - t; s.lam[1] = t;
+}
+DEV void closest_segment(Simplex& s) {
+  const v3 ab = s.Y[1] - s.Y[0];
+  float t = -dot(s.Y[0], ab);
+  const float den = dot(ab, ab);
+  if (t <= 0.f || den <= 0.f) { sx_keep1(s, 0); return; }
+  if (t >= den) { sx_keep1(s, 1); return; }
+  t /= den; s.lam[0] = 1.f - t; s.lam[1] = t;
+}
+DEV void closest_triangle(Simplex& s) {
+  const v3 a = s.Y[0], b = s.Y[1], c = s.Y[2];
+  const v3 ab = b - a, ac = c - a;
+  const float d1 = -dot(ab, a), d2 = -dot(ac, a);
+  if (d1 <= 0.f && d2 <= 0.f) { sx_keep1(s, 0); return; }
+  const float d3 = -dot(ab, b), d4 = -dot(ac, b);
+  if (d3 >= 0.f && d4 <= d3) { sx_keep1(s, 1); return; }
+  const float vc = d1 * d4 - d3 * d2;
+  if (vc <= 0.f && d1 >= 0.f && d3 <= 0.f) { sx_keep2(s, 0, 1, d1 / (d1 - d3)); return; }
+  const float d5 = -dot(ab, c), d6 = -dot(ac, c);
+  if (d6 >= 0.f && d5 <= d6) { sx_keep1(s, 2); return; }
+  const float vb = d5 * d2 - d1 * d6;
+  if (vb <= 0.f && d2 >= 0.f && d6 <= 0.f) { sx_keep2(s, 0, 2, d2 / (d2 - d6)); return; }
+  const float va = d3 * d6 - d5 * d4;
+  if (va <= 0.f && (d4 - d3) >= 0.f && (d5 - d6) >= 0.f) { sx_keep2(s, 1, 2, (d4 - d3) / ((d4 - d3) + (d5 - d6))); return; }
+  const float den = va + vb + vc;
+  if (den <= 0.f) { s.n = 2; closest_segment(s); return; }      // collinear
+  s.lam[1] = vb / den; s.lam[2] = vc / den; s.lam[0] = 1.f - s.lam[1] - s.lam[2];
+}
+DEV v3 sx_point(const v3* P, const Simplex& s) {
+  v3 r = mk3(0.f, 0.f, 0.f);
+  for (int i = 0; i < s.n; i++) r = r + P[i] * s.lam[i];
+  return r;
+}
+// true: the origin is inside the tetrahedron (simplex untouched); else reduced to the closest face feature
+__device__ __noinline__ bool closest_tetrahedron(Simplex& s, float scale2) {
+  float bestd = -1.f;
+  Simplex best;
+  best.n = 0;
+#pragma unroll 1
+  for (int f = 0; f < 4; f++) {
+    const int i0 = f == 3 ? 1 : 0, i1 = f == 0 ? 1 : (f == 1 ? 2 : 3), i2 = f == 0 ? 2 : (f == 1 ? 3 : (f == 2 ? 1 : 2)), i3 = f == 0 ? 3 : (f == 1 ? 1 : (f == 2 ? 2 : 0));
+    const v3 a = s.Y[i0], b = s.Y[i1], c = s.Y[i2], dd = s.Y[i3];
+    const v3 nn = cross(b - a, c - a);
+    const float sp = -dot(a, nn), sd = dot(dd - a, nn);
+    // outer side of this face, or a (nearly) flat tetrahedron: resolved through its faces, never certified as enclosing
+    if (sp * sd < 0.f || sd * sd <= 1e-10f * dot(nn, nn) * scale2) {
+      Simplex t;
+      t.Y[0] = a; t.Y[1] = b; t.Y[2] = c; t.A[0] = s.A[i0]; t.A[1] = s.A[i1]; t.A[2] = s.A[i2]; t.n = 3;
+      closest_triangle(t);
+      const v3 v = sx_point(t.Y, t);
+      const float d2 = dot(v, v);
+      if (bestd < 0.f || d2 < bestd) { bestd = d2; best = t; }
+    }
+  }
+  if (bestd < 0.f) return true;
+  s = best;
+  return false;
+}
+
+// ---- EPA: triangle faces with outward normals; the face closest to the origin is expanded along its normal
+struct EpaFace { unsigned char v[3], alive; v3 n; float d; };
+DEV void epa_make_face(EpaFace& f, const v3* V, int a, int b, int c) {
+  f.v[0] = (unsigned char)a; f.v[1] = (unsigned char)b; f.v[2] = (unsigned char)c; f.alive = 1;
+  v3 n = cross(V[b] - V[a], V[c] - V[a]);
+  const float len = norm(n);
+  if (len < 1e-20f) { f.n = mk3(0.f, 0.f, 0.f); f.d = 1e30f; return; }      // sliver: never chosen
+  f.n = mk3(n.x / len, n.y / len, n.z / len);
+  f.d = dot(f.n, V[a]);
+}
+__device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const Simplex& s, CvxRes& out) {
+  v3 V[EPA_MAXV], VA[EPA_MAXV];
+  EpaFace F[EPA_MAXF];
+  unsigned char E[EPA_MAXF * 3][2];
+  int nv = 4, nf = 0;
+  for (int i = 0; i < 4; i++) { V[i] = s.Y[i]; VA[i] = s.A[i]; }
+  if (dot(cross(V[1] - V[0], V[2] - V[0]), V[3] - V[0]) > 0.f) {      // make (0,1,2) face away from vertex 3
+    v3 t = V[1]; V[1] = V[2]; V[2] = t; t = VA[1]; VA[1] = VA[2]; VA[2] = t;
+  }
+  epa_make_face(F[nf++], V, 0, 1, 2);
+  epa_make_face(F[nf++], V, 0, 3, 1);
+  epa_make_face(F[nf++], V, 0, 2, 3);
+  epa_make_face(F[nf++], V, 1, 3, 2);
+  int best = 0;
+#pragma unroll 1
+  for (int it = 0; it < EPA_MAXIT; it++) {
+    best = -1;
+    for (int f = 0; f < nf; f++) if (F[f].alive && (best < 0 || F[f].d < F[best].d)) best = f;
+    if (best < 0) return false;
+    v3 w, wa;
+    mink_support(A, B, F[best].n, w, wa);
+    const float gain = dot(w, F[best].n) - F[best].d;
+    const float tol = CVX_TOL * (1.f + fabsf(F[best].d));
+    if (gain <= tol || nv >= EPA_MAXV) break;
+    int ne = 0, nvis = 0;
+    for (int f = 0; f < nf; f++) {
+      if (!F[f].alive) continue;
+      if (dot(F[f].n, w - V[F[f].v[0]]) > 0.f || F[f].d >= 1e30f) {
+        F[f].alive = 0; nvis++;
+        for (int k = 0; k < 3; k++) { E[ne][0] = F[f].v[k]; E[ne][1] = F[f].v[(k + 1) % 3]; ne++; }
+      }
+    }
+    if (nvis == 0) break;
+    V[nv] = w; VA[nv] = wa;
+    int added = 0;
+    bool full = false;
+    for (int e = 0; e < ne; e++) {
+      bool twin = false;
+      for (int g = 0; g < ne; g++) if (E[g][0] == E[e][1] && E[g][1] == E[e][0]) { twin = true; break; }
+      if (twin) continue;
+      int slot = -1;
+      for (int f = 0; f < nf; f++) if (!F[f].alive) { slot = f; break; }
+      if (slot < 0) { if (nf >= EPA_MAXF) { full = true; break; } slot = nf++; }
+      epa_make_face(F[slot], V, E[e][0], E[e][1], nv);
+      added++;
+    }
+    nv++;
+    if (full || added == 0) break;
+  }
+  best = -1;
+  for (int f = 0; f < nf; f++) if (F[f].alive && (best < 0 || F[f].d < F[best].d)) best = f;
+  if (best < 0) return false;
+  Simplex t;
+  for (int i = 0; i < 3; i++) { t.Y[i] = V[F[best].v[i]]; t.A[i] = VA[F[best].v[i]]; }
+  t.n = 3;
+  closest_triangle(t);
+  const v3 p = sx_point(t.Y, t);
+  out.pa = sx_point(t.A, t);
+  out.n = F[best].n;
+  out.pb = out.pa - p;
+  out.dist = -fmaxf(F[best].d, 0.f);
+  return true;
+}
+
+// GJK on the cores.  false: farther apart than `cutoff`.  Separated: dist > 0, n from A to B, pa / pb closest core
+// points.  Overlapping cores: the simplex is grown to a tetrahedron around the origin and handed to EPA.
+__device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, CvxRes& out) {
+  Simplex s;
+  v3 dir = B.pos - A.pos;
+  if (dot(dir, dir) < 1e-20f) dir = mk3(1.f, 0.f, 0.f);
+  mink_support(A, B, dir, s.Y[0], s.A[0]);
+  s.n = 1; s.lam[0] = 1.f;
+  v3 v = s.Y[0];
+  float scale2 = dot(v, v);
+  bool inside = false;
+#pragma unroll 1
+  for (int it = 0; it < GJK_MAXIT; it++) {
+    const float vv = dot(v, v);
+    if (vv <= CVX_TOL * CVX_TOL * scale2 || vv < 1e-30f) { inside = true; break; }
+    v3 w, wa;
+    mink_support(A, B, v * -1.f, w, wa);
+    const float vw = dot(v, w);
+    if (vw > 0.f && vw * vw > cutoff * cutoff * vv) return false;
+    const float ww = dot(w, w);
+    if (ww > scale2) scale2 = ww;
+    if (vv - vw <= CVX_TOL * vv + 1e-12f * scale2) break;
+    bool dup = false;
+    for (int i = 0; i < s.n; i++) { const v3 e = w - s.Y[i]; if (dot(e, e) <= 1e-14f * scale2) dup = true; }
+    if (dup) break;
+    s.Y[s.n] = w; s.A[s.n] = wa; s.n++;
+    if (s.n == 2) closest_segment(s);
+    else if (s.n == 3) closest_triangle(s);
+    else if (closest_tetrahedron(s, scale2)) { inside = true; break; }
+    v = sx_point(s.Y, s);
+  }
+  if (!inside) {
+    const float vv = dot(v, v), dist = sqrtf(vv);
+    if (dist > cutoff) return false;
+    out.pa = sx_point(s.A, s);
+    out.pb = out.pa - v;
+    out.n = mk3(-v.x / dist, -v.y / dist, -v.z / dist);
+    out.dist = dist;
+    return true;
+  }
+  if (s.n < 4) {
+    if (s.n == 1) {
+      for (int a = 0; a < 6 && s.n == 1; a++) {
+        const v3 ax = mk3(a == 0 ? 1.f : (a == 1 ? -1.f : 0.f), a == 2 ? 1.f : (a == 3 ? -1.f : 0.f), a == 4 ? 1.f : (a == 5 ? -1.f : 0.f));
+        v3 w, wa; mink_support(A, B, ax, w, wa);
+        const v3 e = w - s.Y[0];
+        if (dot(e, e) > 1e-12f * scale2 + 1e-30f) { s.Y[1] = w; s.A[1] = wa; s.n = 2; }
+      }
+    }
+    if (s.n == 2) {
+      const v3 ab = s.Y[1] - s.Y[0];
+      for (int a = 0; a < 6 && s.n == 2; a++) {
+        const v3 ax = mk3(a == 0 ? 1.f : (a == 1 ? -1.f : 0.f), a == 2 ? 1.f : (a == 3 ? -1.f : 0.f), a == 4 ? 1.f : (a == 5 ? -1.f : 0.f));
+        const v3 dd = cross(ab, ax);
+        if (dot(dd, dd) < 1e-12f * dot(ab, ab)) continue;
+        v3 w, wa; mink_support(A, B, dd, w, wa);
+        const v3 cr = cross(ab, w - s.Y[0]);
+        if (dot(cr, cr) > 1e-12f * scale2 * dot(ab, ab)) { s.Y[2] = w; s.A[2] = wa; s.n = 3; }
+      }
+    }
+    if (s.n == 3) {
+      const v3 nn = cross(s.Y[1] - s.Y[0], s.Y[2] - s.Y[0]);
+      for (int sgn = 0; sgn < 2 && s.n == 3; sgn++) {
+        v3 w, wa; mink_support(A, B, sgn ? nn * -1.f : nn, w, wa);
+        const float vol = dot(w - s.Y[0], nn);
+        if (vol * vol > 1e-12f * dot(nn, nn) * scale2) { s.Y[3] = w; s.A[3] = wa; s.n = 4; }
+      }
+    }
+    if (s.n < 4) {       // flat Minkowski difference: zero-depth contact
+      v3 nn = B.pos - A.pos;
+      const float l = norm(nn);
+      nn = l < 1e-12f ? mk3(0.f, 0.f, 1.f) : mk3(nn.x / l, nn.y / l, nn.z / l);
+      out.pa = s.A[0]; out.pb = s.A[0] - s.Y[0]; out.n = nn; out.dist = 0.f;
+      return true;
+    }
+  }
+  return epa_penetration(A, B, s, out);
+}
+
+// one contact between two convex geoms (cores + radii); normal from A to B.  Rc is the kernel's contact scratch type.
+template <class Rc>
+DEV int convex_pair(Rc* c, float margin, const Cvx& A, const Cvx& B) {
+  CvxRes r;
+  if (!gjk_epa(A, B, margin + A.radius + B.radius, r)) return 0;
+  const float dist = r.dist - A.radius - B.radius;
+  if (dist > margin) return 0;
+  const v3 sa = r.pa + r.n * A.radius, sb = r.pb - r.n * B.radius;
+  c->dist = dist; c->pos = (sa + sb) * 0.5f; c->n = r.n; c->t = mk3(0.f, 0.f, 0.f);
+  return 1;
+}
+
+// plane - mesh: hull vertices within 1 mm of the deepest one are candidates; up to 4 span the manifold
+// (A deepest, B farthest from A, C farthest from line AB, D farthest from line BC or AC)
+template <class Rc>
+DEV int plane_mesh(Rc* c, float margin, v3 ppos, const m33& pmat, v3 mpos, const m33& mmat, const float* vert, int nvert) {
+  const v3 n = col(pmat, 2), nl = mulTv(mmat, n), pl = mulTv(mmat, ppos - mpos);
+  const float pd = dot(pl, nl);
+  float smax = -1e30f;
+  int ia = -1;
+  for (int i = 0; i < nvert; i++) {
+    const float sup = pd - (vert[3 * i] * nl.x + vert[3 * i + 1] * nl.y + vert[3 * i + 2] * nl.z);
+    if (sup > smax) { smax = sup; ia = i; }
+  }
+  if (ia < 0 || -smax > margin) return 0;
+  float thr = smax - 1e-3f;
+  if (thr < 0.f && smax >= 0.f) thr = 0.f;
+  if (-thr > margin) thr = -margin;
+  int idx[4] = {ia, -1, -1, -1};
+  const v3 a = ld3(vert + 3 * ia);
+  float best = 0.f;
+  for (int i = 0; i < nvert; i++) {
+    const v3 v = ld3(vert + 3 * i);
+    if (pd - dot(v, nl) < thr) continue;
+    const v3 e = v - a; const float q = dot(e, e);
+    if (q > best) { best = q; idx[1] = i; }
+  }
+  if (idx[1] >= 0 && best > 1e-10f) {
+    const v3 b = ld3(vert + 3 * idx[1]), ab = b - a, side = cross(nl, ab);
+    best = 0.f;
+    for (int i = 0; i < nvert; i++) {
+      const v3 v = ld3(vert + 3 * i);
+      if (pd - dot(v, nl) < thr) continue;
+      const float q = fabsf(dot(v - a, side));
+      if (q > best) { best = q; idx[2] = i; }
+    }
+    if (idx[2] >= 0 && best > 1e-7f) {
+      const v3 cc = ld3(vert + 3 * idx[2]), sac = cross(nl, cc - a), sbc = cross(nl, cc - b);
+      float bestb = 0.f, besta = 0.f; int ib = -1, iaa = -1;
+      for (int i = 0; i < nvert; i++) {
+        const v3 v = ld3(vert + 3 * i);
+        if (pd - dot(v, nl) < thr) continue;
+        if (i == idx[0] || i == idx[1] || i == idx[2]) continue;
+        const float qb = fabsf(dot(v - b, sbc)), qa = fabsf(dot(v - a, sac));
+        if (qb > bestb) { bestb = qb; ib = i; }
+        if (qa > besta) { besta = qa; iaa = i; }
+      }
+      if (bestb >= besta) { best = bestb; idx[3] = ib; } else { best = besta; idx[3] = iaa; }
+      if (best <= 1e-7f) idx[3] = -1;
+    } else idx[2] = -1;
+  } else idx[1] = -1;
+  int nc = 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const int i = idx[k];
+    if (i < 0) continue;
+    bool dup = false;
+    for (int q = 0; q < k; q++) if (idx[q] == i) dup = true;
+    if (dup) continue;
+    const v3 v = ld3(vert + 3 * i);
+    const float sup = pd - dot(v, nl);
+    if (-sup > margin) continue;
+    c[nc].dist = -sup; c[nc].pos = mulv(mmat, v) + mpos + n * (sup * 0.5f); c[nc].n = n; c[nc].t = mk3(0.f, 0.f, 0.f);
+    nc++;
+  }
+  return nc;
+}
+
+// height field (geom 1) against convex B: prisms of the cells under B's bounding sphere in (row, column, lower / upper
+// triangle) order, one contact per prism, the deepest MAXC kept (in visiting order).  hs = (x half, y half, z top, base).
+template <int MAXC, class Rc>
+DEV int hfield_convex(Rc* c, float margin, const float* hs, int nrow, int ncol, const float* data, v3 hpos, const m33& hmat,
+                      const Cvx& B, float rbound) {
+  const float sx = hs[0], sy = hs[1], sz = hs[2], sb = hs[3];
+  const v3 p = mulTv(hmat, B.pos - hpos);
+  const float r = rbound + margin;
+  if (p.x + r < -sx || p.x - r > sx || p.y + r < -sy || p.y - r > sy || p.z - r > sz || p.z + r < -sb) return 0;
+  const float dx = 2.f * sx / (float)(ncol - 1), dy = 2.f * sy / (float)(nrow - 1);
+  const int cmin = max((int)floorf((p.x - r + sx) / dx), 0), cmax = min((int)ceilf((p.x + r + sx) / dx), ncol - 1);
+  const int rmin = max((int)floorf((p.y - r + sy) / dy), 0), rmax = min((int)ceilf((p.y + r + sy) / dy), nrow - 1);
+  int nc = 0;
+#pragma unroll 1
+  for (int rr = rmin; rr < rmax; rr++)
+#pragma unroll 1
+    for (int cc = cmin; cc < cmax; cc++)
+#pragma unroll 1
+      for (int tri = 0; tri < 2; tri++) {
+        const int r0 = tri ? rr + 1 : rr, k0 = cc, r1 = rr + 1, k1 = tri ? cc + 1 : cc, r2 = rr, k2 = cc + 1;
+        float wv[18];
+        float zmax = -sb;
+        {
+          const int cr[3] = {r0, r1, r2}, ck[3] = {k0, k1, k2};
+#pragma unroll
+          for (int i = 0; i < 3; i++) {
+            const float z = data[cr[i] * ncol + ck[i]] * sz;
+            const v3 top = mk3((float)ck[i] * dx - sx, (float)cr[i] * dy - sy, z), bot = mk3(top.x, top.y, -sb);
+            st3(wv + 3 * i, mulv(hmat, top) + hpos);
+            st3(wv + 9 + 3 * i, mulv(hmat, bot) + hpos);
+            zmax = fmaxf(zmax, z);
+          }
+        }
+        if (zmax < p.z - r) continue;
+        Cvx P;
+        P.type = CVX_VERTS; P.vert = wv; P.nvert = 6; P.world = true; P.radius = 0.f;
+        P.pos = mk3((wv[0] + wv[3] + wv[6] + wv[9] + wv[12] + wv[15]) / 6.f, (wv[1] + wv[4] + wv[7] + wv[10] + wv[13] + wv[16]) / 6.f,
+                    (wv[2] + wv[5] + wv[8] + wv[11] + wv[14] + wv[17]) / 6.f);
+        Rc one;
+        if (!convex_pair(&one, margin, P, B)) continue;
+        if (nc < MAXC) c[nc++] = one;
+        else {
+          int sh = 0;
+          for (int i = 1; i < MAXC; i++) if (c[i].dist > c[sh].dist) sh = i;
+          if (one.dist < c[sh].dist) { for (int i = sh; i < MAXC - 1; i++) c[i] = c[i + 1]; c[MAXC - 1] = one; }
+        }
+      }
+  return nc;
+}

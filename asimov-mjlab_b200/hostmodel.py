@@ -36,8 +36,12 @@ class _Stat:
 
 class HostModel:
   """Attribute bag with MjModel field names (numpy arrays, float64 / int32)."""
-  ntendon = 0     # defaults for model blobs exported before tendons existed
+  ntendon = 0     # defaults for model blobs exported before tendons / meshes / height fields existed
   nwrap = 0
+  nmesh = 0
+  nmeshvert = 0
+  nhfield = 0
+  nhfielddata = 0
 
   def __init__(self):
     self.opt = _Opt()

@@ -22,6 +22,7 @@ from __future__ import annotations
 
 import copy
 import math
+import os
 import re
 import xml.etree.ElementTree as ET
 from dataclasses import dataclass, field
@@ -107,6 +108,28 @@ class GeomSpec:
   density: float = 1000.0
   rgba: list = field(default_factory=lambda: [0.5, 0.5, 0.5, 1.0])
   mesh: str = ""
+  hfield: str = ""
+
+
+@dataclass
+class MeshSpec:
+  """<asset><mesh>: vertices come from `vertex` (inline) or from a binary STL `file` (read lazily, at compile time,
+  and only for meshes that a COLLIDING geom uses)."""
+  name: str = ""
+  file: str = ""
+  vertex: object = None            # (n, 3) array or None
+  scale: list = field(default_factory=lambda: [1.0, 1.0, 1.0])
+
+
+@dataclass
+class HFieldSpec:
+  """<asset><hfield>: size = (x half extent, y half extent, z top, z base thickness); data[nrow, ncol] in [0, 1]
+  (row <-> y, column <-> x; MuJoCo normalises elevation data the same way)."""
+  name: str = ""
+  nrow: int = 0
+  ncol: int = 0
+  size: list = field(default_factory=lambda: [1.0, 1.0, 1.0, 0.1])
+  data: object = None
 
 
 @dataclass
@@ -227,6 +250,8 @@ class Spec:
     self.worldbody = BodySpec(name="world")
     self.actuators: list[ActuatorSpec] = []
     self.tendons: list[TendonSpec] = []
+    self.meshes: dict[str, MeshSpec] = {}
+    self.hfields: dict[str, HFieldSpec] = {}
     self.sensors: list[SensorSpec] = []
     self.excludes: list[tuple[str, str]] = []
     self.keys: dict[str, dict] = {}
@@ -241,7 +266,7 @@ class Spec:
 
   @classmethod
   def from_file(cls, path) -> "Spec":
-    return _Parser().parse(ET.parse(str(path)).getroot())
+    return _Parser(basedir=os.path.dirname(os.path.abspath(str(path)))).parse(ET.parse(str(path)).getroot())
 
   # -- queries --------------------------------------------------------------
   def _walk(self, body=None):
@@ -295,6 +320,18 @@ class Spec:
     self.sensors.append(s)
     return s
 
+  def add_mesh(self, name, vertex=None, file="", scale=(1.0, 1.0, 1.0)):
+    self.meshes[name] = MeshSpec(name=name, file=str(file), vertex=None if vertex is None else np.asarray(vertex, float).reshape(-1, 3),
+                                 scale=list(scale))
+    return self.meshes[name]
+
+  def add_hfield(self, name, data, size):
+    data = np.asarray(data, float)
+    lo, hi = float(data.min()), float(data.max())
+    norm = (data - lo)/(hi - lo) if hi > lo else np.zeros_like(data)
+    self.hfields[name] = HFieldSpec(name=name, nrow=data.shape[0], ncol=data.shape[1], size=list(map(float, size)), data=norm)
+    return self.hfields[name]
+
   def add_exclude(self, body1, body2):
     self.excludes.append((body1, body2))
 
@@ -311,6 +348,12 @@ class Spec:
       for lst in (b.joints, b.geoms, b.sites):
         for e in lst:
           e.name = ren(e.name)
+      for g in b.geoms:
+        g.mesh, g.hfield = ren(g.mesh), ren(g.hfield)
+    for k, v in child.meshes.items():
+      v.name = ren(k); self.meshes[ren(k)] = v
+    for k, v in child.hfields.items():
+      v.name = ren(k); self.hfields[ren(k)] = v
     self.worldbody.bodies.extend(child.worldbody.bodies)
     self.worldbody.geoms.extend(child.worldbody.geoms)
     self.worldbody.sites.extend(child.worldbody.sites)
@@ -333,7 +376,9 @@ class Spec:
 
 
 class _Parser:
-  def __init__(self):
+  def __init__(self, basedir=""):
+    self.basedir = basedir
+    self.meshdir = ""
     self.defaults: dict[str, dict[str, dict[str, str]]] = {"main": {}}
     self.angle_deg = True
     self.autolimits = True
@@ -349,6 +394,8 @@ class _Parser:
         self.autolimits = comp.get("autolimits") == "true"
       if comp.get("eulerseq"):
         self.eulerseq = comp.get("eulerseq")
+      if comp.get("meshdir"):
+        self.meshdir = comp.get("meshdir")
     for opt in root.findall("option"):
       for k in ("timestep", "tolerance", "ls_tolerance", "impratio"):
         if opt.get(k):
@@ -363,6 +410,23 @@ class _Parser:
         spec.option["gravity"] = _floats(opt.get("gravity"), 3)
     for d in root.findall("default"):
       self._parse_default(d, "main", top=True)
+    for sec in root.findall("asset"):
+      for el in sec:
+        if el.tag == "mesh":
+          f = el.get("file", "")
+          name = el.get("name") or os.path.splitext(os.path.basename(f))[0]
+          vert = np.array(_floats(el.get("vertex"))).reshape(-1, 3) if el.get("vertex") else None
+          # asset search order of the reference's Entity (update_assets puts <robot>/meshes beside <robot>/xmls)
+          cands = [os.path.join(self.basedir, self.meshdir, f), os.path.join(self.basedir, f),
+                   os.path.join(self.basedir, "assets", f), os.path.join(os.path.dirname(self.basedir), "meshes", f)]
+          path = next((c for c in cands if f and os.path.exists(c)), cands[0] if f else "")
+          spec.meshes[name] = MeshSpec(name=name, file=path, vertex=vert, scale=_floats(el.get("scale", "1 1 1"), 3))
+        elif el.tag == "hfield":
+          if el.get("file"):
+            raise NotImplementedError("<hfield file=...> is not supported (inline elevation only)")
+          nrow, ncol = int(el.get("nrow")), int(el.get("ncol"))
+          data = np.array(_floats(el.get("elevation"))).reshape(nrow, ncol) if el.get("elevation") else np.zeros((nrow, ncol))
+          spec.add_hfield(el.get("name", ""), data, _floats(el.get("size"), 4))
     wb = root.find("worldbody")
     if wb is not None:
       self._parse_body_children(wb, spec.worldbody, None)
@@ -501,6 +565,7 @@ class _Parser:
           v = _floats(a["solimp"]); g.solimp[:len(v)] = v
         if "rgba" in a: g.rgba = _floats(a["rgba"], 4)
         g.mesh = a.get("mesh", "")
+        g.hfield = a.get("hfield", "")
       elif t == "site":
         a = self._attrs(ch, childclass)
         body.add_site(name=a.get("name", ""), pos=_floats(a.get("pos", "0 0 0"), 3), quat=self._orient(a))
@@ -616,6 +681,31 @@ def _geom_mass_inertia(g: GeomSpec, size):
   return mass, unit*mass
 
 
+def load_stl(path) -> np.ndarray:
+  """Vertices of a binary STL (80-byte header, uint32 count, 50 bytes per triangle)."""
+  with open(path, "rb") as f:
+    b = f.read()
+  n = int.from_bytes(b[80:84], "little")
+  if len(b) < 84 + 50*n:
+    raise ValueError(f"{path}: not a binary STL")
+  tri = np.frombuffer(b, dtype=np.dtype([("n", "<f4", 3), ("v", "<f4", (3, 3)), ("a", "<u2")]), count=n, offset=84)
+  return tri["v"].reshape(-1, 3).astype(np.float64)
+
+
+def convex_hull_vertices(v: np.ndarray) -> np.ndarray:
+  """Hull vertices in first-occurrence order of the input (qhull via scipy; MuJoCo's compiler uses qhull too).
+  Coordinates are rounded to float32 first: that is what the device holds, and it keeps the hull reproducible."""
+  v = np.unique(np.asarray(v, np.float32).astype(np.float64), axis=0)
+  if len(v) <= 4:
+    return v
+  from scipy.spatial import ConvexHull
+  try:
+    idx = np.sort(ConvexHull(v).vertices)
+  except Exception:       # flat or degenerate input: keep every vertex
+    return v
+  return v[idx]
+
+
 def _resolve_geom(g: GeomSpec):
   """size/pos/quat after `fromto` resolution (MuJoCo: z axis along from-to, pos = midpoint)."""
   size, pos, quat = list(g.size), np.array(g.pos, float), np.array(g.quat, float)
@@ -652,12 +742,29 @@ def _compile(spec: Spec) -> HostModel:
   J = dict(type=[], qposadr=[], dofadr=[], bodyid=[], limited=[], pos=[], axis=[], stiffness=[],
            range=[], margin=[], solref=[], solimp=[])
   D = dict(bodyid=[], jntid=[], armature=[], damping=[], frictionloss=[])
-  G = dict(type=[], bodyid=[], contype=[], conaffinity=[], condim=[], priority=[], size=[], pos=[],
+  G = dict(dataid=[], type=[], bodyid=[], contype=[], conaffinity=[], condim=[], priority=[], size=[], pos=[],
            quat=[], friction=[], solmix=[], solref=[], solimp=[], margin=[], gap=[], rbound=[], rgba=[])
+  mesh_index: dict[str, int] = {}
+  mesh_hulls: list = []
+
+  def mesh_id(name):
+    """Index + convex-hull vertices (geom frame) of mesh `name`; MuJoCo collides mesh geoms by their convex hull."""
+    if name in mesh_index:
+      return mesh_index[name], mesh_hulls[mesh_index[name]]
+    if name not in spec.meshes:
+      raise ValueError(f"unknown mesh {name!r}")
+    ms = spec.meshes[name]
+    v = ms.vertex if ms.vertex is not None else load_stl(ms.file)
+    v = np.asarray(v, float)*np.asarray(ms.scale, float)[None, :]
+    hull = convex_hull_vertices(v)
+    mesh_index[name] = len(mesh_hulls); mesh_hulls.append(hull)
+    return mesh_index[name], hull
   S = dict(bodyid=[], pos=[], quat=[])
   qpos0, qpos_spring = [], []
   nq = nv = nmocap = 0
+  is_static = [True]*nbody
   for i, b in enumerate(bodies):
+    is_static[i] = (not b.joints) and (i == 0 or is_static[parent[i]])
     body_pos[i] = b.pos
     q = np.array(b.quat, float); body_quat[i] = q/np.linalg.norm(q)
     if b.mocap:
@@ -709,12 +816,22 @@ def _compile(spec: Spec) -> HostModel:
       elif t in (4,): rb = max(size)
       elif t == 6: rb = float(np.linalg.norm(size))
       else: rb = 0.0
-      G["rbound"].append(rb)
+      dataid = -1
+      if t == 7 and (g.contype or g.conaffinity):
+        dataid, hull = mesh_id(g.mesh)
+        rb = float(np.linalg.norm(hull, axis=1).max())
+        G["size"][-1] = list(np.abs(hull).max(axis=0))
+      if t == 1:
+        if g.hfield not in spec.hfields:
+          raise ValueError(f"geom {g.name!r}: unknown hfield {g.hfield!r}")
+        dataid = list(spec.hfields).index(g.hfield)
+        hs = spec.hfields[g.hfield].size
+        rb = float(np.linalg.norm([hs[0], hs[1], max(hs[2], hs[3])]))
+        G["size"][-1] = [hs[0], hs[1], max(hs[2], hs[3])]
+      G["rbound"].append(rb); G["dataid"].append(dataid)
       if t == 7:
-        if g.contype or g.conaffinity:
-          raise NotImplementedError(f"mesh geom {g.name!r} collides: convex mesh collision is not supported yet")
-        if b.inertial is None and (g.mass or (g.mass is None and g.density > 0)):
-          raise NotImplementedError(f"mesh geom {g.name!r} contributes inertia but mesh loading is not supported")
+        if b.inertial is None and not is_static[i] and (g.mass or (g.mass is None and g.density > 0)):
+          raise NotImplementedError(f"mesh geom {g.name!r} contributes inertia but mesh inertia is not supported (give the body an <inertial>)")
         continue
       if t in (0, 1):
         continue
@@ -784,6 +901,20 @@ def _compile(spec: Spec) -> HostModel:
   m.geom_solmix = arr(G["solmix"]); m.geom_solref = arr(G["solref"], float, (ngeom, 2))
   m.geom_solimp = arr(G["solimp"], float, (ngeom, 5)); m.geom_margin = arr(G["margin"]); m.geom_gap = arr(G["gap"])
   m.geom_rbound = arr(G["rbound"]); m.geom_rgba = arr(G["rgba"], float, (ngeom, 4))
+  m.geom_dataid = arr(G["dataid"], np.int32)
+  # convex meshes (hull vertices of the meshes that colliding geoms use) and height fields
+  m.nmesh = len(mesh_hulls); m.names["mesh"] = list(mesh_index)
+  m.mesh_vertnum = arr([len(h) for h in mesh_hulls], np.int32)
+  m.mesh_vertadr = arr(np.concatenate([[0], np.cumsum(m.mesh_vertnum)[:-1]]) if m.nmesh else [], np.int32)
+  m.mesh_vert = np.concatenate(mesh_hulls, axis=0) if m.nmesh else np.zeros((0, 3))
+  m.nmeshvert = int(m.mesh_vert.shape[0])
+  hf = list(spec.hfields.values())
+  m.nhfield = len(hf); m.names["hfield"] = [h.name for h in hf]
+  m.hfield_size = arr([h.size for h in hf], float, (len(hf), 4))
+  m.hfield_nrow = arr([h.nrow for h in hf], np.int32); m.hfield_ncol = arr([h.ncol for h in hf], np.int32)
+  m.hfield_adr = arr(np.concatenate([[0], np.cumsum([h.nrow*h.ncol for h in hf])[:-1]]) if hf else [], np.int32)
+  m.hfield_data = np.concatenate([np.asarray(h.data, float).reshape(-1) for h in hf]) if hf else np.zeros(0)
+  m.nhfielddata = int(m.hfield_data.size)
   m.site_bodyid = arr(S["bodyid"], np.int32); m.site_pos = arr(S["pos"], float, (nsite, 3))
   m.site_quat = arr(S["quat"], float, (nsite, 4))
   # actuators

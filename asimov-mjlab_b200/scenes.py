@@ -444,7 +444,7 @@ _OPT_KEYS = ("timestep", "integrator", "cone", "solver", "iterations", "ls_itera
 def save_model(m: HostModel, path) -> None:
   import json
   d = {k: v for k, v in m.__dict__.items() if isinstance(v, np.ndarray)}
-  for k in ("nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nsensor", "nsensordata", "nexclude", "nmocap", "ntendon", "nwrap"):
+  for k in ("nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nsensor", "nsensordata", "nexclude", "nmocap", "ntendon", "nwrap", "nmesh", "nmeshvert", "nhfield", "nhfielddata"):
     d["_" + k] = np.int64(getattr(m, k, 0))
   meta = dict(names=m.names, keys=m.keys, opt={k: getattr(m.opt, k) for k in _OPT_KEYS},
               gravity=list(map(float, m.opt.gravity)), meaninertia=m.stat.meaninertia,

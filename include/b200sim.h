@@ -82,6 +82,10 @@ typedef struct b2s_model_desc {
   int32_t nmocap;
   int32_t ntendon;
   int32_t nwrap;
+  int32_t nmesh;
+  int32_t nmeshvert;
+  int32_t nhfield;
+  int32_t nhfielddata;
   /* options (MjModel.opt; reference MujocoCfg.apply, sim.py:64-76) */
   double opt_timestep;
   double opt_gravity[3];
@@ -155,6 +159,16 @@ typedef struct b2s_model_desc {
   const double* geom_margin;      /* ngeom */
   const double* geom_gap;         /* ngeom */
   const double* geom_rbound;      /* ngeom */
+  const int32_t* geom_dataid;     /* ngeom */
+  /* convex meshes (collision uses the convex hull; vertices in the geom frame) and height fields */
+  const int32_t* mesh_vertadr;    /* nmesh */
+  const int32_t* mesh_vertnum;    /* nmesh */
+  const double* mesh_vert;        /* nmeshvert*3 */
+  const double* hfield_size;      /* nhfield*4 */
+  const int32_t* hfield_nrow;     /* nhfield */
+  const int32_t* hfield_ncol;     /* nhfield */
+  const int32_t* hfield_adr;      /* nhfield */
+  const double* hfield_data;      /* nhfielddata */
   /* sites */
   const int32_t* site_bodyid;     /* nsite */
   const double* site_pos;         /* nsite*3 */

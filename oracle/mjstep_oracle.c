@@ -642,6 +642,8 @@ static int col_box_box(rawcon* c, real margin, const real* p1, const real* m1, c
 }
 
 /* mj_contactParam */
+#include "convex_oracle.h"
+
 static void contact_param(const b2s_model_desc* m, int g1, int g2, int* condim, real* fri5, real* solref, real* solimp, real* margin, real* gap) {
   int p1 = m->geom_priority[g1], p2 = m->geom_priority[g2];
   real f[3];
@@ -716,6 +718,8 @@ void orc_collision(const b2s_model_desc* m, orc_data* d) {
     if (t1 == B2S_GEOM_PLANE) {
       real n[3] = {m1[2], m1[5], m1[8]}, dif[3] = {p2[0]-p1[0], p2[1]-p1[1], p2[2]-p1[2]};
       if (dot3(dif, n) > (real)m->geom_rbound[g2] + margin) continue;
+    } else if (t1 == B2S_GEOM_HFIELD) {
+      /* the sub-grid test inside col_hfield is the rejection */
     } else {
       real dif[3] = {p2[0]-p1[0], p2[1]-p1[1], p2[2]-p1[2]};
       real bound = (real)m->geom_rbound[g1] + (real)m->geom_rbound[g2] + margin;
@@ -739,6 +743,16 @@ void orc_collision(const b2s_model_desc* m, orc_data* d) {
     else if (t1 == B2S_GEOM_SPHERE && t2 == B2S_GEOM_BOX) n = col_sphere_box(rc, margin, p1, s1, p2, m2, s2);
     else if (t1 == B2S_GEOM_CAPSULE && t2 == B2S_GEOM_BOX) n = col_capsule_box(rc, margin, p1, m1, s1, p2, m2, s2);
     else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) n = col_box_box(rc, margin, p1, m1, s1, p2, m2, s2);
+    else if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_MESH) {
+      int id = m->geom_dataid[g2];
+      n = col_plane_mesh(rc, margin, p1, m1, p2, m2, m->mesh_vert + 3*m->mesh_vertadr[id], m->mesh_vertnum[id]);
+    } else if (t1 == B2S_GEOM_HFIELD && t2 >= B2S_GEOM_SPHERE && t2 != B2S_GEOM_ELLIPSOID && t2 != B2S_GEOM_CYLINDER) {
+      cvx B; cvx_from_geom(m, d, g2, &B);
+      n = col_hfield(rc, 8, margin, m, m->geom_dataid[g1], p1, m1, &B, (real)m->geom_rbound[g2]);
+    } else if (t2 == B2S_GEOM_MESH && t1 >= B2S_GEOM_SPHERE && t1 != B2S_GEOM_ELLIPSOID && t1 != B2S_GEOM_CYLINDER) {
+      cvx A, B; cvx_from_geom(m, d, g1, &A); cvx_from_geom(m, d, g2, &B);
+      n = col_convex(rc, margin, &A, &B);
+    }
     else n = 0; /* unsupported pair types are rejected at model creation by the product */
     for (int i = 0; i < n && ncon < d->nconmax; i++) {
       int c = ncon++;

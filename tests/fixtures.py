@@ -273,3 +273,39 @@ def legged_with_contact_sensors():
   S.append(dict(name="c_any_maxforce", type="contact", objtype="xbody", objname="trunk", reftype="geom", refname="floor", intprm=[1 | 2 | 32, 2, 2]))
   S.append(dict(name="c_geom", type="contact", objtype="geom", objname="fr_foot", intprm=[1 | 2 | 4, 3, 1]))
   return compile_xml(LEGGED, S)
+
+
+def box_mesh_vertices(hx, hy, hz):
+  return " ".join(f"{sx*hx} {sy*hy} {sz*hz}" for sx in (-1, 1) for sy in (-1, 1) for sz in (-1, 1))
+
+
+# convex-mesh fixtures: "cube" is a mesh whose hull is a box, so that GJK/EPA and the plane-mesh manifold can be checked
+# against the analytic box colliders on identical geometry
+def convex_scene(ground="plane", movers=("mesh",), hfield_elev=None, hfield_size=(2.0, 2.0, 0.4, 0.2), nrow=9, ncol=9, margin=0.0):
+  elev = hfield_elev if hfield_elev is not None else [0.0]*(nrow*ncol)
+  g = {"plane": '<geom name="floor" type="plane" size="5 5 0.1"/>',
+       "hfield": '<geom name="floor" type="hfield" hfield="hf"/>',
+       "box": '<geom name="floor" type="box" size="1 1 0.1" pos="0 0 -0.1"/>',
+       "meshbox": '<geom name="floor" type="mesh" mesh="slab" pos="0 0 -0.1"/>'}[ground]
+  kinds = {"mesh": '<geom name="m{i}" type="mesh" mesh="cube" margin="%g"/>' % margin,
+           "box": '<geom name="m{i}" type="box" size="0.1 0.08 0.06" margin="%g"/>' % margin,
+           "sphere": '<geom name="m{i}" type="sphere" size="0.1" margin="%g"/>' % margin,
+           "capsule": '<geom name="m{i}" type="capsule" size="0.05 0.1" margin="%g"/>' % margin}
+  bodies = "".join(
+    f'<body name="b{i}" pos="{0.5*i} 0 0.5"><freejoint/><inertial pos="0 0 0" mass="1" diaginertia="0.01 0.01 0.01"/>'
+    + kinds[k].format(i=i) + "</body>" for i, k in enumerate(movers))
+  return f"""
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.002"/>
+  <asset>
+    <mesh name="cube" vertex="{box_mesh_vertices(0.1, 0.08, 0.06)}"/>
+    <mesh name="slab" vertex="{box_mesh_vertices(1.0, 1.0, 0.1)}"/>
+    <hfield name="hf" nrow="{nrow}" ncol="{ncol}" size="{' '.join(map(str, hfield_size))}" elevation="{' '.join(map(str, elev))}"/>
+  </asset>
+  <worldbody>
+    <body name="ground">{g}</body>
+    {bodies}
+  </worldbody>
+</mujoco>
+"""

@@ -315,6 +315,64 @@ def test_asimov_toe_rough_box_terrain_matches_oracle(asimov_toe_rough):
   assert ncon_total > 100
 
 
+@pytest.mark.parametrize("ground", ["plane", "meshbox", "hfield"])
+def test_convex_mesh_and_height_field_contacts_match_oracle(ground):
+  """K7: GJK/EPA (mesh-mesh, box-mesh, sphere-mesh, capsule-mesh), plane-mesh manifold and height-field prisms on a
+  bumpy field: same contacts in the same order, same distances / frames; the oracle drives a tumbling trajectory and
+  the device is compared at every 10th state."""
+  import torch
+  rng = np.random.default_rng(31)
+  nrow = ncol = 17
+  elev = (0.5 + 0.5 * np.sin(np.linspace(0, 7, nrow))[:, None] * np.cos(np.linspace(0, 5, ncol))[None, :]).reshape(-1).tolist()
+  movers = ("mesh", "box", "sphere", "capsule", "mesh")
+  m = fx.compile_xml(fx.convex_scene(ground, movers, hfield_elev=elev, hfield_size=(1.0, 1.0, 0.15, 0.1), nrow=nrow, ncol=ncol, margin=0.004))
+  W = 16
+  qpos = np.tile(m.qpos0, (W, 1)); qvel = np.zeros((W, m.nv)); ctrl = np.zeros((W, m.nu))
+  for w in range(W):
+    for k in range(len(movers)):
+      ax = rng.normal(size=3); ax /= np.linalg.norm(ax); ang = rng.normal(0, 0.8)
+      qpos[w, 7 * k: 7 * k + 3] = [rng.uniform(-0.6, 0.6), rng.uniform(-0.6, 0.6), rng.uniform(0.05, 0.3) + (0.1 if ground == "hfield" else 0.0)]
+      qpos[w, 7 * k + 3: 7 * k + 7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
+    qvel[w] = rng.normal(0, 0.5, m.nv)
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=48, njmax=200)
+  seen, total, ncmp, tight, tight_pos = set(), 0, 0, 0, 0
+  for chunk in range(10):
+    if chunk:
+      for w in worlds:
+        orc.step(w, 10)
+      for f in ("qpos", "qvel", "qacc_warmstart"):
+        getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+    engine.forward(M, D)
+    for w in worlds:
+      orc.forward(w)
+    n_all = D.ncon.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9); Di = D.contact_dist.cpu().numpy()
+    for i, w in enumerate(worlds):
+      n = int(w["ncon"][0])
+      # a contact whose distance sits within float rounding of the margin (or of the plane-mesh 1 mm band) may exist on
+      # one side only: compare worlds whose contact lists agree, and require that almost all do
+      if int(n_all[i]) != n or G[i, :n].reshape(-1).tolist() != w["con_geom"][: 2 * n].tolist():
+        continue
+      total += 1
+      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
+      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
+      dp = np.abs(P[i, :n] - w["con_pos"][: 3 * n].reshape(n, 3)).max(axis=1, initial=0)
+      # fp32 GJK/EPA is a discrete search: a different simplex / polytope path moves a near-touching distance by
+      # ~1e-4 m and slides the witness point along parallel faces.  Everything must agree loosely, nearly all tightly.
+      assert dd.max(initial=0) < 4e-3 and dn.max(initial=0) < 5e-2
+      ncmp += n; tight += int(((dd < 2e-5) & (dn < 2e-3)).sum()); tight_pos += int((dp < 2e-4).sum())
+      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
+        seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
+  assert total >= 0.95 * 10 * W, total
+  assert ncmp > 200 and tight >= 0.97 * ncmp and tight_pos >= 0.93 * ncmp, (ncmp, tight, tight_pos)
+  if ground == "plane":
+    assert (0, 7) in seen and (7, 7) in seen
+  elif ground == "meshbox":
+    assert {(2, 7), (3, 7), (6, 7), (7, 7)} <= seen
+  else:
+    assert {(1, 2), (1, 3), (1, 6), (1, 7)} <= seen
+
+
 def test_g1_friction_domain_randomisation_per_world(g1):
   """expand_model_fields + per-world geom_friction (reference events.py:228-253, randomization.py:20-54)."""
   import torch

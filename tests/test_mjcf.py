@@ -104,8 +104,28 @@ def test_defaults_classes_degrees_and_limits():
 def test_unsupported_mjcf_raises():
   with pytest.raises(NotImplementedError):
     Spec.from_string("<mujoco><tendon><spatial name='t'/></tendon></mujoco>")
-  with pytest.raises(NotImplementedError):
+  with pytest.raises(ValueError):           # colliding mesh geom whose mesh asset is missing
     Spec.from_string("<mujoco><worldbody><body><geom type='mesh' mesh='m'/></body></worldbody></mujoco>").compile()
+  with pytest.raises(NotImplementedError):  # mesh inertia: bodies with mesh geoms need an explicit <inertial>
+    Spec.from_string("<mujoco><asset><mesh name='m' vertex='0 0 0 1 0 0 0 1 0 0 0 1'/></asset><worldbody><body><joint/>"
+                     "<geom type='mesh' mesh='m'/></body></worldbody></mujoco>").compile()
+
+
+def test_mesh_hull_and_hfield_assets_compile():
+  """K7 inputs: a mesh collides by its convex hull (interior vertices dropped), an hfield keeps normalised elevation."""
+  xml = """<mujoco><asset>
+      <mesh name="tet" vertex="0 0 0  1 0 0  0 1 0  0 0 1  0.2 0.2 0.2" scale="2 2 2"/>
+      <hfield name="hf" nrow="3" ncol="4" size="2 1.5 0.5 0.1" elevation="0 0 0 0  0 2 4 0  0 0 0 0"/></asset>
+    <worldbody><geom type="hfield" hfield="hf" name="ground"/>
+      <body pos="0 0 1"><freejoint/><inertial pos="0 0 0" mass="1" diaginertia="0.1 0.1 0.1"/>
+        <geom type="mesh" mesh="tet" name="g"/><geom type="mesh" mesh="tet" name="vis" contype="0" conaffinity="0"/></body>
+    </worldbody></mujoco>"""
+  m = Spec.from_string(xml).compile()
+  assert (m.nmesh, m.nmeshvert, m.nhfield, m.nhfielddata) == (1, 4, 1, 12)
+  assert sorted(map(tuple, m.mesh_vert.tolist())) == [(0, 0, 0), (0, 0, 2), (0, 2, 0), (2, 0, 0)]
+  assert m.geom_dataid.tolist() == [0, 0, -1] and m.geom_rbound[1] == pytest.approx(2.0)
+  assert m.hfield_data.max() == 1.0 and m.hfield_data.reshape(3, 4)[1, 1] == pytest.approx(0.5)
+  assert m.hfield_size.tolist() == [[2.0, 1.5, 0.5, 0.1]]
 
 
 def test_fixed_tendon_and_tendon_actuator_compile():

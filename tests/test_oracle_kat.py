@@ -284,3 +284,106 @@ def test_box_box_edge_contact_and_separation():
   assert np.allclose(w["con_frame"][:3], [0, 0, 1], atol=1e-9) and np.allclose(w["con_pos"][:3], [0, 0, 0.135], atol=1e-9)
   w = orc.new_world(); w["qpos"][2] = 2 * r + 0.01; orc.forward(w)
   assert w["ncon"][0] == 0
+
+
+# ---------------------------------------------------------------- K7: convex meshes and height fields
+def _quat(ax, ang):
+  ax = np.asarray(ax, float); ax /= np.linalg.norm(ax)
+  return [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
+
+
+def _contacts(w, m=None):
+  n = int(w["ncon"][0])
+  return [dict(dist=w["con_dist"][i], pos=w["con_pos"][3 * i:3 * i + 3], n=w["con_frame"][9 * i:9 * i + 3],
+               geom=tuple(w["con_geom"][2 * i:2 * i + 2])) for i in range(n)]
+
+
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_gjk_epa_agrees_with_analytic_box_colliders(dtype):
+  """A mesh whose hull is a box must collide like the box: EPA depth / normal against box-box SAT, sphere-box and
+  capsule-box closed forms, on the same poses (mesh floor 'slab' = box 1 x 1 x 0.1)."""
+  tol = 1e-7 if dtype == "f64" else 2e-5      # hull vertices are stored rounded to float32
+  q_tilt = _quat([1, 0.3, 0], 0.05)
+  for movers in (("mesh",), ("box",), ("sphere",), ("capsule",)):
+    res = {}
+    for ground in ("box", "meshbox"):
+      m = fx.compile_xml(fx.convex_scene(ground, movers))
+      orc = Oracle(m, dtype)
+      q = np.array(m.qpos0); q[0:3] = [0.2, -0.1, {"mesh": 0.055, "box": 0.055, "sphere": 0.09, "capsule": 0.13}[movers[0]]]
+      q[3:7] = q_tilt
+      res[ground] = _contacts(orc.forward(orc.new_world(q)))
+    a, b = res["box"], res["meshbox"]
+    assert len(b) == 1 and len(a) >= 1
+    deepest = min(a, key=lambda c: c["dist"])
+    assert b[0]["dist"] == pytest.approx(deepest["dist"], abs=tol)
+    # geom order: box floor / box mover -> the floor is geom 1; mesh floor / box mover -> the mover is geom 1 (lower
+    # type first), so that one normal flips
+    sign = -1.0 if movers[0] == "box" else 1.0
+    assert np.allclose(sign * np.asarray(b[0]["n"]), deepest["n"], atol=1e-6 if dtype == "f64" else 1e-4)
+    if movers[0] in ("sphere", "capsule"):
+      assert np.allclose(b[0]["pos"], deepest["pos"], atol=tol * 10)
+
+
+@pytest.mark.parametrize("dtype", ["f64", "f32"])
+def test_gjk_distance_inside_margin(dtype):
+  """Separated shapes within `margin` give a positive-distance contact (GJK branch, no EPA)."""
+  m = fx.compile_xml(fx.convex_scene("meshbox", ("sphere", "mesh"), margin=0.02))
+  orc = Oracle(m, dtype)
+  q = np.array(m.qpos0); q[0:3] = [0.0, 0.0, 0.11]; q[7:10] = [0.5, 0.0, 0.075]
+  cs = _contacts(orc.forward(orc.new_world(q)))
+  assert len(cs) == 2
+  tol = 1e-7 if dtype == "f64" else 1e-6
+  assert cs[0]["dist"] == pytest.approx(0.01, abs=tol) and cs[1]["dist"] == pytest.approx(0.015, abs=tol)   # sphere, cube
+  assert np.allclose(cs[0]["n"], [0, 0, -1], atol=1e-6) and np.allclose(cs[0]["pos"], [0, 0, 0.005], atol=1e-6)
+  q[2] = 0.125; q[9] = 0.085        # outside the margin
+  assert _contacts(orc.forward(orc.new_world(q))) == []
+
+
+def test_plane_mesh_manifold_of_a_resting_cube():
+  m = fx.compile_xml(fx.convex_scene("plane", ("mesh",)))
+  orc = Oracle(m, "f64")
+  q = np.array(m.qpos0); q[0:3] = [0.3, 0.2, 0.059]
+  cs = _contacts(orc.forward(orc.new_world(q)))
+  assert len(cs) == 4 and all(c["dist"] == pytest.approx(-0.001, abs=1e-7) for c in cs)
+  xy = sorted((round(c["pos"][0] - 0.3, 6), round(c["pos"][1] - 0.2, 6)) for c in cs)
+  assert xy == [(-0.1, -0.08), (-0.1, 0.08), (0.1, -0.08), (0.1, 0.08)]
+  # tilted by more than the 1 mm band: only the deepest corner remains
+  q[3:7] = _quat([1, 0, 0], 0.2)
+  cs = _contacts(orc.forward(orc.new_world(q)))
+  assert 1 <= len(cs) <= 2
+
+
+def test_height_field_flat_and_sloped():
+  """Flat field == plane at z = 0 for a sphere; a field that rises linearly in x gives the slope's normal."""
+  m = fx.compile_xml(fx.convex_scene("hfield", ("sphere",)))
+  orc = Oracle(m, "f64")
+  q = np.array(m.qpos0); q[0:3] = [0.13, -0.21, 0.095]
+  cs = _contacts(orc.forward(orc.new_world(q)))
+  assert len(cs) >= 1
+  for c in cs:
+    assert c["dist"] == pytest.approx(-0.005, abs=1e-9) and np.allclose(c["n"], [0, 0, 1], atol=1e-9)
+    assert np.allclose(c["pos"], [0.13, -0.21, -0.0025], atol=1e-9)
+  nrow = ncol = 9
+  elev = [c / (ncol - 1) for r in range(nrow) for c in range(ncol)]        # 0 .. 1 across x = -2 .. 2, top = 0.4
+  m = fx.compile_xml(fx.convex_scene("hfield", ("sphere",), hfield_elev=elev))
+  orc = Oracle(m, "f64")
+  slope = 0.4 / 4.0
+  nrm = np.array([-slope, 0, 1]) / np.hypot(slope, 1)
+  x, y = 0.13, -0.21
+  surf = 0.2 + slope * x
+  q[0:3] = np.array([x, y, surf]) + nrm * 0.097
+  cs = _contacts(orc.forward(orc.new_world(q)))
+  assert len(cs) >= 1
+  for c in cs:
+    assert c["dist"] == pytest.approx(-0.003, abs=1e-9) and np.allclose(c["n"], nrm, atol=1e-9)
+
+
+def test_mesh_cube_settles_on_plane_and_height_field():
+  for ground in ("plane", "hfield"):
+    m = fx.compile_xml(fx.convex_scene(ground, ("mesh", "sphere")))
+    orc = Oracle(m, "f64")
+    q = np.array(m.qpos0); q[2] = 0.1; q[3:7] = _quat([1, 1, 0], 0.3); q[7:10] = [0.6, 0.1, 0.15]
+    w = orc.new_world(q)
+    orc.step(w, 1500)
+    assert np.abs(w["qvel"]).max() < 5e-2
+    assert w["qpos"][2] == pytest.approx(0.06, abs=4e-3) and w["qpos"][9] == pytest.approx(0.1, abs=2e-3)
