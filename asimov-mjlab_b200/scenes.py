@@ -358,6 +358,9 @@ ASIMOV_TOE_ACTUATORS = (
 _ASV_FOOT = r"^(left|right)_(foot|toe)\d+_collision$"
 ASIMOV_FEET_ONLY_COLLISION = CollisionCfg(
   geom_names_expr=(_ASV_FOOT,), contype=0, conaffinity=1, condim=3, priority=1, friction=(0.8,))
+ASIMOV_FULL_COLLISION = CollisionCfg(
+  geom_names_expr=(".*_collision",), condim={_ASV_FOOT: 3, ".*_collision": 1}, priority={_ASV_FOOT: 1},
+  friction={_ASV_FOOT: (0.8,)})
 ASIMOV_KNEES_BENT = dict(pos=(0.0, 0.0, 0.73), rot=(1.0, 0.0, 0.0, 0.0), joint_pos={
   "left_hip_pitch_joint": 0.2, "right_hip_pitch_joint": -0.2, ".*_hip_roll_joint": 0.0, ".*_hip_yaw_joint": 0.0,
   "left_knee_joint": 0.4, "right_knee_joint": -0.4, "left_ankle_pitch_joint": -0.25, "right_ankle_pitch_joint": 0.25,
@@ -382,22 +385,20 @@ def ankle_pr_to_tendon(pitch_l, roll_l, pitch_r, roll_r):
                    L * pitch_r - D * roll_r, L * pitch_r + D * roll_r], axis=-1)
 
 
-def build_asimov_toe(xml_path, terrain="plane", terrain_seed=0, mesh_collision="drop") -> HostModel:
+def build_asimov_toe(xml_path, terrain="plane", terrain_seed=0, collision="feet_only") -> HostModel:
   """Compiled model of the fork's Asimov-toe velocity task (tasks/velocity/config/asimov_toe/env_cfgs.py:22-180):
   4 fixed ankle tendons with tendon position actuators from the XML, then the joint actuators of
-  ASIMOV_ARTICULATION, FEET_ONLY_COLLISION capsules, KNEES_BENT keyframe.
+  ASIMOV_ARTICULATION, KNEES_BENT keyframe.
 
-  The XML's link meshes are collision geoms too (class "collision", contype 0 / conaffinity 1: they hit the terrain
-  once the robot has fallen).  Convex-mesh colliders are SURVEY.md §8 row K7 and not built yet, so
-  mesh_collision="drop" clears their conaffinity and records it in meta["dropped_mesh_collision"]."""
+  collision="feet_only" is the task's own FEET_ONLY_COLLISION (asimov_toe_constants.py:243-250): the 20 foot / toe
+  capsules against the terrain; CollisionCfg.disable_other_geoms (spec_config.py:163,233-237) switches the link
+  meshes' collision off.  collision="full" is FULL_COLLISION (:219-227): every *_collision geom, link meshes included,
+  collides by its convex hull with the terrain and with the other links (K7: plane-mesh, GJK/EPA)."""
   robot = Spec.from_file(xml_path)
-  dropped = []
-  if mesh_collision == "drop":
-    for g in robot.geoms:
-      if g.type == "mesh" and (g.contype or g.conaffinity):
-        g.contype = g.conaffinity = 0
-        dropped.append(g.name)
-  apply_collision_cfg(robot, ASIMOV_FEET_ONLY_COLLISION)
+  if collision == "full":
+    apply_collision_cfg(robot, ASIMOV_FULL_COLLISION)
+  else:
+    apply_collision_cfg(robot, ASIMOV_FEET_ONLY_COLLISION)
   apply_actuator_cfgs(robot, ASIMOV_TOE_ACTUATORS)
   add_init_state_key(robot, **ASIMOV_KNEES_BENT)
   # zero-action ctrl of the tendon actuators: AnklePrToTendonAction with the default ankle angles as offset
@@ -427,7 +428,7 @@ def build_asimov_toe(xml_path, terrain="plane", terrain_seed=0, mesh_collision="
   velocity_sim_options(scene)
   m = scene.compile()
   m.meta = dict(task="Mjlab-Velocity-%s-Asimov-Toe" % ("Flat" if terrain == "plane" else "Rough"), nconmax=50, njmax=300,
-                decimation=4, dropped_mesh_collision=dropped)
+                decimation=4, collision=collision)
   if terrain != "plane":
     m.meta["terrain_origins"] = np.asarray(scene.terrain_origins).tolist()
     m.meta["terrain_seed"] = terrain_seed

@@ -32,6 +32,12 @@ def asimov_toe():
 
 
 @pytest.fixture(scope="session")
+def asimov_toe_full():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("asimov_toe_full_flat")
+
+
+@pytest.fixture(scope="session")
 def asimov_toe_rough():
   from asimov_mjlab_b200 import scenes
   return scenes.load_asset("asimov_toe_rough")

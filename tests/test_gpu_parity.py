@@ -373,6 +373,47 @@ def test_convex_mesh_and_height_field_contacts_match_oracle(ground):
     assert {(1, 2), (1, 3), (1, 6), (1, 7)} <= seen
 
 
+def test_asimov_toe_full_collision_link_meshes_match_oracle(asimov_toe_full):
+  """FULL_COLLISION variant of the Asimov-toe robot (asimov_toe_constants.py:219-227): 11 link meshes (convex hulls,
+  4111 vertices) + 20 capsules, terrain and self collisions.  Robots are dropped tilted so that they fall onto their
+  link meshes; contacts and the solved accelerations are compared at every 10th oracle state."""
+  import copy
+  import torch
+  m = copy.deepcopy(asimov_toe_full); m.opt.iterations = 30
+  W = 16
+  qpos, qvel, ctrl = asimov_states(m, W, seed=19, spread=0.3, vel=0.3, zlo=0.45, zhi=0.8)
+  rng = np.random.default_rng(19)
+  for w in range(W):
+    ax = rng.normal(size=3); ax /= np.linalg.norm(ax); ang = rng.normal(0, 1.0)
+    qpos[w, 3:7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True)
+  seen, total, ncmp, tight = set(), 0, 0, 0
+  for chunk in range(12):
+    for w in worlds:
+      orc.step(w, 10)
+    for f in ("qpos", "qvel", "qacc_warmstart"):
+      getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+    engine.forward(M, D)
+    for w in worlds:
+      orc.forward(w)
+    n_all = D.ncon.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9); Di = D.contact_dist.cpu().numpy()
+    for i, w in enumerate(worlds):
+      n = int(w["ncon"][0])
+      if int(n_all[i]) != n or G[i, :n].reshape(-1).tolist() != w["con_geom"][: 2 * n].tolist():
+        continue
+      total += 1
+      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
+      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
+      assert dd.max(initial=0) < 4e-3 and dn.max(initial=0) < 5e-2
+      ncmp += n; tight += int(((dd < 2e-5) & (dn < 2e-3)).sum())
+      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
+        seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
+  assert total >= 0.9 * 12 * W, total
+  assert ncmp > 300 and tight >= 0.97 * ncmp, (ncmp, tight)
+  assert (0, 7) in seen and ((7, 7) in seen or (3, 7) in seen), seen
+
+
 def test_g1_friction_domain_randomisation_per_world(g1):
   """expand_model_fields + per-world geom_friction (reference events.py:228-253, randomization.py:20-54)."""
   import torch

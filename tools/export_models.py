@@ -26,4 +26,8 @@ for terr in ("plane", "rough"):
   name = "asimov_toe_flat" if terr == "plane" else "asimov_toe_rough"
   scenes.save_model(a, os.path.join(scenes.ASSET_DIR, name + ".npz"))
   print(name, ": nq", a.nq, "nv", a.nv, "nu", a.nu, "nbody", a.nbody, "ngeom", a.ngeom, "ntendon", a.ntendon,
-        "nsensordata", a.nsensordata, "meaninertia", a.stat.meaninertia)
+        "nmesh", a.nmesh, "nmeshvert", a.nmeshvert, "nsensordata", a.nsensordata, "meaninertia", a.stat.meaninertia)
+
+a = scenes.build_asimov_toe(os.path.join(zoo, "asimov/xmls/asimov_toe.xml"), terrain="plane", collision="full")
+scenes.save_model(a, os.path.join(scenes.ASSET_DIR, "asimov_toe_full_flat.npz"))
+print("asimov_toe_full_flat: ngeom", a.ngeom, "nmesh", a.nmesh, "nmeshvert", a.nmeshvert)
