@@ -913,7 +913,7 @@ def _compile(spec: Spec) -> HostModel:
   m.hfield_size = arr([h.size for h in hf], float, (len(hf), 4))
   m.hfield_nrow = arr([h.nrow for h in hf], np.int32); m.hfield_ncol = arr([h.ncol for h in hf], np.int32)
   m.hfield_adr = arr(np.concatenate([[0], np.cumsum([h.nrow*h.ncol for h in hf])[:-1]]) if hf else [], np.int32)
-  m.hfield_data = np.concatenate([np.asarray(h.data, float).reshape(-1) for h in hf]) if hf else np.zeros(0)
+  m.hfield_data = (np.concatenate([np.asarray(h.data, np.float32).reshape(-1) for h in hf]) if hf else np.zeros(0, np.float32))
   m.nhfielddata = int(m.hfield_data.size)
   m.site_bodyid = arr(S["bodyid"], np.int32); m.site_pos = arr(S["pos"], float, (nsite, 3))
   m.site_quat = arr(S["quat"], float, (nsite, 4))

@@ -322,14 +322,16 @@ def build_go1(xml_path, terrain="plane", terrain_seed=0) -> HostModel:
   else:
     from . import terrains
     scene = Spec()
-    terrains.add_rough_terrain(scene, seed=terrain_seed)
+    # "rough_hf": the height-field sub-terrains that terrains/config.py:28-53 keeps commented out, enabled
+    terrains.add_rough_terrain(scene, seed=terrain_seed, cfg=terrains.rough_terrains_hf_cfg() if terrain == "rough_hf" else None)
     ent_bodies = {"robot": tuple(b.name for b in robot.bodies[1:]), "robot#geoms": tuple(g.name for g in robot.geoms if g.name)}
     scene.attach(robot, prefix="robot/")
     for sc in _go1_sensors():
       add_contact_sensor(scene, sc, ent_bodies)
   velocity_sim_options(scene)
   m = scene.compile()
-  m.meta = dict(task="Mjlab-Velocity-%s-Unitree-Go1" % ("Flat" if terrain == "plane" else "Rough"), nconmax=50, njmax=300, decimation=4)
+  m.meta = dict(task="Mjlab-Velocity-%s-Unitree-Go1" % ("Flat" if terrain == "plane" else "Rough"), nconmax=50, njmax=300, decimation=4,
+                terrain=terrain)
   if terrain != "plane":
     m.meta["terrain_origins"] = np.asarray(scene.terrain_origins).tolist()   # [num_rows][num_cols][3] spawn points
     m.meta["terrain_seed"] = terrain_seed

@@ -8,6 +8,11 @@ Follows the reference's generator for the sub-terrains that are ACTIVE in its de
   * BoxInvertedPyramidStairsTerrainCfg     src/mjlab/terrains/primitive_terrains.py:225-373
   * make_border                            src/mjlab/terrains/utils.py:36-107
   * outer border                           src/mjlab/terrains/terrain_generator.py:250-275
+  * HfPyramidSlopedTerrainCfg              src/mjlab/terrains/heightfield_terrains.py:104-252
+  * HfRandomUniformTerrainCfg              src/mjlab/terrains/heightfield_terrains.py:255-391
+  * HfWaveTerrainCfg                       src/mjlab/terrains/heightfield_terrains.py:394-499
+    (the height-field ones are commented out of ROUGH_TERRAINS_CFG "due to compilation issues in mujoco-warp",
+    config.py:28-53; ROUGH_TERRAINS_HF_CFG below is that commented configuration, enabled)
 Colours and lights are not physics and are left out.  Geoms are named terrain_<k> in creation order
 (terrain_generator.py:110-113), all on one static body "terrain".
 """
@@ -31,6 +36,41 @@ class StairsCfg:
 @dataclass
 class FlatCfg:
   proportion: float
+
+
+@dataclass
+class HfPyramidSlopeCfg:
+  proportion: float
+  slope_range: tuple = (0.0, 1.0)
+  platform_width: float = 2.0
+  border_width: float = 0.25
+  inverted: bool = False
+  horizontal_scale: float = 0.1
+  vertical_scale: float = 0.005
+  base_thickness_ratio: float = 1.0
+
+
+@dataclass
+class HfRandomUniformCfg:
+  proportion: float
+  noise_range: tuple = (0.02, 0.10)
+  noise_step: float = 0.02
+  downsampled_scale: float | None = None
+  border_width: float = 0.25
+  horizontal_scale: float = 0.1
+  vertical_scale: float = 0.005
+  base_thickness_ratio: float = 1.0
+
+
+@dataclass
+class HfWaveCfg:
+  proportion: float
+  amplitude_range: tuple = (0.0, 0.2)
+  num_waves: float = 4
+  border_width: float = 0.25
+  horizontal_scale: float = 0.1
+  vertical_scale: float = 0.005
+  base_thickness_ratio: float = 0.25
 
 
 @dataclass
@@ -98,8 +138,99 @@ def _stairs(c: StairsCfg, size, difficulty):
   return out, origin
 
 
+def rough_terrains_hf_cfg() -> RoughTerrainCfg:
+  """ROUGH_TERRAINS_CFG with its commented-out height-field sub-terrains enabled (terrains/config.py:14-53)."""
+  return RoughTerrainCfg(sub_terrains=(
+    FlatCfg(0.2), StairsCfg(0.2), StairsCfg(0.2, inverted=True),
+    HfPyramidSlopeCfg(0.1), HfPyramidSlopeCfg(0.1, inverted=True), HfRandomUniformCfg(0.2), HfWaveCfg(0.2)))
+
+
+def _hf_finish(noise, c, size):
+  """Common tail of the reference's hfield sub-terrains: int16 elevation -> normalised data + hfield size."""
+  emin, emax = int(noise.min()), int(noise.max())
+  erange = emax - emin if emax != emin else 1
+  max_h = erange * c.vertical_scale
+  base = max_h * c.base_thickness_ratio
+  norm = (noise - emin) / erange
+  return norm, [size[0] / 2, size[1] / 2, max_h, base], max_h, base
+
+
+def _hf_inner(c, size):
+  bp = int(c.border_width / c.horizontal_scale)
+  wp, lp = int(size[0] / c.horizontal_scale), int(size[1] / c.horizontal_scale)
+  return bp, wp, lp, wp - 2 * bp, lp - 2 * bp
+
+
+def _hf_pyramid(c: HfPyramidSlopeCfg, size, difficulty, rng):
+  slope = c.slope_range[0] + difficulty * (c.slope_range[1] - c.slope_range[0])
+  if c.inverted:
+    slope = -slope
+  bp, wp, lp, iw, il = _hf_inner(c, size)
+  noise = np.zeros((wp, lp), dtype=np.int16)
+  w, l = (iw, il) if bp > 0 else (wp, lp)
+  span = iw * c.horizontal_scale if bp > 0 else size[0]
+  height_max = int(slope * span / 2 / c.vertical_scale)
+  cx, cy = int(w / 2), int(l / 2)
+  xx = ((cx - np.abs(cx - np.arange(w))) / cx).reshape(w, 1)
+  yy = ((cy - np.abs(cy - np.arange(l))) / cy).reshape(1, l)
+  raw = height_max * xx * yy
+  pf = int(c.platform_width / c.horizontal_scale / 2)
+  xp, yp = w // 2 - pf, l // 2 - pf
+  zp = raw[xp, yp] if xp >= 0 and yp >= 0 else 0
+  raw = np.clip(raw, min(0, zp), max(0, zp))
+  if bp > 0:
+    noise[bp:-bp, bp:-bp] = np.rint(raw).astype(np.int16)
+  else:
+    noise = np.rint(raw).astype(np.int16)
+  norm, hsize, max_h, base = _hf_finish(noise, c, size)
+  zoff = -max_h if c.inverted else 0.0
+  spawn = zoff - base if c.inverted else max_h - base
+  return norm, hsize, [size[0] / 2, size[1] / 2, zoff], np.array([size[0] / 2, size[1] / 2, spawn])
+
+
+def _hf_random(c: HfRandomUniformCfg, size, difficulty, rng):
+  from scipy import interpolate
+  ds = c.horizontal_scale if c.downsampled_scale is None else c.downsampled_scale
+  bp, wp, lp, iw, il = _hf_inner(c, size)
+  noise = np.zeros((wp, lp), dtype=np.int16)
+  inner = (iw * c.horizontal_scale, il * c.horizontal_scale) if bp > 0 else (size[0], size[1])
+  w, l = (iw, il) if bp > 0 else (wp, lp)
+  wd, ld = int(inner[0] / ds), int(inner[1] / ds)
+  hmin, hmax, hstep = int(c.noise_range[0] / c.vertical_scale), int(c.noise_range[1] / c.vertical_scale), int(c.noise_step / c.vertical_scale)
+  coarse = rng.choice(np.arange(hmin, hmax + hstep, hstep), size=(wd, ld))
+  f = interpolate.RectBivariateSpline(np.linspace(0, inner[0], wd), np.linspace(0, inner[1], ld), coarse)
+  z = f(np.linspace(0, inner[0], w), np.linspace(0, inner[1], l))
+  if bp > 0:
+    noise[bp:-bp, bp:-bp] = np.rint(z).astype(np.int16)
+  else:
+    noise = np.rint(z).astype(np.int16)
+  norm, hsize, max_h, base = _hf_finish(noise, c, size)
+  spawn = (c.noise_range[0] + c.noise_range[1]) / 2
+  return norm, hsize, [size[0] / 2, size[1] / 2, 0.0], np.array([size[0] / 2, size[1] / 2, spawn])
+
+
+def _hf_wave(c: HfWaveCfg, size, difficulty, rng):
+  amp = c.amplitude_range[0] + difficulty * (c.amplitude_range[1] - c.amplitude_range[0])
+  bp, wp, lp, iw, il = _hf_inner(c, size)
+  noise = np.zeros((wp, lp), dtype=np.int16)
+  w, l = (iw, il) if bp > 0 else (wp, lp)
+  ap = int(0.5 * amp / c.vertical_scale)
+  k = 2 * np.pi / (l / c.num_waves)
+  raw = ap * (np.cos(np.arange(l).reshape(1, l) * k) + np.sin(np.arange(w).reshape(w, 1) * k))
+  if bp > 0:
+    noise[bp:-bp, bp:-bp] = np.rint(raw).astype(np.int16)
+  else:
+    noise = np.rint(raw).astype(np.int16)
+  norm, hsize, max_h, base = _hf_finish(noise, c, size)
+  return norm, hsize, [size[0] / 2, size[1] / 2, -max_h / 2], np.array([size[0] / 2, size[1] / 2, 0.0])
+
+
+_HF = {HfPyramidSlopeCfg: _hf_pyramid, HfRandomUniformCfg: _hf_random, HfWaveCfg: _hf_wave}
+
+
 def generate(cfg: RoughTerrainCfg, seed: int):
-  """-> (list of (half_size[3], pos[3]) boxes in creation order, terrain_origins[num_rows, num_cols, 3])."""
+  """-> (geoms in creation order: (half_size[3], pos[3]) boxes or ("hfield", data[nrow, ncol] in [0, 1], size[4], pos[3]),
+  terrain_origins[num_rows, num_cols, 3])."""
   rng = np.random.default_rng(seed)
   props = np.array([s.proportion for s in cfg.sub_terrains], float)
   props /= props.sum()
@@ -111,8 +242,12 @@ def generate(cfg: RoughTerrainCfg, seed: int):
       d = lo + (hi - lo) * ((row + rng.uniform()) / cfg.num_rows)
       wp = np.array([-cfg.num_rows * cfg.size[0] * 0.5 + row * cfg.size[0], -cfg.num_cols * cfg.size[1] * 0.5 + col * cfg.size[1], 0.0])
       sc = cfg.sub_terrains[sub_idx[col]]
-      tile, org = _flat(cfg.size) if isinstance(sc, FlatCfg) else _stairs(sc, cfg.size, d)
-      boxes += [(h, p + wp) for h, p in tile]
+      if type(sc) in _HF:
+        norm, hsize, gpos, org = _HF[type(sc)](sc, cfg.size, d, rng)
+        boxes.append(("hfield", norm, hsize, np.asarray(gpos, float) + wp))      # kept in creation order with the boxes
+      else:
+        tile, org = _flat(cfg.size) if isinstance(sc, FlatCfg) else _stairs(sc, cfg.size, d)
+        boxes += [(h, p + wp) for h, p in tile]
       origins[row, col] = org + wp
   bs = (cfg.num_rows * cfg.size[0] + 2 * cfg.border_width, cfg.num_cols * cfg.size[1] + 2 * cfg.border_width)
   _make_border(boxes, bs, (cfg.num_rows * cfg.size[0], cfg.num_cols * cfg.size[1]), abs(cfg.border_height),
@@ -125,8 +260,14 @@ def add_rough_terrain(scene, seed=0, cfg: RoughTerrainCfg | None = None):
   cfg = cfg or RoughTerrainCfg()
   boxes, origins = generate(cfg, seed)
   body = scene.worldbody.add_body(name="terrain")
-  for k, (half, pos) in enumerate(boxes):
-    body.add_geom(name=f"terrain_{k}", type="box", size=[float(x) for x in half], pos=[float(x) for x in pos])
+  for k, item in enumerate(boxes):
+    if isinstance(item[0], str):
+      _, norm, hsize, pos = item
+      scene.add_hfield(f"hfield_{k}", norm, hsize)
+      body.add_geom(name=f"terrain_{k}", type="hfield", hfield=f"hfield_{k}", pos=[float(x) for x in pos])
+    else:
+      half, pos = item
+      body.add_geom(name=f"terrain_{k}", type="box", size=[float(x) for x in half], pos=[float(x) for x in pos])
   scene.terrain_origins = origins
   return origins
 

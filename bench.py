@@ -28,6 +28,8 @@ WORKLOADS = {
   "go1_flat": ("go1_flat", "Mjlab-Velocity-Flat-Unitree-Go1 physics step, random actions"),
   "asimov_toe_flat": ("asimov_toe_flat", "Asimov-toe velocity task physics step on the plane (fixed ankle tendons + tendon position actuators; mesh collision geoms dropped), random actions"),
   "asimov_toe_rough": ("asimov_toe_rough", "Asimov-toe velocity task physics step on the reference's default box terrain, random actions"),
+  "go1_rough_hf": ("go1_rough_hf", "Go1 rough task with the generator's height-field sub-terrains enabled (terrains/config.py:28-53, commented out in the reference), random actions (BASELINE.json configs[2], hfield variant)"),
+  "asimov_toe_full_flat": ("asimov_toe_full_flat", "Asimov-toe, FULL_COLLISION (11 link meshes by convex hull + 20 capsules, self collisions) on the plane, random actions"),
   "go1_rough": ("go1_rough", "Mjlab-Velocity-Rough-Unitree-Go1 physics step on the reference's default box terrain, random actions (BASELINE.json configs[2], box variant)"),
 }
 

@@ -44,6 +44,12 @@ def asimov_toe_rough():
 
 
 @pytest.fixture(scope="session")
+def go1_rough_hf():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("go1_rough_hf")
+
+
+@pytest.fixture(scope="session")
 def go1_rough():
   from asimov_mjlab_b200 import scenes
   return scenes.load_asset("go1_rough")

@@ -414,6 +414,53 @@ def test_asimov_toe_full_collision_link_meshes_match_oracle(asimov_toe_full):
   assert (0, 7) in seen and ((7, 7) in seen or (3, 7) in seen), seen
 
 
+def test_go1_on_height_field_terrain_matches_oracle(go1_rough_hf):
+  """Go1 on the generator's height-field sub-terrains (pyramid slope, random rough, wave; 80 x 80 fields found through
+  the static-geom grid): sphere / capsule / box against hfield prisms.  Oracle-driven, compared every 10 steps."""
+  import torch
+  m = go1_rough_hf
+  W = 16
+  org = np.asarray(m.meta["terrain_origins"])
+  hf_geoms = [g for g in range(m.ngeom) if m.geom_type[g] == 1]
+  assert len(hf_geoms) == 100
+  rng = np.random.default_rng(41)
+  qpos, qvel, ctrl = legged_states(m, W, seed=41, spread=0.2, vel=0.3)
+  z0 = m.keys["robot/init_state"]["qpos"][2]
+  tiles = [(r, c) for c in range(org.shape[1]) for r in range(org.shape[0])
+           if org[r, c, 2] >= 0.0 and any(abs(m.geom_pos[g][0] - org[r, c, 0]) < 1e-6 and abs(m.geom_pos[g][1] - org[r, c, 1]) < 1e-6 for g in hf_geoms)]
+  assert len(tiles) >= 40
+  for w in range(W):
+    r, c = tiles[rng.integers(len(tiles))]
+    qpos[w, 0:2] = org[r, c, :2] + rng.uniform(-2.5, 2.5, 2)
+    qpos[w, 2] = org[r, c, 2] + z0 + rng.uniform(0.0, 0.15)
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True)
+  seen, total, ncmp, tight = set(), 0, 0, 0
+  for chunk in range(8):
+    for w in worlds:
+      orc.step(w, 10)
+    for f in ("qpos", "qvel", "qacc_warmstart"):
+      getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+    engine.forward(M, D)
+    for w in worlds:
+      orc.forward(w)
+    n_all = D.ncon.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9); Di = D.contact_dist.cpu().numpy()
+    for i, w in enumerate(worlds):
+      n = int(w["ncon"][0])
+      if int(n_all[i]) != n or G[i, :n].reshape(-1).tolist() != w["con_geom"][: 2 * n].tolist():
+        continue
+      total += 1
+      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
+      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
+      assert dd.max(initial=0) < 4e-3 and dn.max(initial=0) < 5e-2
+      ncmp += n; tight += int(((dd < 2e-5) & (dn < 2e-3)).sum())
+      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
+        seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
+  assert total >= 0.9 * 8 * W, total
+  assert ncmp > 300 and tight >= 0.97 * ncmp, (ncmp, tight)
+  assert (1, 2) in seen and (1, 3) in seen, seen
+
+
 def test_g1_friction_domain_randomisation_per_world(g1):
   """expand_model_fields + per-world geom_friction (reference events.py:228-253, randomization.py:20-54)."""
   import torch

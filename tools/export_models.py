@@ -14,9 +14,9 @@ scenes.save_model(m, os.path.join(scenes.ASSET_DIR, "g1_flat.npz"))
 print("g1_flat: nq", m.nq, "nv", m.nv, "nu", m.nu, "nbody", m.nbody, "ngeom", m.ngeom,
       "nsite", m.nsite, "nsensordata", m.nsensordata, "meaninertia", m.stat.meaninertia)
 
-for terr in ("plane", "rough"):
+for terr in ("plane", "rough", "rough_hf"):
   g = scenes.build_go1(os.path.join(zoo, "unitree_go1/xmls/go1.xml"), terrain=terr)
-  name = "go1_flat" if terr == "plane" else "go1_rough"
+  name = {"plane": "go1_flat", "rough": "go1_rough", "rough_hf": "go1_rough_hf"}[terr]
   scenes.save_model(g, os.path.join(scenes.ASSET_DIR, name + ".npz"))
   print(name, ": nq", g.nq, "nv", g.nv, "nu", g.nu, "nbody", g.nbody, "ngeom", g.ngeom,
         "nsite", g.nsite, "nsensordata", g.nsensordata, "meaninertia", g.stat.meaninertia)
