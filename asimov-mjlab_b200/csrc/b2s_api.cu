@@ -398,6 +398,30 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     d.pose_geom = up.raw(pg); d.pose_site = up.raw(ps); d.stat_geom = up.raw(sg); d.stat_site = up.raw(ss);
   }
   d.geom_contype = up.i(s->geom_contype, s->ngeom); d.geom_conaffinity = up.i(s->geom_conaffinity, s->ngeom);
+  {
+    // broadphase volumes: a box in the geom frame (centre offset + half sizes) and the radius of the sphere around it
+    std::vector<float> bcen((size_t)3 * s->ngeom, 0.f), bsize((size_t)3 * s->ngeom, 0.f), brad((size_t)s->ngeom, 0.f);
+    for (int g = 0; g < s->ngeom; g++) {
+      const double* sz = s->geom_size + 3 * g;
+      float* bs = &bsize[(size_t)3 * g];
+      const int t = s->geom_type[g];
+      brad[g] = (float)s->geom_rbound[g];
+      bs[0] = bs[1] = bs[2] = brad[g];
+      if (t == B2S_GEOM_SPHERE) { bs[0] = bs[1] = bs[2] = (float)sz[0]; }
+      else if (t == B2S_GEOM_CAPSULE) { bs[0] = bs[1] = (float)sz[0]; bs[2] = (float)(sz[0] + sz[1]); }
+      else if (t == B2S_GEOM_BOX) { bs[0] = (float)sz[0]; bs[1] = (float)sz[1]; bs[2] = (float)sz[2]; }
+      else if (t == B2S_GEOM_MESH && s->geom_dataid[g] >= 0 && s->geom_dataid[g] < s->nmesh) {
+        const int id = s->geom_dataid[g], a0 = s->mesh_vertadr[id], nvt = s->mesh_vertnum[id];
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (int i = a0; i < a0 + nvt; i++) for (int a = 0; a < 3; a++) { lo[a] = std::fmin(lo[a], s->mesh_vert[3*i + a]); hi[a] = std::fmax(hi[a], s->mesh_vert[3*i + a]); }
+        double r2 = 0;
+        for (int a = 0; a < 3; a++) { bcen[(size_t)3*g + a] = (float)(0.5*(lo[a] + hi[a])); bs[a] = (float)(0.5*(hi[a] - lo[a]) * 1.000001 + 1e-7); }
+        for (int i = a0; i < a0 + nvt; i++) { double q = 0; for (int a = 0; a < 3; a++) { const double e = s->mesh_vert[3*i + a] - 0.5*(lo[a] + hi[a]); q += e*e; } r2 = std::fmax(r2, q); }
+        brad[g] = (float)(std::sqrt(r2) * 1.000001 + 1e-7);
+      }
+    }
+    d.geom_bcen = up.raw(bcen); d.geom_bsize = up.raw(bsize); d.geom_brad = up.raw(brad);
+  }
   d.col_maxc = col_maxc <= 2 ? 2 : (col_maxc <= 4 ? 4 : 8);
   d.col_convex = col_convex;
   d.geom_dataid = up.i(s->geom_dataid, s->ngeom);

@@ -71,6 +71,7 @@ struct ModelDev {
   int col_convex;    // 1: some pair needs the GJK/EPA, plane-mesh or height-field colliders
   const int *geom_dataid, *mesh_vertadr, *mesh_vertnum, *hfield_nrow, *hfield_ncol, *hfield_adr;
   const float *mesh_vert, *hfield_size, *hfield_data;
+  const float *geom_bcen, *geom_bsize, *geom_brad;   // broadphase volume: local box (centre offset, half sizes) and its radius
   int ntendon, nwrap;
   const int *tendon_adr, *tendon_num, *wrap_dof, *wrap_qpos;
   const float *wrap_coef, *tendon_stiffness, *tendon_damping, *tendon_lengthspring;

@@ -297,6 +297,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   unsigned* s_list = (unsigned*)b2s_smem + warp * (2 * B2S_MAX_SURVIVORS + 1);
   unsigned* s_sort = s_list + B2S_MAX_SURVIVORS;
   int* s_cnt = (int*)(s_sort + B2S_MAX_SURVIVORS);
+  CvxStage* s_stage = (CvxStage*)((unsigned*)b2s_smem + B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1)) + warp * (MAXC + 32);
   if (m.disableflags & (B2S_DSBL_CONSTRAINT | B2S_DSBL_CONTACT)) { if (lane == 0) d.ncon[w] = 0; return; }
   const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
   const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
@@ -310,24 +311,38 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
     if (p < m.npair) {
       const int g1 = m.pair_geom[2 * p], g2 = m.pair_geom[2 * p + 1];
       const float margin = fmaxf(m.geom_margin[g1], m.geom_margin[g2]);
-      v3 dif = ld3(gx + 3 * g2) - ld3(gx + 3 * g1);
-      if (m.geom_type[g1] == B2S_GEOM_PLANE) {
-        v3 n = mk3(gm[9 * g1 + 2], gm[9 * g1 + 5], gm[9 * g1 + 8]);
-        pass = dot(dif, n) <= m.geom_rbound[g2] + margin;
-      } else if (CONVEX && m.geom_type[g1] == B2S_GEOM_HFIELD) {
+      const int ty1 = m.geom_type[g1];
+      // broadphase volume of geom 2: box (centre c2, axes R2, half sizes b2) inside a sphere of radius brad
+      const m33 R2 = ldm(gm + 9 * g2);
+      const v3 b2 = ld3(m.geom_bsize + 3 * g2);
+      const v3 c2 = ld3(gx + 3 * g2) + (CONVEX ? mulv(R2, ld3(m.geom_bcen + 3 * g2)) : mk3(0.f, 0.f, 0.f));
+      if (ty1 == B2S_GEOM_PLANE) {
+        const v3 n = mk3(gm[9 * g1 + 2], gm[9 * g1 + 5], gm[9 * g1 + 8]);
+        const v3 nl = mulTv(R2, n);
+        const float ext = fabsf(nl.x) * b2.x + fabsf(nl.y) * b2.y + fabsf(nl.z) * b2.z;     // box extent along the normal
+        pass = dot(c2 - ld3(gx + 3 * g1), n) <= fminf(ext, m.geom_brad[g2]) + margin;
+      } else if (CONVEX && ty1 == B2S_GEOM_HFIELD) {
         // bounding sphere of geom 2 against the field's box, in the field's frame
         const float* hs = m.hfield_size + 4 * m.geom_dataid[g1];
-        const v3 pl = mulTv(ldm(gm + 9 * g1), dif);
-        const float r = m.geom_rbound[g2] + margin;
+        const v3 pl = mulTv(ldm(gm + 9 * g1), c2 - ld3(gx + 3 * g1));
+        const float r = m.geom_brad[g2] + margin;
         pass = !(pl.x + r < -hs[0] || pl.x - r > hs[0] || pl.y + r < -hs[1] || pl.y - r > hs[1] || pl.z - r > hs[2] || pl.z + r < -hs[3]);
       } else {
-        const float bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
-        pass = dot(dif, dif) <= bound * bound;
-        if (pass && m.geom_type[g2] == B2S_GEOM_BOX) {   // bounding sphere of geom 1 against the oriented box 2
-          const v3 loc = mulTv(ldm(gm + 9 * g2), dif * -1.f), h = ld3(m.geom_size + 3 * g2);
-          const float ex = fmaxf(fabsf(loc.x) - h.x, 0.f), ey = fmaxf(fabsf(loc.y) - h.y, 0.f), ez = fmaxf(fabsf(loc.z) - h.z, 0.f);
-          const float rb = m.geom_rbound[g1] + margin;
-          pass = ex * ex + ey * ey + ez * ez <= rb * rb;
+        const m33 R1 = ldm(gm + 9 * g1);
+        const v3 c1 = ld3(gx + 3 * g1) + (CONVEX ? mulv(R1, ld3(m.geom_bcen + 3 * g1)) : mk3(0.f, 0.f, 0.f));
+        const v3 dif = c2 - c1;
+        const float r1 = m.geom_brad[g1] + margin, r2 = m.geom_brad[g2];
+        pass = dot(dif, dif) <= (r1 + r2) * (r1 + r2);
+        if (pass) {           // sphere 1 against box 2, then sphere 2 against box 1
+          const v3 l = mulTv(R2, dif);
+          const float ex = fmaxf(fabsf(l.x) - b2.x, 0.f), ey = fmaxf(fabsf(l.y) - b2.y, 0.f), ez = fmaxf(fabsf(l.z) - b2.z, 0.f);
+          pass = ex * ex + ey * ey + ez * ez <= r1 * r1;
+        }
+        if (pass) {
+          const v3 l = mulTv(R1, dif), b1 = ld3(m.geom_bsize + 3 * g1);
+          const float ex = fmaxf(fabsf(l.x) - b1.x, 0.f), ey = fmaxf(fabsf(l.y) - b1.y, 0.f), ez = fmaxf(fabsf(l.z) - b1.z, 0.f);
+          const float rr = r2 + margin;
+          pass = ex * ex + ey * ey + ez * ez <= rr * rr;
         }
       }
       key = ((unsigned)min(g1, g2) << 16) | (unsigned)max(g1, g2);
@@ -344,8 +359,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
     __syncwarp();
     for (int k = lane; k < m.ndyngeom; k += 32) {
       const int g = m.dyn_geom[k];
-      const v3 c = ld3(gx + 3 * g);
-      const float r = m.geom_rbound[g] + fmaxf(m.geom_margin[g], m.grid_margin);
+      const v3 c = ld3(gx + 3 * g) + (CONVEX ? mulv(ldm(gm + 9 * g), ld3(m.geom_bcen + 3 * g)) : mk3(0.f, 0.f, 0.f));
+      const float r = m.geom_brad[g] + fmaxf(m.geom_margin[g], m.grid_margin);
       const int ix0 = max((int)floorf((c.x - r - m.grid_x0) * m.grid_inv), 0), ix1 = min((int)floorf((c.x + r - m.grid_x0) * m.grid_inv), m.grid_nx - 1);
       const int iy0 = max((int)floorf((c.y - r - m.grid_y0) * m.grid_inv), 0), iy1 = min((int)floorf((c.y + r - m.grid_y0) * m.grid_inv), m.grid_ny - 1);
       for (int ix = ix0; ix <= ix1; ix++) for (int iy = iy0; iy <= iy1; iy++) {
@@ -387,6 +402,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
     RawCon rc[MAXC];
     int n = 0, g1 = 0, g2 = 0;
     float margin = 0.f;
+    bool cvx = false;
     if (i < nsurv) {
       const unsigned key = s_list[i];
       g1 = (int)(key >> 16); g2 = (int)(key & 0xffffu);
@@ -407,29 +423,48 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t2 == B2S_GEOM_CAPSULE) n = capsule_capsule(rc, margin, p1, m1, s1, p2, m2, s2);
         else if (t2 == B2S_GEOM_BOX) n = capsule_box(rc, margin, p1, m1, s1, p2, m2, s2);
       } else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) { if constexpr (MAXC >= 8) n = box_box(rc, margin, p1, m1, s1, p2, m2, s2); }
-      if constexpr (CONVEX) {
-        if (t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_HFIELD) {
-          Cvx B;
-          B.pos = p2; B.mat = m2; B.size = s2; B.vert = nullptr; B.nvert = 0; B.world = false; B.radius = 0.f;
-          if (t2 == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = s2.x; }
-          else if (t2 == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = s2.x; }
-          else if (t2 == B2S_GEOM_BOX) B.type = CVX_BOX;
-          else { const int id = m.geom_dataid[g2]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
-          if (t1 == B2S_GEOM_PLANE) n = plane_mesh(rc, margin, p1, m1, p2, m2, B.vert, B.nvert);
-          else if (t1 == B2S_GEOM_HFIELD) {
-            const int h = m.geom_dataid[g1];
-            n = hfield_convex<MAXC>(rc, margin, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h],
-                                    p1, m1, B, m.geom_rbound[g2]);
-          } else {
-            Cvx A;
-            A.pos = p1; A.mat = m1; A.size = s1; A.vert = nullptr; A.nvert = 0; A.world = false; A.radius = 0.f;
-            if (t1 == B2S_GEOM_SPHERE) { A.type = CVX_POINT; A.radius = s1.x; }
-            else if (t1 == B2S_GEOM_CAPSULE) { A.type = CVX_SEGMENT; A.radius = s1.x; }
-            else if (t1 == B2S_GEOM_BOX) A.type = CVX_BOX;
-            else { const int id = m.geom_dataid[g1]; A.type = CVX_VERTS; A.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; A.nvert = m.mesh_vertnum[id]; }
-            n = convex_pair(rc, margin, A, B);
-          }
+      if constexpr (CONVEX) cvx = (t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_HFIELD);
+    }
+    if constexpr (CONVEX) {
+      // mesh / height-field pairs of this pass, one at a time with the whole warp: hull scans are lane-strided, a
+      // height field's prisms are handed out one per lane; the results go back to the pair's lane through smem
+      unsigned todo = __ballot_sync(FULL, cvx);
+      while (todo) {
+        const int L = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int bg1 = __shfl_sync(FULL, g1, L), bg2 = __shfl_sync(FULL, g2, L);
+        const float bm = __shfl_sync(FULL, margin, L);
+        const int t1 = m.geom_type[bg1], t2 = m.geom_type[bg2];
+        const v3 p1 = ld3(gx + 3 * bg1), p2 = ld3(gx + 3 * bg2), s1 = ld3(m.geom_size + 3 * bg1), s2 = ld3(m.geom_size + 3 * bg2);
+        const m33 m1 = ldm(gm + 9 * bg1), m2 = ldm(gm + 9 * bg2);
+        Cvx A, B;
+        B.pos = p2; B.mat = m2; B.size = s2; B.vert = nullptr; B.nvert = 0; B.world = false; B.coop = false; B.radius = 0.f;
+        if (t2 == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = s2.x; }
+        else if (t2 == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = s2.x; }
+        else if (t2 == B2S_GEOM_BOX) B.type = CVX_BOX;
+        else { const int id = m.geom_dataid[bg2]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
+        int nres;
+        if (t1 == B2S_GEOM_PLANE) nres = plane_mesh_warp(s_stage, bm, p1, m1, p2, m2, B.vert, B.nvert, lane);
+        else if (t1 == B2S_GEOM_HFIELD) {
+          const int h = m.geom_dataid[bg1];
+          nres = hfield_convex_warp<MAXC>(s_stage, bm, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h],
+                                          p1, m1, B, lane);
+        } else {
+          A.pos = p1; A.mat = m1; A.size = s1; A.vert = nullptr; A.nvert = 0; A.world = false; A.coop = false; A.radius = 0.f;
+          if (t1 == B2S_GEOM_SPHERE) { A.type = CVX_POINT; A.radius = s1.x; }
+          else if (t1 == B2S_GEOM_CAPSULE) { A.type = CVX_SEGMENT; A.radius = s1.x; }
+          else if (t1 == B2S_GEOM_BOX) A.type = CVX_BOX;
+          else { const int id = m.geom_dataid[bg1]; A.type = CVX_VERTS; A.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; A.nvert = m.mesh_vertnum[id]; A.coop = true; }
+          B.coop = (B.type == CVX_VERTS);
+          nres = convex_pair_warp(s_stage, bm, A, B, lane);
         }
+        __syncwarp();
+        if (lane == L) {
+          n = nres;
+#pragma unroll
+          for (int k = 0; k < MAXC; k++) if (k < nres) { rc[k].dist = s_stage[k].dist; rc[k].pos = s_stage[k].pos; rc[k].n = s_stage[k].n; rc[k].t = mk3(0.f, 0.f, 0.f); }
+        }
+        __syncwarp();
       }
     }
     int total;
@@ -495,7 +530,9 @@ void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   COL_DISPATCH(m, (k_collision<MAXC, CONVEX><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
   b2s_count_launch();
 }
-size_t smem_collision(const ModelDev&) { return (size_t)B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1) * sizeof(int); }
+size_t smem_collision(const ModelDev& m) {
+  return (size_t)B2S_WARPS_PER_CTA * ((2 * B2S_MAX_SURVIVORS + 1) * sizeof(int) + (m.col_convex ? (8 + 32) * sizeof(CvxStage) : 0));
+}
 const void* fn_collision(const ModelDev& m) {
   const void* f = nullptr;
   COL_DISPATCH(m, (f = (const void*)k_collision<MAXC, CONVEX>));

@@ -27,6 +27,7 @@ struct Cvx {
   const float* vert;   // VERTS: vertices in the local frame (world == false) or already in the world frame
   int nvert;
   bool world;
+  bool coop;           // true: all 32 lanes are in this call with identical arguments and share the vertex scan
   float radius;
 };
 struct CvxRes { float dist; v3 n, pa, pb; };
@@ -44,7 +45,22 @@ __device__ __noinline__ v3 cvx_support(const Cvx& s, v3 dir) {
   v3 loc;
   if (s.type == CVX_SEGMENT) loc = mk3(0.f, 0.f, dl.z >= 0.f ? s.size.y : -s.size.y);
   else if (s.type == CVX_BOX) loc = mk3(dl.x >= 0.f ? s.size.x : -s.size.x, dl.y >= 0.f ? s.size.y : -s.size.y, dl.z >= 0.f ? s.size.z : -s.size.z);
-  else {
+  else if (s.coop) {
+    // warp-cooperative scan: lane-strided vertices, then (max value, lowest index) across the warp
+    const int lane = threadIdx.x & 31;
+    int best = 0x7fffffff; float bd = -3.0e38f;
+    for (int i = lane; i < s.nvert; i += 32) {
+      const float t = s.vert[3 * i] * dl.x + s.vert[3 * i + 1] * dl.y + s.vert[3 * i + 2] * dl.z;
+      if (t > bd) { bd = t; best = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, bd, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, best, o);
+      if (ob > bd || (ob == bd && oi < best)) { bd = ob; best = oi; }
+    }
+    loc = ld3(s.vert + 3 * best);
+  } else {
     int best = 0; float bd = s.vert[0] * dl.x + s.vert[1] * dl.y + s.vert[2] * dl.z;
     for (int i = 1; i < s.nvert; i++) {
       const float t = s.vert[3 * i] * dl.x + s.vert[3 * i + 1] * dl.y + s.vert[3 * i + 2] * dl.z;
@@ -289,55 +305,74 @@ DEV int convex_pair(Rc* c, float margin, const Cvx& A, const Cvx& B) {
   return 1;
 }
 
+// ---- warp-level drivers.  All 32 lanes call these with identical arguments; results land in `out` (shared memory).
+struct CvxStage { float dist; v3 pos, n; int idx; };
+
+// (max value, lowest index) over the warp of a per-lane candidate
+DEV void warp_argmax(float& v, int& i) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+    if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+  }
+}
+
 // plane - mesh: hull vertices within 1 mm of the deepest one are candidates; up to 4 span the manifold
-// (A deepest, B farthest from A, C farthest from line AB, D farthest from line BC or AC)
-template <class Rc>
-DEV int plane_mesh(Rc* c, float margin, v3 ppos, const m33& pmat, v3 mpos, const m33& mmat, const float* vert, int nvert) {
+// (A deepest, B farthest from A, C farthest from line AB, D farthest from line BC or AC among the rest).
+// Four lane-strided scans of the hull with warp arg-max (ties: lowest vertex index, as a sequential scan would pick).
+DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v3 mpos, const m33& mmat, const float* vert, int nvert, int lane) {
   const v3 n = col(pmat, 2), nl = mulTv(mmat, n), pl = mulTv(mmat, ppos - mpos);
   const float pd = dot(pl, nl);
-  float smax = -1e30f;
-  int ia = -1;
-  for (int i = 0; i < nvert; i++) {
+  float smax = -1e30f; int ia = 0x7fffffff;
+  for (int i = lane; i < nvert; i += 32) {
     const float sup = pd - (vert[3 * i] * nl.x + vert[3 * i + 1] * nl.y + vert[3 * i + 2] * nl.z);
     if (sup > smax) { smax = sup; ia = i; }
   }
-  if (ia < 0 || -smax > margin) return 0;
+  warp_argmax(smax, ia);
+  if (ia == 0x7fffffff || -smax > margin) return 0;
   float thr = smax - 1e-3f;
   if (thr < 0.f && smax >= 0.f) thr = 0.f;
   if (-thr > margin) thr = -margin;
   int idx[4] = {ia, -1, -1, -1};
   const v3 a = ld3(vert + 3 * ia);
-  float best = 0.f;
-  for (int i = 0; i < nvert; i++) {
+  float best = 0.f; int ib = 0x7fffffff;
+  for (int i = lane; i < nvert; i += 32) {
     const v3 v = ld3(vert + 3 * i);
     if (pd - dot(v, nl) < thr) continue;
     const v3 e = v - a; const float q = dot(e, e);
-    if (q > best) { best = q; idx[1] = i; }
+    if (q > best) { best = q; ib = i; }
   }
-  if (idx[1] >= 0 && best > 1e-10f) {
-    const v3 b = ld3(vert + 3 * idx[1]), ab = b - a, side = cross(nl, ab);
-    best = 0.f;
-    for (int i = 0; i < nvert; i++) {
+  warp_argmax(best, ib);
+  if (ib != 0x7fffffff && best > 1e-10f) {
+    idx[1] = ib;
+    const v3 b = ld3(vert + 3 * ib), ab = b - a, side = cross(nl, ab);
+    best = 0.f; int ic = 0x7fffffff;
+    for (int i = lane; i < nvert; i += 32) {
       const v3 v = ld3(vert + 3 * i);
       if (pd - dot(v, nl) < thr) continue;
       const float q = fabsf(dot(v - a, side));
-      if (q > best) { best = q; idx[2] = i; }
+      if (q > best) { best = q; ic = i; }
     }
-    if (idx[2] >= 0 && best > 1e-7f) {
-      const v3 cc = ld3(vert + 3 * idx[2]), sac = cross(nl, cc - a), sbc = cross(nl, cc - b);
-      float bestb = 0.f, besta = 0.f; int ib = -1, iaa = -1;
-      for (int i = 0; i < nvert; i++) {
+    warp_argmax(best, ic);
+    if (ic != 0x7fffffff && best > 1e-7f) {
+      idx[2] = ic;
+      const v3 cc = ld3(vert + 3 * ic), sac = cross(nl, cc - a), sbc = cross(nl, cc - b);
+      float bestb = 0.f, besta = 0.f; int jb = 0x7fffffff, ja = 0x7fffffff;
+      for (int i = lane; i < nvert; i += 32) {
         const v3 v = ld3(vert + 3 * i);
         if (pd - dot(v, nl) < thr) continue;
         if (i == idx[0] || i == idx[1] || i == idx[2]) continue;
         const float qb = fabsf(dot(v - b, sbc)), qa = fabsf(dot(v - a, sac));
-        if (qb > bestb) { bestb = qb; ib = i; }
-        if (qa > besta) { besta = qa; iaa = i; }
+        if (qb > bestb) { bestb = qb; jb = i; }
+        if (qa > besta) { besta = qa; ja = i; }
       }
-      if (bestb >= besta) { best = bestb; idx[3] = ib; } else { best = besta; idx[3] = iaa; }
-      if (best <= 1e-7f) idx[3] = -1;
-    } else idx[2] = -1;
-  } else idx[1] = -1;
+      warp_argmax(bestb, jb); warp_argmax(besta, ja);
+      float bq; int id;
+      if (bestb >= besta) { bq = bestb; id = jb; } else { bq = besta; id = ja; }
+      if (id != 0x7fffffff && bq > 1e-7f) idx[3] = id;
+    }
+  }
   int nc = 0;
 #pragma unroll
   for (int k = 0; k < 4; k++) {
@@ -349,58 +384,110 @@ DEV int plane_mesh(Rc* c, float margin, v3 ppos, const m33& pmat, v3 mpos, const
     const v3 v = ld3(vert + 3 * i);
     const float sup = pd - dot(v, nl);
     if (-sup > margin) continue;
-    c[nc].dist = -sup; c[nc].pos = mulv(mmat, v) + mpos + n * (sup * 0.5f); c[nc].n = n; c[nc].t = mk3(0.f, 0.f, 0.f);
+    if (lane == 0) { out[nc].dist = -sup; out[nc].pos = mulv(mmat, v) + mpos + n * (sup * 0.5f); out[nc].n = n; out[nc].idx = nc; }
     nc++;
   }
   return nc;
 }
 
-// height field (geom 1) against convex B: prisms of the cells under B's bounding sphere in (row, column, lower / upper
-// triangle) order, one contact per prism, the deepest MAXC kept (in visiting order).  hs = (x half, y half, z top, base).
-template <int MAXC, class Rc>
-DEV int hfield_convex(Rc* c, float margin, const float* hs, int nrow, int ncol, const float* data, v3 hpos, const m33& hmat,
-                      const Cvx& B, float rbound) {
+// one convex pair, every lane in the call: the hull scans are shared (Cvx::coop), the simplex / polytope logic runs
+// redundantly and identically on all lanes
+DEV int convex_pair_warp(CvxStage* out, float margin, const Cvx& A, const Cvx& B, int lane) {
+  CvxRes r;
+  if (!gjk_epa(A, B, margin + A.radius + B.radius, r)) return 0;
+  const float dist = r.dist - A.radius - B.radius;
+  if (dist > margin) return 0;
+  const v3 sa = r.pa + r.n * A.radius, sb = r.pb - r.n * B.radius;
+  if (lane == 0) { out[0].dist = dist; out[0].pos = (sa + sb) * 0.5f; out[0].n = r.n; out[0].idx = 0; }
+  return 1;
+}
+
+// height field (geom 1) against convex B.  B's exact bounding box in the field's frame (six support calls) selects the
+// cells; their triangular prisms, numbered t = (row * ncol + col) * 2 + (upper triangle), are handed out one per lane,
+// 32 per round, and each lane runs GJK/EPA on its prism unless the prism's top lies below B's lowest point.  One
+// contact per prism; the MAXC deepest are kept, ordered by t (ties: lower t stays).  `out` holds MAXC + 32 entries.
+// hs = (x half, y half, z top, base).
+template <int MAXC>
+DEV int hfield_convex_warp(CvxStage* out, float margin, const float* hs, int nrow, int ncol, const float* data, v3 hpos, const m33& hmat,
+                           const Cvx& B, int lane) {
   const float sx = hs[0], sy = hs[1], sz = hs[2], sb = hs[3];
-  const v3 p = mulTv(hmat, B.pos - hpos);
-  const float r = rbound + margin;
-  if (p.x + r < -sx || p.x - r > sx || p.y + r < -sy || p.y - r > sy || p.z - r > sz || p.z + r < -sb) return 0;
-  const float dx = 2.f * sx / (float)(ncol - 1), dy = 2.f * sy / (float)(nrow - 1);
-  const int cmin = max((int)floorf((p.x - r + sx) / dx), 0), cmax = min((int)ceilf((p.x + r + sx) / dx), ncol - 1);
-  const int rmin = max((int)floorf((p.y - r + sy) / dy), 0), rmax = min((int)ceilf((p.y + r + sy) / dy), nrow - 1);
-  int nc = 0;
-#pragma unroll 1
-  for (int rr = rmin; rr < rmax; rr++)
-#pragma unroll 1
-    for (int cc = cmin; cc < cmax; cc++)
-#pragma unroll 1
-      for (int tri = 0; tri < 2; tri++) {
-        const int r0 = tri ? rr + 1 : rr, k0 = cc, r1 = rr + 1, k1 = tri ? cc + 1 : cc, r2 = rr, k2 = cc + 1;
-        float wv[18];
-        float zmax = -sb;
-        {
-          const int cr[3] = {r0, r1, r2}, ck[3] = {k0, k1, k2};
+  float lo[3], hi[3];
+  {
+    Cvx Bc = B;
+    Bc.coop = (B.type == CVX_VERTS);        // all lanes are here with the same B: share the hull scans
 #pragma unroll
-          for (int i = 0; i < 3; i++) {
-            const float z = data[cr[i] * ncol + ck[i]] * sz;
-            const v3 top = mk3((float)ck[i] * dx - sx, (float)cr[i] * dy - sy, z), bot = mk3(top.x, top.y, -sb);
-            st3(wv + 3 * i, mulv(hmat, top) + hpos);
-            st3(wv + 9 + 3 * i, mulv(hmat, bot) + hpos);
-            zmax = fmaxf(zmax, z);
-          }
-        }
-        if (zmax < p.z - r) continue;
+    for (int a = 0; a < 3; a++) {
+      const v3 ax = col(hmat, a);
+      hi[a] = dot(cvx_support(Bc, ax) - hpos, ax) + B.radius + margin;
+      lo[a] = dot(cvx_support(Bc, ax * -1.f) - hpos, ax) - B.radius - margin;
+    }
+  }
+  if (hi[0] < -sx || lo[0] > sx || hi[1] < -sy || lo[1] > sy || lo[2] > sz || hi[2] < -sb) return 0;
+  const float dx = 2.f * sx / (float)(ncol - 1), dy = 2.f * sy / (float)(nrow - 1);
+  const int cmin = max((int)floorf((lo[0] + sx) / dx), 0), cmax = min((int)ceilf((hi[0] + sx) / dx), ncol - 1);
+  const int rmin = max((int)floorf((lo[1] + sy) / dy), 0), rmax = min((int)ceilf((hi[1] + sy) / dy), nrow - 1);
+  const int ncell = cmax - cmin, T = (rmax - rmin) * ncell * 2;
+  int nk = 0;
+#pragma unroll 1
+  for (int t0 = 0; t0 < T; t0 += 32) {
+    const int t = t0 + lane;
+    bool has = false;
+    CvxStage one;
+    if (t < T) {
+      const int tri = t & 1, cell = t >> 1, rr = rmin + cell / ncell, cc = cmin + cell % ncell;
+      const int r0 = tri ? rr + 1 : rr, k0 = cc, r1 = rr + 1, k1 = tri ? cc + 1 : cc, r2 = rr, k2 = cc + 1;
+      float wv[18];
+      float zmax = -sb;
+      const int cr[3] = {r0, r1, r2}, ck[3] = {k0, k1, k2};
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        const float z = data[cr[i] * ncol + ck[i]] * sz;
+        const v3 top = mk3((float)ck[i] * dx - sx, (float)cr[i] * dy - sy, z), bot = mk3(top.x, top.y, -sb);
+        st3(wv + 3 * i, mulv(hmat, top) + hpos);
+        st3(wv + 9 + 3 * i, mulv(hmat, bot) + hpos);
+        zmax = fmaxf(zmax, z);
+      }
+      if (zmax >= lo[2]) {
         Cvx P;
-        P.type = CVX_VERTS; P.vert = wv; P.nvert = 6; P.world = true; P.radius = 0.f;
+        P.type = CVX_VERTS; P.vert = wv; P.nvert = 6; P.world = true; P.coop = false; P.radius = 0.f;
         P.pos = mk3((wv[0] + wv[3] + wv[6] + wv[9] + wv[12] + wv[15]) / 6.f, (wv[1] + wv[4] + wv[7] + wv[10] + wv[13] + wv[16]) / 6.f,
                     (wv[2] + wv[5] + wv[8] + wv[11] + wv[14] + wv[17]) / 6.f);
-        Rc one;
-        if (!convex_pair(&one, margin, P, B)) continue;
-        if (nc < MAXC) c[nc++] = one;
-        else {
-          int sh = 0;
-          for (int i = 1; i < MAXC; i++) if (c[i].dist > c[sh].dist) sh = i;
-          if (one.dist < c[sh].dist) { for (int i = sh; i < MAXC - 1; i++) c[i] = c[i + 1]; c[MAXC - 1] = one; }
+        CvxRes res;
+        if (gjk_epa(P, B, margin + B.radius, res)) {
+          const float dist = res.dist - B.radius;
+          if (dist <= margin) {
+            has = true;
+            const v3 sbp = res.pb - res.n * B.radius;
+            one.dist = dist; one.pos = (res.pa + sbp) * 0.5f; one.n = res.n; one.idx = (rr * ncol + cc) * 2 + tri;
+          }
         }
       }
-  return nc;
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, has);
+    if (has) out[nk + __popc(mask & ((1u << lane) - 1u))] = one;
+    const int ntot = nk + __popc(mask);
+    __syncwarp();
+    if (ntot > MAXC) {
+      // keep the MAXC smallest by (dist, t); entries are already in t order, so compaction preserves it
+      CvxStage e0, e1;
+      bool k0 = false, k1 = false;
+      if (lane < ntot) {
+        e0 = out[lane]; int rank = 0;
+        for (int j = 0; j < ntot; j++) rank += (out[j].dist < e0.dist) || (out[j].dist == e0.dist && out[j].idx < e0.idx);
+        k0 = rank < MAXC;
+      }
+      if (lane + 32 < ntot) {
+        e1 = out[lane + 32]; int rank = 0;
+        for (int j = 0; j < ntot; j++) rank += (out[j].dist < e1.dist) || (out[j].dist == e1.dist && out[j].idx < e1.idx);
+        k1 = rank < MAXC;
+      }
+      const unsigned m0 = __ballot_sync(0xffffffffu, k0), m1 = __ballot_sync(0xffffffffu, k1);
+      __syncwarp();
+      if (k0) out[__popc(m0 & ((1u << lane) - 1u))] = e0;
+      if (k1) out[__popc(m0) + __popc(m1 & ((1u << lane) - 1u))] = e1;
+      __syncwarp();
+      nk = MAXC;
+    } else nk = ntot;
+  }
+  return nk;
 }

@@ -280,3 +280,35 @@ def env_origins_curriculum(num_envs, origins, seed=0, max_init_level=None):
   levels = rng.integers(0, mx + 1, num_envs)
   types = np.floor(np.arange(num_envs) / (num_envs / nc)).astype(int)
   return origins[levels, types], levels, types
+
+
+def surface_height(m, xy) -> np.ndarray:
+  """Highest terrain surface under each (x, y): box tops, height-field surfaces (max of the cell's four corners), 0 for
+  a plane.  Static, axis-aligned terrain geoms only (what `generate` makes).  Used to spawn robots ON the terrain:
+  the generator's own origins of the height-field pyramids lie inside the field's slab
+  (heightfield_terrains.py:243-246: spawn_height = max_height - base_thickness = 0 for base_thickness_ratio = 1)."""
+  xy = np.atleast_2d(np.asarray(xy, float))
+  z = np.full(len(xy), -np.inf)
+  gt = np.asarray(m.geom_type); gp = np.asarray(m.geom_pos); gs = np.asarray(m.geom_size)
+  stat = np.asarray(m.body_weldid)[np.asarray(m.geom_bodyid)] == 0
+  if np.any(stat & (gt == 0)):
+    z = np.maximum(z, 0.0)
+  bx = np.where(stat & (gt == 6))[0]
+  for k0 in range(0, len(bx), 512):          # boxes, in chunks (points x boxes masks)
+    b = bx[k0:k0 + 512]
+    inside = (np.abs(xy[:, None, 0] - gp[None, b, 0]) <= gs[None, b, 0]) & (np.abs(xy[:, None, 1] - gp[None, b, 1]) <= gs[None, b, 1])
+    top = np.where(inside, (gp[b, 2] + gs[b, 2])[None, :], -np.inf).max(axis=1)
+    z = np.maximum(z, top)
+  for g in np.where(stat & (gt == 1))[0]:
+    h = int(m.geom_dataid[g]); sx, sy, sz, _ = np.asarray(m.hfield_size)[h]
+    nrow, ncol = int(m.hfield_nrow[h]), int(m.hfield_ncol[h])
+    data = np.asarray(m.hfield_data)[int(m.hfield_adr[h]): int(m.hfield_adr[h]) + nrow * ncol].reshape(nrow, ncol)
+    lx, ly = xy[:, 0] - gp[g, 0], xy[:, 1] - gp[g, 1]
+    inside = (np.abs(lx) <= sx) & (np.abs(ly) <= sy)
+    if not inside.any():
+      continue
+    c = np.clip(np.floor((lx[inside] + sx) / (2 * sx) * (ncol - 1)).astype(int), 0, ncol - 2)
+    r = np.clip(np.floor((ly[inside] + sy) / (2 * sy) * (nrow - 1)).astype(int), 0, nrow - 2)
+    top = np.maximum.reduce([data[r, c], data[r + 1, c], data[r, c + 1], data[r + 1, c + 1]]) * sz + gp[g, 2]
+    z[inside] = np.maximum(z[inside], top)
+  return np.where(np.isfinite(z), z, 0.0)

@@ -220,7 +220,11 @@ def run_b200(args):
     eo, _, _ = terrains.env_origins_curriculum(E, np.asarray(m.meta["terrain_origins"]), seed=rank)
     origins[:] = torch.as_tensor(eo, dtype=torch.float32, device=dev)
     origins[:, 0:2] += (torch.rand(E, 2, generator=g) - 0.5).to(dev) * 2.0     # off the platform centre, onto the steps
-    origins[:, 2].clamp_(min=0.0).add_(0.05)
+    # spawn ON the terrain: highest surface under the robot's footprint (the generator's own hfield-pyramid origins
+    # lie inside the field's slab, heightfield_terrains.py:243-246)
+    xy = origins[:, 0:2].cpu().numpy()
+    surf = np.max([terrains.surface_height(m, xy + np.array(o)) for o in ((0, 0), (0.3, 0.2), (0.3, -0.2), (-0.3, 0.2), (-0.3, -0.2))], axis=0)
+    origins[:, 2] = torch.as_tensor(surf, dtype=torch.float32, device=dev) + 0.05
   else:
     side = int(np.ceil(np.sqrt(E)))
     idx = torch.arange(E, device=dev)

@@ -447,7 +447,8 @@ static int col_hfield(rawcon* c, int maxc, real margin, const b2s_model_desc* m,
     if (nc < maxc) c[nc++] = one;
     else {
       int sh = 0;
-      for (int i = 1; i < maxc; i++) if (c[i].dist > c[sh].dist) sh = i;     /* shallowest kept contact */
+      for (int i = 1; i < maxc; i++) if (c[i].dist >= c[sh].dist) sh = i;    /* shallowest kept contact, the latest of equals:
+                                                                                 the kept set is the maxc smallest by (dist, visit index) */
       if (one.dist < c[sh].dist) { for (int i = sh; i < maxc - 1; i++) c[i] = c[i + 1]; c[maxc - 1] = one; }
     }
   }

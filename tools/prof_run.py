@@ -12,7 +12,8 @@ from asimov_mjlab_b200.hostmodel import HostData
 W = int(os.environ.get("W", "4096"))
 warm = int(os.environ.get("WARM", "60"))
 steps = int(os.environ.get("STEPS", "4"))
-m = scenes.load_asset("g1_flat")
+asset = os.environ.get("ASSET", "g1_flat")
+m = scenes.load_asset(asset)
 m.opt.ls_parallel = bool(int(os.environ.get("LSP", "1")))
 M = engine.put_model(m)
 key = m.keys["robot/init_state"]
@@ -20,6 +21,16 @@ hd = HostData(m)
 hd.qpos[:] = key["qpos"]; hd.ctrl[:] = key["ctrl"]
 D = engine.put_data(m, hd, W, 50, 300, model=M)
 g = torch.Generator().manual_seed(0)
+if "terrain_origins" in m.meta:       # spawn on the generated terrain like bench.py does
+  import numpy as np
+  from asimov_mjlab_b200 import terrains
+  eo, _, _ = terrains.env_origins_curriculum(W, np.asarray(m.meta["terrain_origins"]), seed=0)
+  org = torch.as_tensor(eo, dtype=torch.float32)
+  org[:, 0:2] += (torch.rand(W, 2, generator=g) - 0.5) * 2.0
+  xy = org[:, 0:2].numpy()
+  surf = np.max([terrains.surface_height(m, xy + np.array(o)) for o in ((0, 0), (0.3, 0.2), (0.3, -0.2), (-0.3, 0.2), (-0.3, -0.2))], axis=0)
+  org[:, 2] = torch.as_tensor(surf, dtype=torch.float32) + 0.05
+  D.qpos[:, 0:3] += org.cuda()
 D.qpos[:, 7:] += (0.05 * torch.randn(W, m.nq - 7, generator=g)).cuda()
 D.ctrl[:] += (0.1 * torch.randn(W, m.nu, generator=g)).cuda()
 engine.step(M, D, warm)
