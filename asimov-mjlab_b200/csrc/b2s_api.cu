@@ -166,6 +166,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       if (id < 0 || id >= s->nhfield || s->hfield_nrow[id] < 2 || s->hfield_ncol[id] < 2 ||
           s->hfield_adr[id] < 0 || s->hfield_adr[id] + s->hfield_nrow[id] * s->hfield_ncol[id] > s->nhfielddata)
         return fail("height-field geom " + std::to_string(g) + " has no elevation data");
+      if ((long long)s->hfield_nrow[id] * s->hfield_ncol[id] * 2 >= (1LL << 26)) return fail("height field with more than 2^25 cells is not supported");
     }
   }
   if (s->ntendon < 0 || s->nwrap < 0) return fail("negative tendon sizes");

@@ -285,6 +285,19 @@ DEV int box_box(RawCon* c, float margin, v3 p1, const m33& M1, v3 S1, v3 p2, con
   return n;
 }
 
+// convex core of geom g (k_convex.cuh): sphere / capsule = point / segment + radius, box, mesh hull
+DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
+  Cvx B;
+  const int t = m.geom_type[g];
+  B.pos = ld3(gx + 3 * g); B.mat = ldm(gm + 9 * g); B.size = ld3(m.geom_size + 3 * g);
+  B.vert = nullptr; B.nvert = 0; B.world = false; B.coop = false; B.radius = 0.f;
+  if (t == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = B.size.x; }
+  else if (t == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = B.size.x; }
+  else if (t == B2S_GEOM_BOX) B.type = CVX_BOX;
+  else { const int id = m.geom_dataid[g]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
+  return B;
+}
+
 // MAXC = most contacts one pair of this model can produce (put_model picks 2 / 4 / 8): the contact scratch stays in
 // registers for sphere / capsule robots and the box colliders are compiled out where no box pair exists
 template <int MAXC, bool CONVEX>
@@ -297,7 +310,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   unsigned* s_list = (unsigned*)b2s_smem + warp * (2 * B2S_MAX_SURVIVORS + 1);
   unsigned* s_sort = s_list + B2S_MAX_SURVIVORS;
   int* s_cnt = (int*)(s_sort + B2S_MAX_SURVIVORS);
-  CvxStage* s_stage = (CvxStage*)((unsigned*)b2s_smem + B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1)) + warp * (MAXC + 32);
+  CvxStage* s_stage = (CvxStage*)((unsigned*)b2s_smem + B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1)) + warp * CVX_STAGE_CAP;
   if (m.disableflags & (B2S_DSBL_CONSTRAINT | B2S_DSBL_CONTACT)) { if (lane == 0) d.ncon[w] = 0; return; }
   const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
   const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
@@ -428,7 +441,73 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
     if constexpr (CONVEX) {
       // mesh / height-field pairs of this pass, one at a time with the whole warp: hull scans are lane-strided, a
       // height field's prisms are handed out one per lane; the results go back to the pair's lane through smem
-      unsigned todo = __ballot_sync(FULL, cvx);
+      // height-field pairs first, flattened: every (pair, prism) of this pass is one task, 32 tasks per round, so a
+      // capsule over 12 prisms and a sphere over 4 share rounds.  Hits are staged in task order = (pair, prism) order;
+      // each pair's lane then takes its segment.  If the stage overflows (robot buried in the field) the pairs fall
+      // back to the one-pair-at-a-time driver below, which has no such limit.
+      bool hf = false, hf_done = false;
+      if (cvx) hf = m.geom_type[g1] == B2S_GEOM_HFIELD;
+      if (__any_sync(FULL, hf)) {
+        HfRange R; R.cmin = 0; R.ncell = 0; R.rmin = 0; R.T = 0; R.loz = 0.f;
+        if (hf) {
+          Cvx B = geom_core(m, gx, gm, g2);
+          const int h = m.geom_dataid[g1];
+          R = hfield_range(margin, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], ld3(gx + 3 * g1), ldm(gm + 9 * g1), B);
+        }
+        int Ttot;
+        const int off = warp_excl_scan(R.T, lane, &Ttot);
+        int nst = 0;
+#pragma unroll 1
+        for (int q0 = 0; q0 < Ttot; q0 += 32) {
+          const int q = min(q0 + lane, Ttot - 1);
+          int own = 0;                                  // largest lane whose offset is <= q
+#pragma unroll
+          for (int b = 16; b > 0; b >>= 1) { const int cand = own + b; const int o = __shfl_sync(FULL, off, cand & 31); if (cand < 32 && o <= q) own = cand; }
+          const int og1 = __shfl_sync(FULL, g1, own), og2 = __shfl_sync(FULL, g2, own), ooff = __shfl_sync(FULL, off, own);
+          const float om = __shfl_sync(FULL, margin, own);
+          HfRange OR;
+          OR.cmin = __shfl_sync(FULL, R.cmin, own); OR.ncell = __shfl_sync(FULL, R.ncell, own); OR.rmin = __shfl_sync(FULL, R.rmin, own);
+          OR.T = 0; OR.loz = __shfl_sync(FULL, R.loz, own);
+          bool has = false;
+          CvxStage one;
+          if (q0 + lane < Ttot) {
+            const Cvx B = geom_core(m, gx, gm, og2);
+            const int h = m.geom_dataid[og1];
+            has = hfield_prism_task(one, q - ooff, OR, om, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h],
+                                    ld3(gx + 3 * og1), ldm(gm + 9 * og1), B);
+            one.idx |= own << 26;
+          }
+          const unsigned hm = __ballot_sync(FULL, has);
+          const int pos = nst + __popc(hm & ((1u << lane) - 1u));
+          if (has && pos < CVX_STAGE_CAP) s_stage[pos] = one;
+          nst += __popc(hm);
+        }
+        __syncwarp();
+        hf_done = nst <= CVX_STAGE_CAP;
+        if (hf_done && hf) {
+          int cnt = 0;
+          for (int e = 0; e < nst; e++) cnt += (s_stage[e].idx >> 26) == lane;
+          n = 0;
+          for (int e = 0; e < nst; e++) {
+            if ((s_stage[e].idx >> 26) != lane) continue;
+            bool keep = true;
+            if (cnt > MAXC) {        // the MAXC deepest by (dist, prism id), still in prism order
+              int rank = 0;
+              const float de = s_stage[e].dist; const int ie = s_stage[e].idx;
+              for (int j = 0; j < nst; j++)
+                if ((s_stage[j].idx >> 26) == lane) rank += (s_stage[j].dist < de) || (s_stage[j].dist == de && s_stage[j].idx < ie);
+              keep = rank < MAXC;
+            }
+            if (keep) {
+#pragma unroll
+              for (int k = 0; k < MAXC; k++) if (k == n) { rc[k].dist = s_stage[e].dist; rc[k].pos = s_stage[e].pos; rc[k].n = s_stage[e].n; rc[k].t = mk3(0.f, 0.f, 0.f); }
+              n++;
+            }
+          }
+        }
+        __syncwarp();
+      }
+      unsigned todo = __ballot_sync(FULL, cvx && !(hf && hf_done));
       while (todo) {
         const int L = __ffs(todo) - 1;
         todo &= todo - 1;
@@ -531,7 +610,7 @@ void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   b2s_count_launch();
 }
 size_t smem_collision(const ModelDev& m) {
-  return (size_t)B2S_WARPS_PER_CTA * ((2 * B2S_MAX_SURVIVORS + 1) * sizeof(int) + (m.col_convex ? (8 + 32) * sizeof(CvxStage) : 0));
+  return (size_t)B2S_WARPS_PER_CTA * ((2 * B2S_MAX_SURVIVORS + 1) * sizeof(int) + (m.col_convex ? CVX_STAGE_CAP * sizeof(CvxStage) : 0));
 }
 const void* fn_collision(const ModelDev& m) {
   const void* f = nullptr;

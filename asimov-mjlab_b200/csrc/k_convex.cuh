@@ -491,3 +491,56 @@ DEV int hfield_convex_warp(CvxStage* out, float margin, const float* hs, int nro
   }
   return nk;
 }
+
+// ---- flattened height-field tasks (used by k_collision): per-lane set-up and one prism task
+#define CVX_STAGE_CAP 96
+struct HfRange { int cmin, ncell, rmin, T; float loz; };
+
+// B's bounding box in the field's frame (six support calls, this lane only) -> cell range and prism count
+DEV HfRange hfield_range(float margin, const float* hs, int nrow, int ncol, v3 hpos, const m33& hmat, const Cvx& B) {
+  HfRange R; R.cmin = 0; R.ncell = 0; R.rmin = 0; R.T = 0; R.loz = 0.f;
+  const float sx = hs[0], sy = hs[1], sz = hs[2], sb = hs[3];
+  float lo[3], hi[3];
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    const v3 ax = col(hmat, a);
+    hi[a] = dot(cvx_support(B, ax) - hpos, ax) + B.radius + margin;
+    lo[a] = dot(cvx_support(B, ax * -1.f) - hpos, ax) - B.radius - margin;
+  }
+  if (hi[0] < -sx || lo[0] > sx || hi[1] < -sy || lo[1] > sy || lo[2] > sz || hi[2] < -sb) return R;
+  const float dx = 2.f * sx / (float)(ncol - 1), dy = 2.f * sy / (float)(nrow - 1);
+  const int cmin = max((int)floorf((lo[0] + sx) / dx), 0), cmax = min((int)ceilf((hi[0] + sx) / dx), ncol - 1);
+  const int rmin = max((int)floorf((lo[1] + sy) / dy), 0), rmax = min((int)ceilf((hi[1] + sy) / dy), nrow - 1);
+  R.cmin = cmin; R.ncell = max(cmax - cmin, 0); R.rmin = rmin; R.T = max(rmax - rmin, 0) * R.ncell * 2; R.loz = lo[2];
+  return R;
+}
+// prism number t (local to the range) against B; true + `one` when they touch within the margin
+DEV bool hfield_prism_task(CvxStage& one, int t, const HfRange& R, float margin, const float* hs, int nrow, int ncol, const float* data,
+                           v3 hpos, const m33& hmat, const Cvx& B) {
+  const float sx = hs[0], sy = hs[1], sz = hs[2], sb = hs[3];
+  const float dx = 2.f * sx / (float)(ncol - 1), dy = 2.f * sy / (float)(nrow - 1);
+  const int tri = t & 1, cell = t >> 1, rr = R.rmin + cell / R.ncell, cc = R.cmin + cell % R.ncell;
+  const int cr[3] = {tri ? rr + 1 : rr, rr + 1, rr}, ck[3] = {cc, tri ? cc + 1 : cc, cc + 1};
+  float wv[18];
+  float zmax = -sb;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const float z = data[cr[i] * ncol + ck[i]] * sz;
+    const v3 top = mk3((float)ck[i] * dx - sx, (float)cr[i] * dy - sy, z), bot = mk3(top.x, top.y, -sb);
+    st3(wv + 3 * i, mulv(hmat, top) + hpos);
+    st3(wv + 9 + 3 * i, mulv(hmat, bot) + hpos);
+    zmax = fmaxf(zmax, z);
+  }
+  if (zmax < R.loz) return false;
+  Cvx P;
+  P.type = CVX_VERTS; P.vert = wv; P.nvert = 6; P.world = true; P.coop = false; P.radius = 0.f;
+  P.pos = mk3((wv[0] + wv[3] + wv[6] + wv[9] + wv[12] + wv[15]) / 6.f, (wv[1] + wv[4] + wv[7] + wv[10] + wv[13] + wv[16]) / 6.f,
+              (wv[2] + wv[5] + wv[8] + wv[11] + wv[14] + wv[17]) / 6.f);
+  CvxRes res;
+  if (!gjk_epa(P, B, margin + B.radius, res)) return false;
+  const float dist = res.dist - B.radius;
+  if (dist > margin) return false;
+  const v3 sbp = res.pb - res.n * B.radius;
+  one.dist = dist; one.pos = (res.pa + sbp) * 0.5f; one.n = res.n; one.idx = (rr * ncol + cc) * 2 + tri;
+  return true;
+}
