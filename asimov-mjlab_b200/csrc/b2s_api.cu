@@ -427,7 +427,11 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.col_convex = col_convex;
   d.geom_dataid = up.i(s->geom_dataid, s->ngeom);
   d.mesh_vertadr = up.i(s->mesh_vertadr, s->nmesh); d.mesh_vertnum = up.i(s->mesh_vertnum, s->nmesh);
-  d.mesh_vert = up.f(s->mesh_vert, 3LL * s->nmeshvert);
+  {
+    std::vector<float> v4((size_t)4 * s->nmeshvert, 0.f);       // 16-byte vertices: one load per vertex in the hull scans
+    for (int i = 0; i < s->nmeshvert; i++) for (int a = 0; a < 3; a++) v4[(size_t)4 * i + a] = (float)s->mesh_vert[3 * i + a];
+    d.mesh_vert = up.raw(v4);
+  }
   d.hfield_size = up.f(s->hfield_size, 4LL * s->nhfield); d.hfield_data = up.f(s->hfield_data, s->nhfielddata);
   d.hfield_nrow = up.i(s->hfield_nrow, s->nhfield); d.hfield_ncol = up.i(s->hfield_ncol, s->nhfield); d.hfield_adr = up.i(s->hfield_adr, s->nhfield);
   d.ngrid = use_grid ? (int)grid_geoms.size() : 0;

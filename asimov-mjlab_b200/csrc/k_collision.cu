@@ -285,6 +285,35 @@ DEV int box_box(RawCon* c, float margin, v3 p1, const m33& M1, v3 S1, v3 p2, con
   return n;
 }
 
+// separating-axis test of two oriented boxes (Gottschalk et al.): t = centre of box 2 in box 1's frame; true when a
+// separating axis leaves more than `margin` between them
+DEV bool obb_separated(const m33& R1, v3 a, const m33& R2, v3 b, v3 t, float margin) {
+  float R[3][3], AR[3][3];
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      R[i][j] = R1.m[i] * R2.m[j] + R1.m[3 + i] * R2.m[3 + j] + R1.m[6 + i] * R2.m[6 + j];     // column i of R1 . column j of R2
+      AR[i][j] = fabsf(R[i][j]) + 1e-6f;
+    }
+  const float A[3] = {a.x, a.y, a.z}, B[3] = {b.x, b.y, b.z}, T[3] = {t.x, t.y, t.z};
+#pragma unroll
+  for (int i = 0; i < 3; i++) if (fabsf(T[i]) > A[i] + B[0] * AR[i][0] + B[1] * AR[i][1] + B[2] * AR[i][2] + margin) return true;
+#pragma unroll
+  for (int j = 0; j < 3; j++)
+    if (fabsf(T[0] * R[0][j] + T[1] * R[1][j] + T[2] * R[2][j]) > A[0] * AR[0][j] + A[1] * AR[1][j] + A[2] * AR[2][j] + B[j] + margin) return true;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+      const float ra = A[i1] * AR[i2][j] + A[i2] * AR[i1][j], rb = B[j1] * AR[i][j2] + B[j2] * AR[i][j1];
+      // the cross-product axis is not unit length: scale the margin by its length bound (<= 1)
+      if (fabsf(T[i2] * R[i1][j] - T[i1] * R[i2][j]) > ra + rb + margin) return true;
+    }
+  return false;
+}
+
 // convex core of geom g (k_convex.cuh): sphere / capsule = point / segment + radius, box, mesh hull
 DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
   Cvx B;
@@ -294,7 +323,7 @@ DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
   if (t == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = B.size.x; }
   else if (t == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = B.size.x; }
   else if (t == B2S_GEOM_BOX) B.type = CVX_BOX;
-  else { const int id = m.geom_dataid[g]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
+  else { const int id = m.geom_dataid[g]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
   return B;
 }
 
@@ -356,6 +385,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
           const float ex = fmaxf(fabsf(l.x) - b1.x, 0.f), ey = fmaxf(fabsf(l.y) - b1.y, 0.f), ez = fmaxf(fabsf(l.z) - b1.z, 0.f);
           const float rr = r2 + margin;
           pass = ex * ex + ey * ey + ez * ez <= rr * rr;
+          // a mesh pair costs a warp-wide GJK: spend a 15-axis box-box separation test (lane-parallel) on it first
+          if (CONVEX && pass && (ty1 == B2S_GEOM_MESH || m.geom_type[g2] == B2S_GEOM_MESH)) pass = !obb_separated(R1, b1, R2, b2, l, margin);
         }
       }
       key = ((unsigned)min(g1, g2) << 16) | (unsigned)max(g1, g2);
@@ -521,7 +552,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t2 == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = s2.x; }
         else if (t2 == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = s2.x; }
         else if (t2 == B2S_GEOM_BOX) B.type = CVX_BOX;
-        else { const int id = m.geom_dataid[bg2]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
+        else { const int id = m.geom_dataid[bg2]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
         int nres;
         if (t1 == B2S_GEOM_PLANE) nres = plane_mesh_warp(s_stage, bm, p1, m1, p2, m2, B.vert, B.nvert, lane);
         else if (t1 == B2S_GEOM_HFIELD) {
@@ -533,7 +564,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
           if (t1 == B2S_GEOM_SPHERE) { A.type = CVX_POINT; A.radius = s1.x; }
           else if (t1 == B2S_GEOM_CAPSULE) { A.type = CVX_SEGMENT; A.radius = s1.x; }
           else if (t1 == B2S_GEOM_BOX) A.type = CVX_BOX;
-          else { const int id = m.geom_dataid[bg1]; A.type = CVX_VERTS; A.vert = m.mesh_vert + 3 * m.mesh_vertadr[id]; A.nvert = m.mesh_vertnum[id]; A.coop = true; }
+          else { const int id = m.geom_dataid[bg1]; A.type = CVX_VERTS; A.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; A.nvert = m.mesh_vertnum[id]; A.coop = true; }
           B.coop = (B.type == CVX_VERTS);
           nres = convex_pair_warp(s_stage, bm, A, B, lane);
         }

@@ -24,7 +24,7 @@ struct Cvx {
   v3 pos;
   m33 mat;
   v3 size;             // SEGMENT: size.y = half length along local z; BOX: half sizes
-  const float* vert;   // VERTS: vertices in the local frame (world == false) or already in the world frame
+  const float* vert;   // VERTS: local frame, 4 floats per vertex (mesh hull; world == false), or world frame, 3 floats per vertex (prism)
   int nvert;
   bool world;
   bool coop;           // true: all 32 lanes are in this call with identical arguments and share the vertex scan
@@ -49,8 +49,10 @@ __device__ __noinline__ v3 cvx_support(const Cvx& s, v3 dir) {
     // warp-cooperative scan: lane-strided vertices, then (max value, lowest index) across the warp
     const int lane = threadIdx.x & 31;
     int best = 0x7fffffff; float bd = -3.0e38f;
+    const float4* v4 = reinterpret_cast<const float4*>(s.vert);        // mesh hulls are stored 4 floats per vertex
     for (int i = lane; i < s.nvert; i += 32) {
-      const float t = s.vert[3 * i] * dl.x + s.vert[3 * i + 1] * dl.y + s.vert[3 * i + 2] * dl.z;
+      const float4 p = __ldg(v4 + i);
+      const float t = p.x * dl.x + p.y * dl.y + p.z * dl.z;
       if (t > bd) { bd = t; best = i; }
     }
 #pragma unroll
@@ -59,14 +61,16 @@ __device__ __noinline__ v3 cvx_support(const Cvx& s, v3 dir) {
       const int oi = __shfl_xor_sync(0xffffffffu, best, o);
       if (ob > bd || (ob == bd && oi < best)) { bd = ob; best = oi; }
     }
-    loc = ld3(s.vert + 3 * best);
+    loc = ld3(s.vert + 4 * best);
   } else {
-    int best = 0; float bd = s.vert[0] * dl.x + s.vert[1] * dl.y + s.vert[2] * dl.z;
-    for (int i = 1; i < s.nvert; i++) {
-      const float t = s.vert[3 * i] * dl.x + s.vert[3 * i + 1] * dl.y + s.vert[3 * i + 2] * dl.z;
+    const float4* v4 = reinterpret_cast<const float4*>(s.vert);
+    int best = 0; float bd = -3.0e38f;
+    for (int i = 0; i < s.nvert; i++) {
+      const float4 p = __ldg(v4 + i);
+      const float t = p.x * dl.x + p.y * dl.y + p.z * dl.z;
       if (t > bd) { bd = t; best = i; }
     }
-    loc = ld3(s.vert + 3 * best);
+    loc = ld3(s.vert + 4 * best);
   }
   return mulv(s.mat, loc) + s.pos;
 }
@@ -326,7 +330,7 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
   const float pd = dot(pl, nl);
   float smax = -1e30f; int ia = 0x7fffffff;
   for (int i = lane; i < nvert; i += 32) {
-    const float sup = pd - (vert[3 * i] * nl.x + vert[3 * i + 1] * nl.y + vert[3 * i + 2] * nl.z);
+    const float sup = pd - (vert[4 * i] * nl.x + vert[4 * i + 1] * nl.y + vert[4 * i + 2] * nl.z);
     if (sup > smax) { smax = sup; ia = i; }
   }
   warp_argmax(smax, ia);
@@ -335,10 +339,10 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
   if (thr < 0.f && smax >= 0.f) thr = 0.f;
   if (-thr > margin) thr = -margin;
   int idx[4] = {ia, -1, -1, -1};
-  const v3 a = ld3(vert + 3 * ia);
+  const v3 a = ld3(vert + 4 * ia);
   float best = 0.f; int ib = 0x7fffffff;
   for (int i = lane; i < nvert; i += 32) {
-    const v3 v = ld3(vert + 3 * i);
+    const v3 v = ld3(vert + 4 * i);
     if (pd - dot(v, nl) < thr) continue;
     const v3 e = v - a; const float q = dot(e, e);
     if (q > best) { best = q; ib = i; }
@@ -346,10 +350,10 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
   warp_argmax(best, ib);
   if (ib != 0x7fffffff && best > 1e-10f) {
     idx[1] = ib;
-    const v3 b = ld3(vert + 3 * ib), ab = b - a, side = cross(nl, ab);
+    const v3 b = ld3(vert + 4 * ib), ab = b - a, side = cross(nl, ab);
     best = 0.f; int ic = 0x7fffffff;
     for (int i = lane; i < nvert; i += 32) {
-      const v3 v = ld3(vert + 3 * i);
+      const v3 v = ld3(vert + 4 * i);
       if (pd - dot(v, nl) < thr) continue;
       const float q = fabsf(dot(v - a, side));
       if (q > best) { best = q; ic = i; }
@@ -357,10 +361,10 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
     warp_argmax(best, ic);
     if (ic != 0x7fffffff && best > 1e-7f) {
       idx[2] = ic;
-      const v3 cc = ld3(vert + 3 * ic), sac = cross(nl, cc - a), sbc = cross(nl, cc - b);
+      const v3 cc = ld3(vert + 4 * ic), sac = cross(nl, cc - a), sbc = cross(nl, cc - b);
       float bestb = 0.f, besta = 0.f; int jb = 0x7fffffff, ja = 0x7fffffff;
       for (int i = lane; i < nvert; i += 32) {
-        const v3 v = ld3(vert + 3 * i);
+        const v3 v = ld3(vert + 4 * i);
         if (pd - dot(v, nl) < thr) continue;
         if (i == idx[0] || i == idx[1] || i == idx[2]) continue;
         const float qb = fabsf(dot(v - b, sbc)), qa = fabsf(dot(v - a, sac));
@@ -381,7 +385,7 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
     bool dup = false;
     for (int q = 0; q < k; q++) if (idx[q] == i) dup = true;
     if (dup) continue;
-    const v3 v = ld3(vert + 3 * i);
+    const v3 v = ld3(vert + 4 * i);
     const float sup = pd - dot(v, nl);
     if (-sup > margin) continue;
     if (lane == 0) { out[nc].dist = -sup; out[nc].pos = mulv(mmat, v) + mpos + n * (sup * 0.5f); out[nc].n = n; out[nc].idx = nc; }
