@@ -459,8 +459,10 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.sensor_objid = up.i(s->sensor_objid, s->nsensor); d.sensor_reftype = up.i(s->sensor_reftype, s->nsensor);
   d.sensor_refid = up.i(s->sensor_refid, s->nsensor); d.sensor_intprm = up.i(s->sensor_intprm, 3 * s->nsensor);
   d.sensor_dim = up.i(s->sensor_dim, s->nsensor); d.sensor_adr = up.i(s->sensor_adr, s->nsensor); d.sensor_cutoff = up.f(s->sensor_cutoff, s->nsensor);
-  for (int k = 0; k < s->nsensor; k++)
+  for (int k = 0; k < s->nsensor; k++) {
     if (s->sensor_type[k] == B2S_SENS_SUBTREELINVEL || s->sensor_type[k] == B2S_SENS_SUBTREEANGMOM) d.need_subtreevel = 1;
+    if (s->sensor_type[k] == B2S_SENS_CONTACT) d.need_concache = 1;
+  }
   // expandable (per-world capable) fields: leading dim 1 with world stride 0 until b2s_model_expand
   std::vector<double> rgba((size_t)4 * s->ngeom, 0.5);
   for (int g = 0; g < s->ngeom; g++) rgba[4 * g + 3] = 1.0;
@@ -693,7 +695,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   // raise the dynamic shared-memory limit of every stage once
   struct { const void* fn; size_t smem; } st[] = {
     {fn_position(), smem_position(md)}, {fn_dynamics(md), smem_dynamics(md)}, {fn_collision(md), smem_collision(md)},
-    {fn_constraint(), smem_constraint(md)}, {fn_solve(md), smem_solve(md, d)}, {fn_sensors(), smem_sensors(md)},
+    {fn_constraint(), smem_constraint(md)}, {fn_solve(md), smem_solve(md, d)}, {fn_sensors(), smem_sensors(md, d)},
     {fn_integrate(md), smem_integrate(md)}};
   for (auto& e : st) {
     if (e.smem > 227 * 1024) { delete D; return fail("model too large for the shared-memory working set (" + std::to_string(e.smem) + " B per CTA)"); }

@@ -83,6 +83,7 @@ struct ModelDev {
   const int *sensor_type, *sensor_objtype, *sensor_objid, *sensor_reftype, *sensor_refid, *sensor_intprm, *sensor_dim, *sensor_adr;
   const float *sensor_cutoff;
   int need_subtreevel;
+  int need_concache;   // some sensor is a contact sensor: k_sensors stages the world's contacts in shared memory
 };
 
 struct DataDev {

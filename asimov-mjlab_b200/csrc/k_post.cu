@@ -13,25 +13,45 @@ DEV sv6 object_velocity(const ModelDev& m, const float* cvel, const float* com, 
   sv6 r; r.v[0] = ang.x; r.v[1] = ang.y; r.v[2] = ang.z; r.v[3] = lin.x; r.v[4] = lin.y; r.v[5] = lin.z;
   return r;
 }
-DEV bool side_match(const ModelDev& m, int objtype, int objid, int geom) {
-  const int body = m.geom_bodyid[geom];
+// Per-world contact cache for the contact sensors, filled once by the whole warp (one lane per contact): geoms, bodies,
+// the pyramid-decoded wrench in the contact frame (mju_decodePyramid) and rotated to the world frame, the position.
+// The sensors then match and reduce out of shared memory instead of chasing global loads contact by contact.
+#define CC_WORDS 19
+struct ConCache {
+  const int* i;     // [ncon][4]: geom1, geom2, body1, body2
+  const float* f;   // [ncon][15]: f6 contact frame | force world 3 | torque world 3 | pos 3
+};
+DEV void fill_contact_cache(const ModelDev& m, const DataDev& d, int w, int ncon, int* ci, float* cf, int lane) {
+  const size_t con0 = (size_t)w * d.nconmax, row0 = (size_t)w * d.njmax;
+  for (int c = lane; c < ncon; c += 32) {
+    const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
+    ci[4 * c] = g1; ci[4 * c + 1] = g2; ci[4 * c + 2] = m.geom_bodyid[g1]; ci[4 * c + 3] = m.geom_bodyid[g2];
+    float f6[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) f6[k] = 0.f;
+    const int adr = d.con_efc_address[con0 + c], dim = d.con_dim[con0 + c];
+    if (adr >= 0) {
+      if (dim == 1) f6[0] = d.efc_force[row0 + adr];
+      else for (int k = 0; k < dim - 1; k++) {
+        const float a = d.efc_force[row0 + adr + 2 * k], b = d.efc_force[row0 + adr + 2 * k + 1];
+        f6[0] += a + b;
+        f6[1 + k] = d.con_friction[5 * (con0 + c) + k] * (a - b);
+      }
+    }
+    const m33 fr = ldm(d.con_frame + 9 * (con0 + c));
+    float* o = cf + 15 * c;
+#pragma unroll
+    for (int k = 0; k < 6; k++) o[k] = f6[k];
+    st3(o + 6, mulTv(fr, mk3(f6[0], f6[1], f6[2])));
+    st3(o + 9, mulTv(fr, mk3(f6[3], f6[4], f6[5])));
+    st3(o + 12, ld3(d.con_pos + 3 * (con0 + c)));
+  }
+}
+DEV bool side_match(const ModelDev& m, int objtype, int objid, int geom, int body) {
   if (objtype == B2S_OBJ_GEOM) return geom == objid;
   if (objtype == B2S_OBJ_BODY) return body == objid;
   if (objtype == B2S_OBJ_XBODY) return m.body_ancmask[(size_t)body * m.nbody + objid] != 0;
   return true;
-}
-// contact wrench in the contact frame from the pyramid forces (mju_decodePyramid)
-DEV void contact_wrench(const DataDev& d, size_t con0, size_t row0, int c, float* f6) {
-#pragma unroll
-  for (int k = 0; k < 6; k++) f6[k] = 0.f;
-  const int adr = d.con_efc_address[con0 + c], dim = d.con_dim[con0 + c];
-  if (adr < 0) return;
-  if (dim == 1) { f6[0] = d.efc_force[row0 + adr]; return; }
-  for (int k = 0; k < dim - 1; k++) {
-    const float a = d.efc_force[row0 + adr + 2 * k], b = d.efc_force[row0 + adr + 2 * k + 1];
-    f6[0] += a + b;
-    f6[1 + k] = d.con_friction[5 * (con0 + c) + k] * (a - b);
-  }
 }
 struct Frame { v3 pos; m33 mat; int body; };
 DEV Frame obj_frame(const ModelDev& m, const DataDev& d, int w, int type, int id) {
@@ -43,27 +63,26 @@ DEV Frame obj_frame(const ModelDev& m, const DataDev& d, int w, int type, int id
   return f;
 }
 
-DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float* out) {
+DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float* out, int ncon, const ConCache cc) {
   const int bits = m.sensor_intprm[3 * s], reduce = m.sensor_intprm[3 * s + 1], nslot = m.sensor_intprm[3 * s + 2];
   const int ot = m.sensor_objtype[s], id = m.sensor_objid[s], rt = m.sensor_reftype[s], rid = m.sensor_refid[s];
   const int dim = m.sensor_dim[s], maxm = m.contact_sensor_maxmatch;
-  const size_t con0 = (size_t)w * d.nconmax, row0 = (size_t)w * d.njmax;
-  const int ncon = d.ncon[w];
+  const size_t con0 = (size_t)w * d.nconmax;
   for (int k = 0; k < dim; k++) out[k] = 0.f;
   if (nslot <= 0) return;
   const int slotdim = dim / nslot;
   // pass 1: count matches (capped), and for netforce the force-weighted centroid
   int nmatch = 0; float wsum = 0.f; v3 P = mk3(0.f, 0.f, 0.f), Pm = mk3(0.f, 0.f, 0.f);
   for (int c = 0; c < ncon && nmatch < maxm; c++) {
-    const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
-    const bool fwd = side_match(m, ot, id, g1) && (rid < 0 || side_match(m, rt, rid, g2));
-    const bool bwd = side_match(m, ot, id, g2) && (rid < 0 || side_match(m, rt, rid, g1));
+    const int g1 = cc.i[4 * c], g2 = cc.i[4 * c + 1], b1 = cc.i[4 * c + 2], b2 = cc.i[4 * c + 3];
+    const bool fwd = side_match(m, ot, id, g1, b1) && (rid < 0 || side_match(m, rt, rid, g2, b2));
+    const bool bwd = side_match(m, ot, id, g2, b2) && (rid < 0 || side_match(m, rt, rid, g1, b1));
     if (!fwd && !bwd) continue;
     nmatch++;
     if (reduce == B2S_REDUCE_NETFORCE) {
-      float f6[6]; contact_wrench(d, con0, row0, c, f6);
+      const float* f6 = cc.f + 15 * c;
       const float wt = sqrtf(f6[0] * f6[0] + f6[1] * f6[1] + f6[2] * f6[2]);
-      v3 cp = ld3(d.con_pos + 3 * (con0 + c));
+      v3 cp = ld3(f6 + 12);
       P = P + cp * wt; Pm = Pm + cp; wsum += wt;
     }
   }
@@ -73,16 +92,15 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
     v3 F = mk3(0.f, 0.f, 0.f), Tq = mk3(0.f, 0.f, 0.f);
     int seen = 0;
     for (int c = 0; c < ncon && seen < maxm; c++) {
-      const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
-      const bool fwd = side_match(m, ot, id, g1) && (rid < 0 || side_match(m, rt, rid, g2));
-      const bool bwd = side_match(m, ot, id, g2) && (rid < 0 || side_match(m, rt, rid, g1));
+      const int g1 = cc.i[4 * c], g2 = cc.i[4 * c + 1], b1 = cc.i[4 * c + 2], b2 = cc.i[4 * c + 3];
+      const bool fwd = side_match(m, ot, id, g1, b1) && (rid < 0 || side_match(m, rt, rid, g2, b2));
+      const bool bwd = side_match(m, ot, id, g2, b2) && (rid < 0 || side_match(m, rt, rid, g1, b1));
       if (!fwd && !bwd) continue;
       seen++;
       const float dir = fwd ? 1.f : -1.f;
-      float f6[6]; contact_wrench(d, con0, row0, c, f6);
-      m33 fr = ldm(d.con_frame + 9 * (con0 + c));
-      v3 fg = mulTv(fr, mk3(f6[0], f6[1], f6[2])) * dir, tg = mulTv(fr, mk3(f6[3], f6[4], f6[5])) * dir;
-      v3 arm = ld3(d.con_pos + 3 * (con0 + c)) - P;
+      const float* f = cc.f + 15 * c;
+      v3 fg = ld3(f + 6) * dir, tg = ld3(f + 9) * dir;
+      v3 arm = ld3(f + 12) - P;
       F = F + fg; Tq = Tq + tg + cross(arm, fg);
     }
     float* o = out;
@@ -101,14 +119,14 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
     float bkey = 3.0e38f; int bord = -1, bc = -1; float bdir = 1.f;
     int ord = 0;
     for (int c = 0; c < ncon && ord < maxm; c++) {
-      const int g1 = d.con_geom[2 * (con0 + c)], g2 = d.con_geom[2 * (con0 + c) + 1];
-      const bool fwd = side_match(m, ot, id, g1) && (rid < 0 || side_match(m, rt, rid, g2));
-      const bool bwd = side_match(m, ot, id, g2) && (rid < 0 || side_match(m, rt, rid, g1));
+      const int g1 = cc.i[4 * c], g2 = cc.i[4 * c + 1], b1 = cc.i[4 * c + 2], b2 = cc.i[4 * c + 3];
+      const bool fwd = side_match(m, ot, id, g1, b1) && (rid < 0 || side_match(m, rt, rid, g2, b2));
+      const bool bwd = side_match(m, ot, id, g2, b2) && (rid < 0 || side_match(m, rt, rid, g1, b1));
       if (!fwd && !bwd) continue;
       float key;
       if (reduce == B2S_REDUCE_NONE) key = (float)ord;
       else if (reduce == B2S_REDUCE_MINDIST) key = d.con_dist[con0 + c];
-      else { float f6[6]; contact_wrench(d, con0, row0, c, f6); key = -sqrtf(f6[0] * f6[0] + f6[1] * f6[1] + f6[2] * f6[2]); }
+      else { const float* f6 = cc.f + 15 * c; key = -sqrtf(f6[0] * f6[0] + f6[1] * f6[1] + f6[2] * f6[2]); }
       const bool after = key > pkey || (key == pkey && ord > pord);
       const bool better = key < bkey || (key == bkey && ord < bord);
       if (after && (bord < 0 || better)) { bkey = key; bord = ord; bc = c; bdir = fwd ? 1.f : -1.f; }
@@ -116,14 +134,14 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
     }
     if (bc < 0) break;
     pkey = bkey; pord = bord;
-    float f6[6]; contact_wrench(d, con0, row0, bc, f6);
+    const float* f6 = cc.f + 15 * bc;
     const float* fr = d.con_frame + 9 * (con0 + bc);
     float* o = out + sl * slotdim;
     if (bits & B2S_CON_FOUND) *o++ = (float)nmatch;
     if (bits & B2S_CON_FORCE) { o[0] = f6[0]; o[1] = bdir * f6[1]; o[2] = bdir * f6[2]; o += 3; }
     if (bits & B2S_CON_TORQUE) { o[0] = f6[3]; o[1] = bdir * f6[4]; o[2] = bdir * f6[5]; o += 3; }
     if (bits & B2S_CON_DIST) *o++ = d.con_dist[con0 + bc];
-    if (bits & B2S_CON_POS) { st3(o, ld3(d.con_pos + 3 * (con0 + bc))); o += 3; }
+    if (bits & B2S_CON_POS) { st3(o, ld3(f6 + 12)); o += 3; }
     if (bits & B2S_CON_NORMAL) { st3(o, ld3(fr) * bdir); o += 3; }
     if (bits & B2S_CON_TANGENT) { st3(o, ld3(fr + 3) * bdir); o += 3; }
   }
@@ -141,6 +159,11 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
   float* s_am = s_lm + 3 * nb;
   float* s_slv = s_am + 3 * nb;
   const float* qvel = d.qvel + (size_t)w * nv;
+  // contact cache (only when the model has contact sensors): per-warp [nconmax][4] ints then [nconmax][15] floats
+  int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * 21 * nb) + (size_t)warp * CC_WORDS * d.nconmax;
+  float* s_cf = (float*)(s_ci + 4 * d.nconmax);
+  const int ncon = m.need_concache ? d.ncon[w] : 0;
+  if (m.need_concache) fill_contact_cache(m, d, w, ncon, s_ci, s_cf, lane);
   const float* qacc = d.qacc + (size_t)w * nv;
   const float* cdof = d.cdof + (size_t)w * 6 * nv;
   const float* cdd = d.cdof_dot + (size_t)w * 6 * nv;
@@ -242,7 +265,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
         sv6 v = object_velocity(m, cvel, com, f.body, f.pos);
         if (type == B2S_SENS_FRAMELINVEL) st3(out, mk3(v.v[3], v.v[4], v.v[5])); else st3(out, mk3(v.v[0], v.v[1], v.v[2]));
       } break;
-      case B2S_SENS_CONTACT: contact_sensor(m, d, w, s, out); break;
+      case B2S_SENS_CONTACT: { ConCache cc; cc.i = s_ci; cc.f = s_cf; contact_sensor(m, d, w, s, out, ncon, cc); } break;
       default: for (int k = 0; k < dim; k++) out[k] = 0.f;
     }
     const float cut = m.sensor_cutoff[s];
@@ -384,7 +407,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const Mode
 
 void launch_sensors(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
-  k_sensors<<<grid, 32 * B2S_WARPS_PER_CTA, smem_sensors(m), st>>>(m, d);
+  k_sensors<<<grid, 32 * B2S_WARPS_PER_CTA, smem_sensors(m, d), st>>>(m, d);
   b2s_count_launch();
 }
 void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st) {
@@ -401,7 +424,9 @@ void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   }
   b2s_count_launch();
 }
-size_t smem_sensors(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * 21 * m.nbody * sizeof(float); }
+size_t smem_sensors(const ModelDev& m, const DataDev& d) {
+  return (size_t)B2S_WARPS_PER_CTA * (21 * m.nbody + (m.need_concache ? CC_WORDS * d.nconmax : 0)) * sizeof(float);
+}
 size_t smem_integrate(const ModelDev& m) {
   const int T = b2s_tile_for(m.nv);
   return (size_t)B2S_WARPS_PER_CTA * (b2s_hdim(T) * b2s_hld(T) + 7 * T + 2 * m.nvp) * sizeof(float);
