@@ -225,14 +225,18 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   for (int i = lane; i < nv; i += 32) { s_qvel[i] = qvel[i]; s_act[i] = 0.f; }
   for (int i = lane; i < b2s_hdim(T) * ld; i += 32) s_M[i] = 0.f;
   __syncwarp();
-  // composite inertia: sum of cinert over the subtree range (same frame for all bodies)
+  // composite inertia: sum of cinert over the subtree range (same frame for all bodies).  cinert is staged once,
+  // coalesced, into the cfrc|fext region (12 nb floats, not written until the RNE pass below)
+  float* s_cin = s_cfrc;
+  for (int i = lane; i < 10 * nb; i += 32) s_cin[i] = d.cinert[(size_t)w * nb * 10 + i];
+  __syncwarp();
   for (int b = lane; b < nb; b += 32) {
     float acc[10];
 #pragma unroll
     for (int k = 0; k < 10; k++) acc[k] = 0.f;
     const int e = m.body_subtree_end[b];
     for (int j = b; j < e; j++) {
-      const float* c = d.cinert + ((size_t)w * nb + j) * 10;
+      const float* c = s_cin + 10 * j;
 #pragma unroll
       for (int k = 0; k < 10; k++) acc[k] += c[k];
     }
@@ -312,8 +316,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   }
   __syncwarp();
   // write M (symmetric, dense, row stride nvp) to HBM
-  for (int i = lane; i < nv * nvp; i += 32) {
-    const int r = i / nvp, c = i - r * nvp;
+  for (int i = lane, r = 0, c = lane; i < nv * nvp; i += 32, c += 32) {
+    while (c >= nvp) { c -= nvp; r++; }
     float v = 0.f;
     if (c < nv) v = (c <= r) ? s_M[r * ld + c] : s_M[c * ld + r];
     d.qM[(size_t)w * nv * nvp + i] = v;
