@@ -1,0 +1,153 @@
+"""N1/N2: velocity-task MDP terms (pure tensor functions), PPO pieces, and the multi-rank reductions (gloo, world 2)."""
+import math
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from asimov_mjlab_b200.rl import velocity_mdp as mdp
+
+
+def test_quaternion_helpers_and_heading():
+  yaw = torch.tensor([0.3, -2.0, 3.0])
+  q = mdp.quat_from_yaw(yaw)
+  assert torch.allclose(mdp.heading_w(q), yaw, atol=1e-6)
+  v = torch.randn(3, 3)
+  assert torch.allclose(mdp.quat_apply_inverse(q, mdp.quat_apply(q, v)), v, atol=1e-6)
+  # projected gravity of an upright base is (0, 0, -1); tilted by 80 degrees about x -> bad_orientation at 70 degrees
+  g = torch.tensor([[0.0, 0.0, -1.0]])
+  assert torch.allclose(mdp.quat_apply_inverse(mdp.quat_from_yaw(torch.tensor([1.0])), g), g, atol=1e-6)
+  a = math.radians(80.0)
+  qx = torch.tensor([[math.cos(a / 2), math.sin(a / 2), 0.0, 0.0]])
+  pg = mdp.quat_apply_inverse(qx, g)
+  assert bool(mdp.bad_orientation(pg, math.radians(70.0))[0]) and not bool(mdp.bad_orientation(g, math.radians(70.0))[0])
+  assert torch.allclose(mdp.wrap_to_pi(torch.tensor([3.5, -3.5, 0.5])), torch.tensor([3.5 - 2 * math.pi, -3.5 + 2 * math.pi, 0.5]), atol=1e-6)
+
+
+def test_air_time_state_machine_matches_reference_semantics():
+  """contact_sensor.py:327-367: air time accumulates while detached, is latched into last_air_time on landing."""
+  z = lambda: torch.zeros(1, 2)       # noqa: E731
+  st = dict(current_air_time=z(), last_air_time=z(), current_contact_time=z(), last_contact_time=z(), last_time=torch.zeros(1))
+  seq = [(1, 1), (0, 1), (0, 1), (0, 0), (1, 0), (1, 1)]
+  t = 0.0
+  for f in seq:
+    t += 0.005
+    mdp.update_air_time(st, torch.tensor([f], dtype=torch.float32), torch.tensor([t]))
+  # foot 0: contact, 3 steps in the air, landed 2 steps ago; foot 1: 3 steps of contact, 2 in the air, just landed.
+  # The reference latches `current + elapsed` on the transition step, so a phase of n steps reads (n + 1) * dt.
+  assert st["last_air_time"][0, 0] == pytest.approx(0.020) and st["current_air_time"][0, 0] == 0
+  assert st["current_contact_time"][0, 0] == pytest.approx(0.010)
+  assert st["last_air_time"][0, 1] == pytest.approx(0.015) and st["last_contact_time"][0, 1] == pytest.approx(0.020)
+  assert mdp.first_contact(st, 0.02).tolist() == [[True, True]] and mdp.first_contact(st, 0.004).tolist() == [[False, False]]
+
+
+def test_reward_terms_closed_forms():
+  cmd = torch.tensor([[1.0, 0.0, 0.5], [0.0, 0.0, 0.0]])
+  lin = torch.tensor([[1.0, 0.0, 0.0], [0.5, 0.0, 0.0]])
+  assert torch.allclose(mdp.track_linear_velocity(cmd, lin, 0.5), torch.tensor([1.0, math.exp(-1.0)]))
+  ang = torch.tensor([[0.0, 0.0, 0.5], [0.1, 0.0, 0.0]])
+  assert torch.allclose(mdp.track_angular_velocity(cmd, ang, math.sqrt(0.5)), torch.tensor([1.0, math.exp(-0.02)]))
+  jp = torch.tensor([[0.0, 1.2], [-1.3, 0.0]])
+  lim = torch.tensor([[-1.0, 1.0], [-1.0, 1.0]])
+  assert torch.allclose(mdp.joint_pos_limits(jp, lim), torch.tensor([0.2, 0.3]))
+  # posture: standing command uses the standing std
+  d = torch.zeros(2)
+  p = mdp.variable_posture(cmd, torch.tensor([[0.1, 0.0], [0.1, 0.0]]), d, torch.tensor([0.05, 0.05]), torch.tensor([0.3, 0.3]),
+                           torch.tensor([0.5, 0.5]), 0.05, 1.5)
+  assert p[0] == pytest.approx(math.exp(-0.5 * (0.1 / 0.5) ** 2)) and p[1] == pytest.approx(math.exp(-0.5 * (0.1 / 0.05) ** 2))
+  # swing height: peak tracked in the air, cost on landing, then cleared
+  peak = torch.tensor([[0.05, 0.0]])
+  cost, new = mdp.feet_swing_height(peak, torch.tensor([[0.08, 0.02]]), torch.tensor([[0.0, 1.0]]), torch.tensor([[False, False]]), cmd[:1], 0.1, 0.05)
+  assert cost.item() == 0 and new.tolist() == [[pytest.approx(0.08), 0.0]]
+  cost, new = mdp.feet_swing_height(new, torch.tensor([[0.0, 0.02]]), torch.tensor([[1.0, 1.0]]), torch.tensor([[True, False]]), cmd[:1], 0.1, 0.05)
+  assert cost.item() == pytest.approx((0.08 / 0.1 - 1) ** 2) and new.tolist() == [[0.0, 0.0]]
+  f = torch.tensor([[[3.0, 0.0, -4.0], [0.0, 0.0, 0.0]]])
+  assert mdp.soft_landing(f, torch.tensor([[True, True]]), cmd[:1], 0.05).item() == pytest.approx(5.0)
+  assert torch.allclose(mdp.contact_force_obs(f)[0, :3], torch.tensor([math.log(4.0), 0.0, -math.log(5.0)]))
+
+
+def test_empirical_normalization_matches_numpy():
+  from asimov_mjlab_b200.rl.ppo import EmpiricalNormalization
+  torch.manual_seed(0)
+  n = EmpiricalNormalization(4)
+  xs = [torch.randn(50, 4) * 3 + 1, torch.randn(20, 4) - 2, torch.randn(70, 4)]
+  for x in xs[:2]:
+    n.update(x)
+  n.sync()
+  n.update(xs[2]); n.sync()
+  allx = torch.cat(xs).numpy()
+  assert np.allclose(n.mean.numpy(), allx.mean(0), atol=1e-5) and np.allclose((n.m2 / n.count).numpy(), allx.var(0), atol=1e-4)
+  assert torch.allclose(n(xs[0]), (xs[0] - n.mean) / (torch.sqrt(n.m2 / n.count) + 1e-2))
+
+
+def _rank_main(rank, world, port, out):
+  os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+  import torch.distributed as dist
+  from asimov_mjlab_b200.rl.ppo import ActorCritic, EmpiricalNormalization, all_reduce_mean_
+  dist.init_process_group("gloo", rank=rank, world_size=world)
+  torch.manual_seed(100 + rank)
+  x = torch.randn(40 + 10 * rank, 3) * (1 + rank) + rank
+  n = EmpiricalNormalization(3)
+  n.update(x); n.sync()
+  # gradient all-reduce == gradient of the mean loss over the union of the shards (equal shard sizes)
+  torch.manual_seed(7)
+  ac = ActorCritic(5, 6, 2, hidden=(8,))
+  torch.manual_seed(200 + rank)
+  obs = torch.randn(16, 5)
+  loss = ac.actor(obs).pow(2).mean()
+  loss.backward()
+  g = torch.cat([p.grad.reshape(-1) for p in ac.actor.parameters()])
+  all_reduce_mean_(g)
+  torch.save(dict(mean=n.mean, var=n.m2 / n.count, count=n.count, x=x, g=g, obs=obs), os.path.join(out, f"r{rank}.pt"))
+  dist.destroy_process_group()
+
+
+def test_two_rank_normaliser_merge_and_gradient_average(tmp_path):
+  import torch.multiprocessing as mp
+  port = 29600 + os.getpid() % 300
+  mp.spawn(_rank_main, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+  r = [torch.load(os.path.join(tmp_path, f"r{k}.pt")) for k in range(2)]
+  allx = torch.cat([r[0]["x"], r[1]["x"]]).numpy()
+  for k in range(2):
+    assert np.allclose(r[k]["mean"].numpy(), allx.mean(0), atol=1e-5) and np.allclose(r[k]["var"].numpy(), allx.var(0), atol=1e-4)
+    assert float(r[k]["count"]) == len(allx)
+  assert torch.allclose(r[0]["g"], r[1]["g"])
+  from asimov_mjlab_b200.rl.ppo import ActorCritic
+  torch.manual_seed(7)
+  ac = ActorCritic(5, 6, 2, hidden=(8,))
+  ac.actor(torch.cat([r[0]["obs"], r[1]["obs"]])).pow(2).mean().backward()
+  g = torch.cat([p.grad.reshape(-1) for p in ac.actor.parameters()])
+  assert torch.allclose(g, r[0]["g"], atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_velocity_env_graph_step_and_ppo_iteration():
+  """The whole env step replays as one CUDA graph: standing robots stay up, rewards are finite, resets restore the
+  keyframe; one PPO iteration runs and changes the policy."""
+  from asimov_mjlab_b200.rl.ppo import PPO
+  from asimov_mjlab_b200.rl.velocity_env import G1VelocityFlatEnv
+  env = G1VelocityFlatEnv(256, "cuda:0", seed=1)
+  assert env.num_obs == 99 and env.num_privileged_obs == 111 and env.max_episode_length == 1000
+  obs, ex = env.get_observations()
+  assert obs.shape == (256, 99) and ex["observations"]["critic"].shape == (256, 111)
+  tot = torch.zeros(256, device="cuda:0")
+  for _ in range(50):
+    obs, rew, dones, ex = env.step(torch.zeros(256, env.num_actions, device="cuda:0"))
+    tot += rew
+  assert torch.isfinite(obs).all() and torch.isfinite(tot).all()
+  assert env.D.qpos[:, 2].mean() > 0.6 and dones.float().mean() < 0.1          # zero action = hold the keyframe: robots stand
+  assert tot.mean() > 0.5 * 50 * 0.02 * 4.0                                    # tracking / posture rewards dominate while standing
+  assert (env.episode_length_buf > 0).all()
+  # random actions make robots fall: terminated envs are reset to the keyframe height
+  for _ in range(60):
+    env.step(torch.randn(256, env.num_actions, device="cuda:0") * 3.0)
+  assert env.episode_length_buf.min() < 60
+  fresh = env.episode_length_buf == 0
+  if fresh.any():
+    assert (env.D.qpos[fresh, 2] - 0.76).abs().max() < 1e-3
+  algo = PPO(env, torch.device("cuda:0"), steps_per_env=8)
+  w0 = algo.ac.actor[0].weight.clone()
+  algo.rollout(); info = algo.update()
+  assert math.isfinite(info["value_loss"]) and not torch.equal(w0, algo.ac.actor[0].weight)
