@@ -308,6 +308,14 @@ DEV void warp_chol_solve_inv(const float* L, const float* invd, int n, int ld, i
 // Same substitution with the PADDED dimension N = 7T as a compile-time constant: fully unrolled, shared-memory
 // offsets become immediates.  Rows/cols n..N-1 of L are the identity padding written by the tile Cholesky and
 // the matching entries of b must be 0 on entry.  REQUIRES a zero strict upper triangle in L's storage.
+#define B2S_STR_(x) #x
+#define B2S_STR(x) B2S_STR_(x)
+// Unrolled by 7 (N = 7T), not fully: the fully unrolled form is ~900 SASS instructions per call site and the solver's
+// loop body is already larger than the 32 KB instruction cache (solve 0.452 -> 0.412 ms with the small loops rolled).
+#ifndef B2S_SUBST_UNROLL
+#define B2S_SUBST_UNROLL 7
+#endif
+#define B2S_SUBST_PRAGMA _Pragma(B2S_STR(unroll B2S_SUBST_UNROLL))
 template <int T>
 DEV void tile_chol_solve(const float* L, const float* invd, int ld, int lane, float& b0, float& b1) {
   constexpr int N = 7 * T;
@@ -317,14 +325,14 @@ DEV void tile_chol_solve(const float* L, const float* invd, int ld, int lane, fl
   const float* Lc0 = L + min(lane, N - 1);
   const float* Lc1 = L + min(lane + 32, N - 1);
   float y0 = 0.f, y1 = 0.f;
-#pragma unroll
+  B2S_SUBST_PRAGMA
   for (int k = 0; k < N; k++) {
     const float yk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
     if (k < 32) { if (lane == k) y0 = yk; } else { if (lane == k - 32) y1 = yk; }
     b0 -= Lr0[k] * yk;
     if (HI) b1 -= Lr1[k] * yk;
   }
-#pragma unroll
+  B2S_SUBST_PRAGMA
   for (int k = N - 1; k >= 0; k--) {
     const float xk = __shfl_sync(FULL, k < 32 ? y0 : y1, k & 31) * invd[k];
     if (k < 32) { if (lane == k) b0 = xk; } else { if (lane == k - 32) b1 = xk; }

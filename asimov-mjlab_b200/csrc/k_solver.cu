@@ -17,6 +17,23 @@
 
 extern __shared__ float b2s_smem[];
 
+// The solver has its own CTA shape: ONE warp (= one world) per CTA.  Newton iteration counts differ from world to
+// world, and a multi-warp CTA keeps its shared memory and registers until its slowest warp is done; measured on
+// B200 at 4096 G1 worlds: 4 warps x 4 CTAs/SM 0.480 ms, 3 x 5 0.473, 2 x 7 0.467, 1 x 14..18 0.449-0.456 (occupancy
+// between 12 and 18 warps per SM makes no difference; 96 registers with 18 warps of 3 or 6 per CTA is slower, 0.54).
+#ifndef SOLVE_WARPS
+#define SOLVE_WARPS 1
+#endif
+#ifndef SOLVE_MINB
+#define SOLVE_MINB 16
+#endif
+// small per-dof / per-row loops stay rolled: the kernel's loop body is several times the 32 KB instruction cache
+#ifdef SOLVE_UNROLL_SMALL
+#define ROLL
+#else
+#define ROLL _Pragma("unroll 1")
+#endif
+
 __host__ __device__ inline int solve_scratch_floats(int nb) { return 6 * (nb > 32 ? nb : 32) + 32 + 32; }
 __host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      // offset of the scratch area
   const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
@@ -89,12 +106,15 @@ DEV void mat_vec_M(const SolveCtx<T>& c, const float* x, float* y) {
 template <int T>
 DEV void mat_vec_J(const SolveCtx<T>& c, const ModelDev& m, const float* x, const float* sub, float* out) {
   __syncwarp();
+  ROLL
   for (int b = c.lane; b < c.nb; b += 32) {
     sv6 v = zero6();
+    ROLL
     for (int k = m.body_chain_adr[b]; k < m.body_chain_adr[b + 1]; k++) { const int i = m.body_chain[k]; axpy6(v, x[i], ld6(c.cdof() + 6 * i)); }
     st6(c.X() + 6 * b, v);
   }
   __syncwarp();
+  ROLL
   for (int r = c.lane; r < c.nefc; r += 32) {
     const int bp = c.bp[r];
     const float2* gp = reinterpret_cast<const float2*>(c.G + (size_t)r * 6);
@@ -115,12 +135,14 @@ DEV void mat_vec_J(const SolveCtx<T>& c, const ModelDev& m, const float* x, cons
 template <int T>
 DEV float gauss_term(const SolveCtx<T>& c) {
   float g = 0.f;
+  ROLL
   for (int i = c.lane; i < c.nv; i += 32) g += (c.Ma()[i] - c.qfs()[i]) * (c.qacc()[i] - c.qas()[i]);
   return 0.5f * warp_sum(g);
 }
 template <int T>
 DEV float constraint_cost(const SolveCtx<T>& c, const float* jar) {
   float s = 0.f;
+  ROLL
   for (int r = c.lane; r < c.nefc; r += 32) { const float x = jar[r]; if (x < 0.f) s += 0.5f * c.D()[r] * x * x; }
   return warp_sum(s);
 }
@@ -314,13 +336,16 @@ DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, b
 template <int T>
 DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, int ib) {
   __syncwarp();
+  ROLL
   for (int i = c.lane; i < c.nvp; i += 32) c.qfc()[i] = 0.f;
   if (withH) {
     float4* h4 = reinterpret_cast<float4*>(c.H());
+    _Pragma("unroll 2")
     for (int i = c.lane; i < c.hfloats / 4; i += 32) h4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncwarp();
   // limit rows (they come first): one lane per row, J is +-1 on one dof
+  ROLL
   for (int r = c.lane; r < c.nl; r += 32) {
     const float jar = c.Jaref()[r];
     if (jar < 0.f) {
@@ -385,9 +410,9 @@ DEV void factor_H(const SolveCtx<T>& c, int bi, int bj) {
 }
 
 template <int T>
-__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 4) k_solve(const ModelDev m, const DataDev d) {
+__global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
+  const int w = blockIdx.x * SOLVE_WARPS + warp;
   if (w >= d.nworld) return;
   const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
   SolveCtx<T> c;
@@ -549,13 +574,13 @@ static int tile_for(int nv) { return b2s_tile_for(nv); }
   }
 
 void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
-  const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
+  const int grid = (d.nworld + SOLVE_WARPS - 1) / SOLVE_WARPS;
   const size_t smem = smem_solve(m, d);
-  SOLVE_DISPATCH((k_solve<T><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d)));
+  SOLVE_DISPATCH((k_solve<T><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d)));
   b2s_count_launch();
 }
 size_t smem_solve(const ModelDev& m, const DataDev& d) {
-  return (size_t)B2S_WARPS_PER_CTA * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv)) * sizeof(float);
+  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv)) * sizeof(float);
 }
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;
