@@ -651,6 +651,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"efc_force", B2S_F32, (void**)&d.efc_force, {njmax}},
     {"qacc", B2S_F32, (void**)&d.qacc, {nv}}, {"qfrc_constraint", B2S_F32, (void**)&d.qfrc_constraint, {nv}},
     {"solver_cost", B2S_F32, (void**)&d.solver_cost, {}}, {"solver_niter", B2S_I32, (void**)&d.solver_niter, {}},
+    {"solve_order", B2S_I32, (void**)&d.solve_order, {B2S_SOLVE_CLASSES}}, {"solve_count", B2S_I32, (void**)&d.solve_count, {B2S_SOLVE_CLASSES}},
     {"cacc", B2S_F32, (void**)&d.cacc, {nb, 6}}, {"subtree_linvel", B2S_F32, (void**)&d.subtree_linvel, {nb, 3}},
     {"subtree_angmom", B2S_F32, (void**)&d.subtree_angmom, {nb, 3}}, {"sensordata", B2S_F32, (void**)&d.sensordata, {md.nsensordata}},
   };

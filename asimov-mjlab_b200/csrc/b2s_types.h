@@ -86,6 +86,7 @@ struct ModelDev {
   int need_concache;   // some sensor is a contact sensor: k_sensors stages the world's contacts in shared memory
 };
 
+#define B2S_SOLVE_CLASSES 16
 struct DataDev {
   int nworld, nconmax, njmax;
   // state / inputs
@@ -106,6 +107,9 @@ struct DataDev {
   // solver
   float *qacc, *qfrc_constraint, *solver_cost;
   int *solver_niter;
+  // scheduling only (never affects results): worlds binned by expected solve cost (previous Newton iteration count x rows), so that the
+  // solver's CTAs start the expensive worlds first; solve_order[class][nworld], solve_count[class]
+  int *solve_order, *solve_count;
   // post
   float *cacc, *subtree_linvel, *subtree_angmom, *sensordata;
 };

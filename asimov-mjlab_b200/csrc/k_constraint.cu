@@ -63,7 +63,10 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
   if (w >= d.nworld) return;
   const int nv = m.nv, nb = m.nbody, njmax = d.njmax;
   float* s_cvel = b2s_smem + (size_t)warp * 6 * nb;     // body velocities about the world's reference point
-  if (m.disableflags & B2S_DSBL_CONSTRAINT) { if (lane == 0) { d.nefc[w] = 0; d.nl[w] = 0; } return; }
+  if (m.disableflags & B2S_DSBL_CONSTRAINT) {
+    if (lane == 0) { d.nefc[w] = 0; d.nl[w] = 0; d.solve_order[atomicAdd(&d.solve_count[0], 1)] = w; }
+    return;
+  }
   const float* com = d.subtree_com + (size_t)w * nb * 3;
   const v3 cref = ld3(com + 3 * m.ref_root);
   for (int b = lane; b < nb; b += 32) {
@@ -196,7 +199,14 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
       }
     }
   }
-  if (lane == 0) { d.nefc[w] = nefc; d.nl[w] = nl; }
+  if (lane == 0) {
+    d.nefc[w] = nefc; d.nl[w] = nl;
+    // queue this world for the solver by expected cost: the Newton iteration count of its previous solve (temporal
+    // coherence) x a per-iteration cost that grows with the row count; 0 rows = cheapest.  Order inside a class is whatever the atomics give; results do not depend on it.
+    const int cls = nefc == 0 ? 0 : min(B2S_SOLVE_CLASSES - 1, 1 + (1 + min(d.solver_niter[w], 15)) * (32 + nefc) / 64);
+    const int slot = atomicAdd(&d.solve_count[cls], 1);
+    d.solve_order[(size_t)cls * d.nworld + slot] = w;
+  }
 }
 
 // Dense efc_J from the matrix-free rows (on demand; not part of step/forward).

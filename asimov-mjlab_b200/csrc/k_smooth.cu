@@ -19,6 +19,8 @@ extern __shared__ float b2s_smem[];
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
+  // first kernel of step / forward: reset the solver's scheduling queues (k_constraint refills them)
+  if (blockIdx.x == 0 && threadIdx.x < B2S_SOLVE_CLASSES) d.solve_count[threadIdx.x] = 0;
   if (w >= d.nworld) return;
   const int nb = m.nbody;
   float* sx = b2s_smem + (size_t)warp * 22 * nb;   // xpos

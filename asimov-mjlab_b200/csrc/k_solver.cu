@@ -412,8 +412,15 @@ DEV void factor_H(const SolveCtx<T>& c, int bi, int bj) {
 template <int T>
 __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int w = blockIdx.x * SOLVE_WARPS + warp;
+  // worlds are taken from the cost-ordered queues, most expensive class first (k_constraint filled them)
+  int w = blockIdx.x * SOLVE_WARPS + warp;
   if (w >= d.nworld) return;
+  {
+    int cls = B2S_SOLVE_CLASSES - 1, before = 0;
+#pragma unroll 1
+    for (; cls > 0; cls--) { const int n = d.solve_count[cls]; if (w < before + n) break; before += n; }
+    w = d.solve_order[(size_t)cls * d.nworld + (w - before)];
+  }
   const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
   SolveCtx<T> c;
   c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.njmax = njmax;

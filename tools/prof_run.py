@@ -34,6 +34,11 @@ if "terrain_origins" in m.meta:       # spawn on the generated terrain like benc
 D.qpos[:, 7:] += (0.05 * torch.randn(W, m.nq - 7, generator=g)).cuda()
 D.ctrl[:] += (0.1 * torch.randn(W, m.nu, generator=g)).cuda()
 engine.step(M, D, warm)
+if int(os.environ.get("RAND", "0")):      # the bench's state distribution: random action targets, resampled every 4 sub-steps
+  import bench
+  pool = torch.as_tensor(bench.action_targets(m, 40, W, seed=1000)).cuda()
+  for k in range(40):
+    D.ctrl.copy_(pool[k]); engine.step(M, D, 4)
 torch.cuda.synchronize()
 print("ncon mean %.1f nefc mean %.1f niter mean %.2f" % (D.ncon.float().mean().item(), D.nefc.float().mean().item(), D.solver_niter.float().mean().item()))
 print("nefc hist", torch.bincount(D.nefc.cpu() // 8).tolist())
