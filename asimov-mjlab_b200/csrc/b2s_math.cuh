@@ -308,36 +308,46 @@ DEV void warp_chol_solve_inv(const float* L, const float* invd, int n, int ld, i
 // Same substitution with the PADDED dimension N = 7T as a compile-time constant: fully unrolled, shared-memory
 // offsets become immediates.  Rows/cols n..N-1 of L are the identity padding written by the tile Cholesky and
 // the matching entries of b must be 0 on entry.  REQUIRES a zero strict upper triangle in L's storage.
-#define B2S_STR_(x) #x
-#define B2S_STR(x) B2S_STR_(x)
-// Unrolled by 7 (N = 7T), not fully: the fully unrolled form is ~900 SASS instructions per call site and the solver's
-// loop body is already larger than the 32 KB instruction cache (solve 0.452 -> 0.412 ms with the small loops rolled).
-#ifndef B2S_SUBST_UNROLL
-#define B2S_SUBST_UNROLL 7
-#endif
-#define B2S_SUBST_PRAGMA _Pragma(B2S_STR(unroll B2S_SUBST_UNROLL))
+// Partially unrolled (8 or 7 steps), not fully: the fully unrolled form is ~900 SASS instructions per call site and the
+// solver's loop body is already larger than the 32 KB instruction cache.  Rows 0..31 (held in b0) and rows 32..N-1
+// (held in b1 on lanes 0..N-33) are separate loops so that no step has to select between the two.
 template <int T>
 DEV void tile_chol_solve(const float* L, const float* invd, int ld, int lane, float& b0, float& b1) {
   constexpr int N = 7 * T;
   constexpr bool HI = N > 32;
+  constexpr int N0 = HI ? 32 : N, U = HI ? 8 : 7;
   const float* Lr0 = L + min(lane, N - 1) * ld;
   const float* Lr1 = L + min(lane + 32, N - 1) * ld;
   const float* Lc0 = L + min(lane, N - 1);
   const float* Lc1 = L + min(lane + 32, N - 1);
   float y0 = 0.f, y1 = 0.f;
-  B2S_SUBST_PRAGMA
-  for (int k = 0; k < N; k++) {
-    const float yk = __shfl_sync(FULL, k < 32 ? b0 : b1, k & 31) * invd[k];
-    if (k < 32) { if (lane == k) y0 = yk; } else { if (lane == k - 32) y1 = yk; }
+#pragma unroll U
+  for (int k = 0; k < N0; k++) {                 // forward: L y = b
+    const float yk = __shfl_sync(FULL, b0, k) * invd[k];
+    if (lane == k) y0 = yk;
     b0 -= Lr0[k] * yk;
     if (HI) b1 -= Lr1[k] * yk;
   }
-  B2S_SUBST_PRAGMA
-  for (int k = N - 1; k >= 0; k--) {
-    const float xk = __shfl_sync(FULL, k < 32 ? y0 : y1, k & 31) * invd[k];
-    if (k < 32) { if (lane == k) b0 = xk; } else { if (lane == k - 32) b1 = xk; }
-    y0 -= Lc0[k * ld] * xk;
-    if (HI) y1 -= Lc1[k * ld] * xk;
+  if (HI) {
+#pragma unroll
+    for (int k = 32; k < N; k++) {
+      const float yk = __shfl_sync(FULL, b1, k - 32) * invd[k];
+      if (lane == k - 32) y1 = yk;
+      b1 -= Lr1[k] * yk;                         // rows < 32 have zeros in columns >= 32
+    }
+#pragma unroll
+    for (int k = N - 1; k >= 32; k--) {          // backward: L^T x = y
+      const float xk = __shfl_sync(FULL, y1, k - 32) * invd[k];
+      if (lane == k - 32) b1 = xk;
+      y0 -= Lc0[k * ld] * xk;
+      y1 -= Lc1[k * ld] * xk;
+    }
+  }
+#pragma unroll U
+  for (int k = N0 - 1; k >= 0; k--) {
+    const float xk = __shfl_sync(FULL, y0, k) * invd[k];
+    if (lane == k) b0 = xk;
+    y0 -= Lc0[k * ld] * xk;                      // column entries above the diagonal are zero: rows >= 32 need none
   }
 }
 __host__ __device__ inline int b2s_hdim(int T) { return 7 * T; }                         // padded matrix dimension

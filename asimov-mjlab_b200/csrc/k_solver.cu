@@ -74,33 +74,30 @@ struct SolveCtx {
   DEV int* Li() const { return (int*)(sm + soff + 6 * max(nb, 32) + 32); }
 };
 
-// y[i] = sum_j M[i][j] x[j]; M symmetric in HBM/L2, read column-wise so lanes hit contiguous addresses
+// y[i] = sum_j M[i][j] x[j].  M is dense and symmetric in HBM/L2 with row stride nvp (a multiple of 4, padding columns
+// are zero): lane = row, the row is read as float4 (all of them in flight before the first use), x as float4
+// broadcasts from shared memory (zero-padded to NVP).  One accumulator, columns in ascending order.
 template <int T>
 DEV void mat_vec_M(const SolveCtx<T>& c, const float* x, float* y) {
-  // all row loads are issued before the first use (static trip count 7T): one L2 round trip instead of nv
-  constexpr int N = 7 * T;
-  const float* col0 = c.M + min(c.lane, c.nv - 1);
-  const float* col1 = c.M + min(c.lane + 32, c.nv - 1);
-  constexpr int B = 12;          // loads in flight per batch
-  float a0 = 0.f, a1 = 0.f;
+  constexpr int N = 7 * T, Q = SolveCtx<T>::NVP / 4;
+  const int n4 = c.nvp >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
 #pragma unroll 1
-  for (int j0 = 0; j0 < N; j0 += B) {
-    float m0[B], m1[B];
+  for (int half = 0; half < (N > 32 ? 2 : 1); half++) {
+    const int row = c.lane + 32 * half;
+    if (half == 1 && __all_sync(FULL, row >= c.nv)) break;
+    const float4* r = reinterpret_cast<const float4*>(c.M + (size_t)min(row, c.nv - 1) * c.nvp);
+    float4 mrow[Q];
 #pragma unroll
-    for (int k = 0; k < B; k++) {
-      const int jj = min(j0 + k, c.nv - 1);
-      m0[k] = col0[(size_t)jj * c.nvp];
-      if (N > 32) m1[k] = col1[(size_t)jj * c.nvp];
-    }
+    for (int j = 0; j < Q; j++) mrow[j] = r[min(j, n4 - 1)];     // j >= n4 meets x == 0
+    float a = 0.f;
 #pragma unroll
-    for (int k = 0; k < B; k++) if (j0 + k < N) {
-      const float xj = x[j0 + k];          // x is padded with zeros up to NVP >= N
-      a0 += m0[k] * xj;
-      if (N > 32) a1 += m1[k] * xj;
+    for (int j = 0; j < Q; j++) {
+      const float4 xv = x4[j];
+      a += mrow[j].x * xv.x; a += mrow[j].y * xv.y; a += mrow[j].z * xv.z; a += mrow[j].w * xv.w;
     }
+    if (row < c.nv) y[row] = a;
   }
-  if (c.lane < c.nv) y[c.lane] = a0;
-  if (N > 32 && c.lane + 32 < c.nv) y[c.lane + 32] = a1;
 }
 // out[r] = J[r] . x - sub[r], matrix-free: body spatial vectors X[b] first (one lane per body), then one lane per row
 template <int T>
