@@ -9,6 +9,11 @@ resets and forward() -- is captured in ONE CUDA graph (torch ops and the engine'
 a policy step costs one graph launch and no host synchronisation (N2).  Interface follows the reference's
 RslRlVecEnvWrapper (rl/vecenv_wrapper.py:11-111): num_envs, num_actions, num_obs, num_privileged_obs,
 max_episode_length, episode_length_buf, get_observations(), step(actions) -> (obs, rew, dones, extras).
+
+Two implementations of the manager side share every buffer: `use_fused=True` (default) launches the four fused CUDA
+kernels of csrc/k_mdp.cu (7 launches per env step next to the physics), `use_fused=False` evaluates the same terms as
+torch ops (~490 small kernels) and is the oracle the fused kernels are tested against.  Both take their randomness from
+one uniform buffer `U` (W, nrand) refilled once per env step and read at fixed slots (include/b200sim.h).
 """
 from __future__ import annotations
 
@@ -20,6 +25,7 @@ import torch
 from .. import engine, scenes
 from ..mjcf import resolve_expr
 from ..sim import MujocoCfg, Simulation, SimulationCfg
+from . import fused
 from . import velocity_mdp as mdp
 
 G1_POSTURE_WALKING = {r".*hip_pitch.*": 0.3, r".*hip_roll.*": 0.15, r".*hip_yaw.*": 0.15, r".*knee.*": 0.35, r".*ankle_pitch.*": 0.25,
@@ -37,8 +43,10 @@ class G1VelocityFlatEnv:
   decimation = 4
   episode_length_s = 20.0
 
-  def __init__(self, num_envs: int, device: str = "cuda:0", seed: int = 0, env_spacing: float = 2.5, use_graph: bool = True):
+  def __init__(self, num_envs: int, device: str = "cuda:0", seed: int = 0, env_spacing: float = 2.5, use_graph: bool = True,
+               use_fused: bool = True):
     self.num_envs, self.device = num_envs, torch.device(device)
+    self.use_fused = use_fused
     torch.cuda.set_device(self.device)
     m = scenes.load_asset("g1_flat")
     self.m = m
@@ -97,9 +105,17 @@ class G1VelocityFlatEnv:
     self.num_obs, self.num_privileged_obs = 3 + 3 + 3 + 3 * self.num_actions + 3, 3 + 3 + 3 + 3 * self.num_actions + 3 + 2 + 2 + 2 + 6
     self.obs, self.critic_obs = z(W, self.num_obs), z(W, self.num_privileged_obs)
     self.rew, self.dones, self.time_outs = z(W), torch.zeros(W, dtype=torch.bool, device=dev), torch.zeros(W, dtype=torch.bool, device=dev)
-    self.term_sums = {k: z(W) for k in REWARD_WEIGHTS}
+    self.term_sums_buf = z(fused.NTERM, W)
+    self.term_sums = {k: self.term_sums_buf[i] for i, k in enumerate(fused.TERMS)}
+    assert list(REWARD_WEIGHTS) == list(fused.TERMS)
+    # uniform draws of one env step: observation noise first, then the slots of include/b200sim.h
+    self.u0 = 9 + 2 * self.num_actions
+    self.nrand = self.u0 + 21
+    self.U = z(W, self.nrand)
+    self.external_U = False      # tests fill U themselves to drive both implementations with the same draws
     self.cmd_ranges = dict(lin_vel_x=(-1.0, 1.0), lin_vel_y=(-1.0, 1.0), ang_vel_z=(-0.5, 0.5), heading=(-math.pi, math.pi))
     torch.manual_seed(seed)
+    self._params = self._make_params() if use_fused else None
     self._reset_all()
     self.graph = None
     if use_graph:
@@ -120,16 +136,19 @@ class G1VelocityFlatEnv:
     return cv[:, 3:6] + torch.cross(cv[:, 0:3], off, dim=-1)
 
   # ------------------------------------------------------------------------------------------------ pieces of the step
-  def _resample_commands(self, mask):
-    W, dev = self.num_envs, self.device
-    u = lambda lo, hi: lo + (hi - lo) * torch.rand(W, device=dev)      # noqa: E731
+  def _u(self, slot, lo, hi):
+    """lo + (hi - lo) * U[:, slot]"""
+    return lo + (hi - lo) * self.U[:, slot]
+
+  def _resample_commands(self, mask, s0):
+    """s0: first of the 7 slots of U this resample consumes (reset: u0 + 4, timer: u0 + 11)."""
     r = self.cmd_ranges
-    new = torch.stack([u(*r["lin_vel_x"]), u(*r["lin_vel_y"]), u(*r["ang_vel_z"])], dim=1)
+    new = torch.stack([self._u(s0, *r["lin_vel_x"]), self._u(s0 + 1, *r["lin_vel_y"]), self._u(s0 + 2, *r["ang_vel_z"])], dim=1)
     self.command.copy_(torch.where(mask.unsqueeze(1), new, self.command))
-    self.heading_target.copy_(torch.where(mask, u(*r["heading"]), self.heading_target))
-    self.is_heading.copy_(torch.where(mask, torch.rand(W, device=dev) <= 0.3, self.is_heading))
-    self.is_standing.copy_(torch.where(mask, torch.rand(W, device=dev) <= 0.1, self.is_standing))
-    self.cmd_time_left.copy_(torch.where(mask, u(3.0, 8.0), self.cmd_time_left))
+    self.heading_target.copy_(torch.where(mask, self._u(s0 + 3, *r["heading"]), self.heading_target))
+    self.is_heading.copy_(torch.where(mask, self.U[:, s0 + 4] <= 0.3, self.is_heading))
+    self.is_standing.copy_(torch.where(mask, self.U[:, s0 + 5] <= 0.1, self.is_standing))
+    self.cmd_time_left.copy_(torch.where(mask, self._u(s0 + 6, 3.0, 8.0), self.cmd_time_left))
 
   def _update_commands(self):
     err = mdp.wrap_to_pi(self.heading_target - mdp.heading_w(self._root_quat()))
@@ -139,13 +158,12 @@ class G1VelocityFlatEnv:
 
   def _reset_masked(self, mask):
     """reset_root_state_uniform + reset_joints_by_offset (velocity_env_cfg.py:206-223), written through a mask."""
-    W, dev, D = self.num_envs, self.device, self.D
-    u = lambda lo, hi: lo + (hi - lo) * torch.rand(W, device=dev)      # noqa: E731
+    W, D, u0 = self.num_envs, self.D, self.u0
     qpos = self.default_qpos.expand(W, -1).clone()
-    qpos[:, 0] += u(-0.5, 0.5) + self.env_origins[:, 0]
-    qpos[:, 1] += u(-0.5, 0.5) + self.env_origins[:, 1]
+    qpos[:, 0] += self._u(u0, -0.5, 0.5) + self.env_origins[:, 0]
+    qpos[:, 1] += self._u(u0 + 1, -0.5, 0.5) + self.env_origins[:, 1]
     qpos[:, 2] += self.env_origins[:, 2]
-    qpos[:, 3:7] = mdp.quat_mul(qpos[:, 3:7], mdp.quat_from_yaw(u(-3.14, 3.14)))
+    qpos[:, 3:7] = mdp.quat_mul(qpos[:, 3:7], mdp.quat_from_yaw(self._u(u0 + 2, -3.14, 3.14)))
     m1 = mask.unsqueeze(1)
     D.qpos.copy_(torch.where(m1, qpos, D.qpos))
     D.qvel.copy_(torch.where(m1, torch.zeros_like(D.qvel), D.qvel))
@@ -157,10 +175,11 @@ class G1VelocityFlatEnv:
       self.air[k].copy_(torch.where(m1, torch.zeros_like(self.air[k]), self.air[k]))
     self.peak_heights.copy_(torch.where(m1, torch.zeros_like(self.peak_heights), self.peak_heights))
     self.episode_length_buf.copy_(torch.where(mask, torch.zeros_like(self.episode_length_buf), self.episode_length_buf))
-    self.push_time_left.copy_(torch.where(mask, u(1.0, 3.0), self.push_time_left))
-    self._resample_commands(mask)
+    self.push_time_left.copy_(torch.where(mask, self._u(u0 + 3, 1.0, 3.0), self.push_time_left))
+    self._resample_commands(mask, u0 + 4)
 
   def _reset_all(self):
+    self.U.uniform_()
     self._reset_masked(torch.ones(self.num_envs, dtype=torch.bool, device=self.device))
     engine.forward(self.M, self.D)
     self.air["last_time"].copy_(self.D.time)
@@ -168,8 +187,8 @@ class G1VelocityFlatEnv:
     self._compute_obs()
 
   def _compute_obs(self):
-    D, W, dev = self.D, self.num_envs, self.device
-    un = lambda t, a: t + (2.0 * torch.rand_like(t) - 1.0) * a      # noqa: E731   Unoise(n_min=-a, n_max=a)
+    D, nu = self.D, self.num_actions
+    un = lambda t, a, s: t + (2.0 * self.U[:, s:s + t.shape[1]] - 1.0) * a      # noqa: E731   Unoise(n_min=-a, n_max=a)
     sd = D.sensordata
     lin, gyro = sd[:, self.s_linvel:self.s_linvel + 3], sd[:, self.s_gyro:self.s_gyro + 3]
     pg = self._projected_gravity(self._root_quat())
@@ -178,12 +197,16 @@ class G1VelocityFlatEnv:
     found = torch.stack([sd[:, a] for a in self.s_found], dim=1)
     force = torch.stack([sd[:, a:a + 3] for a in self.s_force], dim=1)
     clean = [lin, gyro * 0.25, pg, jp, jv * 0.05, self.action, self.command]
-    noisy = [un(lin, 0.5), un(gyro, 0.2) * 0.25, un(pg, 0.05), un(jp, 0.01), un(jv, 1.5) * 0.05, self.action, self.command]
+    noisy = [un(lin, 0.5, 0), un(gyro, 0.2, 3) * 0.25, un(pg, 0.05, 6), un(jp, 0.01, 9), un(jv, 1.5, 9 + nu) * 0.05, self.action, self.command]
     foot_z = torch.stack([D.site_xpos[:, s, 2] for s in self.feet_sites], dim=1)
     self.obs.copy_(torch.cat(noisy, dim=1))
     self.critic_obs.copy_(torch.cat(clean + [foot_z, self.air["current_air_time"], (found > 0).float(), mdp.contact_force_obs(force)], dim=1))
 
   def _step_impl(self):
+    if not self.external_U:
+      self.U.uniform_()
+    if self.use_fused:
+      return self._step_fused()
     D, M = self.D, self.M
     # action manager: process + apply (the same joint targets on every sub-step)
     self.prev_action.copy_(self.action)
@@ -240,15 +263,59 @@ class G1VelocityFlatEnv:
     self.air["last_time"].copy_(torch.where(self.dones, D.time, self.air["last_time"]))
     # command manager: resample on timers, heading control
     self.cmd_time_left -= self.step_dt
-    self._resample_commands(self.cmd_time_left <= 0.0)
+    self._resample_commands(self.cmd_time_left <= 0.0, self.u0 + 11)
     self._update_commands()
     # interval event: push_by_setting_velocity every U(1, 3) s (velocity_env_cfg.py:224-229)
     self.push_time_left -= self.step_dt
     push = self.push_time_left <= 0.0
-    kick = (torch.rand(self.num_envs, 2, device=self.device) - 0.5)
+    kick = self.U[:, self.u0 + 18:self.u0 + 20] - 0.5
     D.qvel[:, 0:2].copy_(torch.where(push.unsqueeze(1), D.qvel[:, 0:2] + kick, D.qvel[:, 0:2]))
-    self.push_time_left.copy_(torch.where(push, 1.0 + 2.0 * torch.rand(self.num_envs, device=self.device), self.push_time_left))
+    self.push_time_left.copy_(torch.where(push, self._u(self.u0 + 20, 1.0, 3.0), self.push_time_left))
     self._compute_obs()
+
+  # ------------------------------------------------------------------------------------------------ fused path
+  def _make_params(self):
+    m, D, W = self.m, self.D, self.num_envs
+    p = fused.VelocityMdp()
+    p.nworld, p.nq, p.nv, p.nu, p.nbody, p.nsite, p.nsensordata, p.nrand = W, m.nq, m.nv, m.nu, m.nbody, m.nsite, m.nsensordata, self.nrand
+    self.soft_lo, self.soft_hi = self.soft_limits[:, 0].contiguous(), self.soft_limits[:, 1].contiguous()
+    ptr = lambda t: t.data_ptr()      # noqa: E731
+    for n in ("qpos", "qvel", "qacc_warmstart", "ctrl", "time", "sensordata", "xquat", "cvel", "site_xpos", "subtree_com"):
+      setattr(p, n, ptr(getattr(D, n)))
+    for n in ("default_qpos", "action_scale", "soft_lo", "soft_hi", "std_standing", "std_walking", "std_running", "env_origins",
+              "actions_in", "action", "prev_action", "command", "heading_target", "cmd_time_left", "push_time_left", "is_heading",
+              "is_standing", "dones", "time_outs", "episode_length_buf", "peak_heights", "obs", "critic_obs", "rew", "U"):
+      t = getattr(self, n)
+      assert t.is_contiguous()
+      setattr(p, n, ptr(t))
+    p.term_sums = ptr(self.term_sums_buf)
+    p.air_cur, p.air_last = ptr(self.air["current_air_time"]), ptr(self.air["last_air_time"])
+    p.con_cur, p.con_last = ptr(self.air["current_contact_time"]), ptr(self.air["last_contact_time"])
+    p.air_last_time = ptr(self.air["last_time"])
+    p.torso = self.torso
+    for k in range(2):
+      p.feet_site[k], p.feet_body[k] = self.feet_sites[k], self.feet_site_body[k]
+      p.feet_root[k] = int(m.body_rootid[self.feet_site_body[k]])
+      p.s_found[k], p.s_force[k] = self.s_found[k], self.s_force[k]
+    p.s_gyro, p.s_linvel, p.s_angmom, p.s_self = self.s_gyro, self.s_linvel, self.s_angmom, self.s_self
+    p.max_episode_length = self.max_episode_length
+    p.step_dt, p.landed_dt, p.fall_angle = self.step_dt, self.step_dt + 1e-8, math.radians(70.0)
+    for i, k in enumerate(fused.TERMS):
+      p.weight[i] = REWARD_WEIGHTS[k] * self.step_dt
+    for i, k in enumerate(("lin_vel_x", "lin_vel_y", "ang_vel_z", "heading")):
+      lo, hi = self.cmd_ranges[k]
+      p.cmd_lo[i], p.cmd_hi[i], p.cmd_span[i] = lo, hi, hi - lo
+    return p
+
+  def _step_fused(self):
+    p, dev, M, D = self._params, self.device, self.M, self.D
+    fused.apply_action(p, dev)
+    for _ in range(self.decimation):
+      engine.step(M, D)
+      fused.air_time(p, dev)
+    fused.post(p, dev)
+    engine.forward(M, D)
+    fused.observe(p, dev)
 
   def _capture(self):
     side = torch.cuda.Stream(device=self.device)

@@ -297,6 +297,53 @@ int b2s_step_host(const b2s_model* m, b2s_data* d, const float* ctrl_host, int n
 int b2s_profile_step(const b2s_model* m, b2s_data* d, void* stream, int reps,
                      const char** names, float* ms, int cap);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Fused manager side of the velocity task's env step.  The reference runs ~60 manager terms as
+ * ~500 small torch kernels per env step (envs/manager_based_rl_env.py:111-152, tasks/velocity/mdp/rewards.py:23-359,
+ * velocity_env_cfg.py:138-240, sensor/contact_sensor.py:327-367); these four launches read the engine's state arrays
+ * directly, one warp per env.  All pointers are device pointers owned by the caller (torch tensors); `U` is a
+ * (nworld, nrand) buffer of uniform [0,1) numbers refreshed by the caller before every env step, consumed at fixed
+ * slots (B2S_VEL_U_*), so that a host-side restatement can be checked against the kernels on identical draws.
+ * Index fields address the engine's sensordata / body / site arrays.  Weights follow B2S_VEL_TERM_* order. */
+enum {
+  B2S_VEL_TERM_TRACK_LIN = 0, B2S_VEL_TERM_TRACK_ANG, B2S_VEL_TERM_UPRIGHT, B2S_VEL_TERM_POSE, B2S_VEL_TERM_BODY_ANG_VEL,
+  B2S_VEL_TERM_ANGMOM, B2S_VEL_TERM_DOF_LIMITS, B2S_VEL_TERM_ACTION_RATE, B2S_VEL_TERM_SELF_COLLISIONS, B2S_VEL_TERM_AIR_TIME,
+  B2S_VEL_TERM_FOOT_CLEARANCE, B2S_VEL_TERM_FOOT_SWING, B2S_VEL_TERM_FOOT_SLIP, B2S_VEL_TERM_SOFT_LANDING, B2S_VEL_NTERM
+};
+/* slots of U: observation noise (lin 3, gyro 3, gravity 3, joint pos nu, joint vel nu) starts at 0; the rest follows at
+ * base = 9 + 2 nu: reset x, y, yaw, push timer; command resample at reset (vx, vy, wz, heading, is_heading, is_standing,
+ * timer); the same 7 for the timer-driven resample; push kick x, y, next push timer.  nrand >= base + 21. */
+typedef struct b2s_velocity_mdp {
+  int nworld, nq, nv, nu, nbody, nsite, nsensordata, nrand;
+  /* engine state (b2s_data fields) */
+  float *qpos, *qvel, *qacc_warmstart, *ctrl;
+  const float *time, *sensordata, *xquat, *cvel, *site_xpos, *subtree_com;
+  /* task constants */
+  const float *default_qpos, *action_scale, *soft_lo, *soft_hi, *std_standing, *std_walking, *std_running, *env_origins;
+  int torso, feet_site[2], feet_body[2], feet_root[2];
+  int s_gyro, s_linvel, s_angmom, s_found[2], s_force[2], s_self;
+  int max_episode_length;
+  float step_dt, landed_dt, fall_angle;      /* landed_dt = step_dt + 1e-8 rounded to float (first-contact window) */
+  float weight[B2S_VEL_NTERM];              /* term weight x step_dt (0 = term not summed) */
+  float cmd_lo[4], cmd_hi[4], cmd_span[4];  /* lin_vel_x, lin_vel_y, ang_vel_z, heading; span = hi - lo rounded once */
+  /* env buffers */
+  const float* actions_in;
+  float *action, *prev_action, *command, *heading_target, *cmd_time_left, *push_time_left;
+  unsigned char *is_heading, *is_standing, *dones, *time_outs;
+  long long* episode_length_buf;
+  float *air_cur, *air_last, *con_cur, *con_last, *air_last_time, *peak_heights;
+  float *obs, *critic_obs, *rew, *term_sums;   /* term_sums: (B2S_VEL_NTERM, nworld) */
+  const float* U;
+} b2s_velocity_mdp;
+/* process + apply the action: prev_action <- action <- actions_in, ctrl = default joint pos + scale * action */
+int b2s_vel_apply_action(const b2s_velocity_mdp* p, void* stream);
+/* contact air-time tracker after each physics sub-step (ContactSensor._update_air_time_tracking) */
+int b2s_vel_air_time(const b2s_velocity_mdp* p, void* stream);
+/* episode counter, terminations, the 14 reward terms, then the masked reset writes of finished envs */
+int b2s_vel_post(const b2s_velocity_mdp* p, void* stream);
+/* after forward(): command timers / heading control, push event, policy and critic observations */
+int b2s_vel_observe(const b2s_velocity_mdp* p, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

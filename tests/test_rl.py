@@ -151,3 +151,53 @@ def test_velocity_env_graph_step_and_ppo_iteration():
   w0 = algo.ac.actor[0].weight.clone()
   algo.rollout(); info = algo.update()
   assert math.isfinite(info["value_loss"]) and not torch.equal(w0, algo.ac.actor[0].weight)
+
+
+@pytest.mark.gpu
+def test_fused_manager_kernels_match_torch_terms():
+  """csrc/k_mdp.cu against the torch restatement of the same manager terms on identical uniform draws: physics inputs
+  (ctrl, reset qpos / qvel, pushes) bit-identical, so both envs stay on one trajectory; rewards / observations /
+  commands within fp32 rounding; terminations, resets and episode counters equal."""
+  from asimov_mjlab_b200.rl.velocity_env import G1VelocityFlatEnv
+  W = 256
+  a = G1VelocityFlatEnv(W, "cuda:0", seed=3, use_graph=False, use_fused=False)
+  b = G1VelocityFlatEnv(W, "cuda:0", seed=3, use_graph=False, use_fused=True)
+  for e in (a, b):
+    e.external_U = True
+    e.max_episode_length = 37           # time-outs as well as falls
+  b._params.max_episode_length = 37
+  g = torch.Generator(device="cuda:0").manual_seed(11)
+  # same start
+  U = torch.rand(W, a.nrand, device="cuda:0", generator=g)
+  for e in (a, b):
+    e.U.copy_(U); e.external_U = True
+    e._reset_masked(torch.ones(W, dtype=torch.bool, device="cuda:0"))
+    from asimov_mjlab_b200 import engine
+    engine.forward(e.M, e.D)
+    e.air["last_time"].copy_(e.D.time)
+    e._update_commands(); e._compute_obs()
+  assert torch.equal(a.D.qpos, b.D.qpos)
+  ndone = npush = 0
+  for it in range(90):
+    U = torch.rand(W, a.nrand, device="cuda:0", generator=g)
+    act = torch.randn(W, a.num_actions, device="cuda:0", generator=g) * (3.0 if it % 3 == 0 else 0.3)
+    pa, pb = a.push_time_left.clone(), b.push_time_left.clone()
+    for e in (a, b):
+      e.U.copy_(U)
+      e.step(act)
+    assert torch.equal(a.D.ctrl, b.D.ctrl) and torch.equal(a.D.qpos, b.D.qpos) and torch.equal(a.D.qvel, b.D.qvel), it
+    assert torch.equal(a.dones, b.dones) and torch.equal(a.time_outs, b.time_outs)
+    assert torch.equal(a.episode_length_buf, b.episode_length_buf)
+    assert torch.equal(a.is_heading, b.is_heading) and torch.equal(a.is_standing, b.is_standing)
+    for k in a.air:
+      assert torch.allclose(a.air[k], b.air[k], atol=1e-6), k
+    assert torch.allclose(a.rew, b.rew, rtol=2e-5, atol=2e-6)
+    assert torch.allclose(a.obs, b.obs, rtol=1e-5, atol=2e-6) and torch.allclose(a.critic_obs, b.critic_obs, rtol=1e-5, atol=2e-6)
+    assert torch.allclose(a.command, b.command, atol=2e-6) and torch.allclose(a.heading_target, b.heading_target, atol=1e-6)
+    assert torch.allclose(a.cmd_time_left, b.cmd_time_left, atol=1e-6) and torch.allclose(a.push_time_left, b.push_time_left, atol=1e-6)
+    assert torch.allclose(a.peak_heights, b.peak_heights, atol=1e-6)
+    assert torch.equal(a.action, b.action) and torch.equal(a.prev_action, b.prev_action)
+    ndone += int(a.dones.sum()); npush += int((a.push_time_left > pa).sum())
+  assert ndone > W and npush > W // 2          # falls, time-outs and pushes were all exercised
+  for k in a.term_sums:
+    assert torch.allclose(a.term_sums[k], b.term_sums[k], rtol=1e-4, atol=1e-5), k
