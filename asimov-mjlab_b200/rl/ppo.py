@@ -51,10 +51,11 @@ class EmpiricalNormalization(nn.Module):
 
   @torch.no_grad()
   def update(self, x: torch.Tensor) -> None:
-    n = torch.tensor(float(x.shape[0]), device=x.device)
+    """In place and free of host values, so that it can sit inside a CUDA graph (the graph keeps the buffers' storage)."""
     mean = x.mean(dim=0)
     m2 = ((x - mean) ** 2).sum(dim=0)
-    self.d_mean, self.d_m2, self.d_count = self._merge(self.d_mean, self.d_m2, self.d_count, mean, m2, n)
+    new = self._merge(self.d_mean, self.d_m2, self.d_count, mean, m2, float(x.shape[0]))
+    self.d_mean.copy_(new[0]); self.d_m2.copy_(new[1]); self.d_count.copy_(new[2])
 
   @torch.no_grad()
   def sync(self) -> None:
@@ -65,7 +66,8 @@ class EmpiricalNormalization(nn.Module):
       gmean = mean * n; dist.all_reduce(gmean); gmean /= torch.clamp(tot, min=1.0)
       gm2 = m2 + n * (mean - gmean) ** 2; dist.all_reduce(gm2)
       n, mean, m2 = tot, gmean, gm2
-    self.mean, self.m2, self.count = self._merge(self.mean, self.m2, self.count, mean, m2, n)
+    new = self._merge(self.mean, self.m2, self.count, mean, m2, n)
+    self.mean.copy_(new[0]); self.m2.copy_(new[1]); self.count.copy_(new[2])
     self.d_mean.zero_(); self.d_m2.zero_(); self.d_count.zero_()
 
   def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -94,7 +96,7 @@ class ActorCritic(nn.Module):
 
   def dist(self, obs):
     mean = self.actor(self.obs_norm(obs))
-    return torch.distributions.Normal(mean, self.std.expand_as(mean).clamp(min=1e-6))
+    return torch.distributions.Normal(mean, self.std.expand_as(mean).clamp(min=1e-6), validate_args=False)
 
   def value(self, critic_obs):
     return self.critic(self.critic_norm(critic_obs)).squeeze(-1)
@@ -103,13 +105,18 @@ class ActorCritic(nn.Module):
 class PPO:
   def __init__(self, env, device, steps_per_env: int = 24, lr: float = 1e-3, gamma: float = 0.99, lam: float = 0.95, clip: float = 0.2,
                entropy_coef: float = 0.01, value_coef: float = 1.0, epochs: int = 5, mini_batches: int = 4, desired_kl: float = 0.01,
-               max_grad_norm: float = 1.0, seed: int = 0):
+               max_grad_norm: float = 1.0, seed: int = 0, use_graph: bool = True, tf32: bool = True):
     self.env, self.device, self.T = env, device, steps_per_env
+    if tf32:      # the policy MLPs are library GEMMs; TF32 tensor cores for them (the physics stays fp32)
+      torch.backends.cuda.matmul.allow_tf32 = True
+      torch.backends.cudnn.allow_tf32 = True
     self.gamma, self.lam, self.clip, self.entropy_coef, self.value_coef = gamma, lam, clip, entropy_coef, value_coef
     self.epochs, self.mini_batches, self.desired_kl, self.max_grad_norm, self.lr = epochs, mini_batches, desired_kl, max_grad_norm, lr
     torch.manual_seed(seed)            # same seed on every rank: identical initial weights, no broadcast needed
     self.ac = ActorCritic(env.num_obs, env.num_privileged_obs, env.num_actions).to(device)
-    self.opt = torch.optim.Adam(self.ac.parameters(), lr=lr)
+    # learning rate lives on the device: the adaptive-KL schedule then needs no host synchronisation per mini-batch
+    self.lr_t = torch.tensor(float(lr), device=device)
+    self.opt = torch.optim.Adam(self.ac.parameters(), lr=self.lr_t, capturable=True)
     W, T = env.num_envs, steps_per_env
     z = lambda *s: torch.zeros(*s, device=device)      # noqa: E731
     self.b_obs, self.b_cobs = z(T, W, env.num_obs), z(T, W, env.num_privileged_obs)
@@ -117,29 +124,74 @@ class PPO:
     self.b_logp, self.b_val, self.b_rew, self.b_done = z(T, W), z(T, W), z(T, W), z(T, W)
     self.ep_ret, self.ep_len = z(W), z(W)
     self.stats = dict(ret_sum=z(()), len_sum=z(()), episodes=z(()))
+    self.b_ret, self.b_adv = z(T, W), z(T, W)
+    self.loss_s, self.loss_v, self.kl = z(()), z(()), z(())
+    self._params = [p for p in self.ac.parameters()]
+    self._flat, self.flat_g = None, None
+    self.use_graph = bool(use_graph and device.type == "cuda")
+    self.t_idx = torch.zeros(1, dtype=torch.long, device=device)
+    self.step_graph = None
+    if self.use_graph:
+      self._capture()
+
+  @torch.no_grad()
+  def _rollout_step(self):
+    """One policy step + env step + bookkeeping, all in place on static tensors (row `t_idx` of the rollout buffers)."""
+    env, ac, t = self.env, self.ac, self.t_idx
+    obs, cobs = env.obs, env.critic_obs
+    ac.obs_norm.update(obs); ac.critic_norm.update(cobs)
+    d = ac.dist(obs)
+    act = d.mean + d.stddev * torch.randn_like(d.mean)      # Normal.sample() checks std on the host: not capturable
+    val = ac.value(cobs)
+    put = lambda buf, x: buf.index_copy_(0, t, x.unsqueeze(0))      # noqa: E731
+    put(self.b_obs, obs); put(self.b_cobs, cobs); put(self.b_act, act); put(self.b_mu, d.mean); put(self.b_sigma, d.stddev)
+    put(self.b_logp, d.log_prob(act).sum(-1)); put(self.b_val, val)
+    env.actions_in.copy_(act)
+    env._step_impl()
+    rew, donef = env.rew, env.dones.float()
+    # bootstrap through time-outs (rsl_rl: rewards += gamma * value * time_outs)
+    put(self.b_rew, rew + self.gamma * val * env.time_outs.float()); put(self.b_done, donef)
+    self.ep_ret += rew; self.ep_len += 1
+    self.stats["ret_sum"] += (self.ep_ret * donef).sum(); self.stats["len_sum"] += (self.ep_len * donef).sum()
+    self.stats["episodes"] += donef.sum()
+    self.ep_ret *= 1 - donef; self.ep_len *= 1 - donef
+    t += 1
+
+  def _capture(self):
+    """Policy inference, the whole env step and the rollout bookkeeping as ONE CUDA graph per rollout step."""
+    dev = self.device
+    snap = [b.clone() for b in self.ac.buffers()]
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+      for _ in range(3):
+        self.t_idx.zero_()
+        self._rollout_step()
+    torch.cuda.current_stream(dev).wait_stream(side)
+    torch.cuda.synchronize(dev)
+    self.step_graph = torch.cuda.CUDAGraph()
+    self.t_idx.zero_()
+    with torch.cuda.graph(self.step_graph):
+      self._rollout_step()
+    # undo the warm-up's side effects: normaliser statistics, episode statistics, env state
+    for b, v in zip(self.ac.buffers(), snap):
+      b.copy_(v)
+    for v in (self.ep_ret, self.ep_len, *self.stats.values()):
+      v.zero_()
+    self.env._reset_all()
+    for v in self.env.term_sums.values():
+      v.zero_()
 
   @torch.no_grad()
   def rollout(self):
     env, ac = self.env, self.ac
-    obs, extras = env.get_observations()
-    cobs = extras["observations"]["critic"]
-    for t in range(self.T):
-      ac.obs_norm.update(obs); ac.critic_norm.update(cobs)
-      d = ac.dist(obs)
-      act = d.sample()
-      self.b_obs[t].copy_(obs); self.b_cobs[t].copy_(cobs); self.b_act[t].copy_(act)
-      self.b_mu[t].copy_(d.mean); self.b_sigma[t].copy_(d.stddev)
-      self.b_logp[t].copy_(d.log_prob(act).sum(-1)); self.b_val[t].copy_(ac.value(cobs))
-      obs, rew, dones, extras = env.step(act)
-      cobs = extras["observations"]["critic"]
-      donef = dones.float()
-      # bootstrap through time-outs (rsl_rl: rewards += gamma * value * time_outs)
-      self.b_rew[t].copy_(rew + self.gamma * self.b_val[t] * extras["time_outs"].float())
-      self.b_done[t].copy_(donef)
-      self.ep_ret += rew; self.ep_len += 1
-      self.stats["ret_sum"] += (self.ep_ret * donef).sum(); self.stats["len_sum"] += (self.ep_len * donef).sum()
-      self.stats["episodes"] += donef.sum()
-      self.ep_ret *= 1 - donef; self.ep_len *= 1 - donef
+    self.t_idx.zero_()
+    for _ in range(self.T):
+      if self.step_graph is not None:
+        self.step_graph.replay()
+      else:
+        self._rollout_step()
+    cobs = env.critic_obs
     last_val = ac.value(cobs)
     adv = torch.zeros_like(self.b_rew)
     gae = torch.zeros_like(last_val)
@@ -149,55 +201,118 @@ class PPO:
       delta = self.b_rew[t] + self.gamma * nv * nonterm - self.b_val[t]
       gae = delta + self.gamma * self.lam * nonterm * gae
       adv[t] = gae
-    self.b_ret = adv + self.b_val
+    self.b_ret.copy_(adv + self.b_val)
     # advantage normalisation over the GLOBAL batch
     s = torch.stack([adv.sum(), (adv * adv).sum(), torch.tensor(float(adv.numel()), device=adv.device)])
     if _world() > 1:
       dist.all_reduce(s)
     mean = s[0] / s[2]
     std = torch.sqrt(torch.clamp(s[1] / s[2] - mean * mean, min=0.0))
-    self.b_adv = (adv - mean) / (std + 1e-8)
+    self.b_adv.copy_((adv - mean) / (std + 1e-8))
     ac.obs_norm.sync(); ac.critic_norm.sync()
+
+  # ---- update: one mini-batch = [gather, forward, losses, backward, KL, (flatten)] -> (all-reduce) -> [lr, clip, Adam]
+  def _mb_backward(self):
+    """Loss and gradients of the mini-batch whose sample indices sit in `self.mb_idx`; with several ranks the gradients and
+    the KL are also packed into one bucket for the single collective of the mini-batch."""
+    ac, idx = self.ac, self.mb_idx
+    obs, cobs, act, mu0, sig0, logp0, val0, ret, adv = (t[idx] for t in self._flat)
+    d = ac.dist(obs)
+    logp = d.log_prob(act).sum(-1)
+    val = ac.value(cobs)
+    with torch.no_grad():
+      kl = (torch.log(d.stddev / sig0 + 1e-5) + (sig0 ** 2 + (mu0 - d.mean) ** 2) / (2.0 * d.stddev ** 2) - 0.5).sum(-1).mean()
+    ratio = torch.exp(logp - logp0)
+    loss_s = torch.max(-adv * ratio, -adv * ratio.clamp(1.0 - self.clip, 1.0 + self.clip)).mean()
+    vclip = val0 + (val - val0).clamp(-self.clip, self.clip)
+    loss_v = torch.max((val - ret) ** 2, (vclip - ret) ** 2).mean()
+    loss = loss_s + self.value_coef * loss_v - self.entropy_coef * d.entropy().sum(-1).mean()
+    self.opt.zero_grad(set_to_none=True)
+    loss.backward()
+    with torch.no_grad():
+      self.loss_s.copy_(loss_s); self.loss_v.copy_(loss_v); self.kl.copy_(kl)
+      if _world() > 1:
+        self.flat_g = torch.cat([p.grad.reshape(-1) for p in self._params] + [kl.reshape(1)])
+
+  @torch.no_grad()
+  def _mb_apply(self):
+    """Adaptive learning rate on the (all-rank) mean KL (rsl_rl schedule="adaptive"), gradient clipping, Adam step."""
+    kl = self.kl
+    if _world() > 1:
+      o = 0
+      for p in self._params:
+        p.grad.copy_(self.flat_g[o:o + p.numel()].view_as(p)); o += p.numel()
+      kl = self.flat_g[o]
+    up = (kl > 2.0 * self.desired_kl).float(); down = ((kl < 0.5 * self.desired_kl) & (kl > 0.0)).float()
+    self.lr_t.copy_((self.lr_t * (1.0 + 0.5 * down - (1.0 / 3.0) * up)).clamp(1e-5, 1e-2))
+    nn.utils.clip_grad_norm_(self._params, self.max_grad_norm)
+    self.opt.step()
+
+  def _capture_update(self):
+    """The two halves of a mini-batch as CUDA graphs sharing one memory pool (one graph when there is a single rank);
+    the NCCL all-reduce between them stays an ordinary stream-ordered call."""
+    dev = self.device
+    state = [p.detach().clone() for p in self._params]
+    lr0 = self.lr_t.clone()
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+      for _ in range(3):
+        self._mb_backward()
+        if _world() > 1:
+          all_reduce_mean_(self.flat_g)
+        self._mb_apply()
+    torch.cuda.current_stream(dev).wait_stream(side)
+    torch.cuda.synchronize(dev)
+    self.g_back = torch.cuda.CUDAGraph()
+    if _world() > 1:
+      with torch.cuda.graph(self.g_back):
+        self._mb_backward()
+      self.g_apply = torch.cuda.CUDAGraph()
+      with torch.cuda.graph(self.g_apply, pool=self.g_back.pool()):
+        self._mb_apply()
+    else:
+      with torch.cuda.graph(self.g_back):
+        self._mb_backward()
+        self._mb_apply()
+      self.g_apply = None
+    # undo the warm-up steps: weights, optimiser moments, learning rate
+    with torch.no_grad():
+      for p, v in zip(self._params, state):
+        p.copy_(v)
+      for st in self.opt.state.values():
+        for v in st.values():
+          if torch.is_tensor(v):
+            v.zero_()
+      self.lr_t.copy_(lr0)
 
   def update(self):
     ac = self.ac
     N = self.T * self.env.num_envs
     flat = lambda t: t.reshape(N, *t.shape[2:])      # noqa: E731
-    obs, cobs, act, mu0, sig0 = flat(self.b_obs), flat(self.b_cobs), flat(self.b_act), flat(self.b_mu), flat(self.b_sigma)
-    logp0, val0, ret, adv = flat(self.b_logp), flat(self.b_val), flat(self.b_ret), flat(self.b_adv)
     mb = N // self.mini_batches
-    loss_v = loss_s = torch.zeros((), device=self.device)
+    if self._flat is None:
+      # static views / buffers the mini-batch graphs read (b_ret / b_adv are refilled in place by rollout())
+      self._flat = tuple(flat(t) for t in (self.b_obs, self.b_cobs, self.b_act, self.b_mu, self.b_sigma, self.b_logp, self.b_val, self.b_ret, self.b_adv))
+      self.mb_idx = torch.zeros(mb, dtype=torch.long, device=self.device)
+      if self.use_graph:
+        self._capture_update()
     for _ in range(self.epochs):
       perm = torch.randperm(N, device=self.device)
       for k in range(self.mini_batches):
-        idx = perm[k * mb:(k + 1) * mb]
-        d = ac.dist(obs[idx])
-        logp = d.log_prob(act[idx]).sum(-1)
-        val = ac.value(cobs[idx])
-        with torch.no_grad():      # adaptive learning rate on the (all-rank) mean KL, rsl_rl schedule="adaptive"
-          kl = (torch.log(d.stddev / sig0[idx] + 1e-5) + (sig0[idx] ** 2 + (mu0[idx] - d.mean) ** 2) / (2.0 * d.stddev ** 2) - 0.5).sum(-1).mean()
-          kl = all_reduce_mean_(kl.clone())
-          up = (kl > 2.0 * self.desired_kl).float(); down = ((kl < 0.5 * self.desired_kl) & (kl > 0.0)).float()
-          self.lr = float(min(max(self.lr * (1.0 + 0.5 * down.item() - (1.0 / 3.0) * up.item()), 1e-5), 1e-2))
-          for g in self.opt.param_groups:
-            g["lr"] = self.lr
-        ratio = torch.exp(logp - logp0[idx])
-        loss_s = torch.max(-adv[idx] * ratio, -adv[idx] * ratio.clamp(1.0 - self.clip, 1.0 + self.clip)).mean()
-        vclip = val0[idx] + (val - val0[idx]).clamp(-self.clip, self.clip)
-        loss_v = torch.max((val - ret[idx]) ** 2, (vclip - ret[idx]) ** 2).mean()
-        loss = loss_s + self.value_coef * loss_v - self.entropy_coef * d.entropy().sum(-1).mean()
-        self.opt.zero_grad(set_to_none=True)
-        loss.backward()
-        if _world() > 1:       # one bucket: ~0.4 M parameters
-          grads = [p.grad for p in ac.parameters() if p.grad is not None]
-          flat_g = torch.cat([g.reshape(-1) for g in grads])
-          all_reduce_mean_(flat_g)
-          o = 0
-          for g in grads:
-            g.copy_(flat_g[o:o + g.numel()].view_as(g)); o += g.numel()
-        nn.utils.clip_grad_norm_(ac.parameters(), self.max_grad_norm)
-        self.opt.step()
-    return dict(value_loss=float(loss_v.detach()), surrogate_loss=float(loss_s.detach()), lr=self.lr, noise_std=float(ac.std.detach().mean()))
+        self.mb_idx.copy_(perm[k * mb:(k + 1) * mb])
+        if self.use_graph:
+          self.g_back.replay()
+          if self.g_apply is not None:
+            all_reduce_mean_(self.flat_g)      # ONE collective per mini-batch: gradients (~0.4 M parameters) + KL
+            self.g_apply.replay()
+        else:
+          self._mb_backward()
+          if _world() > 1:
+            all_reduce_mean_(self.flat_g)
+          self._mb_apply()
+    self.lr = float(self.lr_t)
+    return dict(value_loss=float(self.loss_v), surrogate_loss=float(self.loss_s), lr=self.lr, noise_std=float(ac.std.detach().mean()))
 
   def episode_stats(self):
     s = torch.stack([self.stats["ret_sum"], self.stats["len_sum"], self.stats["episodes"]])

@@ -148,7 +148,7 @@ def test_velocity_env_graph_step_and_ppo_iteration():
   if fresh.any():
     assert (env.D.qpos[fresh, 2] - 0.76).abs().max() < 1e-3
   algo = PPO(env, torch.device("cuda:0"), steps_per_env=8)
-  w0 = algo.ac.actor[0].weight.clone()
+  w0 = algo.ac.actor[0].weight.detach().clone()      # a grad-tracking clone would pin an AccumulateGrad node made on the default stream and break the update graph capture
   algo.rollout(); info = algo.update()
   assert math.isfinite(info["value_loss"]) and not torch.equal(w0, algo.ac.actor[0].weight)
 
