@@ -43,6 +43,9 @@ def alg_bytes(m, friction_geoms):
   r = m.nq + m.nv + m.nu + m.nv + 1 + 6 * nb + m.nv
   w = m.nq + 3 * m.nv + 1 + m.nsensordata + (3 + 4 + 3 + 6) * nb + 12 * m.nsite
   return 4 * (r + w + 3 * friction_geoms)
+# DRAM traffic of one sub-step (7 stage kernels), dram__bytes_read.sum + dram__bytes_write.sum from the `ncu --set full`
+# capture profiles/step_r1g_metrics.txt (G1-flat, 4096 worlds): 115 813 888 B read + 880 128 B written
+NCU_TRAFFIC = {("g1_flat", 4096): (116694016, "profiles/step_r1g_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step)")}
 DECIMATION = 4
 RESET_PERIOD_STEPS = 250            # reset every 1000 sub-steps, forward() inside the timed region
 
@@ -327,7 +330,9 @@ def run_b200(args):
             "d2h_bytes_per_step": int(E * (m.nq + m.nv + m.nsensordata) * 4), "ms_per_step": ms_e2e / e2e_steps,
             "api": "b2s_step_host (C ABI) with pinned host buffers"},
     "gpu_launches": int(args.steps * per_graph["decimation"] + n_resets * per_graph["forward"]),
-    "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                 "traffic": NCU_TRAFFIC.get((args.workload, E), (None, None))[0], "traffic_source": NCU_TRAFFIC.get((args.workload, E), (None, None))[1],
+                 "algorithmic_bytes_per_launch": E * ab,
                  "peak_source": peak_src, "scope": f"whole sub-step (7 stage kernels); algorithmic bytes {ab} B per world per sub-step",
                  "dominant_kernel": top, "dominant_share": stages[top] / tot, "stage_ms": stages},
     "clocks": clocks,
