@@ -273,6 +273,20 @@ def build_g1_flat(xml_path) -> HostModel:
   return m
 
 
+def build_g1_tracking(xml_path) -> HostModel:
+  """Compiled model of Mjlab-Tracking-Flat-Unitree-G1 (tasks/tracking/config/g1/env_cfgs.py:19-82,
+  tracking_env_cfg.py:47-62): the same robot entity, only the self-collision sensor, nconmax 35 / njmax 250."""
+  robot = build_robot_entity(xml_path, G1_FULL_COLLISION, G1_ACTUATORS, G1_KNEES_BENT)
+  selfc = ContactSensorCfg(
+    name="self_collision", primary=ContactMatch("subtree", "pelvis", "robot"),
+    secondary=ContactMatch("subtree", "pelvis", "robot"), fields=("found",), reduce="none", num_slots=1)
+  scene = build_scene({"robot": robot}, sensors=(selfc,))
+  velocity_sim_options(scene)
+  m = scene.compile()
+  m.meta = dict(task="Mjlab-Tracking-Flat-Unitree-G1", nconmax=35, njmax=250, decimation=4)
+  return m
+
+
 # ---------------------------------------------------------------------------
 # Unitree Go1 (values restated from src/mjlab/asset_zoo/robots/unitree_go1/go1_constants.py:33-153)
 # ---------------------------------------------------------------------------

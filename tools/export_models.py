@@ -14,6 +14,10 @@ scenes.save_model(m, os.path.join(scenes.ASSET_DIR, "g1_flat.npz"))
 print("g1_flat: nq", m.nq, "nv", m.nv, "nu", m.nu, "nbody", m.nbody, "ngeom", m.ngeom,
       "nsite", m.nsite, "nsensordata", m.nsensordata, "meaninertia", m.stat.meaninertia)
 
+t = scenes.build_g1_tracking(os.path.join(zoo, "unitree_g1/xmls/g1.xml"))
+scenes.save_model(t, os.path.join(scenes.ASSET_DIR, "g1_tracking.npz"))
+print("g1_tracking: nsensordata", t.nsensordata, "sensors", t.names["sensor"])
+
 for terr in ("plane", "rough", "rough_hf"):
   g = scenes.build_go1(os.path.join(zoo, "unitree_go1/xmls/go1.xml"), terrain=terr)
   name = {"plane": "go1_flat", "rough": "go1_rough", "rough_hf": "go1_rough_hf"}[terr]

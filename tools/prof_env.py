@@ -10,7 +10,11 @@ import torch
 from asimov_mjlab_b200.rl.velocity_env import G1VelocityFlatEnv
 
 W = int(os.environ.get("W", "4096"))
-env = G1VelocityFlatEnv(W, "cuda:0", seed=0)
+if os.environ.get("ENV", "velocity") == "tracking":
+  from asimov_mjlab_b200.rl.tracking_env import G1TrackingFlatEnv
+  env = G1TrackingFlatEnv(W, "cuda:0", seed=0)
+else:
+  env = G1VelocityFlatEnv(W, "cuda:0", seed=0, use_fused=bool(int(os.environ.get("FUSED", "1"))))
 act = torch.randn(64, W, env.num_actions, device="cuda:0")
 for i in range(40):
   env.step(act[i % 64])
@@ -21,11 +25,6 @@ for i in range(100):
   env.step(act[i % 64])
 e1.record(); torch.cuda.synchronize()
 print("env.step ms", e0.elapsed_time(e1) / 100, "env-steps/s", W * 100 / (e0.elapsed_time(e1) * 1e-3))
-e0.record()
-for i in range(100):
-  env.sim.step_decimation()
-e1.record(); torch.cuda.synchronize()
-print("physics decimation ms", e0.elapsed_time(e1) / 100)
 torch.cuda.profiler.start()
 env.step(act[0])
 torch.cuda.synchronize()
