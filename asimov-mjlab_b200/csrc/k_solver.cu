@@ -37,7 +37,7 @@ extern __shared__ float b2s_smem[];
 __host__ __device__ inline int solve_scratch_floats(int nb) { return 6 * (nb > 32 ? nb : 32) + 32 + 32; }
 __host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      // offset of the scratch area
   const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
-  return (HF + 8 * NVP + 6 * N + 3 * njmax + nconmax + 2 + 3) & ~3;
+  return (HF + 8 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
 }
 __host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T) {
   return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + 3) & ~3;
@@ -45,11 +45,11 @@ __host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int nj
 
 // Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
 //   H hdim*ld | invd 7T (padded to a float4 multiple) | 8 vectors of NVP | cdof 6*hdim | Jaref, Jv, D njmax each |
-//   run list nconmax+2 | scratch X/Y 6*max(nb,32), KW 32, Li 32
+//   run list nconmax+2 | active-set bit mask njmax/32 | scratch X/Y 6*max(nb,32), KW 32, Li 32
 template <int T>
 struct SolveCtx {
   static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 8 * NVP + 6 * N;
-  int lane, nv, nvp, nb, nefc, nl, nrun, njmax, soff;
+  int lane, nv, nvp, nb, nefc, nl, nrun, njmax, nconmax, soff;
   static constexpr int ld = LD, hfloats = HF;
   const float *M, *G, *aref;
   const int* bp;
@@ -69,6 +69,7 @@ struct SolveCtx {
   DEV float* Jv() const { return sm + FIX + njmax; }
   DEV float* D() const { return sm + FIX + 2 * njmax; }
   DEV int* run() const { return (int*)(sm + FIX + 3 * njmax); }
+  DEV unsigned* amask() const { return (unsigned*)(sm + FIX + 3 * njmax) + nconmax + 2; }
   DEV float* X() const { return sm + soff; }
   DEV float* KW() const { return sm + soff + 6 * max(nb, 32); }
   DEV int* Li() const { return (int*)(sm + soff + 6 * max(nb, 32) + 32); }
@@ -374,6 +375,25 @@ DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, i
   __syncwarp();
 }
 
+// Active set (rows with Jaref < 0) as a bit mask in shared memory; returns true when it equals the mask of the previous
+// call.  H = M + J^T D J depends on the state only through this set (pyramidal cones: D is fixed per row), so an
+// unchanged set means the factor of the previous iteration is still the factor of H (MuJoCo's Newton solver also
+// refactors only on a change of the active set).
+template <int T>
+DEV bool active_set_unchanged(const SolveCtx<T>& c) {
+  bool same = true;
+  ROLL
+  for (int base = 0; base < c.nefc; base += 32) {
+    const int r = base + c.lane;
+    const unsigned mk = __ballot_sync(FULL, r < c.nefc && c.Jaref()[r] < 0.f);
+    same &= c.amask()[base >> 5] == mk;
+    __syncwarp();
+    if (c.lane == 0) c.amask()[base >> 5] = mk;
+  }
+  __syncwarp();
+  return same;
+}
+
 // Load the lower-triangular register tiles of H = M + (J^T D J in shared memory) and factorise.
 template <int T>
 DEV void factor_H(const SolveCtx<T>& c, int bi, int bj) {
@@ -420,7 +440,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   }
   const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
   SolveCtx<T> c;
-  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.njmax = njmax;
+  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.njmax = njmax; c.nconmax = d.nconmax;
   c.soff = solve_soff(njmax, d.nconmax, T);
   c.M = d.qM + (size_t)w * nv * nvp;
   c.G = d.efc_g + (size_t)w * njmax * 6;
@@ -510,10 +530,12 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   }
   const float scale = 1.0f / (m.meaninertia * (float)max(nv, 1));
   int iter = 0;
-  bool withH = true;
+  bool withH = true, haveL = false;
 #pragma unroll 1
   while (true) {
-    assemble(c, m, withH, ia, ib);
+    // the factor in shared memory stays valid while the active set does not change
+    const bool reuse = active_set_unchanged(c) && haveL;
+    assemble(c, m, withH && !reuse, ia, ib);
     if (!withH) break;
     float gn = 0.f;
 #pragma unroll 1
@@ -522,7 +544,8 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     if (iter > 0 && scale * gn < m.tolerance) break;
     if (iter >= m.iterations) break;
     // blocked Cholesky of H on register tiles (c.H() ends up holding L), search = -H^-1 grad
-    factor_H<T>(c, bi, bj);
+    if (!reuse) factor_H<T>(c, bi, bj);
+    haveL = true;
     float b0 = lane < nv ? c.grad()[lane] : 0.f, b1 = lane + 32 < nv ? c.grad()[lane + 32] : 0.f;
     tile_chol_solve<T>(c.H(), c.invd(), c.ld, lane, b0, b1);
     if (lane < nv) c.search()[lane] = -b0;
