@@ -638,3 +638,44 @@ def test_full_size_determinism_and_world_independence(g1):
   assert torch.equal(q, q[0:1].expand_as(q))
   assert not torch.isnan(outs[0][1]).any()
   assert int(outs[0][3].max()) <= 50 and int(outs[0][4].max()) <= 300
+
+
+@pytest.mark.gpu
+def test_g1_config1_rollout_1000_steps_teacher_forced(g1):
+  """BASELINE.json configs[0]: 16 worlds, 1000 sub-steps, joint targets = default + scale * a with
+  a ~ U(-1, 1) resampled every 4 sub-steps.  fp32 trajectories of a humanoid decorrelate after a few dozen steps, so the
+  comparison is teacher-forced: the ORACLE drives the trajectory (robots stumble, fall, lie on the ground: up to dozens of
+  contacts), and every 10 sub-steps the CUDA path is restarted from the oracle's state (qpos, qvel, warm start, time) and
+  must reproduce the oracle's next sub-step -- exact contact / row counts and pair order, state within the one-step
+  tolerances -- at 100 points spread over the whole rollout."""
+  import torch
+  import bench
+  W, N = 16, 1000
+  key = g1.keys["robot/init_state"]
+  qpos = np.tile(np.asarray(key["qpos"], np.float64), (W, 1))
+  rng = np.random.default_rng(0)
+  qpos[:, 7:] += 0.02 * rng.standard_normal((W, g1.nq - 7))
+  ctrl0 = np.tile(np.asarray(key["ctrl"], np.float64), (W, 1))
+  engine, M, D, orc, worlds = _setup(g1, W, qpos, None, ctrl0, True)
+  targets = bench.action_targets(g1, N // 4, W, seed=0)
+  checked = ncon_max = 0
+  fell = 0
+  for s in range(N):
+    if s % 4 == 0:
+      for w in range(W):
+        worlds[w]["ctrl"][:] = targets[s // 4, w]
+    if s % 10 == 0:
+      for f in ("qpos", "qvel", "qacc_warmstart", "ctrl"):
+        getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+      D.time[:] = torch.as_tensor(np.array([float(w["time"][0]) for w in worlds]), dtype=torch.float32, device="cuda:0")
+      engine.step(M, D)
+    for w in worlds:
+      orc.step(w)
+    if s % 10 == 0:
+      _check_counts(D, worlds)
+      assert _rel_err(D, worlds, "qpos") < 2e-6 and _rel_err(D, worlds, "qvel") < 1e-3 and _rel_err(D, worlds, "qacc_warmstart") < 2e-3, s
+      checked += 1
+      ncon_max = max(ncon_max, int(D.ncon.max()))
+  fell = sum(float(w["qpos"][2]) < 0.4 for w in worlds)
+  assert checked == 100 and ncon_max >= 12 and fell >= 4      # the rollout reached fallen, many-contact states
+  assert all(np.isfinite(w["qpos"]).all() for w in worlds)
