@@ -147,20 +147,21 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
   }
 }
 
-// shared per warp: cacc 6nb | bvel 6nb | lm 3nb | am 3nb | slv 3nb
+// shared per warp: cacc 6nb | bvel 6nb | lm 3nb | am 3nb | slv 3nb | dof 6nv
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
   const int nb = m.nbody, nv = m.nv;
-  float* s_cacc = b2s_smem + (size_t)warp * 21 * nb;
+  float* s_cacc = b2s_smem + (size_t)warp * (21 * nb + 6 * nv);
   float* s_bvel = s_cacc + 6 * nb;
   float* s_lm = s_bvel + 6 * nb;
   float* s_am = s_lm + 3 * nb;
   float* s_slv = s_am + 3 * nb;
+  float* s_dof = s_slv + 3 * nb;
   const float* qvel = d.qvel + (size_t)w * nv;
   // contact cache (only when the model has contact sensors): per-warp [nconmax][4] ints then [nconmax][15] floats
-  int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * 21 * nb) + (size_t)warp * CC_WORDS * d.nconmax;
+  int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * (21 * nb + 6 * nv)) + (size_t)warp * CC_WORDS * d.nconmax;
   float* s_cf = (float*)(s_ci + 4 * d.nconmax);
   const int ncon = m.need_concache ? d.ncon[w] : 0;
   if (m.need_concache) fill_contact_cache(m, d, w, ncon, s_ci, s_cf, lane);
@@ -172,14 +173,13 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
   const float* xipos = d.xipos + (size_t)w * 3 * nb;
   // cacc = cacc_world + sum over ancestor dofs (cdof_dot qvel + cdof qacc)
   const bool grav = !(m.disableflags & B2S_DSBL_GRAVITY);
+  // per-dof term cdof_dot qvel + cdof qacc, once per dof (coalesced global reads), summed per body from shared memory
+  for (int i = lane; i < 6 * nv; i += 32) { const int j = i / 6; s_dof[i] = cdd[i] * qvel[j] + cdof[i] * qacc[j]; }
+  __syncwarp();
   for (int b = lane; b < nb; b += 32) {
     sv6 a = zero6();
     if (grav) { a.v[3] = -m.gravity[0]; a.v[4] = -m.gravity[1]; a.v[5] = -m.gravity[2]; }
-    for (int c = m.body_chain_adr[b]; c < m.body_chain_adr[b + 1]; c++) {
-      const int j = m.body_chain[c];
-      axpy6(a, qvel[j], ld6(cdd + 6 * j));
-      axpy6(a, qacc[j], ld6(cdof + 6 * j));
-    }
+    for (int c = m.body_chain_adr[b]; c < m.body_chain_adr[b + 1]; c++) axpy6(a, 1.0f, ld6(s_dof + 6 * m.body_chain[c]));
     st6(s_cacc + 6 * b, a);
     st6(d.cacc + ((size_t)w * nb + b) * 6, a);
   }
@@ -328,11 +328,28 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const Mode
   }
   __syncwarp();
   if (use) {
+    // A = lower(M) - dt diag(dg), zero strict upper triangle (the substitution needs it).  One lane per row, the row read
+    // as float4 with every load in flight before the first use (nvp is a multiple of 4, rows are 16-byte aligned).
     const float* M = d.qM + (size_t)w * nv * nvp;
-    for (int i = lane; i < nv * nvp; i += 32) {
-      const int r = i / nvp, c = i - r * nvp;
-      if (c <= r) A[r * ld + c] = M[i] - (c == r ? dt * dg[r] : 0.f);
-      else if (c < nv) A[r * ld + c] = 0.f;     // the substitution needs a zero strict upper triangle
+    constexpr int Q = (7 * T + 3) / 4;
+    const int n4 = nvp >> 2;
+#pragma unroll 1
+    for (int r = lane; r < nv; r += 32) {
+      const float4* r4 = reinterpret_cast<const float4*>(M + (size_t)r * nvp);
+      float4 v[Q];
+#pragma unroll
+      for (int j = 0; j < Q; j++) v[j] = r4[min(j, n4 - 1)];
+      const float dd = dt * dg[r];
+      float* Ar = A + r * ld;
+#pragma unroll
+      for (int j = 0; j < Q; j++) {
+        const float e[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const int c = 4 * j + k;
+          if (c < nv) Ar[c] = c < r ? e[k] : (c == r ? e[k] - dd : 0.f);
+        }
+      }
     }
     __syncwarp();
     if (m.ntendon > 0 && m.integrator == B2S_INT_IMPLICITFAST && lane == 0) {
@@ -425,7 +442,7 @@ void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   b2s_count_launch();
 }
 size_t smem_sensors(const ModelDev& m, const DataDev& d) {
-  return (size_t)B2S_WARPS_PER_CTA * (21 * m.nbody + (m.need_concache ? CC_WORDS * d.nconmax : 0)) * sizeof(float);
+  return (size_t)B2S_WARPS_PER_CTA * (21 * m.nbody + 6 * m.nv + (m.need_concache ? CC_WORDS * d.nconmax : 0)) * sizeof(float);
 }
 size_t smem_integrate(const ModelDev& m) {
   const int T = b2s_tile_for(m.nv);
