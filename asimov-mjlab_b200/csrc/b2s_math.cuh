@@ -208,8 +208,12 @@ DEV void tile_cholesky_regs(float (&a)[T * T], int bi, int bj, float* S, int ld,
         float sdiag = a[y * T + y];
 #pragma unroll
         for (int z = 0; z < y; z++) sdiag -= a[y * T + z] * a[y * T + z];
-        const float dd = sqrtf(fmaxf(sdiag, B2S_MINVAL));
-        const float inv = 1.0f / dd;
+        // 1/sqrt by the SFU approximation + one Newton step (full fp32 accuracy), sqrt = s * rsqrt(s): this runs on ONE
+        // lane, 7T times per factorisation, on the critical path; IEEE sqrt + divide were 10 % of the solver's instructions
+        const float sd = fmaxf(sdiag, B2S_MINVAL);
+        float inv = rsqrtf(sd);
+        inv = inv * (1.5f - 0.5f * sd * inv * inv);
+        const float dd = sd * inv;
         a[y * T + y] = dd;
         out[y * ld + y] = dd;
         invd[kb * T + y] = inv;
