@@ -146,7 +146,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   if (s->na > 0) return fail("stateful actuators (na > 0) are not supported");
   if (s->nv < 1 || s->nv > B2S_MAX_NV) return fail("nv must be in [1, " + std::to_string(B2S_MAX_NV) + "]");
   if (s->opt_cone != B2S_CONE_PYRAMIDAL) return fail("only the pyramidal friction cone is supported");
-  if (s->opt_solver != B2S_SOL_NEWTON) return fail("only the Newton solver is supported");
+  if (s->opt_solver != B2S_SOL_NEWTON && s->opt_solver != B2S_SOL_CG) return fail("solver must be newton or cg (PGS is not supported)");
   if (s->opt_integrator != B2S_INT_EULER && s->opt_integrator != B2S_INT_IMPLICITFAST) return fail("integrator must be euler or implicitfast");
   const int nb = s->nbody, nv = s->nv;
   for (int i = 0; i < nv; i++) if (s->dof_frictionloss[i] != 0.0) return fail("dof_frictionloss is not supported");
@@ -367,7 +367,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.tolerance = (float)s->opt_tolerance; d.ls_tolerance = (float)s->opt_ls_tolerance; d.impratio = (float)s->opt_impratio;
   d.ls_parallel_min_step = (float)(s->opt_ls_parallel_min_step > 0 ? s->opt_ls_parallel_min_step : 1e-6);
   d.meaninertia = (float)s->stat_meaninertia;
-  d.integrator = s->opt_integrator; d.cone = s->opt_cone; d.iterations = s->opt_iterations; d.ls_iterations = s->opt_ls_iterations;
+  d.integrator = s->opt_integrator; d.cone = s->opt_cone; d.solver = s->opt_solver; d.iterations = s->opt_iterations; d.ls_iterations = s->opt_ls_iterations;
   d.disableflags = s->opt_disableflags; d.ls_parallel = s->opt_ls_parallel;
   d.contact_sensor_maxmatch = s->opt_contact_sensor_maxmatch > 0 ? s->opt_contact_sensor_maxmatch : 64;
   d.body_parentid = up.i(s->body_parentid, nb); d.body_rootid = up.i(s->body_rootid, nb); d.body_mocapid = up.i(s->body_mocapid, nb);
@@ -525,6 +525,9 @@ extern "C" int b2s_model_set_opt(b2s_model* m, const char* key, double v) {
   else if (k == "integrator") {
     if ((int)v != B2S_INT_EULER && (int)v != B2S_INT_IMPLICITFAST) return fail("integrator must be euler or implicitfast");
     d.integrator = (int)v;
+  } else if (k == "solver") {
+    if ((int)v != B2S_SOL_NEWTON && (int)v != B2S_SOL_CG) return fail("solver must be newton or cg (PGS is not supported)");
+    d.solver = (int)v;
   } else if (k == "cone") {
     if ((int)v != B2S_CONE_PYRAMIDAL) return fail("only the pyramidal friction cone is supported");
   } else return fail("unknown option " + k);
@@ -549,6 +552,7 @@ extern "C" int b2s_model_get_opt(const b2s_model* m, const char* key, double* v)
   else if (k == "disableflags") *v = d.disableflags;
   else if (k == "integrator") *v = d.integrator;
   else if (k == "cone") *v = d.cone;
+  else if (k == "solver") *v = d.solver;
   else if (k == "npair") *v = d.npair;
   else if (k == "nvp") *v = d.nvp;
   else return fail("unknown option " + k);

@@ -30,7 +30,7 @@ struct ModelDev {
   int ref_root;                     // root body of the first kinematic tree: its subtree COM is the constraint reference point
   // options
   float timestep, gravity[3], tolerance, ls_tolerance, impratio, ls_parallel_min_step, meaninertia;
-  int integrator, cone, iterations, ls_iterations, disableflags, ls_parallel, contact_sensor_maxmatch;
+  int integrator, cone, solver, iterations, ls_iterations, disableflags, ls_parallel, contact_sensor_maxmatch;
   // ---- bodies
   const int *body_parentid, *body_rootid, *body_mocapid, *body_jntnum, *body_jntadr, *body_dofnum, *body_dofadr;
   const int *body_subtree_end;      // bodies are in DFS pre-order: subtree(b) = [b, body_subtree_end[b])

@@ -37,18 +37,18 @@ extern __shared__ float b2s_smem[];
 __host__ __device__ inline int solve_scratch_floats(int nb) { return 6 * (nb > 32 ? nb : 32) + 32 + 32; }
 __host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      // offset of the scratch area
   const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
-  return (HF + 8 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
+  return (HF + 10 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
 }
 __host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T) {
   return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + 3) & ~3;
 }
 
 // Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
-//   H hdim*ld | invd 7T (padded to a float4 multiple) | 8 vectors of NVP | cdof 6*hdim | Jaref, Jv, D njmax each |
+//   H hdim*ld | invd 7T (padded to a float4 multiple) | 10 vectors of NVP | cdof 6*hdim | Jaref, Jv, D njmax each |
 //   run list nconmax+2 | active-set bit mask njmax/32 | scratch X/Y 6*max(nb,32), KW 32, Li 32
 template <int T>
 struct SolveCtx {
-  static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 8 * NVP + 6 * N;
+  static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 10 * NVP + 6 * N;
   int lane, nv, nvp, nb, nefc, nl, nrun, njmax, nconmax, soff;
   static constexpr int ld = LD, hfloats = HF;
   const float *M, *G, *aref;
@@ -64,7 +64,9 @@ struct SolveCtx {
   DEV float* qfs() const { return sm + HF + 5 * NVP; }
   DEV float* qas() const { return sm + HF + 6 * NVP; }
   DEV float* qfc() const { return sm + HF + 7 * NVP; }
-  DEV float* cdof() const { return sm + HF + 8 * NVP; }
+  DEV float* gradold() const { return sm + HF + 8 * NVP; }     // CG only
+  DEV float* Mgradold() const { return sm + HF + 9 * NVP; }    // CG only
+  DEV float* cdof() const { return sm + HF + 10 * NVP; }
   DEV float* Jaref() const { return sm + FIX; }
   DEV float* Jv() const { return sm + FIX + njmax; }
   DEV float* D() const { return sm + FIX + 2 * njmax; }
@@ -531,10 +533,20 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   const float scale = 1.0f / (m.meaninertia * (float)max(nv, 1));
   int iter = 0;
   bool withH = true, haveL = false;
+  const bool newton = m.solver == B2S_SOL_NEWTON;
+  if (!newton) {
+    // CG (mj_solPrimal without the Hessian): the preconditioner is M^-1, so M is factorised once (H storage = 0 + M)
+    float4* h4 = reinterpret_cast<float4*>(c.H());
+    _Pragma("unroll 2")
+    for (int i = lane; i < c.hfloats / 4; i += 32) h4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+    factor_H<T>(c, bi, bj);
+    haveL = true;
+  }
 #pragma unroll 1
   while (true) {
     // the factor in shared memory stays valid while the active set does not change
-    const bool reuse = active_set_unchanged(c) && haveL;
+    const bool reuse = (active_set_unchanged(c) && haveL) || !newton;
     assemble(c, m, withH && !reuse, ia, ib);
     if (!withH) break;
     float gn = 0.f;
@@ -548,8 +560,21 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     haveL = true;
     float b0 = lane < nv ? c.grad()[lane] : 0.f, b1 = lane + 32 < nv ? c.grad()[lane + 32] : 0.f;
     tile_chol_solve<T>(c.H(), c.invd(), c.ld, lane, b0, b1);
-    if (lane < nv) c.search()[lane] = -b0;
-    if (lane + 32 < nv) c.search()[lane + 32] = -b1;
+    if (newton) {
+      if (lane < nv) c.search()[lane] = -b0;
+      if (lane + 32 < nv) c.search()[lane + 32] = -b1;
+    } else {
+      // Polak-Ribiere: beta = grad . (Mgrad - Mgrad_old) / max(MINVAL, grad_old . Mgrad_old), clamped at 0; first pass beta = 0
+      float num = 0.f, den = 0.f;
+      if (iter > 0) {
+        if (lane < nv) { num += c.grad()[lane] * (b0 - c.Mgradold()[lane]); den += c.gradold()[lane] * c.Mgradold()[lane]; }
+        if (lane + 32 < nv) { num += c.grad()[lane + 32] * (b1 - c.Mgradold()[lane + 32]); den += c.gradold()[lane + 32] * c.Mgradold()[lane + 32]; }
+      }
+      num = warp_sum(num); den = warp_sum(den);
+      const float beta = iter > 0 ? fmaxf(num / fmaxf(den, B2S_MINVAL), 0.f) : 0.f;
+      if (lane < nv) { c.search()[lane] = -b0 + beta * c.search()[lane]; c.Mgradold()[lane] = b0; c.gradold()[lane] = c.grad()[lane]; }
+      if (lane + 32 < nv) { c.search()[lane + 32] = -b1 + beta * c.search()[lane + 32]; c.Mgradold()[lane + 32] = b1; c.gradold()[lane + 32] = c.grad()[lane + 32]; }
+    }
     __syncwarp();
     // line-search set-up: Mv, Jv, quadratic Gauss coefficients
     mat_vec_M(c, c.search(), c.Mv());

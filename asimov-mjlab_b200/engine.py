@@ -116,15 +116,14 @@ class _Handle:
 
 
 _OPT_KEYS = ("ls_parallel", "contact_sensor_maxmatch", "iterations", "ls_iterations", "tolerance", "ls_tolerance",
-             "impratio", "integrator", "cone", "disableflags", "ls_parallel_min_step")
+             "impratio", "integrator", "cone", "solver", "disableflags", "ls_parallel_min_step")
 
 
 class _Option:
   """`Model.opt`: plain attribute reads/writes forwarded to the library (sim.py:117-118)."""
 
   def __init__(self, model, solver):
-    object.__setattr__(self, "_m", model)
-    object.__setattr__(self, "solver", solver)
+    object.__setattr__(self, "_m", model)      # `solver` is read back from the library like every other option
 
   def _get(self, key):
     v = C.c_double()

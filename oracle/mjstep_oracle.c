@@ -15,7 +15,7 @@
  *   orc_fwd_velocity    mj_comVel, mj_passive, mj_rne
  *   orc_fwd_actuation   engine_forward.c mj_fwdActuation
  *   orc_fwd_acceleration engine_forward.c mj_fwdAcceleration
- *   orc_solve           engine_solver.c mj_solNewton (+ mjwarp's parallel line search)
+ *   orc_solve           engine_solver.c mj_solNewton / mj_solCG (mj_solPrimal) (+ mjwarp's parallel line search)
  *   orc_sensors         engine_sensor.c mj_sensorPos/Vel/Acc, mj_subtreeVel, mj_rnePostConstraint (cacc only)
  *   orc_integrate       engine_forward.c mj_Euler / mj_implicit (implicitfast)
  * and the reference files that fix WHAT must come out: sim.py:41-76 (options),
@@ -1058,6 +1058,8 @@ typedef struct {
   const b2s_model_desc* m; orc_data* d;
   int nv, nefc;
   real *Ma, *Jaref, *grad, *Mgrad, *search, *Mv, *Jv, *H, *HL, *quad;
+  real *gradold, *Mgradold;   /* CG: previous gradient and M^-1 gradient (Polak-Ribiere) */
+  int cg, have_ml;
   int* active;
   real cost, gauss, quadGauss[3];
 } solctx;
@@ -1081,10 +1083,16 @@ static void sol_update_constraint(solctx* c) {
   c->gauss = (real)0.5*g;
   c->cost = cost + c->gauss;
 }
-/* gradient, Newton Hessian H = M + J^T diag(D active) J, search direction */
+/* gradient; Newton: Hessian H = M + J^T diag(D active) J, search = -H^-1 grad; CG (engine_solver.c mj_solPrimal with
+ * flg_Newton = 0): Mgrad = M^-1 grad, search = -Mgrad + beta search with the Polak-Ribiere beta, clamped at 0 */
 static void sol_update_gradient(solctx* c) {
   orc_data* d = c->d; int nv = c->nv;
   for (int i = 0; i < nv; i++) c->grad[i] = c->Ma[i] - d->qfrc_smooth[i] - d->qfrc_constraint[i];
+  if (c->cg) {
+    if (!c->have_ml) { chol_factor(c->HL, d->qM, nv); c->have_ml = 1; }
+    chol_solve(c->Mgrad, c->HL, c->grad, nv);
+    return;
+  }
   for (int i = 0; i < nv*nv; i++) c->H[i] = d->qM[i];
   for (int r = 0; r < c->nefc; r++) {
     if (!c->active[r]) continue;
@@ -1184,9 +1192,11 @@ void orc_solve(const b2s_model_desc* m, orc_data* d) {
     return;
   }
   solctx c; c.m = m; c.d = d; c.nv = nv; c.nefc = nefc;
-  real* buf = (real*)calloc((size_t)(7*nv + 2*nv*nv + 5*nefc), sizeof(real));
+  real* buf = (real*)calloc((size_t)(9*nv + 2*nv*nv + 5*nefc), sizeof(real));
+  c.cg = m->opt_solver == B2S_SOL_CG; c.have_ml = 0;
   c.Ma = buf; c.grad = c.Ma + nv; c.Mgrad = c.grad + nv; c.search = c.Mgrad + nv; c.Mv = c.search + nv;
   c.H = c.Mv + nv; c.HL = c.H + nv*nv; c.Jaref = c.HL + nv*nv; c.Jv = c.Jaref + nefc; c.quad = c.Jv + nefc;
+  c.gradold = c.quad + 3*nefc; c.Mgradold = c.gradold + nv;
   c.active = (int*)calloc((size_t)nefc, sizeof(int));
   /* warm start: keep qacc_warmstart only if its cost beats qacc_smooth (mj_fwdConstraint) */
   for (int pass = 0; pass < 2; pass++) {
@@ -1207,6 +1217,7 @@ void orc_solve(const b2s_model_desc* m, orc_data* d) {
     }
   }
   sol_update_gradient(&c);
+  if (c.cg) for (int i = 0; i < nv; i++) c.search[i] = -c.Mgrad[i];
   real scale = 1/((real)m->stat_meaninertia*(real)(nv > 1 ? nv : 1));
   int it = 0;
   for (; it < m->opt_iterations; it++) {
@@ -1216,8 +1227,16 @@ void orc_solve(const b2s_model_desc* m, orc_data* d) {
     for (int i = 0; i < nv; i++) { d->qacc[i] += alpha*c.search[i]; c.Ma[i] += alpha*c.Mv[i]; }
     for (int r = 0; r < nefc; r++) c.Jaref[r] += alpha*c.Jv[r];
     real old = c.cost;
+    if (c.cg) for (int i = 0; i < nv; i++) { c.gradold[i] = c.grad[i]; c.Mgradold[i] = c.Mgrad[i]; }
     sol_update_constraint(&c);
     sol_update_gradient(&c);
+    if (c.cg) {
+      real num = 0, den = 0;
+      for (int i = 0; i < nv; i++) { num += c.grad[i]*(c.Mgrad[i] - c.Mgradold[i]); den += c.gradold[i]*c.Mgradold[i]; }
+      real beta = num/(den > MINVAL ? den : MINVAL);
+      if (beta < 0) beta = 0;
+      for (int i = 0; i < nv; i++) c.search[i] = -c.Mgrad[i] + beta*c.search[i];
+    }
     real improvement = scale*(old - c.cost), gn = 0;
     for (int i = 0; i < nv; i++) gn += c.grad[i]*c.grad[i];
     real gradient = scale*(real)sqrt((double)gn);

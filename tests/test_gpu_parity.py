@@ -571,8 +571,8 @@ def test_unsupported_features_raise():
   with pytest.raises(engine.BackendError, match="pyramidal"):
     engine.put_model(m)
   m.opt.cone = 0
-  m.opt.solver = 1
-  with pytest.raises(engine.BackendError, match="Newton"):
+  m.opt.solver = 0        # PGS (dual solver): not built; Newton (2) and CG (1) are
+  with pytest.raises(engine.BackendError, match="PGS"):
     engine.put_model(m)
   m.opt.solver = 2
   m.dof_frictionloss = m.dof_frictionloss + 0.1
@@ -679,3 +679,46 @@ def test_g1_config1_rollout_1000_steps_teacher_forced(g1):
   fell = sum(float(w["qpos"][2]) < 0.4 for w in worlds)
   assert checked == 100 and ncon_max >= 12 and fell >= 4      # the rollout reached fallen, many-contact states
   assert all(np.isfinite(w["qpos"]).all() for w in worlds)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ls_parallel", [True, False])
+def test_g1_cg_solver_matches_oracle_and_newton(g1, ls_parallel):
+  """solver="cg" (reference sim.py:55, used by its own tests/test_sim.py:52-58): mj_solPrimal without the Hessian, M^-1 as
+  preconditioner, Polak-Ribiere directions.  CUDA against the oracle's CG after the same number of iterations, and both
+  against the Newton solution of the same states when CG is given enough iterations to converge."""
+  import copy
+  W = 16
+  qpos, qvel, ctrl = g1_states(g1, W, seed=5)
+  m = copy.copy(g1); m.opt = copy.copy(g1.opt)
+  m.opt.solver, m.opt.iterations = 1, 30
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, ls_parallel)
+  assert M.opt.solver == 1
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  _check_counts(D, worlds)
+  nit_g = D.solver_niter.cpu().numpy(); nit_o = np.array([int(w["solver_niter"][0]) for w in worlds])
+  # same iteration counts, except where the oracle runs into the iteration cap: there the steps are at the level of the
+  # termination tolerance (fp32 noise decides whether `improvement < tolerance` fires) and only the solution is compared
+  free = nit_o < m.opt.iterations
+  assert np.abs(nit_g - nit_o)[free].max() <= (0 if ls_parallel else 3) and nit_o.max() > 5 and free.sum() >= 6
+  qa_g, qa_o = D.qacc.cpu().numpy(), np.stack([w["qacc"] for w in worlds])
+  assert np.abs(qa_g - qa_o)[free].max() < 2e-3 * (1 + np.abs(qa_o[free]).max())
+  # capped worlds are unconverged first-order iterates: their directions decorrelate with rounding, and with the parallel
+  # line search (discrete step set) one side may stop on "no improving step" while the other creeps on -- same cost level only
+  cost_g, cost_o = D.solver_cost.cpu().numpy(), np.array([float(w["solver_cost"][0]) for w in worlds])
+  assert np.isfinite(cost_g).all() and (cost_g <= 1.25 * cost_o + 1.0).all() and (cost_o <= 1.25 * cost_g + 1.0).all()
+  assert np.abs(cost_g - cost_o)[free].max() < 1e-3 * (1 + np.abs(cost_o[free]).max())
+  # converged CG == converged Newton (exact line search; the parallel one stalls on its discrete step set)
+  if not ls_parallel:
+    m.opt.iterations = 200
+    mn = copy.copy(g1); mn.opt = copy.copy(g1.opt); mn.opt.solver, mn.opt.iterations = 2, 50
+    e2, M2, D2, orc2, w2 = _setup(m, W, qpos, qvel, ctrl, False)
+    e3, M3, D3, orc3, w3 = _setup(mn, W, qpos, qvel, ctrl, False)
+    e2.forward(M2, D2); e3.forward(M3, D3)
+    a, b = D2.qacc.cpu().numpy(), D3.qacc.cpu().numpy()
+    assert np.abs(a - b).max() < 5e-3 * (1 + np.abs(b).max())
+  # and a few steps run without NaNs through the CG path
+  engine.step(M, D, 8)
+  assert np.isfinite(D.qpos.cpu().numpy()).all()

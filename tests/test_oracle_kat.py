@@ -387,3 +387,21 @@ def test_mesh_cube_settles_on_plane_and_height_field():
     orc.step(w, 1500)
     assert np.abs(w["qvel"]).max() < 5e-2
     assert w["qpos"][2] == pytest.approx(0.06, abs=4e-3) and w["qpos"][9] == pytest.approx(0.1, abs=2e-3)
+
+
+def test_cg_solver_converges_to_the_newton_solution(g1):
+  """mj_solPrimal's CG variant (M^-1 preconditioner, Polak-Ribiere) minimises the same cost: with the exact line search and
+  enough iterations its qacc equals the Newton solver's on contact-rich G1 states."""
+  import copy
+  from util import g1_states
+  qpos, qvel, ctrl = g1_states(g1, 6, seed=7)
+  out = {}
+  for name, solver, iters in (("newton", 2, 50), ("cg", 1, 300)):
+    m = copy.copy(g1); m.opt = copy.copy(g1.opt)
+    m.opt.solver, m.opt.iterations, m.opt.tolerance = solver, iters, 1e-12
+    orc = Oracle(m, "f64", 50, 300, ls_parallel=0)
+    ws = [orc.forward(orc.new_world(qpos[i], qvel[i], ctrl[i])) for i in range(6)]
+    out[name] = (np.stack([w["qacc"] for w in ws]), np.array([int(w["solver_niter"][0]) for w in ws]), np.array([int(w["nefc"][0]) for w in ws]))
+  assert out["newton"][2].sum() > 50
+  assert np.abs(out["cg"][0] - out["newton"][0]).max() < 1e-5 * (1 + np.abs(out["newton"][0]).max())
+  assert out["cg"][1].max() > out["newton"][1].max()        # first-order directions need more iterations
