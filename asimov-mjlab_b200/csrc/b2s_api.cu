@@ -205,6 +205,11 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       case B2S_SENS_ACCELEROMETER: case B2S_SENS_VELOCIMETER: case B2S_SENS_GYRO: case B2S_SENS_JOINTPOS: case B2S_SENS_JOINTVEL:
       case B2S_SENS_ACTUATORFRC: case B2S_SENS_FRAMEPOS: case B2S_SENS_FRAMEQUAT: case B2S_SENS_FRAMEZAXIS: case B2S_SENS_FRAMELINVEL:
       case B2S_SENS_FRAMEANGVEL: case B2S_SENS_SUBTREECOM: case B2S_SENS_SUBTREELINVEL: case B2S_SENS_SUBTREEANGMOM: case B2S_SENS_CONTACT: break;
+      case B2S_SENS_ACTUATORPOS: case B2S_SENS_ACTUATORVEL: case B2S_SENS_JOINTACTFRC: case B2S_SENS_FRAMEXAXIS: case B2S_SENS_FRAMEYAXIS:
+      case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: case B2S_SENS_CLOCK: break;
+      case B2S_SENS_TENDONPOS: case B2S_SENS_TENDONVEL:
+        if (s->sensor_objid[k] < 0 || s->sensor_objid[k] >= s->ntendon) return fail("tendon sensor refers to an unknown tendon");
+        break;
       default: return fail("unsupported sensor type " + std::to_string(s->sensor_type[k]));
     }
   }

@@ -240,16 +240,31 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
       case B2S_SENS_JOINTPOS: out[0] = d.qpos[(size_t)w * m.nq + m.jnt_qposadr[id]]; break;
       case B2S_SENS_JOINTVEL: out[0] = qvel[m.jnt_dofadr[id]]; break;
       case B2S_SENS_ACTUATORFRC: out[0] = d.actuator_force[(size_t)w * m.nu + id]; break;
+      case B2S_SENS_TENDONPOS: out[0] = d.ten_length[(size_t)w * m.ntendon + id]; break;
+      case B2S_SENS_TENDONVEL: out[0] = d.ten_velocity[(size_t)w * m.ntendon + id]; break;
+      case B2S_SENS_ACTUATORPOS: out[0] = d.actuator_length[(size_t)w * m.nu + id]; break;
+      case B2S_SENS_ACTUATORVEL: out[0] = d.actuator_velocity[(size_t)w * m.nu + id]; break;
+      case B2S_SENS_JOINTACTFRC: out[0] = d.qfrc_actuator[(size_t)w * nv + m.jnt_dofadr[id]]; break;
+      case B2S_SENS_CLOCK: out[0] = d.time[w]; break;
+      case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: {
+        Frame f = obj_frame(m, d, w, ot, id);
+        sv6 v = object_velocity(m, cvel, com, f.body, f.pos);
+        const float* ca = s_cacc + 6 * f.body;
+        const v3 aang = mk3(ca[0], ca[1], ca[2]);
+        if (type == B2S_SENS_FRAMEANGACC) st3(out, aang);
+        else st3(out, mk3(ca[3], ca[4], ca[5]) + cross(aang, f.pos - ld3(com + 3 * m.body_rootid[f.body])) +
+                      cross(mk3(v.v[0], v.v[1], v.v[2]), mk3(v.v[3], v.v[4], v.v[5])));
+      } break;
       case B2S_SENS_SUBTREECOM: st3(out, ld3(com + 3 * id)); break;
       case B2S_SENS_SUBTREELINVEL: st3(out, ld3(s_slv + 3 * id)); break;
       case B2S_SENS_SUBTREEANGMOM: st3(out, ld3(d.subtree_angmom + ((size_t)w * nb + id) * 3)); break;
-      case B2S_SENS_FRAMEPOS: case B2S_SENS_FRAMEQUAT: case B2S_SENS_FRAMEZAXIS: {
+      case B2S_SENS_FRAMEPOS: case B2S_SENS_FRAMEQUAT: case B2S_SENS_FRAMEXAXIS: case B2S_SENS_FRAMEYAXIS: case B2S_SENS_FRAMEZAXIS: {
         Frame f = obj_frame(m, d, w, ot, id);
         const bool hasref = m.sensor_refid[s] >= 0;
         Frame r = f;
         if (hasref) r = obj_frame(m, d, w, m.sensor_reftype[s], m.sensor_refid[s]);
         if (type == B2S_SENS_FRAMEPOS) st3(out, hasref ? mulTv(r.mat, f.pos - r.pos) : f.pos);
-        else if (type == B2S_SENS_FRAMEZAXIS) st3(out, hasref ? mulTv(r.mat, col(f.mat, 2)) : col(f.mat, 2));
+        else if (type != B2S_SENS_FRAMEQUAT) { const int ax = type - B2S_SENS_FRAMEXAXIS; st3(out, hasref ? mulTv(r.mat, col(f.mat, ax)) : col(f.mat, ax)); }
         else {
           m33 R = f.mat;
           if (hasref) for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) {

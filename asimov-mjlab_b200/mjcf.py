@@ -34,15 +34,17 @@ from .hostmodel import HostModel, finalize_model
 JNT = {"free": 0, "ball": 1, "slide": 2, "hinge": 3}
 GEOM = {"plane": 0, "hfield": 1, "sphere": 2, "capsule": 3, "ellipsoid": 4,
         "cylinder": 5, "box": 6, "mesh": 7}
-OBJ = {"body": 1, "xbody": 2, "joint": 3, "dof": 4, "geom": 5, "site": 6, "actuator": 19}
-SENS = {"accelerometer": 1, "velocimeter": 2, "gyro": 3, "jointpos": 9, "jointvel": 10,
-        "actuatorfrc": 15, "framepos": 25, "framequat": 26, "framezaxis": 29,
-        "framelinvel": 30, "frameangvel": 31, "subtreecom": 34, "subtreelinvel": 35,
-        "subtreeangmom": 36, "contact": 42}
-SENS_DIM = {"accelerometer": 3, "velocimeter": 3, "gyro": 3, "jointpos": 1, "jointvel": 1,
-            "actuatorfrc": 1, "framepos": 3, "framequat": 4, "framezaxis": 3,
-            "framelinvel": 3, "frameangvel": 3, "subtreecom": 3, "subtreelinvel": 3,
-            "subtreeangmom": 3}
+OBJ = {"body": 1, "xbody": 2, "joint": 3, "dof": 4, "geom": 5, "site": 6, "tendon": 18, "actuator": 19}
+SENS = {"accelerometer": 1, "velocimeter": 2, "gyro": 3, "jointpos": 9, "jointvel": 10, "tendonpos": 11, "tendonvel": 12,
+        "actuatorpos": 13, "actuatorvel": 14, "actuatorfrc": 15, "jointactuatorfrc": 16,
+        "framepos": 25, "framequat": 26, "framexaxis": 27, "frameyaxis": 28, "framezaxis": 29,
+        "framelinvel": 30, "frameangvel": 31, "framelinacc": 32, "frameangacc": 33, "subtreecom": 34, "subtreelinvel": 35,
+        "subtreeangmom": 36, "contact": 42, "clock": 45}
+SENS_DIM = {"accelerometer": 3, "velocimeter": 3, "gyro": 3, "jointpos": 1, "jointvel": 1, "tendonpos": 1, "tendonvel": 1,
+            "actuatorpos": 1, "actuatorvel": 1, "actuatorfrc": 1, "jointactuatorfrc": 1,
+            "framepos": 3, "framequat": 4, "framexaxis": 3, "frameyaxis": 3, "framezaxis": 3,
+            "framelinvel": 3, "frameangvel": 3, "framelinacc": 3, "frameangacc": 3, "subtreecom": 3, "subtreelinvel": 3,
+            "subtreeangmom": 3, "clock": 1}
 CONTACT_FIELD_DIM = {0: 1, 1: 3, 2: 3, 3: 1, 4: 3, 5: 3, 6: 3}
 
 
@@ -581,10 +583,12 @@ class _Parser:
     s = SensorSpec(name=el.get("name", ""), type=t, cutoff=float(el.get("cutoff", 0)))
     if t in ("accelerometer", "velocimeter", "gyro"):
       s.objtype, s.objname = "site", el.get("site")
-    elif t in ("jointpos", "jointvel"):
+    elif t in ("jointpos", "jointvel", "jointactuatorfrc"):
       s.objtype, s.objname = "joint", el.get("joint")
-    elif t == "actuatorfrc":
+    elif t in ("actuatorpos", "actuatorvel", "actuatorfrc"):
       s.objtype, s.objname = "actuator", el.get("actuator")
+    elif t in ("tendonpos", "tendonvel"):
+      s.objtype, s.objname = "tendon", el.get("tendon")
     elif t.startswith("subtree"):
       s.objtype, s.objname = "body", el.get("body")
     elif t.startswith("frame"):
@@ -984,7 +988,7 @@ def _compile(spec: Spec) -> HostModel:
   m.sensor_objid = -np.ones(ns, np.int32); m.sensor_reftype = np.zeros(ns, np.int32)
   m.sensor_refid = -np.ones(ns, np.int32); m.sensor_intprm = np.zeros((ns, 3), np.int32)
   m.sensor_dim = np.zeros(ns, np.int32); m.sensor_adr = np.zeros(ns, np.int32); m.sensor_cutoff = np.zeros(ns)
-  namekey = {"body": "body", "xbody": "body", "joint": "joint", "geom": "geom", "site": "site", "actuator": "actuator"}
+  namekey = {"body": "body", "xbody": "body", "joint": "joint", "geom": "geom", "site": "site", "actuator": "actuator", "tendon": "tendon"}
   adr = 0
   for k, s in enumerate(spec.sensors):
     m.sensor_type[k] = SENS[s.type]; m.sensor_cutoff[k] = s.cutoff

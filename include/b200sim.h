@@ -42,16 +42,18 @@ enum { B2S_INT_EULER = 0, B2S_INT_RK4 = 1, B2S_INT_IMPLICIT = 2, B2S_INT_IMPLICI
 enum { B2S_CONE_PYRAMIDAL = 0, B2S_CONE_ELLIPTIC = 1 };
 enum { B2S_SOL_PGS = 0, B2S_SOL_CG = 1, B2S_SOL_NEWTON = 2 };
 enum { B2S_OBJ_UNKNOWN = 0, B2S_OBJ_BODY = 1, B2S_OBJ_XBODY = 2, B2S_OBJ_JOINT = 3, B2S_OBJ_DOF = 4,
-       B2S_OBJ_GEOM = 5, B2S_OBJ_SITE = 6, B2S_OBJ_ACTUATOR = 19 };
+       B2S_OBJ_GEOM = 5, B2S_OBJ_SITE = 6, B2S_OBJ_TENDON = 18, B2S_OBJ_ACTUATOR = 19 };
 enum { B2S_BIAS_NONE = 0, B2S_BIAS_AFFINE = 1 };
 enum { B2S_TRN_JOINT = 0, B2S_TRN_TENDON = 3 };
 enum { B2S_GAIN_FIXED = 0, B2S_GAIN_AFFINE = 1 };
 /* sensor types: own numbering (MuJoCo's mjtSensor values moved between
  * releases); the Python binding maps by NAME from a real MjModel. */
 enum { B2S_SENS_ACCELEROMETER = 1, B2S_SENS_VELOCIMETER = 2, B2S_SENS_GYRO = 3,
-       B2S_SENS_JOINTPOS = 9, B2S_SENS_JOINTVEL = 10, B2S_SENS_ACTUATORFRC = 15,
-       B2S_SENS_FRAMEPOS = 25, B2S_SENS_FRAMEQUAT = 26, B2S_SENS_FRAMEZAXIS = 29,
-       B2S_SENS_FRAMELINVEL = 30, B2S_SENS_FRAMEANGVEL = 31,
+       B2S_SENS_JOINTPOS = 9, B2S_SENS_JOINTVEL = 10, B2S_SENS_TENDONPOS = 11, B2S_SENS_TENDONVEL = 12,
+       B2S_SENS_ACTUATORPOS = 13, B2S_SENS_ACTUATORVEL = 14, B2S_SENS_ACTUATORFRC = 15, B2S_SENS_JOINTACTFRC = 16,
+       B2S_SENS_FRAMEPOS = 25, B2S_SENS_FRAMEQUAT = 26, B2S_SENS_FRAMEXAXIS = 27, B2S_SENS_FRAMEYAXIS = 28, B2S_SENS_FRAMEZAXIS = 29,
+       B2S_SENS_FRAMELINVEL = 30, B2S_SENS_FRAMEANGVEL = 31, B2S_SENS_FRAMELINACC = 32, B2S_SENS_FRAMEANGACC = 33,
+       B2S_SENS_CLOCK = 45,
        B2S_SENS_SUBTREECOM = 34, B2S_SENS_SUBTREELINVEL = 35, B2S_SENS_SUBTREEANGMOM = 36,
        B2S_SENS_CONTACT = 42 };
 /* contact-sensor data bits (intprm[0]) and reduce modes (intprm[1]);

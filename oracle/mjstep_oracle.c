@@ -1373,18 +1373,39 @@ void orc_sensors(const b2s_model_desc* m, orc_data* d) {
       case B2S_SENS_JOINTPOS: out[0] = d->qpos[m->jnt_qposadr[id]]; break;
       case B2S_SENS_JOINTVEL: out[0] = d->qvel[m->jnt_dofadr[id]]; break;
       case B2S_SENS_ACTUATORFRC: out[0] = d->actuator_force[id]; break;
+      /* engine_sensor.c mj_sensorPos / mj_sensorVel / mj_sensorAcc scalar read-outs */
+      case B2S_SENS_TENDONPOS: out[0] = d->ten_length[id]; break;
+      case B2S_SENS_TENDONVEL: out[0] = d->ten_velocity[id]; break;
+      case B2S_SENS_ACTUATORPOS: out[0] = d->actuator_length[id]; break;
+      case B2S_SENS_ACTUATORVEL: out[0] = d->actuator_velocity[id]; break;
+      case B2S_SENS_JOINTACTFRC: out[0] = d->qfrc_actuator[m->jnt_dofadr[id]]; break;
+      case B2S_SENS_CLOCK: out[0] = d->time[0]; break;
       case B2S_SENS_SUBTREECOM: for (int k = 0; k < 3; k++) out[k] = d->subtree_com[3*id + k]; break;
       case B2S_SENS_SUBTREELINVEL: for (int k = 0; k < 3; k++) out[k] = d->subtree_linvel[3*id + k]; break;
       case B2S_SENS_SUBTREEANGMOM: for (int k = 0; k < 3; k++) out[k] = d->subtree_angmom[3*id + k]; break;
-      case B2S_SENS_FRAMEPOS: case B2S_SENS_FRAMEQUAT: case B2S_SENS_FRAMEZAXIS: {
+      case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: {
+        /* mj_objectAcceleration, world orientation: cacc moved to the frame origin + the centripetal term w x v */
+        obj_frame(m, d, ot, id, &pos, &mat, &body);
+        object_velocity(m, d, body, pos, NULL, v6);
+        const real* ca = d->cacc + 6*body;
+        if (type == B2S_SENS_FRAMEANGACC) { for (int k = 0; k < 3; k++) out[k] = ca[k]; }
+        else {
+          real dif[3], t[3], corr[3];
+          for (int k = 0; k < 3; k++) dif[k] = pos[k] - d->subtree_com[3*m->body_rootid[body] + k];
+          cross3(t, ca, dif); cross3(corr, v6, v6 + 3);
+          for (int k = 0; k < 3; k++) out[k] = ca[3 + k] + t[k] + corr[k];
+        }
+      } break;
+      case B2S_SENS_FRAMEPOS: case B2S_SENS_FRAMEQUAT: case B2S_SENS_FRAMEXAXIS: case B2S_SENS_FRAMEYAXIS: case B2S_SENS_FRAMEZAXIS: {
         obj_frame(m, d, ot, id, &pos, &mat, &body);
         const real *rp = NULL, *rm = NULL; int rb;
         if (m->sensor_refid[s] >= 0) obj_frame(m, d, m->sensor_reftype[s], m->sensor_refid[s], &rp, &rm, &rb);
         if (type == B2S_SENS_FRAMEPOS) {
           if (rp) { real df[3] = {pos[0] - rp[0], pos[1] - rp[1], pos[2] - rp[2]}; matT_vec(out, rm, df); }
           else for (int k = 0; k < 3; k++) out[k] = pos[k];
-        } else if (type == B2S_SENS_FRAMEZAXIS) {
-          real z[3] = {mat[2], mat[5], mat[8]};
+        } else if (type != B2S_SENS_FRAMEQUAT) {
+          const int ax = type - B2S_SENS_FRAMEXAXIS;      /* column 0 / 1 / 2 of the frame */
+          real z[3] = {mat[ax], mat[3 + ax], mat[6 + ax]};
           if (rm) matT_vec(out, rm, z); else for (int k = 0; k < 3; k++) out[k] = z[k];
         } else {
           real q[4], R[9];

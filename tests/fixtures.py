@@ -221,6 +221,45 @@ TENDON_SLIDERS = """
 </mujoco>
 """
 
+# TENDON_ANKLE-like arm with one of every scalar / frame sensor mjlab's BuiltinSensorCfg accepts beyond the robots' own
+# (sensor/builtin_sensor.py:59-101): tendon, actuator, joint-actuator-force, frame axes, frame accelerations, clock.
+SENSOR_ARM = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.005" integrator="implicitfast"/>
+  <worldbody>
+    <geom name="floor" type="plane" size="5 5 0.1"/>
+    <body name="upper" pos="0 0 1.2">
+      <joint name="sh" type="hinge" axis="0 1 0" damping="0.2"/>
+      <geom type="capsule" fromto="0 0 0 0.4 0 0" size="0.04" mass="1.0"/>
+      <site name="mid" pos="0.2 0 0.05" quat="0.9238795 0 0 0.3826834"/>
+      <body name="fore" pos="0.4 0 0">
+        <joint name="el" type="hinge" axis="0 0 1" damping="0.1" range="-2 2"/>
+        <geom type="capsule" fromto="0 0 0 0.3 0 0" size="0.03" mass="0.5"/>
+        <site name="tip" pos="0.3 0 0"/>
+      </body>
+    </body>
+  </worldbody>
+  <tendon>
+    <fixed name="couple"><joint joint="sh" coef="0.5"/><joint joint="el" coef="-1.5"/></fixed>
+  </tendon>
+  <actuator>
+    <position name="a_sh" joint="sh" kp="30" kv="2" gear="2"/>
+    <position name="a_t" tendon="couple" kp="10" kv="1"/>
+  </actuator>
+  <sensor>
+    <tendonpos name="tp" tendon="couple"/><tendonvel name="tv" tendon="couple"/>
+    <actuatorpos name="ap" actuator="a_sh"/><actuatorvel name="av" actuator="a_sh"/><actuatorfrc name="af" actuator="a_t"/>
+    <jointactuatorfrc name="jf" joint="el"/>
+    <framexaxis name="fx" objtype="site" objname="mid"/><frameyaxis name="fy" objtype="site" objname="tip" reftype="site" refname="mid"/>
+    <framezaxis name="fz" objtype="xbody" objname="fore"/>
+    <framelinacc name="la" objtype="site" objname="tip"/><frameangacc name="aa" objtype="site" objname="tip"/>
+    <accelerometer name="acc" site="tip"/>
+    <clock name="clk"/>
+  </sensor>
+</mujoco>
+"""
+
 # Asimov-toe's ankle in miniature: a pitch/roll hinge pair under gravity driven by two fixed tendons with position
 # actuators (one clamped by ctrlrange / forcerange, one with a velocity gain), a sprung + damped third tendon with
 # a dead band, and a joint motor on the same dof (asimov_toe.xml:175-204).
