@@ -44,8 +44,8 @@ def alg_bytes(m, friction_geoms):
   w = m.nq + 3 * m.nv + 1 + m.nsensordata + (3 + 4 + 3 + 6) * nb + 12 * m.nsite
   return 4 * (r + w + 3 * friction_geoms)
 # DRAM traffic of one sub-step (7 stage kernels), dram__bytes_read.sum + dram__bytes_write.sum from the `ncu --set full`
-# capture profiles/step_r1g_metrics.txt (G1-flat, 4096 worlds): 115 813 888 B read + 880 128 B written
-NCU_TRAFFIC = {("g1_flat", 4096): (116694016, "profiles/step_r1g_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step)")}
+# capture profiles/step_r1i_metrics.txt (G1-flat, 4096 worlds): 117 512 960 B read + 1 043 456 B written
+NCU_TRAFFIC = {("g1_flat", 4096): (118556416, "profiles/step_r1i_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step)")}
 DECIMATION = 4
 RESET_PERIOD_STEPS = 250            # reset every 1000 sub-steps, forward() inside the timed region
 
