@@ -30,6 +30,22 @@ class VelocityMdp(C.Structure):
                        "obs", "critic_obs", "rew", "term_sums", "U")])
 
 
+TRK_NTERM, TRK_NMET = 9, 6
+
+
+class TrackingMdp(C.Structure):
+  """Mirror of b2s_tracking_mdp (include/b200sim.h)."""
+  _fields_ = (
+    [(n, C.c_int) for n in ("nworld", "nq", "nv", "nu", "nbody", "nsensordata", "nrand", "nb", "anchor_k", "ntime")] +
+    [(n, _P) for n in ("qpos", "qvel", "sensordata", "xpos", "xquat", "cvel", "subtree_com")] +
+    [(n, _P) for n in ("mo_jp", "mo_jv", "mo_bpos", "mo_bquat", "mo_blin", "mo_bang", "env_origins", "time_steps", "body_ids", "body_root",
+                       "ee_mask", "default_joint_pos", "soft_lo", "soft_hi", "action", "prev_action")] +
+    [("s_gyro", C.c_int), ("s_linvel", C.c_int), ("s_self", C.c_int), ("max_episode_length", C.c_int),
+     ("weight", C.c_float * TRK_NTERM), ("inv_std2", C.c_float * 6)] +
+    [(n, _P) for n in ("body_pos_relative_w", "body_quat_relative_w", "episode_length_buf", "dones", "time_outs", "terminated",
+                       "rew", "term_sums", "metrics", "obs", "critic_obs", "U")])
+
+
 _bound = False
 
 
@@ -39,6 +55,9 @@ def _lib():
   if not _bound:
     for f in ("b2s_vel_apply_action", "b2s_vel_air_time", "b2s_vel_post", "b2s_vel_observe"):
       getattr(L, f).argtypes = [C.POINTER(VelocityMdp), C.c_void_p]
+      getattr(L, f).restype = C.c_int
+    for f in ("b2s_trk_terms", "b2s_trk_observe"):
+      getattr(L, f).argtypes = [C.POINTER(TrackingMdp), C.c_void_p]
       getattr(L, f).restype = C.c_int
     _bound = True
   return L
@@ -51,10 +70,12 @@ def _stream(device):
 
 def _call(name, p, device):
   if getattr(_lib(), name)(C.byref(p), _stream(device)) != 0:
-    raise engine.BackendError(f"{name}: invalid b2s_velocity_mdp (nworld, nu or nrand)")
+    raise engine.BackendError(f"{name}: invalid parameter struct (nworld, nu, nb or nrand)")
 
 
 def apply_action(p, device): _call("b2s_vel_apply_action", p, device)
 def air_time(p, device): _call("b2s_vel_air_time", p, device)
 def post(p, device): _call("b2s_vel_post", p, device)
 def observe(p, device): _call("b2s_vel_observe", p, device)
+def trk_terms(p, device): _call("b2s_trk_terms", p, device)
+def trk_observe(p, device): _call("b2s_trk_observe", p, device)

@@ -23,6 +23,7 @@ import torch
 from .. import engine, scenes
 from ..hostmodel import HostData
 from ..sim import MujocoCfg, Simulation, SimulationCfg
+from . import fused
 from . import velocity_mdp as mdp
 
 BODY_NAMES = ("pelvis", "left_hip_roll_link", "left_knee_link", "left_ankle_roll_link", "right_hip_roll_link", "right_knee_link",
@@ -123,10 +124,13 @@ class G1TrackingFlatEnv:
   episode_length_s = 10.0
 
   def __init__(self, num_envs: int, device: str = "cuda:0", motion: dict | str | None = None, seed: int = 0, env_spacing: float = 2.5,
-               use_graph: bool = True, sampling_mode: str = "adaptive", adaptive_kernel_size: int = 1, adaptive_lambda: float = 0.8,
+               use_graph: bool = True, use_fused: bool = True, sampling_mode: str = "adaptive", adaptive_kernel_size: int = 1, adaptive_lambda: float = 0.8,
                adaptive_uniform_ratio: float = 0.1, adaptive_alpha: float = 0.001):
     assert sampling_mode in ("adaptive", "uniform", "start")
     self.num_envs, self.device, self.sampling_mode = num_envs, torch.device(device), sampling_mode
+    self.use_fused = use_fused
+    self.gen = None              # tests: a per-env torch.Generator so that two envs draw the same numbers (eager mode only)
+    self.external_U = False      # tests fill U (observation noise) themselves
     torch.cuda.set_device(self.device)
     m = scenes.load_asset("g1_tracking")
     self.m = m
@@ -199,8 +203,16 @@ class G1TrackingFlatEnv:
     self.obs, self.critic_obs = z(W, self.num_obs), z(W, self.num_privileged_obs)
     self.rew = z(W)
     self.dones, self.time_outs, self.terminated = (torch.zeros(W, dtype=torch.bool, device=dev) for _ in range(3))
-    self.term_sums = {k: z(W) for k in REWARD_WEIGHTS}
-    self.metrics = {k: z(W) for k in ("error_anchor_pos", "error_anchor_rot", "error_body_pos", "error_body_rot", "error_joint_pos", "error_joint_vel")}
+    self.term_sums_buf = z(len(REWARD_WEIGHTS), W)
+    self.term_sums = {k: self.term_sums_buf[i] for i, k in enumerate(REWARD_WEIGHTS)}          # B2S_TRK_TERM_* order
+    self.metrics_buf = z(6, W)
+    self.metrics = {k: self.metrics_buf[i] for i, k in enumerate(("error_anchor_pos", "error_anchor_rot", "error_body_pos", "error_body_rot",
+                                                                   "error_joint_pos", "error_joint_vel"))}   # B2S_TRK_MET_* order
+    # observation noise: anchor pos 3 | anchor ori 6 | base lin vel 3 | base ang vel 3 | joint pos nu | joint vel nu
+    self.nrand = 15 + 2 * m.nu
+    self.U = z(W, self.nrand)
+    self.ee_mask = torch.tensor([n in EE_BODY_NAMES for n in BODY_NAMES], dtype=torch.bool, device=dev)
+    self._params = self._make_params() if use_fused else None
     torch.manual_seed(seed)
     self._reset_all()
     self.graph = None
@@ -219,8 +231,11 @@ class G1TrackingFlatEnv:
     lin = cvel[..., 3:6] - torch.cross(cvel[..., 0:3], D.subtree_com[:, self.body_root] - pos, dim=-1)      # entity/data.py:20-31
     return pos, quat, lin, cvel[..., 0:3]
 
+  def _rand(self, *shape):
+    return torch.rand(*shape, device=self.device, generator=self.gen)
+
   def _u(self, lo, hi, *shape):
-    return lo + (hi - lo) * torch.rand(*shape, device=self.device)
+    return lo + (hi - lo) * self._rand(*shape)
 
   # ------------------------------------------------------------------------------------------------ command
   def _sample_time_steps(self, mask):
@@ -229,7 +244,7 @@ class G1TrackingFlatEnv:
     if self.sampling_mode == "start":
       new = torch.zeros_like(self.time_steps)
     elif self.sampling_mode == "uniform":
-      new = (torch.rand(W, device=dev) * self.T).long().clamp(max=self.T - 1)
+      new = (self._rand(W) * self.T).long().clamp(max=self.T - 1)
     else:
       failed = mask & self.terminated
       cur_bin = torch.clamp((self.time_steps * self.bin_count) // max(self.T, 1), 0, self.bin_count - 1)
@@ -241,8 +256,8 @@ class G1TrackingFlatEnv:
       p = torch.nn.functional.conv1d(p, self.kernel.view(1, 1, -1)).view(-1)
       p = p / p.sum()
       cdf = torch.cumsum(p, 0)
-      bins = torch.searchsorted(cdf, torch.rand(W, device=dev) * cdf[-1]).clamp(max=self.bin_count - 1)      # multinomial, replacement=True
-      new = ((bins + torch.rand(W, device=dev)) / self.bin_count * (self.T - 1)).long()
+      bins = torch.searchsorted(cdf, self._rand(W) * cdf[-1]).clamp(max=self.bin_count - 1)      # multinomial, replacement=True
+      new = ((bins + self._rand(W)) / self.bin_count * (self.T - 1)).long()
     self.time_steps.copy_(torch.where(mask, new, self.time_steps))
 
   def _resample_command(self, mask):
@@ -268,8 +283,15 @@ class G1TrackingFlatEnv:
   def _update_command(self):
     """MotionCommand._update_command (commands.py:387-420): advance the phase, wrap finished motions, and re-anchor the
     motion's body poses at the robot's anchor (yaw and xy from the robot, height from the motion)."""
+    self._advance_command()
+    self._reanchor()
+    self._adaptive_ema()
+
+  def _advance_command(self):
     self.time_steps += 1
     self._resample_command(self.time_steps >= self.T)
+
+  def _reanchor(self):
     _, _, bpos, bquat, _, _ = self._motion()
     rpos, rquat, _, _ = self._robot_bodies()
     a = self.anchor_k
@@ -278,14 +300,18 @@ class G1TrackingFlatEnv:
     delta_ori = yaw_quat(mdp.quat_mul(rquat[:, a:a + 1], quat_inv(anchor_quat))).expand(-1, self.nb, -1)
     self.body_quat_relative_w.copy_(mdp.quat_mul(delta_ori, bquat))
     self.body_pos_relative_w.copy_(delta_pos + mdp.quat_apply(delta_ori, bpos - anchor_pos))
+
+  def _adaptive_ema(self):
     if self.sampling_mode == "adaptive":
       self.bin_failed_count.copy_(self.adaptive_alpha * self.current_bin_failed + (1 - self.adaptive_alpha) * self.bin_failed_count)
       self.current_bin_failed.zero_()
 
   # ------------------------------------------------------------------------------------------------ observations
   def _compute_obs(self):
-    D, W = self.D, self.num_envs
-    un = lambda t, a: t + (2.0 * torch.rand_like(t) - 1.0) * a      # noqa: E731
+    D, W, nu = self.D, self.num_envs, self.num_actions
+    if not self.external_U:
+      self.U.uniform_()
+    un = lambda t, a, s0: t + (2.0 * self.U[:, s0:s0 + t.shape[1]] - 1.0) * a      # noqa: E731
     jp_m, jv_m, bpos, bquat, _, _ = self._motion()
     rpos, rquat, _, _ = self._robot_bodies()
     a = self.anchor_k
@@ -297,7 +323,7 @@ class G1TrackingFlatEnv:
     lin, gyro = sd[:, self.s_linvel:self.s_linvel + 3], sd[:, self.s_gyro:self.s_gyro + 3]
     jp, jv = D.qpos[:, 7:] - self.default_joint_pos, D.qvel[:, 6:]
     cmd = torch.cat([jp_m, jv_m], dim=1)
-    self.obs.copy_(torch.cat([cmd, un(pos_b, 0.25), un(ori6, 0.05), un(lin, 0.5), un(gyro, 0.2), un(jp, 0.01), un(jv, 0.5), self.action], dim=1))
+    self.obs.copy_(torch.cat([cmd, un(pos_b, 0.25, 0), un(ori6, 0.05, 3), un(lin, 0.5, 9), un(gyro, 0.2, 12), un(jp, 0.01, 15), un(jv, 0.5, 15 + nu), self.action], dim=1))
     self.critic_obs.copy_(torch.cat([cmd, pos_b, ori6, bp_b.reshape(W, -1), bo6, lin, gyro, jp, jv, self.action], dim=1))
 
   # ------------------------------------------------------------------------------------------------ step
@@ -317,7 +343,62 @@ class G1TrackingFlatEnv:
     self._update_command()
     self._compute_obs()
 
+  def _make_params(self):
+    m, D, W = self.m, self.D, self.num_envs
+    p = fused.TrackingMdp()
+    p.nworld, p.nq, p.nv, p.nu, p.nbody, p.nsensordata, p.nrand = W, m.nq, m.nv, m.nu, m.nbody, m.nsensordata, self.nrand
+    p.nb, p.anchor_k, p.ntime = self.nb, self.anchor_k, self.T
+    self.soft_lo, self.soft_hi = self.soft_limits[:, 0].contiguous(), self.soft_limits[:, 1].contiguous()
+    self.body_ids32, self.body_root32 = self.body_ids.int().contiguous(), self.body_root.int().contiguous()
+    for n in ("qpos", "qvel", "sensordata", "xpos", "xquat", "cvel", "subtree_com"):
+      setattr(p, n, getattr(D, n).data_ptr())
+    for n in ("mo_jp", "mo_jv", "mo_bpos", "mo_bquat", "mo_blin", "mo_bang", "env_origins", "time_steps", "ee_mask", "default_joint_pos",
+              "soft_lo", "soft_hi", "action", "prev_action", "body_pos_relative_w", "body_quat_relative_w", "episode_length_buf",
+              "dones", "time_outs", "terminated", "rew", "obs", "critic_obs", "U"):
+      t = getattr(self, n)
+      assert t.is_contiguous(), n
+      setattr(p, n, t.data_ptr())
+    p.body_ids, p.body_root = self.body_ids32.data_ptr(), self.body_root32.data_ptr()
+    p.term_sums, p.metrics = self.term_sums_buf.data_ptr(), self.metrics_buf.data_ptr()
+    p.s_gyro, p.s_linvel, p.s_self, p.max_episode_length = self.s_gyro, self.s_linvel, self.s_self, self.max_episode_length
+    for i, k in enumerate(REWARD_WEIGHTS):
+      p.weight[i] = REWARD_WEIGHTS[k] * self.step_dt
+    for i, k in enumerate(REWARD_STD):
+      p.inv_std2[i] = 1.0 / REWARD_STD[k] ** 2
+    return p
+
+  def _push(self):
+    """interval event push_by_setting_velocity (tracking_env_cfg.py:216-221, envs/mdp/events.py:173-187)"""
+    D, W = self.D, self.num_envs
+    self.push_time_left -= self.step_dt
+    push = (self.push_time_left <= 0.0).unsqueeze(1)
+    quat = D.qpos[:, 3:7]
+    vel_w = torch.cat([D.qvel[:, 0:3], mdp.quat_apply(quat, D.qvel[:, 3:6])], dim=1) + self._u(self.vel_lo, self.vel_hi, W, 6)
+    new_qvel = torch.cat([vel_w[:, :3], mdp.quat_apply_inverse(quat, vel_w[:, 3:])], dim=1)
+    D.qvel[:, 0:6].copy_(torch.where(push, new_qvel, D.qvel[:, 0:6]))
+    self.push_time_left.copy_(torch.where(push.squeeze(1), self._u(1.0, 3.0, W), self.push_time_left))
+
+  def _step_fused(self):
+    """Same step with the terms / re-anchoring / observations in csrc/k_mdp_tracking.cu; sampling, resets and the push event
+    stay masked tensor ops."""
+    D, M, p, dev = self.D, self.M, self._params, self.device
+    self.prev_action.copy_(self.action)
+    self.action.copy_(self.actions_in)
+    D.ctrl.copy_(self.default_joint_pos + self.action * self.action_scale)
+    engine.step(M, D, self.decimation)
+    fused.trk_terms(p, dev)
+    self._reset_masked(self.dones)
+    engine.forward(M, D)
+    self._advance_command()
+    self._adaptive_ema()
+    self._push()
+    if not self.external_U:
+      self.U.uniform_()
+    fused.trk_observe(p, dev)
+
   def _step_impl(self):
+    if self.use_fused:
+      return self._step_fused()
     D, M, W = self.D, self.M, self.num_envs
     self.prev_action.copy_(self.action)
     self.action.copy_(self.actions_in)
@@ -365,13 +446,7 @@ class G1TrackingFlatEnv:
     engine.forward(M, D)
     # ---- command manager, interval push event (tracking_env_cfg.py:216-221), observations
     self._update_command()
-    self.push_time_left -= self.step_dt
-    push = (self.push_time_left <= 0.0).unsqueeze(1)
-    quat = D.qpos[:, 3:7]
-    vel_w = torch.cat([D.qvel[:, 0:3], mdp.quat_apply(quat, D.qvel[:, 3:6])], dim=1) + self._u(self.vel_lo, self.vel_hi, W, 6)
-    new_qvel = torch.cat([vel_w[:, :3], mdp.quat_apply_inverse(quat, vel_w[:, 3:])], dim=1)
-    D.qvel[:, 0:6].copy_(torch.where(push, new_qvel, D.qvel[:, 0:6]))
-    self.push_time_left.copy_(torch.where(push.squeeze(1), self._u(1.0, 3.0, W), self.push_time_left))
+    self._push()
     self._compute_obs()
 
   def _capture(self):

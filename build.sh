@@ -6,7 +6,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC $*"
 mkdir -p ../_build
 pids=()
-for f in b2s_api k_smooth k_collision k_constraint k_solver k_post k_mdp; do
+for f in b2s_api k_smooth k_collision k_constraint k_solver k_post k_mdp k_mdp_tracking; do
   $NVCC $FLAGS -c $f.cu -o ../_build/$f.o &
   pids+=($!)
 done

@@ -346,6 +346,39 @@ int b2s_vel_post(const b2s_velocity_mdp* p, void* stream);
 /* after forward(): command timers / heading control, push event, policy and critic observations */
 int b2s_vel_observe(const b2s_velocity_mdp* p, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Fused manager terms of the motion-tracking task (tasks/tracking/mdp/{rewards,terminations,observations}.py, the metrics and
+ * the re-anchoring of commands.py:219-259,396-415).  Two launches per env step, one warp per env, one lane per tracked body /
+ * per joint; phase sampling, resets and the push event stay host-side tensor ops.  Motion arrays are (T, nb, 3|4) for the nb
+ * tracked bodies and (T, nu) for the joints; `time_steps` is each env's frame.  U: (nworld, nrand >= 15 + 2 nu) uniform [0,1)
+ * numbers for the observation noise (anchor pos 3, anchor ori 6, base lin vel 3, base ang vel 3, joint pos nu, joint vel nu). */
+enum { B2S_TRK_TERM_ROOT_POS = 0, B2S_TRK_TERM_ROOT_ORI, B2S_TRK_TERM_BODY_POS, B2S_TRK_TERM_BODY_ORI, B2S_TRK_TERM_BODY_LIN_VEL,
+       B2S_TRK_TERM_BODY_ANG_VEL, B2S_TRK_TERM_ACTION_RATE, B2S_TRK_TERM_JOINT_LIMIT, B2S_TRK_TERM_SELF_COLLISIONS, B2S_TRK_NTERM };
+enum { B2S_TRK_MET_ANCHOR_POS = 0, B2S_TRK_MET_ANCHOR_ROT, B2S_TRK_MET_BODY_POS, B2S_TRK_MET_BODY_ROT, B2S_TRK_MET_JOINT_POS,
+       B2S_TRK_MET_JOINT_VEL, B2S_TRK_NMET };
+typedef struct b2s_tracking_mdp {
+  int nworld, nq, nv, nu, nbody, nsensordata, nrand, nb, anchor_k, ntime;
+  const float *qpos, *qvel, *sensordata, *xpos, *xquat, *cvel, *subtree_com;
+  const float *mo_jp, *mo_jv, *mo_bpos, *mo_bquat, *mo_blin, *mo_bang, *env_origins;
+  const long long* time_steps;
+  const int *body_ids, *body_root;          /* model body id / root body id of each tracked body */
+  const unsigned char* ee_mask;             /* [nb] 1 for end-effector bodies (termination) */
+  const float *default_joint_pos, *soft_lo, *soft_hi, *action, *prev_action;
+  int s_gyro, s_linvel, s_self, max_episode_length;
+  float weight[B2S_TRK_NTERM];              /* term weight x step_dt */
+  float inv_std2[6];                        /* 1 / std^2 of the six exponential tracking terms */
+  float *body_pos_relative_w, *body_quat_relative_w;
+  long long* episode_length_buf;
+  unsigned char *dones, *time_outs, *terminated;
+  float *rew, *term_sums, *metrics;         /* term_sums (B2S_TRK_NTERM, nworld), metrics (B2S_TRK_NMET, nworld) */
+  float *obs, *critic_obs;
+  const float* U;
+} b2s_tracking_mdp;
+/* episode counter, terminations (time-out, anchor height, anchor orientation, end-effector height), the 9 reward terms, metrics */
+int b2s_trk_terms(const b2s_tracking_mdp* p, void* stream);
+/* re-anchor the motion's body poses at the robot's anchor (body_*_relative_w), then policy and critic observations */
+int b2s_trk_observe(const b2s_tracking_mdp* p, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

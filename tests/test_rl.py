@@ -260,3 +260,42 @@ def test_tracking_env_follows_its_reference_motion():
 def mdp_quat_yaw(yaw):
   from asimov_mjlab_b200.rl import velocity_mdp as mdp
   return mdp.quat_from_yaw(yaw)
+
+
+@pytest.mark.gpu
+def test_fused_tracking_kernels_match_torch_terms():
+  """csrc/k_mdp_tracking.cu (terminations, rewards, metrics, re-anchoring, observations) against the torch restatement:
+  two envs with identically seeded private generators and the same observation-noise buffer stay on ONE trajectory
+  (resets, phase sampling and pushes are the same tensor ops in both), so every step compares like with like."""
+  from asimov_mjlab_b200.rl import tracking_env as te
+  W = 192
+  mo = te.synthetic_motion(device="cuda:0")
+  envs = [te.G1TrackingFlatEnv(W, "cuda:0", motion=mo, seed=4, use_graph=False, use_fused=f) for f in (False, True)]
+  for e in envs:
+    e.gen = torch.Generator(device="cuda:0").manual_seed(123)
+    e.external_U = True
+    e.bin_failed_count.zero_(); e.current_bin_failed.zero_()
+    e.U.fill_(0.5)
+    e._reset_all()
+  a, b = envs
+  assert torch.equal(a.D.qpos, b.D.qpos) and torch.equal(a.time_steps, b.time_steps)
+  g = torch.Generator(device="cuda:0").manual_seed(9)
+  ndone = 0
+  for it in range(70):
+    U = torch.rand(W, a.nrand, device="cuda:0", generator=g)
+    act = torch.randn(W, a.num_actions, device="cuda:0", generator=g) * (2.0 if it % 4 == 0 else 0.2)
+    for e in envs:
+      e.U.copy_(U)
+      e.step(act)
+    assert torch.equal(a.D.qpos, b.D.qpos) and torch.equal(a.D.qvel, b.D.qvel), it
+    assert torch.equal(a.time_steps, b.time_steps) and torch.equal(a.episode_length_buf, b.episode_length_buf)
+    assert torch.equal(a.dones, b.dones) and torch.equal(a.terminated, b.terminated) and torch.equal(a.time_outs, b.time_outs)
+    assert torch.allclose(a.rew, b.rew, rtol=1e-4, atol=2e-6)
+    assert torch.allclose(a.obs, b.obs, rtol=1e-4, atol=5e-6) and torch.allclose(a.critic_obs, b.critic_obs, rtol=1e-4, atol=5e-6)
+    assert torch.allclose(a.body_pos_relative_w, b.body_pos_relative_w, atol=5e-6)
+    assert torch.allclose(a.body_quat_relative_w, b.body_quat_relative_w, atol=5e-6)
+    assert torch.allclose(a.metrics_buf, b.metrics_buf, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(a.bin_failed_count, b.bin_failed_count)
+    ndone += int(a.dones.sum())
+  assert ndone > W // 2
+  assert torch.allclose(a.term_sums_buf, b.term_sums_buf, rtol=1e-3, atol=1e-5)
