@@ -223,6 +223,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   const float* qvel = d.qvel + (size_t)w * nv;
   const float* qpos = d.qpos + (size_t)w * m.nq;
   // stage cdof, cinert, qvel
+#pragma unroll 4
   for (int i = lane; i < 6 * nv; i += 32) s_cdof[i] = d.cdof[(size_t)w * 6 * nv + i];
   for (int i = lane; i < nv; i += 32) { s_qvel[i] = qvel[i]; s_act[i] = 0.f; }
   for (int i = lane; i < b2s_hdim(T) * ld; i += 32) s_M[i] = 0.f;
@@ -230,6 +231,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   // composite inertia: sum of cinert over the subtree range (same frame for all bodies).  cinert is staged once,
   // coalesced, into the cfrc|fext region (12 nb floats, not written until the RNE pass below)
   float* s_cin = s_cfrc;
+#pragma unroll 4
   for (int i = lane; i < 10 * nb; i += 32) s_cin[i] = d.cinert[(size_t)w * nb * 10 + i];
   __syncwarp();
   for (int b = lane; b < nb; b += 32) {
@@ -318,11 +320,24 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   }
   __syncwarp();
   // write M (symmetric, dense, row stride nvp) to HBM
-  for (int i = lane, r = 0, c = lane; i < nv * nvp; i += 32, c += 32) {
-    while (c >= nvp) { c -= nvp; r++; }
-    float v = 0.f;
-    if (c < nv) v = (c <= r) ? s_M[r * ld + c] : s_M[c * ld + r];
-    d.qM[(size_t)w * nv * nvp + i] = v;
+  // one lane per row, 16-byte stores (nvp is a multiple of 4, rows are 16-byte aligned); row r mirrors the lower triangle
+  {
+    constexpr int Q = (7 * T + 3) / 4;
+    const int n4 = nvp >> 2;
+#pragma unroll 1
+    for (int r = lane; r < nv; r += 32) {
+      float4* out = reinterpret_cast<float4*>(d.qM + ((size_t)w * nv + r) * nvp);
+#pragma unroll
+      for (int j = 0; j < Q; j++) {
+        float e[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const int c = 4 * j + k;
+          e[k] = c < nv ? (c <= r ? s_M[r * ld + c] : s_M[c * ld + r]) : 0.f;
+        }
+        if (j < n4) out[j] = make_float4(e[0], e[1], e[2], e[3]);
+      }
+    }
   }
   // fixed tendons: length / velocity; spring (deadband) and damper forces accumulate in s_tmp
   if (m.ntendon > 0) {
