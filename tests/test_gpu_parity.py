@@ -722,3 +722,45 @@ def test_g1_cg_solver_matches_oracle_and_newton(g1, ls_parallel):
   # and a few steps run without NaNs through the CG path
   engine.step(M, D, 8)
   assert np.isfinite(D.qpos.cpu().numpy()).all()
+
+
+@pytest.mark.gpu
+def test_simulation_config_is_piped_like_the_reference_test():
+  """Mirror of the reference's tests/test_sim.py:43-82 on this backend: euler + cg + non-default iterations / gravity / time
+  step given through SimulationCfg reach both the host model and the device model, and the configured simulation steps."""
+  import torch
+  from asimov_mjlab_b200.sim import MujocoCfg, Simulation, SimulationCfg
+  xml = """
+  <mujoco>
+    <worldbody>
+      <geom name="floor" type="plane" size="5 5 0.1"/>
+      <body name="base" pos="0 0 1">
+        <freejoint name="free_joint"/>
+        <geom name="base_geom" type="box" size="0.1 0.1 0.1" mass="1.0" friction="0.5 0.01 0.005"/>
+        <body name="foot1" pos="0.2 0 0">
+          <joint name="joint1" type="hinge" axis="0 0 1" range="0 1.57"/>
+          <geom name="foot1_geom" type="box" size="0.05 0.05 0.05" mass="0.1" friction="0.5 0.01 0.005"/>
+        </body>
+        <body name="foot2" pos="-0.2 0 0">
+          <joint name="joint2" type="hinge" axis="0 0 1" range="0 1.57"/>
+          <geom name="foot2_geom" type="box" size="0.05 0.05 0.05" mass="0.1" friction="0.5 0.01 0.005"/>
+        </body>
+      </body>
+    </worldbody>
+  </mujoco>"""
+  model = fx.compile_xml(xml)
+  cfg = SimulationCfg(contact_sensor_maxmatch=128, ls_parallel=False,
+                      mujoco=MujocoCfg(timestep=0.02, integrator="euler", solver="cg", iterations=7, ls_iterations=14, gravity=(0, 0, 7.5)))
+  sim = Simulation(num_envs=3, cfg=cfg, model=model, device="cuda:0")
+  assert sim.mj_model.opt.timestep == 0.02 and sim.mj_model.opt.integrator == 0 and sim.mj_model.opt.solver == 1      # mjINT_EULER, mjSOL_CG
+  assert sim.mj_model.opt.iterations == 7 and tuple(sim.mj_model.opt.gravity) == (0, 0, 7.5)
+  np.testing.assert_almost_equal(sim.model.opt.timestep[0].cpu().numpy(), 0.02)
+  np.testing.assert_almost_equal(sim.model.opt.gravity[0].cpu().numpy(), (0, 0, 7.5))
+  assert sim.model.opt.integrator == 0 and sim.model.opt.solver == 1 and sim.model.opt.iterations == 7 and sim.model.opt.ls_iterations == 14
+  assert sim.wp_model.opt.contact_sensor_maxmatch == 128 and sim.wp_model.opt.ls_parallel is False
+  # "gravity" of +7.5 m/s^2 lifts the free body: after 5 euler steps of 0.02 s, z = 1 + 7.5 * dt^2 * (1 + 2 + 3 + 4 + 5)
+  for _ in range(5):
+    sim.step()
+  torch.cuda.synchronize()
+  assert torch.allclose(sim.data.qpos[:, 2], torch.full((3,), 1.0 + 7.5 * 0.02 ** 2 * 15, device="cuda:0"), atol=1e-5)
+  assert float(sim.data.time[0]) == pytest.approx(0.1)
