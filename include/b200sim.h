@@ -62,7 +62,7 @@ enum { B2S_CON_FOUND = 1, B2S_CON_FORCE = 2, B2S_CON_TORQUE = 4, B2S_CON_DIST = 
        B2S_CON_POS = 16, B2S_CON_NORMAL = 32, B2S_CON_TANGENT = 64 };
 enum { B2S_REDUCE_NONE = 0, B2S_REDUCE_MINDIST = 1, B2S_REDUCE_MAXFORCE = 2, B2S_REDUCE_NETFORCE = 3 };
 /* disable flags (subset of mjtDisableBit that this path honours) */
-enum { B2S_DSBL_CONSTRAINT = 1 << 0, B2S_DSBL_LIMIT = 1 << 3, B2S_DSBL_CONTACT = 1 << 4,
+enum { B2S_DSBL_CONSTRAINT = 1 << 0, B2S_DSBL_FRICTIONLOSS = 1 << 2, B2S_DSBL_LIMIT = 1 << 3, B2S_DSBL_CONTACT = 1 << 4,
        B2S_DSBL_PASSIVE = 1 << 5, B2S_DSBL_GRAVITY = 1 << 6, B2S_DSBL_CLAMPCTRL = 1 << 7,
        B2S_DSBL_WARMSTART = 1 << 8, B2S_DSBL_FILTERPARENT = 1 << 9, B2S_DSBL_ACTUATION = 1 << 10,
        B2S_DSBL_REFSAFE = 1 << 11, B2S_DSBL_EULERDAMP = 1 << 13 };

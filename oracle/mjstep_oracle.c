@@ -833,8 +833,22 @@ static void finish_row(const b2s_model_desc* m, orc_data* d, int r, const real* 
 
 void orc_make_constraint(const b2s_model_desc* m, orc_data* d) {
   int nv = m->nv, nefc = 0;
-  d->nefc[0] = 0; d->nl[0] = 0;
+  d->nefc[0] = 0; d->nl[0] = 0; d->nf[0] = 0;
   if (m->opt_disableflags & B2S_DSBL_CONSTRAINT) return;
+  /* dof friction loss (mj_instantiateFriction): one row per dof with frictionloss > 0, J = e_dof, pos = margin = 0, default
+   * solreffriction / solimpfriction; the rows come before the limits (MuJoCo order: equality, friction, limit, contact) */
+  if (!(m->opt_disableflags & B2S_DSBL_FRICTIONLOSS))
+    for (int i = 0; i < nv; i++) {
+      if (!(m->dof_frictionloss[i] > 0) || nefc >= d->njmax) continue;
+      int r = nefc++;
+      for (int k = 0; k < nv; k++) d->efc_J[r*nv + k] = 0;
+      d->efc_J[r*nv + i] = 1;
+      d->efc_pos[r] = 0; d->efc_margin[r] = 0; d->efc_frictionloss[r] = (real)m->dof_frictionloss[i];
+      d->efc_type[r] = ORC_EFC_FRICTION_DOF; d->efc_id[r] = i;
+      real sr[2] = {(real)0.02, 1}, si[5] = {(real)0.9, (real)0.95, (real)0.001, (real)0.5, 2};
+      finish_row(m, d, r, sr, si, (real)m->dof_invweight0[i], 1);
+    }
+  d->nf[0] = nefc;
   /* joint limits: lower side then upper side (mj_instantiateLimit) */
   if (!(m->opt_disableflags & B2S_DSBL_LIMIT))
     for (int j = 0; j < m->njnt; j++) {
@@ -1060,6 +1074,7 @@ typedef struct {
   real *Ma, *Jaref, *grad, *Mgrad, *search, *Mv, *Jv, *H, *HL, *quad;
   real *gradold, *Mgradold;   /* CG: previous gradient and M^-1 gradient (Polak-Ribiere) */
   int cg, have_ml;
+  int nf;                     /* rows [0, nf) are friction-loss rows: quadratic inside |Jaref| < R f, linear outside */
   int* active;
   real cost, gauss, quadGauss[3];
 } solctx;
@@ -1070,6 +1085,14 @@ static void sol_update_constraint(solctx* c) {
   real cost = 0;
   for (int r = 0; r < c->nefc; r++) {
     real jar = c->Jaref[r], D = d->efc_D[r];
+    if (r < c->nf) {
+      /* friction loss (mj_constraintUpdate): force saturates at +-f outside the quadratic zone |jar| < R f */
+      real f = d->efc_frictionloss[r], rf = f/D;
+      if (jar <= -rf) { d->efc_force[r] = f; c->active[r] = 0; cost += -f*((real)0.5*rf + jar); }
+      else if (jar >= rf) { d->efc_force[r] = -f; c->active[r] = 0; cost += -f*((real)0.5*rf - jar); }
+      else { d->efc_force[r] = -D*jar; c->active[r] = 1; cost += (real)0.5*D*jar*jar; }
+      continue;
+    }
     if (jar < 0) { d->efc_force[r] = -D*jar; c->active[r] = 1; cost += (real)0.5*D*jar*jar; }
     else { d->efc_force[r] = 0; c->active[r] = 0; }
   }
@@ -1109,6 +1132,13 @@ static lspoint ls_eval(const solctx* c, real alpha) {
   real q0 = c->quadGauss[0], q1 = c->quadGauss[1], q2 = c->quadGauss[2];
   for (int r = 0; r < c->nefc; r++) {
     real x = c->Jaref[r] + alpha*c->Jv[r];
+    if (r < c->nf) {
+      real f = c->d->efc_frictionloss[r], rf = f/c->d->efc_D[r];
+      if (x <= -rf) { q0 += f*(-(real)0.5*rf - c->Jaref[r]); q1 += -f*c->Jv[r]; }
+      else if (x >= rf) { q0 += f*(-(real)0.5*rf + c->Jaref[r]); q1 += f*c->Jv[r]; }
+      else { q0 += c->quad[3*r]; q1 += c->quad[3*r + 1]; q2 += c->quad[3*r + 2]; }
+      continue;
+    }
     if (x < 0) { q0 += c->quad[3*r]; q1 += c->quad[3*r + 1]; q2 += c->quad[3*r + 2]; }
   }
   lspoint p;
@@ -1191,7 +1221,7 @@ void orc_solve(const b2s_model_desc* m, orc_data* d) {
     for (int i = 0; i < nv; i++) { d->qacc[i] = d->qacc_smooth[i]; d->qfrc_constraint[i] = 0; }
     return;
   }
-  solctx c; c.m = m; c.d = d; c.nv = nv; c.nefc = nefc;
+  solctx c; c.m = m; c.d = d; c.nv = nv; c.nefc = nefc; c.nf = d->nf[0];
   real* buf = (real*)calloc((size_t)(9*nv + 2*nv*nv + 5*nefc), sizeof(real));
   c.cg = m->opt_solver == B2S_SOL_CG; c.have_ml = 0;
   c.Ma = buf; c.grad = c.Ma + nv; c.Mgrad = c.grad + nv; c.search = c.Mgrad + nv; c.Mv = c.search + nv;
@@ -1211,7 +1241,12 @@ void orc_solve(const b2s_model_desc* m, orc_data* d) {
       for (int r = 0; r < nefc; r++) {
         real s = 0; for (int j = 0; j < nv; j++) s += d->efc_J[r*nv + j]*d->qacc_smooth[j];
         s -= d->efc_aref[r];
-        if (s < 0) cost_smooth += (real)0.5*d->efc_D[r]*s*s;
+        if (r < c.nf) {
+          real f = d->efc_frictionloss[r], rf = f/d->efc_D[r];
+          if (s <= -rf) cost_smooth += -f*((real)0.5*rf + s);
+          else if (s >= rf) cost_smooth += -f*((real)0.5*rf - s);
+          else cost_smooth += (real)0.5*d->efc_D[r]*s*s;
+        } else if (s < 0) cost_smooth += (real)0.5*d->efc_D[r]*s*s;
       }
       if (cost_warm <= cost_smooth) break;
     }

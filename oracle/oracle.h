@@ -91,7 +91,9 @@ typedef struct orc_data {
   int32_t* con_efc_address; /* nconmax */
   /* constraints */
   int32_t* nefc;         /* 1 */
+  /* rows [0, nl) act on a single dof: first the nf friction-loss rows, then the joint-limit rows */
   int32_t* nl;           /* 1 */
+  int32_t* nf;           /* 1 */
   int32_t* efc_type;     /* njmax */
   int32_t* efc_id;       /* njmax */
   real* efc_J;           /* njmax*nv */
@@ -101,12 +103,13 @@ typedef struct orc_data {
   real* efc_vel;         /* njmax */
   real* efc_aref;        /* njmax */
   real* efc_force;       /* njmax */
+  real* efc_frictionloss; /* njmax */
   /* solver statistics */
   int32_t* solver_niter; /* 1 */
   real* solver_cost;     /* 1 */
 } orc_data;
 
-enum { ORC_EFC_LIMIT = 3, ORC_EFC_CONTACT_FRICTIONLESS = 4, ORC_EFC_CONTACT_PYRAMIDAL = 5 };
+enum { ORC_EFC_FRICTION_DOF = 1, ORC_EFC_LIMIT = 3, ORC_EFC_CONTACT_FRICTIONLESS = 4, ORC_EFC_CONTACT_PYRAMIDAL = 5 };
 
 int orc_real_size(void);
 /* mjwarp.forward / mjwarp.step for one world (reference call sites: sim.py:143,146). */

@@ -70,6 +70,32 @@ SLIDER_PD = """
 </mujoco>
 """
 
+# two sliders with dry friction (joint frictionloss), one hinge arm with friction on both joints under gravity
+SLIDER_FRICTION = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.005" integrator="implicitfast" gravity="0 0 -9.81"/>
+  <worldbody>
+    <body name="cart" pos="0 0 1">
+      <joint name="s1" type="slide" axis="1 0 0" frictionloss="2.0"/>
+      <geom type="box" size="0.1 0.1 0.1" mass="1.0" contype="0" conaffinity="0"/>
+    </body>
+    <body name="cart2" pos="0 1 1">
+      <joint name="s2" type="slide" axis="1 0 0" frictionloss="0.5" damping="0.3"/>
+      <geom type="box" size="0.1 0.1 0.1" mass="4.0" contype="0" conaffinity="0"/>
+    </body>
+    <body name="arm" pos="0 2 1">
+      <joint name="h1" type="hinge" axis="0 1 0" frictionloss="0.4" range="-2 2"/>
+      <geom type="capsule" fromto="0 0 0 0.4 0 0" size="0.03" mass="1.0" contype="0" conaffinity="0"/>
+      <body name="fore" pos="0.4 0 0">
+        <joint name="h2" type="hinge" axis="0 1 0" frictionloss="0.1"/>
+        <geom type="capsule" fromto="0 0 0 0.3 0 0" size="0.02" mass="0.4" contype="0" conaffinity="0"/>
+      </body>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
 SPINNER = """
 <mujoco>
   <compiler angle="radian"/>

@@ -438,3 +438,38 @@ def test_scalar_and_frame_sensor_readouts():
   sd2 = {n: w2["sensordata"][a:a + d] for n, a, d in zip(m.names["sensor"], m.sensor_adr, m.sensor_dim)}
   qa = w2["qacc"]
   assert np.allclose(sd2["aa"], np.array([0.0, 1.0, 0.0]) * qa[0] + np.array([0.0, 0.0, 1.0]) * qa[1], atol=1e-9)
+
+
+def test_joint_friction_loss_closed_forms():
+  """Dry joint friction (mj_instantiateFriction + the Huber-shaped cost of mj_constraintUpdate).  A 1 kg slider with
+  frictionloss f = 2 N and default solreffriction / solimpfriction: R = (1 - 0.9) / 0.9 * invweight0 = 1/9, D = 9.
+  Pushed with F < f it sits in the quadratic zone, qacc = F / (m + D); pushed with F > f the force saturates at -f and
+  qacc = (F - f) / m; moving and unforced it decelerates with f / m (aref = -B v pushes jar past the zone)."""
+  m = fx.compile_xml(fx.SLIDER_FRICTION)
+  orc = Oracle(m, "f64", 4, 16)
+  def solve(F, v=0.0):
+    w = orc.new_world(None, np.array([v, 0, 0, 0.0]), None)
+    w["qfrc_applied"][0] = F
+    orc.forward(w)
+    return w
+  w = solve(1.0)
+  assert int(w["nf"][0]) == 4 and int(w["nl"][0]) == 4 and int(w["nefc"][0]) == 4
+  assert np.isclose(w["efc_D"][0], 9.0, rtol=1e-9) and np.isclose(w["efc_frictionloss"][0], 2.0)
+  assert np.isclose(w["qacc"][0], 1.0 / (1.0 + 9.0), rtol=1e-8) and np.isclose(w["efc_force"][0], -0.9, rtol=1e-8)
+  w = solve(5.0)
+  assert np.isclose(w["qacc"][0], 3.0, rtol=1e-8) and np.isclose(w["efc_force"][0], -2.0)
+  w = solve(-5.0)
+  assert np.isclose(w["qacc"][0], -3.0, rtol=1e-8) and np.isclose(w["efc_force"][0], 2.0)
+  w = solve(0.0, v=1.5)
+  assert np.isclose(w["qacc"][0], -2.0, rtol=1e-8)
+  # a resting arm under gravity: the elbow's 0.1 N m of friction cannot hold the forearm's gravity torque (0.4 * 9.81 * 0.15)
+  assert abs(w["efc_force"][3]) == pytest.approx(0.1) and abs(w["qacc"][3]) > 1.0
+  # disabling the feature removes the rows
+  import copy
+  m2 = copy.copy(m); m2.opt = copy.copy(m.opt); m2.opt.disableflags = 1 << 2
+  w2 = Oracle(m2, "f64", 4, 16).forward(Oracle(m2, "f64", 4, 16).new_world())
+  assert int(w2["nf"][0]) == 0 and int(w2["nefc"][0]) == 0
+  # a sliding block stops and stays: 1.5 m/s decelerating at 2 m/s^2 is at rest after 0.75 s, within a few mm of v0^2 / (2 a)
+  w = orc.new_world(None, np.array([1.5, 0, 0, 0.0]), None)
+  orc.step(w, 400)
+  assert abs(w["qvel"][0]) < 1e-6 and abs(w["qpos"][0] - 1.5 ** 2 / 4.0) < 5e-3
