@@ -149,7 +149,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   if (s->opt_solver != B2S_SOL_NEWTON && s->opt_solver != B2S_SOL_CG) return fail("solver must be newton or cg (PGS is not supported)");
   if (s->opt_integrator != B2S_INT_EULER && s->opt_integrator != B2S_INT_IMPLICITFAST) return fail("integrator must be euler or implicitfast");
   const int nb = s->nbody, nv = s->nv;
-  for (int i = 0; i < nv; i++) if (s->dof_frictionloss[i] != 0.0) return fail("dof_frictionloss is not supported");
+  for (int i = 0; i < nv; i++) if (s->dof_frictionloss[i] < 0.0) return fail("dof_frictionloss must be non-negative");
   for (int j = 0; j < s->njnt; j++) {
     if (s->jnt_type[j] < 0 || s->jnt_type[j] > 3) return fail("unknown joint type");
     if (s->jnt_type[j] == B2S_JNT_BALL && s->jnt_limited[j]) return fail("ball joint limits are not supported");
@@ -372,7 +372,9 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.tolerance = (float)s->opt_tolerance; d.ls_tolerance = (float)s->opt_ls_tolerance; d.impratio = (float)s->opt_impratio;
   d.ls_parallel_min_step = (float)(s->opt_ls_parallel_min_step > 0 ? s->opt_ls_parallel_min_step : 1e-6);
   d.meaninertia = (float)s->stat_meaninertia;
-  d.integrator = s->opt_integrator; d.cone = s->opt_cone; d.solver = s->opt_solver; d.iterations = s->opt_iterations; d.ls_iterations = s->opt_ls_iterations;
+  d.integrator = s->opt_integrator; d.cone = s->opt_cone; d.solver = s->opt_solver;
+  d.fric = 0;
+  for (int i = 0; i < nv; i++) if (s->dof_frictionloss[i] > 0.0) d.fric = 1; d.iterations = s->opt_iterations; d.ls_iterations = s->opt_ls_iterations;
   d.disableflags = s->opt_disableflags; d.ls_parallel = s->opt_ls_parallel;
   d.contact_sensor_maxmatch = s->opt_contact_sensor_maxmatch > 0 ? s->opt_contact_sensor_maxmatch : 64;
   d.body_parentid = up.i(s->body_parentid, nb); d.body_rootid = up.i(s->body_rootid, nb); d.body_mocapid = up.i(s->body_mocapid, nb);
@@ -582,6 +584,9 @@ extern "C" int b2s_model_expand(b2s_model* m, const char* name, int nworld) {
   CU(cudaDeviceSynchronize());
   r.wf->ptr = p; r.wf->wstride = (int)r.elems;
   m->nexpanded++;
+  // a per-world dof_frictionloss may be written later (domain randomisation, envs/mdp/events.py:231): switch the
+  // friction-loss rows and the solver instantiation that understands them on
+  if (std::string(name) == "dof_frictionloss") m->dev.fric = 1;
   return 0;
 }
 
@@ -654,10 +659,10 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"contact_pos", B2S_F32, (void**)&d.con_pos, {nconmax, 3}}, {"contact_frame", B2S_F32, (void**)&d.con_frame, {nconmax, 3, 3}},
     {"contact_includemargin", B2S_F32, (void**)&d.con_includemargin, {nconmax}}, {"contact_friction", B2S_F32, (void**)&d.con_friction, {nconmax, 5}},
     {"contact_solref", B2S_F32, (void**)&d.con_solref, {nconmax, 2}}, {"contact_solimp", B2S_F32, (void**)&d.con_solimp, {nconmax, 5}},
-    {"nefc", B2S_I32, (void**)&d.nefc, {}}, {"nl", B2S_I32, (void**)&d.nl, {}}, {"efc_type", B2S_I32, (void**)&d.efc_type, {njmax}}, {"efc_id", B2S_I32, (void**)&d.efc_id, {njmax}},
+    {"nefc", B2S_I32, (void**)&d.nefc, {}}, {"nl", B2S_I32, (void**)&d.nl, {}}, {"nf", B2S_I32, (void**)&d.nf, {}}, {"efc_type", B2S_I32, (void**)&d.efc_type, {njmax}}, {"efc_id", B2S_I32, (void**)&d.efc_id, {njmax}},
     {"efc_g", B2S_F32, (void**)&d.efc_g, {njmax, 6}}, {"efc_bp", B2S_I32, (void**)&d.efc_bp, {njmax}}, {"efc_pos", B2S_F32, (void**)&d.efc_pos, {njmax}}, {"efc_margin", B2S_F32, (void**)&d.efc_margin, {njmax}},
     {"efc_D", B2S_F32, (void**)&d.efc_D, {njmax}}, {"efc_vel", B2S_F32, (void**)&d.efc_vel, {njmax}}, {"efc_aref", B2S_F32, (void**)&d.efc_aref, {njmax}},
-    {"efc_force", B2S_F32, (void**)&d.efc_force, {njmax}},
+    {"efc_force", B2S_F32, (void**)&d.efc_force, {njmax}}, {"efc_frictionloss", B2S_F32, (void**)&d.efc_frictionloss, {njmax}},
     {"qacc", B2S_F32, (void**)&d.qacc, {nv}}, {"qfrc_constraint", B2S_F32, (void**)&d.qfrc_constraint, {nv}},
     {"solver_cost", B2S_F32, (void**)&d.solver_cost, {}}, {"solver_niter", B2S_I32, (void**)&d.solver_niter, {}},
     {"solve_order", B2S_I32, (void**)&d.solve_order, {B2S_SOLVE_CLASSES}}, {"solve_count", B2S_I32, (void**)&d.solve_count, {B2S_SOLVE_CLASSES}},

@@ -30,6 +30,7 @@ struct ModelDev {
   int ref_root;                     // root body of the first kinematic tree: its subtree COM is the constraint reference point
   // options
   float timestep, gravity[3], tolerance, ls_tolerance, impratio, ls_parallel_min_step, meaninertia;
+  int fric;                         // 1: the model can have friction-loss rows (dof_frictionloss > 0 somewhere, or the field is per-world)
   int integrator, cone, solver, iterations, ls_iterations, disableflags, ls_parallel, contact_sensor_maxmatch;
   // ---- bodies
   const int *body_parentid, *body_rootid, *body_mocapid, *body_jntnum, *body_jntadr, *body_dofnum, *body_dofadr;
@@ -101,9 +102,9 @@ struct DataDev {
   int *ncon, *con_dim, *con_geom, *con_efc_address;
   float *con_dist, *con_pos, *con_frame, *con_includemargin, *con_friction, *con_solref, *con_solimp;
   // constraints
-  int *nefc, *nl, *efc_type, *efc_id, *efc_bp;   // efc_bp: contact rows body1 | body2 << 16, limit rows -1 - dof
+  int *nefc, *nl, *nf, *efc_type, *efc_id, *efc_bp;   // rows [0, nl) act on one dof: nf friction-loss rows, then the limits;   // efc_bp: contact rows body1 | body2 << 16, limit rows -1 - dof
   float *efc_g;                                  // [njmax][6] row wrench about the reference point (limit rows: g[0] = +-1)
-  float *efc_pos, *efc_margin, *efc_D, *efc_vel, *efc_aref, *efc_force;
+  float *efc_pos, *efc_margin, *efc_D, *efc_vel, *efc_aref, *efc_force, *efc_frictionloss;
   // solver
   float *qacc, *qfrc_constraint, *solver_cost;
   int *solver_niter;

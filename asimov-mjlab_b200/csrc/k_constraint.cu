@@ -21,7 +21,7 @@
 
 extern __shared__ float b2s_smem[];
 
-enum { EFC_LIMIT = 3, EFC_CONTACT_FRICTIONLESS = 4, EFC_CONTACT_PYRAMIDAL = 5 };
+enum { EFC_FRICTION_DOF = 1, EFC_LIMIT = 3, EFC_CONTACT_FRICTIONLESS = 4, EFC_CONTACT_PYRAMIDAL = 5 };
 
 DEV float impedance(const float* si, float pos, float margin) {
   const float d0 = si[0], dw = si[1], width = si[2], mid = si[3], power = si[4];
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
   const int nv = m.nv, nb = m.nbody, njmax = d.njmax;
   float* s_cvel = b2s_smem + (size_t)warp * 6 * nb;     // body velocities about the world's reference point
   if (m.disableflags & B2S_DSBL_CONSTRAINT) {
-    if (lane == 0) { d.nefc[w] = 0; d.nl[w] = 0; d.solve_order[atomicAdd(&d.solve_count[0], 1)] = w; }
+    if (lane == 0) { d.nefc[w] = 0; d.nl[w] = 0; d.nf[w] = 0; d.solve_order[atomicAdd(&d.solve_count[0], 1)] = w; }
     return;
   }
   const float* com = d.subtree_com + (size_t)w * nb * 3;
@@ -81,6 +81,29 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
   __syncwarp();
   const size_t row0 = (size_t)w * njmax;
   int nefc = 0;
+  // ---- dof friction loss (mj_instantiateFriction): one row per dof with frictionloss > 0, J = e_dof, pos = margin = 0,
+  // default solreffriction / solimpfriction; these rows come first
+  if (m.fric && !(m.disableflags & B2S_DSBL_FRICTIONLOSS)) {
+    const float* floss = m.dof_frictionloss.at(w);
+    const float* qvel = d.qvel + (size_t)w * nv;
+    const float si[5] = {0.9f, 0.95f, 0.001f, 0.5f, 2.0f};
+    for (int base = 0; base < nv; base += 32) {
+      const int i = base + lane;
+      const bool act = i < nv && floss[i] > 0.f;
+      const unsigned mask = __ballot_sync(FULL, act);
+      const int r = nefc + __popc(mask & ((1u << lane) - 1u));
+      if (act && r < njmax) {
+        float* g = d.efc_g + (row0 + r) * 6;
+        g[0] = 1.f; g[1] = g[2] = g[3] = g[4] = g[5] = 0.f;
+        d.efc_bp[row0 + r] = -1 - i;
+        d.efc_type[row0 + r] = EFC_FRICTION_DOF; d.efc_id[row0 + r] = i;
+        d.efc_frictionloss[row0 + r] = floss[i];
+        finish_row(m, d, row0 + r, 0.f, 0.f, qvel[i], 0.02f, 1.0f, si, m.dof_invweight0[i], 1.f);
+      }
+      nefc = min(nefc + __popc(mask), njmax);
+    }
+  }
+  if (lane == 0) d.nf[w] = nefc;
   // ---- joint limits
   if (!(m.disableflags & B2S_DSBL_LIMIT)) {
     const float* range = m.jnt_range.at(w);

@@ -37,19 +37,19 @@ extern __shared__ float b2s_smem[];
 __host__ __device__ inline int solve_scratch_floats(int nb) { return 6 * (nb > 32 ? nb : 32) + 32 + 32; }
 __host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      // offset of the scratch area
   const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
-  return (HF + 10 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
+  return (HF + 12 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
 }
 __host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T) {
   return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + 3) & ~3;
 }
 
 // Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
-//   H hdim*ld | invd 7T (padded to a float4 multiple) | 10 vectors of NVP | cdof 6*hdim | Jaref, Jv, D njmax each |
+//   H hdim*ld | invd 7T (padded to a float4 multiple) | 12 vectors of NVP | cdof 6*hdim | Jaref, Jv, D njmax each |
 //   run list nconmax+2 | active-set bit mask njmax/32 | scratch X/Y 6*max(nb,32), KW 32, Li 32
 template <int T>
 struct SolveCtx {
-  static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 10 * NVP + 6 * N;
-  int lane, nv, nvp, nb, nefc, nl, nrun, njmax, nconmax, soff;
+  static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 12 * NVP + 6 * N;
+  int lane, nv, nvp, nb, nefc, nl, nf, nrun, njmax, nconmax, soff;
   static constexpr int ld = LD, hfloats = HF;
   const float *M, *G, *aref;
   const int* bp;
@@ -66,7 +66,9 @@ struct SolveCtx {
   DEV float* qfc() const { return sm + HF + 7 * NVP; }
   DEV float* gradold() const { return sm + HF + 8 * NVP; }     // CG only
   DEV float* Mgradold() const { return sm + HF + 9 * NVP; }    // CG only
-  DEV float* cdof() const { return sm + HF + 10 * NVP; }
+  DEV float* fl() const { return sm + HF + 10 * NVP; }         // friction-loss rows: f of row r < nf
+  DEV float* frf() const { return sm + HF + 11 * NVP; }        // and R f = f / D, the half width of the quadratic zone
+  DEV float* cdof() const { return sm + HF + 12 * NVP; }
   DEV float* Jaref() const { return sm + FIX; }
   DEV float* Jv() const { return sm + FIX + njmax; }
   DEV float* D() const { return sm + FIX + 2 * njmax; }
@@ -139,23 +141,48 @@ DEV float gauss_term(const SolveCtx<T>& c) {
   for (int i = c.lane; i < c.nv; i += 32) g += (c.Ma()[i] - c.qfs()[i]) * (c.qacc()[i] - c.qas()[i]);
   return 0.5f * warp_sum(g);
 }
-template <int T>
+// Zone of row r at residual x: 0 inactive, 1 quadratic (the active set of the Hessian), and for friction-loss rows
+// (r < nf, only in the FRIC instantiation) 2 / 3 = saturated at force +f / -f outside |x| < R f (mj_constraintUpdate)
+template <int T, bool FRIC>
+DEV int row_zone(const SolveCtx<T>& c, int r, float x) {
+  if (FRIC && r < c.nf) { const float rf = c.frf()[r]; return x <= -rf ? 2 : (x >= rf ? 3 : 1); }
+  return x < 0.f ? 1 : 0;
+}
+template <int T, bool FRIC>
+DEV float row_force(const SolveCtx<T>& c, int r, float x) {
+  const int z = row_zone<T, FRIC>(c, r, x);
+  if (FRIC && z >= 2) return z == 2 ? c.fl()[r] : -c.fl()[r];
+  return z == 1 ? -c.D()[r] * x : 0.f;
+}
+template <int T, bool FRIC>
 DEV float constraint_cost(const SolveCtx<T>& c, const float* jar) {
   float s = 0.f;
   ROLL
-  for (int r = c.lane; r < c.nefc; r += 32) { const float x = jar[r]; if (x < 0.f) s += 0.5f * c.D()[r] * x * x; }
+  for (int r = c.lane; r < c.nefc; r += 32) {
+    const float x = jar[r];
+    const int z = row_zone<T, FRIC>(c, r, x);
+    if (z == 1) s += 0.5f * c.D()[r] * x * x;
+    else if (FRIC && z >= 2) s += -c.fl()[r] * (0.5f * c.frf()[r] + (z == 2 ? x : -x));
+  }
   return warp_sum(s);
 }
 struct LsPoint { float alpha, cost, d0, d1; };
 // arguments of the exact (iterative) line search, passed BY VALUE so that this cold, out-of-line path does not
 // force the solver context into local memory
-struct LsArgs { const float *Jaref, *Jv, *D, *search; int nefc, nv, lane, maxit; float gtol_unit, q0, q1, q2; };
+struct LsArgs { const float *Jaref, *Jv, *D, *search, *fl, *frf; int nefc, nf, nv, lane, maxit; float gtol_unit, q0, q1, q2; };
 __device__ __noinline__ LsPoint ls_eval(const LsArgs a, float alpha) {
   float q0 = 0.f, q1 = 0.f, q2 = 0.f;
 #pragma unroll 1
   for (int r = a.lane; r < a.nefc; r += 32) {
-    const float ja = a.Jaref[r], jv = a.Jv[r];
-    if (ja + alpha * jv < 0.f) { const float D = a.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
+    const float ja = a.Jaref[r], jv = a.Jv[r], x = ja + alpha * jv;
+    if (r < a.nf) {       // friction-loss row (nf == 0 unless the model has joint friction)
+      const float f = a.fl[r], rf = a.frf[r];
+      if (x <= -rf) { q0 += f * (-0.5f * rf - ja); q1 += -f * jv; continue; }
+      if (x >= rf) { q0 += f * (-0.5f * rf + ja); q1 += f * jv; continue; }
+      const float D = a.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv;
+      continue;
+    }
+    if (x < 0.f) { const float D = a.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
   }
   q0 = warp_sum(q0) + a.q0; q1 = warp_sum(q1) + a.q1; q2 = warp_sum(q2) + a.q2;
   LsPoint p;
@@ -206,7 +233,7 @@ __device__ __noinline__ float ls_iterative(const LsArgs a) {
 // one lane per candidate step: alpha_k = min_step^(k/(n-1)), k = 0..n-1, and alpha = 0 on one more lane; rows are
 // summed in row order by every lane (same order as the oracle), the best candidate wins (ties: alpha = 0, then
 // the smallest k), so a step is only taken if it strictly improves on alpha = 0
-template <int T>
+template <int T, bool FRIC>
 DEV float ls_parallel(const SolveCtx<T>& c, const ModelDev& m, const float* qg) {
   const int n = m.ls_iterations;
   const float lg = logf(m.ls_parallel_min_step);
@@ -218,7 +245,9 @@ DEV float ls_parallel(const SolveCtx<T>& c, const ModelDev& m, const float* qg) 
       float q0 = qg[0], q1 = qg[1], q2 = qg[2];
       for (int r = 0; r < c.nefc; r++) {
         const float ja = c.Jaref()[r], jv = c.Jv()[r];
-        if (ja + alpha * jv < 0.f) { const float D = c.D()[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
+        const int z = row_zone<T, FRIC>(c, r, ja + alpha * jv);
+        if (z == 1) { const float D = c.D()[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
+        else if (FRIC && z >= 2) { const float f = c.fl()[r], sg = z == 2 ? -1.f : 1.f; q0 += f * (-0.5f * c.frf()[r] + sg * ja); q1 += sg * f * jv; }
       }
       const float cost = alpha * alpha * q2 + alpha * q1 + q0;
       const int kk = k == n ? -1 : k;
@@ -333,7 +362,7 @@ DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, b
 
 // Forces / active set from Jaref, qfrc_constraint = J^T f, and (withH) J^T D J into the (zeroed) lower triangle
 // of H in shared memory; M is added when the tiles are loaded for the factorisation.
-template <int T>
+template <int T, bool FRIC>
 DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, int ib) {
   __syncwarp();
   ROLL
@@ -348,11 +377,12 @@ DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, i
   ROLL
   for (int r = c.lane; r < c.nl; r += 32) {
     const float jar = c.Jaref()[r];
-    if (jar < 0.f) {
-      const float De = c.D()[r], g0 = c.G[(size_t)r * 6];
+    const int z = row_zone<T, FRIC>(c, r, jar);
+    if (z) {
+      const float g0 = c.G[(size_t)r * 6];
       const int dof = -1 - c.bp[r];
-      atomicAdd(&c.qfc()[dof], -g0 * De * jar);
-      if (withH) atomicAdd(&c.H()[dof * c.ld + dof], De);
+      atomicAdd(&c.qfc()[dof], g0 * row_force<T, FRIC>(c, r, jar));
+      if (withH && z == 1) atomicAdd(&c.H()[dof * c.ld + dof], c.D()[r]);
     }
   }
   __syncwarp();
@@ -381,13 +411,13 @@ DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, i
 // call.  H = M + J^T D J depends on the state only through this set (pyramidal cones: D is fixed per row), so an
 // unchanged set means the factor of the previous iteration is still the factor of H (MuJoCo's Newton solver also
 // refactors only on a change of the active set).
-template <int T>
+template <int T, bool FRIC>
 DEV bool active_set_unchanged(const SolveCtx<T>& c) {
   bool same = true;
   ROLL
   for (int base = 0; base < c.nefc; base += 32) {
     const int r = base + c.lane;
-    const unsigned mk = __ballot_sync(FULL, r < c.nefc && c.Jaref()[r] < 0.f);
+    const unsigned mk = __ballot_sync(FULL, r < c.nefc && row_zone<T, FRIC>(c, r, c.Jaref()[r]) == 1);
     same &= c.amask()[base >> 5] == mk;
     __syncwarp();
     if (c.lane == 0) c.amask()[base >> 5] = mk;
@@ -428,7 +458,7 @@ DEV void factor_H(const SolveCtx<T>& c, int bi, int bj) {
   tile_cholesky_regs<T>(a, bi, bj, c.H(), c.ld, c.invd());
 }
 
-template <int T>
+template <int T, bool FRIC>
 __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // worlds are taken from the cost-ordered queues, most expensive class first (k_constraint filled them)
@@ -442,7 +472,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   }
   const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
   SolveCtx<T> c;
-  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.njmax = njmax; c.nconmax = d.nconmax;
+  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.nf = FRIC ? d.nf[w] : 0; c.njmax = njmax; c.nconmax = d.nconmax;
   c.soff = solve_soff(njmax, d.nconmax, T);
   c.M = d.qM + (size_t)w * nv * nvp;
   c.G = d.efc_g + (size_t)w * njmax * 6;
@@ -483,6 +513,13 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     }
 #pragma unroll 1
     for (int r = lane; r < c.nefc; r += 32) c.D()[r] = d.efc_D[(size_t)w * njmax + r];
+    if (FRIC) {
+#pragma unroll 1
+      for (int r = lane; r < c.nf; r += 32) {
+        const float f = d.efc_frictionloss[(size_t)w * njmax + r];
+        c.fl()[r] = f; c.frf()[r] = f / d.efc_D[(size_t)w * njmax + r];
+      }
+    }
   }
   // runs of contact rows that share a body pair (fixed for the whole solve), in row order
   {
@@ -512,7 +549,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   for (int pass = warm ? 0 : 1; pass < 2; pass++) {
     const float* x = (pass == 0 || !warm) ? c.qas() : c.search();
     mat_vec_J(c, m, x, c.aref, c.Jv());
-    float cst = constraint_cost(c, c.Jv());
+    float cst = constraint_cost<T, FRIC>(c, c.Jv());
     mat_vec_M(c, x, c.Mv());
     __syncwarp();
     float g = 0.f;
@@ -546,8 +583,8 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
 #pragma unroll 1
   while (true) {
     // the factor in shared memory stays valid while the active set does not change
-    const bool reuse = (active_set_unchanged(c) && haveL) || !newton;
-    assemble(c, m, withH && !reuse, ia, ib);
+    const bool reuse = (active_set_unchanged<T, FRIC>(c) && haveL) || !newton;
+    assemble<T, FRIC>(c, m, withH && !reuse, ia, ib);
     if (!withH) break;
     float gn = 0.f;
 #pragma unroll 1
@@ -584,10 +621,10 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     for (int i = lane; i < nv; i += 32) { g1 += c.search()[i] * (c.Ma()[i] - c.qfs()[i]); g2 += c.search()[i] * c.Mv()[i]; }
     float qg[3] = {gauss, warp_sum(g1), 0.5f * warp_sum(g2)};
     float alpha;
-    if (m.ls_parallel) alpha = ls_parallel(c, m, qg);
+    if (m.ls_parallel) alpha = ls_parallel<T, FRIC>(c, m, qg);
     else {
       LsArgs la;
-      la.Jaref = c.Jaref(); la.Jv = c.Jv(); la.D = c.D(); la.search = c.search(); la.nefc = c.nefc; la.nv = nv; la.lane = lane;
+      la.Jaref = c.Jaref(); la.Jv = c.Jv(); la.D = c.D(); la.search = c.search(); la.nefc = c.nefc; la.nf = c.nf; la.fl = c.fl(); la.frf = c.frf(); la.nv = nv; la.lane = lane;
       la.maxit = m.ls_iterations; la.gtol_unit = m.tolerance * m.ls_tolerance * m.meaninertia * (float)max(nv, 1);
       la.q0 = qg[0]; la.q1 = qg[1]; la.q2 = qg[2];
       alpha = ls_iterative(la);
@@ -600,7 +637,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     __syncwarp();
     const float old = cost;
     gauss = gauss_term(c);
-    cost = constraint_cost(c, c.Jaref()) + gauss;
+    cost = constraint_cost<T, FRIC>(c, c.Jaref()) + gauss;
     iter++;
     if (scale * (old - cost) < m.tolerance) withH = false;     // converged: one more pass for the final forces only
   }
@@ -608,7 +645,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
 #pragma unroll 1
   for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qacc()[i]; g_qfc[i] = c.qfc()[i]; }
 #pragma unroll 1
-  for (int r = lane; r < c.nefc; r += 32) { const float jar = c.Jaref()[r]; efc_force[r] = jar < 0.f ? -c.D()[r] * jar : 0.f; }
+  for (int r = lane; r < c.nefc; r += 32) efc_force[r] = row_force<T, FRIC>(c, r, c.Jaref()[r]);
   if (lane == 0) { d.solver_niter[w] = iter; d.solver_cost[w] = cost; }
 }
 
@@ -625,10 +662,13 @@ static int tile_for(int nv) { return b2s_tile_for(nv); }
     default: { constexpr int T = 8; EXPR_T; } break;            \
   }
 
+// the friction-loss instantiation is only used by models that can have such rows (ModelDev::fric): the default kernel
+// carries none of that code
 void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + SOLVE_WARPS - 1) / SOLVE_WARPS;
   const size_t smem = smem_solve(m, d);
-  SOLVE_DISPATCH((k_solve<T><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d)));
+  if (m.fric) { SOLVE_DISPATCH((k_solve<T, true><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  else { SOLVE_DISPATCH((k_solve<T, false><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   b2s_count_launch();
 }
 size_t smem_solve(const ModelDev& m, const DataDev& d) {
@@ -636,6 +676,7 @@ size_t smem_solve(const ModelDev& m, const DataDev& d) {
 }
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;
-  SOLVE_DISPATCH((f = (const void*)k_solve<T>));
+  if (m.fric) { SOLVE_DISPATCH((f = (const void*)k_solve<T, true>)); }
+  else { SOLVE_DISPATCH((f = (const void*)k_solve<T, false>)); }
   return f;
 }

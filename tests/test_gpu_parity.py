@@ -48,6 +48,7 @@ def _check_counts(D, worlds):
   assert ncon.tolist() == [int(w["ncon"][0]) for w in worlds]
   assert nefc.tolist() == [int(w["nefc"][0]) for w in worlds]
   assert nl.tolist() == [int(w["nl"][0]) for w in worlds]
+  assert D.nf.cpu().numpy().tolist() == [int(w["nf"][0]) for w in worlds]
   geom = D.contact_geom.cpu().numpy()
   dim = D.contact_dim.cpu().numpy()
   adr = D.contact_efc_address.cpu().numpy()
@@ -490,7 +491,7 @@ def test_g1_friction_domain_randomisation_per_world(g1):
 
 
 @pytest.mark.parametrize("name", ["SPHERE_DROP", "FALLING_BOX", "PENDULUM", "SLIDER_PD", "SPINNER", "TWO_SPHERES",
-                                  "CAPSULE_ON_PLANE", "LIMITED_HINGE", "LEGGED", "SENSOR_ARM"])
+                                  "CAPSULE_ON_PLANE", "LIMITED_HINGE", "LEGGED", "SENSOR_ARM", "SLIDER_FRICTION"])
 def test_small_fixtures_rollout(name):
   """Every joint type, primitive pair and sensor of the small fixtures, 200 steps, both sides from the same seed."""
   import torch
@@ -575,7 +576,7 @@ def test_unsupported_features_raise():
   with pytest.raises(engine.BackendError, match="PGS"):
     engine.put_model(m)
   m.opt.solver = 2
-  m.dof_frictionloss = m.dof_frictionloss + 0.1
+  m.dof_frictionloss = m.dof_frictionloss - 0.1
   with pytest.raises(engine.BackendError, match="frictionloss"):
     engine.put_model(m)
   cyl = fx.compile_xml(fx.FALLING_BOX)
@@ -764,3 +765,48 @@ def test_simulation_config_is_piped_like_the_reference_test():
   torch.cuda.synchronize()
   assert torch.allclose(sim.data.qpos[:, 2], torch.full((3,), 1.0 + 7.5 * 0.02 ** 2 * 15, device="cuda:0"), atol=1e-5)
   assert float(sim.data.time[0]) == pytest.approx(0.1)
+
+
+@pytest.mark.gpu
+def test_joint_friction_loss_matches_oracle_and_domain_randomisation(g1):
+  """Friction-loss rows (K8) and the solver's saturated zones (K13): the closed forms of the oracle KAT on the GPU, then
+  `dof_frictionloss` randomised per world on the G1 through expand_model_fields (reference events.py:231) against
+  per-world oracles -- the field switches the friction-aware solver instantiation on."""
+  import torch
+  from asimov_mjlab_b200.hostmodel import HostData
+  m = fx.compile_xml(fx.SLIDER_FRICTION)
+  qv = np.zeros((4, m.nv)); qv[3, 0] = 1.5
+  engine, M, D, orc, worlds = _setup(m, 4, None, qv, None, True, nconmax=4, njmax=16)
+  F = [1.0, 5.0, -5.0, 0.0]
+  for w in range(4):
+    D.qfrc_applied[w, 0] = F[w]; worlds[w]["qfrc_applied"][0] = F[w]
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  _check_counts(D, worlds)
+  qa = D.qacc.cpu().numpy()
+  assert np.allclose(qa[:, 0], [0.1, 3.0, -3.0, -2.0], rtol=2e-5)
+  assert _rel_err(D, worlds, "qacc") < 1e-4 and _rel_err(D, worlds, "efc_force") < 1e-4
+  # G1 with per-world joint friction
+  W = 8
+  qpos, qvel, ctrl = g1_states(g1, W, seed=11)
+  engine, M, D, _, _ = _setup(g1, W, qpos, qvel, ctrl, True)
+  engine.expand_model_fields(M, W, ["dof_frictionloss"])
+  rng = np.random.default_rng(3)
+  fl = np.zeros((W, g1.nv)); fl[:, 6:] = rng.uniform(0.0, 0.5, (W, g1.nv - 6)) * (rng.random((W, g1.nv - 6)) < 0.7)
+  M.dof_frictionloss[:] = torch.as_tensor(fl, dtype=torch.float32, device="cuda:0")
+  from oracle import Oracle
+  worlds = []
+  for w in range(W):
+    o = Oracle(g1, "f32", D.nconmax, D.njmax, overrides={"dof_frictionloss": fl[w]}, ls_parallel=1)
+    ww = o.new_world(qpos[w], qvel[w], ctrl[w]); o.forward(ww); worlds.append((o, ww))
+  engine.forward(M, D)
+  ws = [ww for _, ww in worlds]
+  _check_counts(D, ws)
+  assert D.nf.cpu().numpy().tolist() == [int((fl[w] > 0).sum()) for w in range(W)] and D.nf.max() > 10
+  assert _rel_err(D, ws, "qacc") < 1e-3 and _rel_err(D, ws, "qfrc_constraint") < 1e-3
+  engine.step(M, D, 10)
+  for o, ww in worlds:
+    o.step(ww, 10)
+  _check_counts(D, ws)
+  assert _rel_err(D, ws, "qpos") < 2e-4 and _rel_err(D, ws, "qvel") < 2e-2
