@@ -25,6 +25,7 @@ def main():
   ap.add_argument("--warmup", type=int, default=2)
   ap.add_argument("--steps-per-env", type=int, default=24)
   ap.add_argument("--seed", type=int, default=0)
+  ap.add_argument("--task", default="velocity", choices=["velocity", "tracking"], help="G1 velocity-flat or G1 tracking-flat (synthetic motion)")
   ap.add_argument("--log", action="store_true", help="rank 0 prints the training statistics of every iteration to stderr")
   a = ap.parse_args()
   rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -34,7 +35,11 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
   from .ppo import PPO
   from .velocity_env import G1VelocityFlatEnv
-  env = G1VelocityFlatEnv(a.envs, str(dev), seed=a.seed + rank)           # per-rank seed = seed + rank (utils/random.py:9-26)
+  if a.task == "tracking":
+    from .tracking_env import G1TrackingFlatEnv
+    env = G1TrackingFlatEnv(a.envs, str(dev), seed=a.seed + rank)
+  else:
+    env = G1VelocityFlatEnv(a.envs, str(dev), seed=a.seed + rank)         # per-rank seed = seed + rank (utils/random.py:9-26)
   algo = PPO(env, dev, steps_per_env=a.steps_per_env, seed=a.seed)
   ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
   t_roll = t_upd = 0.0
@@ -65,7 +70,7 @@ def main():
       "n_gpus": world, "envs_per_gpu": a.envs, "iters": a.iters, "steps_per_env": a.steps_per_env,
       "rollout_ms_per_iter": float(t[0]) / a.iters, "update_ms_per_iter": float(t[1]) / a.iters,
       "rollout_env_steps_per_s": steps / (float(t[0]) * 1e-3), "train": {**info, **stats},
-      "config": {"workload": "Mjlab-Velocity-Flat-Unitree-G1, PPO (rsl_rl hyper-parameters), whole env step in one CUDA graph",
+      "config": {"workload": ("Mjlab-Tracking-Flat-Unitree-G1 (synthetic motion)" if a.task == "tracking" else "Mjlab-Velocity-Flat-Unitree-G1") + ", PPO (rsl_rl hyper-parameters), whole env step in one CUDA graph",
                  "parallelism": f"env-shard x{world}; NCCL: gradient all-reduce per mini-batch, normaliser / KL / statistics reductions"}}), flush=True)
   if world > 1:
     dist.destroy_process_group()
