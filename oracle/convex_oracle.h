@@ -14,12 +14,13 @@
 #ifndef CONVEX_ORACLE_H
 #define CONVEX_ORACLE_H
 
-enum { CVX_POINT = 0, CVX_SEGMENT = 1, CVX_BOX = 2, CVX_VERTS = 3 };
+enum { CVX_POINT = 0, CVX_SEGMENT = 1, CVX_BOX = 2, CVX_VERTS = 3, CVX_CYLINDER = 4, CVX_ELLIPSOID = 5 };
 typedef struct {
   int type;
   real pos[3];
   real mat[9];
-  real size[3];        /* SEGMENT: size[1] = half length along local z; BOX: half sizes */
+  real size[3];        /* SEGMENT: size[1] = half length along local z; BOX: half sizes; CYLINDER: radius, half height (z);
+                          ELLIPSOID: the three radii */
   const double* vert;  /* VERTS: model vertices (double, local frame) ... */
   const real* vertr;   /* ... or `real` vertices already in the world frame when mat is unused (prisms) */
   int nvert;
@@ -45,7 +46,15 @@ static void cvx_support(const cvx* s, const real* dir, real* out) {
   matT_vec(dl, s->mat, dir);
   if (s->type == CVX_SEGMENT) { loc[0] = 0; loc[1] = 0; loc[2] = dl[2] >= 0 ? s->size[1] : -s->size[1]; }
   else if (s->type == CVX_BOX) { for (int k = 0; k < 3; k++) loc[k] = dl[k] >= 0 ? s->size[k] : -s->size[k]; }
-  else {
+  else if (s->type == CVX_CYLINDER) {      /* rim point of the cap facing dir */
+    real h = (real)sqrt((double)(dl[0]*dl[0] + dl[1]*dl[1]));
+    loc[0] = h > MINVAL ? s->size[0]*dl[0]/h : 0; loc[1] = h > MINVAL ? s->size[0]*dl[1]/h : 0;
+    loc[2] = dl[2] >= 0 ? s->size[1] : -s->size[1];
+  } else if (s->type == CVX_ELLIPSOID) {   /* S^2 d / |S d| */
+    real e[3] = {s->size[0]*dl[0], s->size[1]*dl[1], s->size[2]*dl[2]};
+    real h = (real)sqrt((double)dot3(e, e));
+    for (int k = 0; k < 3; k++) loc[k] = h > MINVAL ? s->size[k]*e[k]/h : (k == 0 ? s->size[0] : 0);
+  } else {
     int best = 0; real bd = (real)s->vert[0]*dl[0] + (real)s->vert[1]*dl[1] + (real)s->vert[2]*dl[2];
     for (int i = 1; i < s->nvert; i++) {
       real t = (real)s->vert[3*i]*dl[0] + (real)s->vert[3*i + 1]*dl[1] + (real)s->vert[3*i + 2]*dl[2];
@@ -314,6 +323,8 @@ static void cvx_from_geom(const b2s_model_desc* m, const orc_data* d, int g, cvx
   if (t == B2S_GEOM_SPHERE) { s->type = CVX_POINT; s->radius = s->size[0]; }
   else if (t == B2S_GEOM_CAPSULE) { s->type = CVX_SEGMENT; s->radius = s->size[0]; }
   else if (t == B2S_GEOM_BOX) s->type = CVX_BOX;
+  else if (t == B2S_GEOM_CYLINDER) s->type = CVX_CYLINDER;
+  else if (t == B2S_GEOM_ELLIPSOID) s->type = CVX_ELLIPSOID;
   else {  /* mesh */
     int id = m->geom_dataid[g];
     s->type = CVX_VERTS; s->vert = m->mesh_vert + 3*m->mesh_vertadr[id]; s->nvert = m->mesh_vertnum[id];
@@ -331,6 +342,44 @@ static int col_convex(rawcon* c, real margin, const cvx* A, const cvx* B) {
     c->pos[k] = (real)0.5*(sa + sb); c->frame[k] = r.n[k]; c->frame[3 + k] = 0;
   }
   return 1;
+}
+
+/* plane - ellipsoid: the support point against the plane normal (one contact) */
+static int col_plane_ellipsoid(rawcon* c, real margin, const real* ppos, const real* pmat, const cvx* E) {
+  real n[3] = {pmat[2], pmat[5], pmat[8]}, nn[3] = {-n[0], -n[1], -n[2]}, sp[3];
+  cvx_support(E, nn, sp);
+  real dif[3] = {sp[0] - ppos[0], sp[1] - ppos[1], sp[2] - ppos[2]};
+  real dist = dot3(dif, n);
+  if (dist > margin) return 0;
+  c->dist = dist;
+  for (int k = 0; k < 3; k++) { c->pos[k] = sp[k] - n[k]*(real)0.5*dist; c->frame[k] = n[k]; c->frame[3 + k] = 0; }
+  return 1;
+}
+/* plane - cylinder (own formulation, up to 4 contacts in a fixed order): u = the radial direction that points into the
+ * plane; 0: rim point along u of the cap nearer to the plane, 1: the same on the other cap (a cylinder on its side),
+ * 2, 3: rim points of the nearer cap at +-120 degrees from u (a cylinder standing on a cap).  Each is kept if its own
+ * distance is within the margin.  When the axis is normal to the plane u is the local x axis. */
+static int col_plane_cylinder(rawcon* c, real margin, const real* ppos, const real* pmat, const real* cpos, const real* cmat, const real* size) {
+  real n[3] = {pmat[2], pmat[5], pmat[8]}, ax[3] = {cmat[2], cmat[5], cmat[8]}, ex[3] = {cmat[0], cmat[3], cmat[6]};
+  real r = size[0], h = size[1];
+  real an = dot3(ax, n), u[3], ul;
+  for (int k = 0; k < 3; k++) u[k] = -(n[k] - an*ax[k]);
+  ul = (real)sqrt((double)dot3(u, u));
+  if (ul > (real)1e-6) { for (int k = 0; k < 3; k++) u[k] /= ul; } else { for (int k = 0; k < 3; k++) u[k] = ex[k]; }
+  real sgn = an > 0 ? (real)-1 : (real)1;      /* cap whose centre is nearer to the plane */
+  real v[3]; cross3(v, ax, u);
+  const real cs[4] = {1, 1, (real)-0.5, (real)-0.5}, sn[4] = {0, 0, (real)0.8660254037844386, (real)-0.8660254037844386};
+  int cnt = 0;
+  for (int i = 0; i < 4; i++) {
+    real cap = i == 1 ? -sgn : sgn, p[3], dif[3];
+    for (int k = 0; k < 3; k++) { p[k] = cpos[k] + cap*h*ax[k] + r*(cs[i]*u[k] + sn[i]*v[k]); dif[k] = p[k] - ppos[k]; }
+    real dist = dot3(dif, n);
+    if (dist > margin) continue;
+    c[cnt].dist = dist;
+    for (int k = 0; k < 3; k++) { c[cnt].pos[k] = p[k] - n[k]*(real)0.5*dist; c[cnt].frame[k] = n[k]; c[cnt].frame[3 + k] = 0; }
+    cnt++;
+  }
+  return cnt;
 }
 
 /* plane - mesh: vertices within 1 mm of the deepest one form the candidate set; up to 4 of them span the manifold

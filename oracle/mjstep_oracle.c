@@ -746,10 +746,14 @@ void orc_collision(const b2s_model_desc* m, orc_data* d) {
     else if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_MESH) {
       int id = m->geom_dataid[g2];
       n = col_plane_mesh(rc, margin, p1, m1, p2, m2, m->mesh_vert + 3*m->mesh_vertadr[id], m->mesh_vertnum[id]);
-    } else if (t1 == B2S_GEOM_HFIELD && t2 >= B2S_GEOM_SPHERE && t2 != B2S_GEOM_ELLIPSOID && t2 != B2S_GEOM_CYLINDER) {
+    } else if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_CYLINDER) n = col_plane_cylinder(rc, margin, p1, m1, p2, m2, s2);
+    else if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_ELLIPSOID) { cvx B; cvx_from_geom(m, d, g2, &B); n = col_plane_ellipsoid(rc, margin, p1, m1, &B); }
+    else if (t1 == B2S_GEOM_HFIELD && t2 >= B2S_GEOM_SPHERE) {
       cvx B; cvx_from_geom(m, d, g2, &B);
       n = col_hfield(rc, 8, margin, m, m->geom_dataid[g1], p1, m1, &B, (real)m->geom_rbound[g2]);
-    } else if (t2 == B2S_GEOM_MESH && t1 >= B2S_GEOM_SPHERE && t1 != B2S_GEOM_ELLIPSOID && t1 != B2S_GEOM_CYLINDER) {
+    } else if (t1 >= B2S_GEOM_SPHERE && (t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_ELLIPSOID || t1 == B2S_GEOM_CYLINDER ||
+                                         t2 == B2S_GEOM_ELLIPSOID || t2 == B2S_GEOM_CYLINDER)) {
+      /* every pair with a mesh, a cylinder or an ellipsoid goes through GJK / EPA (one contact) */
       cvx A, B; cvx_from_geom(m, d, g1, &A); cvx_from_geom(m, d, g2, &B);
       n = col_convex(rc, margin, &A, &B);
     }

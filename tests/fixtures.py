@@ -96,6 +96,31 @@ SLIDER_FRICTION = """
 </mujoco>
 """
 
+# free cylinder, ellipsoid and sphere over a plane and a static box (cylinder / ellipsoid colliders: analytic against the
+# plane, GJK / EPA against everything else)
+ROUND_SHAPES = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.005" integrator="implicitfast"/>
+  <worldbody>
+    <geom name="floor" type="plane" size="5 5 0.1"/>
+    <geom name="block" type="box" pos="1.0 0 0.1" size="0.3 0.3 0.1"/>
+    <body name="cyl" pos="0 0 0.5">
+      <freejoint name="cyl_free"/>
+      <geom name="cyl_geom" type="cylinder" size="0.1 0.15" mass="1.0"/>
+    </body>
+    <body name="ell" pos="0 1 0.5">
+      <freejoint name="ell_free"/>
+      <geom name="ell_geom" type="ellipsoid" size="0.1 0.15 0.2" mass="2.0"/>
+    </body>
+    <body name="ball" pos="0 2 0.5">
+      <freejoint name="ball_free"/>
+      <geom name="ball_geom" type="sphere" size="0.05" mass="0.2"/>
+    </body>
+  </worldbody>
+</mujoco>
+"""
+
 SPINNER = """
 <mujoco>
   <compiler angle="radian"/>

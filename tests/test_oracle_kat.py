@@ -473,3 +473,78 @@ def test_joint_friction_loss_closed_forms():
   w = orc.new_world(None, np.array([1.5, 0, 0, 0.0]), None)
   orc.step(w, 400)
   assert abs(w["qvel"][0]) < 1e-6 and abs(w["qpos"][0] - 1.5 ** 2 / 4.0) < 5e-3
+
+
+def _round_world(orc, m, cyl=None, ell=None, ball=None):
+  q = np.array(m.qpos0, float).copy()
+  for i, v in enumerate((cyl, ell, ball)):
+    if v is not None:
+      q[7 * i:7 * i + len(v)] = v
+  w = orc.new_world(q)
+  orc.stage("kinematics", w); orc.stage("com_pos", w); orc.stage("collision", w)
+  return w
+
+
+def test_cylinder_and_ellipsoid_contact_geometry():
+  """Closed forms for the round shapes: a cylinder standing on the plane touches at three rim points 120 degrees apart,
+  lying on its side at one rim point per cap; an ellipsoid touches at the support point of -n; a sphere pressed into the
+  cylinder's wall (GJK on the cores) gets dist = gap and the radial normal."""
+  m = fx.compile_xml(fx.ROUND_SHAPES)
+  orc = Oracle(m, "f64", 16, 64)
+  gi = {n: i for i, n in enumerate(m.names["geom"])}
+  def contacts(w, g):
+    n = int(w["ncon"][0])
+    return [(w["con_dist"][c], w["con_pos"][3 * c:3 * c + 3].copy(), w["con_frame"][9 * c:9 * c + 3].copy())
+            for c in range(n) if g in (w["con_geom"][2 * c], w["con_geom"][2 * c + 1])]
+  far = [5, 5, 3.0]
+  # standing cylinder, 1 mm deep
+  w = _round_world(orc, m, cyl=[0, 0, 0.149], ell=far, ball=[-5, 5, 3.0])
+  cs = contacts(w, gi["cyl_geom"])
+  assert len(cs) == 3 and all(abs(c[0] + 0.001) < 1e-12 and np.allclose(c[2], [0, 0, 1]) for c in cs)
+  assert all(abs(np.hypot(c[1][0], c[1][1]) - 0.1) < 1e-12 and abs(c[1][2] + 0.0005) < 1e-12 for c in cs)
+  ang = sorted(np.degrees(np.arctan2(c[1][1], c[1][0])) % 360 for c in cs)
+  assert np.allclose(np.diff(ang), 120.0)
+  # lying on its side (axis along x): one contact under each cap
+  w = _round_world(orc, m, cyl=[0, 0, 0.099, np.sqrt(0.5), 0, np.sqrt(0.5), 0], ell=far, ball=[-5, 5, 3.0])
+  cs = contacts(w, gi["cyl_geom"])
+  assert len(cs) == 2 and all(abs(c[0] + 0.001) < 1e-9 for c in cs)
+  assert sorted(round(c[1][0], 6) for c in cs) == [-0.15, 0.15]
+  # ellipsoid resting on its long axis, 2 mm deep; then tilted: the contact is where the surface normal is -n
+  w = _round_world(orc, m, cyl=far, ell=[0, 1, 0.198], ball=[-5, 5, 3.0])
+  (dist, pos, nrm), = contacts(w, gi["ell_geom"])
+  assert abs(dist + 0.002) < 1e-12 and np.allclose(pos, [0, 1, -0.001]) and np.allclose(nrm, [0, 0, 1])
+  th = 0.6
+  w = _round_world(orc, m, cyl=far, ell=[0, 1, 0.3, np.cos(th / 2), np.sin(th / 2), 0, 0], ball=[-5, 5, 3.0])
+  R = w["geom_xmat"].reshape(-1, 3, 3)[gi["ell_geom"]]
+  S = np.diag([0.1, 0.15, 0.2]); dl = R.T @ np.array([0, 0, -1.0])
+  sup = R @ (S @ S @ dl / np.linalg.norm(S @ dl)) + np.array([0, 1, 0.3])
+  cs = contacts(w, gi["ell_geom"])
+  assert (len(cs) == 1 and abs(cs[0][0] - sup[2]) < 1e-12) if sup[2] < 0 else len(cs) == 0
+  assert sup[2] > 0 or np.allclose(cs[0][1][:2], sup[:2])
+  # sphere pushed 3 mm into the cylinder's wall at mid height: distance between the cores minus the radius
+  w = _round_world(orc, m, cyl=[0, 0, 1.0], ell=far, ball=[0.1 + 0.05 - 0.003, 0, 1.0])
+  (dist, pos, nrm), = contacts(w, gi["ball_geom"])
+  assert abs(dist + 0.003) < 1e-6 and np.allclose(nrm, [-1, 0, 0], atol=1e-5) and np.allclose(pos, [0.0985, 0, 1.0], atol=1e-5)
+  # ... and onto its cap from above
+  w = _round_world(orc, m, cyl=[0, 0, 1.0], ell=far, ball=[0.03, 0.02, 1.15 + 0.05 - 0.002])
+  (dist, pos, nrm), = contacts(w, gi["ball_geom"])
+  assert abs(dist + 0.002) < 1e-6 and np.allclose(nrm, [0, 0, -1], atol=1e-5)
+
+
+def test_round_shapes_settle_with_their_weight():
+  """Dropped from 2 cm, the cylinder (on its cap), the ellipsoid and the sphere come to rest on the plane: contact forces
+  carry the weight, resting heights are the shape's extent along z minus a sub-millimetre penetration."""
+  m = fx.compile_xml(fx.ROUND_SHAPES)
+  orc = Oracle(m, "f64", 16, 64)
+  w = _round_world(orc, m, cyl=[0, 0, 0.17], ell=[0, 1, 0.22], ball=[0, 2, 0.07])
+  orc.step(w, 600)
+  assert np.abs(w["qvel"]).max() < 1e-3
+  assert abs(w["qpos"][2] - 0.15) < 1e-3 and abs(w["qpos"][9] - 0.2) < 1e-3 and abs(w["qpos"][16] - 0.05) < 1e-3
+  n = int(w["ncon"][0])
+  fz = {}
+  for c in range(n):
+    adr, dim = int(w["con_efc_address"][c]), int(w["con_dim"][c])
+    f = sum(w["efc_force"][adr:adr + 2 * (dim - 1)]) if dim > 1 else w["efc_force"][adr]
+    fz[int(w["con_geom"][2 * c + 1])] = fz.get(int(w["con_geom"][2 * c + 1]), 0.0) + f
+  gi = {nm: i for i, nm in enumerate(m.names["geom"])}
+  assert abs(fz[gi["cyl_geom"]] - 1.0 * 9.81) < 0.05 and abs(fz[gi["ell_geom"]] - 2.0 * 9.81) < 0.05 and abs(fz[gi["ball_geom"]] - 0.2 * 9.81) < 0.01
