@@ -95,22 +95,26 @@ const char* geom_name(int t) {
   static const char* n[] = {"plane", "hfield", "sphere", "capsule", "ellipsoid", "cylinder", "box", "mesh"};
   return (t >= 0 && t < 8) ? n[t] : "?";
 }
-bool convex_core(int t) { return t == B2S_GEOM_SPHERE || t == B2S_GEOM_CAPSULE || t == B2S_GEOM_BOX || t == B2S_GEOM_MESH; }
+bool round_geom(int t) { return t == B2S_GEOM_CYLINDER || t == B2S_GEOM_ELLIPSOID; }
+bool convex_core(int t) { return t == B2S_GEOM_SPHERE || t == B2S_GEOM_CAPSULE || t == B2S_GEOM_BOX || t == B2S_GEOM_MESH || round_geom(t); }
 bool pair_supported(int t1, int t2) {
-  if (t1 == B2S_GEOM_PLANE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX || t2 == B2S_GEOM_MESH;
+  if (t1 == B2S_GEOM_PLANE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX || t2 == B2S_GEOM_MESH || round_geom(t2);
   if (t1 == B2S_GEOM_HFIELD) return convex_core(t2);
   if (t2 == B2S_GEOM_MESH) return convex_core(t1);
+  if (round_geom(t1) || round_geom(t2)) return convex_core(t1) && convex_core(t2);
   if (t1 == B2S_GEOM_SPHERE) return t2 == B2S_GEOM_SPHERE || t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
   if (t1 == B2S_GEOM_CAPSULE) return t2 == B2S_GEOM_CAPSULE || t2 == B2S_GEOM_BOX;
   if (t1 == B2S_GEOM_BOX) return t2 == B2S_GEOM_BOX;
   return false;
 }
 // pairs that go through the GJK/EPA, plane-mesh or height-field colliders (k_convex.cuh)
-bool pair_convex(int t1, int t2) { return t1 == B2S_GEOM_HFIELD || t2 == B2S_GEOM_MESH; }
+// (the analytic plane - cylinder / ellipsoid colliders are only compiled into that instantiation too)
+bool pair_convex(int t1, int t2) { return t1 == B2S_GEOM_HFIELD || t2 == B2S_GEOM_MESH || round_geom(t1) || round_geom(t2); }
 // most contacts the narrowphase returns for a (type-ordered) pair
 int pair_max_contacts(int t1, int t2) {
   if (t1 == B2S_GEOM_HFIELD) return 8;
   if (t2 == B2S_GEOM_MESH) return t1 == B2S_GEOM_PLANE ? 4 : 1;
+  if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_CYLINDER) return 4;
   if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) return 8;
   if (t1 == B2S_GEOM_PLANE && t2 == B2S_GEOM_BOX) return 4;
   if (t2 == B2S_GEOM_CAPSULE && (t1 == B2S_GEOM_PLANE || t1 == B2S_GEOM_CAPSULE)) return 2;
@@ -417,7 +421,8 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       bs[0] = bs[1] = bs[2] = brad[g];
       if (t == B2S_GEOM_SPHERE) { bs[0] = bs[1] = bs[2] = (float)sz[0]; }
       else if (t == B2S_GEOM_CAPSULE) { bs[0] = bs[1] = (float)sz[0]; bs[2] = (float)(sz[0] + sz[1]); }
-      else if (t == B2S_GEOM_BOX) { bs[0] = (float)sz[0]; bs[1] = (float)sz[1]; bs[2] = (float)sz[2]; }
+      else if (t == B2S_GEOM_BOX || t == B2S_GEOM_ELLIPSOID) { bs[0] = (float)sz[0]; bs[1] = (float)sz[1]; bs[2] = (float)sz[2]; }
+      else if (t == B2S_GEOM_CYLINDER) { bs[0] = bs[1] = (float)sz[0]; bs[2] = (float)sz[1]; }
       else if (t == B2S_GEOM_MESH && s->geom_dataid[g] >= 0 && s->geom_dataid[g] < s->nmesh) {
         const int id = s->geom_dataid[g], a0 = s->mesh_vertadr[id], nvt = s->mesh_vertnum[id];
         double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};

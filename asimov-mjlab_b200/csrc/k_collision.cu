@@ -181,6 +181,41 @@ DEV int capsule_box(RawCon* c, float margin, v3 p1, const m33& m1, v3 s1, v3 p2,
 }
 // box-box: separating-axis test (15 axes), then a face manifold (incident face clipped against the reference face's
 // side planes, up to 8 points) or one edge-edge contact (oracle: col_box_box).
+// plane - ellipsoid: the support point against the plane normal
+DEV int plane_ellipsoid(RawCon* c, float margin, v3 ppos, const m33& pmat, v3 epos, const m33& emat, v3 size) {
+  const v3 n = col(pmat, 2), dl = mulTv(emat, n * -1.f);
+  const v3 e = mk3(size.x * dl.x, size.y * dl.y, size.z * dl.z);
+  const float h = sqrtf(dot(e, e));
+  const v3 loc = h > B2S_MINVAL ? mk3(size.x * e.x / h, size.y * e.y / h, size.z * e.z / h) : mk3(size.x, 0.f, 0.f);
+  const v3 sp = mulv(emat, loc) + epos;
+  const float dist = dot(sp - ppos, n);
+  if (dist > margin) return 0;
+  c[0].dist = dist; c[0].pos = sp - n * (0.5f * dist); c[0].n = n; c[0].t = mk3(0.f, 0.f, 0.f);
+  return 1;
+}
+// plane - cylinder, up to 4 contacts in a fixed order (oracle col_plane_cylinder): rim point along u (the radial direction
+// into the plane) of the nearer cap, the same on the other cap, rim points of the nearer cap at +-120 degrees from u
+DEV int plane_cylinder(RawCon* c, float margin, v3 ppos, const m33& pmat, v3 cpos, const m33& cmat, v3 size) {
+  const v3 n = col(pmat, 2), ax = col(cmat, 2);
+  const float r = size.x, h = size.y, an = dot(ax, n);
+  v3 u = (n - ax * an) * -1.f;
+  const float ul = sqrtf(dot(u, u));
+  u = ul > 1e-6f ? u * (1.0f / ul) : col(cmat, 0);
+  const float sgn = an > 0.f ? -1.f : 1.f;
+  const v3 v = cross(ax, u);
+  int cnt = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float cap = i == 1 ? -sgn : sgn, cs = i < 2 ? 1.f : -0.5f, sn = i < 2 ? 0.f : (i == 2 ? 0.8660254037844386f : -0.8660254037844386f);
+    const v3 p = cpos + ax * (cap * h) + (u * cs + v * sn) * r;
+    const float dist = dot(p - ppos, n);
+    if (dist > margin) continue;
+#pragma unroll
+    for (int k = 0; k < 4; k++) if (k == cnt) { c[k].dist = dist; c[k].pos = p - n * (0.5f * dist); c[k].n = n; c[k].t = mk3(0.f, 0.f, 0.f); }
+    cnt++;
+  }
+  return cnt;
+}
 DEV int box_box(RawCon* c, float margin, v3 p1, const m33& M1, v3 S1, v3 p2, const m33& M2, v3 S2) {
   const float* m1 = M1.m; const float* m2 = M2.m;
   const float s1[3] = {S1.x, S1.y, S1.z}, s2[3] = {S2.x, S2.y, S2.z};
@@ -323,6 +358,8 @@ DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
   if (t == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = B.size.x; }
   else if (t == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = B.size.x; }
   else if (t == B2S_GEOM_BOX) B.type = CVX_BOX;
+  else if (t == B2S_GEOM_CYLINDER) B.type = CVX_CYLINDER;
+  else if (t == B2S_GEOM_ELLIPSOID) B.type = CVX_ELLIPSOID;
   else { const int id = m.geom_dataid[g]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
   return B;
 }
@@ -459,6 +496,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t2 == B2S_GEOM_SPHERE) n = plane_sphere(rc, margin, p1, col(m1, 2), p2, s2.x);
         else if (t2 == B2S_GEOM_CAPSULE) n = plane_capsule(rc, margin, p1, m1, p2, m2, s2);
         else if (t2 == B2S_GEOM_BOX) { if constexpr (MAXC >= 4) n = plane_box(rc, margin, p1, m1, p2, m2, s2); }
+        else if (t2 == B2S_GEOM_CYLINDER) { if constexpr (CONVEX) n = plane_cylinder(rc, margin, p1, m1, p2, m2, s2); }
+        else if (t2 == B2S_GEOM_ELLIPSOID) { if constexpr (CONVEX) n = plane_ellipsoid(rc, margin, p1, m1, p2, m2, s2); }
       } else if (t1 == B2S_GEOM_SPHERE) {
         if (t2 == B2S_GEOM_SPHERE) n = sphere_sphere(rc, margin, p1, s1.x, p2, s2.x);
         else if (t2 == B2S_GEOM_CAPSULE) n = sphere_capsule(rc, margin, p1, s1, p2, m2, s2);
@@ -467,7 +506,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t2 == B2S_GEOM_CAPSULE) n = capsule_capsule(rc, margin, p1, m1, s1, p2, m2, s2);
         else if (t2 == B2S_GEOM_BOX) n = capsule_box(rc, margin, p1, m1, s1, p2, m2, s2);
       } else if (t1 == B2S_GEOM_BOX && t2 == B2S_GEOM_BOX) { if constexpr (MAXC >= 8) n = box_box(rc, margin, p1, m1, s1, p2, m2, s2); }
-      if constexpr (CONVEX) cvx = (t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_HFIELD);
+      // every pair with a mesh, a height field, a cylinder or an ellipsoid (other than plane - cylinder / ellipsoid) is convex work
+      if constexpr (CONVEX) cvx = t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_HFIELD ||
+                                  (t1 >= B2S_GEOM_SPHERE && (t1 == B2S_GEOM_CYLINDER || t1 == B2S_GEOM_ELLIPSOID || t2 == B2S_GEOM_CYLINDER || t2 == B2S_GEOM_ELLIPSOID));
     }
     if constexpr (CONVEX) {
       // mesh / height-field pairs of this pass, one at a time with the whole warp: hull scans are lane-strided, a
@@ -552,6 +593,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t2 == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = s2.x; }
         else if (t2 == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = s2.x; }
         else if (t2 == B2S_GEOM_BOX) B.type = CVX_BOX;
+        else if (t2 == B2S_GEOM_CYLINDER) B.type = CVX_CYLINDER;
+        else if (t2 == B2S_GEOM_ELLIPSOID) B.type = CVX_ELLIPSOID;
         else { const int id = m.geom_dataid[bg2]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
         int nres;
         if (t1 == B2S_GEOM_PLANE) nres = plane_mesh_warp(s_stage, bm, p1, m1, p2, m2, B.vert, B.nvert, lane);
@@ -564,6 +607,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
           if (t1 == B2S_GEOM_SPHERE) { A.type = CVX_POINT; A.radius = s1.x; }
           else if (t1 == B2S_GEOM_CAPSULE) { A.type = CVX_SEGMENT; A.radius = s1.x; }
           else if (t1 == B2S_GEOM_BOX) A.type = CVX_BOX;
+          else if (t1 == B2S_GEOM_CYLINDER) A.type = CVX_CYLINDER;
+          else if (t1 == B2S_GEOM_ELLIPSOID) A.type = CVX_ELLIPSOID;
           else { const int id = m.geom_dataid[bg1]; A.type = CVX_VERTS; A.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; A.nvert = m.mesh_vertnum[id]; A.coop = true; }
           B.coop = (B.type == CVX_VERTS);
           nres = convex_pair_warp(s_stage, bm, A, B, lane);

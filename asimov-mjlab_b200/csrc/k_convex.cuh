@@ -13,6 +13,8 @@
 #define CVX_SEGMENT 1
 #define CVX_BOX 2
 #define CVX_VERTS 3
+#define CVX_CYLINDER 4      // size.x radius, size.y half height along local z
+#define CVX_ELLIPSOID 5     // size = the three radii
 #define GJK_MAXIT 48
 #define EPA_MAXIT 48
 #define EPA_MAXV 28
@@ -45,7 +47,14 @@ __device__ __noinline__ v3 cvx_support(const Cvx& s, v3 dir) {
   v3 loc;
   if (s.type == CVX_SEGMENT) loc = mk3(0.f, 0.f, dl.z >= 0.f ? s.size.y : -s.size.y);
   else if (s.type == CVX_BOX) loc = mk3(dl.x >= 0.f ? s.size.x : -s.size.x, dl.y >= 0.f ? s.size.y : -s.size.y, dl.z >= 0.f ? s.size.z : -s.size.z);
-  else if (s.coop) {
+  else if (s.type == CVX_CYLINDER) {       // rim point of the cap facing dir
+    const float h = sqrtf(dl.x * dl.x + dl.y * dl.y);
+    loc = mk3(h > B2S_MINVAL ? s.size.x * dl.x / h : 0.f, h > B2S_MINVAL ? s.size.x * dl.y / h : 0.f, dl.z >= 0.f ? s.size.y : -s.size.y);
+  } else if (s.type == CVX_ELLIPSOID) {    // S^2 d / |S d|
+    const v3 e = mk3(s.size.x * dl.x, s.size.y * dl.y, s.size.z * dl.z);
+    const float h = sqrtf(dot(e, e));
+    loc = h > B2S_MINVAL ? mk3(s.size.x * e.x / h, s.size.y * e.y / h, s.size.z * e.z / h) : mk3(s.size.x, 0.f, 0.f);
+  } else if (s.coop) {
     // warp-cooperative scan: lane-strided vertices, then (max value, lowest index) across the warp
     const int lane = threadIdx.x & 31;
     int best = 0x7fffffff; float bd = -3.0e38f;
