@@ -334,7 +334,10 @@ def run_b200(args):
                  "traffic": NCU_TRAFFIC.get((args.workload, E), (None, None))[0], "traffic_source": NCU_TRAFFIC.get((args.workload, E), (None, None))[1],
                  "algorithmic_bytes_per_launch": E * ab,
                  "peak_source": peak_src, "scope": f"whole sub-step (7 stage kernels); algorithmic bytes {ab} B per world per sub-step",
-                 "dominant_kernel": top, "dominant_share": stages[top] / tot, "stage_ms": stages},
+                 "dominant_kernel": top, "dominant_share": stages[top] / tot, "dominant_kernel_ms": stages[top],
+                 # the same algorithmic bytes over the dominant kernel's own launch duration (CUDA events around that launch)
+                 "achieved_over_dominant_kernel_only": E * ab / (stages[top] * 1e-3) / 1e9,
+                 "stage_ms": stages},
     "clocks": clocks,
   }
   if args.cpu_baseline and world == 1:
