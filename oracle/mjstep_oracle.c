@@ -835,6 +835,18 @@ static void finish_row(const b2s_model_desc* m, orc_data* d, int r, const real* 
   d->efc_force[r] = 0;
 }
 
+/* aref of a row without position term: -B vel with B from solref as in finish_row (efc_vel[r] already holds J qvel) */
+static real friction_row_aref(const b2s_model_desc* m, const orc_data* d, int r, const real* solref, const real* solimp) {
+  real B, dmax = solimp[1];
+  if (solref[0] > 0) {
+    real tc = solref[0];
+    if (!(m->opt_disableflags & B2S_DSBL_REFSAFE) && tc < 2*(real)m->opt_timestep) tc = 2*(real)m->opt_timestep;
+    real bd = dmax*tc; if (bd < MINVAL) bd = MINVAL;
+    B = 2/bd;
+  } else { real bd = dmax; if (bd < MINVAL) bd = MINVAL; B = -solref[1]/bd; }
+  return -B*d->efc_vel[r];
+}
+
 void orc_make_constraint(const b2s_model_desc* m, orc_data* d) {
   int nv = m->nv, nefc = 0;
   d->nefc[0] = 0; d->nl[0] = 0; d->nf[0] = 0;
@@ -882,7 +894,8 @@ void orc_make_constraint(const b2s_model_desc* m, orc_data* d) {
     if (m->opt_disableflags & B2S_DSBL_CONTACT) continue;
     if (d->con_dist[c] >= d->con_includemargin[c]) continue;
     int dim = d->con_dim[c];
-    int nrow = dim == 1 ? 1 : 2*(dim - 1);
+    const int elliptic = m->opt_cone == B2S_CONE_ELLIPTIC && dim > 1;
+    int nrow = dim == 1 ? 1 : (elliptic ? dim : 2*(dim - 1));
     if (full || nefc + nrow > d->njmax) { full = 1; continue; }
     int g1 = d->con_geom[2*c], g2 = d->con_geom[2*c + 1];
     int b1 = m->geom_bodyid[g1], b2 = m->geom_bodyid[g2];
@@ -905,6 +918,28 @@ void orc_make_constraint(const b2s_model_desc* m, orc_data* d) {
       d->efc_pos[r] = d->con_dist[c]; d->efc_margin[r] = d->con_includemargin[c];
       d->efc_type[r] = ORC_EFC_CONTACT_FRICTIONLESS; d->efc_id[r] = c;
       finish_row(m, d, r, sr, d->con_solimp + 5*c, tran, 1);
+    } else if (elliptic) {
+      /* elliptic cone (mj_instantiateContact + mj_makeImpedance): rows = the contact-frame axes (normal, tangents, then
+       * torsional / rolling); the friction rows have pos = 0, share the normal row's impedance, and are regularised by
+       * R_1 = R_n / impratio, R_j = R_1 mu_1^2 / mu_j^2; their aref is -B vel */
+      real rot = (real)m->body_invweight0[2*b1 + 1] + (real)m->body_invweight0[2*b2 + 1];
+      int r0 = nefc;
+      for (int k = 0; k < dim; k++) {
+        int r = nefc++;
+        for (int i = 0; i < nv; i++) d->efc_J[r*nv + i] = Jc[k*nv + i];
+        d->efc_pos[r] = d->con_dist[c]; d->efc_margin[r] = d->con_includemargin[c];
+        d->efc_type[r] = ORC_EFC_CONTACT_ELLIPTIC; d->efc_id[r] = c;
+        finish_row(m, d, r, sr, d->con_solimp + 5*c, k < 3 ? tran : rot, 1);
+        if (k > 0) {
+          real mu1 = d->con_friction[5*c], muk = d->con_friction[5*c + k - 1];
+          real Rn = 1/d->efc_D[r0], R1 = Rn/(real)m->opt_impratio, Rk = R1*mu1*mu1/(muk*muk);
+          if (Rk < MINVAL) Rk = MINVAL;
+          d->efc_D[r] = 1/Rk;
+          /* friction rows: no position term (K = 0) */
+          d->efc_aref[r] = friction_row_aref(m, d, r, sr, d->con_solimp + 5*c);
+          d->efc_pos[r] = 0; d->efc_margin[r] = 0;
+        }
+      }
     } else {
       real mu0 = d->con_friction[5*c];
       /* diagApprox of the first pyramid edge and the common pyramid regulariser Rpy = 2 mu^2 R / impratio */
@@ -1083,6 +1118,25 @@ typedef struct {
   real cost, gauss, quadGauss[3];
 } solctx;
 
+/* One elliptic contact (rows r .. r+dim-1) at residual `jar` (mj_constraintUpdate, elliptic branch): U = jar scaled by
+ * (mu, friction), N = U_0, T = |U_1..|; zone 0 top (N >= mu T: no force), 1 bottom (mu N + T <= 0: every row quadratic),
+ * 2 middle (cost 1/2 Dm (N - mu T)^2).  mu is the regularised cone slope friction_1 sqrt(R_1 / R_n). */
+typedef struct { int dim, zone; real mu, Dm, N, T, U[6], fri[6]; } conezone;
+static void cone_eval(const orc_data* d, int r, const real* jar, conezone* z) {
+  int con = d->efc_id[r], dim = d->con_dim[con];
+  z->dim = dim;
+  z->mu = d->con_friction[5*con]*(real)sqrt((double)(d->efc_D[r]/d->efc_D[r + 1]));
+  z->fri[0] = z->mu;
+  for (int j = 1; j < dim; j++) z->fri[j] = d->con_friction[5*con + j - 1];
+  real tt = 0;
+  for (int k = 0; k < dim; k++) { z->U[k] = jar[r + k]*z->fri[k]; if (k) tt += z->U[k]*z->U[k]; }
+  z->N = z->U[0]; z->T = (real)sqrt((double)tt);
+  real den = z->mu*z->mu*(1 + z->mu*z->mu);
+  z->Dm = d->efc_D[r]/(den > MINVAL ? den : MINVAL);
+  if (z->N >= z->mu*z->T || (z->T <= 0 && z->N >= 0)) z->zone = 0;
+  else if (z->mu*z->N + z->T <= 0 || (z->T <= 0 && z->N < 0)) z->zone = 1;
+  else z->zone = 2;
+}
 /* mj_constraintUpdate: forces, active set and cost s(Jaref) for limit / contact rows, plus the Gauss term */
 static void sol_update_constraint(solctx* c) {
   orc_data* d = c->d; int nv = c->nv;
@@ -1095,6 +1149,23 @@ static void sol_update_constraint(solctx* c) {
       if (jar <= -rf) { d->efc_force[r] = f; c->active[r] = 0; cost += -f*((real)0.5*rf + jar); }
       else if (jar >= rf) { d->efc_force[r] = -f; c->active[r] = 0; cost += -f*((real)0.5*rf - jar); }
       else { d->efc_force[r] = -D*jar; c->active[r] = 1; cost += (real)0.5*D*jar*jar; }
+      continue;
+    }
+    if (d->efc_type[r] == ORC_EFC_CONTACT_ELLIPTIC) {
+      /* active: 1 = row in the quadratic Hessian, 2 = first row of a middle-zone contact (cone Hessian block) */
+      conezone z; cone_eval(d, r, c->Jaref, &z);
+      for (int k = 0; k < z.dim; k++) { d->efc_force[r + k] = 0; c->active[r + k] = 0; }
+      if (z.zone == 1) for (int k = 0; k < z.dim; k++) {
+        real x = c->Jaref[r + k], Dk = d->efc_D[r + k];
+        d->efc_force[r + k] = -Dk*x; c->active[r + k] = 1; cost += (real)0.5*Dk*x*x;
+      } else if (z.zone == 2) {
+        real nmt = z.N - z.mu*z.T;
+        cost += (real)0.5*z.Dm*nmt*nmt;
+        d->efc_force[r] = -z.Dm*nmt*z.mu;
+        for (int j = 1; j < z.dim; j++) d->efc_force[r + j] = -d->efc_force[r]/z.T*z.U[j]*z.fri[j];
+        c->active[r] = 2;
+      }
+      r += z.dim - 1;
       continue;
     }
     if (jar < 0) { d->efc_force[r] = -D*jar; c->active[r] = 1; cost += (real)0.5*D*jar*jar; }
@@ -1123,6 +1194,23 @@ static void sol_update_gradient(solctx* c) {
   for (int i = 0; i < nv*nv; i++) c->H[i] = d->qM[i];
   for (int r = 0; r < c->nefc; r++) {
     if (!c->active[r]) continue;
+    if (c->active[r] == 2) {
+      /* cone Hessian of a middle-zone contact: Dm diag(fri) [1, -mu U'/T; ., mu N/T^3 U U' + (mu^2 - mu N/T) I] diag(fri) */
+      conezone z; cone_eval(d, r, c->Jaref, &z);
+      real Hc[36];
+      for (int a = 0; a < z.dim; a++) for (int b = 0; b < z.dim; b++) {
+        real v;
+        if (a == 0 && b == 0) v = 1;
+        else if (a == 0 || b == 0) v = -z.mu*z.U[a + b]/z.T;
+        else v = z.mu*z.N/(z.T*z.T*z.T)*z.U[a]*z.U[b] + (a == b ? z.mu*z.mu - z.mu*z.N/z.T : 0);
+        Hc[a*z.dim + b] = v*z.Dm*z.fri[a]*z.fri[b];
+      }
+      for (int a = 0; a < z.dim; a++) for (int b = 0; b < z.dim; b++) {
+        const real* Ja = d->efc_J + (r + a)*nv; const real* Jb = d->efc_J + (r + b)*nv; real h = Hc[a*z.dim + b];
+        for (int i = 0; i < nv; i++) { real t = h*Ja[i]; if (t == 0) continue; for (int j = 0; j <= i; j++) c->H[i*nv + j] += t*Jb[j]; }
+      }
+      continue;
+    }
     const real* J = d->efc_J + r*nv; real D = d->efc_D[r];
     for (int i = 0; i < nv; i++) { real t = D*J[i]; if (t == 0) continue; for (int j = 0; j <= i; j++) c->H[i*nv + j] += t*J[j]; }
   }
@@ -1134,6 +1222,7 @@ static void sol_update_gradient(solctx* c) {
 typedef struct { real alpha, cost, d0, d1; } lspoint;
 static lspoint ls_eval(const solctx* c, real alpha) {
   real q0 = c->quadGauss[0], q1 = c->quadGauss[1], q2 = c->quadGauss[2];
+  real xc = 0, xd0 = 0, xd1 = 0;      /* non-quadratic part: middle zones of elliptic contacts */
   for (int r = 0; r < c->nefc; r++) {
     real x = c->Jaref[r] + alpha*c->Jv[r];
     if (r < c->nf) {
@@ -1143,10 +1232,31 @@ static lspoint ls_eval(const solctx* c, real alpha) {
       else { q0 += c->quad[3*r]; q1 += c->quad[3*r + 1]; q2 += c->quad[3*r + 2]; }
       continue;
     }
+    if (c->d->efc_type[r] == ORC_EFC_CONTACT_ELLIPTIC) {
+      /* PrimalEval, elliptic contact: N and T along the search direction, zones as in cone_eval */
+      const orc_data* d = c->d;
+      conezone z; cone_eval(d, r, c->Jaref, &z);       /* gives mu, fri, Dm and U = U(0) */
+      real V[6], UU = 0, UV = 0, VV = 0;
+      for (int k = 0; k < z.dim; k++) { V[k] = c->Jv[r + k]*z.fri[k]; if (k) { UU += z.U[k]*z.U[k]; UV += z.U[k]*V[k]; VV += V[k]*V[k]; } }
+      real N = z.U[0] + alpha*V[0], Tsqr = UU + alpha*(2*UV + alpha*VV);
+      real T = Tsqr > 0 ? (real)sqrt((double)Tsqr) : 0;
+      if (N >= z.mu*T || (Tsqr <= 0 && N >= 0)) { /* top zone */ }
+      else if (z.mu*N + T <= 0 || (Tsqr <= 0 && N < 0)) {
+        for (int k = 0; k < z.dim; k++) { q0 += c->quad[3*(r + k)]; q1 += c->quad[3*(r + k) + 1]; q2 += c->quad[3*(r + k) + 2]; }
+      } else {
+        real N1 = V[0], T1 = (UV + alpha*VV)/T, T2 = VV/T - (UV + alpha*VV)*(UV + alpha*VV)/(T*T*T);
+        real nmt = N - z.mu*T;
+        xc += (real)0.5*z.Dm*nmt*nmt;
+        xd0 += z.Dm*nmt*(N1 - z.mu*T1);
+        xd1 += z.Dm*((N1 - z.mu*T1)*(N1 - z.mu*T1) + nmt*(-z.mu*T2));
+      }
+      r += z.dim - 1;
+      continue;
+    }
     if (x < 0) { q0 += c->quad[3*r]; q1 += c->quad[3*r + 1]; q2 += c->quad[3*r + 2]; }
   }
   lspoint p;
-  p.alpha = alpha; p.cost = alpha*alpha*q2 + alpha*q1 + q0; p.d0 = 2*alpha*q2 + q1; p.d1 = 2*q2;
+  p.alpha = alpha; p.cost = alpha*alpha*q2 + alpha*q1 + q0 + xc; p.d0 = 2*alpha*q2 + q1 + xd0; p.d1 = 2*q2 + xd1;
   if (p.d1 < MINVAL) p.d1 = MINVAL;
   return p;
 }
@@ -1250,7 +1360,15 @@ void orc_solve(const b2s_model_desc* m, orc_data* d) {
           if (s <= -rf) cost_smooth += -f*((real)0.5*rf + s);
           else if (s >= rf) cost_smooth += -f*((real)0.5*rf - s);
           else cost_smooth += (real)0.5*d->efc_D[r]*s*s;
-        } else if (s < 0) cost_smooth += (real)0.5*d->efc_D[r]*s*s;
+        } else if (d->efc_type[r] == ORC_EFC_CONTACT_ELLIPTIC) c.Jv[r] = s;      /* collected, evaluated per contact below */
+        else if (s < 0) cost_smooth += (real)0.5*d->efc_D[r]*s*s;
+      }
+      for (int r = 0; r < nefc; r++) {
+        if (d->efc_type[r] != ORC_EFC_CONTACT_ELLIPTIC) continue;
+        conezone z; cone_eval(d, r, c.Jv, &z);
+        if (z.zone == 1) for (int k = 0; k < z.dim; k++) cost_smooth += (real)0.5*d->efc_D[r + k]*c.Jv[r + k]*c.Jv[r + k];
+        else if (z.zone == 2) { real nmt = z.N - z.mu*z.T; cost_smooth += (real)0.5*z.Dm*nmt*nmt; }
+        r += z.dim - 1;
       }
       if (cost_warm <= cost_smooth) break;
     }
@@ -1313,6 +1431,7 @@ static void contact_wrench(const orc_data* d, int c, real* f6) {
   int adr = d->con_efc_address[c], dim = d->con_dim[c];
   if (adr < 0) return;
   if (dim == 1) { f6[0] = d->efc_force[adr]; return; }
+  if (d->efc_type[adr] == ORC_EFC_CONTACT_ELLIPTIC) { for (int k = 0; k < dim; k++) f6[k] = d->efc_force[adr + k]; return; }
   for (int k = 0; k < dim - 1; k++) {
     real a = d->efc_force[adr + 2*k], b = d->efc_force[adr + 2*k + 1];
     f6[0] += a + b;

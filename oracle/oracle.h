@@ -109,7 +109,7 @@ typedef struct orc_data {
   real* solver_cost;     /* 1 */
 } orc_data;
 
-enum { ORC_EFC_FRICTION_DOF = 1, ORC_EFC_LIMIT = 3, ORC_EFC_CONTACT_FRICTIONLESS = 4, ORC_EFC_CONTACT_PYRAMIDAL = 5 };
+enum { ORC_EFC_FRICTION_DOF = 1, ORC_EFC_LIMIT = 3, ORC_EFC_CONTACT_FRICTIONLESS = 4, ORC_EFC_CONTACT_PYRAMIDAL = 5, ORC_EFC_CONTACT_ELLIPTIC = 6 };
 
 int orc_real_size(void);
 /* mjwarp.forward / mjwarp.step for one world (reference call sites: sim.py:143,146). */

@@ -548,3 +548,65 @@ def test_round_shapes_settle_with_their_weight():
     fz[int(w["con_geom"][2 * c + 1])] = fz.get(int(w["con_geom"][2 * c + 1]), 0.0) + f
   gi = {nm: i for i, nm in enumerate(m.names["geom"])}
   assert abs(fz[gi["cyl_geom"]] - 1.0 * 9.81) < 0.05 and abs(fz[gi["ell_geom"]] - 2.0 * 9.81) < 0.05 and abs(fz[gi["ball_geom"]] - 0.2 * 9.81) < 0.01
+
+
+def _cone_contacts(w, n):
+  """(first row, dim) of every elliptic contact among the n rows"""
+  out, r = [], 0
+  while r < n:
+    if int(w["efc_type"][r]) == 6:
+      dim = int(w["con_dim"][int(w["efc_id"][r])]); out.append((r, dim)); r += dim
+    else:
+      r += 1
+  return out
+
+
+def test_elliptic_cone_solution_properties(g1):
+  """cone="elliptic" (reference sim.py:51): three rows per condim-3 contact (normal, two tangents) instead of four pyramid
+  edges; at the Newton solution the stationarity condition M (qacc - qacc_smooth) = J^T f holds, every contact force lies
+  in the friction cone with the UNREGULARISED coefficient (|f_t| <= mu f_n), sliding contacts sit exactly on it, and a
+  resting box carries its weight on the normal rows alone.  Both line searches reach the same solution."""
+  import copy
+  from util import g1_states
+  mg = copy.copy(g1); mg.opt = copy.copy(g1.opt); mg.opt.cone = 1
+  qpos, qvel, ctrl = g1_states(g1, 6, seed=11)
+  sliding = sticking = 0
+  sols = {}
+  for lsp in (0, 1):
+    orc = Oracle(mg, "f64", 50, 300, ls_parallel=lsp, opt=dict(iterations=100, tolerance=1e-12, ls_iterations=50))
+    for i in range(6):
+      w = orc.forward(orc.new_world(qpos[i], qvel[i], ctrl[i]))
+      n, nv = int(w["nefc"][0]), g1.nv
+      sols[(lsp, i)] = w["qacc"].copy()
+      if n == 0 or lsp == 1:
+        continue
+      J = w["efc_J"][: n * nv].reshape(n, nv); f = w["efc_force"][:n]; M = w["qM"].reshape(nv, nv)
+      res = M @ (w["qacc"] - w["qacc_smooth"]) - J.T @ f
+      assert np.abs(res).max() < 1e-5 * (1 + np.abs(J.T @ f).max())
+      for r, dim in _cone_contacts(w, n):
+        assert dim == 3
+        mu = w["con_friction"][5 * int(w["efc_id"][r])]
+        fn, ft = f[r], np.hypot(f[r + 1], f[r + 2])
+        assert fn >= 0 and ft <= mu * fn * (1 + 1e-9) + 1e-12
+        if fn > 1e-9:
+          sliding += int(abs(ft - mu * fn) < 1e-9 * (1 + fn)); sticking += int(ft < mu * fn * (1 - 1e-6))
+  assert sliding > 3 and sticking > 3
+  for i in range(6):     # parallel search: discrete steps, converges to the same point more loosely
+    assert np.abs(sols[(0, i)] - sols[(1, i)]).max() < 2e-3 * (1 + np.abs(sols[(0, i)]).max())
+  # resting box: 4 contacts x 3 rows, friction rows idle, weight on the normals; pushed below / above mu m g it sticks / slides
+  m = fx.compile_xml(fx.FALLING_BOX)
+  me = copy.copy(m); me.opt = copy.copy(m.opt); me.opt.cone = 1; me.opt.iterations = 50
+  orc = Oracle(me, "f64", 16, 64, ls_parallel=0)
+  w = orc.new_world(); orc.step(w, 500)
+  n = int(w["nefc"][0])
+  assert int(w["ncon"][0]) == 4 and n == 12
+  f = w["efc_force"][:n].reshape(4, 3)
+  assert abs(f[:, 0].sum() - 9.81) < 1e-6 and np.abs(f[:, 1:]).max() < 1e-6
+  def slide(F):
+    w2 = orc.new_world(w["qpos"].copy(), np.zeros(m.nv)); w2["xfrc_applied"][6 * 2] = F
+    orc.step(w2, 150); v1 = w2["qvel"][0]; orc.step(w2, 150)
+    return (w2["qvel"][0] - v1) / (150 * 0.002), w2
+  a, w2 = slide(5.0)
+  assert abs(a) < 1e-3 and abs(w2["qvel"][0]) < 0.01
+  a, w2 = slide(12.0)
+  assert abs(a - (12.0 - 9.81)) < 0.1 * (12.0 - 9.81) + 0.1
