@@ -149,7 +149,8 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   // ---------------------------------------------------------------- validation: unsupported features are errors
   if (s->na > 0) return fail("stateful actuators (na > 0) are not supported");
   if (s->nv < 1 || s->nv > B2S_MAX_NV) return fail("nv must be in [1, " + std::to_string(B2S_MAX_NV) + "]");
-  if (s->opt_cone != B2S_CONE_PYRAMIDAL) return fail("only the pyramidal friction cone is supported");
+  if (s->opt_cone != B2S_CONE_PYRAMIDAL && s->opt_cone != B2S_CONE_ELLIPTIC) return fail("cone must be pyramidal or elliptic");
+  if (s->opt_cone == B2S_CONE_ELLIPTIC) for (int g = 0; g < s->ngeom; g++) if (s->geom_condim[g] > 3) return fail("elliptic cones are supported for condim 1 and 3 only");
   if (s->opt_solver != B2S_SOL_NEWTON && s->opt_solver != B2S_SOL_CG) return fail("solver must be newton or cg (PGS is not supported)");
   if (s->opt_integrator != B2S_INT_EULER && s->opt_integrator != B2S_INT_IMPLICITFAST) return fail("integrator must be euler or implicitfast");
   const int nb = s->nbody, nv = s->nv;
@@ -541,7 +542,8 @@ extern "C" int b2s_model_set_opt(b2s_model* m, const char* key, double v) {
     if ((int)v != B2S_SOL_NEWTON && (int)v != B2S_SOL_CG) return fail("solver must be newton or cg (PGS is not supported)");
     d.solver = (int)v;
   } else if (k == "cone") {
-    if ((int)v != B2S_CONE_PYRAMIDAL) return fail("only the pyramidal friction cone is supported");
+    if ((int)v != B2S_CONE_PYRAMIDAL && (int)v != B2S_CONE_ELLIPTIC) return fail("cone must be pyramidal or elliptic");
+    d.cone = (int)v;
   } else return fail("unknown option " + k);
   return 0;
 }

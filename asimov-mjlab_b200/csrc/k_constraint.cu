@@ -21,7 +21,7 @@
 
 extern __shared__ float b2s_smem[];
 
-enum { EFC_FRICTION_DOF = 1, EFC_LIMIT = 3, EFC_CONTACT_FRICTIONLESS = 4, EFC_CONTACT_PYRAMIDAL = 5 };
+enum { EFC_FRICTION_DOF = 1, EFC_LIMIT = 3, EFC_CONTACT_FRICTIONLESS = 4, EFC_CONTACT_PYRAMIDAL = 5, EFC_CONTACT_ELLIPTIC = 6 };
 
 DEV float impedance(const float* si, float pos, float margin) {
   const float d0 = si[0], dw = si[1], width = si[2], mid = si[3], power = si[4];
@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
     int nrow = 0, dim = 0;
     if (c < ncon && d.con_dist[con0 + c] < d.con_includemargin[con0 + c]) {
       dim = d.con_dim[con0 + c];
-      nrow = dim == 1 ? 1 : 2 * (dim - 1);
+      nrow = dim == 1 ? 1 : (m.cone == B2S_CONE_ELLIPTIC ? dim : 2 * (dim - 1));
     }
     int total;
     const int excl = warp_excl_scan(nrow, lane, &total);
@@ -192,6 +192,38 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
       const float dist = d.con_dist[o], inc = d.con_includemargin[o];
       const float sr0 = d.con_solref[2 * o], sr1 = d.con_solref[2 * o + 1];
       const int bp = b1 | (b2 << 16);
+      if (dim > 1 && m.cone == B2S_CONE_ELLIPTIC) {
+        // elliptic cone: rows = the contact-frame axes; friction rows have pos = 0, share the normal row's impedance and are
+        // regularised by R_1 = R_n / impratio, R_j = R_1 mu_1^2 / mu_j^2; their aref is -B vel (oracle orc_make_constraint)
+        const float rot = m.body_invweight0[2 * b1 + 1] + m.body_invweight0[2 * b2 + 1];
+        const float* si = d.con_solimp + 5 * o;
+        float Rn = 0.f;
+        for (int k = 0; k < nrow; k++) {
+          const size_t row = row0 + adr + k;
+          float* g = d.efc_g + row * 6;
+          float vel = 0.f;
+#pragma unroll
+          for (int kk = 0; kk < 6; kk++) if (kk == k) {
+#pragma unroll
+            for (int q = 0; q < 6; q++) g[q] = gb[kk][q];
+            vel = vb[kk];
+          }
+          d.efc_bp[row] = bp; d.efc_type[row] = EFC_CONTACT_ELLIPTIC; d.efc_id[row] = c;
+          finish_row(m, d, row, dist, inc, vel, sr0, sr1, si, k < 3 ? tran : rot, 1.f);
+          if (k == 0) Rn = 1.f / d.efc_D[row];
+          else {
+            const float mk = fri[k - 1];
+            d.efc_D[row] = 1.f / fmaxf(Rn / m.impratio * mu0 * mu0 / (mk * mk), B2S_MINVAL);
+            float B;
+            if (sr0 > 0.f) {
+              float tc = sr0;
+              if (!(m.disableflags & B2S_DSBL_REFSAFE)) tc = fmaxf(tc, 2.f * m.timestep);
+              B = 2.f / fmaxf(si[1] * tc, B2S_MINVAL);
+            } else B = -sr1 / fmaxf(si[1], B2S_MINVAL);
+            d.efc_aref[row] = -B * vel; d.efc_pos[row] = 0.f; d.efc_margin[row] = 0.f;
+          }
+        }
+      } else
       for (int k = 0; k < nrow; k++) {
         const size_t row = row0 + adr + k;
         float* g = d.efc_g + row * 6;

@@ -32,6 +32,7 @@ DEV void fill_contact_cache(const ModelDev& m, const DataDev& d, int w, int ncon
     const int adr = d.con_efc_address[con0 + c], dim = d.con_dim[con0 + c];
     if (adr >= 0) {
       if (dim == 1) f6[0] = d.efc_force[row0 + adr];
+      else if (d.efc_type[row0 + adr] == 6) { for (int k = 0; k < dim; k++) f6[k] = d.efc_force[row0 + adr + k]; }      // elliptic: the rows are the frame axes
       else for (int k = 0; k < dim - 1; k++) {
         const float a = d.efc_force[row0 + adr + 2 * k], b = d.efc_force[row0 + adr + 2 * k + 1];
         f6[0] += a + b;

@@ -39,8 +39,8 @@ __host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      
   const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
   return (HF + 12 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
 }
-__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T) {
-  return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + 3) & ~3;
+__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T, int elliptic = 0) {
+  return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + (elliptic ? 2 * njmax : 0) + 3) & ~3;
 }
 
 // Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
@@ -77,6 +77,11 @@ struct SolveCtx {
   DEV float* X() const { return sm + soff; }
   DEV float* KW() const { return sm + soff + 6 * max(nb, 32); }
   DEV int* Li() const { return (int*)(sm + soff + 6 * max(nb, 32) + 32); }
+  // elliptic cones only (the arrays exist only in that variant's allocation): per row, 0 = not part of an elliptic contact,
+  // 1 = first (normal) row of one, 2 = one of its friction rows; and the row's scale (regularised mu for the normal row,
+  // the friction coefficient for the others)
+  DEV int* ekind() const { return (int*)(sm + soff + 6 * max(nb, 32) + 64); }
+  DEV float* efri() const { return sm + soff + 6 * max(nb, 32) + 64 + njmax; }
 };
 
 // y[i] = sum_j M[i][j] x[j].  M is dense and symmetric in HBM/L2 with row stride nvp (a multiple of 4, padding columns
@@ -141,26 +146,64 @@ DEV float gauss_term(const SolveCtx<T>& c) {
   for (int i = c.lane; i < c.nv; i += 32) g += (c.Ma()[i] - c.qfs()[i]) * (c.qacc()[i] - c.qas()[i]);
   return 0.5f * warp_sum(g);
 }
+// One elliptic contact (3 rows starting at r) at residuals x[0..2] (mj_constraintUpdate, elliptic branch; oracle cone_eval):
+// U = x scaled by (mu, friction), N = U_0, T = |U_1, U_2|; zone 0 top (no force), 1 bottom (all rows quadratic), 2 middle.
+struct Cone { int zone; float mu, Dm, N, T, U[3], fri[3]; };
+template <int T>
+DEV Cone cone_eval(const SolveCtx<T>& c, int r, float x0, float x1, float x2) {
+  Cone z;
+  z.fri[0] = c.efri()[r]; z.fri[1] = c.efri()[r + 1]; z.fri[2] = c.efri()[r + 2];
+  z.mu = z.fri[0];
+  z.U[0] = x0 * z.fri[0]; z.U[1] = x1 * z.fri[1]; z.U[2] = x2 * z.fri[2];
+  z.N = z.U[0]; z.T = sqrtf(z.U[1] * z.U[1] + z.U[2] * z.U[2]);
+  z.Dm = c.D()[r] / fmaxf(z.mu * z.mu * (1.f + z.mu * z.mu), B2S_MINVAL);
+  if (z.N >= z.mu * z.T || (z.T <= 0.f && z.N >= 0.f)) z.zone = 0;
+  else if (z.mu * z.N + z.T <= 0.f || (z.T <= 0.f && z.N < 0.f)) z.zone = 1;
+  else z.zone = 2;
+  return z;
+}
+// forces of the three rows of an elliptic contact
+template <int T>
+DEV void cone_force(const SolveCtx<T>& c, int r, const Cone& z, float x0, float x1, float x2, float* f) {
+  f[0] = f[1] = f[2] = 0.f;
+  if (z.zone == 1) { f[0] = -c.D()[r] * x0; f[1] = -c.D()[r + 1] * x1; f[2] = -c.D()[r + 2] * x2; }
+  else if (z.zone == 2) {
+    f[0] = -z.Dm * (z.N - z.mu * z.T) * z.mu;
+    f[1] = -f[0] / z.T * z.U[1] * z.fri[1]; f[2] = -f[0] / z.T * z.U[2] * z.fri[2];
+  }
+}
 // Zone of row r at residual x: 0 inactive, 1 quadratic (the active set of the Hessian), and for friction-loss rows
 // (r < nf, only in the FRIC instantiation) 2 / 3 = saturated at force +f / -f outside |x| < R f (mj_constraintUpdate)
-template <int T, bool FRIC>
+template <int T, int V>
 DEV int row_zone(const SolveCtx<T>& c, int r, float x) {
+  constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   if (FRIC && r < c.nf) { const float rf = c.frf()[r]; return x <= -rf ? 2 : (x >= rf ? 3 : 1); }
   return x < 0.f ? 1 : 0;
 }
-template <int T, bool FRIC>
+template <int T, int V>
 DEV float row_force(const SolveCtx<T>& c, int r, float x) {
-  const int z = row_zone<T, FRIC>(c, r, x);
+  constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
+  const int z = row_zone<T, V>(c, r, x);
   if (FRIC && z >= 2) return z == 2 ? c.fl()[r] : -c.fl()[r];
   return z == 1 ? -c.D()[r] * x : 0.f;
 }
-template <int T, bool FRIC>
+template <int T, int V>
 DEV float constraint_cost(const SolveCtx<T>& c, const float* jar) {
+  constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   float s = 0.f;
   ROLL
   for (int r = c.lane; r < c.nefc; r += 32) {
     const float x = jar[r];
-    const int z = row_zone<T, FRIC>(c, r, x);
+    if (ELL && c.ekind()[r]) {
+      if (c.ekind()[r] == 1) {        // the lane of the normal row evaluates the whole contact
+        const float x1 = jar[r + 1], x2 = jar[r + 2];
+        const Cone z = cone_eval<T>(c, r, x, x1, x2);
+        if (z.zone == 1) s += 0.5f * (c.D()[r] * x * x + c.D()[r + 1] * x1 * x1 + c.D()[r + 2] * x2 * x2);
+        else if (z.zone == 2) { const float nmt = z.N - z.mu * z.T; s += 0.5f * z.Dm * nmt * nmt; }
+      }
+      continue;
+    }
+    const int z = row_zone<T, V>(c, r, x);
     if (z == 1) s += 0.5f * c.D()[r] * x * x;
     else if (FRIC && z >= 2) s += -c.fl()[r] * (0.5f * c.frf()[r] + (z == 2 ? x : -x));
   }
@@ -169,12 +212,35 @@ DEV float constraint_cost(const SolveCtx<T>& c, const float* jar) {
 struct LsPoint { float alpha, cost, d0, d1; };
 // arguments of the exact (iterative) line search, passed BY VALUE so that this cold, out-of-line path does not
 // force the solver context into local memory
-struct LsArgs { const float *Jaref, *Jv, *D, *search, *fl, *frf; int nefc, nf, nv, lane, maxit; float gtol_unit, q0, q1, q2; };
+struct LsArgs { const float *Jaref, *Jv, *D, *search, *fl, *frf, *efri; const int* ekind; int nefc, nf, nv, lane, maxit; float gtol_unit, q0, q1, q2; };
+// E: the elliptic-cone branch is compiled in (the default instantiation keeps the smaller function: code size matters here)
+template <bool E>
 __device__ __noinline__ LsPoint ls_eval(const LsArgs a, float alpha) {
-  float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+  float q0 = 0.f, q1 = 0.f, q2 = 0.f, xc = 0.f, xd0 = 0.f, xd1 = 0.f;
 #pragma unroll 1
   for (int r = a.lane; r < a.nefc; r += 32) {
     const float ja = a.Jaref[r], jv = a.Jv[r], x = ja + alpha * jv;
+    if (E && a.ekind[r]) {      // elliptic contact, evaluated by the lane of its normal row (PrimalEval)
+      if (a.ekind[r] != 1) continue;
+      const float mu = a.efri[r], f1 = a.efri[r + 1], f2 = a.efri[r + 2];
+      const float ja1 = a.Jaref[r + 1], ja2 = a.Jaref[r + 2], jv1 = a.Jv[r + 1], jv2 = a.Jv[r + 2];
+      const float U0 = ja * mu, U1 = ja1 * f1, U2 = ja2 * f2, V0 = jv * mu, V1 = jv1 * f1, V2 = jv2 * f2;
+      const float UU = U1 * U1 + U2 * U2, UV = U1 * V1 + U2 * V2, VV = V1 * V1 + V2 * V2;
+      const float N = U0 + alpha * V0, Tsqr = UU + alpha * (2.f * UV + alpha * VV), Tn = Tsqr > 0.f ? sqrtf(Tsqr) : 0.f;
+      if (N >= mu * Tn || (Tsqr <= 0.f && N >= 0.f)) continue;
+      if (mu * N + Tn <= 0.f || (Tsqr <= 0.f && N < 0.f)) {
+        const float D0 = a.D[r], D1 = a.D[r + 1], D2 = a.D[r + 2];
+        q0 += 0.5f * (D0 * ja * ja + D1 * ja1 * ja1 + D2 * ja2 * ja2);
+        q1 += D0 * ja * jv + D1 * ja1 * jv1 + D2 * ja2 * jv2;
+        q2 += 0.5f * (D0 * jv * jv + D1 * jv1 * jv1 + D2 * jv2 * jv2);
+      } else {
+        const float Dm = a.D[r] / fmaxf(mu * mu * (1.f + mu * mu), B2S_MINVAL);
+        const float N1 = V0, T1 = (UV + alpha * VV) / Tn, T2 = VV / Tn - (UV + alpha * VV) * (UV + alpha * VV) / (Tn * Tn * Tn);
+        const float nmt = N - mu * Tn;
+        xc += 0.5f * Dm * nmt * nmt; xd0 += Dm * nmt * (N1 - mu * T1); xd1 += Dm * ((N1 - mu * T1) * (N1 - mu * T1) - nmt * mu * T2);
+      }
+      continue;
+    }
     if (r < a.nf) {       // friction-loss row (nf == 0 unless the model has joint friction)
       const float f = a.fl[r], rf = a.frf[r];
       if (x <= -rf) { q0 += f * (-0.5f * rf - ja); q1 += -f * jv; continue; }
@@ -185,10 +251,12 @@ __device__ __noinline__ LsPoint ls_eval(const LsArgs a, float alpha) {
     if (x < 0.f) { const float D = a.D[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
   }
   q0 = warp_sum(q0) + a.q0; q1 = warp_sum(q1) + a.q1; q2 = warp_sum(q2) + a.q2;
+  if (E) { xc = warp_sum(xc); xd0 = warp_sum(xd0); xd1 = warp_sum(xd1); }
   LsPoint p;
-  p.alpha = alpha; p.cost = alpha * alpha * q2 + alpha * q1 + q0; p.d0 = 2.f * alpha * q2 + q1; p.d1 = fmaxf(2.f * q2, B2S_MINVAL);
+  p.alpha = alpha; p.cost = alpha * alpha * q2 + alpha * q1 + q0 + xc; p.d0 = 2.f * alpha * q2 + q1 + xd0; p.d1 = fmaxf(2.f * q2 + xd1, B2S_MINVAL);
   return p;
 }
+template <bool E>
 __device__ __noinline__ float ls_iterative(const LsArgs a) {
   float sn = 0.f;
 #pragma unroll 1
@@ -198,21 +266,21 @@ __device__ __noinline__ float ls_iterative(const LsArgs a) {
   const float gtol = a.gtol_unit * sn;
   const int maxit = a.maxit;
   int it = 0;
-  const LsPoint p0 = ls_eval(a, 0.f);
-  LsPoint p1 = ls_eval(a, p0.alpha - p0.d0 / p0.d1); it++;
+  const LsPoint p0 = ls_eval<E>(a, 0.f);
+  LsPoint p1 = ls_eval<E>(a, p0.alpha - p0.d0 / p0.d1); it++;
   if (p0.cost < p1.cost) p1 = p0;
   if (fabsf(p1.d0) < gtol) return p1.alpha;
   const float dir = p1.d0 < 0.f ? 1.f : -1.f;
   LsPoint p2 = p0; bool p2upd = false;
   while (p1.d0 * dir <= -gtol && it < maxit) {
     p2 = p1; p2upd = true;
-    p1 = ls_eval(a, p1.alpha - p1.d0 / p1.d1); it++;
+    p1 = ls_eval<E>(a, p1.alpha - p1.d0 / p1.d1); it++;
     if (fabsf(p1.d0) < gtol) return p1.alpha;
   }
   if (it >= maxit || !p2upd) return p1.alpha;
-  LsPoint p2next = p1, p1next = ls_eval(a, p1.alpha - p1.d0 / p1.d1); it++;
+  LsPoint p2next = p1, p1next = ls_eval<E>(a, p1.alpha - p1.d0 / p1.d1); it++;
   while (it < maxit) {
-    const LsPoint pmid = ls_eval(a, 0.5f * (p1.alpha + p2.alpha)); it++;
+    const LsPoint pmid = ls_eval<E>(a, 0.5f * (p1.alpha + p2.alpha)); it++;
     bool b1 = false, b2 = false;
 #pragma unroll
     for (int k = 0; k < 3; k++) {
@@ -223,8 +291,8 @@ __device__ __noinline__ float ls_iterative(const LsArgs a) {
       else if (cd.d0 * dir > 0.f && in && !b1) { p1 = cd; b1 = true; }
     }
     if (!b1 && !b2) return pmid.cost < p0.cost ? pmid.alpha : 0.f;
-    if (b1) { p1next = ls_eval(a, p1.alpha - p1.d0 / p1.d1); it++; }
-    if (b2) { p2next = ls_eval(a, p2.alpha - p2.d0 / p2.d1); it++; }
+    if (b1) { p1next = ls_eval<E>(a, p1.alpha - p1.d0 / p1.d1); it++; }
+    if (b2) { p2next = ls_eval<E>(a, p2.alpha - p2.d0 / p2.d1); it++; }
   }
   if (p1.cost <= p2.cost && p1.cost < p0.cost) return p1.alpha;
   if (p2.cost <= p1.cost && p2.cost < p0.cost) return p2.alpha;
@@ -233,8 +301,9 @@ __device__ __noinline__ float ls_iterative(const LsArgs a) {
 // one lane per candidate step: alpha_k = min_step^(k/(n-1)), k = 0..n-1, and alpha = 0 on one more lane; rows are
 // summed in row order by every lane (same order as the oracle), the best candidate wins (ties: alpha = 0, then
 // the smallest k), so a step is only taken if it strictly improves on alpha = 0
-template <int T, bool FRIC>
+template <int T, int V>
 DEV float ls_parallel(const SolveCtx<T>& c, const ModelDev& m, const float* qg) {
+  constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   const int n = m.ls_iterations;
   const float lg = logf(m.ls_parallel_min_step);
   float best = 3.0e38f, balpha = 0.f; int bk = 0x7fffffff;
@@ -242,14 +311,26 @@ DEV float ls_parallel(const SolveCtx<T>& c, const ModelDev& m, const float* qg) 
     const int k = base + c.lane;
     if (k <= n) {
       const float alpha = k == n ? 0.f : (n > 1 ? expf((float)k / (float)(n - 1) * lg) : 1.f);
-      float q0 = qg[0], q1 = qg[1], q2 = qg[2];
+      float q0 = qg[0], q1 = qg[1], q2 = qg[2], xc = 0.f;
       for (int r = 0; r < c.nefc; r++) {
         const float ja = c.Jaref()[r], jv = c.Jv()[r];
-        const int z = row_zone<T, FRIC>(c, r, ja + alpha * jv);
+        if (ELL && c.ekind()[r]) {      // elliptic contact: N(alpha), T(alpha) and the zone at this candidate (PrimalEval)
+          const float ja1 = c.Jaref()[r + 1], ja2 = c.Jaref()[r + 2], jv1 = c.Jv()[r + 1], jv2 = c.Jv()[r + 2];
+          const Cone z = cone_eval<T>(c, r, ja + alpha * jv, ja1 + alpha * jv1, ja2 + alpha * jv2);
+          if (z.zone == 1) {
+            const float D0 = c.D()[r], D1 = c.D()[r + 1], D2 = c.D()[r + 2];
+            q0 += 0.5f * (D0 * ja * ja + D1 * ja1 * ja1 + D2 * ja2 * ja2);
+            q1 += D0 * ja * jv + D1 * ja1 * jv1 + D2 * ja2 * jv2;
+            q2 += 0.5f * (D0 * jv * jv + D1 * jv1 * jv1 + D2 * jv2 * jv2);
+          } else if (z.zone == 2) { const float nmt = z.N - z.mu * z.T; xc += 0.5f * z.Dm * nmt * nmt; }
+          r += 2;
+          continue;
+        }
+        const int z = row_zone<T, V>(c, r, ja + alpha * jv);
         if (z == 1) { const float D = c.D()[r]; q0 += 0.5f * D * ja * ja; q1 += D * ja * jv; q2 += 0.5f * D * jv * jv; }
         else if (FRIC && z >= 2) { const float f = c.fl()[r], sg = z == 2 ? -1.f : 1.f; q0 += f * (-0.5f * c.frf()[r] + sg * ja); q1 += sg * f * jv; }
       }
-      const float cost = alpha * alpha * q2 + alpha * q1 + q0;
+      const float cost = ELL ? alpha * alpha * q2 + alpha * q1 + q0 + xc : alpha * alpha * q2 + alpha * q1 + q0;
       const int kk = k == n ? -1 : k;
       if (cost < best || (cost == best && kk < bk)) { best = cost; balpha = alpha; bk = kk; }
     }
@@ -362,8 +443,9 @@ DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, b
 
 // Forces / active set from Jaref, qfrc_constraint = J^T f, and (withH) J^T D J into the (zeroed) lower triangle
 // of H in shared memory; M is added when the tiles are loaded for the factorisation.
-template <int T, bool FRIC>
+template <int T, int V>
 DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, int ib) {
+  constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   __syncwarp();
   ROLL
   for (int i = c.lane; i < c.nvp; i += 32) c.qfc()[i] = 0.f;
@@ -377,11 +459,11 @@ DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, i
   ROLL
   for (int r = c.lane; r < c.nl; r += 32) {
     const float jar = c.Jaref()[r];
-    const int z = row_zone<T, FRIC>(c, r, jar);
+    const int z = row_zone<T, V>(c, r, jar);
     if (z) {
       const float g0 = c.G[(size_t)r * 6];
       const int dof = -1 - c.bp[r];
-      atomicAdd(&c.qfc()[dof], g0 * row_force<T, FRIC>(c, r, jar));
+      atomicAdd(&c.qfc()[dof], g0 * row_force<T, V>(c, r, jar));
       if (withH && z == 1) atomicAdd(&c.H()[dof * c.ld + dof], c.D()[r]);
     }
   }
@@ -397,6 +479,36 @@ DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, i
 #pragma unroll 4
     for (int r = r0; r < r1; r++) {
       const float jar = c.Jaref()[r];
+      if (ELL && c.ekind()[r]) {
+        // elliptic contact (3 rows): W += sum_a f_a g_a, K += sum_ab Hc[a][b] g_a g_b^T with Hc = diag(D) in the bottom zone and
+        // the cone Hessian Dm diag(fri) [1, -mu U'/T; ., mu N/T^3 U U' + (mu^2 - mu N/T) I] diag(fri) in the middle zone
+        const float x1 = c.Jaref()[r + 1], x2 = c.Jaref()[r + 2];
+        const Cone z = cone_eval<T>(c, r, jar, x1, x2);
+        if (z.zone) {
+          float f[3], ga3[3], gb3[3];
+          cone_force<T>(c, r, z, jar, x1, x2, f);
+#pragma unroll
+          for (int a = 0; a < 3; a++) { ga3[a] = gA[(size_t)(r + a) * 6]; gb3[a] = gB[(size_t)(r + a) * 6]; }
+          if (!isK) acc += f[0] * ga3[0] + f[1] * ga3[1] + f[2] * ga3[2];
+          else if (z.zone == 1) acc += c.D()[r] * ga3[0] * gb3[0] + c.D()[r + 1] * ga3[1] * gb3[1] + c.D()[r + 2] * ga3[2] * gb3[2];
+          else {
+            const float it = 1.f / z.T, s3 = z.mu * z.N * it * it * it, dg = z.mu * z.mu - z.mu * z.N * it;
+#pragma unroll
+            for (int a = 0; a < 3; a++)
+#pragma unroll
+              for (int b = 0; b < 3; b++) {
+                float h;
+                if (a == 0 && b == 0) h = 1.f;
+                else if (a == 0 || b == 0) h = -z.mu * z.U[a + b] * it;
+                else h = s3 * z.U[a] * z.U[b] + (a == b ? dg : 0.f);
+                acc += h * z.Dm * z.fri[a] * z.fri[b] * ga3[a] * gb3[b];
+              }
+          }
+          any = true;
+        }
+        r += 2;
+        continue;
+      }
       const float De = jar < 0.f ? c.D()[r] : 0.f;
       const float ga = gA[(size_t)r * 6], gb = gB[(size_t)r * 6];
       acc += (isK ? De * gb : -De * jar) * ga;
@@ -411,19 +523,29 @@ DEV void assemble(const SolveCtx<T>& c, const ModelDev& m, bool withH, int ia, i
 // call.  H = M + J^T D J depends on the state only through this set (pyramidal cones: D is fixed per row), so an
 // unchanged set means the factor of the previous iteration is still the factor of H (MuJoCo's Newton solver also
 // refactors only on a change of the active set).
-template <int T, bool FRIC>
+template <int T, int V>
 DEV bool active_set_unchanged(const SolveCtx<T>& c) {
+  constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   bool same = true;
   ROLL
   for (int base = 0; base < c.nefc; base += 32) {
     const int r = base + c.lane;
-    const unsigned mk = __ballot_sync(FULL, r < c.nefc && row_zone<T, FRIC>(c, r, c.Jaref()[r]) == 1);
+    bool on = false;
+    if (r < c.nefc) {
+      if (ELL && c.ekind()[r]) {
+        const int r0 = r - (c.ekind()[r] == 1 ? 0 : (c.ekind()[r - 1] == 1 ? 1 : 2));      // normal row of this contact
+        const Cone z = cone_eval<T>(c, r0, c.Jaref()[r0], c.Jaref()[r0 + 1], c.Jaref()[r0 + 2]);
+        on = z.zone == 1;
+        if (z.zone == 2) same = false;         // the cone Hessian changes with the state: never reuse the factor
+      } else on = row_zone<T, V>(c, r, c.Jaref()[r]) == 1;
+    }
+    const unsigned mk = __ballot_sync(FULL, on);
     same &= c.amask()[base >> 5] == mk;
     __syncwarp();
     if (c.lane == 0) c.amask()[base >> 5] = mk;
   }
   __syncwarp();
-  return same;
+  return ELL ? __all_sync(FULL, same) : same;
 }
 
 // Load the lower-triangular register tiles of H = M + (J^T D J in shared memory) and factorise.
@@ -458,8 +580,9 @@ DEV void factor_H(const SolveCtx<T>& c, int bi, int bj) {
   tile_cholesky_regs<T>(a, bi, bj, c.H(), c.ld, c.invd());
 }
 
-template <int T, bool FRIC>
+template <int T, int V>
 __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const ModelDev m, const DataDev d) {
+  constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // worlds are taken from the cost-ordered queues, most expensive class first (k_constraint filled them)
   int w = blockIdx.x * SOLVE_WARPS + warp;
@@ -478,7 +601,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   c.G = d.efc_g + (size_t)w * njmax * 6;
   c.bp = d.efc_bp + (size_t)w * njmax;
   c.aref = d.efc_aref + (size_t)w * njmax;
-  c.sm = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, d.nconmax, T);
+  c.sm = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, d.nconmax, T, ELL ? 1 : 0);
   float* efc_force = d.efc_force + (size_t)w * njmax;
   float* g_qacc = d.qacc + (size_t)w * nv;
   float* g_qfc = d.qfrc_constraint + (size_t)w * nv;
@@ -513,6 +636,21 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     }
 #pragma unroll 1
     for (int r = lane; r < c.nefc; r += 32) c.D()[r] = d.efc_D[(size_t)w * njmax + r];
+    if (ELL) {
+      // rows of elliptic contacts: kind (normal / friction row) and scale (regularised mu = friction_1 sqrt(R_1 / R_n); friction_j)
+#pragma unroll 1
+      for (int r = lane; r < c.nefc; r += 32) {
+        int kind = 0; float fr = 0.f;
+        if (d.efc_type[(size_t)w * njmax + r] == 6) {
+          const int con = d.efc_id[(size_t)w * njmax + r];
+          const int k = r - d.con_efc_address[(size_t)w * d.nconmax + con];
+          const float* cf = d.con_friction + ((size_t)w * d.nconmax + con) * 5;
+          kind = k == 0 ? 1 : 2;
+          fr = k == 0 ? cf[0] * sqrtf(d.efc_D[(size_t)w * njmax + r] / d.efc_D[(size_t)w * njmax + r + 1]) : cf[k - 1];
+        }
+        c.ekind()[r] = kind; c.efri()[r] = fr;
+      }
+    }
     if (FRIC) {
 #pragma unroll 1
       for (int r = lane; r < c.nf; r += 32) {
@@ -549,7 +687,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   for (int pass = warm ? 0 : 1; pass < 2; pass++) {
     const float* x = (pass == 0 || !warm) ? c.qas() : c.search();
     mat_vec_J(c, m, x, c.aref, c.Jv());
-    float cst = constraint_cost<T, FRIC>(c, c.Jv());
+    float cst = constraint_cost<T, V>(c, c.Jv());
     mat_vec_M(c, x, c.Mv());
     __syncwarp();
     float g = 0.f;
@@ -583,8 +721,8 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
 #pragma unroll 1
   while (true) {
     // the factor in shared memory stays valid while the active set does not change
-    const bool reuse = (active_set_unchanged<T, FRIC>(c) && haveL) || !newton;
-    assemble<T, FRIC>(c, m, withH && !reuse, ia, ib);
+    const bool reuse = (active_set_unchanged<T, V>(c) && haveL) || !newton;
+    assemble<T, V>(c, m, withH && !reuse, ia, ib);
     if (!withH) break;
     float gn = 0.f;
 #pragma unroll 1
@@ -621,13 +759,13 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     for (int i = lane; i < nv; i += 32) { g1 += c.search()[i] * (c.Ma()[i] - c.qfs()[i]); g2 += c.search()[i] * c.Mv()[i]; }
     float qg[3] = {gauss, warp_sum(g1), 0.5f * warp_sum(g2)};
     float alpha;
-    if (m.ls_parallel) alpha = ls_parallel<T, FRIC>(c, m, qg);
+    if (m.ls_parallel) alpha = ls_parallel<T, V>(c, m, qg);
     else {
       LsArgs la;
-      la.Jaref = c.Jaref(); la.Jv = c.Jv(); la.D = c.D(); la.search = c.search(); la.nefc = c.nefc; la.nf = c.nf; la.fl = c.fl(); la.frf = c.frf(); la.nv = nv; la.lane = lane;
+      la.Jaref = c.Jaref(); la.Jv = c.Jv(); la.D = c.D(); la.search = c.search(); la.nefc = c.nefc; la.nf = c.nf; la.fl = c.fl(); la.frf = c.frf(); la.ekind = ELL ? c.ekind() : nullptr; la.efri = ELL ? c.efri() : nullptr; la.nv = nv; la.lane = lane;
       la.maxit = m.ls_iterations; la.gtol_unit = m.tolerance * m.ls_tolerance * m.meaninertia * (float)max(nv, 1);
       la.q0 = qg[0]; la.q1 = qg[1]; la.q2 = qg[2];
-      alpha = ls_iterative(la);
+      alpha = ls_iterative<ELL>(la);
     }
     if (alpha == 0.f) break;
 #pragma unroll 1
@@ -637,7 +775,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     __syncwarp();
     const float old = cost;
     gauss = gauss_term(c);
-    cost = constraint_cost<T, FRIC>(c, c.Jaref()) + gauss;
+    cost = constraint_cost<T, V>(c, c.Jaref()) + gauss;
     iter++;
     if (scale * (old - cost) < m.tolerance) withH = false;     // converged: one more pass for the final forces only
   }
@@ -645,7 +783,18 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
 #pragma unroll 1
   for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qacc()[i]; g_qfc[i] = c.qfc()[i]; }
 #pragma unroll 1
-  for (int r = lane; r < c.nefc; r += 32) efc_force[r] = row_force<T, FRIC>(c, r, c.Jaref()[r]);
+  for (int r = lane; r < c.nefc; r += 32) {
+    if (ELL && c.ekind()[r]) {
+      if (c.ekind()[r] == 1) {
+        const float x0 = c.Jaref()[r], x1 = c.Jaref()[r + 1], x2 = c.Jaref()[r + 2];
+        float f[3];
+        cone_force<T>(c, r, cone_eval<T>(c, r, x0, x1, x2), x0, x1, x2, f);
+        efc_force[r] = f[0]; efc_force[r + 1] = f[1]; efc_force[r + 2] = f[2];
+      }
+      continue;
+    }
+    efc_force[r] = row_force<T, V>(c, r, c.Jaref()[r]);
+  }
   if (lane == 0) { d.solver_niter[w] = iter; d.solver_cost[w] = cost; }
 }
 
@@ -667,16 +816,18 @@ static int tile_for(int nv) { return b2s_tile_for(nv); }
 void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + SOLVE_WARPS - 1) / SOLVE_WARPS;
   const size_t smem = smem_solve(m, d);
-  if (m.fric) { SOLVE_DISPATCH((k_solve<T, true><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
-  else { SOLVE_DISPATCH((k_solve<T, false><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  if (m.cone == B2S_CONE_ELLIPTIC) { SOLVE_DISPATCH((k_solve<T, 3><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  else if (m.fric) { SOLVE_DISPATCH((k_solve<T, 1><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  else { SOLVE_DISPATCH((k_solve<T, 0><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   b2s_count_launch();
 }
 size_t smem_solve(const ModelDev& m, const DataDev& d) {
-  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv)) * sizeof(float);
+  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), m.cone == B2S_CONE_ELLIPTIC) * sizeof(float);
 }
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;
-  if (m.fric) { SOLVE_DISPATCH((f = (const void*)k_solve<T, true>)); }
-  else { SOLVE_DISPATCH((f = (const void*)k_solve<T, false>)); }
+  if (m.cone == B2S_CONE_ELLIPTIC) { SOLVE_DISPATCH((f = (const void*)k_solve<T, 3>)); }
+  else if (m.fric) { SOLVE_DISPATCH((f = (const void*)k_solve<T, 1>)); }
+  else { SOLVE_DISPATCH((f = (const void*)k_solve<T, 0>)); }
   return f;
 }

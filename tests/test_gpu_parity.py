@@ -568,9 +568,11 @@ def test_zero_copy_views_and_readonly_struct(g1):
 def test_unsupported_features_raise():
   from asimov_mjlab_b200 import engine
   m = fx.compile_xml(fx.SPHERE_DROP)
-  m.opt.cone = 1
-  with pytest.raises(engine.BackendError, match="pyramidal"):
+  m.opt.cone = 1        # elliptic cones: condim 1 and 3 only
+  m.geom_condim = m.geom_condim.copy(); m.geom_condim[:] = 4
+  with pytest.raises(engine.BackendError, match="condim"):
     engine.put_model(m)
+  m.geom_condim[:] = 3
   m.opt.cone = 0
   m.opt.solver = 0        # PGS (dual solver): not built; Newton (2) and CG (1) are
   with pytest.raises(engine.BackendError, match="PGS"):
@@ -878,3 +880,51 @@ def test_cylinder_and_ellipsoid_contacts_match_oracle():
   engine.step(M, D, 400)
   qp = D.qpos.cpu().numpy()
   assert np.isfinite(qp).all() and float(D.qvel.abs().max()) < 100.0 and qp[:, 2::7].min() > 0.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ls_parallel", [True, False])
+def test_g1_elliptic_cone_matches_oracle(g1, ls_parallel):
+  """cone="elliptic" (reference sim.py:51): contact-frame rows, cone zones and cone Hessian in the matrix-free solver
+  against the oracle -- forward pass on contact-rich G1 states (row counts, forces, qacc), then a short horizon; every
+  contact force lies in its friction cone."""
+  import copy
+  import torch
+  W = 16
+  qpos, qvel, ctrl = g1_states(g1, W, seed=21)
+  m = copy.copy(g1); m.opt = copy.copy(g1.opt); m.opt.cone = 1
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, ls_parallel)
+  assert M.opt.cone == 1
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  _check_counts(D, worlds)
+  nefc = D.nefc.cpu().numpy(); ty = D.efc_type.cpu().numpy()
+  assert (ty == 6).sum() > 100 and (ty == 5).sum() == 0
+  for f, tol in (("qacc", 1e-3), ("qfrc_constraint", 1e-3), ("sensordata", 2e-3)):
+    assert _rel_err(D, worlds, f) < tol, f
+  fo = D.efc_force.cpu().numpy(); Dg = D.efc_D.cpu().numpy(); cf = D.contact_friction.cpu().numpy(); eid = D.efc_id.cpu().numpy()
+  nit_g = D.solver_niter.cpu().numpy(); nit_o = np.array([int(w["solver_niter"][0]) for w in worlds])
+  assert np.abs(nit_g - nit_o).max() <= (1 if ls_parallel else 3)
+  ncone = 0
+  for i, w in enumerate(worlds):
+    n = int(nefc[i])
+    if n == 0:
+      continue
+    assert np.allclose(Dg[i, :n], w["efc_D"][:n], rtol=5e-4)
+    assert np.abs(fo[i, :n] - w["efc_force"][:n]).max() < 2e-3 * (1 + np.abs(w["efc_force"][:n]).max())
+    r = 0
+    while r < n:
+      if ty[i, r] == 6:
+        mu = cf[i, eid[i, r], 0]
+        assert fo[i, r] >= 0 and np.hypot(fo[i, r + 1], fo[i, r + 2]) <= mu * fo[i, r] * (1 + 1e-4) + 1e-5
+        ncone += 1; r += 3
+      else:
+        r += 1
+  assert ncone > 30
+  engine.step(M, D, 10)
+  torch.cuda.synchronize()
+  for w in worlds:
+    orc.step(w, 10)
+  _check_counts(D, worlds)
+  assert _rel_err(D, worlds, "qpos") < 2e-4 and _rel_err(D, worlds, "qvel") < 2e-2
