@@ -708,7 +708,10 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   const float scale = 1.0f / (m.meaninertia * (float)max(nv, 1));
   int iter = 0;
   bool withH = true, haveL = false;
-  const bool newton = m.solver == B2S_SOL_NEWTON;
+  // variant bit 4: the exact line search and the CG solver are compiled in; without it the kernel is Newton + parallel
+  // line search only (the reference's default, sim.py:55,91) and ~1 k instructions of cold code smaller
+  constexpr bool FULL_OPTS = (V & 4) != 0;
+  const bool newton = !FULL_OPTS || m.solver == B2S_SOL_NEWTON;
   if (!newton) {
     // CG (mj_solPrimal without the Hessian): the preconditioner is M^-1, so M is factorised once (H storage = 0 + M)
     float4* h4 = reinterpret_cast<float4*>(c.H());
@@ -759,7 +762,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     for (int i = lane; i < nv; i += 32) { g1 += c.search()[i] * (c.Ma()[i] - c.qfs()[i]); g2 += c.search()[i] * c.Mv()[i]; }
     float qg[3] = {gauss, warp_sum(g1), 0.5f * warp_sum(g2)};
     float alpha;
-    if (m.ls_parallel) alpha = ls_parallel<T, V>(c, m, qg);
+    if (!FULL_OPTS || m.ls_parallel) alpha = ls_parallel<T, V>(c, m, qg);
     else {
       LsArgs la;
       la.Jaref = c.Jaref(); la.Jv = c.Jv(); la.D = c.D(); la.search = c.search(); la.nefc = c.nefc; la.nf = c.nf; la.fl = c.fl(); la.frf = c.frf(); la.ekind = ELL ? c.ekind() : nullptr; la.efri = ELL ? c.efri() : nullptr; la.nv = nv; la.lane = lane;
@@ -816,17 +819,21 @@ static int tile_for(int nv) { return b2s_tile_for(nv); }
 void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + SOLVE_WARPS - 1) / SOLVE_WARPS;
   const size_t smem = smem_solve(m, d);
-  if (m.cone == B2S_CONE_ELLIPTIC) { SOLVE_DISPATCH((k_solve<T, 3><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  if (!m.ls_parallel || m.solver != B2S_SOL_NEWTON) { SOLVE_DISPATCH((k_solve<T, 7><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  else if (m.cone == B2S_CONE_ELLIPTIC) { SOLVE_DISPATCH((k_solve<T, 3><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   else if (m.fric) { SOLVE_DISPATCH((k_solve<T, 1><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   else { SOLVE_DISPATCH((k_solve<T, 0><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   b2s_count_launch();
 }
 size_t smem_solve(const ModelDev& m, const DataDev& d) {
-  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), m.cone == B2S_CONE_ELLIPTIC) * sizeof(float);
+  // the elliptic per-row arrays exist in every instantiation that has the elliptic code (variants 3 and 7)
+  const bool ell = m.cone == B2S_CONE_ELLIPTIC || !m.ls_parallel || m.solver != B2S_SOL_NEWTON;
+  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), ell) * sizeof(float);
 }
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;
-  if (m.cone == B2S_CONE_ELLIPTIC) { SOLVE_DISPATCH((f = (const void*)k_solve<T, 3>)); }
+  if (!m.ls_parallel || m.solver != B2S_SOL_NEWTON) { SOLVE_DISPATCH((f = (const void*)k_solve<T, 7>)); }
+  else if (m.cone == B2S_CONE_ELLIPTIC) { SOLVE_DISPATCH((f = (const void*)k_solve<T, 3>)); }
   else if (m.fric) { SOLVE_DISPATCH((f = (const void*)k_solve<T, 1>)); }
   else { SOLVE_DISPATCH((f = (const void*)k_solve<T, 0>)); }
   return f;
