@@ -44,8 +44,8 @@ def alg_bytes(m, friction_geoms):
   w = m.nq + 3 * m.nv + 1 + m.nsensordata + (3 + 4 + 3 + 6) * nb + 12 * m.nsite
   return 4 * (r + w + 3 * friction_geoms)
 # DRAM traffic of one sub-step (7 stage kernels), dram__bytes_read.sum + dram__bytes_write.sum from the `ncu --set full`
-# capture profiles/step_r1i_metrics.txt (G1-flat, 4096 worlds): 117 512 960 B read + 1 043 456 B written
-NCU_TRAFFIC = {("g1_flat", 4096): (118556416, "profiles/step_r1i_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step)")}
+# capture profiles/step_r1k_metrics.txt (G1-flat, 4096 worlds): 118 477 568 B read + 978 432 B written
+NCU_TRAFFIC = {("g1_flat", 4096): (119456000, "profiles/step_r1k_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step)")}
 DECIMATION = 4
 RESET_PERIOD_STEPS = 250            # reset every 1000 sub-steps, forward() inside the timed region
 
@@ -60,6 +60,7 @@ def parse():
   ap.add_argument("--cpu-baseline", type=int, default=1)
   ap.add_argument("--ls-parallel", type=int, default=1)
   ap.add_argument("--workload", default="g1_flat", choices=sorted(WORKLOADS))
+  ap.add_argument("--cone", default="pyramidal", choices=["pyramidal", "elliptic"], help="friction cone (the reference's default is pyramidal)")
   return ap.parse_args()
 
 
@@ -108,10 +109,11 @@ class ClockSampler:
     return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def load_model(ls_parallel=1, workload="g1_flat"):
+def load_model(ls_parallel=1, workload="g1_flat", cone="pyramidal"):
   from asimov_mjlab_b200 import scenes
   m = scenes.load_asset(WORKLOADS[workload][0])
   m.opt.ls_parallel = bool(ls_parallel)
+  m.opt.cone = 1 if cone == "elliptic" else 0
   return m
 
 
@@ -161,7 +163,7 @@ def run_reference(args):
   rank = int(os.environ.get("RANK", "0"))
   if rank != 0:
     return
-  m = load_model(args.ls_parallel, args.workload)
+  m = load_model(args.ls_parallel, args.workload, args.cone)
   cores = os.cpu_count() or 1
   nworld = 16 * cores
   # warm-up then K timed steps, each a bounded sample: one decimation of `nworld` worlds
@@ -197,9 +199,9 @@ def run_b200(args):
   if world > 1:
     dist.init_process_group("nccl", device_id=torch.device(dev))
   E = args.envs
-  m = load_model(args.ls_parallel, args.workload)
+  m = load_model(args.ls_parallel, args.workload, args.cone)
   cfg = SimulationCfg(nconmax=50, njmax=300, ls_parallel=bool(args.ls_parallel),
-                      mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20))
+                      mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20, cone=args.cone))
   sim = Simulation(E, cfg, m, dev)
   M, D = sim.model, sim.data
   # foot-friction domain randomisation ON (per-world Model reads stay honest; velocity_env_cfg.py:230-240)
@@ -323,7 +325,7 @@ def run_b200(args):
     "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
     "config": {"workload": WORKLOADS[args.workload][1],
                "envs_per_gpu": E, "decimation": DECIMATION, "substeps_per_step": DECIMATION, "timestep": 0.005,
-               "nconmax": 50, "njmax": 300, "iterations": 10, "ls_iterations": 20, "ls_parallel": bool(args.ls_parallel),
+               "nconmax": 50, "njmax": 300, "iterations": 10, "ls_iterations": 20, "ls_parallel": bool(args.ls_parallel), "cone": args.cone,
                "friction_dr": True, "resets_in_timed_region": n_resets, "parallelism": f"env-shard x{world}, no collective on the step path",
                "l2": f"working set {D.bytes / 2**20:.0f} MiB per GPU (> 126 MB L2); no explicit flush"},
     "e2e": {"value": e2e_value, "unit": "physics sub-steps/s", "h2d_bytes_per_step": int(E * m.nu * 4),
