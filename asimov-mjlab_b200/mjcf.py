@@ -544,6 +544,8 @@ class _Parser:
             setattr(j, k, math.radians(float(a[k])) if ang else float(a[k]))
         for k in ("stiffness", "damping", "armature", "frictionloss", "margin"):
           if k in a: setattr(j, k, float(a[k]))
+        if "solreffriction" in a or "solimpfriction" in a:
+          raise NotImplementedError("joint solreffriction / solimpfriction are not supported (friction-loss rows use MuJoCo's defaults)")
         if "solreflimit" in a: j.solreflimit = _floats(a["solreflimit"], 2)
         if "solimplimit" in a:
           v = _floats(a["solimplimit"]); j.solimplimit[:len(v)] = v
