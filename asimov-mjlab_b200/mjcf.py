@@ -687,6 +687,40 @@ def _geom_mass_inertia(g: GeomSpec, size):
   return mass, unit*mass
 
 
+def mesh_mass_properties(verts: np.ndarray):
+  """Volume, centre of mass and inertia tensor about it (unit density) of the convex hull of `verts`, by summing the
+  tetrahedra (c0, a, b, c) over the hull's triangles: integral x x^T over a tetrahedron with one vertex at the origin is
+  det/120 (a a^T + b b^T + c c^T + (a+b+c)(a+b+c)^T).  (MuJoCo integrates the mesh itself; for convex meshes the two
+  coincide, and collision uses the hull anyway.)"""
+  from scipy.spatial import ConvexHull
+  v = np.asarray(verts, float)
+  hull = ConvexHull(v)
+  c0 = v[hull.vertices].mean(axis=0)
+  vol, com, C = 0.0, np.zeros(3), np.zeros((3, 3))
+  for tri in hull.simplices:
+    a, b, c = v[tri] - c0
+    d = abs(float(np.linalg.det(np.stack([a, b, c]))))
+    S = a + b + c
+    vol += d/6; com += d/24*S
+    C += d/120*(np.outer(a, a) + np.outer(b, b) + np.outer(c, c) + np.outer(S, S))
+  com /= vol
+  Cc = C - vol*np.outer(com, com)
+  return vol, com + c0, np.trace(Cc)*np.eye(3) - Cc
+
+
+def _mat2quat(R):
+  """Unit quaternion (w, x, y, z) of a proper rotation matrix."""
+  t = np.trace(R)
+  if t > 0:
+    s = math.sqrt(t + 1.0)*2; q = [0.25*s, (R[2, 1] - R[1, 2])/s, (R[0, 2] - R[2, 0])/s, (R[1, 0] - R[0, 1])/s]
+  else:
+    i = int(np.argmax(np.diag(R))); j, k = (i + 1) % 3, (i + 2) % 3
+    s = math.sqrt(1.0 + R[i, i] - R[j, j] - R[k, k])*2
+    q = [0.0, 0.0, 0.0, 0.0]
+    q[0] = (R[k, j] - R[j, k])/s; q[1 + i] = 0.25*s; q[1 + j] = (R[j, i] + R[i, j])/s; q[1 + k] = (R[k, i] + R[i, k])/s
+  q = np.array(q); return q/np.linalg.norm(q)
+
+
 def load_stl(path) -> np.ndarray:
   """Vertices of a binary STL (80-byte header, uint32 count, 50 bytes per triangle)."""
   with open(path, "rb") as f:
@@ -837,7 +871,18 @@ def _compile(spec: Spec) -> HostModel:
       G["rbound"].append(rb); G["dataid"].append(dataid)
       if t == 7:
         if b.inertial is None and not is_static[i] and (g.mass or (g.mass is None and g.density > 0)):
-          raise NotImplementedError(f"mesh geom {g.name!r} contributes inertia but mesh inertia is not supported (give the body an <inertial>)")
+          # mesh inertia: uniform density over the convex hull, principal axes found by diagonalising the tensor
+          if g.mesh not in spec.meshes:
+            raise ValueError(f"unknown mesh {g.mesh!r}")
+          ms = spec.meshes[g.mesh]
+          mv = np.asarray(ms.vertex if ms.vertex is not None else load_stl(ms.file), float)*np.asarray(ms.scale, float)[None, :]
+          vol, mcom, I = mesh_mass_properties(mv)
+          mass = g.mass if g.mass is not None else g.density*vol
+          ev, R = np.linalg.eigh(I*(mass/vol))
+          if np.linalg.det(R) < 0:
+            R[:, 2] = -R[:, 2]
+          gq = np.array(quat, float)
+          acc.append((mass, ev, np.array(pos) + quat2mat(gq) @ mcom, quat_mul(gq, _mat2quat(R))))
         continue
       if t in (0, 1):
         continue

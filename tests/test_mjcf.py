@@ -106,9 +106,12 @@ def test_unsupported_mjcf_raises():
     Spec.from_string("<mujoco><tendon><spatial name='t'/></tendon></mujoco>")
   with pytest.raises(ValueError):           # colliding mesh geom whose mesh asset is missing
     Spec.from_string("<mujoco><worldbody><body><geom type='mesh' mesh='m'/></body></worldbody></mujoco>").compile()
-  with pytest.raises(NotImplementedError):  # mesh inertia: bodies with mesh geoms need an explicit <inertial>
-    Spec.from_string("<mujoco><asset><mesh name='m' vertex='0 0 0 1 0 0 0 1 0 0 0 1'/></asset><worldbody><body><joint/>"
-                     "<geom type='mesh' mesh='m'/></body></worldbody></mujoco>").compile()
+  # mesh inertia is computed from the hull: the unit tetrahedron at density 1000 weighs 1000 / 6
+  mt = Spec.from_string("<mujoco><asset><mesh name='m' vertex='0 0 0 1 0 0 0 1 0 0 0 1'/></asset><worldbody><body><joint/>"
+                        "<geom type='mesh' mesh='m'/></body></worldbody></mujoco>").compile()
+  assert mt.body_mass[1] == pytest.approx(1000.0 / 6.0)
+  with pytest.raises(NotImplementedError):  # friction-loss rows use MuJoCo's default solver parameters
+    Spec.from_string("<mujoco><worldbody><body><joint frictionloss='1' solreffriction='0.01 1'/><geom size='0.1'/></body></worldbody></mujoco>")
 
 
 def test_mesh_hull_and_hfield_assets_compile():
@@ -166,3 +169,33 @@ def test_env_origin_grid_matches_reference_formula():
   o = scenes.env_origins_grid(16, 2.5)
   assert o.shape == (16, 3) and np.allclose(o.mean(axis=0), 0)
   assert sorted(set(np.round(o[:, 0], 6))) == [-3.75, -1.25, 1.25, 3.75]
+
+
+def test_mesh_inertia_from_the_convex_hull():
+  """A body whose only geom is a mesh gets its mass, centre of mass and principal inertia from the mesh's convex hull
+  (uniform density): a box-shaped mesh reproduces the box closed forms, wherever it sits in the geom frame; a tetrahedron
+  matches the textbook volume / centroid."""
+  from asimov_mjlab_b200.mjcf import mesh_mass_properties
+  hx, hy, hz = 0.1, 0.2, 0.05
+  off = np.array([0.03, -0.02, 0.01])
+  v = np.array([[sx * hx, sy * hy, sz * hz] for sx in (-1, 1) for sy in (-1, 1) for sz in (-1, 1)], float) + off
+  vol, com, I = mesh_mass_properties(v)
+  assert np.isclose(vol, 8 * hx * hy * hz) and np.allclose(com, off)
+  assert np.allclose(I, np.diag([(hy**2 + hz**2) / 3, (hx**2 + hz**2) / 3, (hx**2 + hy**2) / 3]) * vol, atol=1e-12)
+  tet = np.array([[0, 0, 0], [1, 0, 0], [0, 2, 0], [0, 0, 3.0]])
+  vol, com, _ = mesh_mass_properties(tet)
+  assert np.isclose(vol, 1.0) and np.allclose(com, [0.25, 0.5, 0.75])
+  verts = " ".join(f"{x:.6f}" for x in v.reshape(-1))
+  xml = f"""
+  <mujoco>
+    <asset><mesh name="brick" vertex="{verts}"/></asset>
+    <worldbody>
+      <body name="a" pos="0 0 1"><freejoint/><geom type="mesh" mesh="brick" density="500" pos="0.1 0 0" quat="0.7071068 0 0 0.7071068"/></body>
+      <body name="b" pos="0 1 1"><freejoint/><geom type="box" size="{hx} {hy} {hz}" density="500" pos="{0.1 - off[1]} {off[0]} {off[2]}" quat="0.7071068 0 0 0.7071068"/></body>
+    </worldbody>
+  </mujoco>"""
+  m = fx.compile_xml(xml)
+  ia, ib = m.names["body"].index("a"), m.names["body"].index("b")
+  assert np.isclose(m.body_mass[ia], m.body_mass[ib]) and np.isclose(m.body_mass[ia], 500 * 8 * hx * hy * hz)
+  assert np.allclose(m.body_ipos[ia], m.body_ipos[ib], atol=1e-9)
+  assert np.allclose(np.sort(m.body_inertia[ia]), np.sort(m.body_inertia[ib]), rtol=1e-9)
