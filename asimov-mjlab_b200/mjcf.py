@@ -425,9 +425,21 @@ class _Parser:
           spec.meshes[name] = MeshSpec(name=name, file=path, vertex=vert, scale=_floats(el.get("scale", "1 1 1"), 3))
         elif el.tag == "hfield":
           if el.get("file"):
-            raise NotImplementedError("<hfield file=...> is not supported (inline elevation only)")
-          nrow, ncol = int(el.get("nrow")), int(el.get("ncol"))
-          data = np.array(_floats(el.get("elevation"))).reshape(nrow, ncol) if el.get("elevation") else np.zeros((nrow, ncol))
+            # MuJoCo's own binary height-field format: int32 nrow, int32 ncol, then nrow * ncol float32 (PNG files need an
+            # image decoder that is not available here)
+            f = el.get("file")
+            path = next((c for c in (os.path.join(self.basedir, self.meshdir, f), os.path.join(self.basedir, f)) if os.path.exists(c)), f)
+            if path.lower().endswith(".png"):
+              raise NotImplementedError("<hfield file=*.png> is not supported (binary .bin height fields or inline elevation)")
+            with open(path, "rb") as fh:
+              raw = fh.read()
+            nrow, ncol = (int(x) for x in np.frombuffer(raw, "<i4", 2))
+            if len(raw) < 8 + 4*nrow*ncol:
+              raise ValueError(f"{path}: truncated height field")
+            data = np.frombuffer(raw, "<f4", nrow*ncol, 8).astype(float).reshape(nrow, ncol)
+          else:
+            nrow, ncol = int(el.get("nrow")), int(el.get("ncol"))
+            data = np.array(_floats(el.get("elevation"))).reshape(nrow, ncol) if el.get("elevation") else np.zeros((nrow, ncol))
           spec.add_hfield(el.get("name", ""), data, _floats(el.get("size"), 4))
     wb = root.find("worldbody")
     if wb is not None:

@@ -199,3 +199,15 @@ def test_mesh_inertia_from_the_convex_hull():
   assert np.isclose(m.body_mass[ia], m.body_mass[ib]) and np.isclose(m.body_mass[ia], 500 * 8 * hx * hy * hz)
   assert np.allclose(m.body_ipos[ia], m.body_ipos[ib], atol=1e-9)
   assert np.allclose(np.sort(m.body_inertia[ia]), np.sort(m.body_inertia[ib]), rtol=1e-9)
+
+
+def test_hfield_binary_file(tmp_path):
+  """<hfield file=...> in MuJoCo's binary format (int32 nrow, int32 ncol, float32 data) equals the inline elevation."""
+  elev = np.arange(12, dtype=np.float32).reshape(3, 4)
+  p = tmp_path / "field.bin"
+  p.write_bytes(np.array([3, 4], "<i4").tobytes() + elev.astype("<f4").tobytes())
+  a = Spec.from_string(f"<mujoco><asset><hfield name='h' file='{p}' size='2 1.5 0.5 0.1'/></asset></mujoco>")
+  b = Spec.from_string("<mujoco><asset><hfield name='h' nrow='3' ncol='4' size='2 1.5 0.5 0.1' elevation='" + " ".join(str(float(x)) for x in elev.reshape(-1)) + "'/></asset></mujoco>")
+  assert a.hfields["h"].nrow == 3 and a.hfields["h"].ncol == 4 and np.allclose(a.hfields["h"].data, b.hfields["h"].data)
+  with pytest.raises(NotImplementedError):
+    Spec.from_string("<mujoco><asset><hfield name='h' file='x.png' size='1 1 1 1'/></asset></mujoco>")
