@@ -225,7 +225,8 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   std::vector<int> grid_geoms, dyn_geoms;
   for (int g = 0; g < s->ngeom; g++) {
     const bool collides = (s->geom_contype[g] | s->geom_conaffinity[g]) != 0;
-    const bool stat = s->body_weldid[s->geom_bodyid[g]] == 0;
+    // mocap bodies are welded to the world but move: their geoms stay in the per-step pair table, never in the grid
+    const bool stat = s->body_weldid[s->geom_bodyid[g]] == 0 && s->body_mocapid[s->geom_bodyid[g]] < 0;
     if (collides && stat && s->geom_type[g] != B2S_GEOM_PLANE) grid_geoms.push_back(g);
     if (collides && !stat) dyn_geoms.push_back(g);
   }
@@ -581,6 +582,13 @@ extern "C" int b2s_model_expand(b2s_model* m, const char* name, int nworld) {
   if (!r.wf) return fail(std::string("model field ") + name + " cannot vary per world");
   if (r.wf->wstride != 0) return 0;   // already expanded
   if (r.elems == 0) return 0;
+  {
+    // the static-geom grid (terrain broadphase) is built once from the compile-time poses: a per-world pose of those geoms
+    // would leave it stale, so refuse instead of colliding against the wrong boxes
+    const std::string n(name);
+    if (m->dev.ngrid > 0 && (n == "geom_pos" || n == "geom_quat" || n == "body_pos" || n == "body_quat"))
+      return fail("model field " + n + " cannot vary per world: this model's static terrain geoms are indexed by a broadphase grid built at put_model");
+  }
   CU(cudaSetDevice(m->device));
   float* p = nullptr;
   CU(cudaMalloc(&p, (size_t)nworld * r.elems * sizeof(float)));
@@ -726,6 +734,11 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
       if (e.smem > 48 * 1024) { delete D; return fail("cannot raise the dynamic shared-memory limit"); }
     }
   }
+  {
+    size_t need = 0;
+    const int rc2 = solve_prepare_all(md, d, &need);
+    if (rc2) { delete D; return fail(rc2 == -1 ? "model too large for the solver's shared-memory working set (" + std::to_string(need) + " B per CTA)" : std::string("cannot raise the solver's dynamic shared-memory limit")); }
+  }
   for (auto& e : D->ev) cudaEventCreate(&e);
   D->have_ev = true;
   // frames of everything attached to static bodies, once
@@ -735,13 +748,21 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   *out = D;
   return 0;
 }
+// a launch that failed (bad configuration, shared-memory limit, ...) is reported, never silent: cudaPeekAtLastError is legal
+// during stream capture and does not synchronise
+static int launch_status(const char* what) {
+  const cudaError_t e = cudaPeekAtLastError();
+  if (e == cudaSuccess) return 0;
+  cudaGetLastError();
+  return fail(std::string(what) + ": kernel launch failed: " + cudaGetErrorString(e));
+}
 // Recompute the frames of geoms / sites on static bodies (after writing body_pos, body_quat, geom_pos, geom_quat,
 // site_pos or site_quat of a static body, e.g. per-world terrain randomisation).  step/forward never touch them.
 extern "C" int b2s_refresh_static(const b2s_model* m, b2s_data* d, void* stream) {
   if (!m || !d) return fail("null argument");
   launch_position(m->dev, d->dev, (cudaStream_t)stream);
   launch_static_frames(m->dev, d->dev, (cudaStream_t)stream);
-  return 0;
+  return launch_status("b2s_refresh_static");
 }
 extern "C" int b2s_data_destroy(b2s_data* d) { delete d; return 0; }
 extern "C" int b2s_data_field(b2s_data* d, const char* name, b2s_field_info* out) {
@@ -783,7 +804,7 @@ static void run_forward(const ModelDev& m, const DataDev& d, cudaStream_t st) {
 extern "C" int b2s_forward(const b2s_model* m, b2s_data* d, void* stream) {
   if (!m || !d) return fail("null argument");
   run_forward(m->dev, d->dev, (cudaStream_t)stream);
-  return 0;
+  return launch_status("b2s_forward");
 }
 extern "C" int b2s_step_n(const b2s_model* m, b2s_data* d, int nsub, void* stream) {
   if (!m || !d) return fail("null argument");
@@ -791,7 +812,7 @@ extern "C" int b2s_step_n(const b2s_model* m, b2s_data* d, int nsub, void* strea
     run_forward(m->dev, d->dev, (cudaStream_t)stream);
     launch_integrate(m->dev, d->dev, (cudaStream_t)stream);
   }
-  return 0;
+  return launch_status("b2s_step_n");
 }
 extern "C" int b2s_step(const b2s_model* m, b2s_data* d, void* stream) { return b2s_step_n(m, d, 1, stream); }
 
@@ -803,7 +824,7 @@ extern "C" int b2s_step_host(const b2s_model* m, b2s_data* d, const float* ctrl_
   const size_t W = (size_t)d->dev.nworld;
   CU(cudaSetDevice(m->device));
   if (ctrl_host && md.nu) CU(cudaMemcpyAsync(d->dev.ctrl, ctrl_host, W * md.nu * 4, cudaMemcpyHostToDevice, st));
-  b2s_step_n(m, d, nsub, stream);
+  if (b2s_step_n(m, d, nsub, stream) != 0) return -1;
   if (qpos_host) CU(cudaMemcpyAsync(qpos_host, d->dev.qpos, W * md.nq * 4, cudaMemcpyDeviceToHost, st));
   if (qvel_host) CU(cudaMemcpyAsync(qvel_host, d->dev.qvel, W * md.nv * 4, cudaMemcpyDeviceToHost, st));
   if (sensordata_host && md.nsensordata) CU(cudaMemcpyAsync(sensordata_host, d->dev.sensordata, W * md.nsensordata * 4, cudaMemcpyDeviceToHost, st));

@@ -830,6 +830,27 @@ size_t smem_solve(const ModelDev& m, const DataDev& d) {
   const bool ell = m.cone == B2S_CONE_ELLIPTIC || !m.ls_parallel || m.solver != B2S_SOL_NEWTON;
   return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), ell) * sizeof(float);
 }
+// Raise the dynamic shared-memory limit of EVERY solver instantiation of this model's tile size to the largest request any
+// option combination can make (the elliptic variants carry 2 njmax extra floats): Model.opt.cone / solver / ls_parallel and a
+// per-world dof_frictionloss can switch the instantiation after put_data.
+template <int T>
+static int solve_set_attr(int smem) {
+  int rc = 0;
+  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
+  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
+  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
+  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
+  return rc;
+}
+int solve_prepare_all(const ModelDev& m, const DataDev& d, size_t* need) {
+  const size_t smem = (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), 1) * sizeof(float);
+  *need = smem;
+  if (smem > 227 * 1024) return -1;
+  int rc = 0;
+  SOLVE_DISPATCH(rc = solve_set_attr<T>((int)smem));
+  if (rc) { cudaGetLastError(); return smem > 48 * 1024 ? -2 : 0; }
+  return 0;
+}
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;
   if (!m.ls_parallel || m.solver != B2S_SOL_NEWTON) { SOLVE_DISPATCH((f = (const void*)k_solve<T, 7>)); }

@@ -26,7 +26,8 @@ import numpy as np
 from . import abi
 
 _LIB = None
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200sim.so")
+# B2S_LIB: development override (kernel experiments build variant libraries next to the shipped one)
+_LIB_PATH = os.environ.get("B2S_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200sim.so")
 
 
 class BackendError(RuntimeError):
@@ -189,6 +190,11 @@ class _Struct:
   def field_names(self):
     return tuple(self.__dict__["_names"])
 
+  @property
+  def __dataclass_fields__(self):
+    """Field-name mapping, as on the reference backend's dataclasses (sim/randomization.py:51-54 iterates it)."""
+    return {n: None for n in sorted(self.__dict__["_names"])}
+
 
 class Model(_Struct):
   def __init__(self, handle, device, dims, solver, host_model):
@@ -269,6 +275,9 @@ def _device_index(device) -> int:
   return dev.index if dev.index is not None else torch.cuda.current_device()
 
 
+_LAST_MODEL: dict = {}      # id(host model) -> weakref to the Model put_model returned last (put_data's default)
+
+
 def put_model(mjm, device="cuda:0") -> Model:
   """Upload a compiled model (HostModel or mujoco.MjModel-like).  Raises on unsupported features."""
   idx = _device_index(device)
@@ -281,17 +290,23 @@ def put_model(mjm, device="cuda:0") -> Model:
   if rg is not None and len(rg):
     import torch
     m.geom_rgba[:] = torch.as_tensor(np.asarray(rg, np.float32).reshape(1, -1, 4), device=m._device)
+  import weakref
+  _LAST_MODEL[id(mjm)] = weakref.ref(m)
   return m
 
 
 def put_data(mjm, mjd, nworld: int, nconmax: int | None = None, njmax: int | None = None, *, model: Model | None = None) -> Data:
   """Allocate per-world arrays and initialise every world from `mjd`.
 
-  The reference signature is put_data(mjm, mjd, nworld, nconmax, njmax) (sim.py:120-126); the device
-  Model it belongs to is passed as `model=` (it carries the device and the shared-memory configuration).
+  The reference signature is put_data(mjm, mjd, nworld, nconmax, njmax) (sim.py:120-126) and works as is: the device Model
+  is the one the last put_model(mjm) returned (it carries the device and the shared-memory configuration); `model=` names
+  another one explicitly (several devices / several uploads of one host model).
   """
   if model is None:
-    raise BackendError("put_data needs model=<Model returned by put_model>")
+    ref = _LAST_MODEL.get(id(mjm))
+    model = ref() if ref is not None else None
+    if model is None:
+      raise BackendError("put_data: call put_model(mjm) first (or pass model=<Model returned by put_model>)")
   st, keep = abi.make_state_desc(mjm, mjd)
   h = C.c_void_p()
   _check(lib().b2s_data_create(model._h.ptr, C.byref(st), int(nworld), int(nconmax or 0), int(njmax or 0), C.byref(h)))

@@ -55,13 +55,84 @@ class MujocoCfg:
     o.ls_tolerance = self.ls_tolerance
 
 
+@dataclass
+class NanGuardCfg:
+  """Field-for-field the reference's NanGuardCfg (utils/nan_guard.py:16-23)."""
+  enabled: bool = False
+  buffer_size: int = 100
+  output_dir: str = "/tmp/mjlab/nan_dumps"
+  max_envs_to_dump: int = 5
+
+
+class NanGuard:
+  """Rolling buffer of (qpos, qvel) snapshots, dumped to an .npz when a step leaves NaN / Inf in qpos, qvel, qacc or
+  qacc_warmstart (reference utils/nan_guard.py:26-160: same fields, same trigger; the snapshot is the physics state as plain
+  arrays instead of mj_getState's packed vector).  Disabled = every method is a no-op."""
+
+  def __init__(self, cfg: NanGuardCfg, num_envs: int):
+    self.enabled, self.num_envs = cfg.enabled, num_envs
+    if not self.enabled:
+      return
+    from collections import deque
+    self.cfg = cfg
+    self.buffer = deque(maxlen=cfg.buffer_size)
+    self.step_counter = 0
+    self._dumped = False
+
+  @staticmethod
+  def detect_nans(data):
+    import torch
+    mask = torch.zeros(data.qpos.shape[0], dtype=torch.bool, device=data.qpos.device)
+    for t in (data.qpos, data.qvel, data.qacc, data.qacc_warmstart):
+      mask |= ~torch.isfinite(t).all(dim=-1)
+    return mask
+
+  def capture(self, data) -> None:
+    if not self.enabled:
+      return
+    self.buffer.append({"step": self.step_counter, "qpos": data.qpos.cpu().numpy().copy(), "qvel": data.qvel.cpu().numpy().copy()})
+    self.step_counter += 1
+
+  def check_and_dump(self, data) -> bool:
+    if not self.enabled or self._dumped:
+      return False
+    mask = self.detect_nans(data)
+    if not bool(mask.any()):
+      return False
+    import os
+    from datetime import datetime
+    ids = mask.nonzero().reshape(-1).cpu().numpy().tolist()[: self.cfg.max_envs_to_dump]
+    os.makedirs(self.cfg.output_dir, exist_ok=True)
+    out = {}
+    for item in self.buffer:
+      out[f"qpos_step_{item['step']:06d}"] = item["qpos"][ids]
+      out[f"qvel_step_{item['step']:06d}"] = item["qvel"][ids]
+    out["_metadata"] = np.array({"num_envs_total": self.num_envs, "nan_env_ids": ids, "detection_step": self.step_counter}, dtype=object)
+    self.dump_path = os.path.join(self.cfg.output_dir, f"nan_dump_{datetime.now().strftime('%Y%m%d_%H%M%S')}.npz")
+    np.savez_compressed(self.dump_path, **out)
+    self._dumped = True
+    return True
+
+  def watch(self, data):
+    from contextlib import contextmanager
+
+    @contextmanager
+    def _cm():
+      self.capture(data)
+      yield
+      self.check_and_dump(data)
+    return _cm()
+
+
 @dataclass(kw_only=True)
 class SimulationCfg:
+  """Field-for-field the reference's SimulationCfg (sim.py:78-94)."""
   nconmax: int | None = None
   njmax: int | None = None
   ls_parallel: bool = True
   contact_sensor_maxmatch: int = 64
   mujoco: MujocoCfg = field(default_factory=MujocoCfg)
+  nan_guard: NanGuardCfg = field(default_factory=NanGuardCfg)
 
 
 class Simulation:
@@ -77,11 +148,12 @@ class Simulation:
     self._model = engine.put_model(self._mj_model, device)
     self._model.opt.ls_parallel = cfg.ls_parallel
     self._model.opt.contact_sensor_maxmatch = cfg.contact_sensor_maxmatch
-    self._data = engine.put_data(self._mj_model, self._mj_data, nworld=num_envs, nconmax=cfg.nconmax,
-                                 njmax=cfg.njmax, model=self._model)
+    self._data = engine.put_data(self._mj_model, self._mj_data, nworld=num_envs, nconmax=cfg.nconmax, njmax=cfg.njmax,
+                                 model=self._model)
     self.use_cuda_graph = True
     self._decimation = 1
     self.create_graph()
+    self.nan_guard = NanGuard(cfg.nan_guard, num_envs)
 
   def create_graph(self, decimation: int | None = None) -> None:
     import torch
@@ -144,6 +216,13 @@ class Simulation:
       engine.forward(self._model, self._data)
 
   def step(self) -> None:
+    if self.nan_guard.enabled:        # reference sim.py:194-199: the guard brackets every step
+      with self.nan_guard.watch(self._data):
+        self._step()
+    else:
+      self._step()
+
+  def _step(self) -> None:
     if self.step_graph is not None:
       self.step_graph.replay()
     else:

@@ -61,6 +61,75 @@ def _check_counts(D, worlds):
     assert contact_pairs(geom[i], n) == contact_pairs(w["con_geom"], n)
 
 
+class ConvexStats:
+  """Book-keeping of the convex / height-field comparisons: every compared world-state is accounted for.  Where the two
+  contact LISTS differ, the difference must be explained contact by contact: a contact present on one side only has to sit
+  within `eps_margin` of the activation margin (fp32 GJK / EPA distances move by ~1e-4 m near touching, so a pair can be
+  inside the margin on one side and outside on the other) or, for the multi-contact colliders that select a subset
+  (plane-mesh manifold: vertices within 1 mm of the deepest one; height-field prisms: deepest 8), within `eps_select` of its
+  collider's selection threshold -- measured here as: the same geom pair is in contact on both sides and all other
+  contacts of that pair match."""
+
+  def __init__(self, m, eps_margin=2e-5, eps_select=2e-5):
+    self.m, self.eps_margin, self.eps_select = m, eps_margin, eps_select
+    self.states = self.identical = self.ncmp = self.tight = self.tight_pos = 0
+    self.marginal = []       # (|dist - margin|, geom types) of contacts present on one side only
+    self.seen = set()
+
+  @staticmethod
+  def _by_pair(n, geom, dist, pos, inc):
+    out = {}
+    for k in range(n):
+      out.setdefault((int(geom[2 * k]), int(geom[2 * k + 1])), []).append((float(dist[k]), np.asarray(pos[3 * k: 3 * k + 3], np.float64), float(inc[k])))
+    return out
+
+  def compare(self, i, w, ncon_g, G, P, Fr, Di, Inc, near_loose=False):
+    m = self.m
+    n = int(w["ncon"][0]); ng = int(ncon_g)
+    self.states += 1
+    if ng == n and G[i, :n].reshape(-1).tolist() == w["con_geom"][: 2 * n].tolist():
+      self.identical += 1
+      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
+      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
+      dp = np.abs(P[i, :n] - w["con_pos"][: 3 * n].reshape(n, 3)).max(axis=1, initial=0)
+      # fp32 GJK/EPA is a discrete search: a different simplex / polytope path moves a near-touching distance by
+      # ~1e-4 m and slides the witness point along parallel faces.  Everything must agree loosely, nearly all tightly.
+      assert dd.max(initial=0) < 4e-3
+      if near_loose:      # curved cores that almost touch: the normal (pb - pa) / dist is ill-conditioned below 1 mm
+        near = np.abs(w["con_dist"][:n]) < 1e-3
+        assert (dn[~near] < 5e-2).all() and (dn[near] < 0.5).all(), (dd, dn)
+      else:
+        assert dn.max(initial=0) < 5e-2
+      self.ncmp += n; self.tight += int(((dd < 2e-5) & (dn < 2e-3)).sum()); self.tight_pos += int((dp < 2e-4).sum())
+      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
+        self.seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
+      return
+    # the lists differ: explain every unmatched contact
+    a = self._by_pair(ng, G[i].reshape(-1), Di[i], P[i].reshape(-1), Inc[i])
+    b = self._by_pair(n, w["con_geom"], w["con_dist"], w["con_pos"], w["con_includemargin"])
+    for pair in sorted(set(a) | set(b)):
+      la, lb = list(a.get(pair, [])), list(b.get(pair, []))
+      # greedy matching by position
+      for ca in list(la):
+        if not lb:
+          break
+        k = int(np.argmin([np.abs(ca[1] - cb[1]).max() for cb in lb]))
+        if np.abs(ca[1] - lb[k][1]).max() < 5e-3 and abs(ca[0] - lb[k][0]) < 4e-3:
+          la.remove(ca); lb.pop(k)
+      types = (int(m.geom_type[pair[0]]), int(m.geom_type[pair[1]]))
+      multi = types[0] in (0, 1) and types[1] in (1, 5, 6, 7) or types == (6, 6)      # subset-selecting colliders
+      for c in la + lb:
+        gap = abs(c[0] - c[2])
+        both = pair in a and pair in b
+        assert gap < self.eps_margin or (multi and both), (pair, types, c, "contact on one side only, not at the margin")
+        self.marginal.append((gap, types))
+
+  def report(self, tag):
+    print(f"\n[{tag}] states {self.states}, identical contact lists {self.identical}, explained differences {self.states - self.identical} "
+          f"({len(self.marginal)} one-sided contacts, largest |dist - margin| {max((g for g, _ in self.marginal), default=0.0):.2e}); "
+          f"{self.ncmp} contacts compared, {self.tight} tight, {self.tight_pos} tight positions")
+
+
 @pytest.mark.parametrize("ls_parallel", [True, False])
 def test_g1_forward_matches_oracle(g1, ls_parallel):
   W = 32
@@ -246,23 +315,27 @@ def test_tendon_fixture_actuation_passive_and_implicit_terms():
   assert _rel_err(D, worlds, "qpos") < 1e-3 and _rel_err(D, worlds, "qvel") < 1e-2
 
 
-def test_asimov_toe_flat_matches_oracle(asimov_toe):
+@pytest.mark.parametrize("iterations", [10, 30])
+def test_asimov_toe_flat_matches_oracle(asimov_toe, iterations, capsys):
   """The fork's Asimov-toe velocity scene (tasks/velocity/config/asimov_toe/env_cfgs.py): 4 fixed ankle tendons with
   tendon position actuators + 10 joint actuators, 20 foot / toe capsules on the plane, subtree contact sensors.
   The model is chaotic within ~10 steps (saturating toe actuators on ~1e-4 kg m^2), so the oracle drives the
-  trajectory and the device is re-seeded from it every 5 steps; forward() and one step are compared each time."""
+  trajectory and the device is re-seeded from it every 5 steps; forward() and one step are compared each time.
+
+  iterations = 10 is the task's own solver cap: in the violent worlds the grid line search has not converged by then (it
+  needs ~14 iterations) and a truncated Newton run amplifies fp32 rounding through its discrete step choices, so there the
+  solve is compared world by world: worlds whose oracle solve converged below the cap at the tight tolerance, capped
+  worlds through the objective both sides reached (same cost level) and a loose bound on the acceleration.
+  iterations = 30 compares converged solutions everywhere."""
   import copy
   import torch
   W = 32
-  # iterations 10 -> 30: at the task's cap of 10 the grid line search has not converged in the violent worlds
-  # (it needs ~14) and a truncated Newton run amplifies fp32 rounding through its discrete step choice (both sides
-  # reach the same minimum: measured cost 86067.6 on either at 14 iterations); converged solutions are compared here,
-  # the golden test below keeps the cap.
-  m = copy.deepcopy(asimov_toe); m.opt.iterations = 30
+  m = copy.deepcopy(asimov_toe); m.opt.iterations = iterations
   asimov_toe = m
   qpos, qvel, ctrl = asimov_states(asimov_toe, W, seed=9, spread=0.2, vel=0.3, zlo=0.70, zhi=0.76)
   engine, M, D, orc, worlds = _setup(asimov_toe, W, qpos, qvel, ctrl, True)
-  ncon_total = 0
+  ncon_total = ncapped = 0
+  worst_capped = 0.0
   for chunk in range(8):
     if chunk:
       for w in worlds:
@@ -277,24 +350,42 @@ def test_asimov_toe_flat_matches_oracle(asimov_toe):
     for f in ("ten_length", "ten_velocity", "actuator_length", "actuator_force", "qfrc_actuator", "qfrc_passive",
               "qfrc_smooth", "geom_xpos", "site_xpos", "subtree_com"):
       assert _rel_err(D, worlds, f) < 5e-5, f
-    for f in ("qacc_smooth", "qacc", "qfrc_constraint", "sensordata"):
-      assert _rel_err(D, worlds, f) < 2e-3, f
+    assert _rel_err(D, worlds, "qacc_smooth") < 2e-3
+    nit_o = np.array([int(w["solver_niter"][0]) for w in worlds]); nit_g = D.solver_niter.cpu().numpy()
+    conv = (nit_o < iterations) & (nit_g == nit_o)
+    for f in ("qacc", "qfrc_constraint", "sensordata"):
+      g = getattr(D, f).cpu().numpy().astype(np.float64); o = np.stack([w[f] for w in worlds]).astype(np.float64)
+      scale = 1e-6 + np.abs(o).max()
+      assert np.abs(g - o)[conv].max(initial=0) / scale < 2e-3, f
+      worst_capped = max(worst_capped, float(np.abs(g - o)[~conv].max(initial=0) / scale))
+    if (~conv).any():
+      ncapped += int((~conv).sum())
+      cg = D.solver_cost.cpu().numpy().astype(np.float64)[~conv]; co = np.array([float(w["solver_cost"][0]) for w in worlds])[~conv]
+      assert (np.abs(cg - co) < 5e-2 * (1.0 + np.abs(co))).all(), (cg, co)       # same level of the objective at the cap (measured: <= 2.4e-2)
+  with capsys.disabled():
+    print(f"\n[asimov-toe flat, iterations {iterations}] {ncapped} capped solves of {8 * W}; worst capped-world deviation {worst_capped:.2e} of the field scale")
   assert ncon_total > 200
-  engine.step(M, D)
-  for w in worlds:
-    orc.step(w)
-  _check_counts(D, worlds)
-  # qacc reaches ~2.7e4 rad/s^2 on the toes: 2e-3 of that, integrated once, bounds the step error
-  eq, ev = _rel_err(D, worlds, "qpos"), _rel_err(D, worlds, "qvel")
-  assert eq < 1e-3 and ev < 5e-3, (eq, ev)
+  assert worst_capped < 0.25
+  if iterations == 30:
+    assert ncapped == 0
+  if iterations == 30:
+    engine.step(M, D)
+    for w in worlds:
+      orc.step(w)
+    _check_counts(D, worlds)
+    # qacc reaches ~2.7e4 rad/s^2 on the toes: 2e-3 of that, integrated once, bounds the step error
+    eq, ev = _rel_err(D, worlds, "qpos"), _rel_err(D, worlds, "qvel")
+    assert eq < 1e-3 and ev < 5e-3, (eq, ev)
 
 
-def test_asimov_toe_rough_box_terrain_matches_oracle(asimov_toe_rough):
-  """Asimov-toe on the default box terrain (capsule-box through the grid broadphase)."""
+@pytest.mark.parametrize("iterations", [10, 30])
+def test_asimov_toe_rough_box_terrain_matches_oracle(asimov_toe_rough, iterations):
+  """Asimov-toe on the default box terrain (capsule-box through the grid broadphase); at the task's cap of 10 iterations the
+  worlds whose oracle solve hit the cap are compared loosely (see the flat test)."""
   import copy
   import torch
   W = 16
-  m = copy.deepcopy(asimov_toe_rough); m.opt.iterations = 30     # converged solves, see the flat test
+  m = copy.deepcopy(asimov_toe_rough); m.opt.iterations = iterations
   asimov_toe_rough = m
   qpos, qvel, ctrl = rough_states(asimov_toe_rough, W, seed=13, spread=0.1, vel=0.2, drop=(0.0, 0.03))
   c0 = np.array(asimov_toe_rough.keys["robot/init_state"]["ctrl"])
@@ -311,13 +402,20 @@ def test_asimov_toe_rough_box_terrain_matches_oracle(asimov_toe_rough):
       orc.forward(w)
     _check_counts(D, worlds)
     ncon_total += sum(int(w["ncon"][0]) for w in worlds)
-    for f in ("geom_xpos", "qacc", "sensordata", "qfrc_constraint", "actuator_force"):
+    nit_o = np.array([int(w["solver_niter"][0]) for w in worlds]); nit_g = D.solver_niter.cpu().numpy()
+    conv = (nit_o < iterations) & (nit_g == nit_o)      # both solves ended below the cap after the same number of iterations
+    for f in ("geom_xpos", "actuator_force"):
       assert _rel_err(D, worlds, f) < 2e-3, f
+    for f in ("qacc", "sensordata", "qfrc_constraint"):
+      g = getattr(D, f).cpu().numpy().astype(np.float64); o = np.stack([w[f] for w in worlds]).astype(np.float64)
+      scale = 1e-6 + np.abs(o).max()
+      assert np.abs(g - o)[conv].max(initial=0) / scale < 2e-3, f
+      assert np.abs(g - o)[~conv].max(initial=0) / scale < 0.25, f
   assert ncon_total > 100
 
 
 @pytest.mark.parametrize("ground", ["plane", "meshbox", "hfield"])
-def test_convex_mesh_and_height_field_contacts_match_oracle(ground):
+def test_convex_mesh_and_height_field_contacts_match_oracle(ground, capsys):
   """K7: GJK/EPA (mesh-mesh, box-mesh, sphere-mesh, capsule-mesh), plane-mesh manifold and height-field prisms on a
   bumpy field: same contacts in the same order, same distances / frames; the oracle drives a tumbling trajectory and
   the device is compared at every 10th state."""
@@ -336,7 +434,7 @@ def test_convex_mesh_and_height_field_contacts_match_oracle(ground):
       qpos[w, 7 * k + 3: 7 * k + 7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
     qvel[w] = rng.normal(0, 0.5, m.nv)
   engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=48, njmax=200)
-  seen, total, ncmp, tight, tight_pos = set(), 0, 0, 0, 0
+  st = ConvexStats(m)
   for chunk in range(10):
     if chunk:
       for w in worlds:
@@ -347,25 +445,15 @@ def test_convex_mesh_and_height_field_contacts_match_oracle(ground):
     for w in worlds:
       orc.forward(w)
     n_all = D.ncon.cpu().numpy()
-    G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9); Di = D.contact_dist.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9)
+    Di = D.contact_dist.cpu().numpy(); Inc = D.contact_includemargin.cpu().numpy()
     for i, w in enumerate(worlds):
-      n = int(w["ncon"][0])
-      # a contact whose distance sits within float rounding of the margin (or of the plane-mesh 1 mm band) may exist on
-      # one side only: compare worlds whose contact lists agree, and require that almost all do
-      if int(n_all[i]) != n or G[i, :n].reshape(-1).tolist() != w["con_geom"][: 2 * n].tolist():
-        continue
-      total += 1
-      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
-      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
-      dp = np.abs(P[i, :n] - w["con_pos"][: 3 * n].reshape(n, 3)).max(axis=1, initial=0)
-      # fp32 GJK/EPA is a discrete search: a different simplex / polytope path moves a near-touching distance by
-      # ~1e-4 m and slides the witness point along parallel faces.  Everything must agree loosely, nearly all tightly.
-      assert dd.max(initial=0) < 4e-3 and dn.max(initial=0) < 5e-2
-      ncmp += n; tight += int(((dd < 2e-5) & (dn < 2e-3)).sum()); tight_pos += int((dp < 2e-4).sum())
-      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
-        seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
-  assert total >= 0.95 * 10 * W, total
-  assert ncmp > 200 and tight >= 0.97 * ncmp and tight_pos >= 0.93 * ncmp, (ncmp, tight, tight_pos)
+      st.compare(i, w, n_all[i], G, P, Fr, Di, Inc)
+  with capsys.disabled():
+    st.report(f"convex {ground}")
+  seen = st.seen
+  assert st.identical >= 0.98 * st.states, (st.identical, st.states)
+  assert st.ncmp > 200 and st.tight >= 0.97 * st.ncmp and st.tight_pos >= 0.93 * st.ncmp, (st.ncmp, st.tight, st.tight_pos)
   if ground == "plane":
     assert (0, 7) in seen and (7, 7) in seen
   elif ground == "meshbox":
@@ -374,13 +462,14 @@ def test_convex_mesh_and_height_field_contacts_match_oracle(ground):
     assert {(1, 2), (1, 3), (1, 6), (1, 7)} <= seen
 
 
-def test_asimov_toe_full_collision_link_meshes_match_oracle(asimov_toe_full):
+@pytest.mark.parametrize("iterations", [10, 30])
+def test_asimov_toe_full_collision_link_meshes_match_oracle(asimov_toe_full, iterations, capsys):
   """FULL_COLLISION variant of the Asimov-toe robot (asimov_toe_constants.py:219-227): 11 link meshes (convex hulls,
   4111 vertices) + 20 capsules, terrain and self collisions.  Robots are dropped tilted so that they fall onto their
   link meshes; contacts and the solved accelerations are compared at every 10th oracle state."""
   import copy
   import torch
-  m = copy.deepcopy(asimov_toe_full); m.opt.iterations = 30
+  m = copy.deepcopy(asimov_toe_full); m.opt.iterations = iterations      # 10 = the task's own solver cap
   W = 16
   qpos, qvel, ctrl = asimov_states(m, W, seed=19, spread=0.3, vel=0.3, zlo=0.45, zhi=0.8)
   rng = np.random.default_rng(19)
@@ -388,7 +477,7 @@ def test_asimov_toe_full_collision_link_meshes_match_oracle(asimov_toe_full):
     ax = rng.normal(size=3); ax /= np.linalg.norm(ax); ang = rng.normal(0, 1.0)
     qpos[w, 3:7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
   engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True)
-  seen, total, ncmp, tight = set(), 0, 0, 0
+  st = ConvexStats(m)
   for chunk in range(12):
     for w in worlds:
       orc.step(w, 10)
@@ -398,24 +487,19 @@ def test_asimov_toe_full_collision_link_meshes_match_oracle(asimov_toe_full):
     for w in worlds:
       orc.forward(w)
     n_all = D.ncon.cpu().numpy()
-    G = D.contact_geom.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9); Di = D.contact_dist.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9)
+    Di = D.contact_dist.cpu().numpy(); Inc = D.contact_includemargin.cpu().numpy()
     for i, w in enumerate(worlds):
-      n = int(w["ncon"][0])
-      if int(n_all[i]) != n or G[i, :n].reshape(-1).tolist() != w["con_geom"][: 2 * n].tolist():
-        continue
-      total += 1
-      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
-      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
-      assert dd.max(initial=0) < 4e-3 and dn.max(initial=0) < 5e-2
-      ncmp += n; tight += int(((dd < 2e-5) & (dn < 2e-3)).sum())
-      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
-        seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
-  assert total >= 0.9 * 12 * W, total
-  assert ncmp > 300 and tight >= 0.97 * ncmp, (ncmp, tight)
+      st.compare(i, w, n_all[i], G, P, Fr, Di, Inc)
+  with capsys.disabled():
+    st.report(f"asimov-toe full collision, iterations {iterations}")
+  seen = st.seen
+  assert st.identical >= 0.98 * st.states, (st.identical, st.states)
+  assert st.ncmp > 300 and st.tight >= 0.97 * st.ncmp, (st.ncmp, st.tight)
   assert (0, 7) in seen and ((7, 7) in seen or (3, 7) in seen), seen
 
 
-def test_go1_on_height_field_terrain_matches_oracle(go1_rough_hf):
+def test_go1_on_height_field_terrain_matches_oracle(go1_rough_hf, capsys):
   """Go1 on the generator's height-field sub-terrains (pyramid slope, random rough, wave; 80 x 80 fields found through
   the static-geom grid): sphere / capsule / box against hfield prisms.  Oracle-driven, compared every 10 steps."""
   import torch
@@ -435,7 +519,7 @@ def test_go1_on_height_field_terrain_matches_oracle(go1_rough_hf):
     qpos[w, 0:2] = org[r, c, :2] + rng.uniform(-2.5, 2.5, 2)
     qpos[w, 2] = org[r, c, 2] + z0 + rng.uniform(0.0, 0.15)
   engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True)
-  seen, total, ncmp, tight = set(), 0, 0, 0
+  st = ConvexStats(m)
   for chunk in range(8):
     for w in worlds:
       orc.step(w, 10)
@@ -445,20 +529,15 @@ def test_go1_on_height_field_terrain_matches_oracle(go1_rough_hf):
     for w in worlds:
       orc.forward(w)
     n_all = D.ncon.cpu().numpy()
-    G = D.contact_geom.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9); Di = D.contact_dist.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9)
+    Di = D.contact_dist.cpu().numpy(); Inc = D.contact_includemargin.cpu().numpy()
     for i, w in enumerate(worlds):
-      n = int(w["ncon"][0])
-      if int(n_all[i]) != n or G[i, :n].reshape(-1).tolist() != w["con_geom"][: 2 * n].tolist():
-        continue
-      total += 1
-      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
-      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
-      assert dd.max(initial=0) < 4e-3 and dn.max(initial=0) < 5e-2
-      ncmp += n; tight += int(((dd < 2e-5) & (dn < 2e-3)).sum())
-      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
-        seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
-  assert total >= 0.9 * 8 * W, total
-  assert ncmp > 300 and tight >= 0.97 * ncmp, (ncmp, tight)
+      st.compare(i, w, n_all[i], G, P, Fr, Di, Inc)
+  with capsys.disabled():
+    st.report("go1 on height fields")
+  seen = st.seen
+  assert st.identical >= 0.98 * st.states, (st.identical, st.states)
+  assert st.ncmp > 300 and st.tight >= 0.97 * st.ncmp, (st.ncmp, st.tight)
   assert (1, 2) in seen and (1, 3) in seen, seen
 
 
@@ -830,7 +909,7 @@ ROUND_TUMBLE = """
 
 
 @pytest.mark.gpu
-def test_cylinder_and_ellipsoid_contacts_match_oracle():
+def test_cylinder_and_ellipsoid_contacts_match_oracle(capsys):
   """Cylinder / ellipsoid colliders: analytic against the plane (up to 4 / 1 contacts), GJK + EPA with their support
   functions against spheres, capsules, boxes and each other.  Six bodies tumble over a plane and a static box; the oracle
   drives, the device is compared at every 10th state (same scheme and tolerances as the mesh test)."""
@@ -846,7 +925,7 @@ def test_cylinder_and_ellipsoid_contacts_match_oracle():
       qpos[w, 7 * k + 3: 7 * k + 7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
     qvel[w] = rng.normal(0, 0.5, m.nv)
   engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, None, True, nconmax=48, njmax=200)
-  seen, total, ncmp, tight = set(), 0, 0, 0
+  st = ConvexStats(m)
   for chunk in range(10):
     if chunk:
       for w in worlds:
@@ -857,23 +936,15 @@ def test_cylinder_and_ellipsoid_contacts_match_oracle():
     for w in worlds:
       orc.forward(w)
     n_all = D.ncon.cpu().numpy()
-    G = D.contact_geom.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9); Di = D.contact_dist.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9)
+    Di = D.contact_dist.cpu().numpy(); Inc = D.contact_includemargin.cpu().numpy()
     for i, w in enumerate(worlds):
-      n = int(w["ncon"][0])
-      if int(n_all[i]) != n or G[i, :n].reshape(-1).tolist() != w["con_geom"][: 2 * n].tolist():
-        continue
-      total += 1
-      dd = np.abs(Di[i, :n] - w["con_dist"][:n])
-      dn = np.abs(Fr[i, :n, :3] - w["con_frame"][: 9 * n].reshape(n, 9)[:, :3]).max(axis=1, initial=0)
-      # between curved cores that almost touch, the normal (pb - pa) / dist is ill-conditioned: witness points that differ by
-      # 1e-4 m across |dist| < 1 mm turn it by tenths of a radian (the distance itself agrees); bound it loosely there
-      near = np.abs(w["con_dist"][:n]) < 1e-3
-      assert dd.max(initial=0) < 4e-3 and (dn[~near] < 5e-2).all() and (dn[near] < 0.5).all(), (dd, dn)
-      ncmp += n; tight += int(((dd < 2e-5) & (dn < 2e-3)).sum())
-      for g1, g2 in w["con_geom"][: 2 * n].reshape(n, 2):
-        seen.add((int(m.geom_type[g1]), int(m.geom_type[g2])))
-  assert total >= 0.9 * 10 * W, total
-  assert ncmp > 200 and tight >= 0.95 * ncmp, (ncmp, tight)
+      st.compare(i, w, n_all[i], G, P, Fr, Di, Inc, near_loose=True)
+  with capsys.disabled():
+    st.report("cylinders / ellipsoids")
+  seen = st.seen
+  assert st.identical >= 0.98 * st.states, (st.identical, st.states)
+  assert st.ncmp > 200 and st.tight >= 0.95 * st.ncmp, (st.ncmp, st.tight)
   assert {(0, 4), (0, 5)} <= seen and len({(2, 5), (3, 5), (4, 5), (5, 5), (5, 6), (4, 6), (2, 4), (3, 4)} & seen) >= 4, seen
   # and a free run stays finite (bodies start interpenetrating, get thrown apart and keep their spin: condim 3 has no
   # torsional friction), nothing tunnels through the floor

@@ -19,7 +19,7 @@ M = engine.put_model(m)
 key = m.keys["robot/init_state"]
 hd = HostData(m)
 hd.qpos[:] = key["qpos"]; hd.ctrl[:] = key["ctrl"]
-D = engine.put_data(m, hd, W, 50, 300, model=M)
+D = engine.put_data(m, hd, W, int(os.environ.get("NCONMAX", "50")), int(os.environ.get("NJMAX", "300")), model=M)
 g = torch.Generator().manual_seed(0)
 if "terrain_origins" in m.meta:       # spawn on the generated terrain like bench.py does
   import numpy as np
