@@ -34,6 +34,7 @@ struct FieldRec {
 
 struct b2s_model {
   int device = 0;
+  int overlap = 1;           // independent stages of a step run on a forked branch (option "stage_overlap")
   ModelDev dev;
   std::vector<void*> allocs;
   std::vector<FieldRec> fields;
@@ -50,8 +51,18 @@ struct b2s_data {
   std::map<std::string, int> index;
   cudaEvent_t ev[16];
   bool have_ev = false;
+  // fork / join of independent stages (collision beside dynamics, sensors beside the integrator): one internal side stream,
+  // forked from and joined back into the caller's stream with these events, so a stream capture records a DAG
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr;
   float* efc_J = nullptr;    // dense Jacobian, allocated and filled on demand (b2s_efc_jacobian)
-  ~b2s_data() { if (arena) cudaFree(arena); if (efc_J) cudaFree(efc_J); if (have_ev) for (auto& e : ev) cudaEventDestroy(e); }
+  ~b2s_data() {
+    if (arena) cudaFree(arena);
+    if (efc_J) cudaFree(efc_J);
+    if (have_ev) for (auto& e : ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : {ev_fork, ev_join, ev_fork2, ev_join2}) if (e) cudaEventDestroy(e);
+    if (side) cudaStreamDestroy(side);
+  }
 };
 
 extern "C" const char* b2s_last_error(void) { return g_err.c_str(); }
@@ -524,6 +535,7 @@ extern "C" int b2s_model_set_opt(b2s_model* m, const char* key, double v) {
   ModelDev& d = m->dev;
   const std::string k(key);
   if (k == "ls_parallel") d.ls_parallel = v != 0;
+  else if (k == "stage_overlap") m->overlap = v != 0;
   else if (k == "contact_sensor_maxmatch") d.contact_sensor_maxmatch = (int)v;
   else if (k == "iterations") d.iterations = (int)v;
   else if (k == "ls_iterations") d.ls_iterations = (int)v;
@@ -553,6 +565,7 @@ extern "C" int b2s_model_get_opt(const b2s_model* m, const char* key, double* v)
   const ModelDev& d = m->dev;
   const std::string k(key);
   if (k == "ls_parallel") *v = d.ls_parallel;
+  else if (k == "stage_overlap") *v = m->overlap;
   else if (k == "contact_sensor_maxmatch") *v = d.contact_sensor_maxmatch;
   else if (k == "iterations") *v = d.iterations;
   else if (k == "ls_iterations") *v = d.ls_iterations;
@@ -683,6 +696,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"solve_order", B2S_I32, (void**)&d.solve_order, {B2S_SOLVE_CLASSES}}, {"solve_count", B2S_I32, (void**)&d.solve_count, {B2S_SOLVE_CLASSES}},
     {"cacc", B2S_F32, (void**)&d.cacc, {nb, 6}}, {"subtree_linvel", B2S_F32, (void**)&d.subtree_linvel, {nb, 3}},
     {"subtree_angmom", B2S_F32, (void**)&d.subtree_angmom, {nb, 3}}, {"sensordata", B2S_F32, (void**)&d.sensordata, {md.nsensordata}},
+    {"snap_qpos", B2S_F32, (void**)&d.snap_qpos, {md.nq}}, {"snap_qvel", B2S_F32, (void**)&d.snap_qvel, {nv}}, {"snap_time", B2S_F32, (void**)&d.snap_time, {}},
   };
   // one arena; every field starts on a 256-byte boundary
   size_t total = 0;
@@ -741,6 +755,9 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   }
   for (auto& e : D->ev) cudaEventCreate(&e);
   D->have_ev = true;
+  if (cudaStreamCreateWithFlags(&D->side, cudaStreamNonBlocking) != cudaSuccess) { delete D; return fail("cannot create the side stream"); }
+  for (cudaEvent_t* e : {&D->ev_fork, &D->ev_join, &D->ev_fork2, &D->ev_join2})
+    if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess) { delete D; return fail("cannot create the fork/join events"); }
   // frames of everything attached to static bodies, once
   launch_position(md, d, 0);
   launch_static_frames(md, d, 0);
@@ -793,25 +810,51 @@ extern "C" const char* b2s_data_field_name(const b2s_data* d, int i) {
 extern "C" int64_t b2s_data_bytes(const b2s_data* d) { return d ? (int64_t)d->bytes : 0; }
 
 // ------------------------------------------------------------------------------------------ forward / step
-static void run_forward(const ModelDev& m, const DataDev& d, cudaStream_t st) {
+// One forward pass (and, with `integrate`, one step) as a DAG on the caller's stream `st` plus the data's side stream:
+//
+//   position -> dynamics ------------> constraint -> solve -> integrate ---> (next position)
+//           \-> collision (side) --/                     \-> sensors (side) -/
+//
+// collision needs only the geom frames of `position`; sensors need the solve and the state snapshot k_dynamics took
+// (DataDev::snap_*), so they run beside the integrator, which advances qpos / qvel / time.  Every stage kernel leaves
+// most of the machine idle at 4096 worlds (one warp per world, 18-40 % warps active), so the branches fill each other's
+// gaps.  The side stream is forked from and joined back into `st` with events: under stream capture this records a DAG
+// in the same graph, eagerly it is plain stream concurrency.  Results are identical to the serial order.
+static void run_pass(const b2s_model* M, b2s_data* D, cudaStream_t st, bool integrate) {
+  const ModelDev& m = M->dev; const DataDev& d = D->dev;
+  const bool fork = M->overlap != 0;
   launch_position(m, d, st);
-  launch_dynamics(m, d, st);
-  launch_collision(m, d, st);
+  if (fork) {
+    cudaEventRecord(D->ev_fork, st); cudaStreamWaitEvent(D->side, D->ev_fork, 0);
+    launch_collision(m, d, D->side);
+    cudaEventRecord(D->ev_join, D->side);
+    launch_dynamics(m, d, st);
+    cudaStreamWaitEvent(st, D->ev_join, 0);
+  } else {
+    launch_dynamics(m, d, st);
+    launch_collision(m, d, st);
+  }
   launch_constraint(m, d, st);
   launch_solve(m, d, st);
-  launch_sensors(m, d, st);
+  if (fork && integrate) {
+    cudaEventRecord(D->ev_fork2, st); cudaStreamWaitEvent(D->side, D->ev_fork2, 0);
+    launch_sensors(m, d, D->side);
+    cudaEventRecord(D->ev_join2, D->side);
+    launch_integrate(m, d, st);
+    cudaStreamWaitEvent(st, D->ev_join2, 0);
+  } else {
+    launch_sensors(m, d, st);
+    if (integrate) launch_integrate(m, d, st);
+  }
 }
 extern "C" int b2s_forward(const b2s_model* m, b2s_data* d, void* stream) {
   if (!m || !d) return fail("null argument");
-  run_forward(m->dev, d->dev, (cudaStream_t)stream);
+  run_pass(m, d, (cudaStream_t)stream, false);
   return launch_status("b2s_forward");
 }
 extern "C" int b2s_step_n(const b2s_model* m, b2s_data* d, int nsub, void* stream) {
   if (!m || !d) return fail("null argument");
-  for (int i = 0; i < nsub; i++) {
-    run_forward(m->dev, d->dev, (cudaStream_t)stream);
-    launch_integrate(m->dev, d->dev, (cudaStream_t)stream);
-  }
+  for (int i = 0; i < nsub; i++) run_pass(m, d, (cudaStream_t)stream, true);
   return launch_status("b2s_step_n");
 }
 extern "C" int b2s_step(const b2s_model* m, b2s_data* d, void* stream) { return b2s_step_n(m, d, 1, stream); }

@@ -135,6 +135,31 @@ DEV sv6 cross_force(const sv6& a, const sv6& b) {
   return r;
 }
 
+// ---- TMA bulk copy (cp.async.bulk, the non-tensor 1-D form) completed on an mbarrier: one elected lane arms the barrier with
+// the byte count and issues the copy, the copy engine writes shared memory asynchronously while the warp goes on with its
+// prologue, and every lane waits on the barrier's phase before the first read.  dst / src 16-byte aligned, bytes % 16 == 0.
+DEV unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+DEV void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+DEV void tma_load_1d(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+DEV void mbar_wait(unsigned long long* bar, unsigned phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "B2S_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra B2S_DONE;\n"
+      "bra B2S_WAIT;\n"
+      "B2S_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+
 // ---- warp helpers
 DEV float warp_sum(float v) {
 #pragma unroll

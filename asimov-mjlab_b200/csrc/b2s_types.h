@@ -113,4 +113,7 @@ struct DataDev {
   int *solve_order, *solve_count;
   // post
   float *cacc, *subtree_linvel, *subtree_angmom, *sensordata;
+  // qpos / qvel / time as k_dynamics saw them: k_sensors reads these copies, so that it can run beside k_integrate (which
+  // advances the originals) on a forked graph branch
+  float *snap_qpos, *snap_qvel, *snap_time;
 };

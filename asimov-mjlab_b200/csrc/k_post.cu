@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
   float* s_am = s_lm + 3 * nb;
   float* s_slv = s_am + 3 * nb;
   float* s_dof = s_slv + 3 * nb;
-  const float* qvel = d.qvel + (size_t)w * nv;
+  const float* qvel = d.snap_qvel + (size_t)w * nv;     // the state this forward pass was computed from (see DataDev::snap_*)
   // contact cache (only when the model has contact sensors): per-warp [nconmax][4] ints then [nconmax][15] floats
   int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * (21 * nb + 6 * nv)) + (size_t)warp * CC_WORDS * d.nconmax;
   float* s_cf = (float*)(s_ci + 4 * d.nconmax);
@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
           st3(out, mulTv(f.mat, alin) + cross(wl, vl));
         }
       } break;
-      case B2S_SENS_JOINTPOS: out[0] = d.qpos[(size_t)w * m.nq + m.jnt_qposadr[id]]; break;
+      case B2S_SENS_JOINTPOS: out[0] = d.snap_qpos[(size_t)w * m.nq + m.jnt_qposadr[id]]; break;
       case B2S_SENS_JOINTVEL: out[0] = qvel[m.jnt_dofadr[id]]; break;
       case B2S_SENS_ACTUATORFRC: out[0] = d.actuator_force[(size_t)w * m.nu + id]; break;
       case B2S_SENS_TENDONPOS: out[0] = d.ten_length[(size_t)w * m.ntendon + id]; break;
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
       case B2S_SENS_ACTUATORPOS: out[0] = d.actuator_length[(size_t)w * m.nu + id]; break;
       case B2S_SENS_ACTUATORVEL: out[0] = d.actuator_velocity[(size_t)w * m.nu + id]; break;
       case B2S_SENS_JOINTACTFRC: out[0] = d.qfrc_actuator[(size_t)w * nv + m.jnt_dofadr[id]]; break;
-      case B2S_SENS_CLOCK: out[0] = d.time[w]; break;
+      case B2S_SENS_CLOCK: out[0] = d.snap_time[w]; break;
       case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: {
         Frame f = obj_frame(m, d, w, ot, id);
         sv6 v = object_velocity(m, cvel, com, f.body, f.pos);

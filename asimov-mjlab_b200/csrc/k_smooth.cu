@@ -225,7 +225,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   // stage cdof, cinert, qvel
 #pragma unroll 4
   for (int i = lane; i < 6 * nv; i += 32) s_cdof[i] = d.cdof[(size_t)w * 6 * nv + i];
-  for (int i = lane; i < nv; i += 32) { s_qvel[i] = qvel[i]; s_act[i] = 0.f; }
+  for (int i = lane; i < nv; i += 32) { const float v = qvel[i]; s_qvel[i] = v; s_act[i] = 0.f; d.snap_qvel[(size_t)w * nv + i] = v; }
+  for (int i = lane; i < m.nq; i += 32) d.snap_qpos[(size_t)w * m.nq + i] = qpos[i];
+  if (lane == 0) d.snap_time[w] = d.time[w];
   for (int i = lane; i < b2s_hdim(T) * ld; i += 32) s_M[i] = 0.f;
   __syncwarp();
   // composite inertia: sum of cinert over the subtree range (same frame for all bodies).  cinert is staged once,

@@ -60,6 +60,7 @@ def parse():
   ap.add_argument("--cpu-baseline", type=int, default=1)
   ap.add_argument("--ls-parallel", type=int, default=1)
   ap.add_argument("--workload", default="g1_flat", choices=sorted(WORKLOADS))
+  ap.add_argument("--overlap", type=int, default=1, help="stage overlap on forked graph branches (0: serial stages)")
   ap.add_argument("--cone", default="pyramidal", choices=["pyramidal", "elliptic"], help="friction cone (the reference's default is pyramidal)")
   return ap.parse_args()
 
@@ -210,6 +211,7 @@ def run_b200(args):
   foot = [i for i, n in enumerate(m.names["geom"]) if ("foot" in n or "_toe" in n) and n.endswith("_collision")]
   fr = 0.3 + 0.9 * torch.rand(E, len(foot), generator=g)
   M.geom_friction[:, foot, 0] = fr.to(dev)
+  M.opt.stage_overlap = int(args.overlap)
   n0 = engine.launch_count()
   sim.create_graph(decimation=DECIMATION)
   per_graph = {"step": 7, "forward": 6, "decimation": 7 * DECIMATION}
