@@ -382,7 +382,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   memset(&d, 0, sizeof(d));
   d.nq = s->nq; d.nv = nv; d.nvp = (nv + 3) & ~3; d.nu = s->nu; d.nbody = nb; d.njnt = s->njnt; d.ngeom = s->ngeom; d.nsite = s->nsite;
   d.nsensor = s->nsensor; d.nsensordata = s->nsensordata; d.nmocap = s->nmocap;
-  d.nlevel = nlevel; d.npair = (int)pairs.size() / 2; d.maxchain = maxchain;
+  d.nlevel = nlevel; d.npair = (int)pairs.size() / 2; d.maxchain = maxchain; d.nchain = (int)chain.size();
   d.ref_root = nv > 0 ? s->body_rootid[s->dof_bodyid[0]] : 0;
   d.timestep = (float)s->opt_timestep;
   for (int k = 0; k < 3; k++) d.gravity[k] = (float)s->opt_gravity[k];

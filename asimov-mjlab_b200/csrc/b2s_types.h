@@ -27,6 +27,7 @@ struct ModelDev {
   // sizes
   int nq, nv, nvp, nu, nbody, njnt, ngeom, nsite, nsensor, nsensordata, nmocap;
   int nlevel, npair, ncolgeom, maxchain;
+  int nchain;                       // total length of body_chain (= body_chain_adr[nbody])
   int ref_root;                     // root body of the first kinematic tree: its subtree COM is the constraint reference point
   // options
   float timestep, gravity[3], tolerance, ls_tolerance, impratio, ls_parallel_min_step, meaninertia;

@@ -15,7 +15,7 @@
 #include "b2s_math.cuh"
 #include "b2s_api.h"
 
-extern __shared__ float b2s_smem[];
+extern __shared__ __align__(16) float b2s_smem[];
 
 // The solver has its own CTA shape: ONE warp (= one world) per CTA.  Newton iteration counts differ from world to
 // world, and a multi-warp CTA keeps its shared memory and registers until its slowest warp is done; measured on
@@ -35,12 +35,18 @@ extern __shared__ float b2s_smem[];
 #endif
 
 __host__ __device__ inline int solve_scratch_floats(int nb) { return 6 * (nb > 32 ? nb : 32) + 32 + 32; }
+// Staged per-world / per-model data (north_star: "TMA or shared-memory staging"): the world's mass matrix (nv x nvp floats,
+// one cp.async.bulk completed on an mbarrier), then the barrier itself; at the end of the allocation the model's ancestor-dof
+// chains as bytes + their CSR offsets as 16-bit words (read by every J v product and run flush of every iteration).
+__host__ __device__ inline int solve_stage_front_floats(int T) { const int N = 7 * T; return N * ((N + 3) & ~3) + 4; }
+__host__ __device__ inline int solve_chain_floats(int nb, int nchain) { return ((nchain + 3) >> 2) + ((nb + 2) >> 1); }
 __host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      // offset of the scratch area
   const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
   return (HF + 12 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
 }
-__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T, int elliptic = 0) {
-  return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + (elliptic ? 2 * njmax : 0) + 3) & ~3;
+__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T, int nchain, int elliptic = 0) {
+  return (solve_stage_front_floats(T) + solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + (elliptic ? 2 * njmax : 0) +
+          solve_chain_floats(nb, nchain) + 3) & ~3;
 }
 
 // Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
@@ -51,8 +57,10 @@ struct SolveCtx {
   static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 12 * NVP + 6 * N;
   int lane, nv, nvp, nb, nefc, nl, nf, nrun, njmax, nconmax, soff;
   static constexpr int ld = LD, hfloats = HF;
-  const float *M, *G, *aref;
+  const float *M, *G, *aref;      // M: the staged copy in shared memory (row stride nvp)
   const int* bp;
+  const unsigned char* chain;     // staged body_chain (dof ids) and body_chain_adr
+  const unsigned short* cadr;
   float* sm;
   DEV float* H() const { return sm; }
   DEV float* invd() const { return sm + N * LD; }
@@ -84,9 +92,9 @@ struct SolveCtx {
   DEV float* efri() const { return sm + soff + 6 * max(nb, 32) + 64 + njmax; }
 };
 
-// y[i] = sum_j M[i][j] x[j].  M is dense and symmetric in HBM/L2 with row stride nvp (a multiple of 4, padding columns
-// are zero): lane = row, the row is read as float4 (all of them in flight before the first use), x as float4
-// broadcasts from shared memory (zero-padded to NVP).  One accumulator, columns in ascending order.
+// y[i] = sum_j M[i][j] x[j].  M is dense and symmetric, staged in shared memory by the kernel prologue's bulk copy, row stride
+// nvp (a multiple of 4, padding columns are zero): lane = row, the row is read as float4, x as float4 broadcasts (zero-padded
+// to NVP).  One accumulator, columns in ascending order.
 template <int T>
 DEV void mat_vec_M(const SolveCtx<T>& c, const float* x, float* y) {
   constexpr int N = 7 * T, Q = SolveCtx<T>::NVP / 4;
@@ -117,7 +125,7 @@ DEV void mat_vec_J(const SolveCtx<T>& c, const ModelDev& m, const float* x, cons
   for (int b = c.lane; b < c.nb; b += 32) {
     sv6 v = zero6();
     ROLL
-    for (int k = m.body_chain_adr[b]; k < m.body_chain_adr[b + 1]; k++) { const int i = m.body_chain[k]; axpy6(v, x[i], ld6(c.cdof() + 6 * i)); }
+    for (int k = c.cadr[b], ke = c.cadr[b + 1]; k < ke; k++) { const int i = c.chain[k]; axpy6(v, x[i], ld6(c.cdof() + 6 * i)); }
     st6(c.X() + 6 * b, v);
   }
   __syncwarp();
@@ -351,15 +359,15 @@ template <int T>
 DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, bool withH) {
   c.KW()[c.lane] = acc;
   const int b1 = bp & 0xffff, b2 = bp >> 16;
-  const int a1 = m.body_chain_adr[b1], n1f = m.body_chain_adr[b1 + 1] - a1;
-  const int a2 = m.body_chain_adr[b2], n2f = m.body_chain_adr[b2 + 1] - a2;
+  const int a1 = c.cadr[b1], n1f = c.cadr[b1 + 1] - a1;
+  const int a2 = c.cadr[b2], n2f = c.cadr[b2 + 1] - a2;
   // common ancestors are a common prefix of the two root-first chains: they cancel
   int cp = 0;
   {
     const int nmin = min(n1f, n2f);
     for (int base = 0; base < nmin; base += 32) {
       const int k = base + c.lane;
-      const bool same = k < nmin && m.body_chain[a1 + k] == m.body_chain[a2 + k];
+      const bool same = k < nmin && c.chain[a1 + k] == c.chain[a2 + k];
       const unsigned mk = __ballot_sync(FULL, same);
       if (mk != FULL) { cp = base + __ffs(~mk) - 1; break; }
       cp = base + 32;
@@ -375,7 +383,7 @@ DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, b
     // terms between chunks are handled by the (rare) slow path below
     const int a = base + c.lane;
     if (a < ns) {
-      const int i = a < n2 ? m.body_chain[a2 + cp + a] : m.body_chain[a1 + cp + a - n2];
+      const int i = a < n2 ? c.chain[a2 + cp + a] : c.chain[a1 + cp + a - n2];
       const float s = a < n2 ? 1.f : -1.f;
       const sv6 cd = ld6(c.cdof() + 6 * i);
       c.qfc()[i] += s * (cd.v[0] * W[0] + cd.v[1] * W[1] + cd.v[2] * W[2] + cd.v[3] * W[3] + cd.v[4] * W[4] + cd.v[5] * W[5]);
@@ -424,8 +432,8 @@ DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, b
         while (a * (a + 1) / 2 > t) a--;
         while ((a + 1) * (a + 2) / 2 <= t) a++;
         const int b = t - a * (a + 1) / 2;
-        const int i = a < n2 ? m.body_chain[a2 + cp + a] : m.body_chain[a1 + cp + a - n2];
-        const int j = b < n2 ? m.body_chain[a2 + cp + b] : m.body_chain[a1 + cp + b - n2];
+        const int i = a < n2 ? c.chain[a2 + cp + a] : c.chain[a1 + cp + a - n2];
+        const int j = b < n2 ? c.chain[a2 + cp + b] : c.chain[a1 + cp + b - n2];
         const float s = ((a < n2) == (b < n2)) ? 1.f : -1.f;
         const float* ci = c.cdof() + 6 * i; const float* cj = c.cdof() + 6 * j;
         float v = 0.f; int e = 0;
@@ -597,11 +605,19 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   SolveCtx<T> c;
   c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.nf = FRIC ? d.nf[w] : 0; c.njmax = njmax; c.nconmax = d.nconmax;
   c.soff = solve_soff(njmax, d.nconmax, T);
-  c.M = d.qM + (size_t)w * nv * nvp;
   c.G = d.efc_g + (size_t)w * njmax * 6;
   c.bp = d.efc_bp + (size_t)w * njmax;
   c.aref = d.efc_aref + (size_t)w * njmax;
-  c.sm = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, d.nconmax, T, ELL ? 1 : 0);
+  float* const wbase = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, d.nconmax, T, m.nchain, ELL ? 1 : 0);
+  float* const Msm = wbase;                                                    // staged mass matrix (16-byte aligned)
+  unsigned long long* const mbar = reinterpret_cast<unsigned long long*>(wbase + solve_stage_front_floats(T) - 4);
+  c.M = Msm;
+  c.sm = wbase + solve_stage_front_floats(T);
+  {
+    float* tail = c.sm + c.soff + solve_scratch_floats(nb) + (ELL ? 2 * njmax : 0);
+    c.chain = reinterpret_cast<const unsigned char*>(tail);
+    c.cadr = reinterpret_cast<const unsigned short*>(tail + ((m.nchain + 3) >> 2));
+  }
   float* efc_force = d.efc_force + (size_t)w * njmax;
   float* g_qacc = d.qacc + (size_t)w * nv;
   float* g_qfc = d.qfrc_constraint + (size_t)w * nv;
@@ -619,6 +635,22 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qas()[i]; g_qfc[i] = 0.f; }
     if (lane == 0) { d.solver_niter[w] = 0; d.solver_cost[w] = 0.f; }
     return;
+  }
+  // ---- staging.  The world's mass matrix comes in by ONE bulk async copy (TMA, cp.async.bulk): lane 0 arms the mbarrier with
+  // the byte count and issues it, the copy engine fills shared memory while the warp runs the rest of the prologue, and
+  // the warp waits on the barrier just before the first M product.  (Issued after the nefc == 0 exit: a CTA must not retire
+  // with a copy into its shared memory in flight.)  The model's chain tables are tiny and identical for every world: plain
+  // loads (L1 / L2 hits), narrowed to bytes / 16-bit words.
+  if (lane == 0) mbar_init(mbar, 1);
+  __syncwarp();
+  if (lane == 0) tma_load_1d(Msm, d.qM + (size_t)w * nv * nvp, (unsigned)(nv * nvp * sizeof(float)), mbar);
+  {
+    unsigned char* ch = const_cast<unsigned char*>(c.chain);
+    unsigned short* ca = const_cast<unsigned short*>(c.cadr);
+#pragma unroll 1
+    for (int k = lane; k < m.nchain; k += 32) ch[k] = (unsigned char)m.body_chain[k];
+#pragma unroll 1
+    for (int b = lane; b <= nb; b += 32) ca[b] = (unsigned short)m.body_chain_adr[b];
   }
   // cdof about the world's reference point (other kinematic trees are re-referenced), efc_D of the rows
   {
@@ -683,6 +715,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
   // ---- warm start (mj_fwdConstraint): evaluate the cost at qacc_warmstart (held in c.search()) and at qacc_smooth;
   // keep the warm start only if it is not worse.  One code path evaluates both points (pass 0: smooth, pass 1: warm).
   float gauss = 0.f, cost = 0.f;
+  mbar_wait(mbar, 0);       // the staged mass matrix has landed (phase 0 of the barrier)
 #pragma unroll 1
   for (int pass = warm ? 0 : 1; pass < 2; pass++) {
     const float* x = (pass == 0 || !warm) ? c.qas() : c.search();
@@ -828,7 +861,7 @@ void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
 size_t smem_solve(const ModelDev& m, const DataDev& d) {
   // the elliptic per-row arrays exist in every instantiation that has the elliptic code (variants 3 and 7)
   const bool ell = m.cone == B2S_CONE_ELLIPTIC || !m.ls_parallel || m.solver != B2S_SOL_NEWTON;
-  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), ell) * sizeof(float);
+  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), m.nchain, ell) * sizeof(float);
 }
 // Raise the dynamic shared-memory limit of EVERY solver instantiation of this model's tile size to the largest request any
 // option combination can make (the elliptic variants carry 2 njmax extra floats): Model.opt.cone / solver / ls_parallel and a
@@ -843,7 +876,7 @@ static int solve_set_attr(int smem) {
   return rc;
 }
 int solve_prepare_all(const ModelDev& m, const DataDev& d, size_t* need) {
-  const size_t smem = (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), 1) * sizeof(float);
+  const size_t smem = (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), m.nchain, 1) * sizeof(float);
   *need = smem;
   if (smem > 227 * 1024) return -1;
   int rc = 0;
