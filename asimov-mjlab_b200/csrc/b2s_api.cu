@@ -17,6 +17,21 @@ static std::atomic<long long> g_launches{0};
 void b2s_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 static int fail(const std::string& msg) { g_err = msg; return -1; }
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-function LIMIT: setting it to a smaller value makes launches that were
+// legal before fail with "invalid argument".  Several Data objects of different models share the non-template stage kernels,
+// so the limit is only ever raised: the largest request per (device, function) is remembered here.
+#include <mutex>
+static std::mutex g_smem_mu;
+static std::map<std::pair<int, const void*>, size_t> g_smem_max;
+int b2s_raise_smem(int device, const void* fn, size_t smem) {
+  std::lock_guard<std::mutex> lk(g_smem_mu);
+  size_t& cur = g_smem_max[{device, fn}];
+  if (smem <= cur) return 0;
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return smem > 48 * 1024 ? -1 : 0; }
+  cur = smem;
+  return 0;
+}
 #define CU(call)                                                                         \
   do {                                                                                   \
     cudaError_t e_ = (call);                                                             \
@@ -743,14 +758,11 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {fn_integrate(md), smem_integrate(md)}};
   for (auto& e : st) {
     if (e.smem > 227 * 1024) { delete D; return fail("model too large for the shared-memory working set (" + std::to_string(e.smem) + " B per CTA)"); }
-    if (cudaFuncSetAttribute(e.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e.smem) != cudaSuccess) {
-      cudaGetLastError();
-      if (e.smem > 48 * 1024) { delete D; return fail("cannot raise the dynamic shared-memory limit"); }
-    }
+    if (b2s_raise_smem(m->device, e.fn, e.smem) != 0) { delete D; return fail("cannot raise the dynamic shared-memory limit"); }
   }
   {
     size_t need = 0;
-    const int rc2 = solve_prepare_all(md, d, &need);
+    const int rc2 = solve_prepare_all(md, d, &need, m->device);
     if (rc2) { delete D; return fail(rc2 == -1 ? "model too large for the solver's shared-memory working set (" + std::to_string(need) + " B per CTA)" : std::string("cannot raise the solver's dynamic shared-memory limit")); }
   }
   for (auto& e : D->ev) cudaEventCreate(&e);

@@ -24,6 +24,7 @@ size_t smem_dynamics(const ModelDev& m);  const void* fn_dynamics(const ModelDev
 size_t smem_collision(const ModelDev& m); const void* fn_collision(const ModelDev& m);
 size_t smem_constraint(const ModelDev& m); const void* fn_constraint();
 size_t smem_solve(const ModelDev& m, const DataDev& d); const void* fn_solve(const ModelDev& m);
-int solve_prepare_all(const ModelDev& m, const DataDev& d, size_t* need);
+int solve_prepare_all(const ModelDev& m, const DataDev& d, size_t* need, int device);
+int b2s_raise_smem(int device, const void* fn, size_t smem);   // raise (never lower) a kernel's dynamic shared-memory limit
 size_t smem_sensors(const ModelDev& m, const DataDev& d);   const void* fn_sensors();
 size_t smem_integrate(const ModelDev& m); const void* fn_integrate(const ModelDev& m);

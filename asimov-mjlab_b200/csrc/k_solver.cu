@@ -867,22 +867,21 @@ size_t smem_solve(const ModelDev& m, const DataDev& d) {
 // option combination can make (the elliptic variants carry 2 njmax extra floats): Model.opt.cone / solver / ls_parallel and a
 // per-world dof_frictionloss can switch the instantiation after put_data.
 template <int T>
-static int solve_set_attr(int smem) {
+static int solve_set_attr(int device, size_t smem) {
   int rc = 0;
-  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
-  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
-  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
-  rc |= cudaFuncSetAttribute((const void*)k_solve<T, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess;
+  rc |= b2s_raise_smem(device, (const void*)k_solve<T, 0>, smem);
+  rc |= b2s_raise_smem(device, (const void*)k_solve<T, 1>, smem);
+  rc |= b2s_raise_smem(device, (const void*)k_solve<T, 3>, smem);
+  rc |= b2s_raise_smem(device, (const void*)k_solve<T, 7>, smem);
   return rc;
 }
-int solve_prepare_all(const ModelDev& m, const DataDev& d, size_t* need) {
+int solve_prepare_all(const ModelDev& m, const DataDev& d, size_t* need, int device) {
   const size_t smem = (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), m.nchain, 1) * sizeof(float);
   *need = smem;
   if (smem > 227 * 1024) return -1;
   int rc = 0;
-  SOLVE_DISPATCH(rc = solve_set_attr<T>((int)smem));
-  if (rc) { cudaGetLastError(); return smem > 48 * 1024 ? -2 : 0; }
-  return 0;
+  SOLVE_DISPATCH(rc = solve_set_attr<T>(device, smem));
+  return rc ? -2 : 0;
 }
 const void* fn_solve(const ModelDev& m) {
   const void* f = nullptr;

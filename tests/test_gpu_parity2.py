@@ -378,3 +378,26 @@ def test_free_running_divergence_curve(asset, request, capsys):
   ok = first > 50
   if ok.any():
     assert err[50][ok].max() < 1e-4
+
+
+def test_two_models_in_one_process_keep_their_shared_memory_limits(g1):
+  """Regression (round 2): the dynamic shared-memory limit of a kernel is per function, and the stage kernels are shared between
+  models -- creating a Data for a SMALLER model must not lower the limit under an existing Data of a larger one (its next
+  launch failed with "invalid argument")."""
+  import torch
+  W = 8
+  qpos, qvel, ctrl = g1_states(g1, W, seed=3)
+  engine, M, D, orc, worlds = _setup(g1, W, qpos, qvel, ctrl, True)
+  engine.step(M, D, 2)
+  small = fx.compile_xml(fx.LEGGED)
+  e2, M2, D2, orc2, w2 = _setup(small, 4, None, None, None, True, nconmax=16, njmax=64)
+  e2.step(M2, D2, 2)
+  engine.step(M, D, 2)                                      # the larger model again
+  e2.step(M2, D2, 2)
+  torch.cuda.synchronize()
+  for w in worlds:
+    orc.step(w, 4)
+  for w in w2:
+    orc2.step(w, 4)
+  _check_counts(D, worlds); _check_counts(D2, w2)
+  assert _rel_err(D, worlds, "qpos") < 2e-4 and _rel_err(D2, w2, "qpos") < 2e-4
