@@ -904,3 +904,62 @@ extern "C" int b2s_profile_step(const b2s_model* m, b2s_data* d, void* stream, i
   for (int k = 0; k < n; k++) { names[k] = nm[k]; ms[k] = acc[k] / (reps > 0 ? reps : 1); }
   return n;
 }
+
+// ------------------------------------------------------------------------------------------ allocation-free re-solve
+// b2s_solve_noalloc (include/b200sim.h; no counterpart in the reference): the
+// constraint solve (k_solve) on the rows the last forward / step left in `d`, with the solver's scheduling scratch -- the
+// cost-ordered world queues k_constraint normally fills in the data arena -- in a file-scope device array instead.  For callers
+// that may not allocate (CUDA graph capture, tight serving loops): no cudaMalloc / cudaFree / allocating library call here.
+//
+// The array is shared by every call on a device and keeps the last call's contents: the per-class counters are cleared at the
+// start of each call (the order slots need no clearing: only [0, count) of a class is read), and two calls whose GPU work
+// overlaps (different streams) race on it.  Every GPU that loads the library holds the array until exit
+// (B2S_NOALLOC_MAX_WORLDS x B2S_SOLVE_CLASSES ints + the counters = 4 MiB + 64 B).
+static __device__ __align__(256) int g_noalloc_scratch[B2S_SOLVE_CLASSES * (B2S_NOALLOC_MAX_WORLDS + 1)];
+
+// per world: the cost class k_constraint would pick (previous Newton iteration count x rows), appended to that class's queue
+__global__ void k_noalloc_queue(const DataDev d, int* order, int* count) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= d.nworld) return;
+  const int nefc = d.nefc[w];
+  const int cls = nefc == 0 ? 0 : min(B2S_SOLVE_CLASSES - 1, 1 + (1 + min(d.solver_niter[w], 15)) * (32 + nefc) / 64);
+  order[(size_t)cls * d.nworld + atomicAdd(&count[cls], 1)] = w;
+}
+
+// device address of the scratch array, looked up once per device with that device current.  In host code the array's NAME is
+// a host-side stand-in, not a device address: only cudaGetSymbolAddress gives the pointer a kernel may be handed.
+static int noalloc_scratch_ptr(int device, int** out) {
+  static std::atomic<int*> ptrs[64];
+  if (device < 0 || device >= 64) return fail("b2s_solve_noalloc: device index out of range");
+  int* p = ptrs[device].load(std::memory_order_acquire);
+  if (!p) {
+    CU(cudaSetDevice(device));
+    void* sym = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&sym, g_noalloc_scratch);
+    if (e != cudaSuccess || !sym) return fail(std::string("b2s_solve_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+    p = (int*)sym;
+    ptrs[device].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return 0;
+}
+
+extern "C" int b2s_solve_noalloc(const b2s_model* m, b2s_data* d, void* stream) {
+  if (!m || !d) return fail("null argument");
+  if (d->dev.nworld > B2S_NOALLOC_MAX_WORLDS)
+    return fail("b2s_solve_noalloc: nworld " + std::to_string(d->dev.nworld) + " exceeds the static scratch capacity of " +
+                std::to_string(B2S_NOALLOC_MAX_WORLDS) + " worlds (B2S_NOALLOC_MAX_WORLDS); use b2s_forward");
+  int* scratch = nullptr;
+  if (noalloc_scratch_ptr(d->device, &scratch) != 0) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  int* count = scratch;                           // [B2S_SOLVE_CLASSES]
+  int* order = scratch + B2S_SOLVE_CLASSES;       // [B2S_SOLVE_CLASSES][nworld]
+  CU(cudaMemsetAsync(count, 0, B2S_SOLVE_CLASSES * sizeof(int), st));
+  DataDev dv = d->dev;                            // same inputs / outputs, the queue in the static array
+  dv.solve_order = order; dv.solve_count = count;
+  k_noalloc_queue<<<(dv.nworld + 127) / 128, 128, 0, st>>>(dv, order, count);
+  b2s_count_launch();
+  launch_solve(m->dev, dv, st);
+  return launch_status("b2s_solve_noalloc");
+}
+extern "C" int b2s_noalloc_max_worlds(void) { return B2S_NOALLOC_MAX_WORLDS; }

@@ -358,3 +358,15 @@ def expand_model_fields(m: Model, nworld: int, fields) -> None:
   """Give each named Model field per-world storage (reference sim/randomization.py:20-54)."""
   for f in fields:
     m.expand(f, nworld)
+
+
+def solve_noalloc(m: Model, d: Data) -> None:
+  """Allocation-free re-solve of the constraint problem left in `d` (b2s_solve_noalloc, include/b200sim.h: no counterpart in
+  the reference; scheduling scratch in a fixed device array, nworld <= noalloc_max_worlds())."""
+  L = lib()
+  L.b2s_solve_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+  _check(L.b2s_solve_noalloc(m._h.ptr, d._h.ptr, _stream(m)))
+
+
+def noalloc_max_worlds() -> int:
+  return int(lib().b2s_noalloc_max_worlds())

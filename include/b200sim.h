@@ -288,6 +288,21 @@ int b2s_step(const b2s_model* m, b2s_data* d, void* stream);
 /* nsub sub-steps with ctrl held (one control decimation; manager_based_rl_env.py:114-119). */
 int b2s_step_n(const b2s_model* m, b2s_data* d, int nsub, void* stream);
 
+/* Allocation-free re-solve.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Runs the constraint
+ * solve (the k_solve stage of b2s_forward: SURVEY.md row K13) on the constraint rows, smooth forces and warm start that the
+ * last b2s_forward / b2s_step left in `d`, and rewrites d's qacc, qfrc_constraint, efc_force, solver_niter and solver_cost.
+ * The solver's scheduling scratch (cost-ordered world queues, normally part of d's arena and filled by the constraint stage)
+ * lives in a file-scope device array of fixed size instead, so the call allocates nothing: no cudaMalloc, cudaFree or
+ * allocating library routine.  Limit: d's nworld <= B2S_NOALLOC_MAX_WORLDS (larger -> error, nothing launched); every GPU
+ * that loads the library holds the array (4 MiB + 64 B) until exit.  The array is shared by all calls on a device: the call
+ * clears the part that must start at zero, and calls whose GPU work overlaps (different streams) race on it -- serialise
+ * them on one stream.  Results are identical to b2s_forward's solve (the queue only orders the work).  The first call on a
+ * device looks the array's device address up (cudaGetSymbolAddress): make that call outside stream capture. */
+#define B2S_NOALLOC_MAX_WORLDS 65536
+int b2s_solve_noalloc(const b2s_model* m, b2s_data* d, void* stream);
+int b2s_noalloc_max_worlds(void);
+
 /* Host-buffer convenience used by the end-to-end benchmark and by FFI callers
  * without a device allocator: copy ctrl (nworld*nu floats) from host, run nsub
  * sub-steps, copy qpos|qvel|sensordata back.  Pinned buffers recommended. */
