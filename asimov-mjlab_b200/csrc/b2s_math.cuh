@@ -379,6 +379,138 @@ DEV void tile_chol_solve(const float* L, const float* invd, int ld, int lane, fl
     y0 -= Lc0[k * ld] * xk;                      // column entries above the diagonal are zero: rows >= 32 need none
   }
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Row-owner Cholesky (round 2; replaces the 28-lane tile version in every stage kernel).  The symmetric matrix A (N = 7T
+// padded rows, n <= N real ones, identity padding) is factored as A = U U^T with U UPPER triangular, i.e. eliminating the LAST
+// dof first (MuJoCo's own order, which is also the order in which a kinematic tree has no fill-in).  Lane i owns row i of the
+// upper triangle in REGISTERS (a[j] = A_ij, j >= i; lanes 0 .. N-33 also own row i + 32 in b[]), the loop over pivots is fully
+// unrolled so every register index is static.  Step k: the pivot comes from its owner by shuffle, every lane scales its own
+// column entry l_i = a[k] / U_kk, the column goes through a double-buffered shared-memory line (one contiguous store, then
+// broadcast LDS.128 reads), and each lane applies a[j] -= l_i l_j for j < k.  About 17 instructions of overhead per pivot and
+// k FMAs: ~1.2 k warp instructions for N = 35 (the tile version: ~2.5 k, at 28/32 lanes and 7 x 3 phases).
+// Output: U row-major in S (entry (i, k), k >= i, at S[i * ld + k]; the strict lower triangle of S is NOT cleared and the
+// substitution below does not need it to be), 1 / U_kk in invd[k].  colbuf: 2 x RC_LINE floats, 16-byte aligned.
+#define RC_LINE 64
+template <int T>
+struct RowChol {
+  static constexpr int N = 7 * T;
+  static constexpr bool HI = N > 32;
+  static constexpr int NB = HI ? N - 32 : 1;      // second rows (32 .. N-1), one per lane 0 .. NB-1
+};
+// rows of the symmetric matrix whose LOWER triangle is stored in S (row stride ld; entry (i, j), j >= i, is read at S[j * ld + i],
+// which is contiguous across lanes); rows / columns >= n are identity padding
+template <int T>
+DEV void rowchol_load_lower(const float* S, int ld, int n, int lane, float (&a)[7 * T], float (&b)[RowChol<T>::NB]) {
+  constexpr int N = RowChol<T>::N;
+  const int i0 = min(lane, N - 1);
+#pragma unroll
+  for (int j = 0; j < N; j++) a[j] = (lane < n && j < n) ? S[j * ld + i0] : (j == lane ? 1.0f : 0.0f);
+  if (RowChol<T>::HI) {
+    const int i1 = min(lane + 32, N - 1);
+#pragma unroll
+    for (int j = 32; j < N; j++) b[j - 32] = (lane + 32 < n && j < n) ? S[j * ld + i1] : (j == lane + 32 ? 1.0f : 0.0f);
+  }
+}
+// steps k = k_hi-1 .. 0 of the elimination (k_hi = N: the whole factorisation)
+template <int T>
+DEV void rowchol_factor(float (&a)[7 * T], float (&b)[RowChol<T>::NB], int lane, float* S, int ld, float* invd, float* colbuf, int k_hi = 7 * T) {
+  constexpr int N = RowChol<T>::N;
+  constexpr bool HI = RowChol<T>::HI;
+  float* const Ur0 = S + min(lane, N - 1) * ld;
+  float* const Ur1 = S + min(lane + 32, N - 1) * ld;
+#pragma unroll
+  for (int k = N - 1; k >= 0; k--) {
+    if (k < k_hi) {
+      float* const line = colbuf + (k & 1) * RC_LINE;
+      // pivot: 1/sqrt by the SFU approximation + one Newton step (full fp32 accuracy), sqrt = s * rsqrt(s)
+      const float p = __shfl_sync(FULL, k < 32 ? a[k] : b[k >= 32 ? k - 32 : 0], k & 31);
+      const float sd = fmaxf(p, B2S_MINVAL);
+      float inv = rsqrtf(sd);
+      inv = inv * (1.5f - 0.5f * sd * inv * inv);
+      float la = a[k] * inv;
+      if (k < 32 && lane == k) la = sd * inv;
+      a[k] = la;
+      line[lane] = la;
+      if (lane <= k && lane < N) Ur0[k] = la;
+      if (HI && k >= 32) {
+        float lb = b[k >= 32 ? k - 32 : 0] * inv;
+        if (lane == k - 32) lb = sd * inv;
+        b[k >= 32 ? k - 32 : 0] = lb;
+        if (lane < RowChol<T>::NB) { line[32 + lane] = lb; if (lane + 32 <= k) Ur1[k] = lb; }
+      }
+      if (lane == 0) invd[k] = inv;
+      __syncwarp();
+      const float4* l4 = reinterpret_cast<const float4*>(line);
+#pragma unroll
+      for (int q = 0; q < (k + 3) / 4; q++) {
+        const float4 v = l4[q];
+        if (4 * q + 0 < k) a[4 * q + 0] -= la * v.x;
+        if (4 * q + 1 < k) a[4 * q + 1] -= la * v.y;
+        if (4 * q + 2 < k) a[4 * q + 2] -= la * v.z;
+        if (4 * q + 3 < k) a[4 * q + 3] -= la * v.w;
+      }
+      if (HI && k > 32) {
+        const float lb = b[k >= 32 ? k - 32 : 0];
+#pragma unroll
+        for (int j = 32; j < k; j++) b[j - 32] -= lb * line[j];
+      }
+    }
+  }
+  __syncwarp();
+}
+// Solve U U^T x = g with the factor above: lane l holds g[l] in b0 and g[l + 32] in b1 (entries of padding rows must be 0).
+// U y = g runs from the last row up, U^T x = y from the first down; a finished lane keeps its result in a second register, so
+// the junk in S's strict lower triangle (and the clamped rows of lanes >= N) only ever lands in values that are not read again.
+template <int T>
+DEV void rowchol_solve(const float* S, const float* invd, int ld, int lane, float& b0, float& b1) {
+  constexpr int N = RowChol<T>::N;
+  constexpr bool HI = RowChol<T>::HI;
+  constexpr int N0 = HI ? 32 : N, UN = HI ? 8 : 7;
+  const float* Ur0 = S + min(lane, N - 1) * ld;
+  const float* Ur1 = S + min(lane + 32, N - 1) * ld;
+  const float* Uc0 = S + min(lane, N - 1);
+  const float* Uc1 = S + min(lane + 32, N - 1);
+  float y0 = 0.f, y1 = 0.f;
+  if (HI) {
+#pragma unroll
+    for (int k = N - 1; k >= 32; k--) {
+      const float yk = __shfl_sync(FULL, b1, k - 32) * invd[k];
+      if (lane == k - 32) y1 = yk;
+      b0 -= Ur0[k] * yk;
+      b1 -= Ur1[k] * yk;
+    }
+  }
+#pragma unroll UN
+  for (int k = N0 - 1; k >= 0; k--) {
+    const float yk = __shfl_sync(FULL, b0, k) * invd[k];
+    if (lane == k) y0 = yk;
+    b0 -= Ur0[k] * yk;
+  }
+#pragma unroll UN
+  for (int k = 0; k < N0; k++) {
+    const float xk = __shfl_sync(FULL, y0, k) * invd[k];
+    if (lane == k) b0 = xk;
+    y0 -= Uc0[k * ld] * xk;
+    if (HI) y1 -= Uc1[k * ld] * xk;
+  }
+  if (HI) {
+#pragma unroll
+    for (int k = 32; k < N; k++) {
+      const float xk = __shfl_sync(FULL, y1, k - 32) * invd[k];
+      if (lane == k - 32) b1 = xk;
+      y1 -= Uc1[k * ld] * xk;
+    }
+  }
+}
+// factor the symmetric matrix whose lower triangle is in S (n real rows) in place: S ends up holding U (see above)
+template <int T>
+DEV void rowchol_smem(float* S, int n, int ld, int lane, float* invd, float* colbuf) {
+  float a[7 * T], b[RowChol<T>::NB];
+  rowchol_load_lower<T>(S, ld, n, lane, a, b);
+  __syncwarp();
+  rowchol_factor<T>(a, b, lane, S, ld, invd, colbuf);
+}
 __host__ __device__ inline int b2s_hdim(int T) { return 7 * T; }                         // padded matrix dimension
 __host__ __device__ inline int b2s_hld(int T) { return (7 * T + 1) | 1; }                 // odd row stride > 7T
 __host__ __device__ inline int b2s_tile_for(int nv) { int T = (nv + 6) / 7; if (T < 1) T = 1; if (T == 7) T = 8; return T; }

@@ -3,7 +3,7 @@
 #include "b2s_math.cuh"
 #include "b2s_api.h"
 
-extern __shared__ float b2s_smem[];
+extern __shared__ __align__(16) float b2s_smem[];
 
 // 6D velocity [ang, lin] of a frame at `pos` riding on `body` (mj_objectVelocity), world orientation
 DEV sv6 object_velocity(const ModelDev& m, const float* cvel, const float* com, int body, v3 pos) {
@@ -290,14 +290,16 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
 }
 
 // ------------------------------------------------------------------------------------------- k_integrate
-// shared per warp: A hdim*ld | invd 7T | dg nvp | qa nvp
+// shared per warp: Cholesky scratch line 2*RC_LINE | A hdim*ld | invd 7T | dg nvp | qa nvp
+__host__ __device__ inline int integ_smem_floats(int T, int nvp) { return (2 * RC_LINE + b2s_hdim(T) * b2s_hld(T) + 7 * T + 2 * nvp + 3) & ~3; }
 template <int T>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
   const int nv = m.nv, nvp = m.nvp, ld = b2s_hld(T);
-  float* A = b2s_smem + (size_t)warp * (b2s_hdim(T) * ld + 7 * T + 2 * nvp);
+  float* s_col = b2s_smem + (size_t)warp * integ_smem_floats(T, nvp);
+  float* A = s_col + 2 * RC_LINE;
   float* invd = A + b2s_hdim(T) * ld;
   float* dg = invd + 7 * T;
   float* qa = dg + nvp;
@@ -410,11 +412,11 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_integrate(const Mode
         }
     }
     __syncwarp();
-    tile_cholesky_smem<T>(A, nv, ld, lane, invd);
+    rowchol_smem<T>(A, nv, ld, lane, invd, s_col);
     float b0 = 0.f, b1 = 0.f;
     if (lane < nv) b0 = d.qfrc_smooth[(size_t)w * nv + lane] + d.qfrc_constraint[(size_t)w * nv + lane];
     if (lane + 32 < nv) b1 = d.qfrc_smooth[(size_t)w * nv + lane + 32] + d.qfrc_constraint[(size_t)w * nv + lane + 32];
-    warp_chol_solve_inv(A, invd, nv, ld, lane, b0, b1);
+    rowchol_solve<T>(A, invd, ld, lane, b0, b1);
     if (lane < nv) qa[lane] = b0;
     if (lane + 32 < nv) qa[lane + 32] = b1;
   }
@@ -462,7 +464,7 @@ size_t smem_sensors(const ModelDev& m, const DataDev& d) {
 }
 size_t smem_integrate(const ModelDev& m) {
   const int T = b2s_tile_for(m.nv);
-  return (size_t)B2S_WARPS_PER_CTA * (b2s_hdim(T) * b2s_hld(T) + 7 * T + 2 * m.nvp) * sizeof(float);
+  return (size_t)B2S_WARPS_PER_CTA * integ_smem_floats(T, m.nvp) * sizeof(float);
 }
 const void* fn_sensors() { return (const void*)k_sensors; }
 const void* fn_integrate(const ModelDev& m) {

@@ -13,7 +13,7 @@
 #include "b2s_math.cuh"
 #include "b2s_api.h"
 
-extern __shared__ float b2s_smem[];
+extern __shared__ __align__(16) float b2s_smem[];
 
 // ---------------------------------------------------------------------------------------------- k_position
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const ModelDev m, const DataDev d) {
@@ -197,9 +197,9 @@ void launch_static_frames(const ModelDev& m, const DataDev& d, cudaStream_t st) 
 }
 
 // ---------------------------------------------------------------------------------------------- k_dynamics
-// shared memory per warp (floats): cdof 6nv | crb 10nb | cvel 6nb | cdd 6nv | cfrc 6nb | fext 6nb | M nv*ld | vec 4*nvp
+// shared memory per warp (floats): Cholesky scratch line 2*RC_LINE | cdof 6nv | crb 10nb | cvel 6nb | cdd 6nv | cfrc 6nb | fext 6nb | M nv*ld | vec 4*nvp
 __host__ __device__ inline int dyn_smem_floats(int nv, int nvp, int nb, int T) {
-  return 6 * nv + 10 * nb + 6 * nb + 6 * nv + 6 * nb + 6 * nb + b2s_hdim(T) * b2s_hld(T) + 7 * T + 4 * nvp;
+  return (2 * RC_LINE + 6 * nv + 10 * nb + 6 * nb + 6 * nv + 6 * nb + 6 * nb + b2s_hdim(T) * b2s_hld(T) + 7 * T + 4 * nvp + 3) & ~3;
 }
 
 template <int T>
@@ -208,7 +208,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
   const int nb = m.nbody, nv = m.nv, nvp = m.nvp, ld = b2s_hld(T);
-  float* s_cdof = b2s_smem + (size_t)warp * dyn_smem_floats(nv, nvp, nb, T);
+  float* s_col = b2s_smem + (size_t)warp * dyn_smem_floats(nv, nvp, nb, T);     // 16-byte aligned
+  float* s_cdof = s_col + 2 * RC_LINE;
   float* s_crb = s_cdof + 6 * nv;
   float* s_cvel = s_crb + 10 * nb;
   float* s_cdd = s_cvel + 6 * nb;
@@ -423,9 +424,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   }
   __syncwarp();
   // factor M in shared memory and solve for the unconstrained acceleration
-  tile_cholesky_smem<T>(s_M, nv, ld, lane, s_invd);
+  rowchol_smem<T>(s_M, nv, ld, lane, s_invd, s_col);
   float b0 = lane < nv ? s_rhs[lane] : 0.f, b1 = lane + 32 < nv ? s_rhs[lane + 32] : 0.f;
-  warp_chol_solve_inv(s_M, s_invd, nv, ld, lane, b0, b1);
+  rowchol_solve<T>(s_M, s_invd, ld, lane, b0, b1);
   if (lane < nv) d.qacc_smooth[(size_t)w * nv + lane] = b0;
   if (lane + 32 < nv) d.qacc_smooth[(size_t)w * nv + lane + 32] = b1;
 }

@@ -592,6 +592,9 @@ template <int T, int V>
 __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const ModelDev m, const DataDev d) {
   constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#ifdef SOLVE_TIMING
+  const long long t_start = clock64();      // development builds only (tools/exp_solve_time.py): per-world solve time in cycles -> solver_cost
+#endif
   // worlds are taken from the cost-ordered queues, most expensive class first (k_constraint filled them)
   int w = blockIdx.x * SOLVE_WARPS + warp;
   if (w >= d.nworld) return;
@@ -832,6 +835,9 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     efc_force[r] = row_force<T, V>(c, r, c.Jaref()[r]);
   }
   if (lane == 0) { d.solver_niter[w] = iter; d.solver_cost[w] = cost; }
+#ifdef SOLVE_TIMING
+  if (lane == 0) d.solver_cost[w] = (float)(clock64() - t_start);
+#endif
 }
 
 static int tile_for(int nv) { return b2s_tile_for(nv); }

@@ -33,8 +33,19 @@ if "terrain_origins" in m.meta:       # spawn on the generated terrain like benc
   D.qpos[:, 0:3] += org.cuda()
 D.qpos[:, 7:] += (0.05 * torch.randn(W, m.nq - 7, generator=g)).cuda()
 D.ctrl[:] += (0.1 * torch.randn(W, m.nu, generator=g)).cuda()
-engine.step(M, D, warm)
-if int(os.environ.get("RAND", "0")):      # the bench's state distribution: random action targets, resampled every 4 sub-steps
+if not int(os.environ.get("STAND", "0")):
+  engine.step(M, D, warm)
+if int(os.environ.get("STAND", "0")):     # the bench's first 40 steps / the RL regime: robots still upright, both feet loaded (nefc ~ 50, 5 Newton iterations)
+  import bench
+  key = m.keys["robot/init_state"]
+  D.qpos[:] = torch.tensor(key["qpos"], dtype=torch.float32, device="cuda")
+  D.qpos[:, 7:] += (0.02 * torch.randn(W, m.nq - 7, generator=g)).cuda()
+  D.qvel.zero_(); D.qacc_warmstart.zero_(); D.ctrl[:] = torch.tensor(key["ctrl"], dtype=torch.float32, device="cuda")
+  engine.forward(M, D)
+  pool = torch.as_tensor(bench.action_targets(m, 16, W, seed=1000)).cuda()
+  for k in range(10):
+    D.ctrl.copy_(pool[k]); engine.step(M, D, 4)
+elif int(os.environ.get("RAND", "0")):      # the bench's state distribution: random action targets, resampled every 4 sub-steps
   import bench
   pool = torch.as_tensor(bench.action_targets(m, 40, W, seed=1000)).cuda()
   for k in range(40):
