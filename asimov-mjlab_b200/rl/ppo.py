@@ -102,6 +102,17 @@ class ActorCritic(nn.Module):
     return self.critic(self.critic_norm(critic_obs)).squeeze(-1)
 
 
+def init_policy(seed: int, num_obs: int, num_critic_obs: int, num_actions: int, device) -> ActorCritic:
+  """Identical initial weights on every rank (no broadcast needed) WITHOUT touching the process's random streams: the
+  env seeded them with seed + rank (reference utils/random.py:9-26), and commands, reset poses, observation noise, pushes
+  and the action noise must keep differing between ranks.  The network is initialised under a forked generator state."""
+  device = torch.device(device)
+  with torch.random.fork_rng(devices=[device] if device.type == "cuda" else []):
+    torch.manual_seed(seed)
+    ac = ActorCritic(num_obs, num_critic_obs, num_actions)
+  return ac.to(device)
+
+
 class PPO:
   def __init__(self, env, device, steps_per_env: int = 24, lr: float = 1e-3, gamma: float = 0.99, lam: float = 0.95, clip: float = 0.2,
                entropy_coef: float = 0.01, value_coef: float = 1.0, epochs: int = 5, mini_batches: int = 4, desired_kl: float = 0.01,
@@ -112,8 +123,7 @@ class PPO:
       torch.backends.cudnn.allow_tf32 = True
     self.gamma, self.lam, self.clip, self.entropy_coef, self.value_coef = gamma, lam, clip, entropy_coef, value_coef
     self.epochs, self.mini_batches, self.desired_kl, self.max_grad_norm, self.lr = epochs, mini_batches, desired_kl, max_grad_norm, lr
-    torch.manual_seed(seed)            # same seed on every rank: identical initial weights, no broadcast needed
-    self.ac = ActorCritic(env.num_obs, env.num_privileged_obs, env.num_actions).to(device)
+    self.ac = init_policy(seed, env.num_obs, env.num_privileged_obs, env.num_actions, device)
     # learning rate lives on the device: the adaptive-KL schedule then needs no host synchronisation per mini-batch
     self.lr_t = torch.tensor(float(lr), device=device)
     self.opt = torch.optim.Adam(self.ac.parameters(), lr=self.lr_t, capturable=True)

@@ -48,3 +48,34 @@ def test_shard_range_properties():
       assert sum(len(p) for p in parts) == total
       assert all(parts[i].stop == parts[i + 1].start for i in range(world - 1))
       assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+
+
+def _policy_worker(rank, q):
+  """What rl/train.py does on rank `rank`: the env seeds the process with seed + rank, then PPO builds the policy."""
+  from asimov_mjlab_b200.rl.ppo import init_policy
+  torch.manual_seed(100 + rank)                      # the env's per-rank seed
+  before = torch.rand(4)                             # env draws ...
+  ac = init_policy(0, 12, 15, 5, "cpu")
+  after = torch.rand(4)                              # ... and keeps drawing from ITS stream afterwards
+  torch.manual_seed(100 + rank)
+  ref = torch.rand(8)
+  w = torch.cat([p.detach().reshape(-1) for p in ac.parameters()])
+  q.put((rank, w.numpy(), torch.cat([before, after]).numpy(), ref.numpy()))
+
+
+def test_policy_init_is_identical_across_ranks_and_leaves_the_per_rank_streams_alone():
+  """PPO used to call torch.manual_seed(seed) AFTER the env had seeded itself with seed + rank, which put
+  every rank on the same random stream.  Two spawned 'ranks': same weights, different streams, stream not disturbed."""
+  ctx = mp.get_context("spawn")
+  q = ctx.Queue()
+  ps = [ctx.Process(target=_policy_worker, args=(r, q)) for r in range(2)]
+  for p in ps:
+    p.start()
+  out = sorted((q.get(timeout=120) for _ in ps), key=lambda t: t[0])
+  for p in ps:
+    p.join(timeout=60)
+    assert p.exitcode == 0
+  (_, w0, s0, ref0), (_, w1, s1, ref1) = out
+  assert np.array_equal(w0, w1)                      # identical initial weights
+  assert np.array_equal(s0, ref0) and np.array_equal(s1, ref1)      # the policy init consumed nothing from the rank's stream
+  assert not np.array_equal(s0, s1)                  # and the ranks' streams differ
