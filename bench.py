@@ -44,8 +44,9 @@ def alg_bytes(m, friction_geoms):
   w = m.nq + 3 * m.nv + 1 + m.nsensordata + (3 + 4 + 3 + 6) * nb + 12 * m.nsite
   return 4 * (r + w + 3 * friction_geoms)
 # DRAM traffic of one sub-step (7 stage kernels), dram__bytes_read.sum + dram__bytes_write.sum from the `ncu --set full`
-# capture profiles/step_r1k_metrics.txt (G1-flat, 4096 worlds): 118 477 568 B read + 978 432 B written
-NCU_TRAFFIC = {("g1_flat", 4096): (119456000, "profiles/step_r1k_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step)")}
+# capture profiles/step_r2a_metrics.txt (G1-flat, 4096 worlds, upright regime): 141.3 MB read + 4.9 MB written.  NOT measured
+# live (ncu cannot run inside the timed region): the JSON names the file it comes from in `traffic_from_profile`.
+NCU_TRAFFIC = {("g1_flat", 4096): (146100000, "profiles/step_r2a_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step, upright regime)")}
 DECIMATION = 4
 RESET_PERIOD_STEPS = 250            # reset every 1000 sub-steps, forward() inside the timed region
 
@@ -60,6 +61,7 @@ def parse():
   ap.add_argument("--cpu-baseline", type=int, default=1)
   ap.add_argument("--ls-parallel", type=int, default=1)
   ap.add_argument("--workload", default="g1_flat", choices=sorted(WORKLOADS))
+  ap.add_argument("--extras", type=int, default=1, help="also measure (outside the timed region) the state regimes, the other workloads and PPO")
   ap.add_argument("--overlap", type=int, default=1, help="stage overlap on forked graph branches (0: serial stages)")
   ap.add_argument("--cone", default="pyramidal", choices=["pyramidal", "elliptic"], help="friction cone (the reference's default is pyramidal)")
   return ap.parse_args()
@@ -141,23 +143,59 @@ def action_targets(m, n_batches, envs, seed, device=None):
 
 
 # ------------------------------------------------------------------------------------------- reference arm (CPU)
-def cpu_rollout(m, nworld, nsub_total, nthread, seed=0, ls_parallel=1):
-  """Oracle (CPU restatement of the reference's step) on the host cores: nworld worlds x nsub_total sub-steps,
-  actions resampled every DECIMATION sub-steps.  Returns sub-steps/s.  (bench.py may execute oracle/ only here.)"""
-  sys.path.insert(0, os.path.join(ROOT, "oracle"))
-  from oracle import Oracle
-  orc = Oracle(m, "f32", 50, 300, ls_parallel=ls_parallel)
-  key = m.keys["robot/init_state"]
-  worlds = [orc.new_world(key["qpos"], None, key["ctrl"]) for _ in range(nworld)]
-  nb = nsub_total // DECIMATION
-  ctrl = action_targets(m, nb, nworld, seed)
-  t0 = time.perf_counter()
-  for b in range(nb):
-    for w in range(nworld):
-      worlds[w]["ctrl"][:] = ctrl[b, w]
-    orc.rollout(worlds, DECIMATION, nthread)
-  dt = time.perf_counter() - t0
-  return nworld * nb * DECIMATION / dt, dt
+class CpuSampler:
+  """The CPU arm: the oracle (CPU restatement of the reference's step; bench.py may execute oracle/ only here) on the host
+  cores, OpenMP over worlds.  One EPISODE = `episode_substeps` sub-steps from the reset state with a fresh action batch every
+  DECIMATION sub-steps -- the same state distribution the GPU arm's timed region sees (its K steps follow a reset).  Only the
+  rollout calls are timed: joint targets are written between them, outside the clock.  Both `cpu_baseline` (in the B200 arm's
+  line) and `--impl reference` use this one procedure, so they agree."""
+
+  def __init__(self, m, ls_parallel=1, worlds_per_core=16, seed=0):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    from oracle import Oracle
+    self.m, self.cores = m, os.cpu_count() or 1
+    self.nw = worlds_per_core * self.cores
+    self.orc = Oracle(m, "f32", 50, 300, ls_parallel=ls_parallel)
+    self.key = m.keys["robot/init_state"]
+    self.worlds = [self.orc.new_world(self.key["qpos"], None, self.key["ctrl"]) for _ in range(self.nw)]
+    self.seed = seed
+
+  def reset(self):
+    import numpy as np
+    rng = np.random.default_rng(self.seed)
+    for w in self.worlds:
+      w["qpos"][:] = self.key["qpos"]; w["qpos"][7:] += 0.02 * rng.standard_normal(self.m.nq - 7)
+      w["qvel"][:] = 0; w["qacc_warmstart"][:] = 0; w["time"][:] = 0; w["ctrl"][:] = self.key["ctrl"]
+      self.orc.forward(w)
+
+  def episode(self, episode_substeps):
+    """Returns the seconds spent inside the rollout calls of one episode."""
+    nb = max(episode_substeps // DECIMATION, 1)
+    ctrl = action_targets(self.m, nb, self.nw, self.seed)
+    self.seed += 1
+    self.reset()
+    t = 0.0
+    for b in range(nb):
+      for w in range(self.nw):
+        self.worlds[w]["ctrl"][:] = ctrl[b, w]
+      t0 = time.perf_counter()
+      self.orc.rollout(self.worlds, DECIMATION, self.cores)
+      t += time.perf_counter() - t0
+    return t, nb * DECIMATION * self.nw
+
+  def run(self, episode_substeps, min_seconds, max_seconds=60.0, min_episodes=1):
+    self.episode(min(episode_substeps, 8 * DECIMATION))          # warm: OpenMP team, page faults, caches
+    t = n = 0.0
+    ep = 0
+    while (t < min_seconds or ep < min_episodes) and t < max_seconds:
+      dt, dn = self.episode(episode_substeps)
+      t += dt; n += dn; ep += 1
+    return n / t, t, ep
+
+
+def cpu_sample_desc(cs, episode_substeps, t, ep):
+  return (f"{cs.nw} worlds x {ep} episode(s) of {episode_substeps} sub-steps from the reset state (the GPU arm's timed window), "
+          f"oracle f32 with OpenMP on {cs.cores} threads, {t:.1f} s inside the rollout calls")
 
 
 def run_reference(args):
@@ -165,30 +203,189 @@ def run_reference(args):
   if rank != 0:
     return
   m = load_model(args.ls_parallel, args.workload, args.cone)
-  cores = os.cpu_count() or 1
-  nworld = 16 * cores
-  # warm-up then K timed steps, each a bounded sample: one decimation of `nworld` worlds
-  cpu_rollout(m, nworld, DECIMATION * max(args.warmup, 1), cores)
-  rate, dt = cpu_rollout(m, nworld, DECIMATION * args.steps, cores)
-  sample = f"{nworld} worlds x {DECIMATION * args.steps} sub-steps, oracle f32 (CPU restatement of the step), OpenMP {cores} threads"
+  cs = CpuSampler(m, args.ls_parallel)
+  # a "step" of this arm = one episode of the GPU arm's timed window (K decimations after a reset) on cs.nw worlds; W warm-up
+  # and K timed steps would take hours on the CPU, so the sample is bounded: at least 5 s, at most 60 s of rollout time
+  window = min(args.steps, RESET_PERIOD_STEPS) * DECIMATION
+  rate, t, ep = cs.run(window, min_seconds=5.0)
   out = {
     "impl": "reference", "metric": "env_steps_per_s", "value": rate, "unit": "physics sub-steps/s (1 env-step = 1 sim.step per world)",
-    "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+    "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t / max(ep, 1) / max(window // DECIMATION, 1) * 1e3,
     "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-    "config": {"workload": WORKLOADS[args.workload][1], "envs_per_step": nworld, "decimation": DECIMATION},
-    "cpu_baseline": {"value": rate, "unit": "physics sub-steps/s", "cores": cores, "kind": "port", "sample": sample},
+    "config": {"workload": WORKLOADS[args.workload][1], "envs_per_step": cs.nw, "decimation": DECIMATION,
+               "bounded_sample": f"{ep} episode(s) x {window} sub-steps x {cs.nw} worlds; one step = one decimation of {cs.nw} worlds"},
+    "cpu_baseline": {"value": rate, "unit": "physics sub-steps/s", "cores": cs.cores, "kind": "port", "sample": cpu_sample_desc(cs, window, t, ep)},
     "e2e": {"value": rate, "unit": "physics sub-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
   }
   print(json.dumps(out), flush=True)
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
+class PhysBench:
+  """One physics workload on one GPU: the Simulation, its reset state, a pool of action batches and the bench step."""
+
+  def __init__(self, workload, E, dev, rank, ls_parallel=1, cone="pyramidal", overlap=1):
+    import numpy as np
+    import torch
+    from asimov_mjlab_b200 import engine
+    from asimov_mjlab_b200.sim import MujocoCfg, Simulation, SimulationCfg
+    self.torch, self.engine, self.E, self.dev = torch, engine, E, dev
+    m = self.m = load_model(ls_parallel, workload, cone)
+    cfg = SimulationCfg(nconmax=50, njmax=300, ls_parallel=bool(ls_parallel),
+                        mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20, cone=cone))
+    sim = self.sim = Simulation(E, cfg, m, dev)
+    M, D = self.M, self.D = sim.model, sim.data
+    # foot-friction domain randomisation ON (per-world Model reads stay honest; velocity_env_cfg.py:230-240)
+    sim.expand_model_fields(("geom_friction",))
+    g = torch.Generator(device="cpu").manual_seed(rank)
+    self.foot = foot = [i for i, n in enumerate(m.names["geom"]) if ("foot" in n or "_toe" in n) and n.endswith("_collision")]
+    fr = 0.3 + 0.9 * torch.rand(E, len(foot), generator=g)
+    M.geom_friction[:, foot, 0] = fr.to(dev)
+    M.opt.stage_overlap = int(overlap)
+    n0 = engine.launch_count()
+    sim.create_graph(decimation=DECIMATION)
+    assert engine.launch_count() - n0 >= 7 * DECIMATION
+    key = m.keys["robot/init_state"]
+    self.q0 = torch.tensor(key["qpos"], dtype=torch.float32, device=dev)
+    self.c0 = torch.tensor(key["ctrl"], dtype=torch.float32, device=dev)
+    self.nbatch = 64
+    self.ctrl_pool = torch.as_tensor(action_targets(m, self.nbatch, E, seed=1000 + rank), device=dev)
+    origins = self.origins = torch.zeros(E, 3, device=dev)
+    if "terrain_origins" in m.meta:     # curriculum spawn points of the box terrain (terrain_importer.py:203-223)
+      from asimov_mjlab_b200 import terrains
+      eo, _, _ = terrains.env_origins_curriculum(E, np.asarray(m.meta["terrain_origins"]), seed=rank)
+      origins[:] = torch.as_tensor(eo, dtype=torch.float32, device=dev)
+      origins[:, 0:2] += (torch.rand(E, 2, generator=g) - 0.5).to(dev) * 2.0     # off the platform centre, onto the steps
+      # spawn ON the terrain: highest surface under the robot's footprint (the generator's own hfield-pyramid origins
+      # lie inside the field's slab, heightfield_terrains.py:243-246)
+      xy = origins[:, 0:2].cpu().numpy()
+      surf = np.max([terrains.surface_height(m, xy + np.array(o)) for o in ((0, 0), (0.3, 0.2), (0.3, -0.2), (-0.3, 0.2), (-0.3, -0.2))], axis=0)
+      origins[:, 2] = torch.as_tensor(surf, dtype=torch.float32, device=dev) + 0.05
+    else:
+      side = int(np.ceil(np.sqrt(E)))
+      idx = torch.arange(E, device=dev)
+      origins[:, 0] = (idx // side).float() * 2.5
+      origins[:, 1] = (idx % side).float() * 2.5
+    self.noise = 0.02 * torch.randn(E, m.nq - 7, generator=g).to(dev)
+
+  def reset_all(self):
+    D = self.D
+    D.qpos[:] = self.q0
+    D.qpos[:, 0:3] += self.origins
+    D.qpos[:, 7:] += self.noise
+    D.qvel.zero_(); D.qacc_warmstart.zero_(); D.time.zero_()
+    D.ctrl[:] = self.c0
+    self.sim.forward()
+
+  def one_step(self, i):
+    if i % RESET_PERIOD_STEPS == 0:
+      self.reset_all()
+    self.D.ctrl.copy_(self.ctrl_pool[i % self.nbatch])
+    self.sim.step_decimation()
+
+  def timed(self, steps, warmup, first=0, barrier=None):
+    """W warm-up steps, then exactly K timed steps between CUDA events; step indices start at `first` (a multiple of the reset
+    period resets first).  Returns (milliseconds, resets inside the timed region)."""
+    torch = self.torch
+    for i in range(warmup):
+      self.one_step(first + i)
+    if barrier:
+      barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_resets = 0
+    if barrier:
+      barrier()
+    e0.record()
+    for i in range(steps):
+      n_resets += int((first + i) % RESET_PERIOD_STEPS == 0)
+      self.one_step(first + i)
+    e1.record()
+    if barrier:
+      barrier()
+    else:
+      torch.cuda.synchronize()
+    return e0.elapsed_time(e1), n_resets
+
+  def rate(self, ms, steps, world=1):
+    return world * self.E * DECIMATION * steps / (ms * 1e-3)
+
+
+def extra_measurements(args, world, rank, dev, pb):
+  """Driver-visible numbers for the other BASELINE.json configs, OUTSIDE the headline's timed region: the two state regimes of
+  the headline workload, configs[2] (Go1 rough, box and height-field terrain), configs[3] (G1 tracking env step) and configs[4]
+  (PPO rollout + update at --gpus N, the one place a collective is on the path)."""
+  import torch
+  import torch.distributed as dist
+  ex = {}
+  # ---- regimes of the headline workload (same sim): upright right after a reset vs. fallen after 150 random-action steps
+  ms, _ = pb.timed(20, 3, first=0)
+  up = pb.rate(ms, 20)
+  for i in range(23, 150):
+    pb.one_step(i)
+  ms, _ = pb.timed(20, 0, first=150)
+  ex["regimes"] = {"upright_first_80_substeps_after_reset": up, "fallen_substeps_600_to_680": pb.rate(ms, 20),
+                   "unit": "physics sub-steps/s per GPU", "note": "robots driven by random joint targets stand for ~40 control steps (two loaded feet: ~50 constraint rows, ~5.4 Newton iterations), then lie on the ground (~15 rows, ~3.3 iterations)"}
+  if rank == 0 and world == 1:
+    wl = {}
+    for name in ("go1_rough", "go1_rough_hf", "asimov_toe_flat", "asimov_toe_full_flat"):
+      try:
+        p2 = PhysBench(name, args.envs, dev, rank, args.ls_parallel)
+        ms, _ = p2.timed(40, 5)
+        wl[name] = {"value": p2.rate(ms, 40), "unit": "physics sub-steps/s", "envs": args.envs, "steps": 40, "workload": WORKLOADS[name][1]}
+        del p2
+      except Exception as e:      # an extra must never take the headline line down
+        wl[name] = {"error": repr(e)[:200]}
+    ex["workloads"] = wl
+  # ---- env step of the tracking task (configs[3]) and PPO on the velocity task (configs[4]); all ranks take part
+  try:
+    from asimov_mjlab_b200.rl.ppo import PPO
+    from asimov_mjlab_b200.rl.tracking_env import G1TrackingFlatEnv
+    from asimov_mjlab_b200.rl.velocity_env import G1VelocityFlatEnv
+    if world == 1:
+      env = G1TrackingFlatEnv(args.envs, dev, seed=rank)
+      act = torch.zeros(args.envs, env.num_actions, device=dev)
+      for _ in range(5):
+        env.step(act)
+      e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+      e0.record()
+      for k in range(30):
+        act.uniform_(-1.0, 1.0); env.step(act)
+      e1.record(); torch.cuda.synchronize()
+      ex.setdefault("workloads", {})["g1_tracking_env_step"] = {
+        "value": args.envs * 30 / (e0.elapsed_time(e1) * 1e-3), "unit": "env-steps/s (4 physics sub-steps + fused manager terms each, random actions)",
+        "envs": args.envs, "steps": 30, "workload": "Mjlab-Tracking-Flat-Unitree-G1, synthetic motion (BASELINE.json configs[3])"}
+      del env
+    env = G1VelocityFlatEnv(args.envs, dev, seed=rank)
+    algo = PPO(env, torch.device(dev), steps_per_env=24, seed=0)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    t_roll = t_upd = 0.0
+    iters, warm = 3, 1
+    for it in range(warm + iters):
+      if it == warm and world > 1:
+        dist.barrier()
+      torch.cuda.synchronize()
+      ev[0].record(); algo.rollout(); ev[1].record(); algo.update(); ev[2].record()
+      torch.cuda.synchronize()
+      if it >= warm:
+        t_roll += ev[0].elapsed_time(ev[1]); t_upd += ev[1].elapsed_time(ev[2])
+    t = torch.tensor([t_roll, t_upd], device=dev)
+    if world > 1:
+      dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    n = iters * 24 * args.envs * world
+    ex["ppo"] = {"value": n / (float(t[0] + t[1]) * 1e-3), "unit": "env-steps/s over all GPUs (rollout + update; 4 physics sub-steps per env-step)",
+                 "rollout_env_steps_per_s": n / (float(t[0]) * 1e-3), "rollout_ms_per_iter": float(t[0]) / iters, "update_ms_per_iter": float(t[1]) / iters,
+                 "envs_per_gpu": args.envs, "n_gpus": world, "iters": iters, "steps_per_env": 24, "epochs": 5, "mini_batches": 4,
+                 "collectives": "per mini-batch ONE NCCL all-reduce of the flattened gradients + KL (0.44 M floats, 20 per iteration); per iteration: advantage moments, observation-normaliser statistics, episode statistics",
+                 "workload": "Mjlab-Velocity-Flat-Unitree-G1, rsl_rl PPO hyper-parameters (BASELINE.json configs[4])"}
+  except Exception as e:
+    ex["ppo"] = {"error": repr(e)[:300]}
+  return ex
+
+
 def run_b200(args):
-  import numpy as np
   import torch
   import torch.distributed as dist
   from asimov_mjlab_b200 import engine
-  from asimov_mjlab_b200.sim import MujocoCfg, Simulation, SimulationCfg
 
   world = int(os.environ.get("WORLD_SIZE", "1"))
   rank = int(os.environ.get("RANK", "0"))
@@ -200,104 +397,46 @@ def run_b200(args):
   if world > 1:
     dist.init_process_group("nccl", device_id=torch.device(dev))
   E = args.envs
-  m = load_model(args.ls_parallel, args.workload, args.cone)
-  cfg = SimulationCfg(nconmax=50, njmax=300, ls_parallel=bool(args.ls_parallel),
-                      mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20, cone=args.cone))
-  sim = Simulation(E, cfg, m, dev)
-  M, D = sim.model, sim.data
-  # foot-friction domain randomisation ON (per-world Model reads stay honest; velocity_env_cfg.py:230-240)
-  sim.expand_model_fields(("geom_friction",))
-  g = torch.Generator(device="cpu").manual_seed(rank)
-  foot = [i for i, n in enumerate(m.names["geom"]) if ("foot" in n or "_toe" in n) and n.endswith("_collision")]
-  fr = 0.3 + 0.9 * torch.rand(E, len(foot), generator=g)
-  M.geom_friction[:, foot, 0] = fr.to(dev)
-  M.opt.stage_overlap = int(args.overlap)
-  n0 = engine.launch_count()
-  sim.create_graph(decimation=DECIMATION)
+  pb = PhysBench(args.workload, E, dev, rank, args.ls_parallel, args.cone, args.overlap)
+  m, M, D = pb.m, pb.M, pb.D
   per_graph = {"step": 7, "forward": 6, "decimation": 7 * DECIMATION}
-  assert engine.launch_count() - n0 >= per_graph["decimation"]
-  key = m.keys["robot/init_state"]
-  q0 = torch.tensor(key["qpos"], dtype=torch.float32, device=dev)
-  c0 = torch.tensor(key["ctrl"], dtype=torch.float32, device=dev)
-  nbatch = 64
-  ctrl_pool = torch.as_tensor(action_targets(m, nbatch, E, seed=1000 + rank), device=dev)
-  origins = torch.zeros(E, 3, device=dev)
-  if "terrain_origins" in m.meta:     # curriculum spawn points of the box terrain (terrain_importer.py:203-223)
-    from asimov_mjlab_b200 import terrains
-    eo, _, _ = terrains.env_origins_curriculum(E, np.asarray(m.meta["terrain_origins"]), seed=rank)
-    origins[:] = torch.as_tensor(eo, dtype=torch.float32, device=dev)
-    origins[:, 0:2] += (torch.rand(E, 2, generator=g) - 0.5).to(dev) * 2.0     # off the platform centre, onto the steps
-    # spawn ON the terrain: highest surface under the robot's footprint (the generator's own hfield-pyramid origins
-    # lie inside the field's slab, heightfield_terrains.py:243-246)
-    xy = origins[:, 0:2].cpu().numpy()
-    surf = np.max([terrains.surface_height(m, xy + np.array(o)) for o in ((0, 0), (0.3, 0.2), (0.3, -0.2), (-0.3, 0.2), (-0.3, -0.2))], axis=0)
-    origins[:, 2] = torch.as_tensor(surf, dtype=torch.float32, device=dev) + 0.05
-  else:
-    side = int(np.ceil(np.sqrt(E)))
-    idx = torch.arange(E, device=dev)
-    origins[:, 0] = (idx // side).float() * 2.5
-    origins[:, 1] = (idx % side).float() * 2.5
-  noise = 0.02 * torch.randn(E, m.nq - 7, generator=g).to(dev)
-
-  def reset_all():
-    D.qpos[:] = q0
-    D.qpos[:, 0:3] += origins
-    D.qpos[:, 7:] += noise
-    D.qvel.zero_(); D.qacc_warmstart.zero_(); D.time.zero_()
-    D.ctrl[:] = c0
-    sim.forward()
-
-  def one_step(i):
-    if i % RESET_PERIOD_STEPS == 0:
-      reset_all()
-    D.ctrl.copy_(ctrl_pool[i % nbatch])
-    sim.step_decimation()
 
   def barrier():
     if world > 1:
       dist.barrier()
     torch.cuda.synchronize()
 
-  for i in range(args.warmup):
-    one_step(i)
-  barrier()
+  # ---- headline: W warm-up steps, then exactly K timed steps (CUDA events, barrier + synchronize on both sides)
   sampler = ClockSampler(local)
   if rank == 0:
     sampler.start()
-  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-  n_resets = 0
-  barrier()
-  e0.record()
-  for i in range(args.steps):
-    n_resets += int(i % RESET_PERIOD_STEPS == 0)
-    one_step(i)
-  e1.record()
-  barrier()
-  ms = e0.elapsed_time(e1)
+  ms, n_resets = pb.timed(args.steps, args.warmup, first=0, barrier=barrier)
   clocks = sampler.stop() if rank == 0 else None
   # ---- e2e: same work through the host-buffer C-ABI call, pinned host buffers, copies inside the timed region
   ctrl_host = torch.as_tensor(action_targets(m, 8, E, seed=2000 + rank)).pin_memory()
   qpos_h = torch.empty(E, m.nq).pin_memory(); qvel_h = torch.empty(E, m.nv).pin_memory(); sens_h = torch.empty(E, m.nsensordata).pin_memory()
-  reset_all()
-  for i in range(max(3, args.warmup // 4)):
+  pb.reset_all()
+  for i in range(max(3, args.warmup)):
     engine.step_host(M, D, ctrl_host[i % 8], DECIMATION, qpos_h, qvel_h, sens_h)
+  pb.reset_all()
   barrier()
   e2e_steps = args.steps
   t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
   t0.record()
   for i in range(e2e_steps):
     if i % RESET_PERIOD_STEPS == 0 and i:
-      reset_all()
+      pb.reset_all()
     engine.step_host(M, D, ctrl_host[i % 8], DECIMATION, qpos_h, qvel_h, sens_h)
   t1.record()
   barrier()
   ms_e2e = t0.elapsed_time(t1)
-  # ---- per-kernel shares (CUDA events between launches, live, outside the timed region)
-  reset_all()
-  for i in range(40):
-    one_step(i + 1)
+  # ---- per-kernel shares (CUDA events between launches, live, outside the timed region), in the state the timed region ends in
+  pb.reset_all()
+  for i in range(min(args.steps, 40)):
+    pb.one_step(i + 1)
   torch.cuda.synchronize()
   stages = engine.profile_step(M, D, 20)
+  extras = extra_measurements(args, world, rank, dev, pb) if args.extras else {}
   # ---- max over ranks
   rank_ms = [ms / args.steps]
   if world > 1:
@@ -316,10 +455,11 @@ def run_b200(args):
   e2e_value = world * E * DECIMATION * e2e_steps / (ms_e2e * 1e-3)
   peak, peak_src = measured_peak()
   per_gpu_substep_s = (ms * 1e-3) / (args.steps * DECIMATION)
-  ab = ALG_BYTES_PER_SUBSTEP_WORLD if args.workload == "g1_flat" else alg_bytes(m, len(foot))
+  ab = ALG_BYTES_PER_SUBSTEP_WORLD if args.workload == "g1_flat" else alg_bytes(m, len(pb.foot))
   achieved = E * ab / per_gpu_substep_s / 1e9
   tot = sum(stages.values())
   top = max(stages, key=stages.get)
+  traffic = NCU_TRAFFIC.get((args.workload, E), (None, None))
   out = {
     "metric": "env_steps_per_s", "value": value, "unit": "physics sub-steps/s (1 env-step = 1 sim.step per world)",
     "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
@@ -329,13 +469,14 @@ def run_b200(args):
                "envs_per_gpu": E, "decimation": DECIMATION, "substeps_per_step": DECIMATION, "timestep": 0.005,
                "nconmax": 50, "njmax": 300, "iterations": 10, "ls_iterations": 20, "ls_parallel": bool(args.ls_parallel), "cone": args.cone,
                "friction_dr": True, "resets_in_timed_region": n_resets, "parallelism": f"env-shard x{world}, no collective on the step path",
+               "state_window": f"sub-steps 0..{min(args.steps, RESET_PERIOD_STEPS) * DECIMATION} after a reset (see `regimes`: upright robots cost more than fallen ones)",
                "l2": f"working set {D.bytes / 2**20:.0f} MiB per GPU (> 126 MB L2); no explicit flush"},
     "e2e": {"value": e2e_value, "unit": "physics sub-steps/s", "h2d_bytes_per_step": int(E * m.nu * 4),
             "d2h_bytes_per_step": int(E * (m.nq + m.nv + m.nsensordata) * 4), "ms_per_step": ms_e2e / e2e_steps,
             "api": "b2s_step_host (C ABI) with pinned host buffers"},
     "gpu_launches": int(args.steps * per_graph["decimation"] + n_resets * per_graph["forward"]),
     "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                 "traffic": NCU_TRAFFIC.get((args.workload, E), (None, None))[0], "traffic_source": NCU_TRAFFIC.get((args.workload, E), (None, None))[1],
+                 "traffic": traffic[0], "traffic_from_profile": traffic[1],
                  "algorithmic_bytes_per_launch": E * ab,
                  "peak_source": peak_src, "scope": f"whole sub-step (7 stage kernels); algorithmic bytes {ab} B per world per sub-step",
                  "dominant_kernel": top, "dominant_share": stages[top] / tot, "dominant_kernel_ms": stages[top],
@@ -344,15 +485,13 @@ def run_b200(args):
                  "stage_ms": stages},
     "clocks": clocks,
   }
+  out.update(extras)
   if args.cpu_baseline and world == 1:
-    cores = os.cpu_count() or 1
-    # bounded sample sized for roughly 10-20 s of host work: a short probe sets the number of sub-steps
-    nw = 16 * cores
-    probe, _ = cpu_rollout(m, nw, 2 * DECIMATION, cores, ls_parallel=args.ls_parallel)
-    nsub = int(min(max(12.0 * probe / nw, 2 * DECIMATION), 4000)) // DECIMATION * DECIMATION
-    rate, dt = cpu_rollout(m, nw, nsub, cores, ls_parallel=args.ls_parallel)
-    out["cpu_baseline"] = {"value": rate, "unit": "physics sub-steps/s", "cores": cores, "kind": "port",
-                           "sample": f"{nw} worlds x {nsub} sub-steps, oracle f32 with OpenMP on {cores} threads ({dt:.1f} s)"}
+    cs = CpuSampler(m, args.ls_parallel)
+    window = min(args.steps, RESET_PERIOD_STEPS) * DECIMATION
+    rate, t, ep = cs.run(window, min_seconds=8.0)
+    out["cpu_baseline"] = {"value": rate, "unit": "physics sub-steps/s", "cores": cs.cores, "kind": "port",
+                           "sample": cpu_sample_desc(cs, window, t, ep)}
   print(json.dumps(out), flush=True)
   if world > 1:
     dist.destroy_process_group()
