@@ -45,6 +45,7 @@ struct FieldRec {
   void* ptr;                 // Data fields / fixed Model fields
   WField<float>* wf;         // expandable Model fields (ptr lives in the ModelDev)
   long long elems;           // per-world element count
+  long long shared = 0;      // Data fields: elements stored ONCE ahead of the per-world block (ptr points at the shared block)
 };
 
 struct b2s_model {
@@ -436,6 +437,18 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     for (int k = 0; k < s->nsite; k++) (is_static(s->site_bodyid[k]) ? ss : ps).push_back(k);
     d.nposegeom = (int)pg.size(); d.nposesite = (int)ps.size(); d.nstatgeom = (int)sg.size(); d.nstatsite = (int)ss.size();
     d.pose_geom = up.raw(pg); d.pose_site = up.raw(ps); d.stat_geom = up.raw(sg); d.stat_site = up.raw(ss);
+    // many static sites (mjlab's per-env origin markers, terrain_importer.py:98-120): store their frames once (H3)
+    std::vector<int> slot((size_t)s->nsite);
+    d.site_split = (int)ss.size() >= B2S_SITE_SPLIT_MIN ? 1 : 0;
+    if (d.site_split) {
+      for (size_t k = 0; k < ss.size(); k++) slot[ss[k]] = ~(int)k;
+      for (size_t k = 0; k < ps.size(); k++) slot[ps[k]] = (int)k;
+      d.nsite_world = (int)ps.size();
+    } else {
+      for (int k = 0; k < s->nsite; k++) slot[k] = k;
+      d.nsite_world = s->nsite;
+    }
+    d.site_slot = up.raw(slot);
   }
   d.geom_contype = up.i(s->geom_contype, s->ngeom); d.geom_conaffinity = up.i(s->geom_conaffinity, s->ngeom);
   {
@@ -528,6 +541,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   }
   add_field(m->fields, m->index, "geom_bodyid", B2S_I32, (void*)d.geom_bodyid, nullptr, {s->ngeom});
   add_field(m->fields, m->index, "site_bodyid", B2S_I32, (void*)d.site_bodyid, nullptr, {s->nsite});
+  add_field(m->fields, m->index, "site_slot", B2S_I32, (void*)d.site_slot, nullptr, {s->nsite});
   add_field(m->fields, m->index, "body_parentid", B2S_I32, (void*)d.body_parentid, nullptr, {nb});
   add_field(m->fields, m->index, "body_rootid", B2S_I32, (void*)d.body_rootid, nullptr, {nb});
   add_field(m->fields, m->index, "jnt_qposadr", B2S_I32, (void*)d.jnt_qposadr, nullptr, {s->njnt});
@@ -614,6 +628,8 @@ extern "C" int b2s_model_expand(b2s_model* m, const char* name, int nworld) {
     // the static-geom grid (terrain broadphase) is built once from the compile-time poses: a per-world pose of those geoms
     // would leave it stale, so refuse instead of colliding against the wrong boxes
     const std::string n(name);
+    if (m->dev.site_split && (n == "site_pos" || n == "site_quat" || n == "body_pos" || n == "body_quat"))
+      return fail("model field " + n + " cannot vary per world: this model's " + std::to_string(m->dev.nstatsite) + " static site frames are stored once (site_split)");
     if (m->dev.ngrid > 0 && (n == "geom_pos" || n == "geom_quat" || n == "body_pos" || n == "body_quat"))
       return fail("model field " + n + " cannot vary per world: this model's static terrain geoms are indexed by a broadphase grid built at put_model");
   }
@@ -679,7 +695,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   memset(&d, 0, sizeof(d));
   d.nworld = nworld; d.nconmax = nconmax; d.njmax = njmax;
   const long long W = nworld, nb = md.nbody, nv = md.nv, nvp = md.nvp;
-  struct Slot { const char* name; int dtype; void** dst; std::vector<long long> shape; };
+  struct Slot { const char* name; int dtype; void** dst; std::vector<long long> shape; long long shared = 0; };
   std::vector<Slot> slots = {
     {"qpos", B2S_F32, (void**)&d.qpos, {md.nq}}, {"qvel", B2S_F32, (void**)&d.qvel, {nv}}, {"ctrl", B2S_F32, (void**)&d.ctrl, {md.nu}},
     {"qacc_warmstart", B2S_F32, (void**)&d.qacc_warmstart, {nv}}, {"time", B2S_F32, (void**)&d.time, {}},
@@ -689,7 +705,9 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"xipos", B2S_F32, (void**)&d.xipos, {nb, 3}}, {"ximat", B2S_F32, (void**)&d.ximat, {nb, 3, 3}},
     {"xanchor", B2S_F32, (void**)&d.xanchor, {md.njnt, 3}}, {"xaxis", B2S_F32, (void**)&d.xaxis, {md.njnt, 3}},
     {"geom_xpos", B2S_F32, (void**)&d.geom_xpos, {md.ngeom, 3}}, {"geom_xmat", B2S_F32, (void**)&d.geom_xmat, {md.ngeom, 3, 3}},
-    {"site_xpos", B2S_F32, (void**)&d.site_xpos, {md.nsite, 3}}, {"site_xmat", B2S_F32, (void**)&d.site_xmat, {md.nsite, 3, 3}},
+    // dense: (nworld, nsite, .); split (H3): nstatsite frames once, then (nworld, nsite_world, .) -- see b2s_site_index
+    {md.site_split ? "site_xpos_world" : "site_xpos", B2S_F32, (void**)&d.site_xpos, {md.nsite_world, 3}, md.site_split ? 3LL * md.nstatsite : 0},
+    {md.site_split ? "site_xmat_world" : "site_xmat", B2S_F32, (void**)&d.site_xmat, {md.nsite_world, 3, 3}, md.site_split ? 9LL * md.nstatsite : 0},
     {"subtree_com", B2S_F32, (void**)&d.subtree_com, {nb, 3}}, {"cinert", B2S_F32, (void**)&d.cinert, {nb, 10}}, {"cdof", B2S_F32, (void**)&d.cdof, {nv, 6}},
     {"cvel", B2S_F32, (void**)&d.cvel, {nb, 6}}, {"cdof_dot", B2S_F32, (void**)&d.cdof_dot, {nv, 6}}, {"qM", B2S_F32, (void**)&d.qM, {nv, nvp}},
     {"qfrc_bias", B2S_F32, (void**)&d.qfrc_bias, {nv}}, {"qfrc_passive", B2S_F32, (void**)&d.qfrc_passive, {nv}},
@@ -720,7 +738,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     long long n = 1;
     for (long long v : s.shape) n *= v;
     offs.push_back(total);
-    size_t bytes = (size_t)(W * n) * 4;
+    size_t bytes = (size_t)(W * n + s.shared) * 4;
     if (bytes == 0) bytes = 4;
     total += (bytes + 255) & ~(size_t)255;
   }
@@ -729,8 +747,16 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   cudaMemset(D->arena, 0, total);
   for (size_t i = 0; i < slots.size(); i++) {
     *slots[i].dst = (char*)D->arena + offs[i];
-    add_field(D->fields, D->index, slots[i].name, slots[i].dtype, *slots[i].dst, nullptr, slots[i].shape);
+    // a field with a shared block is exposed as two views: "<name>" = the per-world block, "<base>_static" = the shared one
+    add_field(D->fields, D->index, slots[i].name, slots[i].dtype, (char*)*slots[i].dst + slots[i].shared * 4, nullptr, slots[i].shape);
+    if (slots[i].shared) {
+      std::string sn(slots[i].name); sn = sn.substr(0, sn.size() - 6) + "_static";      // ..._world -> ..._static
+      std::vector<long long> sh = slots[i].shape; sh[0] = md.nstatsite;
+      add_field(D->fields, D->index, sn.c_str(), slots[i].dtype, *slots[i].dst, nullptr, sh);
+      D->fields.back().shared = 1;
+    }
   }
+  d.site_shared = md.site_split ? md.nstatsite : 0;
   // initial state, broadcast to every world
   auto bcast = [&](float* dst, const double* src, long long n) -> int {
     if (n == 0) return 0;
@@ -798,7 +824,8 @@ extern "C" int b2s_data_field(b2s_data* d, const char* name, b2s_field_info* out
   if (!d || !name || !out) return fail("null argument");
   auto it = d->index.find(name);
   if (it == d->index.end()) return fail(std::string("unknown data field ") + name);
-  fill_info(d->fields[it->second], d->dev.nworld, false, d->fields[it->second].ptr, out);
+  const FieldRec& r = d->fields[it->second];
+  fill_info(r, r.shared ? 1 : d->dev.nworld, false, r.ptr, out);
   return 0;
 }
 // Dense constraint Jacobian (mjwarp's Data.efc.J) from the matrix-free rows: allocated on first use, refilled on

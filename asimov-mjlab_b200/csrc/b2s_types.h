@@ -11,6 +11,7 @@
 #define B2S_WARPS_PER_CTA 4
 #define B2S_MAX_NV 56          // register-tiled Hessian: 7 x 7 tiles of up to 8 x 8
 #define B2S_GRID_MIN_GEOMS 64   // static non-plane geoms beyond this count are indexed by a uniform grid
+#define B2S_SITE_SPLIT_MIN 1024  // static sites: from this many on their frames are stored once instead of per world
 #define B2S_MINVAL 1e-15f
 #define B2S_MINMU 1e-5f
 
@@ -64,6 +65,11 @@ struct ModelDev {
   // put_data and by b2s_refresh_static: thousands of terrain geoms would otherwise dominate the position stage)
   int nposegeom, nposesite, nstatgeom, nstatsite;
   const int *pose_geom, *pose_site, *stat_geom, *stat_site;
+  // Site frames (mjlab adds one visualisation site PER ENV to the world body, an O(nworld^2) array in the
+  // reference's layout).  site_slot[s] >= 0: slot of a per-world site; < 0: ~slot of a static site whose frame is stored ONCE
+  // (site_split = 1, chosen at put_model when there are many static sites).  Dense models: site_slot[s] = s, site_split = 0.
+  int site_split, nsite_world;      // nsite_world = sites stored per world (nsite when dense)
+  const int* site_slot;
   const int *pair_geom;             // [npair][2] after type ordering (type1 <= type2), sorted by (min id, max id)
   // ---- sites
   const int *site_bodyid;
@@ -117,4 +123,10 @@ struct DataDev {
   // qpos / qvel / time as k_dynamics saw them: k_sensors reads these copies, so that it can run beside k_integrate (which
   // advances the originals) on a forked graph branch
   float *snap_qpos, *snap_qvel, *snap_time;
+  // element index (in sites) of site s of world w in site_xpos / site_xmat: [shared static block | nworld x nsite_world]
+  int site_shared;                  // static sites stored once ahead of the per-world block (0 when dense)
 };
+__host__ __device__ inline size_t b2s_site_index(const ModelDev& m, const DataDev& d, int w, int s) {
+  const int slot = m.site_slot[s];
+  return slot < 0 ? (size_t)(~slot) : (size_t)d.site_shared + (size_t)w * m.nsite_world + slot;
+}

@@ -57,7 +57,7 @@ DEV bool side_match(const ModelDev& m, int objtype, int objid, int geom, int bod
 struct Frame { v3 pos; m33 mat; int body; };
 DEV Frame obj_frame(const ModelDev& m, const DataDev& d, int w, int type, int id) {
   Frame f;
-  if (type == B2S_OBJ_SITE) { f.pos = ld3(d.site_xpos + ((size_t)w * m.nsite + id) * 3); f.mat = ldm(d.site_xmat + ((size_t)w * m.nsite + id) * 9); f.body = m.site_bodyid[id]; }
+  if (type == B2S_OBJ_SITE) { const size_t si = b2s_site_index(m, d, w, id); f.pos = ld3(d.site_xpos + si * 3); f.mat = ldm(d.site_xmat + si * 9); f.body = m.site_bodyid[id]; }
   else if (type == B2S_OBJ_GEOM) { f.pos = ld3(d.geom_xpos + ((size_t)w * m.ngeom + id) * 3); f.mat = ldm(d.geom_xmat + ((size_t)w * m.ngeom + id) * 9); f.body = m.geom_bodyid[id]; }
   else if (type == B2S_OBJ_XBODY) { f.pos = ld3(d.xpos + ((size_t)w * m.nbody + id) * 3); f.mat = ldm(d.xmat + ((size_t)w * m.nbody + id) * 9); f.body = id; }
   else { f.pos = ld3(d.xipos + ((size_t)w * m.nbody + id) * 3); f.mat = ldm(d.ximat + ((size_t)w * m.nbody + id) * 9); f.body = id; }

@@ -107,8 +107,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
     for (int k = lane; k < m.nposesite; k += 32) {
       const int s = m.pose_site[k];
       const int b = m.site_bodyid[s];
-      st3(d.site_xpos + ((size_t)w * m.nsite + s) * 3, ld3(sx + 3 * b) + mulv(ldm(sm + 9 * b), ld3(spos + 3 * s)));
-      stm(d.site_xmat + ((size_t)w * m.nsite + s) * 9, q2m(qmul(ldq(sq + 4 * b), ldq(squat + 4 * s))));
+      const size_t si = b2s_site_index(m, d, w, s);
+      st3(d.site_xpos + si * 3, ld3(sx + 3 * b) + mulv(ldm(sm + 9 * b), ld3(spos + 3 * s)));
+      stm(d.site_xmat + si * 9, q2m(qmul(ldq(sq + 4 * b), ldq(squat + 4 * s))));
     }
   }
   __syncwarp();
@@ -169,27 +170,31 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
 // Frames of geoms and sites on static (world-welded, joint-less, non-mocap) bodies: they never move, so they are
 // computed once (put_data, b2s_refresh_static) from the body frames k_position left in xpos/xquat.
 __global__ void k_static_frames(const ModelDev m, const DataDev d) {
-  const long long n = (long long)m.nstatgeom + m.nstatsite;
-  const long long total = (long long)d.nworld * n;
+  // static geoms of every world, then static sites: of every world (dense layout) or once (split layout: the frames of world 0)
+  const long long ng = (long long)d.nworld * m.nstatgeom;
+  const long long total = ng + (long long)(m.site_split ? 1 : d.nworld) * m.nstatsite;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
-    const int w = (int)(idx / n), k = (int)(idx - (long long)w * n);
-    if (k < m.nstatgeom) {
+    if (idx < ng) {
+      const int w = (int)(idx / m.nstatgeom), k = (int)(idx - (long long)w * m.nstatgeom);
       const int g = m.stat_geom[k], b = m.geom_bodyid[g];
       const v3 bp = ld3(d.xpos + ((size_t)w * m.nbody + b) * 3);
       const q4 bq = ldq(d.xquat + ((size_t)w * m.nbody + b) * 4);
       st3(d.geom_xpos + ((size_t)w * m.ngeom + g) * 3, bp + mulv(q2m(bq), ld3(m.geom_pos.at(w) + 3 * g)));
       stm(d.geom_xmat + ((size_t)w * m.ngeom + g) * 9, q2m(qmul(bq, ldq(m.geom_quat.at(w) + 4 * g))));
     } else {
-      const int s = m.stat_site[k - m.nstatgeom], b = m.site_bodyid[s];
+      const long long r = idx - ng;
+      const int w = (int)(r / m.nstatsite), k = (int)(r - (long long)w * m.nstatsite);
+      const int s = m.stat_site[k], b = m.site_bodyid[s];
       const v3 bp = ld3(d.xpos + ((size_t)w * m.nbody + b) * 3);
       const q4 bq = ldq(d.xquat + ((size_t)w * m.nbody + b) * 4);
-      st3(d.site_xpos + ((size_t)w * m.nsite + s) * 3, bp + mulv(q2m(bq), ld3(m.site_pos.at(w) + 3 * s)));
-      stm(d.site_xmat + ((size_t)w * m.nsite + s) * 9, q2m(qmul(bq, ldq(m.site_quat.at(w) + 4 * s))));
+      const size_t si = b2s_site_index(m, d, w, s);
+      st3(d.site_xpos + si * 3, bp + mulv(q2m(bq), ld3(m.site_pos.at(w) + 3 * s)));
+      stm(d.site_xmat + si * 9, q2m(qmul(bq, ldq(m.site_quat.at(w) + 4 * s))));
     }
   }
 }
 void launch_static_frames(const ModelDev& m, const DataDev& d, cudaStream_t st) {
-  const long long total = (long long)d.nworld * ((long long)m.nstatgeom + m.nstatsite);
+  const long long total = (long long)d.nworld * m.nstatgeom + (long long)(m.site_split ? 1 : d.nworld) * m.nstatsite;
   if (total == 0) return;
   const int grid = (int)((total + 255) / 256 > 148 * 16 ? 148 * 16 : (total + 255) / 256);
   k_static_frames<<<grid, 256, 0, st>>>(m, d);

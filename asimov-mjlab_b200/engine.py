@@ -232,6 +232,54 @@ class _Sub:
     return getattr(self._d, self._p + k)   # efc.J -> Data.efc_J (materialised on access)
 
 
+class SplitField:
+  """Read view of a (nworld, nsite, ...) Data field whose static columns are stored ONCE (mjlab adds a
+  visualisation site per env to the world body, terrain_importer.py:98-120, which makes `site_xpos` O(nworld^2) in the
+  reference's dense layout -- 206 GB at 65 536 envs).  Indexing follows torch's rules for the patterns mjlab uses
+  (`data.site_xpos[:, site_ids]`, entity/data.py:315-327; `[env_ids, ids]`, `[:, k, 2]`, ...): the selected columns are gathered
+  from the per-world block `world` (nworld, nsite_world, ...) and the shared block `static` (1, nstatic, ...) and the rest of the
+  key is applied to that.  `dense()` materialises the full array (small models / tests only)."""
+
+  def __init__(self, world, static, slot):
+    self.world, self.static, self.slot = world, static, slot
+    self.shape = (world.shape[0], int(slot.numel()), *world.shape[2:])
+    self.device, self.dtype = world.device, world.dtype
+
+  def _columns(self, ids):
+    import torch
+    sl = self.slot[ids]
+    mov = sl >= 0
+    W = self.shape[0]
+    if bool(mov.all()):
+      return self.world[:, sl]
+    if not bool(mov.any()):
+      return self.static[:, ~sl].expand(W, *([-1] * (self.static.dim() - 1)))
+    out = torch.empty((W, int(sl.numel()), *self.shape[2:]), dtype=self.dtype, device=self.device)
+    out[:, mov] = self.world[:, sl[mov]]
+    out[:, ~mov] = self.static[:, ~sl[~mov]]
+    return out
+
+  def __getitem__(self, key):
+    import torch
+    if not isinstance(key, tuple):
+      key = (key,)
+    if len(key) < 2:
+      key = (*key, slice(None))
+    k0, k1, rest = key[0], key[1], key[2:]
+    n = self.shape[1]
+    if isinstance(k1, slice):
+      ids = torch.arange(n, device=self.device)[k1]
+      return self._columns(ids)[(k0, slice(None), *rest)]
+    if isinstance(k1, int):
+      return self._columns(torch.tensor([k1 % n], device=self.device))[(k0, 0, *rest)]
+    ids = torch.as_tensor(k1, device=self.device).long()
+    pos = torch.arange(ids.numel(), device=self.device).view(ids.shape)
+    return self._columns(ids.reshape(-1) % n)[(k0, pos, *rest)]
+
+  def dense(self):
+    return self[:, :]
+
+
 class Data(_Struct):
   def __init__(self, handle, model, nworld, nconmax, njmax):
     d = self.__dict__
@@ -242,8 +290,12 @@ class Data(_Struct):
     d["contact"] = _Sub(self, "contact_", None)
     d["efc"] = _Sub(self, "efc_", None)
     model.__dict__["_nworld"] = nworld
+    if "site_xpos_world" in d["_names"]:          # split site storage (H3): the reference's names resolve to SplitField views
+      d["_names"] |= {"site_xpos", "site_xmat"}
 
   def _make(self, name):
+    if name in ("site_xpos", "site_xmat") and "site_xpos_world" in self.__dict__["_names"]:
+      return SplitField(getattr(self, name + "_world"), getattr(self, name + "_static"), self._model.site_slot.long())
     info = abi.FieldInfo()
     _check(lib().b2s_data_field(self._h.ptr, name.encode(), C.byref(info)))
     t, _ = _as_tensor(self._h, info, self._device)

@@ -26,6 +26,7 @@ def main():
   ap.add_argument("--steps-per-env", type=int, default=24)
   ap.add_argument("--seed", type=int, default=0)
   ap.add_argument("--task", default="velocity", choices=["velocity", "tracking"], help="G1 velocity-flat or G1 tracking-flat (synthetic motion)")
+  ap.add_argument("--origin-sites", action="store_true", help="velocity task: the scene with mjlab's one world-body site per env (SURVEY.md H3)")
   ap.add_argument("--log", action="store_true", help="rank 0 prints the training statistics of every iteration to stderr")
   a = ap.parse_args()
   rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -39,7 +40,7 @@ def main():
     from .tracking_env import G1TrackingFlatEnv
     env = G1TrackingFlatEnv(a.envs, str(dev), seed=a.seed + rank)
   else:
-    env = G1VelocityFlatEnv(a.envs, str(dev), seed=a.seed + rank)         # per-rank seed = seed + rank (utils/random.py:9-26)
+    env = G1VelocityFlatEnv(a.envs, str(dev), seed=a.seed + rank, origin_sites=a.origin_sites)         # per-rank seed = seed + rank (utils/random.py:9-26)
   algo = PPO(env, dev, steps_per_env=a.steps_per_env, seed=a.seed)
   ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
   t_roll = t_upd = 0.0

@@ -44,11 +44,13 @@ class G1VelocityFlatEnv:
   episode_length_s = 20.0
 
   def __init__(self, num_envs: int, device: str = "cuda:0", seed: int = 0, env_spacing: float = 2.5, use_graph: bool = True,
-               use_fused: bool = True):
+               use_fused: bool = True, origin_sites: bool = False):
     self.num_envs, self.device = num_envs, torch.device(device)
     self.use_fused = use_fused
     torch.cuda.set_device(self.device)
     m = scenes.load_asset("g1_flat")
+    if origin_sites:      # the scene as mjlab compiles it: one world-body site per env (terrain_importer.py:98-120)
+      m = scenes.with_env_origin_sites(m, num_envs, env_spacing)
     self.m = m
     cfg = SimulationCfg(nconmax=50, njmax=300, ls_parallel=True, mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20))
     self.sim = Simulation(num_envs, cfg, m, str(self.device))
@@ -280,8 +282,14 @@ class G1VelocityFlatEnv:
     p.nworld, p.nq, p.nv, p.nu, p.nbody, p.nsite, p.nsensordata, p.nrand = W, m.nq, m.nv, m.nu, m.nbody, m.nsite, m.nsensordata, self.nrand
     self.soft_lo, self.soft_hi = self.soft_limits[:, 0].contiguous(), self.soft_limits[:, 1].contiguous()
     ptr = lambda t: t.data_ptr()      # noqa: E731
-    for n in ("qpos", "qvel", "qacc_warmstart", "ctrl", "time", "sensordata", "xquat", "cvel", "site_xpos", "subtree_com"):
+    for n in ("qpos", "qvel", "qacc_warmstart", "ctrl", "time", "sensordata", "xquat", "cvel", "subtree_com"):
       setattr(p, n, ptr(getattr(D, n)))
+    # site frames: dense (nworld, nsite, 3), or -- with many static world-body sites (engine.SplitField) -- the per-world block
+    # (nworld, nsite_world, 3) addressed by slot
+    split = not torch.is_tensor(D.site_xpos)
+    site_w = D.site_xpos.world if split else D.site_xpos
+    p.site_xpos, p.nsite = ptr(site_w), int(site_w.shape[1])
+    site_slot = (lambda k: int(D.site_xpos.slot[k])) if split else (lambda k: k)
     for n in ("default_qpos", "action_scale", "soft_lo", "soft_hi", "std_standing", "std_walking", "std_running", "env_origins",
               "actions_in", "action", "prev_action", "command", "heading_target", "cmd_time_left", "push_time_left", "is_heading",
               "is_standing", "dones", "time_outs", "episode_length_buf", "peak_heights", "obs", "critic_obs", "rew", "U"):
@@ -294,7 +302,7 @@ class G1VelocityFlatEnv:
     p.air_last_time = ptr(self.air["last_time"])
     p.torso = self.torso
     for k in range(2):
-      p.feet_site[k], p.feet_body[k] = self.feet_sites[k], self.feet_site_body[k]
+      p.feet_site[k], p.feet_body[k] = site_slot(self.feet_sites[k]), self.feet_site_body[k]
       p.feet_root[k] = int(m.body_rootid[self.feet_site_body[k]])
       p.s_found[k], p.s_force[k] = self.s_found[k], self.s_force[k]
     p.s_gyro, p.s_linvel, p.s_angmom, p.s_self = self.s_gyro, self.s_linvel, self.s_angmom, self.s_self

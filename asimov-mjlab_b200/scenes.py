@@ -233,8 +233,9 @@ def build_scene(entities: dict, sensors=(), plane=True, num_origin_sites=0, env_
   if plane:
     t = scene.worldbody.add_body(name="terrain")
     t.add_geom(name="terrain", type="plane", size=[0.0, 0.0, 0.01])
+  origins = env_origins_grid(num_origin_sites, env_spacing) if num_origin_sites else ()
   for e in range(num_origin_sites):  # SURVEY.md §0 fact 10 (one site per env on the world body)
-    scene.worldbody.add_site(name=f"env_origin_{e}", pos=list(env_origins_grid(num_origin_sites, env_spacing)[e]))
+    scene.worldbody.add_site(name=f"env_origin_{e}", pos=list(origins[e]))
   ent_bodies = {}
   for name, espec in entities.items():
     ent_bodies[name] = tuple(b.name for b in espec.bodies[1:])
@@ -254,6 +255,31 @@ def env_origins_grid(num_envs: int, spacing: float) -> np.ndarray:
   o[:, 0] = -(ii.flatten()[:num_envs] - (rows - 1) / 2) * spacing
   o[:, 1] = (jj.flatten()[:num_envs] - (cols - 1) / 2) * spacing
   return o
+
+
+def with_env_origin_sites(model: HostModel, num_envs: int, env_spacing: float = 2.5) -> HostModel:
+  """Copy of a compiled scene with the visualisation sites mjlab's terrain importer adds to the world body: one `env_origin_<i>`
+  per environment at its grid origin (terrains/terrain_importer.py:95,98-120).  World-body sites precede the entities' sites in
+  MuJoCo's numbering, so every site reference (site ids of sensors) moves up by `num_envs` -- as in a scene the reference
+  compiles itself.  This is the O(num_envs) model array that makes `site_xpos` O(num_envs^2) in the reference (SURVEY.md §0
+  fact 10); the engine stores such static frames once (Data.site_xpos becomes a SplitField)."""
+  import copy
+  m = copy.copy(model)
+  m.names = dict(model.names)
+  n = int(num_envs)
+  o = env_origins_grid(n, env_spacing)
+  m.site_bodyid = np.concatenate([np.zeros(n, np.int32), np.asarray(model.site_bodyid, np.int32)])
+  m.site_pos = np.concatenate([o, np.asarray(model.site_pos, float).reshape(-1, 3)])
+  q = np.zeros((n, 4)); q[:, 0] = 1.0
+  m.site_quat = np.concatenate([q, np.asarray(model.site_quat, float).reshape(-1, 4)])
+  m.names["site"] = [f"env_origin_{e}" for e in range(n)] + list(model.names["site"])
+  m.nsite = model.nsite + n
+  OBJ_SITE = 6
+  oid = np.asarray(model.sensor_objid, np.int32).copy(); rid = np.asarray(model.sensor_refid, np.int32).copy()
+  oid[np.asarray(model.sensor_objtype) == OBJ_SITE] += n
+  rid[(np.asarray(model.sensor_reftype) == OBJ_SITE) & (rid >= 0)] += n
+  m.sensor_objid, m.sensor_refid = oid, rid
+  return m
 
 
 def build_g1_flat(xml_path) -> HostModel:

@@ -401,3 +401,46 @@ def test_two_models_in_one_process_keep_their_shared_memory_limits(g1):
     orc2.step(w, 4)
   _check_counts(D, worlds); _check_counts(D2, w2)
   assert _rel_err(D, worlds, "qpos") < 2e-4 and _rel_err(D2, w2, "qpos") < 2e-4
+
+
+# --------------------------------------------------------------------------------------------- H3: per-env origin sites
+def test_env_origin_sites_are_stored_once(g1):
+  """mjlab's terrain importer adds one world-body site per env (terrain_importer.py:95,98-120), so the
+  reference's `site_xpos` is (W, 6 + W, 3): 206 GB with `site_xmat` at W = 65 536.  Here static sites beyond 1024 are stored
+  once: the G1 scene WITH its W origin sites at W = 65 536 fits in < 3 GB, `data.site_xpos[:, site_ids]` (entity/data.py:315-327)
+  equals the dense computation of the same worlds, the origin sites read back their model positions, and the site-based
+  sensors (gyro / velocimeter / accelerometer sit on sites) are unchanged."""
+  import torch
+  from asimov_mjlab_b200 import engine, scenes
+  from asimov_mjlab_b200.hostmodel import HostData
+  W = 65536
+  big = scenes.with_env_origin_sites(g1, W)
+  assert big.nsite == g1.nsite + W
+  M = engine.put_model(big, "cuda:0")
+  D = engine.put_data(big, HostData(big), W, 50, 300, model=M)
+  assert D.bytes < 3 * 2 ** 30, D.bytes
+  assert isinstance(D.site_xpos, engine.SplitField) and D.site_xpos.shape == (W, g1.nsite + W, 3) and D.site_xmat.shape == (W, g1.nsite + W, 3, 3)
+  # a dense model of the same robot (no origin sites), same states in the first 64 worlds
+  n = 64
+  qpos, qvel, ctrl = g1_states(g1, n, seed=8)
+  Md = engine.put_model(g1, "cuda:0")
+  Dd = engine.put_data(g1, HostData(g1), n, 50, 300, model=Md)
+  for name, arr in (("qpos", qpos), ("qvel", qvel), ("ctrl", ctrl)):
+    t = torch.as_tensor(arr, dtype=torch.float32, device="cuda:0")
+    getattr(D, name)[:n] = t; getattr(Dd, name)[:] = t
+  engine.step(M, D, 3); engine.step(Md, Dd, 3)
+  torch.cuda.synchronize()
+  ids = torch.tensor([big.name2id("site", s) for s in g1.names["site"]], device="cuda:0")
+  assert int(ids.min()) == W                                            # the robot's sites follow the W world-body sites
+  assert torch.equal(D.site_xpos[:, ids][:n], Dd.site_xpos) and torch.equal(D.site_xmat[:, ids][:n], Dd.site_xmat)
+  assert torch.equal(D.site_xpos[:n, int(ids[1]), 2], Dd.site_xpos[:, 1, 2])
+  assert torch.equal(D.sensordata[:n], Dd.sensordata) and torch.equal(D.qpos[:n], Dd.qpos)
+  # origin sites: stride-0 in the world dimension, values = the model's site_pos
+  o = D.site_xpos[:, :W]
+  assert o.shape == (W, W, 3) and o.stride(0) == 0
+  assert torch.allclose(o[12345, :, :], torch.as_tensor(big.site_pos[:W], dtype=torch.float32, device="cuda:0"), atol=1e-6)
+  mixed = D.site_xpos[:4, torch.tensor([0, W + 1, 5, W + 2], device="cuda:0")]
+  assert mixed.shape == (4, 4, 3) and torch.equal(mixed[:, 1], Dd.site_xpos[:4, 1]) and torch.equal(mixed[:, 3], Dd.site_xpos[:4, 2])
+  # per-world poses of static sites cannot be honoured in this layout: refused, not ignored
+  with pytest.raises(engine.BackendError, match="site_split"):
+    engine.expand_model_fields(M, W, ["site_pos"])
