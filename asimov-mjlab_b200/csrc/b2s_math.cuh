@@ -4,6 +4,14 @@
 #include "b2s_types.h"
 
 #define FULL 0xffffffffu
+// Device-side bounds / invariant checks of a CHECK build (tools/build_variant.sh check -DB2S_CHECK; compute-sanitizer is closed on
+// this pool): a failed check traps the kernel and the next synchronisation reports it.  Compiled out of the shipped library.
+#ifdef B2S_CHECK
+#include <cassert>
+#define B2S_ASSERT(c) assert(c)
+#else
+#define B2S_ASSERT(c) ((void)0)
+#endif
 #define DEV __device__ __forceinline__
 
 struct v3 { float x, y, z; };

@@ -657,6 +657,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         const int c = ncon + excl + k;
         if (c >= cmax) break;
         const size_t o = (size_t)w * cmax + c;
+        B2S_ASSERT(c >= 0 && g1 >= 0 && g1 < m.ngeom && g2 >= 0 && g2 < m.ngeom && condim >= 1 && condim <= 6);
         d.con_dist[o] = rc[k].dist;
         st3(d.con_pos + 3 * o, rc[k].pos);
         make_frame(rc[k].n, rc[k].t, d.con_frame + 9 * o);
@@ -670,6 +671,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
     }
     ncon += total;
   }
+  B2S_ASSERT(nsurv <= B2S_MAX_SURVIVORS);
   if (lane == 0) d.ncon[w] = min(ncon, cmax);
 }
 

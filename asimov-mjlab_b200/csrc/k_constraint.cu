@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
     } else nefc += total;
     if (c < ncon) d.con_efc_address[con0 + c] = nrow > 0 ? adr : -1;
     if (nrow > 0) {
+      B2S_ASSERT(adr >= 0 && adr + nrow <= njmax && c < d.nconmax);
       const size_t o = con0 + c;
       const int g1 = d.con_geom[2 * o], g2 = d.con_geom[2 * o + 1];
       const int b1 = m.geom_bodyid[g1], b2 = m.geom_bodyid[g2];
@@ -260,6 +261,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const Mod
     // coherence) x a per-iteration cost that grows with the row count; 0 rows = cheapest.  Order inside a class is whatever the atomics give; results do not depend on it.
     const int cls = nefc == 0 ? 0 : min(B2S_SOLVE_CLASSES - 1, 1 + (1 + min(d.solver_niter[w], 15)) * (32 + nefc) / 64);
     const int slot = atomicAdd(&d.solve_count[cls], 1);
+    B2S_ASSERT(cls >= 0 && cls < B2S_SOLVE_CLASSES && slot >= 0 && slot < d.nworld && nefc <= njmax && nl <= nefc);
     d.solve_order[(size_t)cls * d.nworld + slot] = w;
   }
 }

@@ -223,6 +223,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
   // one lane per sensor
   for (int s = lane; s < m.nsensor; s += 32) {
     const int type = m.sensor_type[s], id = m.sensor_objid[s], ot = m.sensor_objtype[s], dim = m.sensor_dim[s];
+    B2S_ASSERT(m.sensor_adr[s] >= 0 && m.sensor_adr[s] + dim <= m.nsensordata && ncon <= d.nconmax);
     float* out = d.sensordata + (size_t)w * m.nsensordata + m.sensor_adr[s];
     switch (type) {
       case B2S_SENS_GYRO: case B2S_SENS_VELOCIMETER: case B2S_SENS_ACCELEROMETER: {

@@ -375,6 +375,7 @@ DEV void flush_run(const SolveCtx<T>& c, const ModelDev& m, int bp, float acc, b
     cp = min(cp, nmin);
   }
   const int n2 = n2f - cp, n1 = n1f - cp, ns = n1 + n2;
+  B2S_ASSERT(b1 >= 0 && b1 < c.nb && b2 >= 0 && b2 < c.nb && ns >= 0 && ns <= 2 * m.maxchain);
   __syncwarp();
   const float* K = c.KW(); const float* W = c.KW() + 21;
   float* Y = c.X();    // 6 floats per support entry (the body-vector scratch is idle during assembly)
@@ -602,7 +603,9 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     int cls = B2S_SOLVE_CLASSES - 1, before = 0;
 #pragma unroll 1
     for (; cls > 0; cls--) { const int n = d.solve_count[cls]; if (w < before + n) break; before += n; }
+    B2S_ASSERT(w - before >= 0 && w - before < d.solve_count[cls]);      // every queue slot below the class count was filled
     w = d.solve_order[(size_t)cls * d.nworld + (w - before)];
+    B2S_ASSERT(w >= 0 && w < d.nworld);
   }
   const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
   SolveCtx<T> c;
@@ -705,6 +708,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
       if (start) c.run()[nrun + __popc(mk & ((1u << lane) - 1u))] = r;
       nrun += __popc(mk);
     }
+    B2S_ASSERT(nrun <= c.nconmax && c.nefc <= njmax && c.nl <= c.nefc);      // run list holds nconmax + 2 entries
     if (lane == 0) c.run()[nrun] = c.nefc;
     c.nrun = nrun;
   }
