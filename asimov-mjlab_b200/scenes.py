@@ -478,6 +478,59 @@ def build_asimov_toe(xml_path, terrain="plane", terrain_seed=0, collision="feet_
 
 
 # ---------------------------------------------------------------------------
+# Asimov, the 12-dof biped whose collision geometry is ALL link meshes (values restated from
+# src/mjlab/asset_zoo/robots/asimov/asimov_constants.py:40-276; task: tasks/velocity/config/asimov/env_cfgs.py)
+# ---------------------------------------------------------------------------
+G1_ARM_5020_X2 = 2.0 * (0.139e-4 + 0.017e-4 * (1 + 46 / 18) ** 2 + 0.169e-4 * ((1 + 46 / 18) * (1 + 56 / 16)) ** 2)   # two 5020s on the parallel ankle linkage (:68-82,136-142)
+ASIMOV_ACTUATORS = (
+  _asv_act((".*_hip_pitch_joint", ".*_hip_yaw_joint"), G1_ARM_7520_14, 88.0),
+  _asv_act((".*_hip_roll_joint", ".*_knee_joint"), G1_ARM_7520_22, 139.0),
+  _asv_act((".*_ankle_pitch_joint", ".*_ankle_roll_joint"), G1_ARM_5020_X2, 50.0),
+)
+_ASM_FOOT = r"^(left|right)_ankle_roll_link_collision$"
+ASIMOV12_FEET_ONLY_COLLISION = CollisionCfg(geom_names_expr=(_ASM_FOOT,), contype=0, conaffinity=1, condim=3, priority=1, friction=(0.8,))
+ASIMOV12_FULL_COLLISION = CollisionCfg(geom_names_expr=(".*_collision",), condim={_ASM_FOOT: 3, ".*_collision": 1}, priority={_ASM_FOOT: 1},
+                                       friction={_ASM_FOOT: (0.8,)})
+ASIMOV12_KNEES_BENT = dict(pos=(0.0, 0.0, 0.73), rot=(1.0, 0.0, 0.0, 0.0), joint_pos={
+  "left_hip_pitch_joint": 0.2, "right_hip_pitch_joint": -0.2, ".*_hip_roll_joint": 0.0, ".*_hip_yaw_joint": 0.0,
+  "left_knee_joint": -0.4, "right_knee_joint": 0.4, "left_ankle_pitch_joint": -0.25, "right_ankle_pitch_joint": 0.25,
+  ".*_ankle_roll_joint": 0.0})
+
+
+def asimov12_action_scale(joint_names) -> np.ndarray:
+  """ASIMOV_ACTION_SCALE (asimov_constants.py:262-276): 0.3 * effort / stiffness per actuated joint."""
+  out = np.zeros(len(joint_names))
+  for c in ASIMOV_ACTUATORS:
+    for n in filter_names(c.joint_names_expr, tuple(joint_names)):
+      out[list(joint_names).index(n)] = 0.3 * c.effort_limit / c.stiffness
+  return out
+
+
+def build_asimov(xml_path, collision="feet_only") -> HostModel:
+  """Compiled model of Mjlab-Velocity-Flat-Asimov (tasks/velocity/config/asimov/env_cfgs.py:16-124): free base + 12 hinges,
+  13 link meshes as the ONLY collision geometry (asimov.xml:50-110) -- each collides by its convex hull.
+  collision="feet_only" is the task's own FEET_ONLY_COLLISION (asimov_constants.py:227-235): the two foot meshes against the
+  terrain, a plane-mesh manifold of up to four contacts per foot.  collision="full" is FULL_COLLISION (:195-205): every link
+  mesh against the terrain and the other links (12 <exclude> pairs, asimov.xml:140-153): GJK / EPA mesh-mesh."""
+  robot = Spec.from_file(xml_path)
+  apply_collision_cfg(robot, ASIMOV12_FULL_COLLISION if collision == "full" else ASIMOV12_FEET_ONLY_COLLISION)
+  apply_actuator_cfgs(robot, ASIMOV_ACTUATORS)
+  add_init_state_key(robot, **ASIMOV12_KNEES_BENT)
+  feet = ContactSensorCfg(
+    name="feet_ground_contact",
+    primary=ContactMatch("subtree", r"^(left_ankle_roll_link|right_ankle_roll_link)$", "robot"),
+    secondary=ContactMatch("body", "terrain"), fields=("found", "force"), reduce="netforce", num_slots=1)
+  selfc = ContactSensorCfg(
+    name="self_collision", primary=ContactMatch("subtree", "pelvis_link", "robot"),
+    secondary=ContactMatch("subtree", "pelvis_link", "robot"), fields=("found",), reduce="none", num_slots=1)
+  scene = build_scene({"robot": robot}, sensors=(feet, selfc))
+  velocity_sim_options(scene)
+  m = scene.compile()
+  m.meta = dict(task="Mjlab-Velocity-Flat-Asimov", nconmax=50, njmax=300, decimation=4, collision=collision)
+  return m
+
+
+# ---------------------------------------------------------------------------
 # model blob (.npz) save / load
 # ---------------------------------------------------------------------------
 _OPT_KEYS = ("timestep", "integrator", "cone", "solver", "iterations", "ls_iterations", "tolerance",

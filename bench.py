@@ -30,6 +30,7 @@ WORKLOADS = {
   "asimov_toe_rough": ("asimov_toe_rough", "Asimov-toe velocity task physics step on the reference's default box terrain, random actions"),
   "go1_rough_hf": ("go1_rough_hf", "Go1 rough task with the generator's height-field sub-terrains enabled (terrains/config.py:28-53, commented out in the reference), random actions (BASELINE.json configs[2], hfield variant)"),
   "asimov_toe_full_flat": ("asimov_toe_full_flat", "Asimov-toe, FULL_COLLISION (11 link meshes by convex hull + 20 capsules, self collisions) on the plane, random actions"),
+  "asimov_flat": ("asimov_flat", "Mjlab-Velocity-Flat-Asimov physics step (12-dof biped, all-mesh collision geometry: the two foot meshes on the plane, plane-mesh manifolds), random actions"),
   "go1_rough": ("go1_rough", "Mjlab-Velocity-Rough-Unitree-Go1 physics step on the reference's default box terrain, random actions (BASELINE.json configs[2], box variant)"),
 }
 
@@ -138,6 +139,8 @@ def action_targets(m, n_batches, envs, seed, device=None):
     for k, n in enumerate(("left_ankle_A", "left_ankle_B", "right_ankle_A", "right_ankle_B")):
       ctrl[..., jn.index(n)] = ab[..., k]
     return ctrl.astype(np.float32)
+  if m.meta.get("task") == "Mjlab-Velocity-Flat-Asimov":
+    return (np.asarray(key["ctrl"], np.float32)[None, None, :] + scenes.asimov12_action_scale(jn).astype(np.float32)[None, None, :] * a)
   scale = scenes.g1_action_scale(jn) if m.nu == 29 else scenes.go1_action_scale(jn)
   return (np.asarray(key["ctrl"], np.float32)[None, None, :] + scale.astype(np.float32)[None, None, :] * a)
 
@@ -238,7 +241,7 @@ class PhysBench:
     # foot-friction domain randomisation ON (per-world Model reads stay honest; velocity_env_cfg.py:230-240)
     sim.expand_model_fields(("geom_friction",))
     g = torch.Generator(device="cpu").manual_seed(rank)
-    self.foot = foot = [i for i, n in enumerate(m.names["geom"]) if ("foot" in n or "_toe" in n) and n.endswith("_collision")]
+    self.foot = foot = [i for i, n in enumerate(m.names["geom"]) if ("foot" in n or "_toe" in n or "ankle_roll_link" in n) and n.endswith("_collision")]
     fr = 0.3 + 0.9 * torch.rand(E, len(foot), generator=g)
     M.geom_friction[:, foot, 0] = fr.to(dev)
     M.opt.stage_overlap = int(overlap)
@@ -327,7 +330,7 @@ def extra_measurements(args, world, rank, dev, pb):
                    "unit": "physics sub-steps/s per GPU", "note": "robots driven by random joint targets stand for ~40 control steps (two loaded feet: ~50 constraint rows, ~5.4 Newton iterations), then lie on the ground (~15 rows, ~3.3 iterations)"}
   if rank == 0 and world == 1:
     wl = {}
-    for name in ("go1_rough", "go1_rough_hf", "asimov_toe_flat", "asimov_toe_full_flat"):
+    for name in ("go1_rough", "go1_rough_hf", "asimov_flat", "asimov_toe_flat", "asimov_toe_full_flat"):
       try:
         p2 = PhysBench(name, args.envs, dev, rank, args.ls_parallel)
         ms, _ = p2.timed(40, 5)

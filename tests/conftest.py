@@ -53,3 +53,15 @@ def go1_rough_hf():
 def go1_rough():
   from asimov_mjlab_b200 import scenes
   return scenes.load_asset("go1_rough")
+
+
+@pytest.fixture(scope="session")
+def asimov12():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("asimov_flat")
+
+
+@pytest.fixture(scope="session")
+def asimov12_full():
+  from asimov_mjlab_b200 import scenes
+  return scenes.load_asset("asimov_full_flat")

@@ -444,3 +444,92 @@ def test_env_origin_sites_are_stored_once(g1):
   # per-world poses of static sites cannot be honoured in this layout: refused, not ignored
   with pytest.raises(engine.BackendError, match="site_split"):
     engine.expand_model_fields(M, W, ["site_pos"])
+
+
+# --------------------------------------------------------------------------------------------- the 12-dof Asimov (all-mesh collision)
+def test_asimov12_feet_meshes_on_the_plane_match_oracle(asimov12, capsys):
+  """Mjlab-Velocity-Flat-Asimov (tasks/velocity/config/asimov/env_cfgs.py; robot asset_zoo/robots/asimov/xmls/asimov.xml:50-110):
+  the task's FEET_ONLY_COLLISION leaves the two foot MESHES against the terrain -- the plane-mesh manifold (up to 4 contacts
+  per foot) carries the robot.  forward() fields, contact lists and 40 free-running steps from standing states against the
+  oracle; then oracle-driven states of falling robots, compared at every 10th state."""
+  import torch
+  from test_gpu_parity import ConvexStats
+  m = asimov12
+  assert (m.nq, m.nv, m.nu, m.nbody) == (19, 18, 12, 16) and int((np.asarray(m.geom_type) == 7).sum()) >= 2
+  W = 32
+  qpos, qvel, ctrl = legged_states(m, W, seed=3, spread=0.1, vel=0.2, zlo=0.725, zhi=0.74)
+  qpos[:, 3:7] = [1.0, 0.0, 0.0, 0.0]                          # upright: both feet load their manifolds
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True)
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  _check_counts(D, worlds)
+  assert sum(int(w["ncon"][0]) for w in worlds) >= 3 * W      # multi-contact manifolds
+  for f in ("geom_xpos", "site_xpos", "subtree_com", "qacc_smooth"):
+    assert _rel_err(D, worlds, f) < TOL_FORWARD[f] * 4, f
+  # the task's cap of 10 Newton iterations: a world whose solve hits it on either side is an unconverged iterate (measured: one
+  # of 32, 1e-2 apart, 2e-3 in cost); every other world agrees at the forward tolerances
+  nit_o = np.array([int(w["solver_niter"][0]) for w in worlds]); nit_g = D.solver_niter.cpu().numpy()
+  conv = (nit_o < m.opt.iterations) & (nit_g < m.opt.iterations)
+  assert conv.sum() >= W - 8 and np.abs(nit_g - nit_o)[conv].max() <= 1      # 5 of 32 worlds sit at the cap (niter = 10)
+  for f in ("qacc", "qfrc_constraint", "sensordata"):
+    g = getattr(D, f).cpu().numpy().astype(np.float64); o = np.stack([w[f] for w in worlds]).astype(np.float64)
+    scale = 1e-6 + np.abs(o).max()
+    assert np.abs(g - o)[conv].max() / scale < TOL_FORWARD[f], f
+    assert np.abs(g - o)[~conv].max(initial=0) / scale < 0.1, f
+  # free run with converged solves (iterations 30): dynamics through the manifolds.  Which hull vertices make up a manifold is a
+  # discrete choice (vertices within 1 mm of the deepest one), so a free run separates once one side picks another vertex; until
+  # then the states agree closely
+  m30 = copy.copy(m); m30.opt = copy.copy(m.opt); m30.opt.iterations = 30
+  first, err = _free_run(m30, qpos, qvel, ctrl, 40, (5, 20))
+  with capsys.disabled():
+    print(f"\n[asimov 12-dof free run] first contact-list difference per world (41 = never): {np.sort(first).tolist()}")
+  assert err[5][first > 5].max() < 1e-4 and np.median(first) > 20
+  assert err[20][first > 20].max() < 1e-3
+  st = ConvexStats(m)
+  for chunk in range(10):
+    for w in worlds:
+      orc.step(w, 10)
+    for f in ("qpos", "qvel", "qacc_warmstart"):
+      getattr(D, f)[:] = torch.as_tensor(np.stack([w[f] for w in worlds]), dtype=torch.float32, device="cuda:0")
+    engine.forward(M, D)
+    for w in worlds:
+      orc.forward(w)
+    n_all = D.ncon.cpu().numpy()
+    G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9)
+    Di = D.contact_dist.cpu().numpy(); Inc = D.contact_includemargin.cpu().numpy()
+    for i, w in enumerate(worlds):
+      st.compare(i, w, n_all[i], G, P, Fr, Di, Inc)
+  with capsys.disabled():
+    st.report("asimov 12-dof, feet meshes on the plane")
+  assert st.identical >= 0.98 * st.states and st.ncmp > 300 and st.tight >= 0.97 * st.ncmp, (st.identical, st.states, st.ncmp, st.tight)
+
+
+def test_asimov12_full_collision_mesh_mesh_contacts_match_oracle(asimov12_full, capsys):
+  """FULL_COLLISION of the same robot (asimov_constants.py:195-205): 13 link hulls (6501 vertices) against the plane and each
+  other.  Random joint configurations put neighbouring hulls into DEEP overlap (the convex hulls of grand-parent / grand-child
+  links intersect at the joints): GJK + EPA on penetrating mesh-mesh pairs.  forward() only -- such states are not a physical
+  workload -- contact lists, distances and frames against the oracle."""
+  import torch
+  from test_gpu_parity import ConvexStats
+  m = asimov12_full
+  W = 32
+  qpos, qvel, ctrl = legged_states(m, W, seed=5, spread=0.6, vel=0.0, zlo=0.3, zhi=0.8)
+  rng = np.random.default_rng(5)
+  for w in range(W):
+    ax = rng.normal(size=3); ax /= np.linalg.norm(ax); ang = rng.normal(0, 0.8)
+    qpos[w, 3:7] = [np.cos(ang / 2), *(ax * np.sin(ang / 2))]
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True)
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  st = ConvexStats(m)
+  n_all = D.ncon.cpu().numpy()
+  G = D.contact_geom.cpu().numpy(); P = D.contact_pos.cpu().numpy(); Fr = D.contact_frame.cpu().numpy().reshape(W, -1, 9)
+  Di = D.contact_dist.cpu().numpy(); Inc = D.contact_includemargin.cpu().numpy()
+  for i, w in enumerate(worlds):
+    st.compare(i, w, n_all[i], G, P, Fr, Di, Inc)
+  with capsys.disabled():
+    st.report("asimov 12-dof, full collision, random poses")
+  assert (7, 7) in st.seen and st.ncmp > 150
+  assert st.identical >= 0.9 * st.states and st.tight >= 0.9 * st.ncmp, (st.identical, st.states, st.ncmp, st.tight)

@@ -35,3 +35,10 @@ for terr in ("plane", "rough"):
 a = scenes.build_asimov_toe(os.path.join(zoo, "asimov/xmls/asimov_toe.xml"), terrain="plane", collision="full")
 scenes.save_model(a, os.path.join(scenes.ASSET_DIR, "asimov_toe_full_flat.npz"))
 print("asimov_toe_full_flat: ngeom", a.ngeom, "nmesh", a.nmesh, "nmeshvert", a.nmeshvert)
+
+for col in ("feet_only", "full"):
+  a = scenes.build_asimov(os.path.join(zoo, "asimov/xmls/asimov.xml"), collision=col)
+  name = "asimov_flat" if col == "feet_only" else "asimov_full_flat"
+  scenes.save_model(a, os.path.join(scenes.ASSET_DIR, name + ".npz"))
+  print(name, ": nq", a.nq, "nv", a.nv, "nu", a.nu, "nbody", a.nbody, "ngeom", a.ngeom, "nmesh", a.nmesh, "nmeshvert", a.nmeshvert,
+        "nsensordata", a.nsensordata, "npair-capable geoms", int(((a.geom_contype | a.geom_conaffinity) != 0).sum()))
