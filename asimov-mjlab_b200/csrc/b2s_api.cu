@@ -336,7 +336,8 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   }
   // ---------------------------------------------------------------- static collision pair table
   std::vector<int> pairs;
-  int col_convex = 0;
+  int col_convex = 0, col_defer = 0;
+  auto pair_deferred = [&](int t1, int t2) { return pair_convex(t1, t2) && t1 != B2S_GEOM_PLANE && t1 != B2S_GEOM_HFIELD; };
   int col_maxc = 1;          // most contacts one geom pair of this model can produce: picks the narrowphase variant
   for (int ga = 0; ga < s->ngeom; ga++) for (int gb = ga + 1; gb < s->ngeom; gb++) {
     if (in_grid[ga] || in_grid[gb]) continue;      // found through the grid at run time
@@ -360,6 +361,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     pairs.push_back(g1); pairs.push_back(g2);
     col_maxc = std::max(col_maxc, pair_max_contacts(s->geom_type[g1], s->geom_type[g2]));
     col_convex |= pair_convex(s->geom_type[g1], s->geom_type[g2]) ? 1 : 0;
+    col_defer |= pair_deferred(s->geom_type[g1], s->geom_type[g2]) ? 1 : 0;
   }
   if (use_grid)   // grid pairs: every dynamic geom against every geom type present in the grid
     for (int ga : dyn_geoms) for (int gb : grid_geoms) {
@@ -367,6 +369,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       const int t1 = std::min(s->geom_type[ga], s->geom_type[gb]), t2 = std::max(s->geom_type[ga], s->geom_type[gb]);
       col_maxc = std::max(col_maxc, pair_max_contacts(t1, t2));
       col_convex |= pair_convex(t1, t2) ? 1 : 0;
+      col_defer |= pair_deferred(t1, t2) ? 1 : 0;
     }
   // ---------------------------------------------------------------- traversal tables
   int nlevel = 0;
@@ -477,7 +480,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     d.geom_bcen = up.raw(bcen); d.geom_bsize = up.raw(bsize); d.geom_brad = up.raw(brad);
   }
   d.col_maxc = col_maxc <= 2 ? 2 : (col_maxc <= 4 ? 4 : 8);
-  d.col_convex = col_convex;
+  d.col_convex = col_convex; d.col_defer = col_defer;
   d.geom_dataid = up.i(s->geom_dataid, s->ngeom);
   d.mesh_vertadr = up.i(s->mesh_vertadr, s->nmesh); d.mesh_vertnum = up.i(s->mesh_vertnum, s->nmesh);
   {
@@ -720,6 +723,10 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"contact_pos", B2S_F32, (void**)&d.con_pos, {nconmax, 3}}, {"contact_frame", B2S_F32, (void**)&d.con_frame, {nconmax, 3, 3}},
     {"contact_includemargin", B2S_F32, (void**)&d.con_includemargin, {nconmax}}, {"contact_friction", B2S_F32, (void**)&d.con_friction, {nconmax, 5}},
     {"contact_solref", B2S_F32, (void**)&d.con_solref, {nconmax, 2}}, {"contact_solimp", B2S_F32, (void**)&d.con_solimp, {nconmax, 5}},
+    {"col_surv", B2S_I32, (void**)&d.col_surv, {md.col_defer ? B2S_MAX_SURVIVORS : 0}}, {"col_nsurv", B2S_I32, (void**)&d.col_nsurv, {md.col_defer ? 1 : 0}},
+    {"col_pidx", B2S_I32, (void**)&d.col_pidx, {md.col_defer ? B2S_MAX_SURVIVORS : 0}}, {"cvx_ntask", B2S_I32, (void**)&d.cvx_ntask, {md.col_defer ? 1 : 0}},
+    {"cvx_task", B2S_I32, (void**)&d.cvx_task, {md.col_defer ? B2S_MAX_SURVIVORS : 0, 2}}, {"cvx_stage", B2S_F32, (void**)&d.cvx_stage, {md.col_defer ? B2S_MAX_SURVIVORS : 0, 8}},
+    {"col_axis", B2S_F32, (void**)&d.col_axis, {(md.col_convex && md.ngrid == 0) ? md.npair : 0, 3}},
     {"nefc", B2S_I32, (void**)&d.nefc, {}}, {"nl", B2S_I32, (void**)&d.nl, {}}, {"nf", B2S_I32, (void**)&d.nf, {}}, {"efc_type", B2S_I32, (void**)&d.efc_type, {njmax}}, {"efc_id", B2S_I32, (void**)&d.efc_id, {njmax}},
     {"efc_g", B2S_F32, (void**)&d.efc_g, {njmax, 6}}, {"efc_bp", B2S_I32, (void**)&d.efc_bp, {njmax}}, {"efc_pos", B2S_F32, (void**)&d.efc_pos, {njmax}}, {"efc_margin", B2S_F32, (void**)&d.efc_margin, {njmax}},
     {"efc_D", B2S_F32, (void**)&d.efc_D, {njmax}}, {"efc_vel", B2S_F32, (void**)&d.efc_vel, {njmax}}, {"efc_aref", B2S_F32, (void**)&d.efc_aref, {njmax}},

@@ -11,6 +11,7 @@
 #define B2S_WARPS_PER_CTA 4
 #define B2S_MAX_NV 56          // register-tiled Hessian: 7 x 7 tiles of up to 8 x 8
 #define B2S_GRID_MIN_GEOMS 64   // static non-plane geoms beyond this count are indexed by a uniform grid
+#define B2S_MAX_SURVIVORS 160    // broadphase survivors (candidate geom pairs) kept per world and step
 #define B2S_SITE_SPLIT_MIN 1024  // static sites: from this many on their frames are stored once instead of per world
 #define B2S_MINVAL 1e-15f
 #define B2S_MINMU 1e-5f
@@ -77,6 +78,7 @@ struct ModelDev {
   // ---- fixed tendons (wraps flattened to dof / qpos addresses) and actuators
   int col_maxc;      // narrowphase variant: most contacts per geom pair (2, 4 or 8)
   int col_convex;    // 1: some pair needs the GJK/EPA, plane-mesh or height-field colliders
+  int col_defer;     // 1: GJK/EPA pairs between two convex cores exist: they run as (world, pair) tasks of a second kernel (k_convex_tasks)
   const int *geom_dataid, *mesh_vertadr, *mesh_vertnum, *hfield_nrow, *hfield_ncol, *hfield_adr;
   const float *mesh_vert, *hfield_size, *hfield_data;
   const float *geom_bcen, *geom_bsize, *geom_brad;   // broadphase volume: local box (centre offset, half sizes) and its radius
@@ -108,6 +110,10 @@ struct DataDev {
   // collision
   int *ncon, *con_dim, *con_geom, *con_efc_address;
   float *con_dist, *con_pos, *con_frame, *con_includemargin, *con_friction, *con_solref, *con_solimp;
+  // deferred convex pairs (ModelDev::col_defer): survivor list of each world [B2S_MAX_SURVIVORS] (+ count, + pair-table index),
+  // global task list (world, survivor index) with its counter, and one staged result (CvxStage, 8 floats) per survivor
+  unsigned* col_surv; int *col_nsurv, *col_pidx, *cvx_ntask, *cvx_task; float* cvx_stage;
+  float* col_axis;   // [npair][3] per world, convex models only: last separating direction of each table pair (k_convex.cuh gjk_epa)
   // constraints
   int *nefc, *nl, *nf, *efc_type, *efc_id, *efc_bp;   // rows [0, nl) act on one dof: nf friction-loss rows, then the limits;   // efc_bp: contact rows body1 | body2 << 16, limit rows -1 - dof
   float *efc_g;                                  // [njmax][6] row wrench about the reference point (limit rows: g[0] = +-1)

@@ -14,7 +14,6 @@
 #include "k_convex.cuh"
 
 extern __shared__ float b2s_smem[];
-#define B2S_MAX_SURVIVORS 160
 
 struct RawCon { float dist; v3 pos, n, t; };
 
@@ -366,7 +365,12 @@ DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
 
 // MAXC = most contacts one pair of this model can produce (put_model picks 2 / 4 / 8): the contact scratch stays in
 // registers for sphere / capsule robots and the box colliders are compiled out where no box pair exists
-template <int MAXC, bool CONVEX>
+// PHASE (models with GJK / EPA pairs between two convex cores, ModelDev::col_defer): such a pair costs a warp 2 - 100 us and a
+// crumpled robot has a hundred of them, so one world's warp used to hold the whole kernel (measured: mean 154 us per world,
+// slowest world 6.6 ms).  The stage is split: PHASE 1 = broadphase, survivor list to global memory, one (world, survivor) TASK
+// per deferred pair; k_convex_tasks = one warp per task from the global list, results staged per survivor; PHASE 2 = the
+// narrowphase as before, reading the staged result where a pair was deferred.  PHASE 0 = everything in one kernel.
+template <int MAXC, bool CONVEX, int PHASE>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
@@ -377,13 +381,24 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   unsigned* s_sort = s_list + B2S_MAX_SURVIVORS;
   int* s_cnt = (int*)(s_sort + B2S_MAX_SURVIVORS);
   CvxStage* s_stage = (CvxStage*)((unsigned*)b2s_smem + B2S_WARPS_PER_CTA * (2 * B2S_MAX_SURVIVORS + 1)) + warp * CVX_STAGE_CAP;
+  // pair-table index of each survivor (convex models without a terrain grid): addresses the pair's cached separating direction
+  const bool use_axis = CONVEX && m.ngrid == 0 && d.col_axis != nullptr;
+  int* s_pidx = (int*)(s_stage + (size_t)(B2S_WARPS_PER_CTA - warp) * CVX_STAGE_CAP) + warp * B2S_MAX_SURVIVORS;
   if (m.disableflags & (B2S_DSBL_CONSTRAINT | B2S_DSBL_CONTACT)) { if (lane == 0) d.ncon[w] = 0; return; }
   const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
   const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
   const float* gfri = m.geom_friction.at(w);
+#ifdef COL_TIMING      // development builds only (tools/exp_col_time.py): phase cycles and pair counts into the tail of efc_force
+  long long t_ph[4] = {clock64(), 0, 0, 0}; int n_cvx = 0, n_hit = 0;
+#endif
   // A1) static pair table (dynamic-dynamic and plane-dynamic pairs, already in key order): bounding spheres
   int nsurv = 0;
-  for (int base = 0; base < m.npair; base += 32) {
+  if constexpr (PHASE == 2) {       // the survivors phase 1 found
+    nsurv = d.col_nsurv[w];
+    for (int i = lane; i < nsurv; i += 32) s_list[i] = d.col_surv[(size_t)w * B2S_MAX_SURVIVORS + i];
+    __syncwarp();
+  }
+  for (int base = 0; PHASE != 2 && base < m.npair; base += 32) {
     const int p = base + lane;
     bool pass = false;
     unsigned key = 0;
@@ -429,13 +444,13 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       key = ((unsigned)min(g1, g2) << 16) | (unsigned)max(g1, g2);
     }
     const unsigned mask = __ballot_sync(FULL, pass);
-    if (pass) { const int pos = nsurv + __popc(mask & ((1u << lane) - 1u)); if (pos < B2S_MAX_SURVIVORS) s_list[pos] = key; }
+    if (pass) { const int pos = nsurv + __popc(mask & ((1u << lane) - 1u)); if (pos < B2S_MAX_SURVIVORS) { s_list[pos] = key; if (CONVEX && use_axis) s_pidx[pos] = p; } }
     nsurv += __popc(mask);
   }
   nsurv = min(nsurv, B2S_MAX_SURVIVORS);
   // A2) static terrain geoms through the uniform xy grid built at put_model: one lane per dynamic geom walks the
   // cells under its bounding sphere; a static geom that spans several cells is taken in its first common cell only
-  if (m.ngrid > 0) {
+  if (PHASE != 2 && m.ngrid > 0) {
     if (lane == 0) *s_cnt = nsurv;
     __syncwarp();
     for (int k = lane; k < m.ndyngeom; k += 32) {
@@ -475,6 +490,34 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
     nsurv = ntot;
   }
   __syncwarp();
+#ifdef COL_TIMING
+  t_ph[1] = clock64();
+#endif
+  if constexpr (PHASE == 1) {
+    // survivors to global memory; one task per pair that needs GJK / EPA between two convex cores
+    __syncwarp();
+    for (int base = 0; base < nsurv; base += 32) {
+      const int i = base + lane;
+      bool defer = false;
+      if (i < nsurv) {
+        const unsigned key = s_list[i];
+        d.col_surv[(size_t)w * B2S_MAX_SURVIVORS + i] = key;
+        if (use_axis) d.col_pidx[(size_t)w * B2S_MAX_SURVIVORS + i] = s_pidx[i];
+        int t1 = m.geom_type[key >> 16], t2 = m.geom_type[key & 0xffffu];
+        if (t1 > t2) { const int tt = t1; t1 = t2; t2 = tt; }
+        defer = t1 >= B2S_GEOM_SPHERE && (t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_CYLINDER || t1 == B2S_GEOM_ELLIPSOID || t2 == B2S_GEOM_CYLINDER || t2 == B2S_GEOM_ELLIPSOID);
+      }
+      const unsigned dm = __ballot_sync(FULL, defer);
+      if (dm) {
+        int k0 = 0;
+        if (lane == 0) k0 = atomicAdd(d.cvx_ntask, __popc(dm));
+        k0 = __shfl_sync(FULL, k0, 0);
+        if (defer) { const int k = k0 + __popc(dm & ((1u << lane) - 1u)); d.cvx_task[2 * (size_t)k] = w; d.cvx_task[2 * (size_t)k + 1] = i; }
+      }
+    }
+    if (lane == 0) d.col_nsurv[w] = nsurv;
+    return;
+  }
   // B) narrowphase, 32 survivors per pass, ordered append
   int ncon = 0;
   const int cmax = d.nconmax;
@@ -509,6 +552,14 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       // every pair with a mesh, a height field, a cylinder or an ellipsoid (other than plane - cylinder / ellipsoid) is convex work
       if constexpr (CONVEX) cvx = t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_HFIELD ||
                                   (t1 >= B2S_GEOM_SPHERE && (t1 == B2S_GEOM_CYLINDER || t1 == B2S_GEOM_ELLIPSOID || t2 == B2S_GEOM_CYLINDER || t2 == B2S_GEOM_ELLIPSOID));
+      if constexpr (CONVEX && PHASE == 2) {
+        if (cvx && t1 >= B2S_GEOM_SPHERE) {      // deferred pair: k_convex_tasks staged its result
+          const CvxStage* sg = reinterpret_cast<const CvxStage*>(d.cvx_stage + ((size_t)w * B2S_MAX_SURVIVORS + i) * 8);
+          n = sg->idx;
+          if (n) { rc[0].dist = sg->dist; rc[0].pos = sg->pos; rc[0].n = sg->n; rc[0].t = mk3(0.f, 0.f, 0.f); }
+          cvx = false;
+        }
+      }
     }
     if constexpr (CONVEX) {
       // mesh / height-field pairs of this pass, one at a time with the whole warp: hull scans are lane-strided, a
@@ -580,7 +631,13 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         __syncwarp();
       }
       unsigned todo = __ballot_sync(FULL, cvx && !(hf && hf_done));
+#ifdef COL_TIMING
+      n_cvx += __popc(todo);
+#endif
       while (todo) {
+#ifdef COL_TIMING
+        const long long t_c0 = clock64();
+#endif
         const int L = __ffs(todo) - 1;
         todo &= todo - 1;
         const int bg1 = __shfl_sync(FULL, g1, L), bg2 = __shfl_sync(FULL, g2, L);
@@ -611,9 +668,13 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
           else if (t1 == B2S_GEOM_ELLIPSOID) A.type = CVX_ELLIPSOID;
           else { const int id = m.geom_dataid[bg1]; A.type = CVX_VERTS; A.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; A.nvert = m.mesh_vertnum[id]; A.coop = true; }
           B.coop = (B.type == CVX_VERTS);
-          nres = convex_pair_warp(s_stage, bm, A, B, lane);
+          float* axis = use_axis ? d.col_axis + ((size_t)w * m.npair + s_pidx[base + L]) * 3 : nullptr;
+          nres = convex_pair_warp(s_stage, bm, A, B, lane, axis);
         }
         __syncwarp();
+#ifdef COL_TIMING
+        n_hit += nres > 0; t_ph[2] += clock64() - t_c0;
+#endif
         if (lane == L) {
           n = nres;
 #pragma unroll
@@ -672,7 +733,41 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
     ncon += total;
   }
   B2S_ASSERT(nsurv <= B2S_MAX_SURVIVORS);
+#ifdef COL_TIMING
+  if (lane == 0) {
+    float* o = d.efc_force + (size_t)(w + 1) * d.njmax - 8;
+    o[0] = (float)(t_ph[1] - t_ph[0]); o[1] = (float)(clock64() - t_ph[1]); o[2] = (float)t_ph[2]; o[3] = (float)nsurv; o[4] = (float)n_cvx; o[5] = (float)n_hit;
+  }
+#endif
   if (lane == 0) d.ncon[w] = min(ncon, cmax);
+}
+
+// One warp per (world, survivor) task of the global list phase 1 filled: GJK / EPA between the two convex cores with the hull
+// scans shared by the 32 lanes, result staged for phase 2.  A persistent grid strides over the list, so a world with a hundred
+// such pairs is spread over the whole machine instead of serialising on its own warp.
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const ModelDev m, const DataDev d) {
+  const int lane = threadIdx.x & 31;
+  const int gw = blockIdx.x * B2S_WARPS_PER_CTA + (threadIdx.x >> 5), nwarp = gridDim.x * B2S_WARPS_PER_CTA;
+  const int ntask = min(d.cvx_ntask[0], d.nworld * B2S_MAX_SURVIVORS);
+  const bool use_axis = m.ngrid == 0;
+#pragma unroll 1
+  for (int k = gw; k < ntask; k += nwarp) {
+    const int w = d.cvx_task[2 * (size_t)k], i = d.cvx_task[2 * (size_t)k + 1];
+    const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
+    const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
+    const unsigned key = d.col_surv[(size_t)w * B2S_MAX_SURVIVORS + i];
+    int g1 = (int)(key >> 16), g2 = (int)(key & 0xffffu);
+    if (m.geom_type[g1] > m.geom_type[g2]) { const int t = g1; g1 = g2; g2 = t; }
+    const float margin = fmaxf(m.geom_margin[g1], m.geom_margin[g2]);
+    Cvx A = geom_core(m, gx, gm, g1), B = geom_core(m, gx, gm, g2);
+    A.coop = A.type == CVX_VERTS; B.coop = B.type == CVX_VERTS;
+    CvxStage* out = reinterpret_cast<CvxStage*>(d.cvx_stage + ((size_t)w * B2S_MAX_SURVIVORS + i) * 8);
+    float* axis = use_axis ? d.col_axis + ((size_t)w * m.npair + d.col_pidx[(size_t)w * B2S_MAX_SURVIVORS + i]) * 3 : nullptr;
+    const int nres = convex_pair_warp(out, margin, A, B, lane, axis);
+    __syncwarp();
+    if (lane == 0) out->idx = nres;
+    __syncwarp();
+  }
 }
 
 #define COL_DISPATCH(M, EXPR)                                                                   \
@@ -684,14 +779,21 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   }
 void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
-  COL_DISPATCH(m, (k_collision<MAXC, CONVEX><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
+  if (m.col_convex && m.col_defer) {      // broadphase + task emission, the GJK / EPA tasks over the whole machine, narrowphase + ordered append
+    k_collision<8, true, 1><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
+    k_convex_tasks<<<148 * 4, 32 * B2S_WARPS_PER_CTA, 0, st>>>(m, d);
+    k_collision<8, true, 2><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
+    b2s_count_launch(); b2s_count_launch(); b2s_count_launch();
+    return;
+  }
+  COL_DISPATCH(m, (k_collision<MAXC, CONVEX, 0><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
   b2s_count_launch();
 }
 size_t smem_collision(const ModelDev& m) {
-  return (size_t)B2S_WARPS_PER_CTA * ((2 * B2S_MAX_SURVIVORS + 1) * sizeof(int) + (m.col_convex ? CVX_STAGE_CAP * sizeof(CvxStage) : 0));
+  return (size_t)B2S_WARPS_PER_CTA * ((2 * B2S_MAX_SURVIVORS + 1) * sizeof(int) + (m.col_convex ? CVX_STAGE_CAP * sizeof(CvxStage) + B2S_MAX_SURVIVORS * sizeof(int) : 0));
 }
 const void* fn_collision(const ModelDev& m) {
   const void* f = nullptr;
-  COL_DISPATCH(m, (f = (const void*)k_collision<MAXC, CONVEX>));
+  COL_DISPATCH(m, (f = (const void*)k_collision<MAXC, CONVEX, 0>));
   return f;
 }

@@ -229,8 +229,25 @@ __device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const S
 
 // GJK on the cores.  false: farther apart than `cutoff`.  Separated: dist > 0, n from A to B, pa / pb closest core
 // points.  Overlapping cores: the simplex is grown to a tetrahedron around the origin and handed to EPA.
-__device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, CvxRes& out) {
+// `axis` (optional, 3 floats of per-pair storage that lives across steps; warp-level callers only): TEMPORAL COHERENCE.  A pair that
+// was separated in the last step is almost always separated by nearly the same plane now, so the direction GJK ended with is
+// tried first: one support evaluation, and if that plane still separates the cores by more than `cutoff` there is no contact --
+// the same bound (valid for ANY direction) that ends the GJK loop early, so the outcome is the one the full search would reach.
+// Otherwise the search runs exactly as without the cache (same start direction, same iterates).  The cache is refreshed
+// whenever the search proves separation and cleared when it finds a contact.
+__device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, CvxRes& out, float* axis = nullptr) {
   Simplex s;
+  if (axis) {
+    const v3 vc = ld3(axis);
+    const float vv = dot(vc, vc);
+    if (vv > 0.f) {
+      v3 w, wa;
+      mink_support(A, B, vc * -1.f, w, wa);
+      const float vw = dot(vc, w);
+      if (vw > 0.f && vw * vw > cutoff * cutoff * vv) return false;
+    }
+    __syncwarp();
+  }
   v3 dir = B.pos - A.pos;
   if (dot(dir, dir) < 1e-20f) dir = mk3(1.f, 0.f, 0.f);
   mink_support(A, B, dir, s.Y[0], s.A[0]);
@@ -245,7 +262,7 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
     v3 w, wa;
     mink_support(A, B, v * -1.f, w, wa);
     const float vw = dot(v, w);
-    if (vw > 0.f && vw * vw > cutoff * cutoff * vv) return false;
+    if (vw > 0.f && vw * vw > cutoff * cutoff * vv) { if (axis && (threadIdx.x & 31) == 0) st3(axis, v); return false; }
     const float ww = dot(w, w);
     if (ww > scale2) scale2 = ww;
     if (vv - vw <= CVX_TOL * vv + 1e-12f * scale2) break;
@@ -257,6 +274,10 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
     else if (s.n == 3) closest_triangle(s);
     else if (closest_tetrahedron(s, scale2)) { inside = true; break; }
     v = sx_point(s.Y, s);
+  }
+  if (axis && (threadIdx.x & 31) == 0) {      // separated beyond the cutoff: remember the direction; anything else: no cached plane
+    const bool sep = !inside && dot(v, v) > cutoff * cutoff;
+    st3(axis, sep ? v : mk3(0.f, 0.f, 0.f));
   }
   if (!inside) {
     const float vv = dot(v, v), dist = sqrtf(vv);
@@ -405,9 +426,9 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
 
 // one convex pair, every lane in the call: the hull scans are shared (Cvx::coop), the simplex / polytope logic runs
 // redundantly and identically on all lanes
-DEV int convex_pair_warp(CvxStage* out, float margin, const Cvx& A, const Cvx& B, int lane) {
+DEV int convex_pair_warp(CvxStage* out, float margin, const Cvx& A, const Cvx& B, int lane, float* axis = nullptr) {
   CvxRes r;
-  if (!gjk_epa(A, B, margin + A.radius + B.radius, r)) return 0;
+  if (!gjk_epa(A, B, margin + A.radius + B.radius, r, axis)) return 0;
   const float dist = r.dist - A.radius - B.radius;
   if (dist > margin) return 0;
   const v3 sa = r.pa + r.n * A.radius, sb = r.pb - r.n * B.radius;

@@ -1,0 +1,20 @@
+"""Where k_collision spends its time (needs a -DCOL_TIMING build via B2S_LIB): per-world phase cycles and pair counts."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT]
+import numpy as np, torch
+import bench
+from asimov_mjlab_b200 import engine
+W = int(os.environ.get("W", "4096"))
+for wl in os.environ.get("WL", "asimov_toe_full_flat,go1_rough_hf").split(","):
+  pb = bench.PhysBench(wl, W, "cuda:0", 0)
+  pb.reset_all()
+  for i in range(1, 12):
+    pb.one_step(i)
+  engine.forward(pb.M, pb.D)
+  torch.cuda.synchronize()
+  t = pb.D.efc_force[:, -8:].cpu().numpy().astype(np.float64)
+  us = t[:, :3] / 1965.0
+  print(f"[{wl}] per world: broadphase {us[:,0].mean():.1f} us, narrowphase {us[:,1].mean():.1f} us (max {us[:,1].max():.0f}), of which convex-pair loop {us[:,2].mean():.1f} us; "
+        f"survivors {t[:,3].mean():.1f} (max {t[:,3].max():.0f}), convex pairs {t[:,4].mean():.1f} (max {t[:,4].max():.0f}), with a contact {t[:,5].mean():.2f}; ncon {pb.D.ncon.float().mean():.2f}")
+  print("   stage ms", engine.profile_step(pb.M, pb.D, 5))
