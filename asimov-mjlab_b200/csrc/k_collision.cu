@@ -750,8 +750,15 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const M
   const int gw = blockIdx.x * B2S_WARPS_PER_CTA + (threadIdx.x >> 5), nwarp = gridDim.x * B2S_WARPS_PER_CTA;
   const int ntask = min(d.cvx_ntask[0], d.nworld * B2S_MAX_SURVIVORS);
   const bool use_axis = m.ngrid == 0;
+  // tasks differ by two orders of magnitude (a cached separating plane: one support evaluation; a deep overlap: GJK + 24 EPA
+  // rounds): warps pull the next task from a cursor instead of striding statically
+  (void)gw; (void)nwarp;
 #pragma unroll 1
-  for (int k = gw; k < ntask; k += nwarp) {
+  while (true) {
+    int k = 0;
+    if (lane == 0) k = atomicAdd(d.cvx_ntask + 1, 1);
+    k = __shfl_sync(FULL, k, 0);
+    if (k >= ntask) break;
     const int w = d.cvx_task[2 * (size_t)k], i = d.cvx_task[2 * (size_t)k + 1];
     const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
     const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;

@@ -59,10 +59,19 @@ __device__ __noinline__ v3 cvx_support(const Cvx& s, v3 dir) {
     const int lane = threadIdx.x & 31;
     int best = 0x7fffffff; float bd = -3.0e38f;
     const float4* v4 = reinterpret_cast<const float4*>(s.vert);        // mesh hulls are stored 4 floats per vertex
-    for (int i = lane; i < s.nvert; i += 32) {
-      const float4 p = __ldg(v4 + i);
-      const float t = p.x * dl.x + p.y * dl.y + p.z * dl.z;
-      if (t > bd) { bd = t; best = i; }
+    // four independent 16-byte loads in flight per lane before the first compare (the scan is latency-bound: L1 / L2 hits);
+    // candidates are still visited in ascending index order per lane, so ties keep the lowest index
+#pragma unroll 1
+    for (int i0 = lane; i0 < s.nvert; i0 += 128) {
+      float4 p[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) p[u] = __ldg(v4 + min(i0 + 32 * u, s.nvert - 1));
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int i = i0 + 32 * u;
+        const float t = p[u].x * dl.x + p[u].y * dl.y + p[u].z * dl.z;
+        if (i < s.nvert && t > bd) { bd = t; best = i; }
+      }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -359,9 +368,20 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
   const v3 n = col(pmat, 2), nl = mulTv(mmat, n), pl = mulTv(mmat, ppos - mpos);
   const float pd = dot(pl, nl);
   float smax = -1e30f; int ia = 0x7fffffff;
-  for (int i = lane; i < nvert; i += 32) {
-    const float sup = pd - (vert[4 * i] * nl.x + vert[4 * i + 1] * nl.y + vert[4 * i + 2] * nl.z);
-    if (sup > smax) { smax = sup; ia = i; }
+  {
+    const float4* v4 = reinterpret_cast<const float4*>(vert);       // 4 loads in flight per lane, ascending index order per lane
+#pragma unroll 1
+    for (int i0 = lane; i0 < nvert; i0 += 128) {
+      float4 p[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) p[u] = __ldg(v4 + min(i0 + 32 * u, nvert - 1));
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int i = i0 + 32 * u;
+        const float sup = pd - (p[u].x * nl.x + p[u].y * nl.y + p[u].z * nl.z);
+        if (i < nvert && sup > smax) { smax = sup; ia = i; }
+      }
+    }
   }
   warp_argmax(smax, ia);
   if (ia == 0x7fffffff || -smax > margin) return 0;
