@@ -750,6 +750,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const M
   const int gw = blockIdx.x * B2S_WARPS_PER_CTA + (threadIdx.x >> 5), nwarp = gridDim.x * B2S_WARPS_PER_CTA;
   const int ntask = min(d.cvx_ntask[0], d.nworld * B2S_MAX_SURVIVORS);
   const bool use_axis = m.ngrid == 0;
+  EpaWork* wk = reinterpret_cast<EpaWork*>(b2s_smem) + (threadIdx.x >> 5);       // this warp's EPA polytope
   // tasks differ by two orders of magnitude (a cached separating plane: one support evaluation; a deep overlap: GJK + 24 EPA
   // rounds): warps pull the next task from a cursor instead of striding statically
   (void)gw; (void)nwarp;
@@ -770,7 +771,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const M
     A.coop = A.type == CVX_VERTS; B.coop = B.type == CVX_VERTS;
     CvxStage* out = reinterpret_cast<CvxStage*>(d.cvx_stage + ((size_t)w * B2S_MAX_SURVIVORS + i) * 8);
     float* axis = use_axis ? d.col_axis + ((size_t)w * m.npair + d.col_pidx[(size_t)w * B2S_MAX_SURVIVORS + i]) * 3 : nullptr;
-    const int nres = convex_pair_warp(out, margin, A, B, lane, axis);
+    const int nres = convex_pair_warp(out, margin, A, B, lane, axis, wk);
     __syncwarp();
     if (lane == 0) out->idx = nres;
     __syncwarp();
@@ -788,7 +789,7 @@ void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
   if (m.col_convex && m.col_defer) {      // broadphase + task emission, the GJK / EPA tasks over the whole machine, narrowphase + ordered append
     k_collision<8, true, 1><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
-    k_convex_tasks<<<148 * 4, 32 * B2S_WARPS_PER_CTA, 0, st>>>(m, d);
+    k_convex_tasks<<<148 * 4, 32 * B2S_WARPS_PER_CTA, B2S_WARPS_PER_CTA * sizeof(EpaWork), st>>>(m, d);
     k_collision<8, true, 2><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
     b2s_count_launch(); b2s_count_launch(); b2s_count_launch();
     return;

@@ -172,10 +172,16 @@ DEV void epa_make_face(EpaFace& f, const v3* V, int a, int b, int c) {
   f.n = mk3(n.x / len, n.y / len, n.z / len);
   f.d = dot(f.n, V[a]);
 }
-__device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const Simplex& s, CvxRes& out) {
-  v3 V[EPA_MAXV], VA[EPA_MAXV];
-  EpaFace F[EPA_MAXF];
-  unsigned char E[EPA_MAXF * 3][2];
+// polytope storage of one EPA run.  Per lane in local memory by default; warp-level callers (all 32 lanes run the SAME polytope
+// redundantly) pass one copy in shared memory instead: every lane stores the same value to the same address and reads it back
+// itself, so no synchronisation is needed and the 32 x 2.7 KB of local-memory traffic per warp disappear.
+struct EpaWork { v3 V[EPA_MAXV], VA[EPA_MAXV]; EpaFace F[EPA_MAXF]; unsigned char E[EPA_MAXF * 3][2]; };
+__device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const Simplex& s, CvxRes& out, EpaWork* wk = nullptr) {
+  EpaWork local_wk;
+  if (!wk) wk = &local_wk;
+  v3* const V = wk->V; v3* const VA = wk->VA;
+  EpaFace* const F = wk->F;
+  unsigned char (*const E)[2] = wk->E;
   int nv = 4, nf = 0;
   for (int i = 0; i < 4; i++) { V[i] = s.Y[i]; VA[i] = s.A[i]; }
   if (dot(cross(V[1] - V[0], V[2] - V[0]), V[3] - V[0]) > 0.f) {      // make (0,1,2) face away from vertex 3
@@ -244,7 +250,7 @@ __device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const S
 // the same bound (valid for ANY direction) that ends the GJK loop early, so the outcome is the one the full search would reach.
 // Otherwise the search runs exactly as without the cache (same start direction, same iterates).  The cache is refreshed
 // whenever the search proves separation and cleared when it finds a contact.
-__device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, CvxRes& out, float* axis = nullptr) {
+__device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, CvxRes& out, float* axis = nullptr, EpaWork* wk = nullptr) {
   Simplex s;
   if (axis) {
     const v3 vc = ld3(axis);
@@ -333,7 +339,7 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
       return true;
     }
   }
-  return epa_penetration(A, B, s, out);
+  return epa_penetration(A, B, s, out, wk);
 }
 
 // one contact between two convex geoms (cores + radii); normal from A to B.  Rc is the kernel's contact scratch type.
@@ -446,9 +452,9 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
 
 // one convex pair, every lane in the call: the hull scans are shared (Cvx::coop), the simplex / polytope logic runs
 // redundantly and identically on all lanes
-DEV int convex_pair_warp(CvxStage* out, float margin, const Cvx& A, const Cvx& B, int lane, float* axis = nullptr) {
+DEV int convex_pair_warp(CvxStage* out, float margin, const Cvx& A, const Cvx& B, int lane, float* axis = nullptr, EpaWork* wk = nullptr) {
   CvxRes r;
-  if (!gjk_epa(A, B, margin + A.radius + B.radius, r, axis)) return 0;
+  if (!gjk_epa(A, B, margin + A.radius + B.radius, r, axis, wk)) return 0;
   const float dist = r.dist - A.radius - B.radius;
   if (dist > margin) return 0;
   const v3 sa = r.pa + r.n * A.radius, sb = r.pb - r.n * B.radius;
