@@ -239,6 +239,11 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       case B2S_SENS_FRAMEANGVEL: case B2S_SENS_SUBTREECOM: case B2S_SENS_SUBTREELINVEL: case B2S_SENS_SUBTREEANGMOM: case B2S_SENS_CONTACT: break;
       case B2S_SENS_ACTUATORPOS: case B2S_SENS_ACTUATORVEL: case B2S_SENS_JOINTACTFRC: case B2S_SENS_FRAMEXAXIS: case B2S_SENS_FRAMEYAXIS:
       case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: case B2S_SENS_CLOCK: break;
+      case B2S_SENS_MAGNETOMETER: case B2S_SENS_E_POTENTIAL: case B2S_SENS_E_KINETIC: break;
+      case B2S_SENS_JOINTLIMITPOS: case B2S_SENS_JOINTLIMITVEL: case B2S_SENS_JOINTLIMITFRC:
+        if (s->sensor_objid[k] < 0 || s->sensor_objid[k] >= s->njnt) return fail("joint-limit sensor refers to an unknown joint");
+        break;
+      case B2S_SENS_TENDONACTFRC:
       case B2S_SENS_TENDONPOS: case B2S_SENS_TENDONVEL:
         if (s->sensor_objid[k] < 0 || s->sensor_objid[k] >= s->ntendon) return fail("tendon sensor refers to an unknown tendon");
         break;
@@ -404,7 +409,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   d.nlevel = nlevel; d.npair = (int)pairs.size() / 2; d.maxchain = maxchain; d.nchain = (int)chain.size();
   d.ref_root = nv > 0 ? s->body_rootid[s->dof_bodyid[0]] : 0;
   d.timestep = (float)s->opt_timestep;
-  for (int k = 0; k < 3; k++) d.gravity[k] = (float)s->opt_gravity[k];
+  for (int k = 0; k < 3; k++) { d.gravity[k] = (float)s->opt_gravity[k]; d.magnetic[k] = (float)s->opt_magnetic[k]; }
   d.tolerance = (float)s->opt_tolerance; d.ls_tolerance = (float)s->opt_ls_tolerance; d.impratio = (float)s->opt_impratio;
   d.ls_parallel_min_step = (float)(s->opt_ls_parallel_min_step > 0 ? s->opt_ls_parallel_min_step : 1e-6);
   d.meaninertia = (float)s->stat_meaninertia;

@@ -32,7 +32,7 @@ struct ModelDev {
   int nchain;                       // total length of body_chain (= body_chain_adr[nbody])
   int ref_root;                     // root body of the first kinematic tree: its subtree COM is the constraint reference point
   // options
-  float timestep, gravity[3], tolerance, ls_tolerance, impratio, ls_parallel_min_step, meaninertia;
+  float timestep, gravity[3], magnetic[3], tolerance, ls_tolerance, impratio, ls_parallel_min_step, meaninertia;
   int fric;                         // 1: the model can have friction-loss rows (dof_frictionloss > 0 somewhere, or the field is per-world)
   int integrator, cone, solver, iterations, ls_iterations, disableflags, ls_parallel, contact_sensor_maxmatch;
   // ---- bodies

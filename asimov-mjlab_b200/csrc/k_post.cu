@@ -248,6 +248,53 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
       case B2S_SENS_ACTUATORVEL: out[0] = d.actuator_velocity[(size_t)w * m.nu + id]; break;
       case B2S_SENS_JOINTACTFRC: out[0] = d.qfrc_actuator[(size_t)w * nv + m.jnt_dofadr[id]]; break;
       case B2S_SENS_CLOCK: out[0] = d.snap_time[w]; break;
+      case B2S_SENS_MAGNETOMETER: {
+        const Frame f = obj_frame(m, d, w, B2S_OBJ_SITE, id);
+        st3(out, mulTv(f.mat, mk3(m.magnetic[0], m.magnetic[1], m.magnetic[2])));
+      } break;
+      case B2S_SENS_JOINTLIMITPOS: case B2S_SENS_JOINTLIMITVEL: case B2S_SENS_JOINTLIMITFRC: {
+        // the joint's limit row if one is active (rows nf .. nl-1 are the limits)
+        const size_t row0 = (size_t)w * d.njmax;
+        float v = 0.f;
+        for (int r = d.nf[w]; r < d.nl[w]; r++)
+          if (d.efc_id[row0 + r] == id) {
+            v = type == B2S_SENS_JOINTLIMITPOS ? d.efc_pos[row0 + r] - d.efc_margin[row0 + r] : (type == B2S_SENS_JOINTLIMITVEL ? d.efc_vel[row0 + r] : d.efc_force[row0 + r]);
+            break;
+          }
+        out[0] = v;
+      } break;
+      case B2S_SENS_TENDONACTFRC: {
+        float f = 0.f;
+        for (int u = 0; u < m.nu; u++) if (m.actuator_trntype[u] == B2S_TRN_TENDON && m.actuator_trnid[u] == id) f += d.actuator_force[(size_t)w * m.nu + u];
+        out[0] = f;
+      } break;
+      case B2S_SENS_E_POTENTIAL: {
+        float e = 0.f;
+        const float* mass = m.body_mass.at(w);
+        if (grav) for (int i = 1; i < nb; i++) e -= mass[i] * (m.gravity[0] * xipos[3 * i] + m.gravity[1] * xipos[3 * i + 1] + m.gravity[2] * xipos[3 * i + 2]);
+        if (!(m.disableflags & B2S_DSBL_PASSIVE)) {
+          const float* stiff = m.jnt_stiffness.at(w);
+          const float* qspring = m.qpos_spring.at(w);
+          for (int j = 0; j < m.njnt; j++) {
+            const float k = stiff[j];
+            if (k == 0.f || (m.jnt_type[j] != B2S_JNT_HINGE && m.jnt_type[j] != B2S_JNT_SLIDE)) continue;
+            const float dq = d.snap_qpos[(size_t)w * m.nq + m.jnt_qposadr[j]] - qspring[m.jnt_qposadr[j]];
+            e += 0.5f * k * dq * dq;
+          }
+          for (int t = 0; t < m.ntendon; t++) {
+            const float k = m.tendon_stiffness[t], len = d.ten_length[(size_t)w * m.ntendon + t], lo = m.tendon_lengthspring[2 * t], hi = m.tendon_lengthspring[2 * t + 1];
+            const float dl = len > hi ? len - hi : (len < lo ? len - lo : 0.f);
+            e += 0.5f * k * dl * dl;
+          }
+        }
+        out[0] = e;
+      } break;
+      case B2S_SENS_E_KINETIC: {
+        const float* M = d.qM + (size_t)w * nv * m.nvp;
+        float e = 0.f;
+        for (int i = 0; i < nv; i++) { float r = 0.f; for (int j = 0; j < nv; j++) r += M[i * m.nvp + j] * qvel[j]; e += qvel[i] * r; }
+        out[0] = 0.5f * e;
+      } break;
       case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: {
         Frame f = obj_frame(m, d, w, ot, id);
         sv6 v = object_velocity(m, cvel, com, f.body, f.pos);

@@ -39,12 +39,14 @@ SENS = {"accelerometer": 1, "velocimeter": 2, "gyro": 3, "jointpos": 9, "jointve
         "actuatorpos": 13, "actuatorvel": 14, "actuatorfrc": 15, "jointactuatorfrc": 16,
         "framepos": 25, "framequat": 26, "framexaxis": 27, "frameyaxis": 28, "framezaxis": 29,
         "framelinvel": 30, "frameangvel": 31, "framelinacc": 32, "frameangacc": 33, "subtreecom": 34, "subtreelinvel": 35,
-        "subtreeangmom": 36, "contact": 42, "clock": 45}
+        "subtreeangmom": 36, "contact": 42, "clock": 45, "magnetometer": 6, "tendonactuatorfrc": 17,
+        "jointlimitpos": 20, "jointlimitvel": 21, "jointlimitfrc": 22, "e_potential": 43, "e_kinetic": 44}
 SENS_DIM = {"accelerometer": 3, "velocimeter": 3, "gyro": 3, "jointpos": 1, "jointvel": 1, "tendonpos": 1, "tendonvel": 1,
             "actuatorpos": 1, "actuatorvel": 1, "actuatorfrc": 1, "jointactuatorfrc": 1,
             "framepos": 3, "framequat": 4, "framexaxis": 3, "frameyaxis": 3, "framezaxis": 3,
             "framelinvel": 3, "frameangvel": 3, "framelinacc": 3, "frameangacc": 3, "subtreecom": 3, "subtreelinvel": 3,
-            "subtreeangmom": 3, "clock": 1}
+            "subtreeangmom": 3, "clock": 1, "magnetometer": 3, "tendonactuatorfrc": 1, "jointlimitpos": 1, "jointlimitvel": 1,
+            "jointlimitfrc": 1, "e_potential": 1, "e_kinetic": 1}
 CONTACT_FIELD_DIM = {0: 1, 1: 3, 2: 3, 3: 1, 4: 3, 5: 3, 6: 3}
 
 
@@ -410,6 +412,8 @@ class _Parser:
           spec.option[k] = opt.get(k).lower()
       if opt.get("gravity"):
         spec.option["gravity"] = _floats(opt.get("gravity"), 3)
+      if opt.get("magnetic"):
+        spec.option["magnetic"] = _floats(opt.get("magnetic"), 3)
     for d in root.findall("default"):
       self._parse_default(d, "main", top=True)
     for sec in root.findall("asset"):
@@ -595,13 +599,13 @@ class _Parser:
     if t not in SENS or t == "contact":
       raise NotImplementedError(f"sensor <{t}> is not supported")
     s = SensorSpec(name=el.get("name", ""), type=t, cutoff=float(el.get("cutoff", 0)))
-    if t in ("accelerometer", "velocimeter", "gyro"):
+    if t in ("accelerometer", "velocimeter", "gyro", "magnetometer"):
       s.objtype, s.objname = "site", el.get("site")
-    elif t in ("jointpos", "jointvel", "jointactuatorfrc"):
+    elif t in ("jointpos", "jointvel", "jointactuatorfrc", "jointlimitpos", "jointlimitvel", "jointlimitfrc"):
       s.objtype, s.objname = "joint", el.get("joint")
     elif t in ("actuatorpos", "actuatorvel", "actuatorfrc"):
       s.objtype, s.objname = "actuator", el.get("actuator")
-    elif t in ("tendonpos", "tendonvel"):
+    elif t in ("tendonpos", "tendonvel", "tendonactuatorfrc"):
       s.objtype, s.objname = "tendon", el.get("tendon")
     elif t.startswith("subtree"):
       s.objtype, s.objname = "body", el.get("body")
@@ -1073,6 +1077,7 @@ def _compile(spec: Spec) -> HostModel:
   m.exclude_signature = ((m.exclude_body1.astype(np.int64) << 16) + m.exclude_body2).astype(np.int32)
   o = spec.option
   m.opt.timestep = o["timestep"]; m.opt.gravity = np.array(o["gravity"], float)
+  m.opt.magnetic = np.array(o.get("magnetic", (0.0, -0.5, 0.0)), float)
   m.opt.integrator = {"euler": 0, "rk4": 1, "implicit": 2, "implicitfast": 3}[o["integrator"]]
   m.opt.cone = {"pyramidal": 0, "elliptic": 1}[o["cone"]]
   m.opt.solver = {"pgs": 0, "cg": 1, "newton": 2}[o["solver"]]

@@ -53,7 +53,9 @@ enum { B2S_SENS_ACCELEROMETER = 1, B2S_SENS_VELOCIMETER = 2, B2S_SENS_GYRO = 3,
        B2S_SENS_ACTUATORPOS = 13, B2S_SENS_ACTUATORVEL = 14, B2S_SENS_ACTUATORFRC = 15, B2S_SENS_JOINTACTFRC = 16,
        B2S_SENS_FRAMEPOS = 25, B2S_SENS_FRAMEQUAT = 26, B2S_SENS_FRAMEXAXIS = 27, B2S_SENS_FRAMEYAXIS = 28, B2S_SENS_FRAMEZAXIS = 29,
        B2S_SENS_FRAMELINVEL = 30, B2S_SENS_FRAMEANGVEL = 31, B2S_SENS_FRAMELINACC = 32, B2S_SENS_FRAMEANGACC = 33,
-       B2S_SENS_CLOCK = 45,
+       B2S_SENS_CLOCK = 45, B2S_SENS_MAGNETOMETER = 6, B2S_SENS_TENDONACTFRC = 17,
+       B2S_SENS_JOINTLIMITPOS = 20, B2S_SENS_JOINTLIMITVEL = 21, B2S_SENS_JOINTLIMITFRC = 22,
+       B2S_SENS_E_POTENTIAL = 43, B2S_SENS_E_KINETIC = 44,
        B2S_SENS_SUBTREECOM = 34, B2S_SENS_SUBTREELINVEL = 35, B2S_SENS_SUBTREEANGMOM = 36,
        B2S_SENS_CONTACT = 42 };
 /* contact-sensor data bits (intprm[0]) and reduce modes (intprm[1]);
@@ -91,6 +93,7 @@ typedef struct b2s_model_desc {
   /* options (MjModel.opt; reference MujocoCfg.apply, sim.py:64-76) */
   double opt_timestep;
   double opt_gravity[3];
+  double opt_magnetic[3];
   double opt_tolerance;
   double opt_ls_tolerance;
   double opt_impratio;

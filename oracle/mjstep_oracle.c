@@ -1538,6 +1538,48 @@ void orc_sensors(const b2s_model_desc* m, orc_data* d) {
       case B2S_SENS_ACTUATORVEL: out[0] = d->actuator_velocity[id]; break;
       case B2S_SENS_JOINTACTFRC: out[0] = d->qfrc_actuator[m->jnt_dofadr[id]]; break;
       case B2S_SENS_CLOCK: out[0] = d->time[0]; break;
+      case B2S_SENS_MAGNETOMETER: {      /* mj_sensorPos: the global field opt.magnetic in the site frame */
+        obj_frame(m, d, B2S_OBJ_SITE, id, &pos, &mat, &body);
+        for (int k = 0; k < 3; k++) out[k] = mat[k]*(real)m->opt_magnetic[0] + mat[3 + k]*(real)m->opt_magnetic[1] + mat[6 + k]*(real)m->opt_magnetic[2];
+      } break;
+      case B2S_SENS_JOINTLIMITPOS: case B2S_SENS_JOINTLIMITVEL: case B2S_SENS_JOINTLIMITFRC: {
+        /* the joint's limit row, if one is active: pos - margin (mj_sensorPos), its velocity (mj_sensorVel), its force (mj_sensorAcc) */
+        out[0] = 0;
+        for (int r = 0; r < d->nefc[0]; r++)
+          if (d->efc_type[r] == ORC_EFC_LIMIT && d->efc_id[r] == id) {
+            out[0] = type == B2S_SENS_JOINTLIMITPOS ? d->efc_pos[r] - d->efc_margin[r] : (type == B2S_SENS_JOINTLIMITVEL ? d->efc_vel[r] : d->efc_force[r]);
+            break;
+          }
+      } break;
+      case B2S_SENS_TENDONACTFRC: {      /* sum of the forces of the actuators that pull on this tendon */
+        real f = 0;
+        for (int u = 0; u < m->nu; u++) if (m->actuator_trntype[u] == B2S_TRN_TENDON && m->actuator_trnid[u] == id) f += d->actuator_force[u];
+        out[0] = f;
+      } break;
+      case B2S_SENS_E_POTENTIAL: {       /* mj_energyPos: gravity + joint springs (hinge / slide) + tendon springs outside their dead band */
+        real e = 0;
+        if (grav) for (int i = 1; i < nb; i++)
+          e -= (real)m->body_mass[i]*((real)m->opt_gravity[0]*d->xipos[3*i] + (real)m->opt_gravity[1]*d->xipos[3*i + 1] + (real)m->opt_gravity[2]*d->xipos[3*i + 2]);
+        if (!(m->opt_disableflags & B2S_DSBL_PASSIVE)) {
+          for (int j = 0; j < m->njnt; j++) {
+            real k = (real)m->jnt_stiffness[j];
+            if (k == 0 || (m->jnt_type[j] != B2S_JNT_HINGE && m->jnt_type[j] != B2S_JNT_SLIDE)) continue;
+            real dq = d->qpos[m->jnt_qposadr[j]] - (real)m->qpos_spring[m->jnt_qposadr[j]];
+            e += (real)0.5*k*dq*dq;
+          }
+          for (int t = 0; t < m->ntendon; t++) {
+            real k = (real)m->tendon_stiffness[t], len = d->ten_length[t], lo = (real)m->tendon_lengthspring[2*t], hi = (real)m->tendon_lengthspring[2*t + 1];
+            real dl = len > hi ? len - hi : (len < lo ? len - lo : 0);
+            e += (real)0.5*k*dl*dl;
+          }
+        }
+        out[0] = e;
+      } break;
+      case B2S_SENS_E_KINETIC: {         /* mj_energyVel: 1/2 v' M v */
+        real e = 0;
+        for (int i = 0; i < m->nv; i++) { real r = 0; for (int j = 0; j < m->nv; j++) r += d->qM[i*m->nv + j]*d->qvel[j]; e += d->qvel[i]*r; }
+        out[0] = (real)0.5*e;
+      } break;
       case B2S_SENS_SUBTREECOM: for (int k = 0; k < 3; k++) out[k] = d->subtree_com[3*id + k]; break;
       case B2S_SENS_SUBTREELINVEL: for (int k = 0; k < 3; k++) out[k] = d->subtree_linvel[3*id + k]; break;
       case B2S_SENS_SUBTREEANGMOM: for (int k = 0; k < 3; k++) out[k] = d->subtree_angmom[3*id + k]; break;

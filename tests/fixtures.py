@@ -311,6 +311,41 @@ SENSOR_ARM = """
 </mujoco>
 """
 
+# the remaining scalar sensors of mjlab's BuiltinSensorCfg list that need no ray casting / reaction forces: magnetometer, joint-limit
+# position / velocity / force, tendon actuator force, potential and kinetic energy (sensor/builtin_sensor.py:59-101)
+SENSOR_MISC = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.004" integrator="implicitfast" magnetic="0.2 -0.5 0.1"/>
+  <worldbody>
+    <body name="cart" pos="0 0 1">
+      <joint name="sl" type="slide" axis="0 0 1" stiffness="40" springref="0.1" range="-0.3 0.3" damping="0.5"/>
+      <geom type="box" size="0.1 0.1 0.1" mass="2.0" contype="0" conaffinity="0"/>
+      <body name="arm" pos="0 0 0.1">
+        <joint name="hg" type="hinge" axis="0 1 0" range="-0.5 0.6" damping="0.05" stiffness="3"/>
+        <geom type="capsule" fromto="0 0 0 0.3 0 0" size="0.03" mass="0.7" contype="0" conaffinity="0"/>
+        <site name="tip" pos="0.3 0 0" quat="0.9238795 0 0.3826834 0"/>
+      </body>
+    </body>
+  </worldbody>
+  <tendon>
+    <fixed name="tn" stiffness="15" springlength="-0.05 0.05"><joint joint="sl" coef="1.0"/><joint joint="hg" coef="0.3"/></fixed>
+  </tendon>
+  <actuator>
+    <position name="a1" tendon="tn" kp="20" kv="1"/>
+    <motor name="a2" tendon="tn" gear="2"/>
+    <motor name="a3" joint="hg"/>
+  </actuator>
+  <sensor>
+    <magnetometer name="mag" site="tip"/>
+    <jointlimitpos name="lp" joint="hg"/><jointlimitvel name="lv" joint="hg"/><jointlimitfrc name="lf" joint="hg"/>
+    <jointlimitpos name="lps" joint="sl"/><jointlimitfrc name="lfs" joint="sl"/>
+    <tendonactuatorfrc name="taf" tendon="tn"/>
+    <e_potential name="ep"/><e_kinetic name="ek"/>
+  </sensor>
+</mujoco>
+"""
+
 # Asimov-toe's ankle in miniature: a pitch/roll hinge pair under gravity driven by two fixed tendons with position
 # actuators (one clamped by ctrlrange / forcerange, one with a velocity gain), a sprung + damped third tendon with
 # a dead band, and a joint motor on the same dof (asimov_toe.xml:175-204).

@@ -576,7 +576,7 @@ def test_g1_friction_domain_randomisation_per_world(g1):
 
 
 @pytest.mark.parametrize("name", ["SPHERE_DROP", "FALLING_BOX", "PENDULUM", "SLIDER_PD", "SPINNER", "TWO_SPHERES",
-                                  "CAPSULE_ON_PLANE", "LIMITED_HINGE", "LEGGED", "SENSOR_ARM", "SLIDER_FRICTION"])
+                                  "CAPSULE_ON_PLANE", "LIMITED_HINGE", "LEGGED", "SENSOR_ARM", "SLIDER_FRICTION", "SENSOR_MISC"])
 def test_small_fixtures_rollout(name):
   """Every joint type, primitive pair and sensor of the small fixtures, 200 steps, both sides from the same seed."""
   import torch
@@ -586,6 +586,8 @@ def test_small_fixtures_rollout(name):
   qpos = np.tile(m.qpos0, (W, 1)); qvel = rng.normal(0, 0.3, (W, m.nv)); ctrl = rng.normal(0, 0.3, (W, m.nu))
   if name == "LIMITED_HINGE":
     qpos[:, 0] = [-0.35, 0.0, 0.39, 0.45]
+  if name == "SENSOR_MISC":      # hinge beyond / at / inside its limits, slider beyond its upper limit in one world
+    qpos[:, 1] = [0.7, -0.55, 0.2, 0.6]; qpos[:, 0] = [0.25, 0.0, 0.33, -0.1]
   if name in ("FALLING_BOX", "LEGGED", "SPHERE_DROP"):
     qpos[:, 2] += rng.uniform(-0.05, 0.05, W)
   engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=16, njmax=64)

@@ -610,3 +610,36 @@ def test_elliptic_cone_solution_properties(g1):
   assert abs(a) < 1e-3 and abs(w2["qvel"][0]) < 0.01
   a, w2 = slide(12.0)
   assert abs(a - (12.0 - 9.81)) < 0.1 * (12.0 - 9.81) + 0.1
+
+
+def test_misc_scalar_sensors_closed_forms():
+  """magnetometer / joint-limit / tendon-actuator-force / energy sensors (sensor/builtin_sensor.py:59-101) on SENSOR_MISC."""
+  import fixtures as fx
+  from oracle import Oracle
+  m = fx.compile_xml(fx.SENSOR_MISC)
+  assert m.nsensordata == 3 + 5 + 1 + 2
+  o = Oracle(m, "f64", 4, 16)
+  adr = {n: int(m.sensor_adr[m.name2id("sensor", n)]) for n in m.names["sensor"]}
+  # state: slider 0.25 (inside its range), hinge 0.7 (0.1 beyond its upper limit), some velocities, controls
+  w = o.new_world([0.25, 0.7], [0.3, 0.8], [0.05, 1.5, 0.0])
+  o.forward(w)
+  sd = w["sensordata"]
+  # magnetometer: B in the site frame; the site frame = hinge rotation (about y by 0.7) times the site's own 45 deg about y
+  ang = 0.7 + np.pi / 4
+  R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+  assert np.allclose(sd[adr["mag"]:adr["mag"] + 3], R.T @ np.array([0.2, -0.5, 0.1]), atol=1e-9)
+  # hinge upper limit active: pos - margin = hi - q = -0.1, velocity of the row = -qvel, force >= 0; the slider's limit is inactive
+  assert sd[adr["lp"]] == pytest.approx(0.6 - 0.7) and sd[adr["lv"]] == pytest.approx(-0.8) and sd[adr["lf"]] > 0.0
+  assert sd[adr["lps"]] == 0.0 and sd[adr["lfs"]] == 0.0
+  assert sd[adr["lf"]] == pytest.approx(float(w["efc_force"][0]))
+  # tendon actuators: position servo + motor (gear 2 enters the moment, not the actuator force)
+  L = 1.0 * 0.25 + 0.3 * 0.7; V = 1.0 * 0.3 + 0.3 * 0.8
+  f1 = 20.0 * (0.05 - L) - 1.0 * V; f2 = 1.5
+  assert sd[adr["taf"]] == pytest.approx(f1 + f2, rel=1e-9)
+  # energies
+  z_cart = 1.0 + 0.25
+  xi_arm = np.array([0.15 * np.cos(0.7), 0.0, z_cart + 0.1 - 0.15 * np.sin(0.7)])     # capsule COM 0.15 along the rotated x axis
+  ep = 9.81 * (2.0 * z_cart + 0.7 * xi_arm[2]) + 0.5 * 40.0 * (0.25 - 0.1) ** 2 + 0.5 * 3.0 * 0.7 ** 2 + 0.5 * 15.0 * (L - 0.05) ** 2
+  assert sd[adr["ep"]] == pytest.approx(ep, rel=1e-6)
+  qv = np.array([0.3, 0.8]); M = w["qM"].reshape(2, 2)
+  assert sd[adr["ek"]] == pytest.approx(0.5 * qv @ M @ qv, rel=1e-9) and sd[adr["ek"]] > 0.0
