@@ -31,6 +31,7 @@ WORKLOADS = {
   "go1_rough_hf": ("go1_rough_hf", "Go1 rough task with the generator's height-field sub-terrains enabled (terrains/config.py:28-53, commented out in the reference), random actions (BASELINE.json configs[2], hfield variant)"),
   "asimov_toe_full_flat": ("asimov_toe_full_flat", "Asimov-toe, FULL_COLLISION (11 link meshes by convex hull + 20 capsules, self collisions) on the plane, random actions"),
   "asimov_flat": ("asimov_flat", "Mjlab-Velocity-Flat-Asimov physics step (12-dof biped, all-mesh collision geometry: the two foot meshes on the plane, plane-mesh manifolds), random actions"),
+  "g1_flat_origins": ("g1_flat", "the G1-flat scene WITH the reference's per-env origin sites on the world body (terrain_importer.py:95,98-120; SURVEY.md §0 fact 10): num_envs static sites stored once, not per world (H3)"),
   "go1_rough": ("go1_rough", "Mjlab-Velocity-Rough-Unitree-Go1 physics step on the reference's default box terrain, random actions (BASELINE.json configs[2], box variant)"),
 }
 
@@ -113,9 +114,11 @@ class ClockSampler:
     return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def load_model(ls_parallel=1, workload="g1_flat", cone="pyramidal"):
+def load_model(ls_parallel=1, workload="g1_flat", cone="pyramidal", origin_sites=0):
   from asimov_mjlab_b200 import scenes
   m = scenes.load_asset(WORKLOADS[workload][0])
+  if origin_sites:
+    m = scenes.with_env_origin_sites(m, origin_sites)
   m.opt.ls_parallel = bool(ls_parallel)
   m.opt.cone = 1 if cone == "elliptic" else 0
   return m
@@ -233,7 +236,7 @@ class PhysBench:
     from asimov_mjlab_b200 import engine
     from asimov_mjlab_b200.sim import MujocoCfg, Simulation, SimulationCfg
     self.torch, self.engine, self.E, self.dev = torch, engine, E, dev
-    m = self.m = load_model(ls_parallel, workload, cone)
+    m = self.m = load_model(ls_parallel, workload, cone, origin_sites=E if workload.endswith("_origins") else 0)
     cfg = SimulationCfg(nconmax=50, njmax=300, ls_parallel=bool(ls_parallel),
                         mujoco=MujocoCfg(timestep=0.005, iterations=10, ls_iterations=20, cone=cone))
     sim = self.sim = Simulation(E, cfg, m, dev)
@@ -330,7 +333,7 @@ def extra_measurements(args, world, rank, dev, pb):
                    "unit": "physics sub-steps/s per GPU", "note": "robots driven by random joint targets stand for ~40 control steps (two loaded feet: ~50 constraint rows, ~5.4 Newton iterations), then lie on the ground (~15 rows, ~3.3 iterations)"}
   if rank == 0 and world == 1:
     wl = {}
-    for name in ("go1_rough", "go1_rough_hf", "asimov_flat", "asimov_toe_flat", "asimov_toe_full_flat"):
+    for name in ("g1_flat_origins", "go1_rough", "go1_rough_hf", "asimov_flat", "asimov_toe_flat", "asimov_toe_full_flat"):
       try:
         p2 = PhysBench(name, args.envs, dev, rank, args.ls_parallel)
         ms, _ = p2.timed(40, 5)
@@ -458,7 +461,8 @@ def run_b200(args):
   e2e_value = world * E * DECIMATION * e2e_steps / (ms_e2e * 1e-3)
   peak, peak_src = measured_peak()
   per_gpu_substep_s = (ms * 1e-3) / (args.steps * DECIMATION)
-  ab = ALG_BYTES_PER_SUBSTEP_WORLD if args.workload == "g1_flat" else alg_bytes(m, len(pb.foot))
+  # the per-env origin sites are static and stored once for all worlds: they add no per-world bytes
+  ab = ALG_BYTES_PER_SUBSTEP_WORLD if args.workload in ("g1_flat", "g1_flat_origins") else alg_bytes(m, len(pb.foot))
   achieved = E * ab / per_gpu_substep_s / 1e9
   tot = sum(stages.values())
   top = max(stages, key=stages.get)
