@@ -46,9 +46,9 @@ def alg_bytes(m, friction_geoms):
   w = m.nq + 3 * m.nv + 1 + m.nsensordata + (3 + 4 + 3 + 6) * nb + 12 * m.nsite
   return 4 * (r + w + 3 * friction_geoms)
 # DRAM traffic of one sub-step (7 stage kernels), dram__bytes_read.sum + dram__bytes_write.sum from the `ncu --set full`
-# capture profiles/step_r2a_metrics.txt (G1-flat, 4096 worlds, upright regime): 141.3 MB read + 4.9 MB written.  NOT measured
+# capture profiles/step_r2c_metrics.txt (G1-flat, 4096 worlds, upright regime): 141.2 MB read + 4.8 MB written.  NOT measured
 # live (ncu cannot run inside the timed region): the JSON names the file it comes from in `traffic_from_profile`.
-NCU_TRAFFIC = {("g1_flat", 4096): (146100000, "profiles/step_r2a_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step, upright regime)")}
+NCU_TRAFFIC = {("g1_flat", 4096): (146000000, "profiles/step_r2c_metrics.txt (ncu --set full, sum over the 7 stage kernels of one sub-step, upright regime)")}
 DECIMATION = 4
 RESET_PERIOD_STEPS = 250            # reset every 1000 sub-steps, forward() inside the timed region
 
