@@ -22,6 +22,7 @@ static int fail(const std::string& msg) { g_err = msg; return -1; }
 // legal before fail with "invalid argument".  Several Data objects of different models share the non-template stage kernels,
 // so the limit is only ever raised: the largest request per (device, function) is remembered here.
 #include <mutex>
+#include <nvtx3/nvToolsExt.h>
 static std::mutex g_smem_mu;
 static std::map<std::pair<int, const void*>, size_t> g_smem_max;
 int b2s_raise_smem(int device, const void* fn, size_t smem) {
@@ -240,6 +241,9 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       case B2S_SENS_ACTUATORPOS: case B2S_SENS_ACTUATORVEL: case B2S_SENS_JOINTACTFRC: case B2S_SENS_FRAMEXAXIS: case B2S_SENS_FRAMEYAXIS:
       case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: case B2S_SENS_CLOCK: break;
       case B2S_SENS_MAGNETOMETER: case B2S_SENS_E_POTENTIAL: case B2S_SENS_E_KINETIC: break;
+      case B2S_SENS_FORCE: case B2S_SENS_TORQUE:
+        if (s->sensor_objtype[k] != B2S_OBJ_SITE || s->sensor_objid[k] < 0 || s->sensor_objid[k] >= s->nsite) return fail("force / torque sensor needs a site");
+        break;
       case B2S_SENS_JOINTLIMITPOS: case B2S_SENS_JOINTLIMITVEL: case B2S_SENS_JOINTLIMITFRC:
         if (s->sensor_objid[k] < 0 || s->sensor_objid[k] >= s->njnt) return fail("joint-limit sensor refers to an unknown joint");
         break;
@@ -523,6 +527,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   for (int k = 0; k < s->nsensor; k++) {
     if (s->sensor_type[k] == B2S_SENS_SUBTREELINVEL || s->sensor_type[k] == B2S_SENS_SUBTREEANGMOM) d.need_subtreevel = 1;
     if (s->sensor_type[k] == B2S_SENS_CONTACT) d.need_concache = 1;
+    if (s->sensor_type[k] == B2S_SENS_FORCE || s->sensor_type[k] == B2S_SENS_TORQUE) d.need_concache = d.need_cfrc = 1;
   }
   // expandable (per-world capable) fields: leading dim 1 with world stride 0 until b2s_model_expand
   std::vector<double> rgba((size_t)4 * s->ngeom, 0.5);
@@ -871,31 +876,39 @@ extern "C" int64_t b2s_data_bytes(const b2s_data* d) { return d ? (int64_t)d->by
 // most of the machine idle at 4096 worlds (one warp per world, 18-40 % warps active), so the branches fill each other's
 // gaps.  The side stream is forked from and joined back into `st` with events: under stream capture this records a DAG
 // in the same graph, eagerly it is plain stream concurrency.  Results are identical to the serial order.
+// NVTX ranges around the passes and the stage launches (host-side markers: in a timeline they bracket the eager launches or
+// the graph capture).  Off unless B2S_NVTX=1 is set when the library is loaded.
+static const bool g_nvtx = [] { const char* e = getenv("B2S_NVTX"); return e && e[0] == '1'; }();
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { if (g_nvtx) nvtxRangePushA(name); }
+  ~NvtxRange() { if (g_nvtx) nvtxRangePop(); }
+};
 static void run_pass(const b2s_model* M, b2s_data* D, cudaStream_t st, bool integrate) {
   const ModelDev& m = M->dev; const DataDev& d = D->dev;
   const bool fork = M->overlap != 0;
-  launch_position(m, d, st);
+  NvtxRange pass(integrate ? "b2s step" : "b2s forward");
+  { NvtxRange r("position"); launch_position(m, d, st); }
   if (fork) {
     cudaEventRecord(D->ev_fork, st); cudaStreamWaitEvent(D->side, D->ev_fork, 0);
-    launch_collision(m, d, D->side);
+    { NvtxRange r("collision (side stream)"); launch_collision(m, d, D->side); }
     cudaEventRecord(D->ev_join, D->side);
-    launch_dynamics(m, d, st);
+    { NvtxRange r("dynamics"); launch_dynamics(m, d, st); }
     cudaStreamWaitEvent(st, D->ev_join, 0);
   } else {
-    launch_dynamics(m, d, st);
-    launch_collision(m, d, st);
+    { NvtxRange r("dynamics"); launch_dynamics(m, d, st); }
+    { NvtxRange r("collision"); launch_collision(m, d, st); }
   }
-  launch_constraint(m, d, st);
-  launch_solve(m, d, st);
+  { NvtxRange r("constraint"); launch_constraint(m, d, st); }
+  { NvtxRange r("solve"); launch_solve(m, d, st); }
   if (fork && integrate) {
     cudaEventRecord(D->ev_fork2, st); cudaStreamWaitEvent(D->side, D->ev_fork2, 0);
-    launch_sensors(m, d, D->side);
+    { NvtxRange r("sensors (side stream)"); launch_sensors(m, d, D->side); }
     cudaEventRecord(D->ev_join2, D->side);
-    launch_integrate(m, d, st);
+    { NvtxRange r("integrate"); launch_integrate(m, d, st); }
     cudaStreamWaitEvent(st, D->ev_join2, 0);
   } else {
-    launch_sensors(m, d, st);
-    if (integrate) launch_integrate(m, d, st);
+    { NvtxRange r("sensors"); launch_sensors(m, d, st); }
+    if (integrate) { NvtxRange r("integrate"); launch_integrate(m, d, st); }
   }
 }
 extern "C" int b2s_forward(const b2s_model* m, b2s_data* d, void* stream) {

@@ -148,21 +148,24 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
   }
 }
 
-// shared per warp: cacc 6nb | bvel 6nb | lm 3nb | am 3nb | slv 3nb | dof 6nv
+// shared per warp: cacc 6nb | bvel 6nb | lm 3nb | am 3nb | slv 3nb | dof 6nv | (force / torque sensors only) cfrc 6nb
+__host__ __device__ inline int sens_smem_floats(int nb, int nv, int need_cfrc) { return 21 * nb + 6 * nv + (need_cfrc ? 6 * nb : 0); }
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;
   const int nb = m.nbody, nv = m.nv;
-  float* s_cacc = b2s_smem + (size_t)warp * (21 * nb + 6 * nv);
+  const int wfl = sens_smem_floats(nb, nv, m.need_cfrc);
+  float* s_cacc = b2s_smem + (size_t)warp * wfl;
   float* s_bvel = s_cacc + 6 * nb;
   float* s_lm = s_bvel + 6 * nb;
   float* s_am = s_lm + 3 * nb;
   float* s_slv = s_am + 3 * nb;
   float* s_dof = s_slv + 3 * nb;
+  float* s_cfi = s_dof + 6 * nv;
   const float* qvel = d.snap_qvel + (size_t)w * nv;     // the state this forward pass was computed from (see DataDev::snap_*)
   // contact cache (only when the model has contact sensors): per-warp [nconmax][4] ints then [nconmax][15] floats
-  int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * (21 * nb + 6 * nv)) + (size_t)warp * CC_WORDS * d.nconmax;
+  int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * wfl) + (size_t)warp * CC_WORDS * d.nconmax;
   float* s_cf = (float*)(s_ci + 4 * d.nconmax);
   const int ncon = m.need_concache ? d.ncon[w] : 0;
   if (m.need_concache) fill_contact_cache(m, d, w, ncon, s_ci, s_cf, lane);
@@ -219,6 +222,39 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
       st3(d.subtree_angmom + ((size_t)w * nb + b) * 3, L);
     }
   }
+  if (m.need_cfrc) {
+    // force half of mj_rnePostConstraint: per body, inertial force cinert cacc + cvel x* (cinert cvel) minus the external
+    // wrenches on it (xfrc_applied at xipos; contact forces at the contact point, -f on geom1's body and +f on geom2's), as
+    // spatial forces [torque, force] about the subtree COM of the body's root.  A sensor sums its body's subtree.
+    __syncwarp();
+    for (int b = lane; b < nb; b += 32) {
+      sv6 f = zero6();
+      if (b > 0) {
+        const float* I = d.cinert + ((size_t)w * nb + b) * 10;
+        const sv6 v = ld6(cvel + 6 * b);
+        f = mul_inert(I, ld6(s_cacc + 6 * b));
+        axpy6(f, 1.0f, cross_force(v, mul_inert(I, v)));
+        const v3 cr = ld3(com + 3 * m.body_rootid[b]);
+        const float* x = d.xfrc_applied + ((size_t)w * nb + b) * 6;
+        const v3 frc = ld3(x), trq = ld3(x + 3);
+        if (frc.x != 0.f || frc.y != 0.f || frc.z != 0.f || trq.x != 0.f || trq.y != 0.f || trq.z != 0.f) {
+          const v3 t = trq - cross(cr - ld3(xipos + 3 * b), frc);
+          f.v[0] -= t.x; f.v[1] -= t.y; f.v[2] -= t.z; f.v[3] -= frc.x; f.v[4] -= frc.y; f.v[5] -= frc.z;
+        }
+        for (int c = 0; c < ncon; c++) {
+          const int b1 = s_ci[4 * c + 2], b2 = s_ci[4 * c + 3];
+          if (b1 != b && b2 != b) continue;
+          if (d.con_efc_address[(size_t)w * d.nconmax + c] < 0) continue;
+          const float* cf = s_cf + 15 * c;
+          const v3 fw = ld3(cf + 6), tw = ld3(cf + 9);
+          const v3 t = tw - cross(cr - ld3(cf + 12), fw);
+          const float sg = (b2 == b ? 1.f : 0.f) - (b1 == b ? 1.f : 0.f);
+          f.v[0] -= sg * t.x; f.v[1] -= sg * t.y; f.v[2] -= sg * t.z; f.v[3] -= sg * fw.x; f.v[4] -= sg * fw.y; f.v[5] -= sg * fw.z;
+        }
+      }
+      st6(s_cfi + 6 * b, f);
+    }
+  }
   __syncwarp();
   // one lane per sensor
   for (int s = lane; s < m.nsensor; s += 32) {
@@ -238,6 +274,16 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
           v3 alin = mk3(ca[3], ca[4], ca[5]) + cross(aang, f.pos - ld3(com + 3 * m.body_rootid[f.body]));
           st3(out, mulTv(f.mat, alin) + cross(wl, vl));
         }
+      } break;
+      case B2S_SENS_FORCE: case B2S_SENS_TORQUE: {
+        // interaction force between the site's body and its parent (cfrc_int = sum over the body's subtree), moved from
+        // the root's subtree COM to the site and expressed in the site frame
+        Frame f = obj_frame(m, d, w, B2S_OBJ_SITE, id);
+        sv6 ci = zero6();
+        for (int j = f.body; j < m.body_subtree_end[f.body]; j++) axpy6(ci, 1.0f, ld6(s_cfi + 6 * j));
+        const v3 frc = mk3(ci.v[3], ci.v[4], ci.v[5]);
+        const v3 trq = mk3(ci.v[0], ci.v[1], ci.v[2]) - cross(f.pos - ld3(com + 3 * m.body_rootid[f.body]), frc);
+        st3(out, mulTv(f.mat, type == B2S_SENS_FORCE ? frc : trq));
       } break;
       case B2S_SENS_JOINTPOS: out[0] = d.snap_qpos[(size_t)w * m.nq + m.jnt_qposadr[id]]; break;
       case B2S_SENS_JOINTVEL: out[0] = qvel[m.jnt_dofadr[id]]; break;
@@ -508,7 +554,7 @@ void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   b2s_count_launch();
 }
 size_t smem_sensors(const ModelDev& m, const DataDev& d) {
-  return (size_t)B2S_WARPS_PER_CTA * (21 * m.nbody + 6 * m.nv + (m.need_concache ? CC_WORDS * d.nconmax : 0)) * sizeof(float);
+  return (size_t)B2S_WARPS_PER_CTA * (sens_smem_floats(m.nbody, m.nv, m.need_cfrc) + (m.need_concache ? CC_WORDS * d.nconmax : 0)) * sizeof(float);
 }
 size_t smem_integrate(const ModelDev& m) {
   const int T = b2s_tile_for(m.nv);

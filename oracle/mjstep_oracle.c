@@ -1499,6 +1499,51 @@ void orc_sensors(const b2s_model_desc* m, orc_data* d) {
   for (int s = 0; s < m->nsensor; s++)
     if (m->sensor_type[s] == B2S_SENS_SUBTREELINVEL || m->sensor_type[s] == B2S_SENS_SUBTREEANGMOM) need_sub = 1;
   if (need_sub) subtree_vel(m, d);
+  /* mj_rnePostConstraint, force part (only when a force / torque sensor asks for it): cfrc_ext from xfrc_applied and the
+     contact forces, cfrc_int = cinert cacc + cvel x* (cinert cvel) - cfrc_ext, summed from the leaves to the root.  Spatial
+     vectors are [torque, force] about the subtree COM of the body's root, world orientation. */
+  real* cfrc_int = NULL;
+  for (int s = 0; s < m->nsensor; s++)
+    if (m->sensor_type[s] == B2S_SENS_FORCE || m->sensor_type[s] == B2S_SENS_TORQUE) need_sub |= 2;
+  if (need_sub & 2) {
+    cfrc_int = (real*)malloc(sizeof(real)*12*nb);
+    real* cfrc_ext = cfrc_int + 6*nb;
+    for (int k = 0; k < 12*nb; k++) cfrc_int[k] = 0;
+    for (int b = 1; b < nb; b++) {
+      const real* x = d->xfrc_applied + 6*b;
+      if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
+      real dif[3], cr[3];
+      for (int k = 0; k < 3; k++) dif[k] = d->subtree_com[3*m->body_rootid[b] + k] - d->xipos[3*b + k];
+      cross3(cr, dif, x);
+      for (int k = 0; k < 3; k++) { cfrc_ext[6*b + k] += x[3 + k] - cr[k]; cfrc_ext[6*b + 3 + k] += x[k]; }
+    }
+    for (int c = 0; c < d->ncon[0]; c++) {
+      if (d->con_efc_address[c] < 0) continue;
+      real f6[6], fw[3], tw[3];
+      contact_wrench(d, c, f6);
+      matT_vec(fw, d->con_frame + 9*c, f6);
+      matT_vec(tw, d->con_frame + 9*c, f6 + 3);
+      for (int side = 0; side < 2; side++) {
+        int b = m->geom_bodyid[d->con_geom[2*c + side]];
+        if (!b) continue;
+        real dif[3], cr[3], sg = side ? (real)1 : (real)-1;
+        for (int k = 0; k < 3; k++) dif[k] = d->subtree_com[3*m->body_rootid[b] + k] - d->con_pos[3*c + k];
+        cross3(cr, dif, fw);
+        for (int k = 0; k < 3; k++) { cfrc_ext[6*b + k] += sg*(tw[k] - cr[k]); cfrc_ext[6*b + 3 + k] += sg*fw[k]; }
+      }
+    }
+    for (int i = 1; i < nb; i++) {
+      real t0[6], t1[6], t2[6];
+      mul_inert_vec(t0, d->cinert + 10*i, d->cacc + 6*i);
+      mul_inert_vec(t1, d->cinert + 10*i, d->cvel + 6*i);
+      cross_force(t2, d->cvel + 6*i, t1);
+      for (int k = 0; k < 6; k++) cfrc_int[6*i + k] = t0[k] + t2[k] - cfrc_ext[6*i + k];
+    }
+    for (int i = nb - 1; i > 0; i--) {
+      int p = m->body_parentid[i];
+      if (p) for (int k = 0; k < 6; k++) cfrc_int[6*p + k] += cfrc_int[6*i + k];
+    }
+  }
   for (int s = 0; s < m->nsensor; s++) {
     int type = m->sensor_type[s], id = m->sensor_objid[s], ot = m->sensor_objtype[s], dim = m->sensor_dim[s];
     real* out = d->sensordata + m->sensor_adr[s];
@@ -1515,6 +1560,17 @@ void orc_sensors(const b2s_model_desc* m, orc_data* d) {
         object_velocity(m, d, body, pos, mat, v6);
         for (int k = 0; k < 3; k++) out[k] = v6[3 + k];
         break;
+      case B2S_SENS_FORCE: case B2S_SENS_TORQUE: {
+        /* interaction force between the site's body and its parent, moved to the site and expressed in its frame
+           (mju_transformSpatial with flg_force: the torque changes by -(newpos - oldpos) x force) */
+        obj_frame(m, d, B2S_OBJ_SITE, id, &pos, &mat, &body);
+        const real* ci = cfrc_int + 6*body;
+        real dif[3], cr[3], tq[3];
+        for (int k = 0; k < 3; k++) dif[k] = pos[k] - d->subtree_com[3*m->body_rootid[body] + k];
+        cross3(cr, dif, ci + 3);
+        for (int k = 0; k < 3; k++) tq[k] = ci[k] - cr[k];
+        matT_vec(out, mat, type == B2S_SENS_FORCE ? ci + 3 : tq);
+      } break;
       case B2S_SENS_ACCELEROMETER: {
         /* mj_objectAcceleration (local frame): cacc moved to the site + centripetal correction */
         obj_frame(m, d, B2S_OBJ_SITE, id, &pos, &mat, &body);
@@ -1699,6 +1755,7 @@ void orc_sensors(const b2s_model_desc* m, orc_data* d) {
     if (cut > 0 && type != B2S_SENS_CONTACT)
       for (int k = 0; k < dim; k++) out[k] = clipr(out[k], -cut, cut);
   }
+  free(cfrc_int);
 }
 
 /* -------------------------------------------------------------- integrate */

@@ -346,6 +346,49 @@ SENSOR_MISC = """
 </mujoco>
 """
 
+# force / torque sensors (sensor/builtin_sensor.py:59-101; MuJoCo's mj_rnePostConstraint cfrc_int): a mast on a horizontal slider
+# carrying a hinged boom (reaction forces through joints, a two-body subtree), and a free puck with a hinged lid resting on the
+# plane (contact forces enter cfrc_ext; the root of a free body transmits nothing)
+SENSOR_FORCE = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.004" integrator="implicitfast"/>
+  <worldbody>
+    <geom name="floor" type="plane" size="5 5 0.1"/>
+    <body name="mast" pos="0 0 1">
+      <joint name="sx" type="slide" axis="1 0 0" damping="0.2"/>
+      <geom type="box" size="0.1 0.1 0.1" mass="2.0" contype="0" conaffinity="0"/>
+      <site name="s_mast" pos="0.05 0.02 -0.03" quat="0.9238795 0 0.3826834 0"/>
+      <body name="boom" pos="0 0 0.1">
+        <joint name="hb" type="hinge" axis="0 1 0" damping="0.05"/>
+        <geom type="capsule" fromto="0 0 0 0.4 0 0" size="0.03" mass="0.7" contype="0" conaffinity="0"/>
+        <site name="s_boom" pos="0 0 0"/>
+      </body>
+    </body>
+    <body name="puck" pos="1 0 0.06">
+      <freejoint/>
+      <geom name="puck_g" type="box" size="0.1 0.1 0.05" mass="1.5"/>
+      <site name="s_puck" pos="0.02 0 0.01"/>
+      <body name="lid" pos="0 0 0.05">
+        <joint name="hl" type="hinge" axis="1 0 0" range="-0.2 1.2" damping="0.02"/>
+        <geom name="lid_g" type="capsule" fromto="0 0 0.03 0 0.25 0.03" size="0.03" mass="0.4"/>
+        <site name="s_lid" pos="0 0 0" quat="0.9659258 0.2588190 0 0"/>
+      </body>
+    </body>
+  </worldbody>
+  <actuator>
+    <motor name="mb" joint="hb"/>
+    <position name="pl" joint="hl" kp="5" kv="0.2"/>
+  </actuator>
+  <sensor>
+    <force name="f_mast" site="s_mast"/><torque name="t_mast" site="s_mast"/>
+    <force name="f_boom" site="s_boom"/><torque name="t_boom" site="s_boom"/>
+    <force name="f_puck" site="s_puck"/><torque name="t_puck" site="s_puck"/>
+    <force name="f_lid" site="s_lid"/><torque name="t_lid" site="s_lid" cutoff="0.5"/>
+  </sensor>
+</mujoco>
+"""
+
 # Asimov-toe's ankle in miniature: a pitch/roll hinge pair under gravity driven by two fixed tendons with position
 # actuators (one clamped by ctrlrange / forcerange, one with a velocity gain), a sprung + damped third tendon with
 # a dead band, and a joint motor on the same dof (asimov_toe.xml:175-204).

@@ -60,6 +60,43 @@ def test_xfrc_applied_on_several_bodies_matches_oracle(g1):
   assert torch.equal(D.qfrc_smooth, qfs0)
 
 
+def test_force_and_torque_sensors_with_contacts_and_wrenches_match_oracle():
+  """force / torque sensors (sensor/builtin_sensor.py:59-101): cfrc_int with contact forces and xfrc_applied in cfrc_ext, on the
+  SENSOR_FORCE fixture (joint reactions of a two-body arm; a free puck with a hinged lid on the plane) in 8 worlds."""
+  import torch
+  m = fx.compile_xml(fx.SENSOR_FORCE)
+  W = 8
+  rng = np.random.default_rng(3)
+  qpos = np.tile(m.qpos0, (W, 1)); qvel = rng.normal(0, 0.4, (W, m.nv)); ctrl = rng.normal(0, 0.5, (W, m.nu))
+  qpos[:, 1] = rng.uniform(-1.0, 1.0, W)                    # boom angle
+  qpos[:, 4] += rng.uniform(0.0, 0.05, W)                   # puck height: some worlds in flight, some in contact
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=16, njmax=64)
+  x = np.zeros((W, m.nbody, 6))
+  for k, b in enumerate(("mast", "boom", "lid")):
+    x[:, m.name2id("body", b), 0:3] = rng.uniform(-6.0, 6.0, (W, 3)); x[:, m.name2id("body", b), 3:6] = rng.uniform(-0.5, 0.5, (W, 3))
+  x[0] = 0.0
+  _push(D, worlds, "xfrc_applied", x)
+  adr = {n: int(m.sensor_adr[m.name2id("sensor", n)]) for n in m.names["sensor"]}
+  touched = 0
+  for chunk in (0, 1, 10, 60):
+    if chunk:
+      engine.step(M, D, chunk)
+      for w in worlds:
+        orc.step(w, chunk)
+    else:
+      engine.forward(M, D)
+      for w in worlds:
+        orc.forward(w)
+    torch.cuda.synchronize()
+    _check_counts(D, worlds)
+    sd = D.sensordata.cpu().numpy(); so = np.stack([w["sensordata"] for w in worlds])
+    assert np.abs(sd - so).max() < 2e-3 * (1 + np.abs(so).max()), chunk
+    # the free puck's root transmits nothing except the wrench applied to the lid... no: to ITS subtree the lid's wrench is external too
+    assert np.abs(sd[:, adr["f_puck"]:adr["f_puck"] + 3]).max() < 2e-3
+    touched += int((D.ncon > 0).sum())
+  assert touched > 0 and np.abs(so[:, adr["f_lid"]:adr["f_lid"] + 3]).max() > 0.5
+
+
 def test_external_force_translates_and_torque_rotates():
   """The reference's own acceptance test of the wrench inputs (tests/test_entity.py:245-272): +x force -> +x motion, z torque ->
   rotation primarily about z; on a free box far above the floor, and the closed form x = F/m t^2/2 for the semi-implicit steps."""

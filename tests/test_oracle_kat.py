@@ -643,3 +643,56 @@ def test_misc_scalar_sensors_closed_forms():
   assert sd[adr["ep"]] == pytest.approx(ep, rel=1e-6)
   qv = np.array([0.3, 0.8]); M = w["qM"].reshape(2, 2)
   assert sd[adr["ek"]] == pytest.approx(0.5 * qv @ M @ qv, rel=1e-9) and sd[adr["ek"]] > 0.0
+
+
+def test_force_and_torque_sensors_closed_forms():
+  """force / torque sensors (sensor/builtin_sensor.py:59-101) on SENSOR_FORCE: the interaction force between a body and its
+  parent, cfrc_int of mj_rnePostConstraint, at the site and in its frame."""
+  import fixtures as fx
+  from oracle import Oracle
+  m = fx.compile_xml(fx.SENSOR_FORCE)
+  assert m.nsensordata == 24
+  o = Oracle(m, "f64", 16, 64)
+  adr = {n: int(m.sensor_adr[m.name2id("sensor", n)]) for n in m.names["sensor"]}
+  g = 9.81
+  # (1) boom horizontal and held by the motor torque m g l/2: nothing accelerates; the slider carries no x force
+  q0 = np.array(m.qpos0, float)
+  w = o.new_world(q0, np.zeros(m.nv), [-0.7 * g * 0.2, 0.0])
+  o.forward(w)
+  sd = w["sensordata"]
+  assert np.abs(w["qacc"][:2]).max() < 1e-9
+  # boom: force = its weight (up), torque about the hinge = -(site - com) x F = (0, -m g l/2, 0), which is what the motor supplies
+  assert np.allclose(sd[adr["f_boom"]:adr["f_boom"] + 3], [0, 0, 0.7 * g], atol=1e-9)
+  assert np.allclose(sd[adr["t_boom"]:adr["t_boom"] + 3], [0, -0.7 * g * 0.2, 0], atol=1e-9)
+  # mast: carries both bodies; the site is rotated 45 deg about y and offset from the COM
+  R = np.array([[np.cos(np.pi / 4), 0, np.sin(np.pi / 4)], [0, 1, 0], [-np.sin(np.pi / 4), 0, np.cos(np.pi / 4)]])
+  F = np.array([0, 0, 2.7 * g])
+  assert np.allclose(sd[adr["f_mast"]:adr["f_mast"] + 3], R.T @ F, atol=1e-9)
+  site = np.array([0.05, 0.02, 0.97]); com = (2.0 * np.array([0, 0, 1.0]) + 0.7 * np.array([0.2, 0, 1.1])) / 2.7
+  assert np.allclose(sd[adr["t_mast"]:adr["t_mast"] + 3], R.T @ (-np.cross(site - com, F)), atol=1e-9)
+  # (2) an external force on the mast: the slider accelerates along x (no x reaction), the z part is taken off the joint load
+  w = o.new_world(q0, np.zeros(m.nv), [-0.7 * g * 0.2, 0.0])
+  xf = np.zeros((m.nbody, 6)); xf[m.name2id("body", "mast"), :3] = [3.0, 0.0, 4.0]
+  w["xfrc_applied"][:] = xf.reshape(-1)
+  o.forward(w)
+  Fm = R @ w["sensordata"][adr["f_mast"]:adr["f_mast"] + 3]
+  # (the site's quaternion has 7 digits in the XML: its matrix differs from the exact 45 degrees by 3e-8)
+  assert abs(Fm[2] - (2.7 * g - 4.0)) < 1e-5 and abs(Fm[1]) < 1e-9
+  # x: the slider transmits nothing along its axis: the subtree's inertial force sum(m a_x) equals the applied 3 N
+  assert abs(Fm[0]) < 1e-5 and abs(w["qacc"][0] - 3.0 / 2.7) < 1e-12
+  # (3) the puck is free: its root joint transmits nothing, whatever the contacts do (equation of motion) -- in flight and on the ground
+  w = o.new_world(q0, np.zeros(m.nv), [0.0, 0.3])
+  for n in (1, 60, 400):
+    o.step(w, n)
+    sd = w["sensordata"]
+    assert np.abs(sd[adr["f_puck"]:adr["f_puck"] + 3]).max() < 1e-6 and np.abs(sd[adr["t_puck"]:adr["t_puck"] + 3]).max() < 1e-6
+  assert w["ncon"][0] >= 4
+  # the lid at rest on its servo / limit: the hinge carries its weight (site frame rotated 30 deg about x)
+  c, s_ = np.cos(np.pi / 6), np.sin(np.pi / 6)
+  Rl = np.array([[1, 0, 0], [0, c, -s_], [0, s_, c]])
+  xq = w["xquat"].reshape(-1, 4)[m.name2id("body", "lid")]
+  from asimov_mjlab_b200.mjcf import quat2mat as quat_to_mat
+  Fl = quat_to_mat(xq) @ Rl @ sd[adr["f_lid"]:adr["f_lid"] + 3]
+  assert np.allclose(Fl, [0, 0, 0.4 * g], atol=2e-3)
+  # cutoff clamps the torque reading
+  assert np.abs(sd[adr["t_lid"]:adr["t_lid"] + 3]).max() <= 0.5 + 1e-12
