@@ -241,6 +241,11 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       case B2S_SENS_ACTUATORPOS: case B2S_SENS_ACTUATORVEL: case B2S_SENS_JOINTACTFRC: case B2S_SENS_FRAMEXAXIS: case B2S_SENS_FRAMEYAXIS:
       case B2S_SENS_FRAMELINACC: case B2S_SENS_FRAMEANGACC: case B2S_SENS_CLOCK: break;
       case B2S_SENS_MAGNETOMETER: case B2S_SENS_E_POTENTIAL: case B2S_SENS_E_KINETIC: break;
+      case B2S_SENS_RANGEFINDER:
+        if (s->sensor_objtype[k] != B2S_OBJ_SITE || s->sensor_objid[k] < 0 || s->sensor_objid[k] >= s->nsite) return fail("rangefinder needs a site");
+        for (int g = 0; g < s->ngeom; g++)
+          if (s->geom_type[g] == B2S_GEOM_MESH || s->geom_type[g] == B2S_GEOM_HFIELD) return fail("rangefinder: rays against mesh / height-field geoms are not implemented");
+        break;
       case B2S_SENS_FORCE: case B2S_SENS_TORQUE:
         if (s->sensor_objtype[k] != B2S_OBJ_SITE || s->sensor_objid[k] < 0 || s->sensor_objid[k] >= s->nsite) return fail("force / torque sensor needs a site");
         break;
@@ -528,6 +533,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     if (s->sensor_type[k] == B2S_SENS_SUBTREELINVEL || s->sensor_type[k] == B2S_SENS_SUBTREEANGMOM) d.need_subtreevel = 1;
     if (s->sensor_type[k] == B2S_SENS_CONTACT) d.need_concache = 1;
     if (s->sensor_type[k] == B2S_SENS_FORCE || s->sensor_type[k] == B2S_SENS_TORQUE) d.need_concache = d.need_cfrc = 1;
+    if (s->sensor_type[k] == B2S_SENS_RANGEFINDER) d.need_ray = 1;
   }
   // expandable (per-world capable) fields: leading dim 1 with world stride 0 until b2s_model_expand
   std::vector<double> rgba((size_t)4 * s->ngeom, 0.5);

@@ -94,6 +94,7 @@ struct ModelDev {
   const float *sensor_cutoff;
   int need_subtreevel;
   int need_concache;   // some sensor is a contact sensor: k_sensors stages the world's contacts in shared memory
+  int need_ray;        // some sensor is a rangefinder
   int need_cfrc;       // some sensor is a force / torque sensor: k_sensors runs the force half of rne_postconstraint (needs the contact cache)
 };
 

@@ -148,6 +148,80 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
   }
 }
 
+// ---------------------------------------------------------------------------------------------- rays (rangefinder)
+// Distance along a ray to the surface of one primitive geom, -1 without intersection (MuJoCo engine_ray.c mj_rayGeom [ext]:
+// the ray is taken into the geom frame; quadratics return the smaller non-negative root, so a ray that starts inside a solid
+// reports its exit point; planes only count from their front side and inside their rendered rectangle).
+DEV float ray_quad(float a, float b, float c) {
+  const float det = b * b - a * c;
+  if (det < B2S_MINVAL) return -1.f;
+  const float sq = sqrtf(det);
+  const float x0 = (-b - sq) / a, x1 = (-b + sq) / a;
+  return x0 >= 0.f ? x0 : (x1 >= 0.f ? x1 : -1.f);
+}
+DEV float ray_geom(int type, const float* size, v3 gpos, const m33& gmat, v3 pnt, v3 vec) {
+  const v3 p = mulTv(gmat, pnt - gpos), v = mulTv(gmat, vec);
+  float x = -1.f;
+  switch (type) {
+    case B2S_GEOM_PLANE: {
+      if (v.z > -B2S_MINVAL) return -1.f;
+      const float t = -p.z / v.z;
+      if (t < 0.f) return -1.f;
+      const float px = p.x + t * v.x, py = p.y + t * v.y;
+      if ((size[0] <= 0.f || fabsf(px) <= size[0]) && (size[1] <= 0.f || fabsf(py) <= size[1])) x = t;
+    } break;
+    case B2S_GEOM_SPHERE: x = ray_quad(dot(v, v), dot(v, p), dot(p, p) - size[0] * size[0]); break;
+    case B2S_GEOM_CAPSULE: {
+      const float r = size[0], h = size[1];
+      float t = ray_quad(v.x * v.x + v.y * v.y, v.x * p.x + v.y * p.y, p.x * p.x + p.y * p.y - r * r);
+      if (t >= 0.f && fabsf(p.z + t * v.z) <= h) x = t;
+#pragma unroll
+      for (int side = -1; side <= 1; side += 2) {
+        const v3 q = mk3(p.x, p.y, p.z - side * h);
+        t = ray_quad(dot(v, v), dot(v, q), dot(q, q) - r * r);
+        if (t >= 0.f && (x < 0.f || t < x) && side * (p.z + t * v.z) >= h) x = t;
+      }
+    } break;
+    case B2S_GEOM_ELLIPSOID: {
+      const float s0 = 1.f / (size[0] * size[0]), s1 = 1.f / (size[1] * size[1]), s2 = 1.f / (size[2] * size[2]);
+      x = ray_quad(s0 * v.x * v.x + s1 * v.y * v.y + s2 * v.z * v.z, s0 * p.x * v.x + s1 * p.y * v.y + s2 * p.z * v.z,
+                   s0 * p.x * p.x + s1 * p.y * p.y + s2 * p.z * p.z - 1.f);
+    } break;
+    case B2S_GEOM_CYLINDER: {
+      const float r = size[0], h = size[1];
+      if (fabsf(v.z) > B2S_MINVAL) {
+#pragma unroll
+        for (int side = -1; side <= 1; side += 2) {
+          const float t = (side * h - p.z) / v.z;
+          if (t >= 0.f && (x < 0.f || t < x)) {
+            const float px = p.x + t * v.x, py = p.y + t * v.y;
+            if (px * px + py * py <= r * r) x = t;
+          }
+        }
+      }
+      const float t = ray_quad(v.x * v.x + v.y * v.y, v.x * p.x + v.y * p.y, p.x * p.x + p.y * p.y - r * r);
+      if (t >= 0.f && (x < 0.f || t < x) && fabsf(p.z + t * v.z) <= h) x = t;
+    } break;
+    case B2S_GEOM_BOX: {
+      const float pp[3] = {p.x, p.y, p.z}, vv[3] = {v.x, v.y, v.z};
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        if (fabsf(vv[i]) <= B2S_MINVAL) continue;
+#pragma unroll
+        for (int side = -1; side <= 1; side += 2) {
+          const float t = (side * size[i] - pp[i]) / vv[i];
+          if (t >= 0.f && (x < 0.f || t < x)) {
+            const int j = (i + 1) % 3, k = (i + 2) % 3;
+            if (fabsf(pp[j] + t * vv[j]) <= size[j] && fabsf(pp[k] + t * vv[k]) <= size[k]) x = t;
+          }
+        }
+      }
+    } break;
+    default: break;
+  }
+  return x;
+}
+
 // shared per warp: cacc 6nb | bvel 6nb | lm 3nb | am 3nb | slv 3nb | dof 6nv | (force / torque sensors only) cfrc 6nb
 __host__ __device__ inline int sens_smem_floats(int nb, int nv, int need_cfrc) { return 21 * nb + 6 * nv + (need_cfrc ? 6 * nb : 0); }
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelDev m, const DataDev d) {
@@ -375,11 +449,37 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
         sv6 v = object_velocity(m, cvel, com, f.body, f.pos);
         if (type == B2S_SENS_FRAMELINVEL) st3(out, mk3(v.v[3], v.v[4], v.v[5])); else st3(out, mk3(v.v[0], v.v[1], v.v[2]));
       } break;
+      case B2S_SENS_RANGEFINDER: break;      // written by the warp-wide ray pass below
       case B2S_SENS_CONTACT: { ConCache cc; cc.i = s_ci; cc.f = s_cf; contact_sensor(m, d, w, s, out, ncon, cc); } break;
       default: for (int k = 0; k < dim; k++) out[k] = 0.f;
     }
     const float cut = m.sensor_cutoff[s];
-    if (cut > 0.f && type != B2S_SENS_CONTACT) for (int k = 0; k < dim; k++) out[k] = clampf(out[k], -cut, cut);
+    if (cut > 0.f && type != B2S_SENS_CONTACT && type != B2S_SENS_RANGEFINDER) for (int k = 0; k < dim; k++) out[k] = clampf(out[k], -cut, cut);
+  }
+  if (m.need_ray) {
+    // rangefinders (mj_ray from the site along its z axis; geoms of the site's own body are skipped): the warp scans the geoms
+    // together, nearest hit by a min-reduction; -1 without a hit; a cutoff caps hits only (MuJoCo's "positive" data type)
+    const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
+    const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
+    for (int s = 0; s < m.nsensor; s++) {
+      if (m.sensor_type[s] != B2S_SENS_RANGEFINDER) continue;
+      const Frame f = obj_frame(m, d, w, B2S_OBJ_SITE, m.sensor_objid[s]);
+      const v3 dir = mk3(f.mat.m[2], f.mat.m[5], f.mat.m[8]);
+      float best = 3.0e38f;
+      for (int g = lane; g < m.ngeom; g += 32) {
+        if (m.geom_bodyid[g] == f.body) continue;
+        const float x = ray_geom(m.geom_type[g], m.geom_size + 3 * g, ld3(gx + 3 * g), ldm(gm + 9 * g), f.pos, dir);
+        if (x >= 0.f && x < best) best = x;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) best = fminf(best, __shfl_xor_sync(FULL, best, o));
+      if (lane == 0) {
+        float r = best < 1.0e38f ? best : -1.f;
+        const float cut = m.sensor_cutoff[s];
+        if (cut > 0.f && r > cut) r = cut;
+        d.sensordata[(size_t)w * m.nsensordata + m.sensor_adr[s]] = r;
+      }
+    }
   }
 }
 

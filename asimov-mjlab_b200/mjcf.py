@@ -40,13 +40,13 @@ SENS = {"accelerometer": 1, "velocimeter": 2, "gyro": 3, "jointpos": 9, "jointve
         "framepos": 25, "framequat": 26, "framexaxis": 27, "frameyaxis": 28, "framezaxis": 29,
         "framelinvel": 30, "frameangvel": 31, "framelinacc": 32, "frameangacc": 33, "subtreecom": 34, "subtreelinvel": 35,
         "subtreeangmom": 36, "contact": 42, "clock": 45, "magnetometer": 6, "tendonactuatorfrc": 17,
-        "jointlimitpos": 20, "jointlimitvel": 21, "jointlimitfrc": 22, "e_potential": 43, "e_kinetic": 44, "force": 4, "torque": 5}
+        "jointlimitpos": 20, "jointlimitvel": 21, "jointlimitfrc": 22, "e_potential": 43, "e_kinetic": 44, "force": 4, "torque": 5, "rangefinder": 7}
 SENS_DIM = {"accelerometer": 3, "velocimeter": 3, "gyro": 3, "jointpos": 1, "jointvel": 1, "tendonpos": 1, "tendonvel": 1,
             "actuatorpos": 1, "actuatorvel": 1, "actuatorfrc": 1, "jointactuatorfrc": 1,
             "framepos": 3, "framequat": 4, "framexaxis": 3, "frameyaxis": 3, "framezaxis": 3,
             "framelinvel": 3, "frameangvel": 3, "framelinacc": 3, "frameangacc": 3, "subtreecom": 3, "subtreelinvel": 3,
             "subtreeangmom": 3, "clock": 1, "magnetometer": 3, "tendonactuatorfrc": 1, "jointlimitpos": 1, "jointlimitvel": 1,
-            "jointlimitfrc": 1, "e_potential": 1, "e_kinetic": 1, "force": 3, "torque": 3}
+            "jointlimitfrc": 1, "e_potential": 1, "e_kinetic": 1, "force": 3, "torque": 3, "rangefinder": 1}
 CONTACT_FIELD_DIM = {0: 1, 1: 3, 2: 3, 3: 1, 4: 3, 5: 3, 6: 3}
 
 
@@ -599,7 +599,7 @@ class _Parser:
     if t not in SENS or t == "contact":
       raise NotImplementedError(f"sensor <{t}> is not supported")
     s = SensorSpec(name=el.get("name", ""), type=t, cutoff=float(el.get("cutoff", 0)))
-    if t in ("accelerometer", "velocimeter", "gyro", "magnetometer", "force", "torque"):
+    if t in ("accelerometer", "velocimeter", "gyro", "magnetometer", "force", "torque", "rangefinder"):
       s.objtype, s.objname = "site", el.get("site")
     elif t in ("jointpos", "jointvel", "jointactuatorfrc", "jointlimitpos", "jointlimitvel", "jointlimitfrc"):
       s.objtype, s.objname = "joint", el.get("joint")

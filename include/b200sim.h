@@ -55,7 +55,7 @@ enum { B2S_SENS_ACCELEROMETER = 1, B2S_SENS_VELOCIMETER = 2, B2S_SENS_GYRO = 3,
        B2S_SENS_FRAMELINVEL = 30, B2S_SENS_FRAMEANGVEL = 31, B2S_SENS_FRAMELINACC = 32, B2S_SENS_FRAMEANGACC = 33,
        B2S_SENS_CLOCK = 45, B2S_SENS_MAGNETOMETER = 6, B2S_SENS_TENDONACTFRC = 17,
        B2S_SENS_JOINTLIMITPOS = 20, B2S_SENS_JOINTLIMITVEL = 21, B2S_SENS_JOINTLIMITFRC = 22,
-       B2S_SENS_E_POTENTIAL = 43, B2S_SENS_E_KINETIC = 44, B2S_SENS_FORCE = 4, B2S_SENS_TORQUE = 5,
+       B2S_SENS_E_POTENTIAL = 43, B2S_SENS_E_KINETIC = 44, B2S_SENS_FORCE = 4, B2S_SENS_TORQUE = 5, B2S_SENS_RANGEFINDER = 7,
        B2S_SENS_SUBTREECOM = 34, B2S_SENS_SUBTREELINVEL = 35, B2S_SENS_SUBTREEANGMOM = 36,
        B2S_SENS_CONTACT = 42 };
 /* contact-sensor data bits (intprm[0]) and reduce modes (intprm[1]);

@@ -1482,6 +1482,76 @@ static void mat2quat_(real* q, const real* R) {
   normalize4(q);
 }
 
+/* engine_ray.c [ext]: distance along the ray (pnt, vec) to one primitive geom, -1 if none.  The ray is moved into the geom
+   frame; ray_quad returns the smaller non-negative root of a x^2 + 2 b x + c = 0. */
+static real ray_quad(real a, real b, real c) {
+  real det = b*b - a*c;
+  if (det < MINVAL) return -1;
+  real sq = (real)sqrt((double)det);
+  real x0 = (-b - sq)/a, x1 = (-b + sq)/a;
+  if (x0 >= 0) return x0;
+  if (x1 >= 0) return x1;
+  return -1;
+}
+static real ray_geom(int type, const double* size, const real* gpos, const real* gmat, const real* pnt, const real* vec) {
+  real dif[3], p[3], v[3], x = -1, t;
+  for (int k = 0; k < 3; k++) dif[k] = pnt[k] - gpos[k];
+  matT_vec(p, gmat, dif); matT_vec(v, gmat, vec);
+  real r = (real)size[0], h = (real)size[1];
+  switch (type) {
+    case B2S_GEOM_PLANE:
+      if (v[2] > -MINVAL) return -1;
+      t = -p[2]/v[2];
+      if (t < 0) return -1;
+      if ((size[0] <= 0 || fabs((double)(p[0] + t*v[0])) <= size[0]) && (size[1] <= 0 || fabs((double)(p[1] + t*v[1])) <= size[1])) x = t;
+      break;
+    case B2S_GEOM_SPHERE:
+      x = ray_quad(dot3(v, v), dot3(v, p), dot3(p, p) - r*r);
+      break;
+    case B2S_GEOM_CAPSULE:
+      t = ray_quad(v[0]*v[0] + v[1]*v[1], v[0]*p[0] + v[1]*p[1], p[0]*p[0] + p[1]*p[1] - r*r);
+      if (t >= 0 && fabs((double)(p[2] + t*v[2])) <= h) x = t;
+      for (int side = -1; side <= 1; side += 2) {
+        real q[3] = {p[0], p[1], p[2] - side*h};
+        t = ray_quad(dot3(v, v), dot3(v, q), dot3(q, q) - r*r);
+        if (t >= 0 && (x < 0 || t < x) && side*(p[2] + t*v[2]) >= h) x = t;
+      }
+      break;
+    case B2S_GEOM_ELLIPSOID: {
+      real s[3];
+      for (int k = 0; k < 3; k++) s[k] = (real)(1.0/(size[k]*size[k]));
+      x = ray_quad(s[0]*v[0]*v[0] + s[1]*v[1]*v[1] + s[2]*v[2]*v[2], s[0]*p[0]*v[0] + s[1]*p[1]*v[1] + s[2]*p[2]*v[2],
+                   s[0]*p[0]*p[0] + s[1]*p[1]*p[1] + s[2]*p[2]*p[2] - 1);
+    } break;
+    case B2S_GEOM_CYLINDER:
+      if (fabs((double)v[2]) > MINVAL)
+        for (int side = -1; side <= 1; side += 2) {
+          t = (side*h - p[2])/v[2];
+          if (t >= 0 && (x < 0 || t < x)) {
+            real px = p[0] + t*v[0], py = p[1] + t*v[1];
+            if (px*px + py*py <= r*r) x = t;
+          }
+        }
+      t = ray_quad(v[0]*v[0] + v[1]*v[1], v[0]*p[0] + v[1]*p[1], p[0]*p[0] + p[1]*p[1] - r*r);
+      if (t >= 0 && (x < 0 || t < x) && fabs((double)(p[2] + t*v[2])) <= h) x = t;
+      break;
+    case B2S_GEOM_BOX:
+      for (int i = 0; i < 3; i++) {
+        if (fabs((double)v[i]) <= MINVAL) continue;
+        for (int side = -1; side <= 1; side += 2) {
+          t = (side*(real)size[i] - p[i])/v[i];
+          if (t >= 0 && (x < 0 || t < x)) {
+            int j = (i + 1)%3, k = (i + 2)%3;
+            if (fabs((double)(p[j] + t*v[j])) <= size[j] && fabs((double)(p[k] + t*v[k])) <= size[k]) x = t;
+          }
+        }
+      }
+      break;
+    default: break;
+  }
+  return x;
+}
+
 void orc_sensors(const b2s_model_desc* m, orc_data* d) {
   int nb = m->nbody;
   /* mj_rnePostConstraint, acceleration part only: cacc with the solved qacc */
@@ -1560,6 +1630,17 @@ void orc_sensors(const b2s_model_desc* m, orc_data* d) {
         object_velocity(m, d, body, pos, mat, v6);
         for (int k = 0; k < 3; k++) out[k] = v6[3 + k];
         break;
+      case B2S_SENS_RANGEFINDER: {
+        /* mj_ray from the site along its z axis, geoms of the site's own body excluded; -1 without a hit */
+        obj_frame(m, d, B2S_OBJ_SITE, id, &pos, &mat, &body);
+        real dir[3] = {mat[2], mat[5], mat[8]}, best = -1;
+        for (int g = 0; g < m->ngeom; g++) {
+          if (m->geom_bodyid[g] == body) continue;
+          real x = ray_geom(m->geom_type[g], m->geom_size + 3*g, d->geom_xpos + 3*g, d->geom_xmat + 9*g, pos, dir);
+          if (x >= 0 && (best < 0 || x < best)) best = x;
+        }
+        out[0] = best;
+      } break;
       case B2S_SENS_FORCE: case B2S_SENS_TORQUE: {
         /* interaction force between the site's body and its parent, moved to the site and expressed in its frame
            (mju_transformSpatial with flg_force: the torque changes by -(newpos - oldpos) x force) */
@@ -1752,7 +1833,8 @@ void orc_sensors(const b2s_model_desc* m, orc_data* d) {
       default: for (int k = 0; k < dim; k++) out[k] = 0;
     }
     real cut = (real)m->sensor_cutoff[s];
-    if (cut > 0 && type != B2S_SENS_CONTACT)
+    if (cut > 0 && type == B2S_SENS_RANGEFINDER) { if (out[0] > cut) out[0] = cut; }      /* "positive" data type: caps hits only */
+    else if (cut > 0 && type != B2S_SENS_CONTACT)
       for (int k = 0; k < dim; k++) out[k] = clipr(out[k], -cut, cut);
   }
   free(cfrc_int);

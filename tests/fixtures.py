@@ -389,6 +389,42 @@ SENSOR_FORCE = """
 </mujoco>
 """
 
+# rangefinder (sensor/builtin_sensor.py:59-101; MuJoCo mj_ray along the site's z axis): a free "drone" with six sites looking along
+# -z, +x, -x, +y, -y, +z at one primitive of each kind, and a free capsule that falls through the +x ray
+SENSOR_RAY = """
+<mujoco>
+  <compiler angle="radian"/>
+  <option timestep="0.004" integrator="implicitfast"/>
+  <worldbody>
+    <geom name="floor" type="plane" size="5 5 0.1"/>
+    <geom name="ball" type="sphere" pos="3 0 2" size="0.5"/>
+    <geom name="crate" type="box" pos="-2 0 2" size="0.3 0.4 0.5"/>
+    <geom name="post" type="capsule" pos="0 3 2" size="0.2 0.5"/>
+    <geom name="can" type="cylinder" pos="0 -2.5 2" quat="0.7071068 0.7071068 0 0" size="0.3 0.4"/>
+    <geom name="egg" type="ellipsoid" pos="0 0 4" size="0.5 0.4 0.3"/>
+    <body name="drone" pos="0 0 2">
+      <freejoint/>
+      <geom type="sphere" size="0.1" mass="1.0"/>
+      <site name="s_down" quat="0 1 0 0"/>
+      <site name="s_px" quat="0.7071068 0 0.7071068 0"/>
+      <site name="s_nx" quat="0.7071068 0 -0.7071068 0"/>
+      <site name="s_py" quat="0.7071068 -0.7071068 0 0"/>
+      <site name="s_ny" quat="0.7071068 0.7071068 0 0"/>
+      <site name="s_up"/>
+    </body>
+    <body name="rod" pos="1.5 0 2.6">
+      <freejoint/>
+      <geom type="capsule" fromto="0 -0.3 0 0 0.3 0" size="0.05" mass="0.2"/>
+    </body>
+  </worldbody>
+  <sensor>
+    <rangefinder name="r_down" site="s_down"/><rangefinder name="r_px" site="s_px"/><rangefinder name="r_nx" site="s_nx"/>
+    <rangefinder name="r_py" site="s_py"/><rangefinder name="r_ny" site="s_ny"/><rangefinder name="r_up" site="s_up"/>
+    <rangefinder name="r_down_cut" site="s_down" cutoff="1.0"/>
+  </sensor>
+</mujoco>
+"""
+
 # Asimov-toe's ankle in miniature: a pitch/roll hinge pair under gravity driven by two fixed tendons with position
 # actuators (one clamped by ctrlrange / forcerange, one with a velocity gain), a sprung + damped third tendon with
 # a dead band, and a joint motor on the same dof (asimov_toe.xml:175-204).

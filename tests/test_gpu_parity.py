@@ -577,7 +577,7 @@ def test_g1_friction_domain_randomisation_per_world(g1):
 
 @pytest.mark.parametrize("name", ["SPHERE_DROP", "FALLING_BOX", "PENDULUM", "SLIDER_PD", "SPINNER", "TWO_SPHERES",
                                   "CAPSULE_ON_PLANE", "LIMITED_HINGE", "LEGGED", "SENSOR_ARM", "SLIDER_FRICTION", "SENSOR_MISC",
-                                  "SENSOR_FORCE"])
+                                  "SENSOR_FORCE", "SENSOR_RAY"])
 def test_small_fixtures_rollout(name):
   """Every joint type, primitive pair and sensor of the small fixtures, 200 steps, both sides from the same seed."""
   import torch

@@ -97,6 +97,29 @@ def test_force_and_torque_sensors_with_contacts_and_wrenches_match_oracle():
   assert touched > 0 and np.abs(so[:, adr["f_lid"]:adr["f_lid"] + 3]).max() > 0.5
 
 
+def test_rangefinder_rays_match_oracle_over_random_poses():
+  """rangefinder (sensor/builtin_sensor.py:59-101): 64 random drone poses around the six primitives of SENSOR_RAY, every reading
+  (hit distance or -1) against the oracle."""
+  import torch
+  m = fx.compile_xml(fx.SENSOR_RAY)
+  W = 64
+  rng = np.random.default_rng(11)
+  qpos = np.tile(m.qpos0, (W, 1)); qvel = np.zeros((W, m.nv)); ctrl = np.zeros((W, 0))
+  qpos[:, 0:3] += rng.uniform(-0.8, 0.8, (W, 3))
+  qt = rng.normal(0, 1, (W, 4)); qt[:, 0] += 2.0; qpos[:, 3:7] = qt / np.linalg.norm(qt, axis=1, keepdims=True)
+  qpos[:, 7:10] = rng.uniform(-2.0, 2.0, (W, 3)) + [0, 0, 2.5]
+  qt = rng.normal(0, 1, (W, 4)); qpos[:, 10:14] = qt / np.linalg.norm(qt, axis=1, keepdims=True)
+  engine, M, D, orc, worlds = _setup(m, W, qpos, qvel, ctrl, True, nconmax=16, njmax=64)
+  engine.forward(M, D)
+  for w in worlds:
+    orc.forward(w)
+  torch.cuda.synchronize()
+  sd = D.sensordata.cpu().numpy(); so = np.stack([w["sensordata"] for w in worlds])
+  assert ((sd < 0) == (so < 0)).all()
+  assert np.abs(sd - so).max() < 1e-4
+  assert (so < 0).sum() > 10 and (so > 0).sum() > 100       # hits and misses both occur
+
+
 def test_external_force_translates_and_torque_rotates():
   """The reference's own acceptance test of the wrench inputs (tests/test_entity.py:245-272): +x force -> +x motion, z torque ->
   rotation primarily about z; on a free box far above the floor, and the closed form x = F/m t^2/2 for the semi-implicit steps."""

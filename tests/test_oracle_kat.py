@@ -696,3 +696,41 @@ def test_force_and_torque_sensors_closed_forms():
   assert np.allclose(Fl, [0, 0, 0.4 * g], atol=2e-3)
   # cutoff clamps the torque reading
   assert np.abs(sd[adr["t_lid"]:adr["t_lid"] + 3]).max() <= 0.5 + 1e-12
+
+
+def test_rangefinder_closed_forms():
+  """rangefinder (sensor/builtin_sensor.py:59-101) on SENSOR_RAY: one ray per primitive kind with a known distance, the
+  site's own body excluded, -1 without a hit, the cutoff caps hits only."""
+  import fixtures as fx
+  from oracle import Oracle
+  m = fx.compile_xml(fx.SENSOR_RAY)
+  o = Oracle(m, "f64", 8, 32)
+  adr = {n: int(m.sensor_adr[m.name2id("sensor", n)]) for n in m.names["sensor"]}
+  q = np.array(m.qpos0, float)
+  q[7:10] = [1.5, 0.0, 9.0]                  # the rod far above: out of every ray
+  w = o.new_world(q, np.zeros(m.nv), [])
+  o.forward(w)
+  sd = w["sensordata"]
+  want = {"r_down": 2.0, "r_px": 3.0 - 0.5, "r_nx": 2.0 - 0.3, "r_py": 3.0 - 0.2, "r_ny": 2.5 - 0.4, "r_up": 2.0 - 0.3, "r_down_cut": 1.0}
+  for n, v in want.items():
+    assert sd[adr[n]] == pytest.approx(v, abs=1e-6), n
+  # the rod across the +x ray: its surface is 0.05 in front of its axis
+  q[7:10] = [1.5, 0.0, 2.0]
+  w = o.new_world(q, np.zeros(m.nv), []); o.forward(w)
+  assert w["sensordata"][adr["r_px"]] == pytest.approx(1.5 - 0.05, abs=1e-6)
+  # drone moved and yawed by 90 deg about z: +x site now looks along +y (the post), +y site along -x (the crate); below the floor's
+  # back side nothing is seen; above the egg the up ray misses
+  q[0:3] = [0.0, 0.0, 2.0]; q[3:7] = [np.cos(np.pi / 4), 0, 0, np.sin(np.pi / 4)]; q[7:10] = [1.5, 0.0, 9.0]
+  w = o.new_world(q, np.zeros(m.nv), []); o.forward(w)
+  sd = w["sensordata"]
+  assert sd[adr["r_px"]] == pytest.approx(2.8, abs=1e-6) and sd[adr["r_py"]] == pytest.approx(1.7, abs=1e-6)
+  q[0:3] = [0.0, 0.0, 5.0]; q[3:7] = [1, 0, 0, 0]
+  w = o.new_world(q, np.zeros(m.nv), []); o.forward(w)
+  sd = w["sensordata"]
+  assert sd[adr["r_up"]] == -1.0 and sd[adr["r_down"]] == pytest.approx(5.0 - 4.3, abs=1e-6) and sd[adr["r_px"]] == -1.0
+  # tilted ray onto the floor: distance = height / cos(tilt)
+  th = 0.3
+  q[0:3] = [1.0, 1.0, 1.5]; q[3:7] = [np.cos(th / 2), np.sin(th / 2), 0, 0]
+  w = o.new_world(q, np.zeros(m.nv), []); o.forward(w)
+  assert w["sensordata"][adr["r_down"]] == pytest.approx(1.5 / np.cos(th), rel=1e-9)
+  assert w["sensordata"][adr["r_down_cut"]] == 1.0
