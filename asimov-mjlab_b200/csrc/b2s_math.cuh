@@ -408,25 +408,28 @@ struct RowChol {
 };
 // rows of the symmetric matrix whose LOWER triangle is stored in S (row stride ld; entry (i, j), j >= i, is read at S[j * ld + i],
 // which is contiguous across lanes); rows / columns >= n are identity padding
-template <int T>
+// PK (packed): S holds only a triangle, entry (max, min) at S[max (max + 1) / 2 + min] -- N (N + 1) / 2 floats instead of N x ld.
+// M's lower triangle and the factor U (entry (i, k), i <= k, at k (k + 1) / 2 + i) then share the same slots; the reads of "junk"
+// positions the algorithms rely on being harmless stay in bounds (they land on other entries of the triangle).
+template <int T, bool PK = false>
 DEV void rowchol_load_lower(const float* S, int ld, int n, int lane, float (&a)[7 * T], float (&b)[RowChol<T>::NB]) {
   constexpr int N = RowChol<T>::N;
   const int i0 = min(lane, N - 1);
 #pragma unroll
-  for (int j = 0; j < N; j++) a[j] = (lane < n && j < n) ? S[j * ld + i0] : (j == lane ? 1.0f : 0.0f);
+  for (int j = 0; j < N; j++) a[j] = (lane < n && j < n) ? S[PK ? j * (j + 1) / 2 + i0 : j * ld + i0] : (j == lane ? 1.0f : 0.0f);
   if (RowChol<T>::HI) {
     const int i1 = min(lane + 32, N - 1);
 #pragma unroll
-    for (int j = 32; j < N; j++) b[j - 32] = (lane + 32 < n && j < n) ? S[j * ld + i1] : (j == lane + 32 ? 1.0f : 0.0f);
+    for (int j = 32; j < N; j++) b[j - 32] = (lane + 32 < n && j < n) ? S[PK ? j * (j + 1) / 2 + i1 : j * ld + i1] : (j == lane + 32 ? 1.0f : 0.0f);
   }
 }
 // steps k = k_hi-1 .. 0 of the elimination (k_hi = N: the whole factorisation)
-template <int T>
+template <int T, bool PK = false>
 DEV void rowchol_factor(float (&a)[7 * T], float (&b)[RowChol<T>::NB], int lane, float* S, int ld, float* invd, float* colbuf, int k_hi = 7 * T) {
   constexpr int N = RowChol<T>::N;
   constexpr bool HI = RowChol<T>::HI;
-  float* const Ur0 = S + min(lane, N - 1) * ld;
-  float* const Ur1 = S + min(lane + 32, N - 1) * ld;
+  float* const Ur0 = S + (PK ? min(lane, N - 1) : min(lane, N - 1) * ld);      // entry (row, k) at Ur[PK ? k (k + 1) / 2 : k]
+  float* const Ur1 = S + (PK ? min(lane + 32, N - 1) : min(lane + 32, N - 1) * ld);
 #pragma unroll
   for (int k = N - 1; k >= 0; k--) {
     if (k < k_hi) {
@@ -440,12 +443,12 @@ DEV void rowchol_factor(float (&a)[7 * T], float (&b)[RowChol<T>::NB], int lane,
       if (k < 32 && lane == k) la = sd * inv;
       a[k] = la;
       line[lane] = la;
-      if (lane <= k && lane < N) Ur0[k] = la;
+      if (lane <= k && lane < N) Ur0[PK ? k * (k + 1) / 2 : k] = la;
       if (HI && k >= 32) {
         float lb = b[k >= 32 ? k - 32 : 0] * inv;
         if (lane == k - 32) lb = sd * inv;
         b[k >= 32 ? k - 32 : 0] = lb;
-        if (lane < RowChol<T>::NB) { line[32 + lane] = lb; if (lane + 32 <= k) Ur1[k] = lb; }
+        if (lane < RowChol<T>::NB) { line[32 + lane] = lb; if (lane + 32 <= k) Ur1[PK ? k * (k + 1) / 2 : k] = lb; }
       }
       if (lane == 0) invd[k] = inv;
       __syncwarp();
@@ -470,54 +473,59 @@ DEV void rowchol_factor(float (&a)[7 * T], float (&b)[RowChol<T>::NB], int lane,
 // Solve U U^T x = g with the factor above: lane l holds g[l] in b0 and g[l + 32] in b1 (entries of padding rows must be 0).
 // U y = g runs from the last row up, U^T x = y from the first down; a finished lane keeps its result in a second register, so
 // the junk in S's strict lower triangle (and the clamped rows of lanes >= N) only ever lands in values that are not read again.
-template <int T>
+template <int T, bool PK = false>
 DEV void rowchol_solve(const float* S, const float* invd, int ld, int lane, float& b0, float& b1) {
   constexpr int N = RowChol<T>::N;
   constexpr bool HI = RowChol<T>::HI;
   constexpr int N0 = HI ? 32 : N, UN = HI ? 8 : 7;
-  const float* Ur0 = S + min(lane, N - 1) * ld;
-  const float* Ur1 = S + min(lane + 32, N - 1) * ld;
-  const float* Uc0 = S + min(lane, N - 1);
-  const float* Uc1 = S + min(lane + 32, N - 1);
+  const int r0 = min(lane, N - 1), r1 = min(lane + 32, N - 1);
+  const float* Ur0 = S + (PK ? r0 : r0 * ld);                    // entry (row, k) at Ur[PK ? k (k + 1) / 2 : k]
+  const float* Ur1 = S + (PK ? r1 : r1 * ld);
+  const float* Uc0 = S + (PK ? r0 * (r0 + 1) / 2 : r0);          // entry (k, col) at Uc[PK ? k : k ld]
+  const float* Uc1 = S + (PK ? r1 * (r1 + 1) / 2 : r1);
+#define RC_ROW(k) (PK ? (k) * ((k) + 1) / 2 : (k))
+#define RC_COL(k) (PK ? (k) : (k) * ld)
   float y0 = 0.f, y1 = 0.f;
   if (HI) {
 #pragma unroll
     for (int k = N - 1; k >= 32; k--) {
       const float yk = __shfl_sync(FULL, b1, k - 32) * invd[k];
       if (lane == k - 32) y1 = yk;
-      b0 -= Ur0[k] * yk;
-      b1 -= Ur1[k] * yk;
+      b0 -= Ur0[RC_ROW(k)] * yk;
+      b1 -= Ur1[RC_ROW(k)] * yk;
     }
   }
 #pragma unroll UN
   for (int k = N0 - 1; k >= 0; k--) {
     const float yk = __shfl_sync(FULL, b0, k) * invd[k];
     if (lane == k) y0 = yk;
-    b0 -= Ur0[k] * yk;
+    b0 -= Ur0[RC_ROW(k)] * yk;
   }
 #pragma unroll UN
   for (int k = 0; k < N0; k++) {
     const float xk = __shfl_sync(FULL, y0, k) * invd[k];
     if (lane == k) b0 = xk;
-    y0 -= Uc0[k * ld] * xk;
-    if (HI) y1 -= Uc1[k * ld] * xk;
+    y0 -= Uc0[RC_COL(k)] * xk;
+    if (HI) y1 -= Uc1[RC_COL(k)] * xk;
   }
   if (HI) {
 #pragma unroll
     for (int k = 32; k < N; k++) {
       const float xk = __shfl_sync(FULL, y1, k - 32) * invd[k];
       if (lane == k - 32) b1 = xk;
-      y1 -= Uc1[k * ld] * xk;
+      y1 -= Uc1[RC_COL(k)] * xk;
     }
   }
 }
+#undef RC_ROW
+#undef RC_COL
 // factor the symmetric matrix whose lower triangle is in S (n real rows) in place: S ends up holding U (see above)
-template <int T>
+template <int T, bool PK = false>
 DEV void rowchol_smem(float* S, int n, int ld, int lane, float* invd, float* colbuf) {
   float a[7 * T], b[RowChol<T>::NB];
-  rowchol_load_lower<T>(S, ld, n, lane, a, b);
+  rowchol_load_lower<T, PK>(S, ld, n, lane, a, b);
   __syncwarp();
-  rowchol_factor<T>(a, b, lane, S, ld, invd, colbuf);
+  rowchol_factor<T, PK>(a, b, lane, S, ld, invd, colbuf);
 }
 __host__ __device__ inline int b2s_hdim(int T) { return 7 * T; }                         // padded matrix dimension
 __host__ __device__ inline int b2s_hld(int T) { return (7 * T + 1) | 1; }                 // odd row stride > 7T

@@ -203,9 +203,14 @@ void launch_static_frames(const ModelDev& m, const DataDev& d, cudaStream_t st) 
 }
 
 // ---------------------------------------------------------------------------------------------- k_dynamics
-// shared memory per warp (floats): Cholesky scratch line 2*RC_LINE | cdof 6nv | crb 10nb | cvel 6nb | cdd 6nv | cfrc 6nb | fext 6nb | M nv*ld | vec 4*nvp
+// shared memory per warp (floats): Cholesky scratch line 2*RC_LINE | cdof 6nv | A: cinert 10nb, later cvel 6nb + cdof_dot 6nv |
+// B: crb 10nb, later cfrc 6nb + fext 6nb | M as a packed triangle N(N+1)/2 | invd 7T | vec 4*nvp.  The two aliased regions and
+// the packed matrix bring a G1 world to 7.7 KB: 7 CTAs of 4 warps per SM, so 4096 worlds are ONE wave (was 11.4 KB, 1.73 waves).
+__host__ __device__ inline int dyn_regA(int nv, int nb) { return 10 * nb > 6 * nb + 6 * nv ? 10 * nb : 6 * nb + 6 * nv; }
+__host__ __device__ inline int dyn_regB(int nb) { return 12 * nb; }
+__host__ __device__ inline int dyn_tri(int T) { return (b2s_hdim(T) * (b2s_hdim(T) + 1) / 2 + 3) & ~3; }
 __host__ __device__ inline int dyn_smem_floats(int nv, int nvp, int nb, int T) {
-  return (2 * RC_LINE + 6 * nv + 10 * nb + 6 * nb + 6 * nv + 6 * nb + 6 * nb + b2s_hdim(T) * b2s_hld(T) + 7 * T + 4 * nvp + 3) & ~3;
+  return (2 * RC_LINE + 6 * nv + dyn_regA(nv, nb) + dyn_regB(nb) + dyn_tri(T) + 7 * T + 4 * nvp + 3) & ~3;
 }
 
 template <int T>
@@ -216,13 +221,14 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   const int nb = m.nbody, nv = m.nv, nvp = m.nvp, ld = b2s_hld(T);
   float* s_col = b2s_smem + (size_t)warp * dyn_smem_floats(nv, nvp, nb, T);     // 16-byte aligned
   float* s_cdof = s_col + 2 * RC_LINE;
-  float* s_crb = s_cdof + 6 * nv;
-  float* s_cvel = s_crb + 10 * nb;
+  float* s_cin = s_cdof + 6 * nv;            // region A
+  float* s_cvel = s_cin;
   float* s_cdd = s_cvel + 6 * nb;
-  float* s_cfrc = s_cdd + 6 * nv;
+  float* s_crb = s_cin + dyn_regA(nv, nb);   // region B
+  float* s_cfrc = s_crb;
   float* s_fext = s_cfrc + 6 * nb;
-  float* s_M = s_fext + 6 * nb;
-  float* s_invd = s_M + b2s_hdim(T) * ld;
+  float* s_M = s_crb + dyn_regB(nb);         // packed triangle: entry (i, j), j <= i, at i (i + 1) / 2 + j
+  float* s_invd = s_M + dyn_tri(T);
   float* s_qvel = s_invd + 7 * T;
   float* s_act = s_qvel + nvp;      // qfrc_actuator
   float* s_rhs = s_act + nvp;       // qfrc_smooth
@@ -235,11 +241,10 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   for (int i = lane; i < nv; i += 32) { const float v = qvel[i]; s_qvel[i] = v; s_act[i] = 0.f; d.snap_qvel[(size_t)w * nv + i] = v; }
   for (int i = lane; i < m.nq; i += 32) d.snap_qpos[(size_t)w * m.nq + i] = qpos[i];
   if (lane == 0) d.snap_time[w] = d.time[w];
-  for (int i = lane; i < b2s_hdim(T) * ld; i += 32) s_M[i] = 0.f;
+  for (int i = lane; i < dyn_tri(T); i += 32) s_M[i] = 0.f;
   __syncwarp();
   // composite inertia: sum of cinert over the subtree range (same frame for all bodies).  cinert is staged once,
-  // coalesced, into the cfrc|fext region (12 nb floats, not written until the RNE pass below)
-  float* s_cin = s_cfrc;
+  // coalesced, into region A (cvel / cdof_dot are written there after the sums)
 #pragma unroll 4
   for (int i = lane; i < 10 * nb; i += 32) s_cin[i] = d.cinert[(size_t)w * nb * 10 + i];
   __syncwarp();
@@ -256,6 +261,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
 #pragma unroll
     for (int k = 0; k < 10; k++) s_crb[10 * b + k] = acc[k];
   }
+  __syncwarp();      // region A changes hands: cinert -> cvel | cdof_dot
   // com_vel: cvel(b) = sum over ancestor dofs; cdof_dot of the body's own dofs on the way
   for (int b = lane; b < nb; b += 32) {
     sv6 v = zero6();
@@ -297,9 +303,10 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
       if (j > i) break;
       float v = dot6(ld6(s_cdof + 6 * j), buf);
       if (j == i) v += armature[i];
-      s_M[i * ld + j] = v;
+      s_M[i * (i + 1) / 2 + j] = v;
     }
   }
+  __syncwarp();      // region B changes hands: crb -> cfrc | fext
   // rne: bias force per body, then subtree sums
   {
     const bool grav = !(m.disableflags & B2S_DSBL_GRAVITY);
@@ -342,7 +349,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
 #pragma unroll
         for (int k = 0; k < 4; k++) {
           const int c = 4 * j + k;
-          e[k] = c < nv ? (c <= r ? s_M[r * ld + c] : s_M[c * ld + r]) : 0.f;
+          e[k] = c < nv ? (c <= r ? s_M[r * (r + 1) / 2 + c] : s_M[c * (c + 1) / 2 + r]) : 0.f;
         }
         if (j < n4) out[j] = make_float4(e[0], e[1], e[2], e[3]);
       }
@@ -430,9 +437,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   }
   __syncwarp();
   // factor M in shared memory and solve for the unconstrained acceleration
-  rowchol_smem<T>(s_M, nv, ld, lane, s_invd, s_col);
+  rowchol_smem<T, true>(s_M, nv, ld, lane, s_invd, s_col);
   float b0 = lane < nv ? s_rhs[lane] : 0.f, b1 = lane + 32 < nv ? s_rhs[lane + 32] : 0.f;
-  rowchol_solve<T>(s_M, s_invd, ld, lane, b0, b1);
+  rowchol_solve<T, true>(s_M, s_invd, ld, lane, b0, b1);
   if (lane < nv) d.qacc_smooth[(size_t)w * nv + lane] = b0;
   if (lane + 32 < nv) d.qacc_smooth[(size_t)w * nv + lane + 32] = b1;
 }
