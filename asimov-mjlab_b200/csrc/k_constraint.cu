@@ -57,7 +57,7 @@ DEV void finish_row(const ModelDev& m, const DataDev& d, size_t row, float pos, 
   d.efc_force[row] = 0.f;
 }
 
-__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_constraint(const ModelDev m, const DataDev d) {
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, 7) k_constraint(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   if (w >= d.nworld) return;

@@ -1,7 +1,7 @@
 # A/B of the in-tree library against a variant (under gpurun): GPU suite on the in-tree build, then the driver-shaped bench on both
 cd $GRAFT_REPO_ROOT
 TAG=${TAG:-ab}
-python -m pytest tests -m gpu -q > gpurun_out/gputest_$TAG.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/gputest_$TAG.log
+if [ -z "$NOTEST" ]; then python -m pytest tests -m gpu -q > gpurun_out/gputest_$TAG.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/gputest_$TAG.log; fi
 for rep in 1 2; do
 python bench.py --steps 20 --warmup 5 --extras 0 --cpu-baseline 0 > gpurun_out/bench_${TAG}_new$rep.json 2> gpurun_out/bench_${TAG}_new$rep.err; echo "new exit $?"
 B2S_LIB=$GRAFT_REPO_ROOT/asimov-mjlab_b200/_variants/lib_${BASE:-base}.so python bench.py --steps 20 --warmup 5 --extras 0 --cpu-baseline 0 > gpurun_out/bench_${TAG}_base$rep.json 2> gpurun_out/bench_${TAG}_base$rep.err; echo "base exit $?"
