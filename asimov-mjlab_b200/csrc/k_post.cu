@@ -17,9 +17,14 @@ DEV sv6 object_velocity(const ModelDev& m, const float* cvel, const float* com, 
 // the pyramid-decoded wrench in the contact frame (mju_decodePyramid) and rotated to the world frame, the position.
 // The sensors then match and reduce out of shared memory instead of chasing global loads contact by contact.
 #define CC_WORDS 19
+// per-warp words of the contact cache: [nconmax][4] ints, [nconmax][15] floats, then the match masks [nsensor][R][2]
+__host__ __device__ inline int cc_mask_words(int nconmax) { return (nconmax + 31) / 32; }
+__host__ __device__ inline int cc_warp_words(int nconmax, int nsensor) { return CC_WORDS * nconmax + 2 * cc_mask_words(nconmax) * nsensor; }
 struct ConCache {
   const int* i;     // [ncon][4]: geom1, geom2, body1, body2
   const float* f;   // [ncon][15]: f6 contact frame | force world 3 | torque world 3 | pos 3
+  const unsigned* mm;   // [nsensor][R][2]: per contact sensor, bit c of word r = contact 32 r + c matches forward / backward
+  int R;                // words per mask = ceil(nconmax / 32)
 };
 DEV void fill_contact_cache(const ModelDev& m, const DataDev& d, int w, int ncon, int* ci, float* cf, int lane) {
   const size_t con0 = (size_t)w * d.nconmax, row0 = (size_t)w * d.njmax;
@@ -64,9 +69,40 @@ DEV Frame obj_frame(const ModelDev& m, const DataDev& d, int w, int type, int id
   return f;
 }
 
+// Which contacts each contact sensor matches, for the whole warp at once: one lane per contact, one ballot per sensor and
+// 32 contacts.  (The per-sensor lanes used to re-evaluate side_match for every contact in every pass of their reduction:
+// 35 % of the kernel's samples on 3 active lanes for the G1.)
+DEV void match_contacts(const ModelDev& m, int ncon, const int* ci, unsigned* mm, int R, int lane) {
+  for (int s = 0; s < m.nsensor; s++) {
+    if (m.sensor_type[s] != B2S_SENS_CONTACT) continue;
+    const int ot = m.sensor_objtype[s], id = m.sensor_objid[s], rt = m.sensor_reftype[s], rid = m.sensor_refid[s];
+    for (int r = 0; r < R; r++) {
+      const int c = 32 * r + lane;
+      bool fwd = false, bwd = false;
+      if (c < ncon) {
+        const int g1 = ci[4 * c], g2 = ci[4 * c + 1], b1 = ci[4 * c + 2], b2 = ci[4 * c + 3];
+        fwd = side_match(m, ot, id, g1, b1) && (rid < 0 || side_match(m, rt, rid, g2, b2));
+        bwd = side_match(m, ot, id, g2, b2) && (rid < 0 || side_match(m, rt, rid, g1, b1));
+      }
+      const unsigned mf = __ballot_sync(FULL, fwd), mb = __ballot_sync(FULL, bwd);
+      if (lane == 0) { mm[(s * R + r) * 2] = mf; mm[(s * R + r) * 2 + 1] = mb; }
+    }
+  }
+}
+// iterate the matched contacts of sensor s in contact order: c = contact, fwd = matched in the forward direction
+#define FOR_MATCHED(cc, s, ...)                                                          \
+  for (int r_ = 0; r_ < (cc).R; r_++) {                                                  \
+    const unsigned mf_ = (cc).mm[((s) * (cc).R + r_) * 2];                               \
+    unsigned any_ = mf_ | (cc).mm[((s) * (cc).R + r_) * 2 + 1];                          \
+    while (any_) {                                                                       \
+      const int bit_ = __ffs(any_) - 1; any_ &= any_ - 1;                                \
+      const int c = 32 * r_ + bit_; const bool fwd = (mf_ >> bit_) & 1u; (void)fwd;      \
+      __VA_ARGS__                                                                        \
+    }                                                                                    \
+  }
+
 DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float* out, int ncon, const ConCache cc) {
   const int bits = m.sensor_intprm[3 * s], reduce = m.sensor_intprm[3 * s + 1], nslot = m.sensor_intprm[3 * s + 2];
-  const int ot = m.sensor_objtype[s], id = m.sensor_objid[s], rt = m.sensor_reftype[s], rid = m.sensor_refid[s];
   const int dim = m.sensor_dim[s], maxm = m.contact_sensor_maxmatch;
   const size_t con0 = (size_t)w * d.nconmax;
   for (int k = 0; k < dim; k++) out[k] = 0.f;
@@ -74,11 +110,8 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
   const int slotdim = dim / nslot;
   // pass 1: count matches (capped), and for netforce the force-weighted centroid
   int nmatch = 0; float wsum = 0.f; v3 P = mk3(0.f, 0.f, 0.f), Pm = mk3(0.f, 0.f, 0.f);
-  for (int c = 0; c < ncon && nmatch < maxm; c++) {
-    const int g1 = cc.i[4 * c], g2 = cc.i[4 * c + 1], b1 = cc.i[4 * c + 2], b2 = cc.i[4 * c + 3];
-    const bool fwd = side_match(m, ot, id, g1, b1) && (rid < 0 || side_match(m, rt, rid, g2, b2));
-    const bool bwd = side_match(m, ot, id, g2, b2) && (rid < 0 || side_match(m, rt, rid, g1, b1));
-    if (!fwd && !bwd) continue;
+  FOR_MATCHED(cc, s, {
+    if (nmatch >= maxm) break;
     nmatch++;
     if (reduce == B2S_REDUCE_NETFORCE) {
       const float* f6 = cc.f + 15 * c;
@@ -86,24 +119,22 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
       v3 cp = ld3(f6 + 12);
       P = P + cp * wt; Pm = Pm + cp; wsum += wt;
     }
-  }
+  })
+  (void)ncon;
   if (nmatch == 0) return;
   if (reduce == B2S_REDUCE_NETFORCE) {
     P = wsum > B2S_MINVAL ? P * (1.f / wsum) : Pm * (1.f / (float)nmatch);
     v3 F = mk3(0.f, 0.f, 0.f), Tq = mk3(0.f, 0.f, 0.f);
     int seen = 0;
-    for (int c = 0; c < ncon && seen < maxm; c++) {
-      const int g1 = cc.i[4 * c], g2 = cc.i[4 * c + 1], b1 = cc.i[4 * c + 2], b2 = cc.i[4 * c + 3];
-      const bool fwd = side_match(m, ot, id, g1, b1) && (rid < 0 || side_match(m, rt, rid, g2, b2));
-      const bool bwd = side_match(m, ot, id, g2, b2) && (rid < 0 || side_match(m, rt, rid, g1, b1));
-      if (!fwd && !bwd) continue;
+    FOR_MATCHED(cc, s, {
+      if (seen >= maxm) break;
       seen++;
       const float dir = fwd ? 1.f : -1.f;
       const float* f = cc.f + 15 * c;
       v3 fg = ld3(f + 6) * dir, tg = ld3(f + 9) * dir;
       v3 arm = ld3(f + 12) - P;
       F = F + fg; Tq = Tq + tg + cross(arm, fg);
-    }
+    })
     float* o = out;
     if (bits & B2S_CON_FOUND) *o++ = (float)nmatch;
     if (bits & B2S_CON_FORCE) { st3(o, F); o += 3; }
@@ -119,11 +150,8 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
   for (int sl = 0; sl < nslot && sl < nmatch; sl++) {
     float bkey = 3.0e38f; int bord = -1, bc = -1; float bdir = 1.f;
     int ord = 0;
-    for (int c = 0; c < ncon && ord < maxm; c++) {
-      const int g1 = cc.i[4 * c], g2 = cc.i[4 * c + 1], b1 = cc.i[4 * c + 2], b2 = cc.i[4 * c + 3];
-      const bool fwd = side_match(m, ot, id, g1, b1) && (rid < 0 || side_match(m, rt, rid, g2, b2));
-      const bool bwd = side_match(m, ot, id, g2, b2) && (rid < 0 || side_match(m, rt, rid, g1, b1));
-      if (!fwd && !bwd) continue;
+    FOR_MATCHED(cc, s, {
+      if (ord >= maxm) break;
       float key;
       if (reduce == B2S_REDUCE_NONE) key = (float)ord;
       else if (reduce == B2S_REDUCE_MINDIST) key = d.con_dist[con0 + c];
@@ -132,7 +160,7 @@ DEV void contact_sensor(const ModelDev& m, const DataDev& d, int w, int s, float
       const bool better = key < bkey || (key == bkey && ord < bord);
       if (after && (bord < 0 || better)) { bkey = key; bord = ord; bc = c; bdir = fwd ? 1.f : -1.f; }
       ord++;
-    }
+    })
     if (bc < 0) break;
     pkey = bkey; pord = bord;
     const float* f6 = cc.f + 15 * bc;
@@ -239,10 +267,15 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
   float* s_cfi = s_dof + 6 * nv;
   const float* qvel = d.snap_qvel + (size_t)w * nv;     // the state this forward pass was computed from (see DataDev::snap_*)
   // contact cache (only when the model has contact sensors): per-warp [nconmax][4] ints then [nconmax][15] floats
-  int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * wfl) + (size_t)warp * CC_WORDS * d.nconmax;
+  int* s_ci = (int*)(b2s_smem + (size_t)B2S_WARPS_PER_CTA * wfl) + (size_t)warp * cc_warp_words(d.nconmax, m.nsensor);
   float* s_cf = (float*)(s_ci + 4 * d.nconmax);
+  unsigned* s_mm = (unsigned*)(s_ci + CC_WORDS * d.nconmax);
   const int ncon = m.need_concache ? d.ncon[w] : 0;
-  if (m.need_concache) fill_contact_cache(m, d, w, ncon, s_ci, s_cf, lane);
+  if (m.need_concache) {
+    fill_contact_cache(m, d, w, ncon, s_ci, s_cf, lane);
+    __syncwarp();
+    match_contacts(m, ncon, s_ci, s_mm, cc_mask_words(d.nconmax), lane);
+  }
   const float* qacc = d.qacc + (size_t)w * nv;
   const float* cdof = d.cdof + (size_t)w * 6 * nv;
   const float* cdd = d.cdof_dot + (size_t)w * 6 * nv;
@@ -450,7 +483,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
         if (type == B2S_SENS_FRAMELINVEL) st3(out, mk3(v.v[3], v.v[4], v.v[5])); else st3(out, mk3(v.v[0], v.v[1], v.v[2]));
       } break;
       case B2S_SENS_RANGEFINDER: break;      // written by the warp-wide ray pass below
-      case B2S_SENS_CONTACT: { ConCache cc; cc.i = s_ci; cc.f = s_cf; contact_sensor(m, d, w, s, out, ncon, cc); } break;
+      case B2S_SENS_CONTACT: { ConCache cc; cc.i = s_ci; cc.f = s_cf; cc.mm = s_mm; cc.R = cc_mask_words(d.nconmax); contact_sensor(m, d, w, s, out, ncon, cc); } break;
       default: for (int k = 0; k < dim; k++) out[k] = 0.f;
     }
     const float cut = m.sensor_cutoff[s];
@@ -654,7 +687,7 @@ void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   b2s_count_launch();
 }
 size_t smem_sensors(const ModelDev& m, const DataDev& d) {
-  return (size_t)B2S_WARPS_PER_CTA * (sens_smem_floats(m.nbody, m.nv, m.need_cfrc) + (m.need_concache ? CC_WORDS * d.nconmax : 0)) * sizeof(float);
+  return (size_t)B2S_WARPS_PER_CTA * (sens_smem_floats(m.nbody, m.nv, m.need_cfrc) + (m.need_concache ? cc_warp_words(d.nconmax, m.nsensor) : 0)) * sizeof(float);
 }
 size_t smem_integrate(const ModelDev& m) {
   const int T = b2s_tile_for(m.nv);
