@@ -16,6 +16,14 @@
 extern __shared__ __align__(16) float b2s_smem[];
 
 // ---------------------------------------------------------------------------------------------- k_position
+// Shared memory per warp: body frames 22 nb | local poses 7 nb | joint locals 12 njnt | geom write-out stage 32 x 12.
+// Everything a body contributes that does NOT depend on its parent -- its pose in the parent frame, the joint offsets, the
+// joint rotation from qpos (sincos) -- is computed by one lane per body / joint BEFORE the walk down the tree, so the
+// sequential part (one step per tree level: 11 for the G1) reads shared memory only; it used to chase
+// level_body -> body_parentid -> body_jntadr -> jnt_qposadr -> qpos through global memory on every level (ncu r2d: 19 % of the
+// kernel's samples were long-scoreboard stalls inside the level loop).  The arithmetic and its order are unchanged.
+#define POS_STAGE_LD 13
+__host__ __device__ inline int pos_smem_floats(int nb, int njnt) { return 22 * nb + 7 * nb + 12 * njnt + nb + 32 * POS_STAGE_LD; }
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
@@ -24,11 +32,15 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
   if (blockIdx.x == 0 && threadIdx.x < 2 && m.col_defer) d.cvx_ntask[threadIdx.x] = 0;      // and the convex-pair task list (k_collision phase 1 refills it)
   if (w >= d.nworld) return;
   const int nb = m.nbody;
-  float* sx = b2s_smem + (size_t)warp * 22 * nb;   // xpos
+  float* sx = b2s_smem + (size_t)warp * pos_smem_floats(nb, m.njnt);   // xpos
   float* sq = sx + 3 * nb;                          // xquat
   float* sm = sq + 4 * nb;                          // xmat
   float* sip = sm + 9 * nb;                         // xipos
   float* scom = sip + 3 * nb;                       // subtree_com
+  float* slp = scom + 3 * nb;                       // pose in the parent frame: pos 3, quat 4
+  float* sj = slp + 7 * nb;                         // per joint: jpos 3, jaxis 3, (hinge / ball: local rotation 4 | slide: displacement 1 | free: pos 3 + quat 4 over jpos..)
+  float* smx = sj + 12 * m.njnt;                    // body masses (the subtree-COM loop reads shared memory only)
+  float* stg = smx + nb;                        // geom / site write-out stage
   const float* qpos = d.qpos + (size_t)w * m.nq;
   const float* qpos0 = m.qpos0.at(w);
   const float* bpos = m.body_pos.at(w);
@@ -37,38 +49,54 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
     sx[0] = sx[1] = sx[2] = 0.f; sq[0] = 1.f; sq[1] = sq[2] = sq[3] = 0.f;
     for (int k = 0; k < 9; k++) sm[k] = (k % 4 == 0) ? 1.f : 0.f;
   }
+  for (int b = 1 + lane; b < nb; b += 32) {
+    v3 lp; q4 lq;
+    const int mid = m.body_mocapid[b];
+    if (mid >= 0) {
+      lp = ld3(d.mocap_pos + ((size_t)w * m.nmocap + mid) * 3);
+      lq = qnormalize(ldq(d.mocap_quat + ((size_t)w * m.nmocap + mid) * 4));
+    } else { lp = ld3(bpos + 3 * b); lq = ldq(bquat + 4 * b); }
+    st3(slp + 7 * b, lp); stq(slp + 7 * b + 3, lq);
+  }
+  for (int j = lane; j < m.njnt; j += 32) {
+    const int qa = m.jnt_qposadr[j], t = m.jnt_type[j];
+    float* o = sj + 12 * j;
+    if (t == B2S_JNT_FREE) {
+      st3(o, ld3(qpos + qa)); stq(o + 3, qnormalize(ldq(qpos + qa + 3))); st3(o + 7, ld3(m.jnt_axis + 3 * j));
+      continue;
+    }
+    const v3 jaxis = ld3(m.jnt_axis + 3 * j);
+    st3(o, ld3(m.jnt_pos + 3 * j)); st3(o + 3, jaxis);
+    if (t == B2S_JNT_SLIDE) o[6] = qpos[qa] - qpos0[qa];
+    else stq(o + 6, (t == B2S_JNT_HINGE) ? axis_angle(jaxis, qpos[qa] - qpos0[qa]) : qnormalize(ldq(qpos + qa)));
+  }
   for (int L = 1; L < m.nlevel; L++) {
     __syncwarp();
     for (int idx = m.level_adr[L] + lane; idx < m.level_adr[L + 1]; idx += 32) {
       const int b = m.level_body[idx], p = m.body_parentid[b];
-      v3 lp; q4 lq;
-      const int mid = m.body_mocapid[b];
-      if (mid >= 0) {
-        lp = ld3(d.mocap_pos + ((size_t)w * m.nmocap + mid) * 3);
-        lq = qnormalize(ldq(d.mocap_quat + ((size_t)w * m.nmocap + mid) * 4));
-      } else { lp = ld3(bpos + 3 * b); lq = ldq(bquat + 4 * b); }
+      const v3 lp = ld3(slp + 7 * b); const q4 lq = ldq(slp + 7 * b + 3);
       m33 pm = ldm(sm + 9 * p);
       v3 pos = ld3(sx + 3 * p) + mulv(pm, lp);
       q4 quat = qmul(ldq(sq + 4 * p), lq);
       const int jn = m.body_jntnum[b], ja = m.body_jntadr[b];
       for (int jj = 0; jj < jn; jj++) {
-        const int j = ja + jj, qa = m.jnt_qposadr[j], t = m.jnt_type[j];
-        v3 jpos = ld3(m.jnt_pos + 3 * j), jaxis = ld3(m.jnt_axis + 3 * j);
+        const int j = ja + jj, t = m.jnt_type[j];
+        const float* o = sj + 12 * j;
         float* xan = d.xanchor + ((size_t)w * m.njnt + j) * 3;
         float* xax = d.xaxis + ((size_t)w * m.njnt + j) * 3;
         if (t == B2S_JNT_FREE) {
-          pos = ld3(qpos + qa);
-          quat = qnormalize(ldq(qpos + qa + 3));
-          st3(xan, pos); st3(xax, mulv(q2m(quat), jaxis));
+          pos = ld3(o);
+          quat = ldq(o + 3);
+          st3(xan, pos); st3(xax, mulv(q2m(quat), ld3(o + 7)));
           continue;
         }
+        const v3 jpos = ld3(o), jaxis = ld3(o + 3);
         m33 R = q2m(quat);
         v3 anchor = pos + mulv(R, jpos), axis = mulv(R, jaxis);
         st3(xan, anchor); st3(xax, axis);
-        if (t == B2S_JNT_SLIDE) pos = pos + axis * (qpos[qa] - qpos0[qa]);
+        if (t == B2S_JNT_SLIDE) pos = pos + axis * o[6];
         else {
-          q4 ql = (t == B2S_JNT_HINGE) ? axis_angle(jaxis, qpos[qa] - qpos0[qa]) : qnormalize(ldq(qpos + qa));
-          quat = qmul(quat, ql);
+          quat = qmul(quat, ldq(o + 6));
           pos = anchor - mulv(q2m(quat), jpos);
         }
       }
@@ -78,6 +106,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
   }
   __syncwarp();
   // inertial frames
+  const float* mass = m.body_mass.at(w);
   {
     const float* ipos = m.body_ipos.at(w);
     const float* iquat = m.body_iquat.at(w);
@@ -85,6 +114,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
       m33 R = ldm(sm + 9 * b);
       v3 xi = ld3(sx + 3 * b) + mulv(R, ld3(ipos + 3 * b));
       st3(sip + 3 * b, xi);
+      smx[b] = mass[b];
       st3(d.xipos + ((size_t)w * nb + b) * 3, xi);
       stm(d.ximat + ((size_t)w * nb + b) * 9, q2m(qmul(ldq(sq + 4 * b), ldq(iquat + 4 * b))));
     }
@@ -93,15 +123,33 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
   for (int i = lane; i < 3 * nb; i += 32) d.xpos[(size_t)w * 3 * nb + i] = sx[i];
   for (int i = lane; i < 4 * nb; i += 32) d.xquat[(size_t)w * 4 * nb + i] = sq[i];
   for (int i = lane; i < 9 * nb; i += 32) d.xmat[(size_t)w * 9 * nb + i] = sm[i];
-  // geoms and sites
+  // geoms and sites: 32 frames per pass through the stage; a pass whose ids are consecutive (the usual case: the robot's geoms)
+  // leaves as 3 x 32 + 9 x 32 contiguous floats instead of 12 scattered 4-byte stores per lane
   {
     const float* gpos = m.geom_pos.at(w);
     const float* gquat = m.geom_quat.at(w);
-    for (int k = lane; k < m.nposegeom; k += 32) {
-      const int g = m.pose_geom[k];
-      const int b = m.geom_bodyid[g];
-      st3(d.geom_xpos + ((size_t)w * m.ngeom + g) * 3, ld3(sx + 3 * b) + mulv(ldm(sm + 9 * b), ld3(gpos + 3 * g)));
-      stm(d.geom_xmat + ((size_t)w * m.ngeom + g) * 9, q2m(qmul(ldq(sq + 4 * b), ldq(gquat + 4 * g))));
+    for (int k0 = 0; k0 < m.nposegeom; k0 += 32) {
+      const int k = k0 + lane, cnt = min(32, m.nposegeom - k0);
+      const int g0 = m.pose_geom[k0];
+      int g = -1;
+      if (k < m.nposegeom) {
+        g = m.pose_geom[k];
+        const int b = m.geom_bodyid[g];
+        st3(stg + POS_STAGE_LD * lane, ld3(sx + 3 * b) + mulv(ldm(sm + 9 * b), ld3(gpos + 3 * g)));
+        stm(stg + POS_STAGE_LD * lane + 3, q2m(qmul(ldq(sq + 4 * b), ldq(gquat + 4 * g))));
+      }
+      const bool contig = __all_sync(FULL, g < 0 || g == g0 + lane);
+      __syncwarp();
+      if (contig) {
+        float* op = d.geom_xpos + ((size_t)w * m.ngeom + g0) * 3;
+        float* om = d.geom_xmat + ((size_t)w * m.ngeom + g0) * 9;
+        for (int i = lane; i < 3 * cnt; i += 32) op[i] = stg[POS_STAGE_LD * (i / 3) + i % 3];
+        for (int i = lane; i < 9 * cnt; i += 32) om[i] = stg[POS_STAGE_LD * (i / 9) + 3 + i % 9];
+      } else if (g >= 0) {
+        for (int i = 0; i < 3; i++) d.geom_xpos[((size_t)w * m.ngeom + g) * 3 + i] = stg[POS_STAGE_LD * lane + i];
+        for (int i = 0; i < 9; i++) d.geom_xmat[((size_t)w * m.ngeom + g) * 9 + i] = stg[POS_STAGE_LD * lane + 3 + i];
+      }
+      __syncwarp();
     }
     const float* spos = m.site_pos.at(w);
     const float* squat = m.site_quat.at(w);
@@ -114,12 +162,13 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
     }
   }
   __syncwarp();
-  // subtree COM: direct sum over the subtree's contiguous id range
-  const float* mass = m.body_mass.at(w);
+  // subtree COM: direct sum over the subtree's contiguous id range (masses staged above: the loop reads shared memory only;
+  // the multiply-add stays ONE fused operation per term: the parity tests resolve a product rounded on its own)
   for (int b = lane; b < nb; b += 32) {
     v3 acc = mk3(0.f, 0.f, 0.f);
     const int e = m.body_subtree_end[b];
-    for (int j = b; j < e; j++) acc = acc + ld3(sip + 3 * j) * mass[j];
+#pragma unroll 4
+    for (int j = b; j < e; j++) acc = acc + ld3(sip + 3 * j) * smx[j];
     const float smass = m.body_subtreemass[b];
     v3 com = (smass < B2S_MINVAL) ? ld3(sip + 3 * b) : acc * (1.0f / smass);
     st3(scom + 3 * b, com);
@@ -447,7 +496,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
 // ---------------------------------------------------------------------------------------------- launchers
 void launch_position(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
-  const size_t smem = (size_t)B2S_WARPS_PER_CTA * 22 * m.nbody * sizeof(float);
+  const size_t smem = smem_position(m);
   k_position<<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d);
   b2s_count_launch();
 }
@@ -467,7 +516,7 @@ void launch_dynamics(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   TILE_DISPATCH(m.nv, (k_dynamics<T><<<grid, 32 * B2S_WARPS_PER_CTA, smem, st>>>(m, d)));
   b2s_count_launch();
 }
-size_t smem_position(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * 22 * m.nbody * sizeof(float); }
+size_t smem_position(const ModelDev& m) { return (size_t)B2S_WARPS_PER_CTA * pos_smem_floats(m.nbody, m.njnt) * sizeof(float); }
 size_t smem_dynamics(const ModelDev& m) {
   return (size_t)B2S_WARPS_PER_CTA * dyn_smem_floats(m.nv, m.nvp, m.nbody, b2s_tile_for(m.nv)) * sizeof(float);
 }
