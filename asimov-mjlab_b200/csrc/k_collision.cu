@@ -384,6 +384,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   // pair-table index of each survivor (convex models without a terrain grid): addresses the pair's cached separating direction
   const bool use_axis = CONVEX && m.ngrid == 0 && d.col_axis != nullptr;
   int* s_pidx = (int*)(s_stage + (size_t)(B2S_WARPS_PER_CTA - warp) * CVX_STAGE_CAP) + warp * B2S_MAX_SURVIVORS;
+  int* s_hft = s_pidx + (B2S_WARPS_PER_CTA - warp) * B2S_MAX_SURVIVORS + warp * HF_LIST_CAP;      // live height-field prism tasks of the current pass
+  (void)s_hft;
   if (m.disableflags & (B2S_DSBL_CONSTRAINT | B2S_DSBL_CONTACT)) { if (lane == 0) d.ncon[w] = 0; return; }
   const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
   const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
@@ -579,24 +581,48 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         }
         int Ttot;
         const int off = warp_excl_scan(R.T, lane, &Ttot);
-        int nst = 0;
+        // pass A: the cheap test of every (pair, prism) of this pass -- prism top above B's lowest point -- 32 per round; the live
+        // ones are compacted, in (pair, prism) order, into a task list.  Pass B then runs GJK / EPA on full rounds of live tasks
+        // (a Go1 pass has ~120 prisms under its geoms' bounding boxes and ~30 live ones: 1 - 2 GJK rounds instead of 4).
+        int nlive = 0;
 #pragma unroll 1
         for (int q0 = 0; q0 < Ttot; q0 += 32) {
           const int q = min(q0 + lane, Ttot - 1);
           int own = 0;                                  // largest lane whose offset is <= q
 #pragma unroll
           for (int b = 16; b > 0; b >>= 1) { const int cand = own + b; const int o = __shfl_sync(FULL, off, cand & 31); if (cand < 32 && o <= q) own = cand; }
-          const int og1 = __shfl_sync(FULL, g1, own), og2 = __shfl_sync(FULL, g2, own), ooff = __shfl_sync(FULL, off, own);
+          const int og1 = __shfl_sync(FULL, g1, own), ooff = __shfl_sync(FULL, off, own);
+          HfRange OR;
+          OR.cmin = __shfl_sync(FULL, R.cmin, own); OR.ncell = __shfl_sync(FULL, R.ncell, own); OR.rmin = __shfl_sync(FULL, R.rmin, own);
+          OR.T = 0; OR.loz = __shfl_sync(FULL, R.loz, own);
+          bool live = false;
+          if (q0 + lane < Ttot) {
+            const int h = m.geom_dataid[og1];
+            live = hfield_prism_live(q - ooff, OR, m.hfield_size + 4 * h, m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h]);
+          }
+          const unsigned lm = __ballot_sync(FULL, live);
+          const int pos = nlive + __popc(lm & ((1u << lane) - 1u));
+          if (live && pos < HF_LIST_CAP) s_hft[pos] = (own << 26) | (q - ooff);
+          nlive += __popc(lm);
+        }
+        __syncwarp();
+        int nst = 0;
+        if (nlive > HF_LIST_CAP) nst = CVX_STAGE_CAP + 1;      // too many for the list: the one-pair-at-a-time driver below takes these pairs
+#pragma unroll 1
+        for (int e0 = 0; e0 < nlive && nlive <= HF_LIST_CAP; e0 += 32) {
+          const int e = min(e0 + lane, nlive - 1);
+          const int ent = s_hft[e], own = (ent >> 26) & 31, t = ent & 0x3ffffff;
+          const int og1 = __shfl_sync(FULL, g1, own), og2 = __shfl_sync(FULL, g2, own);
           const float om = __shfl_sync(FULL, margin, own);
           HfRange OR;
           OR.cmin = __shfl_sync(FULL, R.cmin, own); OR.ncell = __shfl_sync(FULL, R.ncell, own); OR.rmin = __shfl_sync(FULL, R.rmin, own);
           OR.T = 0; OR.loz = __shfl_sync(FULL, R.loz, own);
           bool has = false;
           CvxStage one;
-          if (q0 + lane < Ttot) {
+          if (e0 + lane < nlive) {
             const Cvx B = geom_core(m, gx, gm, og2);
             const int h = m.geom_dataid[og1];
-            has = hfield_prism_task(one, q - ooff, OR, om, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h],
+            has = hfield_prism_task(one, t, OR, om, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h],
                                     ld3(gx + 3 * og1), ldm(gm + 9 * og1), B);
             one.idx |= own << 26;
           }
@@ -798,7 +824,7 @@ void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   b2s_count_launch();
 }
 size_t smem_collision(const ModelDev& m) {
-  return (size_t)B2S_WARPS_PER_CTA * ((2 * B2S_MAX_SURVIVORS + 1) * sizeof(int) + (m.col_convex ? CVX_STAGE_CAP * sizeof(CvxStage) + B2S_MAX_SURVIVORS * sizeof(int) : 0));
+  return (size_t)B2S_WARPS_PER_CTA * ((2 * B2S_MAX_SURVIVORS + 1) * sizeof(int) + (m.col_convex ? CVX_STAGE_CAP * sizeof(CvxStage) + (B2S_MAX_SURVIVORS + HF_LIST_CAP) * sizeof(int) : 0));
 }
 const void* fn_collision(const ModelDev& m) {
   const void* f = nullptr;

@@ -554,6 +554,7 @@ DEV int hfield_convex_warp(CvxStage* out, float margin, const float* hs, int nro
 
 // ---- flattened height-field tasks (used by k_collision): per-lane set-up and one prism task
 #define CVX_STAGE_CAP 96
+#define HF_LIST_CAP 128      // live prism tasks of one pass (32 survivors) that k_collision compacts before the GJK rounds
 struct HfRange { int cmin, ncell, rmin, T; float loz; };
 
 // B's bounding box in the field's frame (six support calls, this lane only) -> cell range and prism count
@@ -573,6 +574,17 @@ DEV HfRange hfield_range(float margin, const float* hs, int nrow, int ncol, v3 h
   const int rmin = max((int)floorf((lo[1] + sy) / dy), 0), rmax = min((int)ceilf((hi[1] + sy) / dy), nrow - 1);
   R.cmin = cmin; R.ncell = max(cmax - cmin, 0); R.rmin = rmin; R.T = max(rmax - rmin, 0) * R.ncell * 2; R.loz = lo[2];
   return R;
+}
+// cheap part of a prism task: false when the prism's top lies below B's lowest point (hfield_prism_task would return false
+// before running GJK); k_collision compacts the live prisms of a pass before the GJK rounds
+DEV bool hfield_prism_live(int t, const HfRange& R, const float* hs, int ncol, const float* data) {
+  const float sz = hs[2], sb = hs[3];
+  const int tri = t & 1, cell = t >> 1, rr = R.rmin + cell / R.ncell, cc = R.cmin + cell % R.ncell;
+  const int cr[3] = {tri ? rr + 1 : rr, rr + 1, rr}, ck[3] = {cc, tri ? cc + 1 : cc, cc + 1};
+  float zmax = -sb;
+#pragma unroll
+  for (int i = 0; i < 3; i++) zmax = fmaxf(zmax, data[cr[i] * ncol + ck[i]] * sz);
+  return !(zmax < R.loz);
 }
 // prism number t (local to the range) against B; true + `one` when they touch within the margin
 DEV bool hfield_prism_task(CvxStage& one, int t, const HfRange& R, float margin, const float* hs, int nrow, int ncol, const float* data,

@@ -9,7 +9,7 @@ W = int(os.environ.get("W", "4096"))
 for wl in os.environ.get("WL", "asimov_toe_full_flat,go1_rough_hf").split(","):
   pb = bench.PhysBench(wl, W, "cuda:0", 0)
   pb.reset_all()
-  for i in range(1, 12):
+  for i in range(1, int(os.environ.get('NSTEP', '12'))):
     pb.one_step(i)
   engine.forward(pb.M, pb.D)
   torch.cuda.synchronize()
@@ -17,4 +17,9 @@ for wl in os.environ.get("WL", "asimov_toe_full_flat,go1_rough_hf").split(","):
   us = t[:, :3] / 1965.0
   print(f"[{wl}] per world: broadphase {us[:,0].mean():.1f} us, narrowphase {us[:,1].mean():.1f} us (max {us[:,1].max():.0f}), of which convex-pair loop {us[:,2].mean():.1f} us; "
         f"survivors {t[:,3].mean():.1f} (max {t[:,3].max():.0f}), convex pairs {t[:,4].mean():.1f} (max {t[:,4].max():.0f}), with a contact {t[:,5].mean():.2f}; ncon {pb.D.ncon.float().mean():.2f}")
+  tot = us[:, 0] + us[:, 1]
+  print("   per-world total us percentiles 50/90/99/99.9/max:", [round(float(np.percentile(tot, q)), 1) for q in (50, 90, 99, 99.9, 100)], "sum over worlds %.1f ms" % (tot.sum() / 1e3),
+        " max-of-4 (CTA) mean %.1f us; worlds > 60 us: %d" % (tot.reshape(-1, 4).max(axis=1).mean(), (tot > 60).sum()))
+  hv = np.argsort(-tot)[:5]
+  print("   heaviest worlds:", [(int(w), round(float(tot[w]), 1), int(t[w, 3]), int(pb.D.ncon[w].item())) for w in hv], "(world, us, survivors, ncon)")
   print("   stage ms", engine.profile_step(pb.M, pb.D, 5))
