@@ -494,7 +494,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     d.geom_bcen = up.raw(bcen); d.geom_bsize = up.raw(bsize); d.geom_brad = up.raw(brad);
   }
   d.col_maxc = col_maxc <= 2 ? 2 : (col_maxc <= 4 ? 4 : 8);
-  d.col_convex = col_convex; d.col_defer = col_defer;
+  d.col_convex = col_convex; d.col_defer = col_defer; d.solve_rowcap = 128;
   d.geom_dataid = up.i(s->geom_dataid, s->ngeom);
   d.mesh_vertadr = up.i(s->mesh_vertadr, s->nmesh); d.mesh_vertnum = up.i(s->mesh_vertnum, s->nmesh);
   {
@@ -584,6 +584,7 @@ extern "C" int b2s_model_set_opt(b2s_model* m, const char* key, double v) {
   const std::string k(key);
   if (k == "ls_parallel") d.ls_parallel = v != 0;
   else if (k == "stage_overlap") m->overlap = v != 0;
+  else if (k == "solve_rowcap") { if (v < 1) return fail("solve_rowcap must be positive"); d.solve_rowcap = (int)v; }
   else if (k == "contact_sensor_maxmatch") d.contact_sensor_maxmatch = (int)v;
   else if (k == "iterations") d.iterations = (int)v;
   else if (k == "ls_iterations") d.ls_iterations = (int)v;
@@ -614,6 +615,7 @@ extern "C" int b2s_model_get_opt(const b2s_model* m, const char* key, double* v)
   const std::string k(key);
   if (k == "ls_parallel") *v = d.ls_parallel;
   else if (k == "stage_overlap") *v = m->overlap;
+  else if (k == "solve_rowcap") *v = d.solve_rowcap;
   else if (k == "contact_sensor_maxmatch") *v = d.contact_sensor_maxmatch;
   else if (k == "iterations") *v = d.iterations;
   else if (k == "ls_iterations") *v = d.ls_iterations;
@@ -905,7 +907,12 @@ static void run_pass(const b2s_model* M, b2s_data* D, cudaStream_t st, bool inte
     { NvtxRange r("collision"); launch_collision(m, d, st); }
   }
   { NvtxRange r("constraint"); launch_constraint(m, d, st); }
-  { NvtxRange r("solve"); launch_solve(m, d, st); }
+  if (fork && solve_has_second_launch(m, d)) {      // the solver's launch for worlds with many rows (normally empty) runs beside the main one
+    cudaEventRecord(D->ev_fork, st); cudaStreamWaitEvent(D->side, D->ev_fork, 0);
+    { NvtxRange r("solve"); launch_solve(m, d, st, D->side); }
+    cudaEventRecord(D->ev_join, D->side);
+    cudaStreamWaitEvent(st, D->ev_join, 0);
+  } else { NvtxRange r("solve"); launch_solve(m, d, st); }
   if (fork && integrate) {
     cudaEventRecord(D->ev_fork2, st); cudaStreamWaitEvent(D->side, D->ev_fork2, 0);
     { NvtxRange r("sensors (side stream)"); launch_sensors(m, d, D->side); }
@@ -949,7 +956,8 @@ extern "C" int b2s_profile_step(const b2s_model* m, b2s_data* d, void* stream, i
   if (!m || !d) return fail("null argument");
   static const char* nm[] = {"position", "dynamics", "collision", "constraint", "solve", "sensors", "integrate"};
   typedef void (*fnT)(const ModelDev&, const DataDev&, cudaStream_t);
-  fnT fn[] = {launch_position, launch_dynamics, launch_collision, launch_constraint, launch_solve, launch_sensors, launch_integrate};
+  fnT fn[] = {launch_position, launch_dynamics, launch_collision, launch_constraint,
+              [](const ModelDev& a, const DataDev& b, cudaStream_t s) { launch_solve(a, b, s); }, launch_sensors, launch_integrate};
   cudaStream_t st = (cudaStream_t)stream;
   float acc[7] = {0, 0, 0, 0, 0, 0, 0};
   for (int r = 0; r < reps; r++) {

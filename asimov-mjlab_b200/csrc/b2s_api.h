@@ -13,7 +13,8 @@ void launch_dynamics(const ModelDev& m, const DataDev& d, cudaStream_t st);
 void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st);
 void launch_constraint(const ModelDev& m, const DataDev& d, cudaStream_t st);
 void launch_efc_jacobian(const ModelDev& m, const DataDev& d, float* J, cudaStream_t st);
-void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st);
+void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st, cudaStream_t side = nullptr);
+bool solve_has_second_launch(const ModelDev& m, const DataDev& d);
 void launch_sensors(const ModelDev& m, const DataDev& d, cudaStream_t st);
 void launch_integrate(const ModelDev& m, const DataDev& d, cudaStream_t st);
 

@@ -42,19 +42,28 @@ __host__ __device__ inline int solve_stage_front_floats(int T) { const int N = 7
 __host__ __device__ inline int solve_chain_floats(int nb, int nchain) { return ((nchain + 3) >> 2) + ((nb + 2) >> 1); }
 __host__ __device__ inline int solve_soff(int njmax, int nconmax, int T) {      // offset of the scratch area
   const int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3;
-  return (HF + 12 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
+  return (HF + 8 * NVP + 6 * N + 3 * njmax + nconmax + 2 + (njmax + 31) / 32 + 3) & ~3;
 }
-__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T, int nchain, int elliptic = 0) {
-  return (solve_stage_front_floats(T) + solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + (elliptic ? 2 * njmax : 0) +
-          solve_chain_floats(nb, nchain) + 3) & ~3;
+// nopt: optional vectors at the very end (CG: gradold, Mgradold; friction-loss rows: fl, frf) -- 4 in every variant but the default one
+__host__ __device__ inline int solve_opt_off(int nb, int njmax, int nconmax, int T, int nchain, int elliptic) {
+  return (solve_soff(njmax, nconmax, T) + solve_scratch_floats(nb) + (elliptic ? 2 * njmax : 0) + solve_chain_floats(nb, nchain) + 3) & ~3;
 }
+__host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int njmax, int nconmax, int T, int nchain, int elliptic = 0, int nopt = 4) {
+  const int NVP = (7 * T + 3) & ~3;
+  return (solve_stage_front_floats(T) + solve_opt_off(nb, njmax, nconmax, T, nchain, elliptic) + nopt * NVP + 3) & ~3;
+}
+// Row capacity of the shared-memory layout.  The default variant (V = 0) is launched with room for ModelDev::solve_rowcap (128) rows instead of
+// njmax: with 8 vectors and 128 rows a G1 world needs 15.2 KB instead of 18.2 KB, which is 14 CTAs per SM instead of 12 -- 4096
+// worlds are 27.7 per SM, i.e. two full rounds instead of two and a third.  Worlds with more rows are solved by a second launch
+// with the full layout (k_constraint queues them separately).
+#define SOLVE_BIG_SPAN 16
 
 // Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
-//   H hdim*ld | invd 7T (padded to a float4 multiple) | 12 vectors of NVP | cdof 6*hdim | Jaref, Jv, D njmax each |
+//   H hdim*ld | invd 7T (padded to a float4 multiple) | 8 vectors of NVP | cdof 6*hdim | Jaref, Jv, D rowcap each |
 //   run list nconmax+2 | active-set bit mask njmax/32 | scratch X/Y 6*max(nb,32), KW 32, Li 32
 template <int T>
 struct SolveCtx {
-  static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 12 * NVP + 6 * N;
+  static constexpr int N = 7 * T, LD = (7 * T + 1) | 1, HF = (N * LD + N + 3) & ~3, NVP = (N + 3) & ~3, FIX = HF + 8 * NVP + 6 * N;
   int lane, nv, nvp, nb, nefc, nl, nf, nrun, njmax, nconmax, soff;
   static constexpr int ld = LD, hfloats = HF;
   const float *M, *G, *aref;      // M: the staged copy in shared memory (row stride nvp)
@@ -62,6 +71,7 @@ struct SolveCtx {
   const unsigned char* chain;     // staged body_chain (dof ids) and body_chain_adr
   const unsigned short* cadr;
   float* sm;
+  float* opt;                     // optional vectors (variants with CG / friction-loss rows only)
   DEV float* H() const { return sm; }
   DEV float* invd() const { return sm + N * LD; }
   DEV float* qacc() const { return sm + HF; }
@@ -72,11 +82,11 @@ struct SolveCtx {
   DEV float* qfs() const { return sm + HF + 5 * NVP; }
   DEV float* qas() const { return sm + HF + 6 * NVP; }
   DEV float* qfc() const { return sm + HF + 7 * NVP; }
-  DEV float* gradold() const { return sm + HF + 8 * NVP; }     // CG only
-  DEV float* Mgradold() const { return sm + HF + 9 * NVP; }    // CG only
-  DEV float* fl() const { return sm + HF + 10 * NVP; }         // friction-loss rows: f of row r < nf
-  DEV float* frf() const { return sm + HF + 11 * NVP; }        // and R f = f / D, the half width of the quadratic zone
-  DEV float* cdof() const { return sm + HF + 12 * NVP; }
+  DEV float* gradold() const { return opt; }                   // CG only
+  DEV float* Mgradold() const { return opt + NVP; }            // CG only
+  DEV float* fl() const { return opt + 2 * NVP; }              // friction-loss rows: f of row r < nf
+  DEV float* frf() const { return opt + 3 * NVP; }             // and R f = f / D, the half width of the quadratic zone
+  DEV float* cdof() const { return sm + HF + 8 * NVP; }
   DEV float* Jaref() const { return sm + FIX; }
   DEV float* Jv() const { return sm + FIX + njmax; }
   DEV float* D() const { return sm + FIX + 2 * njmax; }
@@ -589,17 +599,30 @@ DEV void factor_H(const SolveCtx<T>& c, int bi, int bj) {
   tile_cholesky_regs<T>(a, bi, bj, c.H(), c.ld, c.invd());
 }
 
-template <int T, int V>
+// big = 0: shared-memory layout with rows_cap(njmax, V) rows, worlds with more rows are left to the second launch (big = 1: the
+// full layout, only worlds the first launch skipped)
+__host__ __device__ inline int rows_cap(int njmax, int V, int big, int cap) { return (V == 0 && !big && njmax > cap) ? cap : njmax; }
+template <int T, int V, bool BIG = false>
 __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const ModelDev m, const DataDev d) {
+  constexpr int big = BIG ? 1 : 0;
   constexpr bool FRIC = (V & 1) != 0, ELL = (V & 2) != 0; (void)FRIC; (void)ELL;   // variant bits: friction-loss rows, elliptic cones
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #ifdef SOLVE_TIMING
   const long long t_start = clock64();      // development builds only (tools/exp_solve_time.py): per-world solve time in cycles -> solver_cost
 #endif
-  // worlds are taken from the cost-ordered queues, most expensive class first (k_constraint filled them)
-  int w = blockIdx.x * SOLVE_WARPS + warp;
-  if (w >= d.nworld) return;
-  {
+  // big = 0: worlds are taken from the cost-ordered queues, most expensive class first (k_constraint filled them), one per CTA.
+  // big = 1 (a small grid, normally nothing to do): CTA b looks at worlds 16 b .. 16 b + 15 and solves those with more than
+  // solve_rowcap rows one after the other.
+#pragma unroll 1
+  for (int slot = 0; slot < (big ? SOLVE_BIG_SPAN : 1); slot++) {
+  int w;
+  if (big) {
+    w = blockIdx.x * SOLVE_BIG_SPAN + slot;
+    if (w >= d.nworld) break;
+    if (d.nefc[w] <= m.solve_rowcap) continue;
+  } else {
+    w = blockIdx.x * SOLVE_WARPS + warp;
+    if (w >= d.nworld) return;
     int cls = B2S_SOLVE_CLASSES - 1, before = 0;
 #pragma unroll 1
     for (; cls > 0; cls--) { const int n = d.solve_count[cls]; if (w < before + n) break; before += n; }
@@ -608,19 +631,22 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
     B2S_ASSERT(w >= 0 && w < d.nworld);
   }
   const int nv = m.nv, nvp = m.nvp, nb = m.nbody, njmax = d.njmax;
+  const int rcap = rows_cap(njmax, V, big, m.solve_rowcap);       // rows the shared-memory layout holds (global arrays keep the stride njmax)
   SolveCtx<T> c;
-  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.nf = FRIC ? d.nf[w] : 0; c.njmax = njmax; c.nconmax = d.nconmax;
-  c.soff = solve_soff(njmax, d.nconmax, T);
+  c.lane = lane; c.nv = nv; c.nvp = nvp; c.nb = nb; c.nefc = d.nefc[w]; c.nl = d.nl[w]; c.nf = FRIC ? d.nf[w] : 0; c.njmax = rcap; c.nconmax = d.nconmax;
+  if (V == 0 && njmax > m.solve_rowcap && (c.nefc > m.solve_rowcap) != (big != 0)) continue;      // the other launch's world
+  c.soff = solve_soff(rcap, d.nconmax, T);
   c.G = d.efc_g + (size_t)w * njmax * 6;
   c.bp = d.efc_bp + (size_t)w * njmax;
   c.aref = d.efc_aref + (size_t)w * njmax;
-  float* const wbase = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, njmax, d.nconmax, T, m.nchain, ELL ? 1 : 0);
+  float* const wbase = b2s_smem + (size_t)warp * solve_smem_floats(nv, nvp, nb, rcap, d.nconmax, T, m.nchain, ELL ? 1 : 0, V == 0 ? 0 : 4);
   float* const Msm = wbase;                                                    // staged mass matrix (16-byte aligned)
   unsigned long long* const mbar = reinterpret_cast<unsigned long long*>(wbase + solve_stage_front_floats(T) - 4);
   c.M = Msm;
   c.sm = wbase + solve_stage_front_floats(T);
   {
-    float* tail = c.sm + c.soff + solve_scratch_floats(nb) + (ELL ? 2 * njmax : 0);
+    float* tail = c.sm + c.soff + solve_scratch_floats(nb) + (ELL ? 2 * rcap : 0);
+    c.opt = c.sm + solve_opt_off(nb, rcap, d.nconmax, T, m.nchain, ELL ? 1 : 0);
     c.chain = reinterpret_cast<const unsigned char*>(tail);
     c.cadr = reinterpret_cast<const unsigned short*>(tail + ((m.nchain + 3) >> 2));
   }
@@ -640,7 +666,7 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
 #pragma unroll 1
     for (int i = lane; i < nv; i += 32) { g_qacc[i] = c.qas()[i]; g_qfc[i] = 0.f; }
     if (lane == 0) { d.solver_niter[w] = 0; d.solver_cost[w] = 0.f; }
-    return;
+    continue;
   }
   // ---- staging.  The world's mass matrix comes in by ONE bulk async copy (TMA, cp.async.bulk): lane 0 arms the mbarrier with
   // the byte count and issues it, the copy engine fills shared memory while the warp runs the rest of the prologue, and
@@ -842,6 +868,12 @@ __global__ void __launch_bounds__(32 * SOLVE_WARPS, SOLVE_MINB) k_solve(const Mo
 #ifdef SOLVE_TIMING
   if (lane == 0) d.solver_cost[w] = (float)(clock64() - t_start);
 #endif
+  if (big) {      // the next world of this CTA re-arms the barrier and reuses the shared memory
+    __syncwarp();
+    if (lane == 0) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(mbar)) : "memory");
+    __syncwarp();
+  }
+  }
 }
 
 static int tile_for(int nv) { return b2s_tile_for(nv); }
@@ -859,20 +891,35 @@ static int tile_for(int nv) { return b2s_tile_for(nv); }
 
 // the friction-loss instantiation is only used by models that can have such rows (ModelDev::fric): the default kernel
 // carries none of that code
-void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st) {
+static int solve_variant(const ModelDev& m) {
+  if (!m.ls_parallel || m.solver != B2S_SOL_NEWTON) return 7;
+  if (m.cone == B2S_CONE_ELLIPTIC) return 3;
+  return m.fric ? 1 : 0;
+}
+static size_t smem_solve_v(const ModelDev& m, const DataDev& d, int V, int big) {
+  // the elliptic per-row arrays exist in every instantiation that has the elliptic code (variants 3 and 7)
+  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, rows_cap(d.njmax, V, big, m.solve_rowcap), d.nconmax, tile_for(m.nv), m.nchain, V >= 3 ? 1 : 0, V == 0 ? 0 : 4) * sizeof(float);
+}
+// `side` (optional): the stream the second launch goes to; the caller has already made it wait for k_constraint and joins it after
+// the call.  The second launch normally finds nothing to do, so beside the main launch it costs nothing; behind it, it cost 7 us.
+void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st, cudaStream_t side) {
   const int grid = (d.nworld + SOLVE_WARPS - 1) / SOLVE_WARPS;
-  const size_t smem = smem_solve(m, d);
-  if (!m.ls_parallel || m.solver != B2S_SOL_NEWTON) { SOLVE_DISPATCH((k_solve<T, 7><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
-  else if (m.cone == B2S_CONE_ELLIPTIC) { SOLVE_DISPATCH((k_solve<T, 3><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
-  else if (m.fric) { SOLVE_DISPATCH((k_solve<T, 1><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
-  else { SOLVE_DISPATCH((k_solve<T, 0><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  const int V = solve_variant(m);
+  const size_t smem = smem_solve_v(m, d, V, 0);
+  if (V == 7) { SOLVE_DISPATCH((k_solve<T, 7><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  else if (V == 3) { SOLVE_DISPATCH((k_solve<T, 3><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  else if (V == 1) { SOLVE_DISPATCH((k_solve<T, 1><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
+  else {
+    SOLVE_DISPATCH((k_solve<T, 0><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d)));
+    if (solve_has_second_launch(m, d)) {     // worlds with more than solve_rowcap rows: same kernel, full layout
+      SOLVE_DISPATCH((k_solve<T, 0, true><<<(d.nworld + SOLVE_BIG_SPAN - 1) / SOLVE_BIG_SPAN, 32, smem_solve_v(m, d, 0, 1) / SOLVE_WARPS, side ? side : st>>>(m, d)));
+      b2s_count_launch();
+    }
+  }
   b2s_count_launch();
 }
-size_t smem_solve(const ModelDev& m, const DataDev& d) {
-  // the elliptic per-row arrays exist in every instantiation that has the elliptic code (variants 3 and 7)
-  const bool ell = m.cone == B2S_CONE_ELLIPTIC || !m.ls_parallel || m.solver != B2S_SOL_NEWTON;
-  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, d.njmax, d.nconmax, tile_for(m.nv), m.nchain, ell) * sizeof(float);
-}
+bool solve_has_second_launch(const ModelDev& m, const DataDev& d) { return solve_variant(m) == 0 && d.njmax > m.solve_rowcap; }
+size_t smem_solve(const ModelDev& m, const DataDev& d) { return smem_solve_v(m, d, solve_variant(m), 1); }
 // Raise the dynamic shared-memory limit of EVERY solver instantiation of this model's tile size to the largest request any
 // option combination can make (the elliptic variants carry 2 njmax extra floats): Model.opt.cone / solver / ls_parallel and a
 // per-world dof_frictionloss can switch the instantiation after put_data.
@@ -880,6 +927,7 @@ template <int T>
 static int solve_set_attr(int device, size_t smem) {
   int rc = 0;
   rc |= b2s_raise_smem(device, (const void*)k_solve<T, 0>, smem);
+  rc |= b2s_raise_smem(device, (const void*)k_solve<T, 0, true>, smem);
   rc |= b2s_raise_smem(device, (const void*)k_solve<T, 1>, smem);
   rc |= b2s_raise_smem(device, (const void*)k_solve<T, 3>, smem);
   rc |= b2s_raise_smem(device, (const void*)k_solve<T, 7>, smem);

@@ -117,7 +117,7 @@ class _Handle:
 
 
 _OPT_KEYS = ("ls_parallel", "contact_sensor_maxmatch", "iterations", "ls_iterations", "tolerance", "ls_tolerance",
-             "impratio", "integrator", "cone", "solver", "disableflags", "ls_parallel_min_step", "stage_overlap")
+             "impratio", "integrator", "cone", "solver", "disableflags", "ls_parallel_min_step", "stage_overlap", "solve_rowcap")
 
 
 class _Option:

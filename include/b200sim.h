@@ -253,7 +253,11 @@ int b2s_model_destroy(b2s_model* m);
 /* Settable options after creation (sim.py:117-118, tests/test_sim.py:71-82).
  * Keys: "ls_parallel", "contact_sensor_maxmatch", "iterations", "ls_iterations",
  * "tolerance", "ls_tolerance", "timestep", "impratio", "integrator", "cone",
- * "gravity_x", "gravity_y", "gravity_z", "disableflags", "ls_parallel_min_step". */
+ * "gravity_x", "gravity_y", "gravity_z", "disableflags", "ls_parallel_min_step", "solver",
+ * and two scheduling knobs without a counterpart in the reference: "stage_overlap" (0 / 1) and
+ * "solve_rowcap" (rows the default solver launch holds in shared memory, default 128; worlds with
+ * more rows are solved by a second launch sized for njmax; results do not depend on it).
+ * Changing an option after a graph was captured needs a new capture, as in the reference. */
 int b2s_model_set_opt(b2s_model* m, const char* key, double value);
 int b2s_model_get_opt(const b2s_model* m, const char* key, double* value);
 /* expand_model_fields: give `name` per-world storage (leading dim nworld).

@@ -593,3 +593,36 @@ def test_asimov12_full_collision_mesh_mesh_contacts_match_oracle(asimov12_full, 
     st.report("asimov 12-dof, full collision, random poses")
   assert (7, 7) in st.seen and st.ncmp > 150
   assert st.identical >= 0.9 * st.states and st.tight >= 0.9 * st.ncmp, (st.identical, st.states, st.ncmp, st.tight)
+
+
+def test_solver_row_capacity_split_is_bit_identical(g1):
+  """The default solver variant runs with a shared-memory layout for `solve_rowcap` rows (128) and leaves worlds with more rows to a
+  second launch that has room for njmax.  With the capacity forced down to 24 rows the G1 worlds are spread over BOTH launches
+  (a standing G1 has ~50 rows, a flying one a handful of limit rows): results must not depend on which launch solved a world."""
+  import torch
+  from test_gpu_parity import _setup, _check_counts, _rel_err
+  W = 64
+  qpos, qvel, ctrl = g1_states(g1, W, seed=11, spread=0.15, vel=0.2)
+  qpos[::4, 2] += 1.0      # a quarter of the worlds in the air: few rows
+  engine, M, D, orc, worlds = _setup(g1, W, qpos, qvel, ctrl, True)
+  assert M.opt.solve_rowcap == 128
+  engine.step(M, D, 3)
+  ref = {f: getattr(D, f).clone() for f in ("qpos", "qvel", "qacc", "efc_force", "solver_niter", "sensordata")}
+  nefc = D.nefc.cpu().numpy()
+  for cap in (24, 1, 100000):
+    M.opt.solve_rowcap = cap
+    for name, arr in (("qpos", qpos), ("qvel", qvel), ("ctrl", ctrl)):
+      getattr(D, name)[:] = torch.as_tensor(np.asarray(arr), dtype=torch.float32, device="cuda:0")
+    D.qacc_warmstart.zero_(); D.time.zero_()
+    n0 = engine.launch_count()
+    engine.step(M, D, 3)
+    torch.cuda.synchronize()
+    assert engine.launch_count() - n0 == 3 * (8 if cap < D.njmax else 7)
+    for f, r in ref.items():
+      assert torch.equal(getattr(D, f), r), (cap, f)
+  assert (nefc > 24).sum() > 8 and (nefc <= 24).sum() > 8, nefc      # both launches had worlds at cap = 24
+  M.opt.solve_rowcap = 24
+  for w in worlds:
+    orc.step(w, 3)
+  _check_counts(D, worlds)
+  assert _rel_err(D, worlds, "qpos") < 1e-5 and _rel_err(D, worlds, "qvel") < 2e-3
