@@ -71,6 +71,7 @@ struct b2s_data {
   // fork / join of independent stages (collision beside dynamics, sensors beside the integrator): one internal side stream,
   // forked from and joined back into the caller's stream with these events, so a stream capture records a DAG
   cudaStream_t side = nullptr;
+  cudaStream_t side_hi = nullptr;     // highest priority: the solver's launch for worlds with many rows must get its CTAs in before the main launch fills the machine
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr;
   float* efc_J = nullptr;    // dense Jacobian, allocated and filled on demand (b2s_efc_jacobian)
   ~b2s_data() {
@@ -79,6 +80,7 @@ struct b2s_data {
     if (have_ev) for (auto& e : ev) cudaEventDestroy(e);
     for (cudaEvent_t e : {ev_fork, ev_join, ev_fork2, ev_join2}) if (e) cudaEventDestroy(e);
     if (side) cudaStreamDestroy(side);
+    if (side_hi) cudaStreamDestroy(side_hi);
   }
 };
 
@@ -819,6 +821,11 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
   for (auto& e : D->ev) cudaEventCreate(&e);
   D->have_ev = true;
   if (cudaStreamCreateWithFlags(&D->side, cudaStreamNonBlocking) != cudaSuccess) { delete D; return fail("cannot create the side stream"); }
+  {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if (cudaStreamCreateWithPriority(&D->side_hi, cudaStreamNonBlocking, hi) != cudaSuccess) { delete D; return fail("cannot create the priority side stream"); }
+  }
   for (cudaEvent_t* e : {&D->ev_fork, &D->ev_join, &D->ev_fork2, &D->ev_join2})
     if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess) { delete D; return fail("cannot create the fork/join events"); }
   // frames of everything attached to static bodies, once
@@ -891,6 +898,17 @@ struct NvtxRange {
   explicit NvtxRange(const char* name) { if (g_nvtx) nvtxRangePushA(name); }
   ~NvtxRange() { if (g_nvtx) nvtxRangePop(); }
 };
+// the solver's launch for worlds with many rows (normally empty) runs beside the main one, on the priority stream
+static void solve_stage(const b2s_model* M, b2s_data* D, cudaStream_t st, bool fork) {
+  const ModelDev& m = M->dev; const DataDev& d = D->dev;
+  NvtxRange r("solve");
+  if (fork && solve_has_second_launch(m, d)) {
+    cudaEventRecord(D->ev_fork, st); cudaStreamWaitEvent(D->side_hi, D->ev_fork, 0);
+    launch_solve(m, d, st, D->side_hi);
+    cudaEventRecord(D->ev_join, D->side_hi);
+    cudaStreamWaitEvent(st, D->ev_join, 0);
+  } else launch_solve(m, d, st);
+}
 static void run_pass(const b2s_model* M, b2s_data* D, cudaStream_t st, bool integrate) {
   const ModelDev& m = M->dev; const DataDev& d = D->dev;
   const bool fork = M->overlap != 0;
@@ -907,12 +925,7 @@ static void run_pass(const b2s_model* M, b2s_data* D, cudaStream_t st, bool inte
     { NvtxRange r("collision"); launch_collision(m, d, st); }
   }
   { NvtxRange r("constraint"); launch_constraint(m, d, st); }
-  if (fork && solve_has_second_launch(m, d)) {      // the solver's launch for worlds with many rows (normally empty) runs beside the main one
-    cudaEventRecord(D->ev_fork, st); cudaStreamWaitEvent(D->side, D->ev_fork, 0);
-    { NvtxRange r("solve"); launch_solve(m, d, st, D->side); }
-    cudaEventRecord(D->ev_join, D->side);
-    cudaStreamWaitEvent(st, D->ev_join, 0);
-  } else { NvtxRange r("solve"); launch_solve(m, d, st); }
+  solve_stage(M, D, st, fork);
   if (fork && integrate) {
     cudaEventRecord(D->ev_fork2, st); cudaStreamWaitEvent(D->side, D->ev_fork2, 0);
     { NvtxRange r("sensors (side stream)"); launch_sensors(m, d, D->side); }
@@ -962,7 +975,10 @@ extern "C" int b2s_profile_step(const b2s_model* m, b2s_data* d, void* stream, i
   float acc[7] = {0, 0, 0, 0, 0, 0, 0};
   for (int r = 0; r < reps; r++) {
     cudaEventRecord(d->ev[0], st);
-    for (int k = 0; k < 7; k++) { fn[k](m->dev, d->dev, st); cudaEventRecord(d->ev[k + 1], st); }
+    for (int k = 0; k < 7; k++) {
+      if (k == 4) solve_stage(m, d, st, m->overlap != 0); else fn[k](m->dev, d->dev, st);
+      cudaEventRecord(d->ev[k + 1], st);
+    }
     CU(cudaStreamSynchronize(st));
     for (int k = 0; k < 7; k++) { float t = 0; cudaEventElapsedTime(&t, d->ev[k], d->ev[k + 1]); acc[k] += t; }
   }

@@ -56,7 +56,7 @@ __host__ __device__ inline int solve_smem_floats(int nv, int nvp, int nb, int nj
 // njmax: with 8 vectors and 128 rows a G1 world needs 15.2 KB instead of 18.2 KB, which is 14 CTAs per SM instead of 12 -- 4096
 // worlds are 27.7 per SM, i.e. two full rounds instead of two and a third.  Worlds with more rows are solved by a second launch
 // with the full layout (k_constraint queues them separately).
-#define SOLVE_BIG_SPAN 16
+#define SOLVE_BIG_SPAN 1       // worlds one CTA of the second launch looks at (16 was tried: a model whose worlds often exceed the capacity -- Asimov-toe -- then solves them 16 deep)
 
 // Per-warp shared-memory layout with compile-time offsets (one base register instead of ~18 pointers):
 //   H hdim*ld | invd 7T (padded to a float4 multiple) | 8 vectors of NVP | cdof 6*hdim | Jaref, Jv, D rowcap each |
@@ -896,30 +896,43 @@ static int solve_variant(const ModelDev& m) {
   if (m.cone == B2S_CONE_ELLIPTIC) return 3;
   return m.fric ? 1 : 0;
 }
-static size_t smem_solve_v(const ModelDev& m, const DataDev& d, int V, int big) {
+static size_t smem_solve_c(const ModelDev& m, const DataDev& d, int V, int rows) {
   // the elliptic per-row arrays exist in every instantiation that has the elliptic code (variants 3 and 7)
-  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, rows_cap(d.njmax, V, big, m.solve_rowcap), d.nconmax, tile_for(m.nv), m.nchain, V >= 3 ? 1 : 0, V == 0 ? 0 : 4) * sizeof(float);
+  return (size_t)SOLVE_WARPS * solve_smem_floats(m.nv, m.nvp, m.nbody, rows, d.nconmax, tile_for(m.nv), m.nchain, V >= 3 ? 1 : 0, V == 0 ? 0 : 4) * sizeof(float);
 }
+// CTAs per SM at a given shared-memory request: 228 KB per SM, 1 KB reserved per CTA, and the register bound of __launch_bounds__
+static int solve_slots(size_t smem) { const int s = (int)(233472 / (smem + 1024)); return s < SOLVE_MINB ? s : SOLVE_MINB; }
+// Row capacity the default variant's main launch really uses: the requested one (Model.opt.solve_rowcap) where the smaller layout
+// buys CTAs per SM (G1: 12 -> 14), njmax (one launch, no split) where it does not (a 20-dof Asimov is register-bound at 16 either
+// way, and its few worlds with > 128 rows would only pay for the second launch).
+static int solve_eff_cap(const ModelDev& m, const DataDev& d) {
+  if (solve_variant(m) != 0 || d.njmax <= m.solve_rowcap) return d.njmax;
+  return solve_slots(smem_solve_c(m, d, 0, m.solve_rowcap)) > solve_slots(smem_solve_c(m, d, 0, d.njmax)) ? m.solve_rowcap : d.njmax;
+}
+bool solve_has_second_launch(const ModelDev& m, const DataDev& d) { return solve_eff_cap(m, d) < d.njmax; }
 // `side` (optional): the stream the second launch goes to; the caller has already made it wait for k_constraint and joins it after
 // the call.  The second launch normally finds nothing to do, so beside the main launch it costs nothing; behind it, it cost 7 us.
-void launch_solve(const ModelDev& m, const DataDev& d, cudaStream_t st, cudaStream_t side) {
+void launch_solve(const ModelDev& m0, const DataDev& d, cudaStream_t st, cudaStream_t side) {
   const int grid = (d.nworld + SOLVE_WARPS - 1) / SOLVE_WARPS;
-  const int V = solve_variant(m);
-  const size_t smem = smem_solve_v(m, d, V, 0);
+  const int V = solve_variant(m0);
+  ModelDev m = m0;
+  m.solve_rowcap = solve_eff_cap(m0, d);      // the kernels read the capacity from their copy of the model
+  const size_t smem = smem_solve_c(m, d, V, V == 0 ? m.solve_rowcap : d.njmax);
   if (V == 7) { SOLVE_DISPATCH((k_solve<T, 7><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   else if (V == 3) { SOLVE_DISPATCH((k_solve<T, 3><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   else if (V == 1) { SOLVE_DISPATCH((k_solve<T, 1><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d))); }
   else {
-    SOLVE_DISPATCH((k_solve<T, 0><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d)));
-    if (solve_has_second_launch(m, d)) {     // worlds with more than solve_rowcap rows: same kernel, full layout
-      SOLVE_DISPATCH((k_solve<T, 0, true><<<(d.nworld + SOLVE_BIG_SPAN - 1) / SOLVE_BIG_SPAN, 32, smem_solve_v(m, d, 0, 1) / SOLVE_WARPS, side ? side : st>>>(m, d)));
+    // the second launch goes FIRST: its few worlds are the most expensive ones of the step (most rows), and behind the main launch's
+    // 4096 CTAs they would start half a kernel late (Asimov-toe: 25 such worlds cost 55 us per sub-step that way)
+    if (m.solve_rowcap < d.njmax) {     // worlds with more than solve_rowcap rows: same kernel, full layout
+      SOLVE_DISPATCH((k_solve<T, 0, true><<<(d.nworld + SOLVE_BIG_SPAN - 1) / SOLVE_BIG_SPAN, 32, smem_solve_c(m, d, 0, d.njmax) / SOLVE_WARPS, side ? side : st>>>(m, d)));
       b2s_count_launch();
     }
+    SOLVE_DISPATCH((k_solve<T, 0><<<grid, 32 * SOLVE_WARPS, smem, st>>>(m, d)));
   }
   b2s_count_launch();
 }
-bool solve_has_second_launch(const ModelDev& m, const DataDev& d) { return solve_variant(m) == 0 && d.njmax > m.solve_rowcap; }
-size_t smem_solve(const ModelDev& m, const DataDev& d) { return smem_solve_v(m, d, solve_variant(m), 1); }
+size_t smem_solve(const ModelDev& m, const DataDev& d) { return smem_solve_c(m, d, solve_variant(m), d.njmax); }
 // Raise the dynamic shared-memory limit of EVERY solver instantiation of this model's tile size to the largest request any
 // option combination can make (the elliptic variants carry 2 njmax extra floats): Model.opt.cone / solver / ls_parallel and a
 // per-world dof_frictionloss can switch the instantiation after put_data.
