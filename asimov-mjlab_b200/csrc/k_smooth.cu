@@ -303,9 +303,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
     for (int k = 0; k < 10; k++) acc[k] = 0.f;
     const int e = m.body_subtree_end[b];
     for (int j = b; j < e; j++) {
-      const float* c = s_cin + 10 * j;
+      const float2* c = reinterpret_cast<const float2*>(s_cin + 10 * j);      // 40-byte stride from an 8-byte aligned base
 #pragma unroll
-      for (int k = 0; k < 10; k++) acc[k] += c[k];
+      for (int k = 0; k < 5; k++) { const float2 v = c[k]; acc[2 * k] += v.x; acc[2 * k + 1] += v.y; }
     }
 #pragma unroll
     for (int k = 0; k < 10; k++) s_crb[10 * b + k] = acc[k];
@@ -317,26 +317,26 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
     const int c0 = m.body_chain_adr[b], c1 = m.body_chain_adr[b + 1], own = m.body_dofadr[b];
     const int nown = m.body_dofnum[b];
     int c = c0;
-    for (; c < c1 - nown; c++) { const int j = m.body_chain[c]; axpy6(v, s_qvel[j], ld6(s_cdof + 6 * j)); }
+    for (; c < c1 - nown; c++) { const int j = m.body_chain[c]; axpy6(v, s_qvel[j], ld6s(s_cdof + 6 * j)); }
     // own joints, in order
     const int jn = m.body_jntnum[b], ja = m.body_jntadr[b];
     for (int jj = 0; jj < jn; jj++) {
       const int t = m.jnt_type[ja + jj];
       int da = m.jnt_dofadr[ja + jj];
       if (t == B2S_JNT_FREE) {
-        for (int a = 0; a < 3; a++) { st6(s_cdd + 6 * (da + a), zero6()); axpy6(v, s_qvel[da + a], ld6(s_cdof + 6 * (da + a))); }
+        for (int a = 0; a < 3; a++) { st6s(s_cdd + 6 * (da + a), zero6()); axpy6(v, s_qvel[da + a], ld6s(s_cdof + 6 * (da + a))); }
         da += 3;
       }
       if (t == B2S_JNT_FREE || t == B2S_JNT_BALL) {
-        for (int a = 0; a < 3; a++) st6(s_cdd + 6 * (da + a), cross_motion(v, ld6(s_cdof + 6 * (da + a))));
-        for (int a = 0; a < 3; a++) axpy6(v, s_qvel[da + a], ld6(s_cdof + 6 * (da + a)));
+        for (int a = 0; a < 3; a++) st6s(s_cdd + 6 * (da + a), cross_motion(v, ld6s(s_cdof + 6 * (da + a))));
+        for (int a = 0; a < 3; a++) axpy6(v, s_qvel[da + a], ld6s(s_cdof + 6 * (da + a)));
       } else {
-        st6(s_cdd + 6 * da, cross_motion(v, ld6(s_cdof + 6 * da)));
-        axpy6(v, s_qvel[da], ld6(s_cdof + 6 * da));
+        st6s(s_cdd + 6 * da, cross_motion(v, ld6s(s_cdof + 6 * da)));
+        axpy6(v, s_qvel[da], ld6s(s_cdof + 6 * da));
       }
     }
     (void)own;
-    st6(s_cvel + 6 * b, v);
+    st6s(s_cvel + 6 * b, v);
   }
   __syncwarp();
   for (int i = lane; i < 6 * nb; i += 32) d.cvel[(size_t)w * 6 * nb + i] = s_cvel[i];
@@ -345,12 +345,12 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
   const float* armature = m.dof_armature.at(w);
   for (int i = lane; i < nv; i += 32) {
     const int b = m.dof_bodyid[i];
-    sv6 buf = mul_inert(s_crb + 10 * b, ld6(s_cdof + 6 * i));
+    sv6 buf = mul_inert(s_crb + 10 * b, ld6s(s_cdof + 6 * i));
     const int c0 = m.body_chain_adr[b], c1 = m.body_chain_adr[b + 1];
     for (int c = c0; c < c1; c++) {
       const int j = m.body_chain[c];
       if (j > i) break;
-      float v = dot6(ld6(s_cdof + 6 * j), buf);
+      float v = dot6(ld6s(s_cdof + 6 * j), buf);
       if (j == i) v += armature[i];
       s_M[i * (i + 1) / 2 + j] = v;
     }
@@ -365,9 +365,9 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
       sv6 f = zero6(), fe = zero6();
       if (b > 0) {
         const int c0 = m.body_chain_adr[b], c1 = m.body_chain_adr[b + 1];
-        for (int c = c0; c < c1; c++) { const int j = m.body_chain[c]; axpy6(a, s_qvel[j], ld6(s_cdd + 6 * j)); }
+        for (int c = c0; c < c1; c++) { const int j = m.body_chain[c]; axpy6(a, s_qvel[j], ld6s(s_cdd + 6 * j)); }
         const float* I = d.cinert + ((size_t)w * nb + b) * 10;
-        sv6 v = ld6(s_cvel + 6 * b);
+        sv6 v = ld6s(s_cvel + 6 * b);
         f = mul_inert(I, a);
         sv6 g = cross_force(v, mul_inert(I, v));
         axpy6(f, 1.0f, g);
@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
           fe.v[0] = t.x; fe.v[1] = t.y; fe.v[2] = t.z; fe.v[3] = frc.x; fe.v[4] = frc.y; fe.v[5] = frc.z;
         }
       }
-      st6(s_cfrc + 6 * b, f); st6(s_fext + 6 * b, fe);
+      st6s(s_cfrc + 6 * b, f); st6s(s_fext + 6 * b, fe);
     }
   }
   __syncwarp();
@@ -466,8 +466,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_dynamics(const Model
     for (int i = lane; i < nv; i += 32) {
       const int b = m.dof_bodyid[i], e = m.body_subtree_end[b];
       sv6 fs = zero6(), es = zero6();
-      for (int j = b; j < e; j++) { axpy6(fs, 1.0f, ld6(s_cfrc + 6 * j)); axpy6(es, 1.0f, ld6(s_fext + 6 * j)); }
-      sv6 cd = ld6(s_cdof + 6 * i);
+      for (int j = b; j < e; j++) { axpy6(fs, 1.0f, ld6s(s_cfrc + 6 * j)); axpy6(es, 1.0f, ld6s(s_fext + 6 * j)); }
+      sv6 cd = ld6s(s_cdof + 6 * i);
       const float bias = dot6(cd, fs), ext = dot6(cd, es);
       float pas = 0.f;
       if (passive) {
