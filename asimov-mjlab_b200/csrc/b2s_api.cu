@@ -51,7 +51,8 @@ struct FieldRec {
 
 struct b2s_model {
   int device = 0;
-  int overlap = 1;           // independent stages of a step run on a forked branch (option "stage_overlap")
+  int overlap = 1;           // option "stage_overlap": 0 serial stages; 1 collision beside dynamics, sensors beside the integrator and the solver's second
+                             // launch on side streams; 2 only the solver's second launch.  Set per model at creation (see b2s_model_create)
   ModelDev dev;
   std::vector<void*> allocs;
   std::vector<FieldRec> fields;
@@ -497,6 +498,10 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   }
   d.col_maxc = col_maxc <= 2 ? 2 : (col_maxc <= 4 ? 4 : 8);
   d.col_convex = col_convex; d.col_defer = col_defer; d.solve_rowcap = 128;
+  // stage overlap by default (measured at 4096 worlds, tools/ab7.sh): the side-stream branches pay for the small models (Go1 +2.5 %, on
+  // height fields +6 %, Asimov +1.4 %) and cost where the stage kernels fill the register file by themselves (G1: -0.6 %) or where
+  // collision is three launches with a persistent task kernel that then fights dynamics for CTA slots (Asimov FULL: -11 %)
+  m->overlap = (col_defer || d.nv >= 30) ? 2 : 1;
   d.geom_dataid = up.i(s->geom_dataid, s->ngeom);
   d.mesh_vertadr = up.i(s->mesh_vertadr, s->nmesh); d.mesh_vertnum = up.i(s->mesh_vertnum, s->nmesh);
   {
@@ -585,7 +590,7 @@ extern "C" int b2s_model_set_opt(b2s_model* m, const char* key, double v) {
   ModelDev& d = m->dev;
   const std::string k(key);
   if (k == "ls_parallel") d.ls_parallel = v != 0;
-  else if (k == "stage_overlap") m->overlap = v != 0;
+  else if (k == "stage_overlap") m->overlap = (int)v;      // 0: serial, 1: collision / sensors / the solver's second launch on side streams, 2: only the solver's second launch
   else if (k == "solve_rowcap") { if (v < 1) return fail("solve_rowcap must be positive"); d.solve_rowcap = (int)v; }
   else if (k == "contact_sensor_maxmatch") d.contact_sensor_maxmatch = (int)v;
   else if (k == "iterations") d.iterations = (int)v;
@@ -911,7 +916,7 @@ static void solve_stage(const b2s_model* M, b2s_data* D, cudaStream_t st, bool f
 }
 static void run_pass(const b2s_model* M, b2s_data* D, cudaStream_t st, bool integrate) {
   const ModelDev& m = M->dev; const DataDev& d = D->dev;
-  const bool fork = M->overlap != 0;
+  const bool fork = M->overlap == 1;
   NvtxRange pass(integrate ? "b2s step" : "b2s forward");
   { NvtxRange r("position"); launch_position(m, d, st); }
   if (fork) {
@@ -925,7 +930,7 @@ static void run_pass(const b2s_model* M, b2s_data* D, cudaStream_t st, bool inte
     { NvtxRange r("collision"); launch_collision(m, d, st); }
   }
   { NvtxRange r("constraint"); launch_constraint(m, d, st); }
-  solve_stage(M, D, st, fork);
+  solve_stage(M, D, st, M->overlap != 0);
   if (fork && integrate) {
     cudaEventRecord(D->ev_fork2, st); cudaStreamWaitEvent(D->side, D->ev_fork2, 0);
     { NvtxRange r("sensors (side stream)"); launch_sensors(m, d, D->side); }

@@ -298,8 +298,11 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
     const float* mass = m.body_mass.at(w);
     const float* inertia = m.body_inertia.at(w);
     for (int b = lane; b < nb; b += 32) {
-      sv6 v = object_velocity(m, cvel, com, b, ld3(xipos + 3 * b));
-      st6(s_bvel + 6 * b, v);
+      const v3 xi = ld3(xipos + 3 * b);
+      sv6 v = object_velocity(m, cvel, com, b, xi);
+      // s_bvel: [xipos | linear velocity] -- the angular part is only needed for s_am below, and the angular-momentum loop wants
+      // the inertial-frame positions of the whole subtree from shared memory (it read xipos and mass from global memory per term)
+      st3(s_bvel + 6 * b, xi); st3(s_bvel + 6 * b + 3, mk3(v.v[3], v.v[4], v.v[5]));
       st3(s_lm + 3 * b, mk3(v.v[3], v.v[4], v.v[5]) * mass[b]);
       m33 R = ldm(d.ximat + ((size_t)w * nb + b) * 9);
       v3 loc = mulTv(R, mk3(v.v[0], v.v[1], v.v[2]));
@@ -316,14 +319,17 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_sensors(const ModelD
       st3(d.subtree_linvel + ((size_t)w * nb + b) * 3, acc);
     }
     __syncwarp();
+    for (int b = lane; b < nb; b += 32) s_lm[3 * b] = mass[b];      // the linear momenta are consumed: their slots carry the masses now
+    __syncwarp();
     for (int b = lane; b < nb; b += 32) {
       // angular momentum of the subtree about its own COM (closed form of mj_subtreeVel's recursion)
       v3 L = mk3(0.f, 0.f, 0.f);
       const v3 cb = ld3(com + 3 * b), Vb = ld3(s_slv + 3 * b);
       const int e = m.body_subtree_end[b];
+#pragma unroll 2
       for (int j = b; j < e; j++) {
-        v3 dx = ld3(xipos + 3 * j) - cb;
-        v3 dv = (mk3(s_bvel[6 * j + 3], s_bvel[6 * j + 4], s_bvel[6 * j + 5]) - Vb) * mass[j];
+        v3 dx = ld3(s_bvel + 6 * j) - cb;
+        v3 dv = (ld3(s_bvel + 6 * j + 3) - Vb) * s_lm[3 * j];
         L = L + ld3(s_am + 3 * j) + cross(dx, dv);
       }
       st3(d.subtree_angmom + ((size_t)w * nb + b) * 3, L);

@@ -64,7 +64,7 @@ def parse():
   ap.add_argument("--ls-parallel", type=int, default=1)
   ap.add_argument("--workload", default="g1_flat", choices=sorted(WORKLOADS))
   ap.add_argument("--extras", type=int, default=1, help="also measure (outside the timed region) the state regimes, the other workloads and PPO")
-  ap.add_argument("--overlap", type=int, default=1, help="stage overlap on forked graph branches (0: serial stages)")
+  ap.add_argument("--overlap", type=int, default=-1, help="stage overlap on forked graph branches (-1: the library's per-model default, 0: serial stages, 1: all branches, 2: only the solver's second launch)")
   ap.add_argument("--cone", default="pyramidal", choices=["pyramidal", "elliptic"], help="friction cone (the reference's default is pyramidal)")
   return ap.parse_args()
 
@@ -230,7 +230,7 @@ def run_reference(args):
 class PhysBench:
   """One physics workload on one GPU: the Simulation, its reset state, a pool of action batches and the bench step."""
 
-  def __init__(self, workload, E, dev, rank, ls_parallel=1, cone="pyramidal", overlap=1):
+  def __init__(self, workload, E, dev, rank, ls_parallel=1, cone="pyramidal", overlap=-1):
     import numpy as np
     import torch
     from asimov_mjlab_b200 import engine
@@ -247,7 +247,8 @@ class PhysBench:
     self.foot = foot = [i for i, n in enumerate(m.names["geom"]) if ("foot" in n or "_toe" in n or "ankle_roll_link" in n) and n.endswith("_collision")]
     fr = 0.3 + 0.9 * torch.rand(E, len(foot), generator=g)
     M.geom_friction[:, foot, 0] = fr.to(dev)
-    M.opt.stage_overlap = int(overlap)
+    if int(overlap) >= 0:
+      M.opt.stage_overlap = int(overlap)
     n0 = engine.launch_count()
     sim.create_graph(decimation=DECIMATION)
     assert engine.launch_count() - n0 >= 7 * DECIMATION

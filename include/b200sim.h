@@ -254,7 +254,7 @@ int b2s_model_destroy(b2s_model* m);
  * Keys: "ls_parallel", "contact_sensor_maxmatch", "iterations", "ls_iterations",
  * "tolerance", "ls_tolerance", "timestep", "impratio", "integrator", "cone",
  * "gravity_x", "gravity_y", "gravity_z", "disableflags", "ls_parallel_min_step", "solver",
- * and two scheduling knobs without a counterpart in the reference: "stage_overlap" (0 / 1) and
+ * and two scheduling knobs without a counterpart in the reference: "stage_overlap" (0 / 1 / 2, default per model) and
  * "solve_rowcap" (rows the default solver launch holds in shared memory, default 128; worlds with
  * more rows are solved by a second launch sized for njmax; results do not depend on it).
  * Changing an option after a graph was captured needs a new capture, as in the reference. */
