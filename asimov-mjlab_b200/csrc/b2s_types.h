@@ -117,6 +117,7 @@ struct DataDev {
   // global task list (world, survivor index) with its counter, and one staged result (CvxStage, 8 floats) per survivor
   unsigned* col_surv; int *col_nsurv, *col_pidx, *cvx_ntask, *cvx_task; float* cvx_stage;
   float* col_axis;   // [npair][3] per world, convex models only: last separating direction of each table pair (k_convex.cuh gjk_epa)
+  int* col_cost;     // [npair] per world, same models: GJK iterations (+ 64 if EPA ran) of the pair's last task: expensive pairs are queued first
   // constraints
   int *nefc, *nl, *nf, *efc_type, *efc_id, *efc_bp;   // rows [0, nl) act on one dof: nf friction-loss rows, then the limits;   // efc_bp: contact rows body1 | body2 << 16, limit rows -1 - dof
   float *efc_g;                                  // [njmax][6] row wrench about the reference point (limit rows: g[0] = +-1)

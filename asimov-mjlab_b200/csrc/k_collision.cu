@@ -370,6 +370,7 @@ DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
 // slowest world 6.6 ms).  The stage is split: PHASE 1 = broadphase, survivor list to global memory, one (world, survivor) TASK
 // per deferred pair; k_convex_tasks = one warp per task from the global list, results staged per survivor; PHASE 2 = the
 // narrowphase as before, reading the staged result where a pair was deferred.  PHASE 0 = everything in one kernel.
+#define CVX_COST_HEAVY 12      // GJK iterations (+ 64 for EPA) above which a pair's next task is queued with the expensive ones
 template <int MAXC, bool CONVEX, int PHASE>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -509,12 +510,23 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         if (t1 > t2) { const int tt = t1; t1 = t2; t2 = tt; }
         defer = t1 >= B2S_GEOM_SPHERE && (t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_CYLINDER || t1 == B2S_GEOM_ELLIPSOID || t2 == B2S_GEOM_CYLINDER || t2 == B2S_GEOM_ELLIPSOID);
       }
-      const unsigned dm = __ballot_sync(FULL, defer);
+      // pairs whose last task was expensive (a GJK run of many iterations, or EPA: col_cost) are queued from the END of the list and
+      // taken first by k_convex_tasks -- a handful of pairs cycle to the GJK iteration cap for 250 us each, and the kernel used to
+      // end when the last of them, started at a random time, was done
+      const bool heavy = defer && use_axis && d.col_cost[(size_t)w * m.npair + s_pidx[i]] > CVX_COST_HEAVY;
+      const unsigned hm = __ballot_sync(FULL, heavy);
+      const unsigned dm = __ballot_sync(FULL, defer && !heavy);
       if (dm) {
         int k0 = 0;
         if (lane == 0) k0 = atomicAdd(d.cvx_ntask, __popc(dm));
         k0 = __shfl_sync(FULL, k0, 0);
-        if (defer) { const int k = k0 + __popc(dm & ((1u << lane) - 1u)); d.cvx_task[2 * (size_t)k] = w; d.cvx_task[2 * (size_t)k + 1] = i; }
+        if (defer && !heavy) { const int k = k0 + __popc(dm & ((1u << lane) - 1u)); d.cvx_task[2 * (size_t)k] = w; d.cvx_task[2 * (size_t)k + 1] = i; }
+      }
+      if (hm) {
+        int k0 = 0;
+        if (lane == 0) k0 = atomicAdd(d.cvx_ntask + 2, __popc(hm));
+        k0 = __shfl_sync(FULL, k0, 0);
+        if (heavy) { const size_t k = (size_t)d.nworld * B2S_MAX_SURVIVORS - 1 - (k0 + __popc(hm & ((1u << lane) - 1u))); d.cvx_task[2 * k] = w; d.cvx_task[2 * k + 1] = i; }
       }
     }
     if (lane == 0) d.col_nsurv[w] = nsurv;
@@ -774,7 +786,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31;
   const int gw = blockIdx.x * B2S_WARPS_PER_CTA + (threadIdx.x >> 5), nwarp = gridDim.x * B2S_WARPS_PER_CTA;
-  const int ntask = min(d.cvx_ntask[0], d.nworld * B2S_MAX_SURVIVORS);
+  const int cap = d.nworld * B2S_MAX_SURVIVORS, nheavy = min(d.cvx_ntask[2], cap), ntask = min(d.cvx_ntask[0] + nheavy, cap);
   const bool use_axis = m.ngrid == 0;
   EpaWork* wk = reinterpret_cast<EpaWork*>(b2s_smem) + (threadIdx.x >> 5);       // this warp's EPA polytope
   // tasks differ by two orders of magnitude (a cached separating plane: one support evaluation; a deep overlap: GJK + 24 EPA
@@ -786,6 +798,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const M
     if (lane == 0) k = atomicAdd(d.cvx_ntask + 1, 1);
     k = __shfl_sync(FULL, k, 0);
     if (k >= ntask) break;
+    k = k < nheavy ? cap - 1 - k : k - nheavy;      // the expensive tasks first (queued from the end of the list), then the others
     const int w = d.cvx_task[2 * (size_t)k], i = d.cvx_task[2 * (size_t)k + 1];
     const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
     const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
@@ -796,10 +809,18 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const M
     Cvx A = geom_core(m, gx, gm, g1), B = geom_core(m, gx, gm, g2);
     A.coop = A.type == CVX_VERTS; B.coop = B.type == CVX_VERTS;
     CvxStage* out = reinterpret_cast<CvxStage*>(d.cvx_stage + ((size_t)w * B2S_MAX_SURVIVORS + i) * 8);
-    float* axis = use_axis ? d.col_axis + ((size_t)w * m.npair + d.col_pidx[(size_t)w * B2S_MAX_SURVIVORS + i]) * 3 : nullptr;
-    const int nres = convex_pair_warp(out, margin, A, B, lane, axis, wk);
+    const size_t pslot = use_axis ? (size_t)w * m.npair + d.col_pidx[(size_t)w * B2S_MAX_SURVIVORS + i] : 0;
+    float* axis = use_axis ? d.col_axis + pslot * 3 : nullptr;
+    int work = 0;
+#ifdef COL_TIMING      // development builds only (tools/exp_col_time.py): the consumed task record becomes (iterations | EPA rounds | hull vertices, task cycles / 64 | EPA cycles / 64 << 16)
+    const long long t_task = clock64();
+    const int nres = convex_pair_warp(out, margin, A, B, lane, axis, wk, d.cvx_task + 2 * (size_t)k, &work);
+    if (lane == 0) d.cvx_task[2 * (size_t)k + 1] |= (int)min((clock64() - t_task) >> 6, 65535LL);
+#else
+    const int nres = convex_pair_warp(out, margin, A, B, lane, axis, wk, nullptr, &work);
+#endif
     __syncwarp();
-    if (lane == 0) out->idx = nres;
+    if (lane == 0) { out->idx = nres; if (use_axis) d.col_cost[pslot] = work; }
     __syncwarp();
   }
 }

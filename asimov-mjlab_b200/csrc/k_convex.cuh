@@ -32,7 +32,11 @@ struct Cvx {
   bool coop;           // true: all 32 lanes are in this call with identical arguments and share the vertex scan
   float radius;
 };
-struct CvxRes { float dist; v3 n, pa, pb; };
+struct CvxRes { float dist; v3 n, pa, pb;
+#ifdef COL_TIMING
+  int dbg_gjk, dbg_epa; long long dbg_epa_cyc;      // development builds: GJK iterations, EPA rounds and cycles of this pair
+#endif
+};
 struct Simplex { v3 Y[4], A[4]; float lam[4]; int n; };
 
 // support point of the core in world direction dir (ties: lowest vertex index)
@@ -194,6 +198,9 @@ __device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const S
   int best = 0;
 #pragma unroll 1
   for (int it = 0; it < EPA_MAXIT; it++) {
+#ifdef COL_TIMING
+    out.dbg_epa = it + 1;
+#endif
     best = -1;
     for (int f = 0; f < nf; f++) if (F[f].alive && (best < 0 || F[f].d < F[best].d)) best = f;
     if (best < 0) return false;
@@ -242,6 +249,120 @@ __device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const S
   return true;
 }
 
+// The same algorithm for warp-level callers: all 32 lanes are here with identical arguments and ONE polytope in shared memory, so the
+// per-face and per-edge loops are split over the lanes instead of being run 32 times over -- closest face = warp arg-min of (d,
+// index); visibility = one lane per face, the removed faces' edges appended in face order through a ballot; horizon = one lane
+// per edge looking for its twin; new faces = the j-th horizon edge (ascending) takes the j-th dead slot (ascending), then fresh
+// slots, which is what the serial loop does one edge at a time.  Same polytope after every round, hence the same result.
+// (Measured with -DCOL_TIMING before: 15 us per round, one 25-round pair = 388 us = most of k_convex_tasks' duration.)
+__device__ __noinline__ bool epa_penetration_warp(const Cvx& A, const Cvx& B, const Simplex& s, CvxRes& out, EpaWork* wk) {
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  v3* const V = wk->V; v3* const VA = wk->VA;
+  EpaFace* const F = wk->F;
+  unsigned char (*const E)[2] = wk->E;
+  int nv = 4, nf = 0;
+  __syncwarp();
+  if (lane == 0) {
+    for (int i = 0; i < 4; i++) { V[i] = s.Y[i]; VA[i] = s.A[i]; }
+    if (dot(cross(V[1] - V[0], V[2] - V[0]), V[3] - V[0]) > 0.f) {      // make (0,1,2) face away from vertex 3
+      v3 t = V[1]; V[1] = V[2]; V[2] = t; t = VA[1]; VA[1] = VA[2]; VA[2] = t;
+    }
+    epa_make_face(F[0], V, 0, 1, 2);
+    epa_make_face(F[1], V, 0, 3, 1);
+    epa_make_face(F[2], V, 0, 2, 3);
+    epa_make_face(F[3], V, 1, 3, 2);
+  }
+  nf = 4;
+  __syncwarp();
+  auto closest_face = [&]() {
+    float bd = 0.f; int best = -1;
+    for (int f = lane; f < nf; f += 32) if (F[f].alive && (best < 0 || F[f].d < bd)) { bd = F[f].d; best = f; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, bd, o);
+      const int of = __shfl_xor_sync(0xffffffffu, best, o);
+      if (of >= 0 && (best < 0 || ob < bd || (ob == bd && of < best))) { bd = ob; best = of; }
+    }
+    return best;
+  };
+  int best = 0;
+#pragma unroll 1
+  for (int it = 0; it < EPA_MAXIT; it++) {
+#ifdef COL_TIMING
+    out.dbg_epa = it + 1;
+#endif
+    best = closest_face();
+    if (best < 0) return false;
+    const v3 bn = F[best].n; const float bdist = F[best].d;
+    v3 w, wa;
+    mink_support(A, B, bn, w, wa);
+    const float gain = dot(w, bn) - bdist;
+    const float tol = CVX_TOL * (1.f + fabsf(bdist));
+    if (gain <= tol || nv >= EPA_MAXV) break;
+    int ne = 0, nvis = 0;
+    for (int f0 = 0; f0 < nf; f0 += 32) {
+      const int f = f0 + lane;
+      bool vis = false;
+      if (f < nf && F[f].alive) vis = dot(F[f].n, w - V[F[f].v[0]]) > 0.f || F[f].d >= 1e30f;
+      const unsigned vm = __ballot_sync(0xffffffffu, vis);
+      if (vis) {
+        F[f].alive = 0;
+        const int r = ne + 3 * __popc(vm & lt);
+        for (int k = 0; k < 3; k++) { E[r + k][0] = F[f].v[k]; E[r + k][1] = F[f].v[(k + 1) % 3]; }
+      }
+      ne += 3 * __popc(vm); nvis += __popc(vm);
+    }
+    if (nvis == 0) break;
+    if (lane == 0) { V[nv] = w; VA[nv] = wa; }
+    __syncwarp();
+    // dead slots in ascending order (EPA_MAXF <= 64: two ballots)
+    const unsigned dead0 = __ballot_sync(0xffffffffu, lane < nf && !F[lane].alive);
+    const unsigned dead1 = __ballot_sync(0xffffffffu, lane + 32 < nf && !F[lane + 32].alive);
+    const int nd0 = __popc(dead0), ndead = nd0 + __popc(dead1);
+    int nedge = 0;        // horizon edges so far
+    for (int e0 = 0; e0 < ne; e0 += 32) {
+      const int e = e0 + lane;
+      bool boundary = false;
+      if (e < ne) {
+        boundary = true;
+        const unsigned char a = E[e][0], b = E[e][1];
+        for (int g = 0; g < ne; g++) if (E[g][0] == b && E[g][1] == a) { boundary = false; break; }
+      }
+      const unsigned bm = __ballot_sync(0xffffffffu, boundary);
+      if (boundary) {
+        const int j = nedge + __popc(bm & lt);
+        int slot;
+        if (j < nd0) slot = (int)__fns(dead0, 0, j + 1);
+        else if (j < ndead) slot = 32 + (int)__fns(dead1, 0, j - nd0 + 1);
+        else slot = nf + (j - ndead);
+        if (slot < EPA_MAXF) epa_make_face(F[slot], V, E[e][0], E[e][1], nv);
+      }
+      nedge += __popc(bm);
+    }
+    // the serial loop stops at the first edge that finds no slot: faces exist for the edges before it
+    const int fresh = max(nedge - ndead, 0);
+    const bool full = nf + fresh > EPA_MAXF;
+    const int added = full ? min(nedge, ndead + (EPA_MAXF - nf)) : nedge;
+    nf = full ? EPA_MAXF : nf + fresh;
+    nv++;
+    __syncwarp();
+    if (full || added == 0) break;
+  }
+  best = closest_face();
+  if (best < 0) return false;
+  Simplex t;
+  for (int i = 0; i < 3; i++) { t.Y[i] = V[F[best].v[i]]; t.A[i] = VA[F[best].v[i]]; }
+  t.n = 3;
+  closest_triangle(t);
+  const v3 p = sx_point(t.Y, t);
+  out.pa = sx_point(t.A, t);
+  out.n = F[best].n;
+  out.pb = out.pa - p;
+  out.dist = -fmaxf(F[best].d, 0.f);
+  return true;
+}
+
 // GJK on the cores.  false: farther apart than `cutoff`.  Separated: dist > 0, n from A to B, pa / pb closest core
 // points.  Overlapping cores: the simplex is grown to a tetrahedron around the origin and handed to EPA.
 // `axis` (optional, 3 floats of per-pair storage that lives across steps; warp-level callers only): TEMPORAL COHERENCE.  A pair that
@@ -250,7 +371,8 @@ __device__ __noinline__ bool epa_penetration(const Cvx& A, const Cvx& B, const S
 // the same bound (valid for ANY direction) that ends the GJK loop early, so the outcome is the one the full search would reach.
 // Otherwise the search runs exactly as without the cache (same start direction, same iterates).  The cache is refreshed
 // whenever the search proves separation and cleared when it finds a contact.
-__device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, CvxRes& out, float* axis = nullptr, EpaWork* wk = nullptr) {
+// `work` (optional): GJK iterations of this call, + 64 if EPA ran (k_convex_tasks keeps it per pair to queue expensive pairs first).
+__device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, CvxRes& out, float* axis = nullptr, EpaWork* wk = nullptr, int* work = nullptr) {
   Simplex s;
   if (axis) {
     const v3 vc = ld3(axis);
@@ -259,7 +381,7 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
       v3 w, wa;
       mink_support(A, B, vc * -1.f, w, wa);
       const float vw = dot(vc, w);
-      if (vw > 0.f && vw * vw > cutoff * cutoff * vv) return false;
+      if (vw > 0.f && vw * vw > cutoff * cutoff * vv) { if (work) *work = 0; return false; }
     }
     __syncwarp();
   }
@@ -270,14 +392,23 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
   v3 v = s.Y[0];
   float scale2 = dot(v, v);
   bool inside = false;
+  int it = 0;
+#ifdef COL_TIMING
+  out.dbg_gjk = 0; out.dbg_epa = 0; out.dbg_epa_cyc = 0;
+#endif
 #pragma unroll 1
-  for (int it = 0; it < GJK_MAXIT; it++) {
+  for (; it < GJK_MAXIT; it++) {
     const float vv = dot(v, v);
     if (vv <= CVX_TOL * CVX_TOL * scale2 || vv < 1e-30f) { inside = true; break; }
     v3 w, wa;
     mink_support(A, B, v * -1.f, w, wa);
     const float vw = dot(v, w);
-    if (vw > 0.f && vw * vw > cutoff * cutoff * vv) { if (axis && (threadIdx.x & 31) == 0) st3(axis, v); return false; }
+    if (vw > 0.f && vw * vw > cutoff * cutoff * vv) {
+#ifdef COL_TIMING
+      out.dbg_gjk = it + 1;
+#endif
+      if (work) *work = it + 1;
+      if (axis && (threadIdx.x & 31) == 0) st3(axis, v); return false; }
     const float ww = dot(w, w);
     if (ww > scale2) scale2 = ww;
     if (vv - vw <= CVX_TOL * vv + 1e-12f * scale2) break;
@@ -290,6 +421,10 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
     else if (closest_tetrahedron(s, scale2)) { inside = true; break; }
     v = sx_point(s.Y, s);
   }
+#ifdef COL_TIMING
+  out.dbg_gjk = it;
+#endif
+  if (work) *work = it + (inside ? 64 : 0);
   if (axis && (threadIdx.x & 31) == 0) {      // separated beyond the cutoff: remember the direction; anything else: no cached plane
     const bool sep = !inside && dot(v, v) > cutoff * cutoff;
     st3(axis, sep ? v : mk3(0.f, 0.f, 0.f));
@@ -339,7 +474,14 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
       return true;
     }
   }
-  return epa_penetration(A, B, s, out, wk);
+#ifdef COL_TIMING
+  const long long t_epa = clock64();
+  const bool okk = wk ? epa_penetration_warp(A, B, s, out, wk) : epa_penetration(A, B, s, out, wk);
+  out.dbg_epa_cyc = clock64() - t_epa;
+  return okk;
+#else
+  return wk ? epa_penetration_warp(A, B, s, out, wk) : epa_penetration(A, B, s, out, wk);
+#endif
 }
 
 // one contact between two convex geoms (cores + radii); normal from A to B.  Rc is the kernel's contact scratch type.
@@ -452,9 +594,16 @@ DEV int plane_mesh_warp(CvxStage* out, float margin, v3 ppos, const m33& pmat, v
 
 // one convex pair, every lane in the call: the hull scans are shared (Cvx::coop), the simplex / polytope logic runs
 // redundantly and identically on all lanes
-DEV int convex_pair_warp(CvxStage* out, float margin, const Cvx& A, const Cvx& B, int lane, float* axis = nullptr, EpaWork* wk = nullptr) {
+DEV int convex_pair_warp(CvxStage* out, float margin, const Cvx& A, const Cvx& B, int lane, float* axis = nullptr, EpaWork* wk = nullptr, int* dbg = nullptr, int* work = nullptr) {
   CvxRes r;
-  if (!gjk_epa(A, B, margin + A.radius + B.radius, r, axis, wk)) return 0;
+#ifdef COL_TIMING
+  r.dbg_gjk = 0; r.dbg_epa = 0; r.dbg_epa_cyc = 0;
+  const bool hit = gjk_epa(A, B, margin + A.radius + B.radius, r, axis, wk, work);
+  if (dbg && lane == 0) { dbg[0] = r.dbg_gjk | (r.dbg_epa << 8) | (min(A.nvert + B.nvert, 4095) << 16); dbg[1] = (int)min(r.dbg_epa_cyc >> 6, 65535LL) << 16; }
+  if (!hit) return 0;
+#else
+  if (!gjk_epa(A, B, margin + A.radius + B.radius, r, axis, wk, work)) return 0;
+#endif
   const float dist = r.dist - A.radius - B.radius;
   if (dist > margin) return 0;
   const v3 sa = r.pa + r.n * A.radius, sb = r.pb - r.n * B.radius;

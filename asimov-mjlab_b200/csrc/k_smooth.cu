@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_position(const Model
   const int w = blockIdx.x * B2S_WARPS_PER_CTA + warp;
   // first kernel of step / forward: reset the solver's scheduling queues (k_constraint refills them)
   if (blockIdx.x == 0 && threadIdx.x < B2S_SOLVE_CLASSES) d.solve_count[threadIdx.x] = 0;
-  if (blockIdx.x == 0 && threadIdx.x < 2 && m.col_defer) d.cvx_ntask[threadIdx.x] = 0;      // and the convex-pair task list (k_collision phase 1 refills it)
+  if (blockIdx.x == 0 && threadIdx.x < 3 && m.col_defer) d.cvx_ntask[threadIdx.x] = 0;      // and the convex-pair task list (k_collision phase 1 refills it)
   if (w >= d.nworld) return;
   const int nb = m.nbody;
   float* sx = b2s_smem + (size_t)warp * pos_smem_floats(nb, m.njnt);   // xpos

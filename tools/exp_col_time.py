@@ -22,4 +22,13 @@ for wl in os.environ.get("WL", "asimov_toe_full_flat,go1_rough_hf").split(","):
         " max-of-4 (CTA) mean %.1f us; worlds > 60 us: %d" % (tot.reshape(-1, 4).max(axis=1).mean(), (tot > 60).sum()))
   hv = np.argsort(-tot)[:5]
   print("   heaviest worlds:", [(int(w), round(float(tot[w]), 1), int(t[w, 3]), int(pb.D.ncon[w].item())) for w in hv], "(world, us, survivors, ncon)")
+  if "cvx_task" in pb.D.field_names and os.environ.get("TASKS", "1") == "1":
+    nl, nh = int(pb.D.cvx_ntask.flatten()[0].item()), int(pb.D.cvx_ntask.flatten()[2].item()); nt = nl + nh
+    if nt:
+      allrec = pb.D.cvx_task.reshape(-1, 2); rec = torch.cat([allrec[:nl], allrec[allrec.shape[0] - nh:]]).cpu().numpy(); print(f'   expensive-first tasks: {nh}'); cyc = (rec[:, 1] & 0xffff).astype(np.float64) * 64 / 1965.0
+      gjk = rec[:, 0] & 255; epa = (rec[:, 0] >> 8) & 255; nvt = (rec[:, 0] >> 16) & 4095; epa_us = ((rec[:, 1] >> 16) & 0xffff).astype(np.float64) * 64 / 1965.0
+      print(f"   convex tasks: {nt}; per task us 50/90/99/99.9/max:", [round(float(np.percentile(cyc, q)), 1) for q in (50, 90, 99, 99.9, 100)], "sum %.1f ms" % (cyc.sum() / 1e3))
+      top = np.argsort(-cyc)[:8]
+      print("   slowest tasks (us, gjk iterations, epa rounds, epa us, hull vertices):", [(round(float(cyc[t]), 1), int(gjk[t]), int(epa[t]), round(float(epa_us[t]), 1), int(nvt[t])) for t in top])
+      print("   tasks with EPA: %d (%.1f ms of which EPA %.1f ms); GJK iterations mean %.1f, > 20: %d" % ((epa > 0).sum(), cyc[epa > 0].sum() / 1e3, epa_us.sum() / 1e3, gjk.mean(), (gjk > 20).sum()))
   print("   stage ms", engine.profile_step(pb.M, pb.D, 5))
