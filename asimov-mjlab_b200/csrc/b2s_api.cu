@@ -353,7 +353,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
   }
   // ---------------------------------------------------------------- static collision pair table
   std::vector<int> pairs;
-  int col_convex = 0, col_defer = 0;
+  int col_convex = 0, col_defer = 0, col_hf = 0;
   auto pair_deferred = [&](int t1, int t2) { return pair_convex(t1, t2) && t1 != B2S_GEOM_PLANE && t1 != B2S_GEOM_HFIELD; };
   int col_maxc = 1;          // most contacts one geom pair of this model can produce: picks the narrowphase variant
   for (int ga = 0; ga < s->ngeom; ga++) for (int gb = ga + 1; gb < s->ngeom; gb++) {
@@ -379,6 +379,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     col_maxc = std::max(col_maxc, pair_max_contacts(s->geom_type[g1], s->geom_type[g2]));
     col_convex |= pair_convex(s->geom_type[g1], s->geom_type[g2]) ? 1 : 0;
     col_defer |= pair_deferred(s->geom_type[g1], s->geom_type[g2]) ? 1 : 0;
+    col_hf |= s->geom_type[g1] == B2S_GEOM_HFIELD ? 1 : 0;
   }
   if (use_grid)   // grid pairs: every dynamic geom against every geom type present in the grid
     for (int ga : dyn_geoms) for (int gb : grid_geoms) {
@@ -387,6 +388,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
       col_maxc = std::max(col_maxc, pair_max_contacts(t1, t2));
       col_convex |= pair_convex(t1, t2) ? 1 : 0;
       col_defer |= pair_deferred(t1, t2) ? 1 : 0;
+      col_hf |= t1 == B2S_GEOM_HFIELD ? 1 : 0;
     }
   // ---------------------------------------------------------------- traversal tables
   int nlevel = 0;
@@ -497,7 +499,7 @@ extern "C" int b2s_model_create(const b2s_model_desc* s, int device, b2s_model**
     d.geom_bcen = up.raw(bcen); d.geom_bsize = up.raw(bsize); d.geom_brad = up.raw(brad);
   }
   d.col_maxc = col_maxc <= 2 ? 2 : (col_maxc <= 4 ? 4 : 8);
-  d.col_convex = col_convex; d.col_defer = col_defer; d.solve_rowcap = 128;
+  d.col_convex = col_convex; d.col_defer = col_defer; d.col_hf = col_hf; d.solve_rowcap = 128;
   // stage overlap by default (measured at 4096 worlds, tools/ab7.sh): the side-stream branches pay for the small models (Go1 +2.5 %, on
   // height fields +6 %, Asimov +1.4 %) and cost where the stage kernels fill the register file by themselves (G1: -0.6 %) or where
   // collision is three launches with a persistent task kernel that then fights dynamics for CTA slots (Asimov FULL: -11 %)

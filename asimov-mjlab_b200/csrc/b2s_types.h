@@ -78,6 +78,7 @@ struct ModelDev {
   // ---- fixed tendons (wraps flattened to dof / qpos addresses) and actuators
   int col_maxc;      // narrowphase variant: most contacts per geom pair (2, 4 or 8)
   int col_convex;    // 1: some pair needs the GJK/EPA, plane-mesh or height-field colliders
+  int col_hf;        // 1: the model has height-field pairs (0: the second collision phase is instantiated without GJK / EPA)
   int solve_rowcap;  // rows the DEFAULT solver variant's shared-memory layout holds (option "solve_rowcap", default 128): worlds with more rows go to a second launch with room for njmax
   int col_defer;     // 1: GJK/EPA pairs between two convex cores exist: they run as (world, pair) tasks of a second kernel (k_convex_tasks)
   const int *geom_dataid, *mesh_vertadr, *mesh_vertnum, *hfield_nrow, *hfield_ncol, *hfield_adr;

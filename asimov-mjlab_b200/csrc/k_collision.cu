@@ -370,6 +370,11 @@ DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
 // slowest world 6.6 ms).  The stage is split: PHASE 1 = broadphase, survivor list to global memory, one (world, survivor) TASK
 // per deferred pair; k_convex_tasks = one warp per task from the global list, results staged per survivor; PHASE 2 = the
 // narrowphase as before, reading the staged result where a pair was deferred.  PHASE 0 = everything in one kernel.
+// PHASE 3 = PHASE 2 of a model without height-field pairs: with every core-core pair deferred, only the plane-mesh manifolds are left
+// of the convex code, so GJK / EPA drop out of this kernel's call graph (232 -> ~100 registers, 2 -> 5 CTAs per SM).
+#ifndef CVX_TASK_MINB
+#define CVX_TASK_MINB 4
+#endif
 #define CVX_COST_HEAVY 12      // GJK iterations (+ 64 for EPA) above which a pair's next task is queued with the expensive ones
 template <int MAXC, bool CONVEX, int PHASE>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const ModelDev m, const DataDev d) {
@@ -396,12 +401,14 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
 #endif
   // A1) static pair table (dynamic-dynamic and plane-dynamic pairs, already in key order): bounding spheres
   int nsurv = 0;
-  if constexpr (PHASE == 2) {       // the survivors phase 1 found
+  constexpr bool P2 = PHASE == 2 || PHASE == 3;      // second phase
+  constexpr bool HF = PHASE != 3;                    // height-field (and in-kernel GJK / EPA) code compiled in
+  if constexpr (P2) {       // the survivors phase 1 found
     nsurv = d.col_nsurv[w];
     for (int i = lane; i < nsurv; i += 32) s_list[i] = d.col_surv[(size_t)w * B2S_MAX_SURVIVORS + i];
     __syncwarp();
   }
-  for (int base = 0; PHASE != 2 && base < m.npair; base += 32) {
+  for (int base = 0; !P2 && base < m.npair; base += 32) {
     const int p = base + lane;
     bool pass = false;
     unsigned key = 0;
@@ -453,7 +460,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   nsurv = min(nsurv, B2S_MAX_SURVIVORS);
   // A2) static terrain geoms through the uniform xy grid built at put_model: one lane per dynamic geom walks the
   // cells under its bounding sphere; a static geom that spans several cells is taken in its first common cell only
-  if (PHASE != 2 && m.ngrid > 0) {
+  if (!P2 && m.ngrid > 0) {
     if (lane == 0) *s_cnt = nsurv;
     __syncwarp();
     for (int k = lane; k < m.ndyngeom; k += 32) {
@@ -566,7 +573,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       // every pair with a mesh, a height field, a cylinder or an ellipsoid (other than plane - cylinder / ellipsoid) is convex work
       if constexpr (CONVEX) cvx = t2 == B2S_GEOM_MESH || t1 == B2S_GEOM_HFIELD ||
                                   (t1 >= B2S_GEOM_SPHERE && (t1 == B2S_GEOM_CYLINDER || t1 == B2S_GEOM_ELLIPSOID || t2 == B2S_GEOM_CYLINDER || t2 == B2S_GEOM_ELLIPSOID));
-      if constexpr (CONVEX && PHASE == 2) {
+      if constexpr (CONVEX && P2) {
         if (cvx && t1 >= B2S_GEOM_SPHERE) {      // deferred pair: k_convex_tasks staged its result
           const CvxStage* sg = reinterpret_cast<const CvxStage*>(d.cvx_stage + ((size_t)w * B2S_MAX_SURVIVORS + i) * 8);
           n = sg->idx;
@@ -583,8 +590,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
       // each pair's lane then takes its segment.  If the stage overflows (robot buried in the field) the pairs fall
       // back to the one-pair-at-a-time driver below, which has no such limit.
       bool hf = false, hf_done = false;
-      if (cvx) hf = m.geom_type[g1] == B2S_GEOM_HFIELD;
-      if (__any_sync(FULL, hf)) {
+      if constexpr (HF) { if (cvx) hf = m.geom_type[g1] == B2S_GEOM_HFIELD; }
+      if constexpr (HF) if (__any_sync(FULL, hf)) {
         HfRange R; R.cmin = 0; R.ncell = 0; R.rmin = 0; R.T = 0; R.loz = 0.f;
         if (hf) {
           Cvx B = geom_core(m, gx, gm, g2);
@@ -693,7 +700,8 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         else { const int id = m.geom_dataid[bg2]; B.type = CVX_VERTS; B.vert = m.mesh_vert + 4 * m.mesh_vertadr[id]; B.nvert = m.mesh_vertnum[id]; }
         int nres;
         if (t1 == B2S_GEOM_PLANE) nres = plane_mesh_warp(s_stage, bm, p1, m1, p2, m2, B.vert, B.nvert, lane);
-        else if (t1 == B2S_GEOM_HFIELD) {
+        else if constexpr (HF) {
+        if (t1 == B2S_GEOM_HFIELD) {
           const int h = m.geom_dataid[bg1];
           nres = hfield_convex_warp<MAXC>(s_stage, bm, m.hfield_size + 4 * h, m.hfield_nrow[h], m.hfield_ncol[h], m.hfield_data + m.hfield_adr[h],
                                           p1, m1, B, lane);
@@ -709,6 +717,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
           float* axis = use_axis ? d.col_axis + ((size_t)w * m.npair + s_pidx[base + L]) * 3 : nullptr;
           nres = convex_pair_warp(s_stage, bm, A, B, lane, axis);
         }
+        } else nres = 0;      // PHASE 3: every core-core pair was a task, no height fields
         __syncwarp();
 #ifdef COL_TIMING
         n_hit += nres > 0; t_ph[2] += clock64() - t_c0;
@@ -783,7 +792,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
 // One warp per (world, survivor) task of the global list phase 1 filled: GJK / EPA between the two convex cores with the hull
 // scans shared by the 32 lanes, result staged for phase 2.  A persistent grid strides over the list, so a world with a hundred
 // such pairs is spread over the whole machine instead of serialising on its own warp.
-__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_convex_tasks(const ModelDev m, const DataDev d) {
+__global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, CVX_TASK_MINB) k_convex_tasks(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31;
   const int gw = blockIdx.x * B2S_WARPS_PER_CTA + (threadIdx.x >> 5), nwarp = gridDim.x * B2S_WARPS_PER_CTA;
   const int cap = d.nworld * B2S_MAX_SURVIVORS, nheavy = min(d.cvx_ntask[2], cap), ntask = min(d.cvx_ntask[0] + nheavy, cap);
@@ -836,8 +845,9 @@ void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
   if (m.col_convex && m.col_defer) {      // broadphase + task emission, the GJK / EPA tasks over the whole machine, narrowphase + ordered append
     k_collision<8, true, 1><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
-    k_convex_tasks<<<148 * 4, 32 * B2S_WARPS_PER_CTA, B2S_WARPS_PER_CTA * sizeof(EpaWork), st>>>(m, d);
-    k_collision<8, true, 2><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
+    k_convex_tasks<<<148 * CVX_TASK_MINB, 32 * B2S_WARPS_PER_CTA, B2S_WARPS_PER_CTA * sizeof(EpaWork), st>>>(m, d);
+    if (m.col_hf) k_collision<8, true, 2><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
+    else k_collision<8, true, 3><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d);
     b2s_count_launch(); b2s_count_launch(); b2s_count_launch();
     return;
   }

@@ -166,6 +166,44 @@ __device__ __noinline__ bool closest_tetrahedron(Simplex& s, float scale2) {
   return false;
 }
 
+// The same for warp-level callers (all 32 lanes here with the same simplex): face f is evaluated by the lanes with lane % 4 == f,
+// the winner -- smallest distance, lowest face index on ties, exactly the serial loop's choice -- is broadcast.  A GJK run that
+// cycles to its iteration cap spends most of its time here (measured: 5 us per iteration, 250 us per capped pair).
+__device__ __noinline__ bool closest_tetrahedron_warp(Simplex& s, float scale2) {
+  const int f = threadIdx.x & 3;
+  const int i0 = f == 3 ? 1 : 0, i1 = f == 0 ? 1 : (f == 1 ? 2 : 3), i2 = f == 0 ? 2 : (f == 1 ? 3 : (f == 2 ? 1 : 2)), i3 = f == 0 ? 3 : (f == 1 ? 1 : (f == 2 ? 2 : 0));
+  const v3 a = s.Y[i0], b = s.Y[i1], c = s.Y[i2], dd = s.Y[i3];
+  const v3 nn = cross(b - a, c - a);
+  const float sp = -dot(a, nn), sd = dot(dd - a, nn);
+  const bool cand = sp * sd < 0.f || sd * sd <= 1e-10f * dot(nn, nn) * scale2;
+  Simplex t;
+  t.n = 0;
+  float d2 = 0.f;
+  if (cand) {
+    t.Y[0] = a; t.Y[1] = b; t.Y[2] = c; t.A[0] = s.A[i0]; t.A[1] = s.A[i1]; t.A[2] = s.A[i2]; t.n = 3;
+    closest_triangle(t);
+    const v3 v = sx_point(t.Y, t);
+    d2 = dot(v, v);
+  }
+  __syncwarp();
+  int bestf = -1; float bestd = -1.f;
+#pragma unroll
+  for (int g = 0; g < 4; g++) {
+    const float dg = __shfl_sync(0xffffffffu, d2, g);
+    const int cg = __shfl_sync(0xffffffffu, cand ? 1 : 0, g);
+    if (cg && (bestd < 0.f || dg < bestd)) { bestd = dg; bestf = g; }
+  }
+  if (bestf < 0) return true;
+  s.n = __shfl_sync(0xffffffffu, t.n, bestf);
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    s.Y[i].x = __shfl_sync(0xffffffffu, t.Y[i].x, bestf); s.Y[i].y = __shfl_sync(0xffffffffu, t.Y[i].y, bestf); s.Y[i].z = __shfl_sync(0xffffffffu, t.Y[i].z, bestf);
+    s.A[i].x = __shfl_sync(0xffffffffu, t.A[i].x, bestf); s.A[i].y = __shfl_sync(0xffffffffu, t.A[i].y, bestf); s.A[i].z = __shfl_sync(0xffffffffu, t.A[i].z, bestf);
+    s.lam[i] = __shfl_sync(0xffffffffu, t.lam[i], bestf);
+  }
+  return false;
+}
+
 // ---- EPA: triangle faces with outward normals; the face closest to the origin is expanded along its normal
 struct EpaFace { unsigned char v[3], alive; v3 n; float d; };
 DEV void epa_make_face(EpaFace& f, const v3* V, int a, int b, int c) {
@@ -418,7 +456,7 @@ __device__ __noinline__ bool gjk_epa(const Cvx& A, const Cvx& B, float cutoff, C
     s.Y[s.n] = w; s.A[s.n] = wa; s.n++;
     if (s.n == 2) closest_segment(s);
     else if (s.n == 3) closest_triangle(s);
-    else if (closest_tetrahedron(s, scale2)) { inside = true; break; }
+    else if (wk ? closest_tetrahedron_warp(s, scale2) : closest_tetrahedron(s, scale2)) { inside = true; break; }
     v = sx_point(s.Y, s);
   }
 #ifdef COL_TIMING

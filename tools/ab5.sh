@@ -1,7 +1,7 @@
 cd $GRAFT_REPO_ROOT
 for wl in $WLS; do for rep in 1 2; do
 python bench.py --steps 40 --warmup 10 --extras 0 --cpu-baseline 0 --workload $wl > gpurun_out/bench_ab5_new_${wl}_$rep.json 2>/dev/null
-B2S_LIB=$GRAFT_REPO_ROOT/asimov-mjlab_b200/_variants/lib_base.so python bench.py --steps 40 --warmup 10 --extras 0 --cpu-baseline 0 --workload $wl > gpurun_out/bench_ab5_base_${wl}_$rep.json 2>/dev/null
+B2S_LIB=$GRAFT_REPO_ROOT/asimov-mjlab_b200/_variants/lib_${BASE:-base}.so python bench.py --steps 40 --warmup 10 --extras 0 --cpu-baseline 0 --workload $wl > gpurun_out/bench_ab5_${BASE:-base}_${wl}_$rep.json 2>/dev/null
 done; done
 python - <<'PY'
 import json,glob,os
