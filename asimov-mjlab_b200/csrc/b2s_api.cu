@@ -752,7 +752,7 @@ extern "C" int b2s_data_create(const b2s_model* m, const b2s_state_desc* init, i
     {"contact_solref", B2S_F32, (void**)&d.con_solref, {nconmax, 2}}, {"contact_solimp", B2S_F32, (void**)&d.con_solimp, {nconmax, 5}},
     {"col_surv", B2S_I32, (void**)&d.col_surv, {md.col_defer ? B2S_MAX_SURVIVORS : 0}}, {"col_nsurv", B2S_I32, (void**)&d.col_nsurv, {md.col_defer ? 1 : 0}},
     {"col_pidx", B2S_I32, (void**)&d.col_pidx, {md.col_defer ? B2S_MAX_SURVIVORS : 0}}, {"cvx_ntask", B2S_I32, (void**)&d.cvx_ntask, {md.col_defer ? 4 : 0}}      /* [0] tasks emitted, [1] cursor of k_convex_tasks, [2] expensive tasks (queued from the end of the list) */,
-    {"cvx_task", B2S_I32, (void**)&d.cvx_task, {md.col_defer ? B2S_MAX_SURVIVORS : 0, 2}}, {"cvx_stage", B2S_F32, (void**)&d.cvx_stage, {md.col_defer ? B2S_MAX_SURVIVORS : 0, 8}},
+    {"cvx_task", B2S_I32, (void**)&d.cvx_task, {md.col_defer ? B2S_MAX_SURVIVORS : 0, 8}}, {"cvx_stage", B2S_F32, (void**)&d.cvx_stage, {md.col_defer ? B2S_MAX_SURVIVORS : 0, 8}},
     {"col_axis", B2S_F32, (void**)&d.col_axis, {(md.col_convex && md.ngrid == 0) ? md.npair : 0, 3}},
     {"col_cost", B2S_I32, (void**)&d.col_cost, {(md.col_defer && md.ngrid == 0) ? md.npair : 0}},
     {"nefc", B2S_I32, (void**)&d.nefc, {}}, {"nl", B2S_I32, (void**)&d.nl, {}}, {"nf", B2S_I32, (void**)&d.nf, {}}, {"efc_type", B2S_I32, (void**)&d.efc_type, {njmax}}, {"efc_id", B2S_I32, (void**)&d.efc_id, {njmax}},

@@ -372,6 +372,32 @@ DEV Cvx geom_core(const ModelDev& m, const float* gx, const float* gm, int g) {
 // narrowphase as before, reading the staged result where a pair was deferred.  PHASE 0 = everything in one kernel.
 // PHASE 3 = PHASE 2 of a model without height-field pairs: with every core-core pair deferred, only the plane-mesh manifolds are left
 // of the convex code, so GJK / EPA drop out of this kernel's call graph (232 -> ~100 registers, 2 -> 5 CTAs per SM).
+// One task of k_convex_tasks = 32 bytes that carry everything the task needs from tables: world, survivor index, the two geoms (lower
+// type first), pair-table index, the geom types and the hull addresses / sizes.  The task kernel used to find these through
+// cvx_task -> col_surv -> geom_type -> geom_dataid -> mesh_vertadr, five dependent loads (~3.5 us, as long as the median task).
+DEV void task_record(const ModelDev& m, const DataDev& d, size_t k, int w, int i, unsigned key, int pidx) {
+  int g1 = (int)(key >> 16), g2 = (int)(key & 0xffffu);
+  if (m.geom_type[g1] > m.geom_type[g2]) { const int t = g1; g1 = g2; g2 = t; }
+  const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
+  int va1 = 0, vn1 = 0, va2 = 0, vn2 = 0;
+  if (t1 == B2S_GEOM_MESH) { const int id = m.geom_dataid[g1]; va1 = m.mesh_vertadr[id]; vn1 = m.mesh_vertnum[id]; }
+  if (t2 == B2S_GEOM_MESH) { const int id = m.geom_dataid[g2]; va2 = m.mesh_vertadr[id]; vn2 = m.mesh_vertnum[id]; }
+  int4* r = reinterpret_cast<int4*>(d.cvx_task) + 2 * k;
+  r[0] = make_int4(w, i, g1 | (g2 << 16), pidx);
+  r[1] = make_int4(t1 | (t2 << 8), va1, va2, vn1 | (vn2 << 16));
+}
+DEV Cvx task_core(const ModelDev& m, const float* gx, const float* gm, int g, int t, int vadr, int vnum) {
+  Cvx B;
+  B.pos = ld3(gx + 3 * g); B.mat = ldm(gm + 9 * g); B.size = ld3(m.geom_size + 3 * g);
+  B.vert = nullptr; B.nvert = 0; B.world = false; B.coop = false; B.radius = 0.f;
+  if (t == B2S_GEOM_SPHERE) { B.type = CVX_POINT; B.radius = B.size.x; }
+  else if (t == B2S_GEOM_CAPSULE) { B.type = CVX_SEGMENT; B.radius = B.size.x; }
+  else if (t == B2S_GEOM_BOX) B.type = CVX_BOX;
+  else if (t == B2S_GEOM_CYLINDER) B.type = CVX_CYLINDER;
+  else if (t == B2S_GEOM_ELLIPSOID) B.type = CVX_ELLIPSOID;
+  else { B.type = CVX_VERTS; B.vert = m.mesh_vert + 4 * vadr; B.nvert = vnum; B.coop = true; }
+  return B;
+}
 #ifndef CVX_TASK_MINB
 #define CVX_TASK_MINB 4
 #endif
@@ -527,13 +553,13 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
         int k0 = 0;
         if (lane == 0) k0 = atomicAdd(d.cvx_ntask, __popc(dm));
         k0 = __shfl_sync(FULL, k0, 0);
-        if (defer && !heavy) { const int k = k0 + __popc(dm & ((1u << lane) - 1u)); d.cvx_task[2 * (size_t)k] = w; d.cvx_task[2 * (size_t)k + 1] = i; }
+        if (defer && !heavy) task_record(m, d, (size_t)(k0 + __popc(dm & ((1u << lane) - 1u))), w, i, s_list[i], use_axis ? s_pidx[i] : 0);
       }
       if (hm) {
         int k0 = 0;
         if (lane == 0) k0 = atomicAdd(d.cvx_ntask + 2, __popc(hm));
         k0 = __shfl_sync(FULL, k0, 0);
-        if (heavy) { const size_t k = (size_t)d.nworld * B2S_MAX_SURVIVORS - 1 - (k0 + __popc(hm & ((1u << lane) - 1u))); d.cvx_task[2 * k] = w; d.cvx_task[2 * k + 1] = i; }
+        if (heavy) task_record(m, d, (size_t)d.nworld * B2S_MAX_SURVIVORS - 1 - (k0 + __popc(hm & ((1u << lane) - 1u))), w, i, s_list[i], s_pidx[i]);
       }
     }
     if (lane == 0) d.col_nsurv[w] = nsurv;
@@ -803,28 +829,27 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, CVX_TASK_MINB) k_conve
   (void)gw; (void)nwarp;
 #pragma unroll 1
   while (true) {
+    // one task per cursor increment: chunks of 4 / 8 consecutive cheap tasks per increment were measured slower (5.24 -> 4.88 / 4.45 M:
+    // consecutive tasks belong to one world and their costs are correlated)
     int k = 0;
     if (lane == 0) k = atomicAdd(d.cvx_ntask + 1, 1);
     k = __shfl_sync(FULL, k, 0);
     if (k >= ntask) break;
     k = k < nheavy ? cap - 1 - k : k - nheavy;      // the expensive tasks first (queued from the end of the list), then the others
-    const int w = d.cvx_task[2 * (size_t)k], i = d.cvx_task[2 * (size_t)k + 1];
+    const int4 r0 = reinterpret_cast<const int4*>(d.cvx_task)[2 * (size_t)k], r1 = reinterpret_cast<const int4*>(d.cvx_task)[2 * (size_t)k + 1];
+    const int w = r0.x, i = r0.y, g1 = r0.z & 0xffff, g2 = r0.z >> 16;
     const float* gx = d.geom_xpos + (size_t)w * m.ngeom * 3;
     const float* gm = d.geom_xmat + (size_t)w * m.ngeom * 9;
-    const unsigned key = d.col_surv[(size_t)w * B2S_MAX_SURVIVORS + i];
-    int g1 = (int)(key >> 16), g2 = (int)(key & 0xffffu);
-    if (m.geom_type[g1] > m.geom_type[g2]) { const int t = g1; g1 = g2; g2 = t; }
     const float margin = fmaxf(m.geom_margin[g1], m.geom_margin[g2]);
-    Cvx A = geom_core(m, gx, gm, g1), B = geom_core(m, gx, gm, g2);
-    A.coop = A.type == CVX_VERTS; B.coop = B.type == CVX_VERTS;
+    const Cvx A = task_core(m, gx, gm, g1, r1.x & 0xff, r1.y, r1.w & 0xffff), B = task_core(m, gx, gm, g2, r1.x >> 8, r1.z, r1.w >> 16);
     CvxStage* out = reinterpret_cast<CvxStage*>(d.cvx_stage + ((size_t)w * B2S_MAX_SURVIVORS + i) * 8);
-    const size_t pslot = use_axis ? (size_t)w * m.npair + d.col_pidx[(size_t)w * B2S_MAX_SURVIVORS + i] : 0;
+    const size_t pslot = use_axis ? (size_t)w * m.npair + r0.w : 0;
     float* axis = use_axis ? d.col_axis + pslot * 3 : nullptr;
     int work = 0;
 #ifdef COL_TIMING      // development builds only (tools/exp_col_time.py): the consumed task record becomes (iterations | EPA rounds | hull vertices, task cycles / 64 | EPA cycles / 64 << 16)
     const long long t_task = clock64();
-    const int nres = convex_pair_warp(out, margin, A, B, lane, axis, wk, d.cvx_task + 2 * (size_t)k, &work);
-    if (lane == 0) d.cvx_task[2 * (size_t)k + 1] |= (int)min((clock64() - t_task) >> 6, 65535LL);
+    const int nres = convex_pair_warp(out, margin, A, B, lane, axis, wk, d.cvx_task + 8 * (size_t)k, &work);
+    if (lane == 0) d.cvx_task[8 * (size_t)k + 1] |= (int)min((clock64() - t_task) >> 6, 65535LL);
 #else
     const int nres = convex_pair_warp(out, margin, A, B, lane, axis, wk, nullptr, &work);
 #endif

@@ -25,7 +25,7 @@ for wl in os.environ.get("WL", "asimov_toe_full_flat,go1_rough_hf").split(","):
   if "cvx_task" in pb.D.field_names and os.environ.get("TASKS", "1") == "1":
     nl, nh = int(pb.D.cvx_ntask.flatten()[0].item()), int(pb.D.cvx_ntask.flatten()[2].item()); nt = nl + nh
     if nt:
-      allrec = pb.D.cvx_task.reshape(-1, 2); rec = torch.cat([allrec[:nl], allrec[allrec.shape[0] - nh:]]).cpu().numpy(); print(f'   expensive-first tasks: {nh}'); cyc = (rec[:, 1] & 0xffff).astype(np.float64) * 64 / 1965.0
+      allrec = pb.D.cvx_task.reshape(-1, 8)[:, :2]; rec = torch.cat([allrec[:nl], allrec[allrec.shape[0] - nh:]]).cpu().numpy(); print(f'   expensive-first tasks: {nh}'); cyc = (rec[:, 1] & 0xffff).astype(np.float64) * 64 / 1965.0
       gjk = rec[:, 0] & 255; epa = (rec[:, 0] >> 8) & 255; nvt = (rec[:, 0] >> 16) & 4095; epa_us = ((rec[:, 1] >> 16) & 0xffff).astype(np.float64) * 64 / 1965.0
       print(f"   convex tasks: {nt}; per task us 50/90/99/99.9/max:", [round(float(np.percentile(cyc, q)), 1) for q in (50, 90, 99, 99.9, 100)], "sum %.1f ms" % (cyc.sum() / 1e3))
       top = np.argsort(-cyc)[:8]
