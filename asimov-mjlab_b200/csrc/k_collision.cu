@@ -402,6 +402,8 @@ DEV Cvx task_core(const ModelDev& m, const float* gx, const float* gm, int g, in
 #define CVX_TASK_MINB 4
 #endif
 #define CVX_COST_HEAVY 12      // GJK iterations (+ 64 for EPA) above which a pair's next task is queued with the expensive ones
+// PHASE 4 = PHASE 0 (everything in one kernel) of a convex model without height fields and without deferred pairs: its convex pairs
+// are all against a plane, so it is instantiated without GJK / EPA as well (Asimov 12-dof: 228 -> ~80 registers).
 template <int MAXC, bool CONVEX, int PHASE>
 __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const ModelDev m, const DataDev d) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -428,7 +430,7 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA) k_collision(const Mode
   // A1) static pair table (dynamic-dynamic and plane-dynamic pairs, already in key order): bounding spheres
   int nsurv = 0;
   constexpr bool P2 = PHASE == 2 || PHASE == 3;      // second phase
-  constexpr bool HF = PHASE != 3;                    // height-field (and in-kernel GJK / EPA) code compiled in
+  constexpr bool HF = PHASE != 3 && PHASE != 4;      // height-field (and in-kernel GJK / EPA) code compiled in
   if constexpr (P2) {       // the survivors phase 1 found
     nsurv = d.col_nsurv[w];
     for (int i = lane; i < nsurv; i += 32) s_list[i] = d.col_surv[(size_t)w * B2S_MAX_SURVIVORS + i];
@@ -860,11 +862,12 @@ __global__ void __launch_bounds__(32 * B2S_WARPS_PER_CTA, CVX_TASK_MINB) k_conve
 }
 
 #define COL_DISPATCH(M, EXPR)                                                                   \
-  if ((M).col_convex) { constexpr int MAXC = 8; constexpr bool CONVEX = true; EXPR; }           \
+  if ((M).col_convex && !(M).col_hf && !(M).col_defer) { constexpr int MAXC = 8; constexpr bool CONVEX = true; constexpr int PH = 4; EXPR; } \
+  else if ((M).col_convex) { constexpr int MAXC = 8; constexpr bool CONVEX = true; constexpr int PH = 0; EXPR; }           \
   else switch ((M).col_maxc) {                                                                  \
-    case 2: { constexpr int MAXC = 2; constexpr bool CONVEX = false; EXPR; } break;             \
-    case 4: { constexpr int MAXC = 4; constexpr bool CONVEX = false; EXPR; } break;             \
-    default: { constexpr int MAXC = 8; constexpr bool CONVEX = false; EXPR; } break;            \
+    case 2: { constexpr int MAXC = 2; constexpr bool CONVEX = false; constexpr int PH = 0; EXPR; } break;             \
+    case 4: { constexpr int MAXC = 4; constexpr bool CONVEX = false; constexpr int PH = 0; EXPR; } break;             \
+    default: { constexpr int MAXC = 8; constexpr bool CONVEX = false; constexpr int PH = 0; EXPR; } break;            \
   }
 void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
   const int grid = (d.nworld + B2S_WARPS_PER_CTA - 1) / B2S_WARPS_PER_CTA;
@@ -876,7 +879,7 @@ void launch_collision(const ModelDev& m, const DataDev& d, cudaStream_t st) {
     b2s_count_launch(); b2s_count_launch(); b2s_count_launch();
     return;
   }
-  COL_DISPATCH(m, (k_collision<MAXC, CONVEX, 0><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
+  COL_DISPATCH(m, (k_collision<MAXC, CONVEX, PH><<<grid, 32 * B2S_WARPS_PER_CTA, smem_collision(m), st>>>(m, d)));
   b2s_count_launch();
 }
 size_t smem_collision(const ModelDev& m) {
@@ -884,6 +887,6 @@ size_t smem_collision(const ModelDev& m) {
 }
 const void* fn_collision(const ModelDev& m) {
   const void* f = nullptr;
-  COL_DISPATCH(m, (f = (const void*)k_collision<MAXC, CONVEX, 0>));
+  COL_DISPATCH(m, (f = (const void*)k_collision<MAXC, CONVEX, PH>));
   return f;
 }

@@ -46,9 +46,9 @@ def alg_bytes(m, friction_geoms):
   w = m.nq + 3 * m.nv + 1 + m.nsensordata + (3 + 4 + 3 + 6) * nb + 12 * m.nsite
   return 4 * (r + w + 3 * friction_geoms)
 # DRAM traffic of one sub-step (the 7 stage kernels + the solver's second launch), dram__bytes_read.sum + dram__bytes_write.sum from
-# the `ncu --set full` capture profiles/step_r2f_metrics.txt (G1-flat, 4096 worlds, upright regime): 144.6 MB read + 7.4 MB written.
+# the `ncu --set full` capture profiles/step_r2g_metrics.txt (G1-flat, 4096 worlds, upright regime): 144.6 MB read + 7.4 MB written.
 # NOT measured live (ncu cannot run inside the timed region): the JSON names the file it comes from in `traffic_from_profile`.
-NCU_TRAFFIC = {("g1_flat", 4096): (151900000, "profiles/step_r2f_metrics.txt (ncu --set full, sum over the 8 launches of one sub-step, upright regime)")}
+NCU_TRAFFIC = {("g1_flat", 4096): (151800000, "profiles/step_r2g_metrics.txt (ncu --set full, sum over the 8 launches of one sub-step, upright regime)")}
 DECIMATION = 4
 RESET_PERIOD_STEPS = 250            # reset every 1000 sub-steps, forward() inside the timed region
 
